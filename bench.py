@@ -1,0 +1,403 @@
+#!/usr/bin/env python
+"""bench.py -- train images/sec of the cifar10cnn.py CNN step on N B200s (BASELINE.json metric).
+
+  python bench.py --gpus N --steps K --warmup W            (N>1: launched under torchrun)
+  python bench.py --impl reference ...                      (CPU port of the reference path)
+
+One "step" = one `mon_sess.run([train_op, loss])` (cifar10cnn.py:230) per worker: crop/cast,
+forward, backward, gradient exchange, SGD apply on one batch of 128 synthetic CIFAR records.
+Prints ONE JSON line on rank 0.  See DESIGN.md "Measurement" for every field.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "train images/sec (CIFAR-10 CNN, bs128/GPU)"
+FLOP_PER_IMAGE = 105_295_104          # 2 x train MACs, base model, 24x24 crop
+ACT_ELEMS_PER_IMAGE = 352_542         # layer-boundary activation traffic model
+PARAM_BYTES = 4_273_192
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"hbm_gbs": d["hbm_gbs"], "tflops_burst": d["bf16_tflops"],
+                "tflops_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]), "source": "measured"}
+    return {"hbm_gbs": 6650.0, "tflops_burst": 1590.0, "tflops_sustained": 1400.0, "source": "fallback"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "50"],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.06)
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, smax, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            parts = [x.strip() for x in line.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0])); smax.append(float(parts[1])); power.append(float(parts[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, parts[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        os.unlink(self.f.name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def synthetic_batch(rng, batch):
+    """CIFAR-record-shaped bytes (cifar10cnn.py:57-62): uint8 [B,3,32,32] uniform 0..255, int32 labels 0..9."""
+    import numpy as np
+    return (rng.integers(0, 256, (batch, 3, 32, 32), dtype=np.uint8),
+            rng.integers(0, 10, (batch,)).astype(np.int32))
+
+
+def cpu_baseline(batch, budget_s, threads=None):
+    """The reference's CPU path restated in torch-CPU fp32 (oracle/ref_torch.py, kind 'port';
+    TensorFlow 1.x itself is not installable here) timed on this host's cores."""
+    import numpy as np
+    import torch
+    from oracle import ref_numpy as rn, ref_torch as rt
+    threads = threads or os.cpu_count()
+    tr = rt.CpuTrainer(rn.init_params(0), lr=0.1, threads=threads)
+    rng = np.random.default_rng(1234)
+    pool = [synthetic_batch(rng, batch) for _ in range(4)]
+    tr.step(*pool[0])
+    tr.reset()
+    n, t0 = 0, time.perf_counter()
+    while True:
+        tr.step(*pool[n % 4])
+        tr.reset()                                             # raw-byte inputs diverge: fresh weights
+        n += 1
+        el = time.perf_counter() - t0
+        if el >= budget_s or n >= 2000:
+            break
+    return {"value": batch * n / el, "unit": "images/s", "cores": threads, "kind": "port",
+            "sample": f"{n} steps of batch {batch} in {el:.1f} s (torch-CPU fp32 restatement of cifar10cnn.py:94-176, "
+                      f"{threads} threads, {os.cpu_count()} logical cores)"}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import numpy as np
+    import torch
+    from oracle import ref_numpy as rn, ref_torch as rt
+    threads = os.cpu_count()
+    tr = rt.CpuTrainer(rn.init_params(0), lr=0.1, threads=threads)
+    rng = np.random.default_rng(1234)
+    pool = [synthetic_batch(rng, args.batch) for _ in range(4)]
+    steps = min(args.steps, 400)
+    for i in range(min(args.warmup, 5)):
+        tr.step(*pool[i % 4])
+        tr.reset()
+    t0 = time.perf_counter()
+    for i in range(steps):
+        tr.step(*pool[i % 4])
+        tr.reset()
+    el = time.perf_counter() - t0
+    v = args.batch * steps / el
+    sample = (f"{steps} steps of batch {args.batch}, single process, {threads} threads; the reference's own "
+              f"TensorFlow-1.x runtime is unavailable on this box, this is the torch-CPU restatement")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "images/s", "n_gpus": args.gpus,
+        "steps": steps, "warmup": min(args.warmup, 5), "ms_per_step": 1e3 * el / steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(args), "batch_per_gpu": args.batch, "host_threads": threads},
+        "cpu_baseline": {"value": v, "unit": "images/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def workload_name(args):
+    return (f"cifar10cnn.py CNN train step (conv5x5x64-pool-conv5x5x64-pool-fc384-fc192-fc10, softmax-xent, "
+            f"SGD lr 0.1), 32x32x3 uint8 records centre-cropped to 24x24, batch {args.batch}/GPU")
+
+
+# algorithmic work per launch site: ("tensor", MACs per image) or ("hbm", bytes per image, fixed bytes)
+def site_work(mode):
+    act = 4 if mode == "fp32" else 2
+    c1, p1, c2, p2 = 36864, 9216, 9216, 2304
+    return {
+        "conv1_fwd": ("tensor", 2_764_800), "conv1_wgrad": ("tensor", 2_764_800),
+        "conv2_fwd": ("tensor", 14_745_600), "conv2_dgrad": ("tensor", 14_745_600),
+        "conv2_wgrad": ("tensor", 14_745_600),
+        "full1_fwd": ("tensor", 884_736), "full1_bwd": ("tensor", 2 * 884_736),
+        "full2_fwd": ("tensor", 73_728), "full2_bwd": ("tensor", 2 * 73_728),
+        "full3_fwd": ("tensor", 1_920), "full3_bwd": ("tensor", 2 * 1_920),
+        "crop_cast": ("hbm", 3072 + 1728 * act, 0),
+        "pool1_fwd": ("hbm", c1 * act + p1 * act + p1, 0), "pool2_fwd": ("hbm", c2 * act + p2 * act + p2, 0),
+        "pool1_bwd": ("hbm", p1 * act + p1 + c1 * act * 2, 0), "pool2_bwd": ("hbm", p2 * act + p2 + c2 * act * 2, 0),
+        "head": ("hbm", 10 * 4 * 2 + 4 + 4, 0), "conv2_dgrad_prep": ("hbm", 0, 2 * 102400 * 4),
+        "sgd_apply": ("hbm", 0, 3 * PARAM_BYTES),
+    }
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=300)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=128)
+    ap.add_argument("--mode", default=os.environ.get("B200CNN_MODE", "auto"), choices=["auto", "fp32", "bf16"])
+    ap.add_argument("--reduce", default="sum", choices=["sum", "mean"])
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--sites-json", default=None, help="also write the per-site timing table here")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import b200cnn
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl b200 needs a CUDA device (no CPU fallback)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if args.gpus != world and rank == 0:
+        print(f"warning: --gpus {args.gpus} but WORLD_SIZE {world}; reporting n_gpus={world}", file=sys.stderr)
+    mode = b200cnn.DEFAULT_MODE if args.mode == "auto" else args.mode
+    B, K, W = args.batch, args.steps, args.warmup
+    lr = 0.1
+    peaks = load_peaks()
+
+    eng = b200cnn.TrainStepEngine(batch=B, mode=mode, device=local)
+    eng.init_params(0)
+    params0 = eng.params.clone()
+    ex = b200cnn.GradientExchange(reduce=args.reduce)
+    ex.broadcast_params_(eng.params)
+
+    rng = np.random.default_rng(1234 + rank)
+    POOL, RING = 16, 8
+    pool = []
+    for _ in range(POOL):
+        i, l = synthetic_batch(rng, B)
+        pool.append((torch.as_tensor(i).cuda(), torch.as_tensor(l).cuda()))
+    host_ring = []
+    for _ in range(RING):
+        i, l = synthetic_batch(rng, B)
+        host_ring.append((torch.as_tensor(i).pin_memory(), torch.as_tensor(l).pin_memory(),
+                          torch.zeros(1).pin_memory()))
+    s_img = torch.empty_like(pool[0][0])
+    s_lab = torch.empty_like(pool[0][1])
+
+    def device_step():
+        if world == 1:
+            eng.train_step(s_img, s_lab, lr)
+        else:
+            eng.forward(s_img, s_lab)
+            eng.backward()
+            ex.allreduce_(eng.grads)
+            eng.sgd_apply(lr, ex.grad_scale)
+
+    def host_step(img, lab, out):
+        def fn():
+            if world == 1:
+                eng.train_step_host(img, lab, lr, loss_out=out, sync=False)
+            else:
+                s_img.copy_(img, non_blocking=True)
+                s_lab.copy_(lab, non_blocking=True)
+                eng.forward(s_img, s_lab)
+                eng.backward()
+                ex.allreduce_(eng.grads)
+                eng.sgd_apply(lr, ex.grad_scale)
+                out.copy_(eng.loss(), non_blocking=True)
+        return fn
+
+    s_img.copy_(pool[0][0]); s_lab.copy_(pool[0][1])
+    graph = eng.capture(device_step)
+    host_graphs = [eng.capture(host_step(*h)) for h in host_ring]
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    def reset():
+        # synthetic raw-byte inputs with lr 0.1 blow the weights up within a few steps;
+        # restoring them keeps every timed step numerically ordinary (no inf/nan fast paths)
+        eng.params.copy_(params0)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- warm-up --------------------------------------------------------------------------
+    for i in range(W):
+        s_img.copy_(pool[i % POOL][0]); s_lab.copy_(pool[i % POOL][1])
+        graph.replay()
+        host_graphs[i % RING].replay()
+        if i % 4 == 3:
+            reset()
+    reset()
+    barrier()
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    # ---- timed region 1: device-resident inputs, L2 flushed between steps -------------------------
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    barrier()
+    for i in range(K):
+        flush_buf.zero_()                                   # untimed: evicts weights/activations from the 126 MB L2
+        if i % 4 == 0:
+            reset()                                         # untimed
+        a, b = ev[i]
+        a.record()
+        s_img.copy_(pool[i % POOL][0]); s_lab.copy_(pool[i % POOL][1])
+        graph.replay()
+        b.record()
+    barrier()
+    ms_cold = sum(a.elapsed_time(b) for a, b in ev)
+
+    # ---- timed region 2: same steps back to back, L2 warm (extra information) ---------------------
+    reset()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for i in range(K):
+        s_img.copy_(pool[i % POOL][0]); s_lab.copy_(pool[i % POOL][1])
+        graph.replay()
+    e1.record()
+    barrier()
+    ms_hot = e0.elapsed_time(e1)
+
+    # ---- timed region 3: end to end through the public host-buffer call ---------------------------
+    reset()
+    barrier()
+    e0.record()
+    loss_seen = 0.0
+    for i in range(K):
+        host_graphs[i % RING].replay()                      # H2D records+labels, step, D2H loss
+        torch.cuda.current_stream().synchronize()           # the reference loop returns the loss every step (:230)
+        loss_seen = float(host_ring[i % RING][2][0])
+        if i % 4 == 3:
+            eng.params.copy_(params0)
+    e1.record()
+    barrier()
+    ms_e2e = e0.elapsed_time(e1)
+    clocks = sampler.stop() if sampler else None
+
+    # ---- live per-site timing for the roofline (eager, CUDA events between launch sites) --------
+    reset()
+    n_prof = 10
+    acc = {}
+    for i in range(n_prof + 2):
+        flush_buf.zero_()
+        sites = eng.profile_step(pool[i % POOL][0], pool[i % POOL][1], lr)
+        if i >= 2:
+            for n, ms in sites:
+                acc[n] = acc.get(n, 0.0) + ms / n_prof
+        if i % 4 == 3:
+            reset()
+    work = site_work(mode)
+    table = []
+    for n, ms in acc.items():
+        w = work.get(n)
+        row = {"site": n, "ms": ms}
+        if w and w[0] == "tensor":
+            row.update(bound="tensor", tflops=2 * w[1] * B / (ms * 1e-3) / 1e12)
+        elif w:
+            row.update(bound="hbm", gbs=(w[1] * B + w[2]) / (ms * 1e-3) / 1e9)
+        table.append(row)
+    table.sort(key=lambda r: -r["ms"])
+    dom = table[0]
+    if dom.get("bound") == "tensor":
+        roof = {"bound": "tensor", "kernel": dom["site"], "achieved": dom["tflops"], "peak": peaks["tflops_burst"],
+                "unit": "TFLOP/s", "frac": dom["tflops"] / peaks["tflops_burst"], "traffic": None,
+                "peak_source": peaks["source"] + " (burst: kernel timed alone)", "kernel_ms": dom["ms"]}
+    else:
+        roof = {"bound": "hbm", "kernel": dom["site"], "achieved": dom.get("gbs"), "peak": peaks["hbm_gbs"],
+                "unit": "GB/s", "frac": (dom.get("gbs") or 0) / peaks["hbm_gbs"], "traffic": None,
+                "peak_source": peaks["source"], "kernel_ms": dom["ms"]}
+
+    # max over ranks
+    t = torch.tensor([ms_cold, ms_hot, ms_e2e], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        assert ex.replicas_identical(eng.params), "replicas diverged"
+    ms_cold, ms_hot, ms_e2e = (float(x) for x in t.cpu())
+
+    if rank == 0:
+        imgs = B * world * K
+        step_flops = FLOP_PER_IMAGE * B
+        act_b = 4 if mode == "fp32" else 2
+        step_bytes = ACT_ELEMS_PER_IMAGE * act_b * B + 3 * PARAM_BYTES
+        ms_step = ms_cold / K
+        out = {
+            "metric": METRIC, "value": imgs / (ms_cold * 1e-3), "unit": "images/s", "n_gpus": world, "steps": K,
+            "warmup": W, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32" if mode == "fp32" else "bf16", "data": "synthetic",
+            "config": {"workload": workload_name(args), "batch_per_gpu": B, "global_batch": B * world,
+                       "mode": mode, "parallelism": f"dp{world}", "reduce": args.reduce,
+                       "l2": "flushed between timed steps (256 MiB memset, untimed); per-step CUDA events summed",
+                       "cuda_graph": True},
+            "value_hot_l2": imgs / (ms_hot * 1e-3),
+            "clocks": clocks,
+            "e2e": {"value": imgs / (ms_e2e * 1e-3), "unit": "images/s",
+                    "h2d_bytes_per_step": B * 3072 + B * 4, "d2h_bytes_per_step": 4,
+                    "note": "pinned host records -> H2D -> step -> D2H loss, stream-synchronised and loss read "
+                            "every step; L2 not flushed (inputs arrive from the host each step)",
+                    "last_loss": loss_seen},
+            "gpu_launches": eng.launches_per_step * K,
+            "roofline": roof,
+            "step_roofline": {"tensor_frac_of_sustained": step_flops / (ms_step * 1e-3) / 1e12 / peaks["tflops_sustained"],
+                              "hbm_frac_layer_boundary_model": step_bytes / (ms_step * 1e-3) / 1e9 / peaks["hbm_gbs"],
+                              "flop_per_step": step_flops, "model_bytes_per_step": step_bytes},
+            "sites": [{k: (round(v, 5) if isinstance(v, float) else v) for k, v in r.items()} for r in table[:8]],
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            out["cpu_baseline"] = cpu_baseline(B, args.cpu_seconds)
+        if args.sites_json:
+            os.makedirs(os.path.dirname(os.path.abspath(args.sites_json)), exist_ok=True)
+            json.dump({"mode": mode, "batch": B, "sites": table, "ms_per_step_graph_cold": ms_step,
+                       "ms_per_step_graph_hot": ms_hot / K}, open(args.sites_json, "w"), indent=1)
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

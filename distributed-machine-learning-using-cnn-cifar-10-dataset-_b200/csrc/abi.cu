@@ -1,0 +1,400 @@
+// C ABI of include/b200cnn.h: the opaque handle, workspace carving and the orchestration of
+// one training step (cifar10cnn.py:230) out of the kernels in f32_kernels.cu / bf16_*.cu.
+#include <stdarg.h>
+#include <string.h>
+
+#include <new>
+#include <string>
+#include <vector>
+
+#include <algorithm>
+
+#include "launch.h"
+
+namespace b200 {
+
+static thread_local char g_err[512] = "";
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+struct Tensor {
+  std::string name;
+  int64_t elems;
+  int32_t esize;
+  int64_t offset;   // bytes into the workspace
+};
+
+}  // namespace b200
+
+using namespace b200;
+
+struct b200_model {
+  b200_config cfg;
+  int h1, w1, h2, w2, flat;             // pool1 / pool2 spatial sizes and the FC1 fan-in (:127)
+  int64_t p_off[B200_NUM_PARAMS], p_size[B200_NUM_PARAMS], p_total;
+  float* params = nullptr;
+  float* grads = nullptr;
+  char* ws = nullptr;
+  int64_t ws_bytes = 0;
+  std::vector<Tensor> tensors;
+  bool forward_done = false;
+  // per-launch-site timing (b200_profile_step): events are created lazily, once
+  bool profiling = false;
+  std::vector<std::string> site_names;
+  std::vector<cudaEvent_t> site_events;
+  int site_cursor = 0;
+
+  int64_t add(const char* name, int64_t elems, int32_t esize) {
+    Tensor t{name, elems, esize, ws_bytes};
+    tensors.push_back(t);
+    ws_bytes += round_up(elems * esize, 256);
+    return t.offset;
+  }
+  const Tensor* find(const char* name) const {
+    for (auto& t : tensors)
+      if (t.name == name) return &t;
+    return nullptr;
+  }
+  template <class T>
+  T* ptr(const char* name) const {
+    const Tensor* t = find(name);
+    return t ? reinterpret_cast<T*>(ws + t->offset) : nullptr;
+  }
+  float* P(int i) const { return params + p_off[i]; }
+  float* G(int i) const { return grads + p_off[i]; }
+};
+
+enum { P_W1 = 0, P_B1, P_W2, P_B2, P_FW1, P_FB1, P_FW2, P_FB2, P_FW3, P_FB3 };
+
+extern "C" {
+
+const char* b200_last_error(void) { return g_err; }
+int b200_version(void) { return 100; }
+
+int b200_create(const b200_config* c, b200_handle* out) {
+  B200_REQUIRE(c && out, "b200_create: null argument");
+  B200_REQUIRE(c->batch > 0 && c->batch <= (1 << 16), "b200_create: batch must be in 1..65536");
+  B200_REQUIRE(c->crop_h >= 4 && c->crop_w >= 4 && c->crop_h <= c->img_h && c->crop_w <= c->img_w,
+               "b200_create: crop %dx%d must fit the %dx%d record and be >= 4", c->crop_h, c->crop_w,
+               c->img_h, c->img_w);
+  B200_REQUIRE(c->c_in > 0 && c->c1 > 0 && c->c2 > 0 && c->f1 > 0 && c->f2 > 0, "b200_create: bad widths");
+  B200_REQUIRE(c->c1 % 4 == 0 && c->c2 % 4 == 0 && c->f1 % 4 == 0 && c->f2 % 4 == 0,
+               "b200_create: channel / FC widths must be multiples of 4");
+  B200_REQUIRE(c->n_cls > 0 && c->n_cls <= 16, "b200_create: n_cls must be in 1..16");
+  B200_REQUIRE(c->mode == B200_MODE_FP32, "b200_create: mode %d not available in this build", c->mode);
+  b200_model* h = new (std::nothrow) b200_model();
+  B200_REQUIRE(h, "b200_create: out of host memory");
+  h->cfg = *c;
+  h->h1 = (c->crop_h + 1) / 2; h->w1 = (c->crop_w + 1) / 2;
+  h->h2 = (h->h1 + 1) / 2;     h->w2 = (h->w1 + 1) / 2;
+  h->flat = h->h2 * h->w2 * c->c2;
+  const int64_t sz[B200_NUM_PARAMS] = {25ll * c->c_in * c->c1, c->c1, 25ll * c->c1 * c->c2, c->c2,
+                                       (int64_t)h->flat * c->f1, c->f1, (int64_t)c->f1 * c->f2, c->f2,
+                                       (int64_t)c->f2 * c->n_cls, c->n_cls};
+  int64_t off = 0;
+  for (int i = 0; i < B200_NUM_PARAMS; ++i) {
+    h->p_off[i] = off; h->p_size[i] = sz[i];
+    off += round_up(sz[i], 64);
+  }
+  h->p_total = off;
+
+  const int64_t B = c->batch;
+  const int64_t n_x = B * c->crop_h * c->crop_w * c->c_in, n_c1 = B * c->crop_h * c->crop_w * c->c1,
+                n_p1 = B * h->h1 * h->w1 * c->c1, n_c2 = B * h->h1 * h->w1 * c->c2,
+                n_p2 = B * h->flat;
+  h->add("x", n_x, 4);
+  h->add("conv1", n_c1, 4);   h->add("pool1", n_p1, 4);  h->add("arg1", n_p1, 1);
+  h->add("conv2", n_c2, 4);   h->add("pool2", n_p2, 4);  h->add("arg2", n_p2, 1);
+  h->add("full1", B * c->f1, 4); h->add("full2", B * c->f2, 4); h->add("logits", B * c->n_cls, 4);
+  h->add("dlogits", B * c->n_cls, 4); h->add("dfull2", B * c->f2, 4); h->add("dfull1", B * c->f1, 4);
+  h->add("dpool2", n_p2, 4);  h->add("dconv2", n_c2, 4);
+  h->add("dpool1", n_p1, 4);  h->add("dconv1", n_c1, 4);
+  h->add("wrot", 25ll * c->c1 * c->c2, 4);
+  int64_t scratch = conv5x5_wgrad_scratch_bytes(c->batch, c->crop_h, c->crop_w, c->c_in, c->c1);
+  scratch = std::max(scratch, conv5x5_wgrad_scratch_bytes(c->batch, h->h1, h->w1, c->c1, c->c2));
+  scratch = std::max(scratch, colsum_scratch_bytes(c->batch, std::max(c->f1, std::max(c->f2, c->n_cls))));
+  h->add("scratch", scratch, 1);
+  h->add("loss", 1, 4); h->add("n_correct", 1, 4); h->add("n_bad", 1, 4); h->add("pred", B, 4);
+  h->add("stage_images", B * c->c_in * c->img_h * c->img_w, 1);
+  h->add("stage_labels", B, 4);
+  *out = h;
+  return B200_OK;
+}
+
+int b200_destroy(b200_handle h) {
+  if (h)
+    for (cudaEvent_t ev : h->site_events) cudaEventDestroy(ev);
+  delete h;
+  return B200_OK;
+}
+
+int b200_param_layout(b200_handle h, int64_t* offsets, int64_t* sizes, int64_t* total) {
+  B200_REQUIRE(h, "null handle");
+  for (int i = 0; i < B200_NUM_PARAMS; ++i) {
+    if (offsets) offsets[i] = h->p_off[i];
+    if (sizes) sizes[i] = h->p_size[i];
+  }
+  if (total) *total = h->p_total;
+  return B200_OK;
+}
+int b200_bind_params(b200_handle h, float* p) {
+  B200_REQUIRE(h && p && ((uintptr_t)p & 255) == 0, "bind_params: need a 256-byte aligned device pointer");
+  h->params = p;
+  return B200_OK;
+}
+int b200_bind_grads(b200_handle h, float* g) {
+  B200_REQUIRE(h && g && ((uintptr_t)g & 255) == 0, "bind_grads: need a 256-byte aligned device pointer");
+  h->grads = g;
+  return B200_OK;
+}
+int b200_workspace_bytes(b200_handle h, int64_t* n) {
+  B200_REQUIRE(h && n, "null argument");
+  *n = h->ws_bytes;
+  return B200_OK;
+}
+int b200_bind_workspace(b200_handle h, void* ws, int64_t nbytes) {
+  B200_REQUIRE(h && ws && ((uintptr_t)ws & 255) == 0, "bind_workspace: need a 256-byte aligned device pointer");
+  B200_REQUIRE(nbytes >= h->ws_bytes, "bind_workspace: %lld bytes given, %lld needed", (long long)nbytes,
+               (long long)h->ws_bytes);
+  h->ws = (char*)ws;
+  h->forward_done = false;
+  return B200_OK;
+}
+
+#define B200_READY(h)                                                                              \
+  do {                                                                                             \
+    B200_REQUIRE(h, "null handle");                                                                \
+    if (!(h)->params || !(h)->grads || !(h)->ws) {                                                 \
+      set_error("handle not ready: bind params, grads and workspace first");                       \
+      return B200_E_STATE;                                                                         \
+    }                                                                                              \
+  } while (0)
+#define TRY(expr) do { int rc__ = (expr); if (rc__) return rc__; } while (0)
+
+// A launch site: one logical kernel group of the step.  When b200_profile_step is active an
+// event is recorded on the stream before each site (and one after the last).
+static int site_mark(b200_model* h, const char* name, cudaStream_t st) {
+  if (!h->profiling) return B200_OK;
+  int i = h->site_cursor++;
+  if ((int)h->site_events.size() <= i) {
+    cudaEvent_t ev;
+    B200_CUDA_TRY(cudaEventCreate(&ev));
+    h->site_events.push_back(ev);
+    h->site_names.push_back(name);
+  } else {
+    h->site_names[i] = name;
+  }
+  B200_CUDA_TRY(cudaEventRecord(h->site_events[i], st));
+  return B200_OK;
+}
+#define SITE(name, expr) do { TRY(site_mark(h, name, st)); TRY(expr); } while (0)
+
+int b200_forward(b200_handle h, const uint8_t* images, const int32_t* labels, void* stream) {
+  B200_READY(h);
+  B200_REQUIRE(images && labels, "forward: null input");
+  cudaStream_t st = (cudaStream_t)stream;
+  const b200_config& c = h->cfg;
+  float* x = h->ptr<float>("x");
+  float *conv1 = h->ptr<float>("conv1"), *pool1 = h->ptr<float>("pool1");
+  float *conv2 = h->ptr<float>("conv2"), *pool2 = h->ptr<float>("pool2");
+  float *full1 = h->ptr<float>("full1"), *full2 = h->ptr<float>("full2"), *logits = h->ptr<float>("logits");
+  SITE("crop_cast", crop_cast_f32(images, x, c.batch, c.img_h, c.img_w, c.crop_h, c.crop_w, c.c_in, st));
+  SITE("conv1_fwd", conv5x5_fwd_f32(x, h->P(P_W1), h->P(P_B1), conv1, c.batch, c.crop_h, c.crop_w, c.c_in, c.c1, 1, st));
+  SITE("pool1_fwd", maxpool_fwd_f32(conv1, pool1, h->ptr<uint8_t>("arg1"), c.batch, c.crop_h, c.crop_w, c.c1, st));
+  SITE("conv2_fwd", conv5x5_fwd_f32(pool1, h->P(P_W2), h->P(P_B2), conv2, c.batch, h->h1, h->w1, c.c1, c.c2, 1, st));
+  SITE("pool2_fwd", maxpool_fwd_f32(conv2, pool2, h->ptr<uint8_t>("arg2"), c.batch, h->h1, h->w1, c.c2, st));
+  SITE("full1_fwd", fc_fwd_f32(pool2, h->P(P_FW1), h->P(P_FB1), full1, c.batch, h->flat, c.f1, 1, st));
+  SITE("full2_fwd", fc_fwd_f32(full1, h->P(P_FW2), h->P(P_FB2), full2, c.batch, c.f1, c.f2, 1, st));
+  SITE("full3_fwd", fc_fwd_f32(full2, h->P(P_FW3), h->P(P_FB3), logits, c.batch, c.f2, c.n_cls, 1, st));
+  SITE("head", head_f32(logits, labels, h->ptr<float>("loss"), h->ptr<float>("dlogits"), h->ptr<int32_t>("pred"),
+               h->ptr<int32_t>("n_correct"), h->ptr<int32_t>("n_bad"), c.batch, c.n_cls, st));
+  h->forward_done = true;
+  return B200_OK;
+}
+
+int b200_backward(b200_handle h, void* stream) {
+  B200_READY(h);
+  if (!h->forward_done) {
+    set_error("backward: call b200_forward first");
+    return B200_E_STATE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  const b200_config& c = h->cfg;
+  float* scratch = h->ptr<float>("scratch");
+  float *dlogits = h->ptr<float>("dlogits"), *dfull2 = h->ptr<float>("dfull2"), *dfull1 = h->ptr<float>("dfull1");
+  float *dpool2 = h->ptr<float>("dpool2"), *dconv2 = h->ptr<float>("dconv2");
+  float *dpool1 = h->ptr<float>("dpool1"), *dconv1 = h->ptr<float>("dconv1");
+  SITE("full3_bwd", fc_bwd_f32(h->ptr<float>("full2"), h->P(P_FW3), dlogits, dfull2, h->G(P_FW3), h->G(P_FB3), scratch,
+                 c.batch, c.f2, c.n_cls, 1, st));
+  SITE("full2_bwd", fc_bwd_f32(h->ptr<float>("full1"), h->P(P_FW2), dfull2, dfull1, h->G(P_FW2), h->G(P_FB2), scratch,
+                 c.batch, c.f1, c.f2, 1, st));
+  SITE("full1_bwd", fc_bwd_f32(h->ptr<float>("pool2"), h->P(P_FW1), dfull1, dpool2, h->G(P_FW1), h->G(P_FB1), scratch,
+                 c.batch, h->flat, c.f1, 0, st));
+  SITE("pool2_bwd", maxpool_bwd_f32(dpool2, h->ptr<uint8_t>("arg2"), h->ptr<float>("conv2"), dconv2, c.batch, h->h1, h->w1,
+                      c.c2, 1, st));
+  SITE("conv2_wgrad", conv5x5_wgrad_f32(h->ptr<float>("pool1"), dconv2, h->G(P_W2), h->G(P_B2), scratch, c.batch, h->h1, h->w1,
+                        c.c1, c.c2, st));
+  SITE("conv2_dgrad_prep", conv5x5_rot180_f32(h->P(P_W2), h->ptr<float>("wrot"), c.c1, c.c2, st));
+  SITE("conv2_dgrad", conv5x5_fwd_f32(dconv2, h->ptr<float>("wrot"), nullptr, dpool1, c.batch, h->h1, h->w1, c.c2, c.c1, 0, st));
+  SITE("pool1_bwd", maxpool_bwd_f32(dpool1, h->ptr<uint8_t>("arg1"), h->ptr<float>("conv1"), dconv1, c.batch, c.crop_h,
+                      c.crop_w, c.c1, 1, st));
+  SITE("conv1_wgrad", conv5x5_wgrad_f32(h->ptr<float>("x"), dconv1, h->G(P_W1), h->G(P_B1), scratch, c.batch, c.crop_h,
+                        c.crop_w, c.c_in, c.c1, st));
+  return B200_OK;
+}
+
+int b200_sgd_apply(b200_handle h, float lr, float grad_scale, void* stream) {
+  B200_READY(h);
+  cudaStream_t st = (cudaStream_t)stream;
+  SITE("sgd_apply", sgd_apply_f32(h->params, h->grads, h->p_total, lr, grad_scale, st));
+  return B200_OK;
+}
+
+int b200_train_step(b200_handle h, const uint8_t* images, const int32_t* labels, float lr, void* stream) {
+  TRY(b200_forward(h, images, labels, stream));
+  TRY(b200_backward(h, stream));
+  return b200_sgd_apply(h, lr, 1.f, stream);
+}
+
+int b200_train_step_host(b200_handle h, const uint8_t* images_host, const int32_t* labels_host, float lr,
+                         float* loss_host, void* stream) {
+  B200_READY(h);
+  B200_REQUIRE(images_host && labels_host && loss_host, "train_step_host: null argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  const b200_config& c = h->cfg;
+  uint8_t* si = h->ptr<uint8_t>("stage_images");
+  int32_t* sl = h->ptr<int32_t>("stage_labels");
+  B200_CUDA_TRY(cudaMemcpyAsync(si, images_host, (size_t)c.batch * c.c_in * c.img_h * c.img_w,
+                                cudaMemcpyHostToDevice, st));
+  B200_CUDA_TRY(cudaMemcpyAsync(sl, labels_host, (size_t)c.batch * 4, cudaMemcpyHostToDevice, st));
+  TRY(b200_train_step(h, si, sl, lr, stream));
+  B200_CUDA_TRY(cudaMemcpyAsync(loss_host, h->ptr<float>("loss"), 4, cudaMemcpyDeviceToHost, st));
+  return B200_OK;
+}
+
+int b200_profile_step(b200_handle h, const uint8_t* images, const int32_t* labels, float lr, void* stream,
+                      float* ms_per_site, int32_t max_sites, int32_t* n_sites) {
+  B200_READY(h);
+  B200_REQUIRE(ms_per_site && n_sites && max_sites > 0, "profile_step: null argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  h->profiling = true;
+  h->site_cursor = 0;
+  int rc = b200_train_step(h, images, labels, lr, stream);
+  if (!rc) rc = site_mark(h, "end", st);
+  h->profiling = false;
+  if (rc) return rc;
+  B200_CUDA_TRY(cudaStreamSynchronize(st));
+  int n = h->site_cursor - 1;
+  B200_REQUIRE(n <= max_sites, "profile_step: %d sites, room for %d", n, max_sites);
+  for (int i = 0; i < n; ++i)
+    B200_CUDA_TRY(cudaEventElapsedTime(&ms_per_site[i], h->site_events[i], h->site_events[i + 1]));
+  *n_sites = n;
+  return B200_OK;
+}
+const char* b200_site_name(b200_handle h, int32_t i) {
+  if (!h || i < 0 || i >= (int)h->site_names.size()) return "";
+  return h->site_names[i].c_str();
+}
+
+int b200_result_ptrs(b200_handle h, float** logits, float** loss, int32_t** n_correct, int32_t** pred) {
+  B200_REQUIRE(h && h->ws, "result_ptrs: bind a workspace first");
+  if (logits) *logits = h->ptr<float>("logits");
+  if (loss) *loss = h->ptr<float>("loss");
+  if (n_correct) *n_correct = h->ptr<int32_t>("n_correct");
+  if (pred) *pred = h->ptr<int32_t>("pred");
+  return B200_OK;
+}
+
+int b200_tensor_ptr(b200_handle h, const char* name, void** ptr, int64_t* nbytes, int32_t* esize) {
+  B200_REQUIRE(h && h->ws && name, "tensor_ptr: bind a workspace first");
+  const Tensor* t = h->find(name);
+  B200_REQUIRE(t, "tensor_ptr: no tensor named '%s'", name);
+  if (ptr) *ptr = h->ws + t->offset;
+  if (nbytes) *nbytes = t->elems * t->esize;
+  if (esize) *esize = t->esize;
+  return B200_OK;
+}
+
+int b200_launches_per_step(b200_handle h, int32_t* n) {
+  B200_REQUIRE(h && n, "null argument");
+  // forward 9; fc_bwd 3 x (dw, colsum x2, dx); pool bwd x2; conv wgrad 2 x (gemm, reduce, colsum x2);
+  // dgrad (rot180 + gemm); sgd
+  *n = 9 + 12 + 2 + 8 + 2 + 1;
+  return B200_OK;
+}
+
+// ---- per-op entry points --------------------------------------------------------------------
+int b200_crop_cast_f32(const uint8_t* images, float* out, int32_t batch, int32_t img_h, int32_t img_w,
+                       int32_t crop_h, int32_t crop_w, int32_t c_in, void* stream) {
+  B200_REQUIRE(images && out, "null pointer");
+  return crop_cast_f32(images, out, batch, img_h, img_w, crop_h, crop_w, c_in, (cudaStream_t)stream);
+}
+int b200_conv5x5_fwd_f32(const float* x, const float* w, const float* bias, float* y, int32_t batch, int32_t h,
+                         int32_t wd, int32_t c_in, int32_t c_out, int32_t relu, void* stream) {
+  B200_REQUIRE(x && w && y, "null pointer");
+  return conv5x5_fwd_f32(x, w, bias, y, batch, h, wd, c_in, c_out, relu, (cudaStream_t)stream);
+}
+int b200_conv5x5_dgrad_f32(const float* dy, const float* w, float* w_scratch, float* dx, int32_t batch,
+                           int32_t h, int32_t wd, int32_t c_in, int32_t c_out, void* stream) {
+  B200_REQUIRE(dy && w && w_scratch && dx, "null pointer");
+  TRY(conv5x5_rot180_f32(w, w_scratch, c_in, c_out, (cudaStream_t)stream));
+  return conv5x5_fwd_f32(dy, w_scratch, nullptr, dx, batch, h, wd, c_out, c_in, 0, (cudaStream_t)stream);
+}
+int b200_conv5x5_wgrad_scratch_bytes(int32_t batch, int32_t h, int32_t wd, int32_t c_in, int32_t c_out,
+                                     int64_t* nbytes) {
+  B200_REQUIRE(nbytes && batch > 0 && h > 0 && wd > 0 && c_in > 0 && c_out > 0, "bad argument");
+  *nbytes = conv5x5_wgrad_scratch_bytes(batch, h, wd, c_in, c_out);
+  return B200_OK;
+}
+int b200_conv5x5_wgrad_f32(const float* x, const float* dy, float* dw, float* db, void* scratch,
+                           int64_t scratch_bytes, int32_t batch, int32_t h, int32_t wd, int32_t c_in,
+                           int32_t c_out, void* stream) {
+  B200_REQUIRE(x && dy && dw && scratch, "null pointer");
+  B200_REQUIRE(batch > 0 && h > 0 && wd > 0 && c_in > 0 && c_out > 0, "bad shape");
+  B200_REQUIRE(scratch_bytes >= conv5x5_wgrad_scratch_bytes(batch, h, wd, c_in, c_out), "scratch too small");
+  return conv5x5_wgrad_f32(x, dy, dw, db, (float*)scratch, batch, h, wd, c_in, c_out, (cudaStream_t)stream);
+}
+int b200_maxpool_fwd_f32(const float* x, float* y, uint8_t* arg, int32_t batch, int32_t h, int32_t wd, int32_t c,
+                         void* stream) {
+  B200_REQUIRE(x && y && arg, "null pointer");
+  return maxpool_fwd_f32(x, y, arg, batch, h, wd, c, (cudaStream_t)stream);
+}
+int b200_maxpool_bwd_f32(const float* dy, const uint8_t* arg, const float* x, float* dx, int32_t batch, int32_t h,
+                         int32_t wd, int32_t c, int32_t relu_mask, void* stream) {
+  B200_REQUIRE(dy && arg && dx, "null pointer");
+  return maxpool_bwd_f32(dy, arg, x, dx, batch, h, wd, c, relu_mask, (cudaStream_t)stream);
+}
+int b200_fc_fwd_f32(const float* x, const float* w, const float* b, float* y, int32_t batch, int32_t k, int32_t n,
+                    int32_t relu, void* stream) {
+  B200_REQUIRE(x && w && y, "null pointer");
+  return fc_fwd_f32(x, w, b, y, batch, k, n, relu, (cudaStream_t)stream);
+}
+int b200_colsum_scratch_bytes(int32_t rows, int32_t cols, int64_t* nbytes) {
+  B200_REQUIRE(nbytes && rows > 0 && cols > 0, "bad argument");
+  *nbytes = colsum_scratch_bytes(rows, cols);
+  return B200_OK;
+}
+int b200_fc_bwd_f32(const float* x, const float* w, const float* dy, float* dx, float* dw, float* db,
+                    void* scratch, int64_t scratch_bytes, int32_t batch, int32_t k, int32_t n, int32_t mask_x,
+                    void* stream) {
+  B200_REQUIRE(x && w && dy && dw, "null pointer");
+  B200_REQUIRE(batch > 0 && k > 0 && n > 0, "bad shape");
+  B200_REQUIRE(!db || (scratch && scratch_bytes >= colsum_scratch_bytes(batch, n)), "scratch too small");
+  return fc_bwd_f32(x, w, dy, dx, dw, db, (float*)scratch, batch, k, n, mask_x, (cudaStream_t)stream);
+}
+int b200_head_f32(const float* logits, const int32_t* labels, float* loss_mean, float* dlogits, int32_t* pred,
+                  int32_t* n_correct, int32_t* n_bad, int32_t batch, int32_t n_cls, void* stream) {
+  B200_REQUIRE(logits && labels, "null pointer");
+  return head_f32(logits, labels, loss_mean, dlogits, pred, n_correct, n_bad, batch, n_cls,
+                  (cudaStream_t)stream);
+}
+int b200_sgd_apply_f32(float* p, const float* g, int64_t n, float lr, float scale, void* stream) {
+  B200_REQUIRE(p && g, "null pointer");
+  return sgd_apply_f32(p, g, n, lr, scale, (cudaStream_t)stream);
+}
+
+}  // extern "C"

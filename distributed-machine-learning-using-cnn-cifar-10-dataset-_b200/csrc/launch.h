@@ -1,0 +1,29 @@
+// Internal C++ launch API shared by abi.cu and the kernel files.  Every function enqueues
+// on `st`, returns a B200_* code and never synchronises.
+#pragma once
+#include "common.cuh"
+
+namespace b200 {
+
+// ---- fp32 validation kernels (f32_kernels.cu) ----
+int crop_cast_f32(const uint8_t* img, float* out, int B, int ih, int iw, int ch, int cw, int cin, cudaStream_t st);
+int conv5x5_fwd_f32(const float* x, const float* w, const float* bias, float* y, int B, int H, int W,
+                    int Cin, int Cout, int relu, cudaStream_t st);
+int conv5x5_rot180_f32(const float* w, float* wr, int Cin, int Cout, cudaStream_t st);
+int64_t conv5x5_wgrad_scratch_bytes(int B, int H, int W, int Cin, int Cout);
+int conv5x5_wgrad_f32(const float* x, const float* dy, float* dw, float* db, float* scratch, int B, int H,
+                      int W, int Cin, int Cout, cudaStream_t st);
+int maxpool_fwd_f32(const float* x, float* y, uint8_t* arg, int B, int H, int W, int C, cudaStream_t st);
+int maxpool_bwd_f32(const float* dy, const uint8_t* arg, const float* x, float* dx, int B, int H, int W,
+                    int C, int relu_mask, cudaStream_t st);
+int fc_fwd_f32(const float* x, const float* w, const float* b, float* y, int B, int K, int N, int relu,
+               cudaStream_t st);
+int64_t colsum_scratch_bytes(int rows, int cols);
+int colsum_f32(const float* a, float* out, float* scratch, int rows, int cols, cudaStream_t st);
+int fc_bwd_f32(const float* x, const float* w, const float* dy, float* dx, float* dw, float* db,
+               float* scratch, int B, int K, int N, int mask_x, cudaStream_t st);
+int head_f32(const float* logits, const int32_t* labels, float* loss_mean, float* dlogits, int32_t* pred,
+             int32_t* n_correct, int32_t* n_bad, int B, int ncls, cudaStream_t st);
+int sgd_apply_f32(float* p, const float* g, int64_t n, float lr, float scale, cudaStream_t st);
+
+}  // namespace b200

@@ -1,0 +1,158 @@
+/* b200cnn.h -- C ABI of the B200-native cifar10cnn.py training step.
+ *
+ * The reference (Huzo/Distributed-Machine-Learning-using-CNN-CIFAR-10-dataset-, one file,
+ * cifar10cnn.py) has no FFI or plugin interface: its hot path is reached through four Python
+ * functions (create_cnn :94, cifar_loss :150, train_step :159, batch_accuracy :166) and the
+ * loop line `mon_sess.run([train_op, loss])` (:230).  This header is the boundary a
+ * maintainer binds instead of TensorFlow for that path; every entry point names the
+ * reference lines it replaces.  INTEGRATION.md shows the ctypes stub.
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes, no C++/torch types.
+ *   - every call returns int: 0 = ok, negative = error (B200_E_*); b200_last_error() gives a
+ *     thread-local message.  No C++ exception crosses the boundary.
+ *   - all tensor pointers are DEVICE pointers unless the name says `host`.  The caller owns
+ *     every buffer (parameters, gradients, workspace, inputs, outputs); the library
+ *     owns only its opaque handle.  No call allocates device memory.
+ *   - every call is asynchronous on the `stream` argument (a cudaStream_t passed as void*),
+ *     does no host synchronisation and can be captured in a CUDA graph.
+ *   - layouts are TensorFlow's: activations NHWC, conv filters HWIO, FC weights [in,out],
+ *     labels int32, records uint8 CHW (cifar10cnn.py:57-62).
+ *   - one handle per process / GPU, not thread-safe (the reference loop is one Python thread).
+ */
+#ifndef B200CNN_H_
+#define B200CNN_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_OK            0
+#define B200_E_INVALID    -1   /* bad argument / unsupported shape */
+#define B200_E_CUDA       -2   /* a CUDA runtime call or launch failed */
+#define B200_E_STATE      -3   /* call order violated (e.g. backward before forward) */
+#define B200_E_NODEVICE   -4   /* no usable sm_100 CUDA device */
+
+#define B200_MODE_FP32  0      /* SIMT fp32 everywhere: the validation mode */
+#define B200_MODE_BF16  1      /* tcgen05 bf16 operands, fp32 accumulation, fp32 master weights */
+
+#define B200_NUM_PARAMS 10     /* variables of create_cnn in creation order, cifar10cnn.py:106-144 */
+
+typedef struct b200_model* b200_handle;
+
+/* Model / batch geometry.  Defaults of the script: batch 128 (:13), 32x32x3 records (:15-19)
+ * centre-cropped to 24x24 (:17-18, :68), 64/64 conv channels (:106,:117), FC 384/192 (:131,:137),
+ * 10 classes (:20). */
+typedef struct {
+  int32_t batch;
+  int32_t img_h, img_w;      /* record image size */
+  int32_t crop_h, crop_w;    /* what the CNN sees */
+  int32_t c_in;              /* 3 */
+  int32_t c1, c2;            /* conv1 / conv2 output channels */
+  int32_t f1, f2;            /* full1 / full2 widths */
+  int32_t n_cls;             /* <= 16 */
+  int32_t mode;              /* B200_MODE_* */
+} b200_config;
+
+const char* b200_last_error(void);
+int b200_version(void);
+
+/* ---- handle ------------------------------------------------------------------------------ */
+int b200_create(const b200_config* cfg, b200_handle* out);
+int b200_destroy(b200_handle h);
+
+/* Flat parameter / gradient buffers: the ten tensors of cifar10cnn.py:106-144 in creation
+ * order, each starting at a multiple of 64 floats.  b200_param_layout fills offsets[10] and
+ * sizes[10] (in floats) and the padded total.  Padding floats must be zero. */
+int b200_param_layout(b200_handle h, int64_t* offsets, int64_t* sizes, int64_t* total);
+int b200_bind_params(b200_handle h, float* params_flat);
+int b200_bind_grads(b200_handle h, float* grads_flat);
+int b200_workspace_bytes(b200_handle h, int64_t* nbytes);
+int b200_bind_workspace(b200_handle h, void* workspace, int64_t nbytes);
+
+/* create_cnn (:94-147) + cifar_loss (:150-157) + batch_accuracy (:166-176) on one batch of
+ * records.  images: uint8 [batch,3,img_h,img_w]; labels: int32 [batch] (or [batch,1]).
+ * The crop/transposes/cast of read_cifar_files (:57-68) happen inside.  Results stay in the
+ * workspace; b200_result_ptrs exposes them. */
+int b200_forward(b200_handle h, const uint8_t* images, const int32_t* labels, void* stream);
+/* the gradient graph built by minimize() (:162-163); fills the bound gradient buffer. */
+int b200_backward(b200_handle h, void* stream);
+/* ApplyGradientDescent x10 (:162-163): params -= lr * grad_scale * grads.  grad_scale = 1 for a
+ * single worker or a SUM allreduce, 1/world for a MEAN allreduce. */
+int b200_sgd_apply(b200_handle h, float lr, float grad_scale, void* stream);
+/* forward + backward + sgd_apply: one `mon_sess.run([train_op, loss])` (:230) for world == 1. */
+int b200_train_step(b200_handle h, const uint8_t* images, const int32_t* labels, float lr, void* stream);
+/* The same call with HOST (pinned) inputs and a host loss: copies the records and labels to
+ * the device, runs the step, copies the scalar loss back -- all on `stream`.  The caller
+ * synchronises the stream before reading *loss_host. */
+int b200_train_step_host(b200_handle h, const uint8_t* images_host, const int32_t* labels_host,
+                         float lr, float* loss_host, void* stream);
+
+/* One eager b200_train_step with a CUDA event recorded on `stream` before every launch site
+ * (a site = the kernels of one logical op: "conv2_fwd", "full1_bwd", "sgd_apply" ...).  Blocks
+ * until the step is done and returns the device time of each site in milliseconds; the bench
+ * uses it for the live roofline of the dominant kernel.  Not capturable (it synchronises). */
+int b200_profile_step(b200_handle h, const uint8_t* images, const int32_t* labels, float lr, void* stream,
+                      float* ms_per_site, int32_t max_sites, int32_t* n_sites);
+const char* b200_site_name(b200_handle h, int32_t i);
+
+/* device pointers to the results of the last forward: logits float[batch,n_cls],
+ * loss float[1] (mean), n_correct int32[1], pred int32[batch].  Any out pointer may be NULL. */
+int b200_result_ptrs(b200_handle h, float** logits, float** loss, int32_t** n_correct, int32_t** pred);
+/* named layer-boundary tensor inside the workspace (tests): "x","conv1","pool1","arg1","conv2",
+ * "pool2","arg2","full1","full2","logits","dlogits","dfull2","dfull1","dpool2","dconv2",
+ * "dpool1","dconv1".  Returns the device pointer, its byte size and element size. */
+int b200_tensor_ptr(b200_handle h, const char* name, void** ptr, int64_t* nbytes, int32_t* elem_size);
+/* how many kernels one b200_train_step launches (for the bench's gpu_launches claim). */
+int b200_launches_per_step(b200_handle h, int32_t* n);
+
+/* ---- per-op entry points (kernel-level parity tests; same kernels the handle path uses) ------ */
+/* read_cifar_files crop/cast, cifar10cnn.py:57-68 */
+int b200_crop_cast_f32(const uint8_t* images, float* out, int32_t batch, int32_t img_h, int32_t img_w,
+                       int32_t crop_h, int32_t crop_w, int32_t c_in, void* stream);
+/* tf.nn.conv2d SAME 5x5 s1 + bias_add + relu, :107-110 / :118-121.  bias may be NULL, relu 0/1. */
+int b200_conv5x5_fwd_f32(const float* x, const float* w, const float* bias, float* y,
+                         int32_t batch, int32_t h, int32_t wd, int32_t c_in, int32_t c_out, int32_t relu,
+                         void* stream);
+/* Conv2DBackpropInput (autodiff of :118).  w_scratch: c_in*c_out*25 floats of scratch. */
+int b200_conv5x5_dgrad_f32(const float* dy, const float* w, float* w_scratch, float* dx,
+                           int32_t batch, int32_t h, int32_t wd, int32_t c_in, int32_t c_out, void* stream);
+/* Conv2DBackpropFilter + BiasAddGrad (autodiff of :107-109 / :118-120).  scratch holds the
+ * split-K partial sums; b200_conv5x5_wgrad_scratch_bytes gives its size.  db may be NULL. */
+int b200_conv5x5_wgrad_scratch_bytes(int32_t batch, int32_t h, int32_t wd, int32_t c_in, int32_t c_out,
+                                     int64_t* nbytes);
+int b200_conv5x5_wgrad_f32(const float* x, const float* dy, float* dw, float* db, void* scratch,
+                           int64_t scratch_bytes, int32_t batch, int32_t h, int32_t wd, int32_t c_in,
+                           int32_t c_out, void* stream);
+/* tf.nn.max_pool k3 s2 SAME (:113 / :123); arg = kh*3+kw of the first maximal cell. */
+int b200_maxpool_fwd_f32(const float* x, float* y, uint8_t* arg, int32_t batch, int32_t h, int32_t wd,
+                         int32_t c, void* stream);
+/* MaxPoolGrad fused with the ReluGrad of the layer that fed the pool: dx = scatter(dy) * [x > 0]
+ * (relu_mask = 1) or plain MaxPoolGrad (relu_mask = 0). */
+int b200_maxpool_bwd_f32(const float* dy, const uint8_t* arg, const float* x, float* dx, int32_t batch,
+                         int32_t h, int32_t wd, int32_t c, int32_t relu_mask, void* stream);
+/* relu(x @ w + b), :133 / :139 / :145 */
+int b200_fc_fwd_f32(const float* x, const float* w, const float* b, float* y, int32_t batch, int32_t k,
+                    int32_t n, int32_t relu, void* stream);
+/* gradients of the above given dy (already masked by this layer's ReluGrad):
+ * dw = x^T dy, db = colsum(dy), dx = (dy w^T) * [x > 0] if mask_x else dy w^T.
+ * dx may be NULL.  scratch: b200_colsum_scratch_bytes(batch, n). */
+int b200_colsum_scratch_bytes(int32_t rows, int32_t cols, int64_t* nbytes);
+int b200_fc_bwd_f32(const float* x, const float* w, const float* dy, float* dx, float* dw, float* db,
+                    void* scratch, int64_t scratch_bytes, int32_t batch, int32_t k, int32_t n,
+                    int32_t mask_x, void* stream);
+/* cifar_loss (:150-157), batch_accuracy (:166-176) and the first backward step: dlogits =
+ * (softmax - onehot)/batch * [logits > 0] (ReLU on the logits, :145).  Labels outside
+ * [0,n_cls) set *n_bad (int32, device) > 0 and contribute nothing. */
+int b200_head_f32(const float* logits, const int32_t* labels, float* loss_mean, float* dlogits,
+                  int32_t* pred, int32_t* n_correct, int32_t* n_bad, int32_t batch, int32_t n_cls,
+                  void* stream);
+/* ApplyGradientDescent (:162-163): p -= lr * scale * g over n floats. */
+int b200_sgd_apply_f32(float* p, const float* g, int64_t n, float lr, float scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200CNN_H_ */

@@ -83,7 +83,15 @@ class CpuTrainer:
         if threads:
             torch.set_num_threads(threads)
         self.p = to_torch(params, torch.float32)
+        self.p0 = {k: v.detach().clone() for k, v in self.p.items()}
         self.lr = lr
+
+    def reset(self):
+        """restore the initial weights (raw-byte inputs with lr 0.1 diverge within a few steps, as
+        they do in the reference -- SURVEY.md Q11 -- and inf/nan arithmetic would distort timing)."""
+        with torch.no_grad():
+            for k, v in self.p.items():
+                v.copy_(self.p0[k])
 
     def step(self, images_u8_chw, labels):
         x = crop_cast(images_u8_chw, dtype=torch.float32)
@@ -92,4 +100,4 @@ class CpuTrainer:
         with torch.no_grad():
             for k, g in zip(PARAM_NAMES, grads):
                 self.p[k].sub_(self.lr * g)
-        return float(loss)
+        return float(loss.detach())
