@@ -195,6 +195,27 @@ def _engine(batch, mode="fp32", **kw):
     return e
 
 
+def _oracle_backward_on_gpu_forward(e, params, labels, a_ref):
+    """Backward parity is judged given the GPU's OWN forward values: max-pool argmax and ReLU masks
+    are discontinuous, and a near-tie that fp32 resolves differently from fp64 (expected a few
+    times per batch: ~1e5 pooling windows, values O(100), fp32 spacing 1e-5) legitimately moves a
+    gradient to a neighbouring cell.  So: (1) forward tensors match the oracle to tolerance,
+    (2) the GPU's argmax is exactly the first-max of the GPU's own conv output (checked here,
+    bit-exact), (3) gradients match the oracle's backward evaluated on the GPU's forward tensors."""
+    a = {"x": a_ref["x"]}
+    for name in ("conv1", "pool1", "conv2", "pool2", "full1", "full2", "logits"):
+        a[name] = e.tensor(name).cpu().numpy().astype(np.float64).reshape(a_ref[name].shape)
+    for name, src in (("arg1", "conv1"), ("arg2", "conv2")):
+        a[name] = e.tensor(name).cpu().numpy().reshape(a_ref[name].shape)
+        y, arg = rn.maxpool_3x3s2_same(a[src])
+        np.testing.assert_array_equal(a[name], arg)                   # first-max rule on its own values
+        np.testing.assert_array_equal(a["pool" + name[-1]], y)
+    a["flat"] = a["pool2"].reshape(a["pool2"].shape[0], -1)
+    a["loss"], a["loss_rows"], a["xent_back"] = rn.softmax_xent(a["logits"], labels)
+    g = rn.backward({k: np.asarray(v, np.float64) for k, v in params.items()}, a)
+    return g, a
+
+
 def _grad_check(e, g_oracle, tol):
     got = e.get_grads()
     for k in rn.PARAM_NAMES:
@@ -222,8 +243,12 @@ def test_full_step_matches_golden_fixture(golden_dir, name):
         f = got[k].astype(np.float64).reshape(-1)
         idx = np.unique(np.linspace(0, f.size - 1, 256).astype(np.int64))
         scale = max(np.abs(z["gsmp_" + k]).max(), z["gsum_" + k][1] / f.size)
-        np.testing.assert_allclose(f[idx], z["gsmp_" + k], rtol=0, atol=RTOL_F32 * 10 * scale)
-        assert abs(np.abs(f).sum() - z["gsum_" + k][1]) <= 1e-4 * z["gsum_" + k][1]
+        # gradients below pool2 depend on discrete argmax choices; one fp32-vs-fp64 near-tie moves
+        # O(1%) of a batch-8 gradient (measured with the oracle itself run in fp32), so the golden
+        # digests pin them loosely here and test_full_step_b128_vs_oracle pins them tightly.
+        loose = k.startswith("conv")
+        np.testing.assert_allclose(f[idx], z["gsmp_" + k], rtol=0, atol=(5e-2 if loose else RTOL_F32 * 10) * scale)
+        assert abs(np.abs(f).sum() - z["gsum_" + k][1]) <= (5e-2 if loose else 1e-4) * z["gsum_" + k][1]
 
 
 @pytest.mark.parametrize("kind", ["u8", "soft"])
@@ -255,14 +280,20 @@ def test_full_step_b128_vs_oracle(kind):
     np.testing.assert_array_equal(e.pred().cpu().numpy()[safe], a["pred"][safe])
     if safe.all():
         assert int(e.n_correct()) == a["n_correct"]
+    g_on_gpu_fwd, a2 = _oracle_backward_on_gpu_forward(e, params, lab, a)
+    flips = int((a2["arg1"] != a["arg1"]).sum() + (a2["arg2"] != a["arg2"]).sum())
+    assert flips <= 64, flips                                        # near-ties only, a handful per batch
     for name in ("dlogits", "dfull2", "dfull1", "dpool2", "dconv2", "dpool1", "dconv1"):
-        assert relerr(e.tensor(name).cpu().numpy().reshape(a[name].shape), a[name]) <= 2 * RTOL_F32, name
-    _grad_check(e, g, 2 * RTOL_F32)
+        assert relerr(e.tensor(name).cpu().numpy().reshape(a2[name].shape), a2[name]) <= 2 * RTOL_F32, name
+    _grad_check(e, g_on_gpu_fwd, 2 * RTOL_F32)
+    for k in ("full_weight_1", "full_bias_1", "full_weight_2", "full_bias_2", "full_weight_3", "full_bias_3"):
+        assert relerr(e.get_grads()[k], g[k]) <= 2 * RTOL_F32, k      # tie-insensitive: pure fp64 oracle
     e.sgd_apply(0.1)
     torch.cuda.synchronize()
     got = e.get_params()
+    newp2 = rn.sgd_apply(params, g_on_gpu_fwd, np.float32(0.1))
     for k in rn.PARAM_NAMES:
-        assert relerr(got[k], newp[k]) <= 2 * RTOL_F32, k
+        assert relerr(got[k], newp2[k]) <= 2 * RTOL_F32, k
     # padding floats between tensors stay zero (they ride along in the allreduce)
     used = torch.zeros(e.total, dtype=torch.bool)
     for o, s in zip(e.offsets, e.sizes):
@@ -327,8 +358,8 @@ def test_two_steps_follow_the_oracle_trajectory():
         torch.cuda.synchronize()
         assert abs(float(e.loss()) - loss) <= 1e-4 * abs(loss)
     got = e.get_params()
-    for k in rn.PARAM_NAMES:
-        assert relerr(got[k], p64[k]) <= 1e-4, k
+    for k in rn.PARAM_NAMES:       # loose: a pool near-tie resolved differently moves ~1% of a conv gradient
+        assert relerr(got[k], p64[k]) <= 2e-3, k
 
 
 def test_uncropped_32x32_shape():
@@ -344,7 +375,8 @@ def test_uncropped_32x32_shape():
     torch.cuda.synchronize()
     _, loss, g, a = rn.train_step(params, img, lab, crop=(32, 32))
     assert relerr(e.logits().cpu().numpy(), a["logits"]) <= RTOL_F32
-    _grad_check(e, g, 2 * RTOL_F32)
+    g2, _ = _oracle_backward_on_gpu_forward(e, params, lab, a)
+    _grad_check(e, g2, 2 * RTOL_F32)
 
 
 def test_bad_inputs_raise():
