@@ -386,6 +386,21 @@ int b200_fc_bwd_f32(const float* x, const float* w, const float* dy, float* dx, 
   B200_REQUIRE(!db || (scratch && scratch_bytes >= colsum_scratch_bytes(batch, n)), "scratch too small");
   return fc_bwd_f32(x, w, dy, dx, dw, db, (float*)scratch, batch, k, n, mask_x, (cudaStream_t)stream);
 }
+int b200_fc_fwd_bf16(const float* x, const float* w, const float* b, float* y, int32_t batch, int32_t k, int32_t n,
+                     int32_t relu, void* stream) {
+  B200_REQUIRE(x && w && y, "null pointer");
+  return fc_fwd_tc(x, w, b, y, batch, k, n, relu, (cudaStream_t)stream);
+}
+int b200_fc_bwd_bf16(const float* x, const float* w, const float* dy, float* dx, float* dw, float* db,
+                     void* scratch, int64_t scratch_bytes, int32_t batch, int32_t k, int32_t n, int32_t mask_x,
+                     void* stream) {
+  B200_REQUIRE(x && w && dy && dw, "null pointer");
+  B200_REQUIRE(batch > 0 && k > 0 && n > 0, "bad shape");
+  B200_REQUIRE(!db || (scratch && scratch_bytes >= colsum_scratch_bytes(batch, n)), "scratch too small");
+  TRY(fc_bwd_tc(x, w, dy, dx, dw, batch, k, n, mask_x, (cudaStream_t)stream));
+  if (db) return colsum_f32(dy, db, (float*)scratch, batch, n, (cudaStream_t)stream);
+  return B200_OK;
+}
 int b200_head_f32(const float* logits, const int32_t* labels, float* loss_mean, float* dlogits, int32_t* pred,
                   int32_t* n_correct, int32_t* n_bad, int32_t batch, int32_t n_cls, void* stream) {
   B200_REQUIRE(logits && labels, "null pointer");

@@ -26,4 +26,11 @@ int head_f32(const float* logits, const int32_t* labels, float* loss_mean, float
              int32_t* n_correct, int32_t* n_bad, int B, int ncls, cudaStream_t st);
 int sgd_apply_f32(float* p, const float* g, int64_t n, float lr, float scale, cudaStream_t st);
 
+
+// ---- bf16 tensor-core kernels (tc_*.cu): fp32 tensors in HBM, bf16 operands, fp32 accumulation ----
+int fc_fwd_tc(const float* x, const float* w, const float* b, float* y, int B, int K, int N, int relu,
+              cudaStream_t st);
+int fc_bwd_tc(const float* x, const float* w, const float* dy, float* dx, float* dw, int B, int K, int N,
+              int mask_x, cudaStream_t st);
+
 }  // namespace b200

@@ -1,0 +1,260 @@
+// tcgen05 GEMM for the fully connected layers (cifar10cnn.py:133/:139 and their gradients):
+//   C[M,N] (fp32) = A[M,K] * B[K,N], bf16 operands converted on the fly from fp32 or bf16
+//   global tensors, fp32 accumulation in TMEM, fused epilogue (bias, ReLU, ReluGrad mask).
+// Either operand may be K-major or MN-major in global memory, so forward (x W), dX (dY W^T) and
+// dW (X^T dY) all read the row-major tensors of the TF layouts directly -- no transposes.
+//
+// CTA = 128 x BN output tile, 5 warps: warps 0-3 stage operands (LDG -> bf16 -> STS in the
+// no-swizzle canonical layout, chunk stride padded by 16 B so the stores are conflict-free) and
+// later run the epilogue (warp w owns TMEM lanes 32w..32w+31); warp 4 allocates TMEM and issues
+// the MMAs from one thread.  4-stage ring, full/empty mbarriers; tcgen05.commit frees a stage.
+#include <algorithm>
+
+#include "launch.h"
+#include "tc_common.cuh"
+
+namespace b200 {
+using namespace tc;
+
+namespace {
+constexpr int BM = 128, BK = 64, STAGES = 4;
+constexpr int LOADERS = 128;
+
+struct GemmArgs {
+  int M, N, K;
+  const void* A; int64_t lda;
+  const void* B; int64_t ldb;
+  float* C; int64_t ldc;
+  const float* bias;
+  int relu;
+  const float* mask; int64_t ldmask;
+  float* colsum;           // optional: colsum[n] = sum_m C[m,n] (after mask), needs gridDim.y == 1
+};
+
+template <int BN>
+struct Smem {
+  // K-major: [8 chunks][rows][16 B], chunk stride rows*16+16.  MN-major: [groups][64 k][16 B], stride 1040.
+  static constexpr int A_K_LBO = BM * 16 + 16, A_MN_SBO = BK * 16 + 16;
+  static constexpr int B_K_LBO = BN * 16 + 16, B_MN_SBO = BK * 16 + 16;
+  static constexpr int A_BYTES = (8 * A_K_LBO > (BM / 8) * A_MN_SBO) ? 8 * A_K_LBO : (BM / 8) * A_MN_SBO;
+  static constexpr int B_BYTES = (8 * B_K_LBO > (BN / 8) * B_MN_SBO) ? 8 * B_K_LBO : (BN / 8) * B_MN_SBO;
+  static constexpr int STAGE = ((A_BYTES + B_BYTES + 127) / 128) * 128;
+  static constexpr int TOTAL = STAGES * STAGE + 256;
+};
+
+template <int BN, bool A_MN, bool B_MN, typename TA, typename TB>
+__global__ void __launch_bounds__(160, 1) tc_gemm_kernel(GemmArgs g) {
+  using S = Smem<BN>;
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint8_t* ctrl = smem + STAGES * S::STAGE;
+  uint64_t* full = reinterpret_cast<uint64_t*>(ctrl);
+  uint64_t* empty = full + STAGES;
+  uint64_t* accum = empty + STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum + 1);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+  const int nkb = (g.K + BK - 1) / BK;
+
+  if (tid == 0) {
+    for (int s = 0; s < STAGES; ++s) { mbar_init(smem_u32(full + s), LOADERS); mbar_init(smem_u32(empty + s), 1); }
+    mbar_init(smem_u32(accum), 1);
+    fence_mbar_init();
+  }
+  if (warp == 4) tmem_alloc(smem_u32(tmem_slot), BN < 32 ? 32 : BN);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp < 4) {
+    // ------------------------------ operand staging ------------------------------------------
+    const TA* A = reinterpret_cast<const TA*>(g.A);
+    const TB* B = reinterpret_cast<const TB*>(g.B);
+    for (int kb = 0; kb < nkb; ++kb) {
+      const int s = kb % STAGES;
+      const uint32_t ph = (kb / STAGES) & 1;
+      mbar_wait(smem_u32(empty + s), ph ^ 1);
+      uint8_t* sa = smem + s * S::STAGE;
+      uint8_t* sb = sa + S::A_BYTES;
+      const int k0 = kb * BK;
+      if (!A_MN) {   // A(m,k) = A[m*lda + k]: 8 consecutive threads read one row's 8 chunks
+#pragma unroll 4
+        for (int q = tid; q < BM * 8; q += LOADERS) {
+          int c = q & 7, r = q >> 3;
+          int m = m0 + r, k = k0 + c * 8;
+          uint4 v = make_uint4(0, 0, 0, 0);
+          if (m < g.M && k < g.K) v = load_chunk(A + (int64_t)m * g.lda + k);
+          *reinterpret_cast<uint4*>(sa + c * S::A_K_LBO + r * 16) = v;
+        }
+      } else {       // A(m,k) = A[k*lda + m]: consecutive threads read consecutive m-chunks of one k row
+#pragma unroll 4
+        for (int q = tid; q < BK * (BM / 8); q += LOADERS) {
+          int gi = q % (BM / 8), kk = q / (BM / 8);
+          int m = m0 + gi * 8, k = k0 + kk;
+          uint4 v = make_uint4(0, 0, 0, 0);
+          if (m < g.M && k < g.K) v = load_chunk(A + (int64_t)k * g.lda + m);
+          *reinterpret_cast<uint4*>(sa + gi * S::A_MN_SBO + kk * 16) = v;
+        }
+      }
+      if (!B_MN) {   // B(k,n) = B[n*ldb + k]
+#pragma unroll 4
+        for (int q = tid; q < BN * 8; q += LOADERS) {
+          int c = q & 7, r = q >> 3;
+          int n = n0 + r, k = k0 + c * 8;
+          uint4 v = make_uint4(0, 0, 0, 0);
+          if (n < g.N && k < g.K) v = load_chunk(B + (int64_t)n * g.ldb + k);
+          *reinterpret_cast<uint4*>(sb + c * S::B_K_LBO + r * 16) = v;
+        }
+      } else {       // B(k,n) = B[k*ldb + n]
+#pragma unroll 4
+        for (int q = tid; q < BK * (BN / 8); q += LOADERS) {
+          int gi = q % (BN / 8), kk = q / (BN / 8);
+          int n = n0 + gi * 8, k = k0 + kk;
+          uint4 v = make_uint4(0, 0, 0, 0);
+          if (n < g.N && k < g.K) v = load_chunk(B + (int64_t)k * g.ldb + n);
+          *reinterpret_cast<uint4*>(sb + gi * S::B_MN_SBO + kk * 16) = v;
+        }
+      }
+      fence_proxy_async();
+      mbar_arrive(smem_u32(full + s));
+    }
+    // ------------------------------ epilogue ------------------------------------------------------
+    mbar_wait(smem_u32(accum), 0);
+    tc_fence_after();
+    const int m = m0 + warp * 32 + lane;
+#pragma unroll 1
+    for (int c0 = 0; c0 < BN; c0 += 32) {
+      uint32_t v[32];
+      tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + c0, v);
+      tmem_ld_wait();
+      float o[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        int n = n0 + c0 + j;
+        float x = __uint_as_float(v[j]);
+        if (n < g.N) {
+          if (g.bias) x += __ldg(g.bias + n);
+          if (g.relu) x = fmaxf(x, 0.f);
+        }
+        o[j] = x;
+      }
+      if (g.mask && m < g.M) {
+        const float* mk = g.mask + (int64_t)m * g.ldmask + n0 + c0;
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (n0 + c0 + j < g.N && !(__ldg(mk + j) > 0.f)) o[j] = 0.f;
+      }
+      if (m < g.M) {
+        float* out = g.C + (int64_t)m * g.ldc + n0 + c0;
+        if (n0 + c0 + 32 <= g.N && ((g.ldc & 3) == 0)) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4)
+            *reinterpret_cast<float4*>(out + j) = make_float4(o[j], o[j + 1], o[j + 2], o[j + 3]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (n0 + c0 + j < g.N) out[j] = o[j];
+        }
+      }
+      if (g.colsum) {   // column sums over the rows of this tile (rows >= M contribute 0): warp shuffle tree
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          float x = (m < g.M) ? o[j] : 0.f;
+#pragma unroll
+          for (int off = 16; off > 0; off >>= 1) x += __shfl_xor_sync(0xffffffffu, x, off);
+          if (lane == 0 && n0 + c0 + j < g.N) atomicAdd(g.colsum + n0 + c0 + j, x);
+        }
+      }
+    }
+    tc_fence_before();
+  } else {
+    // ------------------------------ MMA issue (one thread) -----------------------------------------
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(BM, BN, A_MN, B_MN);
+      for (int kb = 0; kb < nkb; ++kb) {
+        const int s = kb % STAGES;
+        const uint32_t ph = (kb / STAGES) & 1;
+        mbar_wait(smem_u32(full + s), ph);
+        tc_fence_after();
+        const uint32_t sa = smem_u32(smem + s * S::STAGE);
+        const uint32_t sb = sa + S::A_BYTES;
+#pragma unroll
+        for (int ks = 0; ks < BK / 16; ++ks) {
+          uint64_t da = A_MN ? make_desc(sa + ks * 256, 128, S::A_MN_SBO)
+                             : make_desc(sa + ks * 2 * S::A_K_LBO, S::A_K_LBO, 128);
+          uint64_t db = B_MN ? make_desc(sb + ks * 256, 128, S::B_MN_SBO)
+                             : make_desc(sb + ks * 2 * S::B_K_LBO, S::B_K_LBO, 128);
+          umma_bf16(tmem, da, db, idesc, (kb | ks) ? 1u : 0u);
+        }
+        umma_commit(smem_u32(empty + s));
+      }
+      umma_commit(smem_u32(accum));
+    }
+    __syncwarp();
+  }
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    tmem_dealloc(tmem, BN < 32 ? 32 : BN);
+  }
+}
+
+template <int BN, bool A_MN, bool B_MN, typename TA, typename TB>
+int launch(const GemmArgs& g, cudaStream_t st) {
+  using S = Smem<BN>;
+  auto kern = tc_gemm_kernel<BN, A_MN, B_MN, TA, TB>;
+  static bool attr_done = false;      // per instantiation; attribute is per-function, device-wide
+  if (!attr_done) {
+    B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
+    attr_done = true;
+  }
+  dim3 grid(cdiv(g.N, BN), cdiv(g.M, BM));
+  kern<<<grid, 160, S::TOTAL, st>>>(g);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+template <bool A_MN, bool B_MN>
+int dispatch(const GemmArgs& g, cudaStream_t st) {
+  // BN = 64 keeps more CTAs in flight for these small problems
+  return launch<64, A_MN, B_MN, float, float>(g, st);
+}
+
+int check_align(const GemmArgs& g, bool a_mn, bool b_mn) {
+  B200_REQUIRE(g.M > 0 && g.N > 0 && g.K > 0, "tc_gemm: bad shape");
+  B200_REQUIRE(((uintptr_t)g.A & 15) == 0 && ((uintptr_t)g.B & 15) == 0 && (g.lda % 4) == 0 && (g.ldb % 4) == 0,
+               "tc_gemm: operands must be 16-byte aligned with leading dimensions that are multiples of 4");
+  B200_REQUIRE((a_mn ? g.M : g.K) % 8 == 0 && (b_mn ? g.N : g.K) % 8 == 0,
+               "tc_gemm: contiguous operand dimensions must be multiples of 8 (M=%d N=%d K=%d)", g.M, g.N, g.K);
+  return B200_OK;
+}
+}  // namespace
+
+// y = relu?(x @ w + b): A = x [B,K] K-major, B = w [K,N] MN-major
+int fc_fwd_tc(const float* x, const float* w, const float* b, float* y, int Bt, int K, int N, int relu,
+              cudaStream_t st) {
+  GemmArgs g{Bt, N, K, x, K, w, N, y, N, b, relu, nullptr, 0, nullptr};
+  int rc = check_align(g, false, true);
+  if (rc) return rc;
+  return dispatch<false, true>(g, st);
+}
+
+// dw = x^T dy, dx = (dy w^T) * [x > 0]?   (bias gradient: colsum_f32)
+int fc_bwd_tc(const float* x, const float* w, const float* dy, float* dx, float* dw, int Bt, int K, int N,
+              int mask_x, cudaStream_t st) {
+  int rc;
+  {  // dw[K,N] = x^T[K,Bt] dy[Bt,N]: A(m=k_feat, k=batch) = x[batch*K + m] MN-major; B(k=batch, n) = dy MN-major
+    GemmArgs g{K, N, Bt, x, K, dy, N, dw, N, nullptr, 0, nullptr, 0, nullptr};
+    if ((rc = check_align(g, true, true))) return rc;
+    if ((rc = dispatch<true, true>(g, st))) return rc;
+  }
+  if (dx) {  // dx[Bt,K] = dy[Bt,N] w^T: A = dy K-major; B(k=n_out, n=k_feat) = w[n*N + k] K-major
+    GemmArgs g{Bt, K, N, dy, N, w, N, dx, K, nullptr, 0, mask_x ? x : nullptr, K, nullptr};
+    if ((rc = check_align(g, false, false))) return rc;
+    if ((rc = dispatch<false, false>(g, st))) return rc;
+  }
+  return B200_OK;
+}
+
+}  // namespace b200

@@ -143,6 +143,13 @@ int b200_colsum_scratch_bytes(int32_t rows, int32_t cols, int64_t* nbytes);
 int b200_fc_bwd_f32(const float* x, const float* w, const float* dy, float* dx, float* dw, float* db,
                     void* scratch, int64_t scratch_bytes, int32_t batch, int32_t k, int32_t n,
                     int32_t mask_x, void* stream);
+/* The same two products on the tensor cores (tcgen05, bf16 operands rounded from the fp32 tensors
+ * on the fly, fp32 accumulation in TMEM).  batch, k and n must be multiples of 8. */
+int b200_fc_fwd_bf16(const float* x, const float* w, const float* b, float* y, int32_t batch, int32_t k, int32_t n,
+                     int32_t relu, void* stream);
+int b200_fc_bwd_bf16(const float* x, const float* w, const float* dy, float* dx, float* dw, float* db,
+                     void* scratch, int64_t scratch_bytes, int32_t batch, int32_t k, int32_t n,
+                     int32_t mask_x, void* stream);
 /* cifar_loss (:150-157), batch_accuracy (:166-176) and the first backward step: dlogits =
  * (softmax - onehot)/batch * [logits > 0] (ReLU on the logits, :145).  Labels outside
  * [0,n_cls) set *n_bad (int32, device) > 0 and contribute nothing. */

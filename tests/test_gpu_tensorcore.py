@@ -1,0 +1,83 @@
+"""GPU parity of the tcgen05 (bf16 operands, fp32 accumulate) kernels, through the C ABI.
+
+Two bars per kernel:
+  * TIGHT  (<= 2e-5 of max-abs): against the fp64 oracle evaluated on the SAME bf16-rounded
+    operands -- products of bf16 values are exact in fp32, so only accumulation order differs.
+    This is what proves the kernel (descriptors, layouts, pipeline) right.
+  * LOOSE  (<= 1e-2 of max-abs): against the fp64 oracle on the unrounded fp32 operands -- the
+    stated precision of the bf16 mode (operand rounding 2^-9 relative per value).
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+from b200cnn import _lib
+from oracle import ref_numpy as rn
+
+pytestmark = pytest.mark.gpu
+TIGHT, LOOSE = 2e-5, 1e-2
+
+
+def dev(a):
+    return torch.as_tensor(np.ascontiguousarray(a)).cuda()
+
+
+def bf16_round(a):
+    return torch.as_tensor(np.asarray(a, np.float32)).to(torch.bfloat16).to(torch.float64).numpy()
+
+
+def relerr(got, want):
+    want = np.asarray(want, np.float64)
+    return np.abs(np.asarray(got, np.float64) - want).max() / (np.abs(want).max() + 1e-30)
+
+
+def stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+@pytest.fixture(scope="module")
+def lib():
+    return _lib.load()
+
+
+@pytest.mark.parametrize("B,K,N", [(128, 2304, 384), (128, 384, 192), (8, 2304, 384), (256, 384, 192),
+                                   (136, 200, 72), (128, 192, 16)])
+def test_fc_tensorcore(lib, B, K, N):
+    rng = np.random.default_rng(21)
+    x = np.maximum(rng.normal(size=(B, K)), 0).astype(np.float32)
+    w = (rng.normal(size=(K, N)) * 0.05).astype(np.float32)
+    b = rng.normal(size=(N,)).astype(np.float32)
+    dy = rng.normal(size=(B, N)).astype(np.float32)
+    xd, wd, bd, dyd = dev(x), dev(w), dev(b), dev(dy)
+    xr, wr, dyr = bf16_round(x), bf16_round(w), bf16_round(dy)
+    y = torch.full((B, N), float("nan"), device="cuda")
+    _lib.check(lib.b200_fc_fwd_bf16(xd.data_ptr(), wd.data_ptr(), bd.data_ptr(), y.data_ptr(), B, K, N, 1, stream()))
+    torch.cuda.synchronize()
+    assert relerr(y.cpu().numpy(), np.maximum(xr @ wr + b, 0)) <= TIGHT
+    assert relerr(y.cpu().numpy(), np.maximum(x.astype(np.float64) @ w + b, 0)) <= LOOSE
+    nb = C.c_int64()
+    _lib.check(lib.b200_colsum_scratch_bytes(B, N, C.byref(nb)))
+    scr = torch.empty(nb.value, dtype=torch.uint8, device="cuda")
+    for mask in (1, 0):
+        dx = torch.full((B, K), float("nan"), device="cuda")
+        dw = torch.full((K, N), float("nan"), device="cuda")
+        db = torch.full((N,), float("nan"), device="cuda")
+        _lib.check(lib.b200_fc_bwd_bf16(xd.data_ptr(), wd.data_ptr(), dyd.data_ptr(), dx.data_ptr(), dw.data_ptr(),
+                                        db.data_ptr(), scr.data_ptr(), nb.value, B, K, N, mask, stream()))
+        torch.cuda.synchronize()
+        wdx = dyr @ wr.T
+        if mask:
+            wdx = wdx * (x > 0)
+        assert relerr(dx.cpu().numpy(), wdx) <= TIGHT
+        assert relerr(dw.cpu().numpy(), xr.T @ dyr) <= TIGHT
+        assert relerr(dw.cpu().numpy(), x.astype(np.float64).T @ dy) <= LOOSE
+        assert relerr(db.cpu().numpy(), dy.astype(np.float64).sum(0)) <= 1e-5
+
+
+def test_fc_tensorcore_rejects_unaligned(lib):
+    x = torch.zeros(5, 33, device="cuda")
+    w = torch.zeros(33, 7, device="cuda")
+    y = torch.zeros(5, 7, device="cuda")
+    assert lib.b200_fc_fwd_bf16(x.data_ptr(), w.data_ptr(), None, y.data_ptr(), 5, 33, 7, 1, stream()) == _lib.E_INVALID
