@@ -386,6 +386,27 @@ int b200_fc_bwd_f32(const float* x, const float* w, const float* dy, float* dx, 
   B200_REQUIRE(!db || (scratch && scratch_bytes >= colsum_scratch_bytes(batch, n)), "scratch too small");
   return fc_bwd_f32(x, w, dy, dx, dw, db, (float*)scratch, batch, k, n, mask_x, (cudaStream_t)stream);
 }
+int b200_conv5x5_fwd_bf16(const float* x, const float* w, const float* bias, float* y, int32_t batch, int32_t h,
+                          int32_t wd, int32_t c_in, int32_t c_out, int32_t relu, void* stream) {
+  B200_REQUIRE(x && w && y, "null pointer");
+  return conv5x5_fwd_tc(x, w, bias, y, batch, h, wd, c_in, c_out, relu, (cudaStream_t)stream);
+}
+int b200_conv5x5_dgrad_bf16(const float* dy, const float* w, float* dx, int32_t batch, int32_t h, int32_t wd,
+                            int32_t c_in, int32_t c_out, void* stream) {
+  B200_REQUIRE(dy && w && dx, "null pointer");
+  return conv5x5_dgrad_tc(dy, w, dx, batch, h, wd, c_in, c_out, (cudaStream_t)stream);
+}
+int b200_conv5x5_wgrad_bf16_scratch_bytes(int32_t batch, int64_t* nbytes) {
+  B200_REQUIRE(nbytes && batch > 0, "bad argument");
+  *nbytes = conv5x5_wgrad_tc_scratch_bytes(batch);
+  return B200_OK;
+}
+int b200_conv5x5_wgrad_bf16(const float* x, const float* dy, float* dw, void* scratch, int64_t scratch_bytes,
+                            int32_t batch, int32_t h, int32_t wd, int32_t c_in, int32_t c_out, void* stream) {
+  B200_REQUIRE(x && dy && dw && scratch, "null pointer");
+  B200_REQUIRE(batch > 0 && scratch_bytes >= conv5x5_wgrad_tc_scratch_bytes(batch), "scratch too small");
+  return conv5x5_wgrad_tc(x, dy, dw, (float*)scratch, batch, h, wd, c_in, c_out, (cudaStream_t)stream);
+}
 int b200_fc_fwd_bf16(const float* x, const float* w, const float* b, float* y, int32_t batch, int32_t k, int32_t n,
                      int32_t relu, void* stream) {
   B200_REQUIRE(x && w && y, "null pointer");

@@ -1,0 +1,427 @@
+// tcgen05 implicit-GEMM kernels for the 5x5 SAME convolutions of cifar10cnn.py (:107, :118) and
+// their gradients (Conv2DBackpropInput / Conv2DBackpropFilter), bf16 operands, fp32 accumulation
+// in TMEM.
+//
+// THE STRIP.  An image (or a few) is kept in shared memory as a zero-padded "strip": pixel (i,j)
+// of image g sits in pixel slot  lead + (g*(H+2) + i)*P + j  with row pitch P = W+4, so every row
+// is followed by 4 zero pixels (right pad of this row = left pad of the next) and every image by
+// 2 zero rows.  Channels are split in chunks of 8 (16 B): byte address = chunk*CH_STRIDE + slot*16.
+// That is exactly the no-swizzle canonical K-major operand layout with 8 consecutive pixel slots
+// as a core matrix -- and because the layout is unswizzled, a filter tap (di,dj) is nothing but the
+// start-address offset ((di-2)*P + (dj-2))*16 of the A descriptor.  The 25 taps x C/16 k-steps of
+// the implicit GEMM therefore all read ONE resident copy of the input; no im2col is ever built.
+// GEMM rows are pixel slots (pad slots compute garbage that the epilogue drops: 224/144 = 1.56x
+// MMA work for 12x12 images), M = 128 rows per MMA at full tensor rate.
+//
+// The same strip read as an MN-major operand (8 channels contiguous, pixel slots along K) feeds
+// the filter gradient: dW[tap] = X_strip(shifted by tap)^T * dY_strip, where the zero pads of the
+// dY strip cancel every out-of-image product.
+#include <algorithm>
+
+#include "launch.h"
+#include "tc_common.cuh"
+
+namespace b200 {
+using namespace tc;
+
+namespace {
+constexpr int LOADERS = 128;
+constexpr int WSTAGES = 6;
+
+struct ConvGeom {
+  int B, H, W, KC, NC;      // batch, image size, contraction channels, output channels
+  int P, rows_per_img;      // row pitch (W+4), H+2
+  int ipc, tiles;           // images per CTA, 128-row M tiles per CTA
+  int lead, npix;           // zero pixels before the first image row, total pixel slots
+  int ch_stride;            // bytes between channel chunks of the strip (npix*16 + 16)
+};
+
+__host__ inline ConvGeom make_geom(int B, int H, int W, int KC, int NC, int ipc) {
+  ConvGeom g;
+  g.B = B; g.H = H; g.W = W; g.KC = KC; g.NC = NC;
+  g.P = W + 4; g.rows_per_img = H + 2; g.ipc = ipc;
+  int mtot = ipc * g.rows_per_img * g.P;
+  g.tiles = (mtot + 127) / 128;
+  g.lead = 2 * g.P + 2;
+  g.npix = g.lead + g.tiles * 128 + 2 * g.P + 2;
+  g.ch_stride = g.npix * 16 + 16;
+  return g;
+}
+
+// zero `bytes` (multiple of 16) of shared memory with the 128 loader threads
+__device__ __forceinline__ void zero_smem(uint8_t* p, int bytes, int tid) {
+  for (int o = tid * 16; o < bytes; o += LOADERS * 16) *reinterpret_cast<uint4*>(p + o) = make_uint4(0, 0, 0, 0);
+}
+__device__ __forceinline__ void loaders_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+// copy the valid pixels of images [n0, n0+ipc) of a dense NHWC fp32 tensor into a strip (bf16)
+__device__ __forceinline__ void fill_strip(uint8_t* strip, const float* __restrict__ x, const ConvGeom& g, int n0,
+                                           int C, int ch_stride, int tid) {
+  const int cpp = C >> 3;                       // chunks per pixel
+  const int per_img = g.H * g.W * cpp;
+  for (int img = 0; img < g.ipc; ++img) {
+    const int n = n0 + img;
+    if (n >= g.B) break;
+    const float* src = x + (int64_t)n * g.H * g.W * C;
+#pragma unroll 4
+    for (int q = tid; q < per_img; q += LOADERS) {
+      int c = q % cpp, pix = q / cpp;
+      int j = pix % g.W, i = pix / g.W;
+      uint4 v = load_chunk(src + (int64_t)pix * C + c * 8);
+      int slot = g.lead + (img * g.rows_per_img + i) * g.P + j;
+      *reinterpret_cast<uint4*>(strip + c * ch_stride + slot * 16) = v;
+    }
+  }
+}
+
+struct ConvArgs {
+  const float* x;      // [B,H,W,KC]
+  const float* w;      // HWIO fp32: forward [25][KC][NC]; dgrad: the FORWARD filter [25][NC][KC]
+  const float* bias;   // [NC] or null
+  float* y;            // [B,H,W,NC]
+  int relu;
+  ConvGeom g;
+};
+
+// ---------------------------------------------------------------------------------------------------
+// forward / input-gradient convolution.  grid = (ceil(B/ipc), NC/64), 160 threads.
+// DGRAD = false: y = conv(x, w)            B operand (kc,nc) = w[tap][kc][nc]     (MN-major)
+// DGRAD = true : y = conv(x, rot180(w)^T)  B operand (kc,nc) = w[24-tap][nc][kc]  (K-major)
+// ---------------------------------------------------------------------------------------------------
+template <bool DGRAD>
+__global__ void __launch_bounds__(160, 1) conv5x5_tc_kernel(ConvArgs a) {
+  constexpr int BN = 64;
+  const ConvGeom& g = a.g;
+  extern __shared__ __align__(128) uint8_t smem[];
+  const int kchunks = g.KC >> 3;
+  const int strip_bytes = kchunks * g.ch_stride;
+  // weight stage: MN-major [BN/8 groups][KC k][16B] (SBO = KC*16+16)  |  K-major [KC/8 chunks][BN rows][16B]
+  const int w_mn_sbo = g.KC * 16 + 16, w_k_lbo = BN * 16 + 16;
+  const int wstage = ((DGRAD ? kchunks * w_k_lbo : (BN / 8) * w_mn_sbo) + 127) & ~127;
+  uint8_t* strip = smem;
+  uint8_t* wring = smem + ((strip_bytes + 127) & ~127);
+  uint8_t* ctrl = wring + WSTAGES * wstage;
+  uint64_t* wfull = reinterpret_cast<uint64_t*>(ctrl);
+  uint64_t* wempty = wfull + WSTAGES;
+  uint64_t* strip_full = wempty + WSTAGES;
+  uint64_t* accum = strip_full + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum + 1);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int n_img0 = blockIdx.x * g.ipc;
+  const int nc0 = blockIdx.y * BN;
+  const int tmem_cols = g.tiles * BN <= 64 ? 64 : g.tiles * BN <= 128 ? 128 : g.tiles * BN <= 256 ? 256 : 512;
+
+  if (tid == 0) {
+    for (int s = 0; s < WSTAGES; ++s) { mbar_init(smem_u32(wfull + s), LOADERS); mbar_init(smem_u32(wempty + s), 1); }
+    mbar_init(smem_u32(strip_full), LOADERS);
+    mbar_init(smem_u32(accum), 1);
+    fence_mbar_init();
+  }
+  if (warp == 4) tmem_alloc(smem_u32(tmem_slot), tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp < 4) {
+    // ---- input strip --------------------------------------------------------------------------
+    zero_smem(strip, strip_bytes, tid);
+    loaders_sync();
+    fill_strip(strip, a.x, g, n_img0, g.KC, g.ch_stride, tid);
+    fence_proxy_async();
+    mbar_arrive(smem_u32(strip_full));
+    // ---- filter taps through the ring ------------------------------------------------------------
+    for (int tap = 0; tap < 25; ++tap) {
+      const int s = tap % WSTAGES;
+      const uint32_t ph = (tap / WSTAGES) & 1;
+      mbar_wait(smem_u32(wempty + s), ph ^ 1);
+      uint8_t* ws = wring + s * wstage;
+      if (!DGRAD) {
+        const float* wt = a.w + (int64_t)tap * g.KC * g.NC;
+        for (int q = tid; q < g.KC * (BN / 8); q += LOADERS) {
+          int gi = q & 7, k = q >> 3;
+          uint4 v = load_chunk(wt + (int64_t)k * g.NC + nc0 + gi * 8);
+          *reinterpret_cast<uint4*>(ws + gi * w_mn_sbo + k * 16) = v;
+        }
+      } else {
+        const float* wt = a.w + (int64_t)(24 - tap) * g.NC * g.KC;       // forward filter [tap][cin=NC][cout=KC]
+        for (int q = tid; q < BN * kchunks; q += LOADERS) {
+          int c = q % kchunks, n = q / kchunks;
+          uint4 v = load_chunk(wt + (int64_t)(nc0 + n) * g.KC + c * 8);
+          *reinterpret_cast<uint4*>(ws + c * w_k_lbo + n * 16) = v;
+        }
+      }
+      fence_proxy_async();
+      mbar_arrive(smem_u32(wfull + s));
+    }
+    // ---- epilogue: TMEM -> registers -> (+bias, relu) -> dense NHWC fp32 ---------------------------
+    mbar_wait(smem_u32(accum), 0);
+    tc_fence_after();
+    for (int t = 0; t < g.tiles; ++t) {
+      const int p = t * 128 + warp * 32 + lane;
+      const int r = p / g.P, c = p - r * g.P;
+      const int img = r / g.rows_per_img, i = r - img * g.rows_per_img;
+      const int n = n_img0 + img;
+      const bool valid = (img < g.ipc) && (n < g.B) && (i < g.H) && (c < g.W);
+      float* out = a.y + (((int64_t)n * g.H + i) * g.W + c) * g.NC + nc0;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + t * BN + c0, v);
+        tmem_ld_wait();
+        if (valid) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            float o[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              float xv = __uint_as_float(v[j + e]);
+              if (a.bias) xv += __ldg(a.bias + nc0 + c0 + j + e);
+              if (a.relu) xv = fmaxf(xv, 0.f);
+              o[e] = xv;
+            }
+            *reinterpret_cast<float4*>(out + c0 + j) = make_float4(o[0], o[1], o[2], o[3]);
+          }
+        }
+      }
+    }
+    tc_fence_before();
+  } else {
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc(128, BN, false, !DGRAD);
+      mbar_wait(smem_u32(strip_full), 0);
+      for (int tap = 0; tap < 25; ++tap) {
+        const int s = tap % WSTAGES;
+        const uint32_t ph = (tap / WSTAGES) & 1;
+        mbar_wait(smem_u32(wfull + s), ph);
+        tc_fence_after();
+        const int di = tap / 5, dj = tap - di * 5;
+        const int slot0 = g.lead + (di - 2) * g.P + (dj - 2);
+        const uint32_t sa = smem_u32(strip) + slot0 * 16;
+        const uint32_t sb = smem_u32(wring + s * wstage);
+        for (int t = 0; t < g.tiles; ++t) {
+          for (int ks = 0; ks < (g.KC >> 4); ++ks) {
+            uint64_t da = make_desc(sa + t * 128 * 16 + ks * 2 * g.ch_stride, g.ch_stride, 128);
+            uint64_t db = DGRAD ? make_desc(sb + ks * 2 * w_k_lbo, w_k_lbo, 128)
+                                : make_desc(sb + ks * 256, 128, w_mn_sbo);
+            umma_bf16(tmem + t * BN, da, db, idesc, (tap | ks) ? 1u : 0u);
+          }
+        }
+        umma_commit(smem_u32(wempty + s));
+      }
+      umma_commit(smem_u32(accum));
+    }
+    __syncwarp();
+  }
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    tmem_dealloc(tmem, tmem_cols);
+  }
+}
+
+int pick_ipc(int B, int H, int W, int KC) {
+  // more images per CTA = fewer wasted rows and less filter re-streaming, but fewer CTAs; keep
+  // the grid at or above one wave of the 148 SMs while TMEM (tiles*64 <= 512) and smem allow
+  int best = 1;
+  for (int ipc : {2, 4}) {
+    ConvGeom g = make_geom(B, H, W, KC, 64, ipc);
+    int64_t smem = (int64_t)(KC / 8) * g.ch_stride + WSTAGES * 9000 + 1024;
+    if (g.tiles * 64 <= 512 && smem <= 200 * 1024 && (B + ipc - 1) / ipc >= 2 * kNumSMs) best = ipc;
+  }
+  return best;
+}
+
+template <bool DGRAD>
+int launch_conv(const float* x, const float* w, const float* bias, float* y, int B, int H, int W, int KC, int NC,
+                int relu, cudaStream_t st) {
+  B200_REQUIRE(B > 0 && H > 0 && W > 0, "conv5x5_tc: bad shape");
+  B200_REQUIRE(KC % 16 == 0 && NC % 64 == 0, "conv5x5_tc: channels must be multiples of 16 (in) / 64 (out), got %d/%d",
+               KC, NC);
+  B200_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)w & 15) == 0 && ((uintptr_t)y & 15) == 0,
+               "conv5x5_tc: pointers must be 16-byte aligned");
+  int ipc = pick_ipc(B, H, W, KC);
+  ConvGeom g = make_geom(B, H, W, KC, NC, ipc);
+  B200_REQUIRE(g.tiles * 64 <= 512, "conv5x5_tc: image %dx%d too large for one CTA's TMEM", H, W);
+  const int kchunks = KC / 8;
+  const int wstage = ((DGRAD ? kchunks * (64 * 16 + 16) : 8 * (KC * 16 + 16)) + 127) & ~127;
+  const int smem = ((kchunks * g.ch_stride + 127) & ~127) + WSTAGES * wstage + 256;
+  B200_REQUIRE(smem <= 227 * 1024, "conv5x5_tc: %d bytes of shared memory needed", smem);
+  auto kern = conv5x5_tc_kernel<DGRAD>;
+  static int attr = 0;
+  if (attr < smem) {
+    B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr = 227 * 1024;
+  }
+  ConvArgs a{x, w, bias, y, relu, g};
+  dim3 grid(cdiv(B, ipc), NC / 64);
+  kern<<<grid, 160, smem, st>>>(a);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// filter gradient.  grid = (5 filter rows, S image splits); each CTA accumulates the 5 taps of
+// one filter row (5 x [64 cin x 64 cout] fp32 in TMEM, M = 64 MMAs) over its share of the images,
+// double-buffering the x / dy strips, and writes one partial; a second kernel sums the S partials
+// in a fixed order (deterministic).
+// ---------------------------------------------------------------------------------------------------
+struct WgradArgs {
+  const float* x;      // [B,H,W,64]
+  const float* dy;     // [B,H,W,64]
+  float* partial;      // [S][25][64][64]
+  ConvGeom g;          // ipc = 1
+  int imgs_per_cta;
+  int nbuf;             // 2 = double-buffered strips, 1 when two pairs do not fit in shared memory
+};
+
+__global__ void __launch_bounds__(160, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
+  constexpr int C = 64;
+  const ConvGeom& g = a.g;
+  extern __shared__ __align__(128) uint8_t smem[];
+  const int strip_bytes = ((C / 8) * g.ch_stride + 127) & ~127;
+  uint8_t* ctrl = smem + 2 * a.nbuf * strip_bytes;        // [buf][x | dy]
+  uint64_t* full = reinterpret_cast<uint64_t*>(ctrl);
+  uint64_t* empty = full + 2;
+  uint64_t* accum = empty + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum + 1);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int di = blockIdx.x;
+  const int img_beg = blockIdx.y * a.imgs_per_cta;
+  const int img_end = min(g.B, img_beg + a.imgs_per_cta);
+  const int nimg = max(0, img_end - img_beg);
+  const int ksteps = (g.rows_per_img * g.P + 15) / 16;
+
+  if (tid == 0) {
+    for (int s = 0; s < 2; ++s) { mbar_init(smem_u32(full + s), LOADERS); mbar_init(smem_u32(empty + s), 1); }
+    mbar_init(smem_u32(accum), 1);
+    fence_mbar_init();
+  }
+  if (warp == 4) tmem_alloc(smem_u32(tmem_slot), 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp < 4) {
+    zero_smem(smem, 2 * a.nbuf * strip_bytes, tid);      // pads stay zero for every image: fills touch valid pixels only
+    loaders_sync();
+    for (int it = 0; it < nimg; ++it) {
+      const int b = it % a.nbuf;
+      const uint32_t ph = (it / a.nbuf) & 1;
+      mbar_wait(smem_u32(empty + b), ph ^ 1);
+      uint8_t* xs = smem + (2 * b) * strip_bytes;
+      uint8_t* ds = xs + strip_bytes;
+      fill_strip(xs, a.x, g, img_beg + it, C, g.ch_stride, tid);
+      fill_strip(ds, a.dy, g, img_beg + it, C, g.ch_stride, tid);
+      fence_proxy_async();
+      mbar_arrive(smem_u32(full + b));
+    }
+    // ---- epilogue: M = 64 accumulators live in lanes 0-15 of each 32-lane subpartition --------------
+    mbar_wait(smem_u32(accum), 0);
+    tc_fence_after();
+    float* part = a.partial + (int64_t)blockIdx.y * 25 * C * C;
+    for (int dj = 0; dj < 5; ++dj) {
+#pragma unroll 1
+      for (int c0 = 0; c0 < C; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + dj * C + c0, v);
+        tmem_ld_wait();
+        if (lane < 16) {
+          const int cin = warp * 16 + lane;
+          float* out = part + ((int64_t)(di * 5 + dj) * C + cin) * C + c0;
+#pragma unroll
+          for (int j = 0; j < 32; j += 4)
+            *reinterpret_cast<float4*>(out + j) =
+                (nimg > 0) ? make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]),
+                                         __uint_as_float(v[j + 3]))
+                           : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      }
+    }
+    tc_fence_before();
+  } else {
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc(64, C, true, true);
+      for (int it = 0; it < nimg; ++it) {
+        const int b = it % a.nbuf;
+        const uint32_t ph = (it / a.nbuf) & 1;
+        mbar_wait(smem_u32(full + b), ph);
+        tc_fence_after();
+        const uint32_t xs = smem_u32(smem + (2 * b) * strip_bytes);
+        const uint32_t ds = xs + strip_bytes;
+        for (int dj = 0; dj < 5; ++dj) {
+          const int slot0 = g.lead + (di - 2) * g.P + (dj - 2);
+          for (int ks = 0; ks < ksteps; ++ks) {
+            uint64_t da = make_desc(xs + (slot0 + ks * 16) * 16, 128, g.ch_stride);
+            uint64_t db = make_desc(ds + (g.lead + ks * 16) * 16, 128, g.ch_stride);
+            umma_bf16(tmem + dj * C, da, db, idesc, (it | ks) ? 1u : 0u);
+          }
+        }
+        umma_commit(smem_u32(empty + b));
+      }
+      umma_commit(smem_u32(accum));   // with nimg == 0 nothing was issued: the commit arrives at once
+    }
+    __syncwarp();
+  }
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 512);
+  }
+}
+
+__global__ void reduce_partials_tc(const float* __restrict__ part, float* __restrict__ out, int n, int S) {
+  int i = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i >= n) return;
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int z = 0; z < S; ++z) {
+    float4 v = __ldg(reinterpret_cast<const float4*>(part + (int64_t)z * n + i));
+    s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+  }
+  *reinterpret_cast<float4*>(out + i) = s;
+}
+
+int wgrad_splits_tc(int B) { return std::max(1, std::min(B, (kNumSMs + 4) / 5)); }
+}  // namespace
+
+int conv5x5_fwd_tc(const float* x, const float* w, const float* bias, float* y, int B, int H, int W, int Cin,
+                   int Cout, int relu, cudaStream_t st) {
+  return launch_conv<false>(x, w, bias, y, B, H, W, Cin, Cout, relu, st);
+}
+// dx = Conv2DBackpropInput(dy, w): contraction over the forward Cout, output the forward Cin
+int conv5x5_dgrad_tc(const float* dy, const float* w, float* dx, int B, int H, int W, int Cin, int Cout,
+                     cudaStream_t st) {
+  return launch_conv<true>(dy, w, nullptr, dx, B, H, W, Cout, Cin, 0, st);
+}
+int64_t conv5x5_wgrad_tc_scratch_bytes(int B) { return (int64_t)wgrad_splits_tc(B) * 25 * 64 * 64 * 4; }
+int conv5x5_wgrad_tc(const float* x, const float* dy, float* dw, float* scratch, int B, int H, int W, int Cin,
+                     int Cout, cudaStream_t st) {
+  B200_REQUIRE(Cin == 64 && Cout == 64, "conv5x5_wgrad_tc: only 64 -> 64 channels (got %d -> %d)", Cin, Cout);
+  B200_REQUIRE(B > 0 && H > 0 && W > 0, "conv5x5_wgrad_tc: bad shape");
+  ConvGeom g = make_geom(B, H, W, 64, 64, 1);
+  const int strip_bytes = ((8 * g.ch_stride) + 127) & ~127;
+  const int nbuf = (4 * strip_bytes + 256 <= 227 * 1024) ? 2 : 1;
+  const int smem = 2 * nbuf * strip_bytes + 256;
+  B200_REQUIRE(smem <= 227 * 1024, "conv5x5_wgrad_tc: image %dx%d needs %d bytes of shared memory", H, W, smem);
+  static bool attr = false;
+  if (!attr) {
+    B200_CUDA_TRY(cudaFuncSetAttribute(conv5x5_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       227 * 1024));
+    attr = true;
+  }
+  int S = wgrad_splits_tc(B);
+  int per = cdiv(B, S);
+  S = cdiv(B, per);
+  WgradArgs a{x, dy, scratch, g, per, nbuf};
+  conv5x5_wgrad_tc_kernel<<<dim3(5, S), 160, smem, st>>>(a);
+  B200_LAUNCH_CHECK();
+  const int n = 25 * 64 * 64;
+  reduce_partials_tc<<<cdiv(n / 4, 256), 256, 0, st>>>(scratch, dw, n, S);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+}  // namespace b200

@@ -143,6 +143,17 @@ int b200_colsum_scratch_bytes(int32_t rows, int32_t cols, int64_t* nbytes);
 int b200_fc_bwd_f32(const float* x, const float* w, const float* dy, float* dx, float* dw, float* db,
                     void* scratch, int64_t scratch_bytes, int32_t batch, int32_t k, int32_t n,
                     int32_t mask_x, void* stream);
+/* conv2d / Conv2DBackpropInput / Conv2DBackpropFilter of :118 on the tensor cores (tcgen05 implicit
+ * GEMM over a zero-padded shared-memory strip; bf16 operands rounded from the fp32 tensors, fp32
+ * accumulation).  c_in % 16 == 0 and c_out % 64 == 0 (wgrad: 64 -> 64 only).  The wgrad scratch
+ * holds per-CTA partial sums that a second kernel adds in a fixed order. */
+int b200_conv5x5_fwd_bf16(const float* x, const float* w, const float* bias, float* y, int32_t batch, int32_t h,
+                          int32_t wd, int32_t c_in, int32_t c_out, int32_t relu, void* stream);
+int b200_conv5x5_dgrad_bf16(const float* dy, const float* w, float* dx, int32_t batch, int32_t h, int32_t wd,
+                            int32_t c_in, int32_t c_out, void* stream);
+int b200_conv5x5_wgrad_bf16_scratch_bytes(int32_t batch, int64_t* nbytes);
+int b200_conv5x5_wgrad_bf16(const float* x, const float* dy, float* dw, void* scratch, int64_t scratch_bytes,
+                            int32_t batch, int32_t h, int32_t wd, int32_t c_in, int32_t c_out, void* stream);
 /* The same two products on the tensor cores (tcgen05, bf16 operands rounded from the fp32 tensors
  * on the fly, fp32 accumulation in TMEM).  batch, k and n must be multiples of 8. */
 int b200_fc_fwd_bf16(const float* x, const float* w, const float* b, float* y, int32_t batch, int32_t k, int32_t n,

@@ -81,3 +81,72 @@ def test_fc_tensorcore_rejects_unaligned(lib):
     w = torch.zeros(33, 7, device="cuda")
     y = torch.zeros(5, 7, device="cuda")
     assert lib.b200_fc_fwd_bf16(x.data_ptr(), w.data_ptr(), None, y.data_ptr(), 5, 33, 7, 1, stream()) == _lib.E_INVALID
+
+
+@pytest.mark.parametrize("B,H,W", [(3, 12, 12), (128, 12, 12), (5, 16, 16), (2, 6, 6)])
+def test_conv_tensorcore_fwd_dgrad_wgrad(lib, B, H, W):
+    """conv2 of cifar10cnn.py:118 (64 -> 64 channels) on tcgen05: forward (+bias+ReLU), input
+    gradient and filter gradient against the oracle on bf16-rounded operands (tight) and on the
+    fp32 operands (loose)."""
+    Cin = Cout = 64
+    rng = np.random.default_rng(31)
+    x = np.maximum(rng.normal(size=(B, H, W, Cin)), 0).astype(np.float32)
+    w = (rng.normal(size=(5, 5, Cin, Cout)) * 0.05).astype(np.float32)
+    b = rng.normal(size=(Cout,)).astype(np.float32)
+    dy = (rng.normal(size=(B, H, W, Cout)) * (rng.random(size=(B, H, W, Cout)) < 0.3)).astype(np.float32)
+    xd, wd, bd, dyd = dev(x), dev(w), dev(b), dev(dy)
+    xr, wr, dyr = bf16_round(x), bf16_round(w), bf16_round(dy)
+    y = torch.full((B, H, W, Cout), float("nan"), device="cuda")
+    _lib.check(lib.b200_conv5x5_fwd_bf16(xd.data_ptr(), wd.data_ptr(), bd.data_ptr(), y.data_ptr(), B, H, W, Cin, Cout,
+                                         1, stream()))
+    torch.cuda.synchronize()
+    assert relerr(y.cpu().numpy(), np.maximum(rn.conv2d_same(xr, wr) + b, 0)) <= TIGHT
+    assert relerr(y.cpu().numpy(), np.maximum(rn.conv2d_same(x.astype(np.float64), w.astype(np.float64)) + b, 0)) <= LOOSE
+    _lib.check(lib.b200_conv5x5_fwd_bf16(xd.data_ptr(), wd.data_ptr(), None, y.data_ptr(), B, H, W, Cin, Cout, 0,
+                                         stream()))
+    torch.cuda.synchronize()
+    assert relerr(y.cpu().numpy(), rn.conv2d_same(xr, wr)) <= TIGHT
+    dx = torch.full((B, H, W, Cin), float("nan"), device="cuda")
+    _lib.check(lib.b200_conv5x5_dgrad_bf16(dyd.data_ptr(), wd.data_ptr(), dx.data_ptr(), B, H, W, Cin, Cout, stream()))
+    torch.cuda.synchronize()
+    assert relerr(dx.cpu().numpy(), rn.conv2d_same_grad_input(dyr, wr)) <= TIGHT
+    assert relerr(dx.cpu().numpy(), rn.conv2d_same_grad_input(dy.astype(np.float64), w.astype(np.float64))) <= LOOSE
+    nb = C.c_int64()
+    _lib.check(lib.b200_conv5x5_wgrad_bf16_scratch_bytes(B, C.byref(nb)))
+    scr = torch.empty(nb.value, dtype=torch.uint8, device="cuda")
+    dw = torch.full((5, 5, Cin, Cout), float("nan"), device="cuda")
+    for _ in range(2):      # twice: the scratch is reused, nothing may depend on its old contents
+        _lib.check(lib.b200_conv5x5_wgrad_bf16(xd.data_ptr(), dyd.data_ptr(), dw.data_ptr(), scr.data_ptr(), nb.value,
+                                               B, H, W, Cin, Cout, stream()))
+        torch.cuda.synchronize()
+        assert relerr(dw.cpu().numpy(), rn.conv2d_same_grad_filter(xr, dyr)) <= TIGHT
+    assert relerr(dw.cpu().numpy(), rn.conv2d_same_grad_filter(x.astype(np.float64), dy.astype(np.float64))) <= LOOSE
+    assert lib.b200_conv5x5_wgrad_bf16(xd.data_ptr(), dyd.data_ptr(), dw.data_ptr(), scr.data_ptr(), 16, B, H, W, Cin,
+                                       Cout, stream()) == _lib.E_INVALID
+
+
+def test_conv_tensorcore_rectangular_and_asymmetric_channels(lib):
+    """forward / dgrad with Cin != Cout and H != W (catches transposed-index slips)."""
+    B, H, W, Cin, Cout = 4, 9, 12, 32, 128
+    rng = np.random.default_rng(32)
+    x = rng.normal(size=(B, H, W, Cin)).astype(np.float32)
+    w = (rng.normal(size=(5, 5, Cin, Cout)) * 0.05).astype(np.float32)
+    dy = rng.normal(size=(B, H, W, Cout)).astype(np.float32)
+    xd, wd, dyd = dev(x), dev(w), dev(dy)
+    xr, wr, dyr = bf16_round(x), bf16_round(w), bf16_round(dy)
+    y = torch.full((B, H, W, Cout), float("nan"), device="cuda")
+    _lib.check(lib.b200_conv5x5_fwd_bf16(xd.data_ptr(), wd.data_ptr(), None, y.data_ptr(), B, H, W, Cin, Cout, 0,
+                                         stream()))
+    dx = torch.full((B, H, W, Cin), float("nan"), device="cuda")
+    assert lib.b200_conv5x5_dgrad_bf16(dyd.data_ptr(), wd.data_ptr(), dx.data_ptr(), B, H, W, Cin, Cout,
+                                       stream()) == _lib.E_INVALID      # output channels (Cin=32) not a multiple of 64
+    torch.cuda.synchronize()
+    assert relerr(y.cpu().numpy(), rn.conv2d_same(xr, wr)) <= TIGHT
+    B, H, W, Cin, Cout = 4, 9, 12, 64, 32
+    w = (rng.normal(size=(5, 5, Cin, Cout)) * 0.05).astype(np.float32)
+    dy = rng.normal(size=(B, H, W, Cout)).astype(np.float32)
+    dx = torch.full((B, H, W, Cin), float("nan"), device="cuda")
+    _lib.check(lib.b200_conv5x5_dgrad_bf16(dev(dy).data_ptr(), dev(w).data_ptr(), dx.data_ptr(), B, H, W, Cin, Cout,
+                                           stream()))
+    torch.cuda.synchronize()
+    assert relerr(dx.cpu().numpy(), rn.conv2d_same_grad_input(bf16_round(dy), bf16_round(w))) <= TIGHT
