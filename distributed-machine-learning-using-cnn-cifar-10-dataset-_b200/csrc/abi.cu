@@ -85,7 +85,10 @@ int b200_create(const b200_config* c, b200_handle* out) {
   B200_REQUIRE(c->c1 % 4 == 0 && c->c2 % 4 == 0 && c->f1 % 4 == 0 && c->f2 % 4 == 0,
                "b200_create: channel / FC widths must be multiples of 4");
   B200_REQUIRE(c->n_cls > 0 && c->n_cls <= 16, "b200_create: n_cls must be in 1..16");
-  B200_REQUIRE(c->mode == B200_MODE_FP32, "b200_create: mode %d not available in this build", c->mode);
+  B200_REQUIRE(c->mode == B200_MODE_FP32 || c->mode == B200_MODE_BF16, "b200_create: unknown mode %d", c->mode);
+  if (c->mode == B200_MODE_BF16)
+    B200_REQUIRE(c->batch % 8 == 0 && c->c1 == 64 && c->c2 == 64 && c->f1 % 8 == 0 && c->f2 % 8 == 0,
+                 "b200_create: bf16 mode needs batch %% 8 == 0, 64/64 conv channels and FC widths %% 8 == 0");
   b200_model* h = new (std::nothrow) b200_model();
   B200_REQUIRE(h, "b200_create: out of host memory");
   h->cfg = *c;
@@ -117,6 +120,8 @@ int b200_create(const b200_config* c, b200_handle* out) {
   int64_t scratch = conv5x5_wgrad_scratch_bytes(c->batch, c->crop_h, c->crop_w, c->c_in, c->c1);
   scratch = std::max(scratch, conv5x5_wgrad_scratch_bytes(c->batch, h->h1, h->w1, c->c1, c->c2));
   scratch = std::max(scratch, colsum_scratch_bytes(c->batch, std::max(c->f1, std::max(c->f2, c->n_cls))));
+  scratch = std::max(scratch, conv5x5_wgrad_tc_scratch_bytes(c->batch) +
+                                  colsum_scratch_bytes(c->batch * h->h1 * h->w1, c->c2));
   h->add("scratch", scratch, 1);
   h->add("loss", 1, 4); h->add("n_correct", 1, 4); h->add("n_bad", 1, 4); h->add("pred", B, 4);
   h->add("stage_images", B * c->c_in * c->img_h * c->img_w, 1);
@@ -198,6 +203,7 @@ int b200_forward(b200_handle h, const uint8_t* images, const int32_t* labels, vo
   B200_REQUIRE(images && labels, "forward: null input");
   cudaStream_t st = (cudaStream_t)stream;
   const b200_config& c = h->cfg;
+  const bool tc = c.mode == B200_MODE_BF16;
   float* x = h->ptr<float>("x");
   float *conv1 = h->ptr<float>("conv1"), *pool1 = h->ptr<float>("pool1");
   float *conv2 = h->ptr<float>("conv2"), *pool2 = h->ptr<float>("pool2");
@@ -205,10 +211,18 @@ int b200_forward(b200_handle h, const uint8_t* images, const int32_t* labels, vo
   SITE("crop_cast", crop_cast_f32(images, x, c.batch, c.img_h, c.img_w, c.crop_h, c.crop_w, c.c_in, st));
   SITE("conv1_fwd", conv5x5_fwd_f32(x, h->P(P_W1), h->P(P_B1), conv1, c.batch, c.crop_h, c.crop_w, c.c_in, c.c1, 1, st));
   SITE("pool1_fwd", maxpool_fwd_f32(conv1, pool1, h->ptr<uint8_t>("arg1"), c.batch, c.crop_h, c.crop_w, c.c1, st));
-  SITE("conv2_fwd", conv5x5_fwd_f32(pool1, h->P(P_W2), h->P(P_B2), conv2, c.batch, h->h1, h->w1, c.c1, c.c2, 1, st));
+  if (tc)
+    SITE("conv2_fwd", conv5x5_fwd_tc(pool1, h->P(P_W2), h->P(P_B2), conv2, c.batch, h->h1, h->w1, c.c1, c.c2, 1, st));
+  else
+    SITE("conv2_fwd", conv5x5_fwd_f32(pool1, h->P(P_W2), h->P(P_B2), conv2, c.batch, h->h1, h->w1, c.c1, c.c2, 1, st));
   SITE("pool2_fwd", maxpool_fwd_f32(conv2, pool2, h->ptr<uint8_t>("arg2"), c.batch, h->h1, h->w1, c.c2, st));
-  SITE("full1_fwd", fc_fwd_f32(pool2, h->P(P_FW1), h->P(P_FB1), full1, c.batch, h->flat, c.f1, 1, st));
-  SITE("full2_fwd", fc_fwd_f32(full1, h->P(P_FW2), h->P(P_FB2), full2, c.batch, c.f1, c.f2, 1, st));
+  if (tc) {
+    SITE("full1_fwd", fc_fwd_tc(pool2, h->P(P_FW1), h->P(P_FB1), full1, c.batch, h->flat, c.f1, 1, st));
+    SITE("full2_fwd", fc_fwd_tc(full1, h->P(P_FW2), h->P(P_FB2), full2, c.batch, c.f1, c.f2, 1, st));
+  } else {
+    SITE("full1_fwd", fc_fwd_f32(pool2, h->P(P_FW1), h->P(P_FB1), full1, c.batch, h->flat, c.f1, 1, st));
+    SITE("full2_fwd", fc_fwd_f32(full1, h->P(P_FW2), h->P(P_FB2), full2, c.batch, c.f1, c.f2, 1, st));
+  }
   SITE("full3_fwd", fc_fwd_f32(full2, h->P(P_FW3), h->P(P_FB3), logits, c.batch, c.f2, c.n_cls, 1, st));
   SITE("head", head_f32(logits, labels, h->ptr<float>("loss"), h->ptr<float>("dlogits"), h->ptr<int32_t>("pred"),
                h->ptr<int32_t>("n_correct"), h->ptr<int32_t>("n_bad"), c.batch, c.n_cls, st));
@@ -224,22 +238,41 @@ int b200_backward(b200_handle h, void* stream) {
   }
   cudaStream_t st = (cudaStream_t)stream;
   const b200_config& c = h->cfg;
+  const bool tc = c.mode == B200_MODE_BF16;
   float* scratch = h->ptr<float>("scratch");
   float *dlogits = h->ptr<float>("dlogits"), *dfull2 = h->ptr<float>("dfull2"), *dfull1 = h->ptr<float>("dfull1");
   float *dpool2 = h->ptr<float>("dpool2"), *dconv2 = h->ptr<float>("dconv2");
   float *dpool1 = h->ptr<float>("dpool1"), *dconv1 = h->ptr<float>("dconv1");
   SITE("full3_bwd", fc_bwd_f32(h->ptr<float>("full2"), h->P(P_FW3), dlogits, dfull2, h->G(P_FW3), h->G(P_FB3), scratch,
                  c.batch, c.f2, c.n_cls, 1, st));
-  SITE("full2_bwd", fc_bwd_f32(h->ptr<float>("full1"), h->P(P_FW2), dfull2, dfull1, h->G(P_FW2), h->G(P_FB2), scratch,
-                 c.batch, c.f1, c.f2, 1, st));
-  SITE("full1_bwd", fc_bwd_f32(h->ptr<float>("pool2"), h->P(P_FW1), dfull1, dpool2, h->G(P_FW1), h->G(P_FB1), scratch,
-                 c.batch, h->flat, c.f1, 0, st));
+  if (tc) {
+    SITE("full2_bwd", fc_bwd_tc(h->ptr<float>("full1"), h->P(P_FW2), dfull2, dfull1, h->G(P_FW2), c.batch, c.f1, c.f2,
+                                1, st));
+    SITE("full2_bias", colsum_f32(dfull2, h->G(P_FB2), scratch, c.batch, c.f2, st));
+    SITE("full1_bwd", fc_bwd_tc(h->ptr<float>("pool2"), h->P(P_FW1), dfull1, dpool2, h->G(P_FW1), c.batch, h->flat,
+                                c.f1, 0, st));
+    SITE("full1_bias", colsum_f32(dfull1, h->G(P_FB1), scratch, c.batch, c.f1, st));
+  } else {
+    SITE("full2_bwd", fc_bwd_f32(h->ptr<float>("full1"), h->P(P_FW2), dfull2, dfull1, h->G(P_FW2), h->G(P_FB2), scratch,
+                                 c.batch, c.f1, c.f2, 1, st));
+    SITE("full1_bwd", fc_bwd_f32(h->ptr<float>("pool2"), h->P(P_FW1), dfull1, dpool2, h->G(P_FW1), h->G(P_FB1), scratch,
+                                 c.batch, h->flat, c.f1, 0, st));
+  }
   SITE("pool2_bwd", maxpool_bwd_f32(dpool2, h->ptr<uint8_t>("arg2"), h->ptr<float>("conv2"), dconv2, c.batch, h->h1, h->w1,
                       c.c2, 1, st));
-  SITE("conv2_wgrad", conv5x5_wgrad_f32(h->ptr<float>("pool1"), dconv2, h->G(P_W2), h->G(P_B2), scratch, c.batch, h->h1, h->w1,
-                        c.c1, c.c2, st));
-  SITE("conv2_dgrad_prep", conv5x5_rot180_f32(h->P(P_W2), h->ptr<float>("wrot"), c.c1, c.c2, st));
-  SITE("conv2_dgrad", conv5x5_fwd_f32(dconv2, h->ptr<float>("wrot"), nullptr, dpool1, c.batch, h->h1, h->w1, c.c2, c.c1, 0, st));
+  if (tc) {
+    SITE("conv2_wgrad", conv5x5_wgrad_tc(h->ptr<float>("pool1"), dconv2, h->G(P_W2), scratch, c.batch, h->h1, h->w1,
+                                         c.c1, c.c2, st));
+    SITE("conv2_bias", colsum_f32(dconv2, h->G(P_B2), scratch + conv5x5_wgrad_tc_scratch_bytes(c.batch) / 4,
+                                  c.batch * h->h1 * h->w1, c.c2, st));
+    SITE("conv2_dgrad", conv5x5_dgrad_tc(dconv2, h->P(P_W2), dpool1, c.batch, h->h1, h->w1, c.c1, c.c2, st));
+  } else {
+    SITE("conv2_wgrad", conv5x5_wgrad_f32(h->ptr<float>("pool1"), dconv2, h->G(P_W2), h->G(P_B2), scratch, c.batch,
+                                          h->h1, h->w1, c.c1, c.c2, st));
+    SITE("conv2_dgrad_prep", conv5x5_rot180_f32(h->P(P_W2), h->ptr<float>("wrot"), c.c1, c.c2, st));
+    SITE("conv2_dgrad", conv5x5_fwd_f32(dconv2, h->ptr<float>("wrot"), nullptr, dpool1, c.batch, h->h1, h->w1, c.c2,
+                                        c.c1, 0, st));
+  }
   SITE("pool1_bwd", maxpool_bwd_f32(dpool1, h->ptr<uint8_t>("arg1"), h->ptr<float>("conv1"), dconv1, c.batch, c.crop_h,
                       c.crop_w, c.c1, 1, st));
   SITE("conv1_wgrad", conv5x5_wgrad_f32(h->ptr<float>("x"), dconv1, h->G(P_W1), h->G(P_B1), scratch, c.batch, c.crop_h,
@@ -324,6 +357,7 @@ int b200_launches_per_step(b200_handle h, int32_t* n) {
   // forward 9; fc_bwd 3 x (dw, colsum x2, dx); pool bwd x2; conv wgrad 2 x (gemm, reduce, colsum x2);
   // dgrad (rot180 + gemm); sgd
   *n = 9 + 12 + 2 + 8 + 2 + 1;
+  if (h->cfg.mode == B200_MODE_BF16) *n = 9 + (4 + 4 + 4) + 2 + (2 + 2 + 1) + 4 + 1;
   return B200_OK;
 }
 

@@ -150,3 +150,39 @@ def test_conv_tensorcore_rectangular_and_asymmetric_channels(lib):
                                            stream()))
     torch.cuda.synchronize()
     assert relerr(dx.cpu().numpy(), rn.conv2d_same_grad_input(bf16_round(dy), bf16_round(w))) <= TIGHT
+
+
+@pytest.mark.parametrize("kind", ["u8", "soft"])
+def test_full_step_bf16_mode_b128(kind):
+    """BASELINE.json config 3 numerics: the whole step in bf16 mode (tensor-core conv2 / FC1 / FC2,
+    fp32 everywhere else, fp32 master weights) against the fp64 oracle.  Stated bounds: forward
+    tensors and loss within 1e-2 of max-abs; gradients within 2e-2 of the oracle's backward
+    evaluated on the GPU's own forward tensors (see test_gpu_parity for why); argmax bit-exact
+    wherever the oracle's top-2 logit gap exceeds the forward bound."""
+    import b200cnn
+    from test_gpu_parity import _oracle_backward_on_gpu_forward
+    rng = np.random.default_rng(41)
+    B = 128
+    if kind == "u8":
+        img = rng.integers(0, 256, (B, 3, 32, 32), dtype=np.uint8)
+    else:
+        img = np.clip(np.rint(rng.normal(8.0, 2.5, (B, 3, 32, 32))), 0, 255).astype(np.uint8)
+    lab = rng.integers(0, 10, (B, 1)).astype(np.int32)
+    params = rn.init_params(0)
+    _, loss, g, a = rn.train_step(params, img, lab, lr=np.float32(0.1))
+    e = b200cnn.TrainStepEngine(batch=B, mode="bf16")
+    e.load_params(params)
+    e.forward(dev(img), dev(lab.reshape(-1)))
+    e.backward()
+    torch.cuda.synchronize()
+    for name in ("conv1", "pool1", "conv2", "pool2", "full1", "full2", "logits"):
+        assert relerr(e.tensor(name).cpu().numpy().reshape(a[name].shape), a[name]) <= LOOSE, name
+    assert abs(float(e.loss()) - loss) <= 2e-2 * abs(loss)
+    srt = np.sort(a["logits"], axis=1)
+    safe = (srt[:, -1] - srt[:, -2]) > 2 * LOOSE * np.abs(a["logits"]).max()
+    np.testing.assert_array_equal(e.pred().cpu().numpy()[safe], a["pred"][safe])
+    assert safe.mean() > 0.5
+    g2, a2 = _oracle_backward_on_gpu_forward(e, params, lab, a)
+    got = e.get_grads()
+    for k in rn.PARAM_NAMES:
+        assert relerr(got[k], g2[k]) <= 2e-2, (k, relerr(got[k], g2[k]))
