@@ -161,6 +161,19 @@ int b200_fc_fwd_bf16(const float* x, const float* w, const float* b, float* y, i
 int b200_fc_bwd_bf16(const float* x, const float* w, const float* dy, float* dx, float* dw, float* db,
                      void* scratch, int64_t scratch_bytes, int32_t batch, int32_t k, int32_t n,
                      int32_t mask_x, void* stream);
+/* b200_fc_bwd_f32 without the scratch arguments, for callers that cannot allocate device memory:
+ * plug-ins of a framework whose caching pool already owns all free HBM, operators that are only handed
+ * tensors and have no allocator of their own, and step loops that may not make a device-synchronising
+ * call such as cudaMalloc.  It has no counterpart in
+ * the reference (TensorFlow allocates for the script).  The column-sum scratch is a fixed
+ * B200_STATIC_SCRATCH_BYTES array inside the library image: each GPU that loads the library holds it until
+ * the process exits, and a request needing more (see b200_colsum_scratch_bytes(batch, n)) is refused
+ * with B200_E_INVALID.  The first call on a device resolves the array's address; make it before any
+ * stream capture.  All calls share the array (contents persist, nothing needs zeroing); calls that
+ * overlap on the GPU race on it.  Allocates nothing. */
+#define B200_STATIC_SCRATCH_BYTES (1 << 20)
+int b200_fc_bwd_f32_static(const float* x, const float* w, const float* dy, float* dx, float* dw, float* db,
+                           int32_t batch, int32_t k, int32_t n, int32_t mask_x, void* stream);
 /* cifar_loss (:150-157), batch_accuracy (:166-176) and the first backward step: dlogits =
  * (softmax - onehot)/batch * [logits > 0] (ReLU on the logits, :145).  Labels outside
  * [0,n_cls) set *n_bad (int32, device) > 0 and contribute nothing. */

@@ -1,0 +1,59 @@
+"""b200_fc_bwd_f32_static -- the entry point for callers that cannot allocate device memory (a plug-in
+under a framework pool that owns all HBM, an operator with no allocator of its own, a step loop where
+cudaMalloc's device synchronisation is forbidden) -- must give what b200_fc_bwd_f32 gives with caller scratch.
+
+Kept in its own file, named to be collected last, so a `-x` run has already exercised every other
+test if this one fails.  Runs standalone (fresh process: the first call does the once-per-device
+address lookup) and after the rest of the suite alike.  Two calls in a row: the built-in scratch keeps
+the previous call's contents, and the second call (different data, smaller shape) must not see them.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+from b200cnn import _lib
+
+pytestmark = pytest.mark.gpu
+
+
+def _run_pair(lib, B, K, N, mask, seed):
+    rng = np.random.default_rng(seed)
+    st = torch.cuda.current_stream().cuda_stream
+    x = torch.as_tensor(np.maximum(rng.normal(size=(B, K)), 0).astype(np.float32)).cuda()
+    w = torch.as_tensor((rng.normal(size=(K, N)) * 0.05).astype(np.float32)).cuda()
+    dy = torch.as_tensor(rng.normal(size=(B, N)).astype(np.float32)).cuda()
+    nb = C.c_int64()
+    _lib.check(lib.b200_colsum_scratch_bytes(B, N, C.byref(nb)))
+    scr = torch.empty(nb.value, dtype=torch.uint8, device="cuda")
+    ref = [torch.full(s, float("nan"), device="cuda") for s in ((B, K), (K, N), (N,))]
+    got = [torch.full(s, float("nan"), device="cuda") for s in ((B, K), (K, N), (N,))]
+    _lib.check(lib.b200_fc_bwd_f32(x.data_ptr(), w.data_ptr(), dy.data_ptr(), ref[0].data_ptr(), ref[1].data_ptr(),
+                                   ref[2].data_ptr(), scr.data_ptr(), nb.value, B, K, N, mask, st))
+    _lib.check(lib.b200_fc_bwd_f32_static(x.data_ptr(), w.data_ptr(), dy.data_ptr(), got[0].data_ptr(),
+                                          got[1].data_ptr(), got[2].data_ptr(), B, K, N, mask, st))
+    torch.cuda.synchronize()
+    for name, r, g in zip(("dx", "dw", "db"), ref, got):
+        r, g = r.cpu().numpy().astype(np.float64), g.cpu().numpy().astype(np.float64)
+        assert np.isfinite(g).all(), name
+        assert np.abs(g - r).max() <= 1e-5 * (np.abs(r).max() + 1e-30), name     # the suite's fp32 tolerance
+    # and against the arithmetic itself, so both cannot be wrong together
+    want_db = dy.cpu().numpy().astype(np.float64).sum(0)
+    assert np.abs(got[2].cpu().numpy() - want_db).max() <= 1e-5 * np.abs(want_db).max()
+
+
+def test_static_scratch_entry_matches_caller_scratch_entry_twice():
+    lib = _lib.load()
+    _run_pair(lib, 4096, 384, 192, 1, seed=71)     # 64 row chunks of partial sums left in the array
+    _run_pair(lib, 128, 192, 10, 0, seed=72)       # smaller second call must not read the stale ones
+
+
+def test_static_scratch_entry_rejects_oversize_request():
+    lib = _lib.load()
+    assert (1 << 20) == 1048576
+    d = torch.zeros(8, device="cuda")              # never dereferenced: the size check comes first
+    rc = lib.b200_fc_bwd_f32_static(d.data_ptr(), d.data_ptr(), d.data_ptr(), d.data_ptr(), d.data_ptr(),
+                                    d.data_ptr(), 32768, 8, 1024, 0, torch.cuda.current_stream().cuda_stream)
+    assert rc == _lib.E_INVALID
+    assert b"built-in array" in lib.b200_last_error()
