@@ -420,6 +420,26 @@ int b200_fc_bwd_f32(const float* x, const float* w, const float* dy, float* dx, 
   B200_REQUIRE(!db || (scratch && scratch_bytes >= colsum_scratch_bytes(batch, n)), "scratch too small");
   return fc_bwd_f32(x, w, dy, dx, dw, db, (float*)scratch, batch, k, n, mask_x, (cudaStream_t)stream);
 }
+int b200_conv1_pool_fwd_bf16(const uint8_t* images, const float* w, const float* bias, float* pool, uint8_t* arg,
+                             float* conv_dbg, int32_t batch, int32_t img_h, int32_t img_w, int32_t crop_h,
+                             int32_t crop_w, void* stream) {
+  B200_REQUIRE(images && w && bias && pool && arg, "null pointer");
+  return conv1_pool_fwd_tc(images, w, bias, pool, arg, conv_dbg, batch, img_h, img_w, crop_h, crop_w,
+                           (cudaStream_t)stream);
+}
+int b200_conv1_wgrad_bf16_scratch_bytes(int32_t batch, int64_t* nbytes) {
+  B200_REQUIRE(nbytes && batch > 0, "bad argument");
+  *nbytes = conv1_wgrad_tc_scratch_bytes(batch);
+  return B200_OK;
+}
+int b200_conv1_wgrad_bf16(const uint8_t* images, const float* dpool, const float* pool, const uint8_t* arg, float* dw,
+                          float* db, void* scratch, int64_t scratch_bytes, int32_t batch, int32_t img_h, int32_t img_w,
+                          int32_t crop_h, int32_t crop_w, void* stream) {
+  B200_REQUIRE(images && dpool && pool && arg && dw && scratch, "null pointer");
+  B200_REQUIRE(batch > 0 && scratch_bytes >= conv1_wgrad_tc_scratch_bytes(batch), "scratch too small");
+  return conv1_wgrad_tc(images, dpool, pool, arg, dw, db, (float*)scratch, batch, img_h, img_w, crop_h, crop_w,
+                        (cudaStream_t)stream);
+}
 int b200_conv5x5_fwd_bf16(const float* x, const float* w, const float* bias, float* y, int32_t batch, int32_t h,
                           int32_t wd, int32_t c_in, int32_t c_out, int32_t relu, void* stream) {
   B200_REQUIRE(x && w && y, "null pointer");

@@ -39,5 +39,11 @@ int conv5x5_dgrad_tc(const float* dy, const float* w, float* dx, int B, int H, i
 int64_t conv5x5_wgrad_tc_scratch_bytes(int B);
 int conv5x5_wgrad_tc(const float* x, const float* dy, float* dw, float* scratch, int B, int H, int W, int Cin,
                      int Cout, cudaStream_t st);
+bool conv1_tc_supported(int H, int W, int c_in, int c1);
+int conv1_pool_fwd_tc(const uint8_t* img, const float* w, const float* bias, float* pool, uint8_t* arg,
+                      float* conv_dbg, int B, int ih, int iw, int H, int W, cudaStream_t st);
+int64_t conv1_wgrad_tc_scratch_bytes(int B);
+int conv1_wgrad_tc(const uint8_t* img, const float* dpool, const float* pool, const uint8_t* arg, float* dw, float* db,
+                   float* scratch, int B, int ih, int iw, int H, int W, cudaStream_t st);
 
 }  // namespace b200

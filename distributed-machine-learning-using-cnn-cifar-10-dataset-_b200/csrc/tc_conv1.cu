@@ -1,0 +1,436 @@
+// conv1 of cifar10cnn.py on tcgen05, fused with everything around it.
+//
+// Forward (`conv1_pool_fwd_tc`): raw uint8 CHW record -> centre crop (:57-68) -> 5x5 SAME conv 3->64
+// + bias + ReLU (:107-110) -> 3x3/2 SAME max-pool with argmax (:113), one image per CTA, nothing
+// but the pooled tensor and its argmax ever reaches HBM.
+//
+// The image is a one-chunk strip (see tc_conv.cu): pixel slot = 16 B = 8 bf16 channels, of which
+// 3 are real (0..255 is exact in bf16) and 5 are zero.  A K=16 MMA consumes two chunks at distance
+// LBO -- and LBO is free, so the second chunk is simply the NEXT FILTER TAP of the same strip:
+// LBO = (slot offset of tap 2s+1 - slot offset of tap 2s) * 16.  13 MMAs per 128-slot tile cover the
+// 25 taps (+1 dummy with zero weights).
+//
+// Filter gradient (`conv1_wgrad_tc`): MaxPoolGrad + ReluGrad are applied while building a dY strip
+// in shared memory (gather form, deterministic), then  D_di[cout, dj*8+c] = sum_slots
+// dY[slot,cout] * X[slot + tap(di,dj), c]  is ONE M=64 x N=40 MMA per filter row and k-step: the
+// five taps of a row are the five N-groups of an MN-major B operand whose group stride SBO is one
+// pixel slot (16 B).  Channel 3 of the x strip is the constant 1, so column dj*8+3 of the centre
+// tap is the bias gradient sum(dY) for free.
+#include <algorithm>
+
+#include "launch.h"
+#include "tc_common.cuh"
+
+namespace b200 {
+using namespace tc;
+
+namespace {
+constexpr int WORKERS = 256;   // 8 warps stage / epilogue; warp 8 issues MMAs
+
+struct C1Geom {
+  int B, ih, iw, H, W;     // batch, record image size, crop size
+  int P, tiles, lead, npix;
+  int OH, OW;
+};
+__host__ inline C1Geom make_c1geom(int B, int ih, int iw, int H, int W) {
+  C1Geom g;
+  g.B = B; g.ih = ih; g.iw = iw; g.H = H; g.W = W;
+  g.P = W + 4;
+  g.tiles = ((H + 2) * g.P + 127) / 128;
+  g.lead = 2 * g.P + 2;
+  g.npix = g.lead + g.tiles * 128 + 2 * g.P + 2;
+  g.OH = (H + 1) / 2; g.OW = (W + 1) / 2;
+  return g;
+}
+__device__ __forceinline__ void workers_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+
+// one 16-byte slot: channels 0..2 = the pixel's bytes, channel 3 = `c3`, channels 4..7 = 0
+__device__ __forceinline__ uint4 pixel_chunk(const uint8_t* __restrict__ rec, int ih, int iw, int y, int x, float c3) {
+  const int plane = ih * iw;
+  float f[8] = {(float)rec[y * iw + x], (float)rec[plane + y * iw + x], (float)rec[2 * plane + y * iw + x], c3,
+                0.f, 0.f, 0.f, 0.f};
+  return pack8(f);
+}
+
+struct Conv1FwdArgs {
+  const uint8_t* img;   // [B,3,ih,iw]
+  const float* w;       // [25][3][64] HWIO
+  const float* bias;    // [64]
+  float* pool;          // [B,OH,OW,64]
+  uint8_t* arg;         // [B,OH,OW,64]
+  float* conv_dbg;      // [B,H,W,64] or null (tests: lets the pool fusion be checked on its own input)
+  C1Geom g;
+};
+
+constexpr int kWLbo = 64 * 16 + 16;      // B operand: [26 k-chunks][64 cout][16 B], chunk stride padded
+constexpr int kConvRow = 68;             // floats per conv-output row in smem (64 + 4: conflict-free STS.128)
+
+__global__ void __launch_bounds__(288, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) {
+  const C1Geom& g = a.g;
+  extern __shared__ __align__(128) uint8_t smem[];
+  const int strip_bytes = (g.npix * 16 + 127) & ~127;
+  uint8_t* strip = smem;
+  uint8_t* wB = strip + strip_bytes;
+  float* convbuf = reinterpret_cast<float*>(wB + 26 * kWLbo + 64);
+  uint8_t* ctrl = reinterpret_cast<uint8_t*>(convbuf + (size_t)g.H * g.W * kConvRow);
+  uint64_t* ready = reinterpret_cast<uint64_t*>(ctrl);
+  uint64_t* accum = ready + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum + 1);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int n = blockIdx.x;
+  const int tmem_cols = g.tiles * 64 <= 64 ? 64 : g.tiles * 64 <= 128 ? 128 : g.tiles * 64 <= 256 ? 256 : 512;
+
+  if (tid == 0) {
+    mbar_init(smem_u32(ready), WORKERS);
+    mbar_init(smem_u32(accum), 1);
+    fence_mbar_init();
+  }
+  if (warp == 8) tmem_alloc(smem_u32(tmem_slot), tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp < 8) {
+    for (int o = tid * 16; o < strip_bytes; o += WORKERS * 16) *reinterpret_cast<uint4*>(strip + o) = make_uint4(0, 0, 0, 0);
+    workers_sync();
+    const uint8_t* rec = a.img + (size_t)n * 3 * g.ih * g.iw;
+    const int oy = (g.ih - g.H) / 2, ox = (g.iw - g.W) / 2;
+    for (int q = tid; q < g.H * g.W; q += WORKERS) {
+      int i = q / g.W, j = q - i * g.W;
+      *reinterpret_cast<uint4*>(strip + (g.lead + i * g.P + j) * 16) = pixel_chunk(rec, g.ih, g.iw, i + oy, j + ox, 0.f);
+    }
+    // filter: k-chunk kc = tap kc (tap 25 = zeros); element e<3 of the chunk = w[tap][e][cout]
+    for (int q = tid; q < 26 * 64; q += WORKERS) {
+      int cout = q & 63, kc = q >> 6;
+      float f[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      if (kc < 25) {
+        f[0] = __ldg(a.w + (kc * 3 + 0) * 64 + cout);
+        f[1] = __ldg(a.w + (kc * 3 + 1) * 64 + cout);
+        f[2] = __ldg(a.w + (kc * 3 + 2) * 64 + cout);
+      }
+      *reinterpret_cast<uint4*>(wB + kc * kWLbo + cout * 16) = pack8(f);
+    }
+    fence_proxy_async();
+    mbar_arrive(smem_u32(ready));
+
+    // ---- epilogue 1: TMEM -> +bias, ReLU -> fp32 conv tile in shared memory ------------------------
+    mbar_wait(smem_u32(accum), 0);
+    tc_fence_after();
+    for (int t = (warp >> 2); t < g.tiles; t += 2) {
+      const int p = t * 128 + (warp & 3) * 32 + lane;
+      const int r = p / g.P, c = p - r * g.P;
+      const bool valid = (r < g.H) && (c < g.W);
+      float* row = convbuf + (size_t)(r * g.W + c) * kConvRow;
+      float* dbg = a.conv_dbg ? a.conv_dbg + (((size_t)n * g.H + r) * g.W + c) * 64 : nullptr;
+#pragma unroll 1
+      for (int c0 = 0; c0 < 64; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(tmem + ((uint32_t)((warp & 3) * 32) << 16) + t * 64 + c0, v);
+        tmem_ld_wait();
+        if (valid) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            float4 o;
+            o.x = fmaxf(__uint_as_float(v[j + 0]) + __ldg(a.bias + c0 + j + 0), 0.f);
+            o.y = fmaxf(__uint_as_float(v[j + 1]) + __ldg(a.bias + c0 + j + 1), 0.f);
+            o.z = fmaxf(__uint_as_float(v[j + 2]) + __ldg(a.bias + c0 + j + 2), 0.f);
+            o.w = fmaxf(__uint_as_float(v[j + 3]) + __ldg(a.bias + c0 + j + 3), 0.f);
+            *reinterpret_cast<float4*>(row + c0 + j) = o;
+            if (dbg) *reinterpret_cast<float4*>(dbg + c0 + j) = o;
+          }
+        }
+      }
+    }
+    tc_fence_before();
+    workers_sync();
+    // ---- epilogue 2: 3x3/2 SAME max-pool (pad 0 before / 1 after), first max in (h,w) scan order ---
+    const int pth = max((g.OH - 1) * 2 + 3 - g.H, 0), ptw = max((g.OW - 1) * 2 + 3 - g.W, 0);
+    const int pbh = pth / 2, pbw = ptw / 2;
+    for (int q = tid; q < g.OH * g.OW * 16; q += WORKERS) {
+      const int cq = q & 15, cell = q >> 4;
+      const int oh = cell / g.OW, ow = cell - oh * g.OW;
+      float best[4];
+      int bi[4] = {0, 0, 0, 0};
+      bool any = false;
+#pragma unroll
+      for (int kh = 0; kh < 3; ++kh) {
+        const int h = 2 * oh + kh - pbh;
+        if ((unsigned)h >= (unsigned)g.H) continue;
+#pragma unroll
+        for (int kw = 0; kw < 3; ++kw) {
+          const int w = 2 * ow + kw - pbw;
+          if ((unsigned)w >= (unsigned)g.W) continue;
+          const float4 v = *reinterpret_cast<const float4*>(convbuf + (size_t)(h * g.W + w) * kConvRow + cq * 4);
+          const float vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            if (!any || vv[e] > best[e]) { best[e] = vv[e]; bi[e] = kh * 3 + kw; }
+          any = true;
+        }
+      }
+      const size_t o = ((size_t)n * g.OH * g.OW + cell) * 64 + cq * 4;
+      *reinterpret_cast<float4*>(a.pool + o) = make_float4(best[0], best[1], best[2], best[3]);
+      *reinterpret_cast<uchar4*>(a.arg + o) = make_uchar4(bi[0], bi[1], bi[2], bi[3]);
+    }
+  } else {
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc(128, 64, false, false);
+      mbar_wait(smem_u32(ready), 0);
+      tc_fence_after();
+      const uint32_t sx = smem_u32(strip), sw = smem_u32(wB);
+      for (int ks = 0; ks < 13; ++ks) {
+        const int t0 = 2 * ks, t1 = 2 * ks + 1;
+        const int off0 = (t0 / 5 - 2) * g.P + (t0 % 5 - 2);
+        const int off1 = (t1 < 25) ? (t1 / 5 - 2) * g.P + (t1 % 5 - 2) : off0 + 1;   // dummy tap: zero weights
+        const uint32_t lbo = (uint32_t)(off1 - off0) * 16;
+        for (int t = 0; t < g.tiles; ++t) {
+          uint64_t da = make_desc(sx + (g.lead + off0 + t * 128) * 16, lbo, 128);
+          uint64_t db = make_desc(sw + ks * 2 * kWLbo, kWLbo, 128);
+          umma_bf16(tmem + t * 64, da, db, idesc, ks ? 1u : 0u);
+        }
+      }
+      umma_commit(smem_u32(accum));
+    }
+    __syncwarp();
+  }
+  __syncthreads();
+  if (warp == 8) {
+    tc_fence_after();
+    tmem_dealloc(tmem, tmem_cols);
+  }
+}
+}  // namespace
+
+bool conv1_tc_supported(int H, int W, int c_in, int c1) {
+  if (c_in != 3 || c1 != 64) return false;
+  C1Geom g = make_c1geom(1, H, W, H, W);
+  size_t smem = ((g.npix * 16 + 127) & ~127) + 26 * kWLbo + 64 + (size_t)H * W * kConvRow * 4 + 256;
+  return g.tiles * 64 <= 512 && smem <= 227 * 1024;
+}
+
+int conv1_pool_fwd_tc(const uint8_t* img, const float* w, const float* bias, float* pool, uint8_t* arg,
+                      float* conv_dbg, int B, int ih, int iw, int H, int W, cudaStream_t st) {
+  B200_REQUIRE(B > 0 && H <= ih && W <= iw && H >= 4 && W >= 4, "conv1_pool_fwd_tc: bad shape");
+  B200_REQUIRE(conv1_tc_supported(H, W, 3, 64), "conv1_pool_fwd_tc: crop %dx%d does not fit one CTA", H, W);
+  C1Geom g = make_c1geom(B, ih, iw, H, W);
+  const int smem = ((g.npix * 16 + 127) & ~127) + 26 * kWLbo + 64 + H * W * kConvRow * 4 + 256;
+  static bool attr = false;
+  if (!attr) {
+    B200_CUDA_TRY(cudaFuncSetAttribute(conv1_pool_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr = true;
+  }
+  Conv1FwdArgs a{img, w, bias, pool, arg, conv_dbg, g};
+  conv1_pool_fwd_kernel<<<B, 288, smem, st>>>(a);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+}  // namespace b200
+
+// =====================================================================================================
+// conv1 filter + bias gradient
+// =====================================================================================================
+namespace b200 {
+namespace {
+
+struct Conv1WgradArgs {
+  const uint8_t* img;     // [B,3,ih,iw]
+  const float* dpool;     // [B,OH,OW,64]  gradient w.r.t. pool1
+  const float* pool;      // [B,OH,OW,64]  pool1 itself (ReluGrad mask: the selected cell is > 0 iff pool1 > 0)
+  const uint8_t* arg;     // [B,OH,OW,64]
+  float* partial;         // [gridDim.x][5][64][40]
+  C1Geom g;
+};
+
+__global__ void __launch_bounds__(288, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
+  const C1Geom& g = a.g;
+  extern __shared__ __align__(128) uint8_t smem[];
+  const int xs_bytes = (g.npix * 16 + 127) & ~127;
+  const int ch_stride = g.npix * 16 + 16;
+  const int ncell = g.OH * g.OW;
+  uint8_t* xs = smem;
+  uint8_t* ds = xs + xs_bytes;
+  float* dpm = reinterpret_cast<float*>(ds + ((8 * ch_stride + 127) & ~127));
+  uint8_t* argb = reinterpret_cast<uint8_t*>(dpm + (size_t)ncell * 64);
+  uint8_t* ctrl = argb + (((size_t)ncell * 64 + 127) & ~127);
+  uint64_t* full = reinterpret_cast<uint64_t*>(ctrl);
+  uint64_t* empty = full + 1;
+  uint64_t* accum = empty + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum + 1);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int nimg = (g.B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  const int ksteps = (g.H * g.P + 15) / 16;
+
+  if (tid == 0) {
+    mbar_init(smem_u32(full), WORKERS);
+    mbar_init(smem_u32(empty), 1);
+    mbar_init(smem_u32(accum), 1);
+    fence_mbar_init();
+  }
+  if (warp == 8) tmem_alloc(smem_u32(tmem_slot), 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp < 8) {
+    for (int o = tid * 16; o < 8 * ch_stride; o += WORKERS * 16) *reinterpret_cast<uint4*>(ds + o) = make_uint4(0, 0, 0, 0);
+    const int pth = max((g.OH - 1) * 2 + 3 - g.H, 0), ptw = max((g.OW - 1) * 2 + 3 - g.W, 0);
+    const int pbh = pth / 2, pbw = ptw / 2;
+    const int oy = (g.ih - g.H) / 2, ox = (g.iw - g.W) / 2;
+    for (int it = 0; it < nimg; ++it) {
+      const int n = blockIdx.x + it * gridDim.x;
+      mbar_wait(smem_u32(empty), (it & 1) ^ 1);          // MMAs of the previous image are done with the strips
+      // masked pool gradient and argmax of this image -> shared memory (coalesced)
+      const float4* dp4 = reinterpret_cast<const float4*>(a.dpool + (size_t)n * ncell * 64);
+      const float4* pl4 = reinterpret_cast<const float4*>(a.pool + (size_t)n * ncell * 64);
+      const uint32_t* ar4 = reinterpret_cast<const uint32_t*>(a.arg + (size_t)n * ncell * 64);
+      for (int q = tid; q < ncell * 16; q += WORKERS) {
+        float4 d = __ldg(dp4 + q), p = __ldg(pl4 + q);
+        d.x = p.x > 0.f ? d.x : 0.f; d.y = p.y > 0.f ? d.y : 0.f;
+        d.z = p.z > 0.f ? d.z : 0.f; d.w = p.w > 0.f ? d.w : 0.f;
+        reinterpret_cast<float4*>(dpm)[q] = d;
+        reinterpret_cast<uint32_t*>(argb)[q] = __ldg(ar4 + q);
+      }
+      // x strip: channels 0..2 = pixel bytes (0 in the pads), channel 3 = 1 in EVERY slot
+      const uint8_t* rec = a.img + (size_t)n * 3 * g.ih * g.iw;
+      for (int s = tid; s < g.npix; s += WORKERS) {
+        const int p = s - g.lead;
+        const int i = p >= 0 ? p / g.P : -1, j = p >= 0 ? p - i * g.P : 0;
+        uint4 v;
+        if (p >= 0 && i < g.H && j < g.W) v = pixel_chunk(rec, g.ih, g.iw, i + oy, j + ox, 1.f);
+        else { float f[8] = {0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 0.f}; v = pack8(f); }
+        *reinterpret_cast<uint4*>(xs + s * 16) = v;
+      }
+      workers_sync();
+      // dY strip: MaxPoolGrad (gather over the <= 4 windows covering a cell) of the masked gradient
+      for (int q = tid; q < g.H * g.W * 8; q += WORKERS) {
+        const int c8 = q & 7, cellq = q >> 3;
+        const int i = cellq / g.W, j = cellq - i * g.W;
+        float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int kh = 0; kh < 3; ++kh) {
+          const int r = i + pbh - kh;
+          if (r < 0 || (r & 1) || (r >> 1) >= g.OH) continue;
+#pragma unroll
+          for (int kw = 0; kw < 3; ++kw) {
+            const int cc = j + pbw - kw;
+            if (cc < 0 || (cc & 1) || (cc >> 1) >= g.OW) continue;
+            const int cell = (r >> 1) * g.OW + (cc >> 1);
+            const uint2 ab = *reinterpret_cast<const uint2*>(argb + cell * 64 + c8 * 8);
+            const float4 d0 = *reinterpret_cast<const float4*>(dpm + cell * 64 + c8 * 8);
+            const float4 d1 = *reinterpret_cast<const float4*>(dpm + cell * 64 + c8 * 8 + 4);
+            const uint32_t code = kh * 3 + kw;
+            const float dv[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const uint32_t ae = ((e < 4 ? ab.x : ab.y) >> (8 * (e & 3))) & 0xffu;
+              if (ae == code) acc[e] += dv[e];
+            }
+          }
+        }
+        *reinterpret_cast<uint4*>(ds + c8 * ch_stride + (g.lead + i * g.P + j) * 16) = pack8(acc);
+      }
+      fence_proxy_async();
+      mbar_arrive(smem_u32(full));
+    }
+    // ---- epilogue: D_di[cout][dj*8 + c] (M = 64: lanes 0-15 of each subpartition) -> partial --------
+    mbar_wait(smem_u32(accum), 0);
+    tc_fence_after();
+    if (warp < 4) {
+      float* part = a.partial + (size_t)blockIdx.x * 5 * 64 * 40;
+      for (int di = 0; di < 5; ++di) {
+#pragma unroll 1
+        for (int c0 = 0; c0 < 64; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + di * 64 + c0, v);
+          tmem_ld_wait();
+          if (lane < 16) {
+            float* out = part + ((size_t)di * 64 + warp * 16 + lane) * 40 + c0;
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (c0 + j < 40) out[j] = nimg > 0 ? __uint_as_float(v[j]) : 0.f;
+          }
+        }
+      }
+    }
+    tc_fence_before();
+  } else {
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc(64, 40, true, true);
+      const uint32_t sx = smem_u32(xs), sd = smem_u32(ds);
+      for (int it = 0; it < nimg; ++it) {
+        mbar_wait(smem_u32(full), it & 1);
+        tc_fence_after();
+        for (int di = 0; di < 5; ++di) {
+          const int slot0 = g.lead + (di - 2) * g.P - 2;
+          for (int ks = 0; ks < ksteps; ++ks) {
+            uint64_t da = make_desc(sd + (g.lead + ks * 16) * 16, 128, ch_stride);
+            uint64_t db = make_desc(sx + (slot0 + ks * 16) * 16, 128, 16);     // N-group stride = one pixel slot
+            umma_bf16(tmem + di * 64, da, db, idesc, (it | ks) ? 1u : 0u);
+          }
+        }
+        umma_commit(smem_u32(empty));
+      }
+      umma_commit(smem_u32(accum));
+    }
+    __syncwarp();
+  }
+  __syncthreads();
+  if (warp == 8) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 512);
+  }
+}
+
+// dW1[tap][c][cout] = sum_s part[s][di][cout][dj*8+c];  db1[cout] = sum_s part[s][2][cout][2*8+3]
+__global__ void conv1_wgrad_finish(const float* __restrict__ part, float* __restrict__ dw, float* __restrict__ db, int S) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 75 * 64 + 64) return;
+  int src;
+  if (i < 75 * 64) {
+    const int cout = i & 63, tc3 = i >> 6;
+    const int c = tc3 % 3, tap = tc3 / 3;
+    src = ((tap / 5) * 64 + cout) * 40 + (tap % 5) * 8 + c;
+  } else {
+    src = (2 * 64 + (i - 75 * 64)) * 40 + 2 * 8 + 3;
+  }
+  float s = 0.f;
+  for (int z = 0; z < S; ++z) s += __ldg(part + (size_t)z * 5 * 64 * 40 + src);
+  if (i < 75 * 64) dw[i] = s;
+  else if (db) db[i - 75 * 64] = s;
+}
+
+int conv1_wgrad_ctas(int B) { return std::min(B, kNumSMs); }
+size_t conv1_wgrad_smem(const C1Geom& g) {
+  size_t xs = (g.npix * 16 + 127) & ~127, ch = g.npix * 16 + 16;
+  return xs + ((8 * ch + 127) & ~127) + (size_t)g.OH * g.OW * 64 * 4 + (((size_t)g.OH * g.OW * 64 + 127) & ~127) + 256;
+}
+}  // namespace
+
+int64_t conv1_wgrad_tc_scratch_bytes(int B) { return (int64_t)conv1_wgrad_ctas(B) * 5 * 64 * 40 * 4; }
+
+int conv1_wgrad_tc(const uint8_t* img, const float* dpool, const float* pool, const uint8_t* arg, float* dw, float* db,
+                   float* scratch, int B, int ih, int iw, int H, int W, cudaStream_t st) {
+  B200_REQUIRE(B > 0 && H <= ih && W <= iw && H >= 4 && W >= 4, "conv1_wgrad_tc: bad shape");
+  C1Geom g = make_c1geom(B, ih, iw, H, W);
+  const size_t smem = conv1_wgrad_smem(g);
+  B200_REQUIRE(smem <= 227 * 1024, "conv1_wgrad_tc: crop %dx%d needs %zu bytes of shared memory", H, W, smem);
+  static bool attr = false;
+  if (!attr) {
+    B200_CUDA_TRY(cudaFuncSetAttribute(conv1_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr = true;
+  }
+  const int S = conv1_wgrad_ctas(B);
+  Conv1WgradArgs a{img, dpool, pool, arg, scratch, g};
+  conv1_wgrad_kernel<<<S, 288, smem, st>>>(a);
+  B200_LAUNCH_CHECK();
+  conv1_wgrad_finish<<<cdiv(75 * 64 + 64, 256), 256, 0, st>>>(scratch, dw, db, S);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+}  // namespace b200

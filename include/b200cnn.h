@@ -143,6 +143,19 @@ int b200_colsum_scratch_bytes(int32_t rows, int32_t cols, int64_t* nbytes);
 int b200_fc_bwd_f32(const float* x, const float* w, const float* dy, float* dx, float* dw, float* db,
                     void* scratch, int64_t scratch_bytes, int32_t batch, int32_t k, int32_t n,
                     int32_t mask_x, void* stream);
+/* The whole first block of create_cnn on the tensor cores, one image per CTA: record crop/cast (:57-68),
+ * conv1 + bias + ReLU (:107-110) and pool1 with argmax (:113); only pool and arg reach HBM (conv_dbg,
+ * if not NULL, also receives the un-pooled [batch,crop_h,crop_w,64] activations for tests).  3 -> 64
+ * channels only; crops up to about 24x24 (TMEM / shared-memory limit). */
+int b200_conv1_pool_fwd_bf16(const uint8_t* images, const float* w, const float* bias, float* pool, uint8_t* arg,
+                             float* conv_dbg, int32_t batch, int32_t img_h, int32_t img_w, int32_t crop_h,
+                             int32_t crop_w, void* stream);
+/* Its gradient: MaxPoolGrad + ReluGrad of pool1 (autodiff of :113, :110) fused with
+ * Conv2DBackpropFilter + BiasAddGrad of :107-109, from the gradient w.r.t. pool1. */
+int b200_conv1_wgrad_bf16_scratch_bytes(int32_t batch, int64_t* nbytes);
+int b200_conv1_wgrad_bf16(const uint8_t* images, const float* dpool, const float* pool, const uint8_t* arg, float* dw,
+                          float* db, void* scratch, int64_t scratch_bytes, int32_t batch, int32_t img_h, int32_t img_w,
+                          int32_t crop_h, int32_t crop_w, void* stream);
 /* conv2d / Conv2DBackpropInput / Conv2DBackpropFilter of :118 on the tensor cores (tcgen05 implicit
  * GEMM over a zero-padded shared-memory strip; bf16 operands rounded from the fp32 tensors, fp32
  * accumulation).  c_in % 16 == 0 and c_out % 64 == 0 (wgrad: 64 -> 64 only).  The wgrad scratch

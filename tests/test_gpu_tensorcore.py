@@ -186,3 +186,56 @@ def test_full_step_bf16_mode_b128(kind):
     got = e.get_grads()
     for k in rn.PARAM_NAMES:
         assert relerr(got[k], g2[k]) <= 2e-2, (k, relerr(got[k], g2[k]))
+
+
+@pytest.mark.parametrize("B,crop", [(3, 24), (128, 24), (2, 16)])
+def test_conv1_pool_fused_fwd_and_wgrad(lib, B, crop):
+    """crop/cast + conv1 + bias + ReLU + pool1 (cifar10cnn.py:57-68, :107-113) in one tcgen05 kernel,
+    and MaxPoolGrad + ReluGrad + Conv2DBackpropFilter + BiasAddGrad in another."""
+    rng = np.random.default_rng(51)
+    img = rng.integers(0, 256, (B, 3, 32, 32), dtype=np.uint8)
+    w = (rng.normal(size=(5, 5, 3, 64)) * 0.05).astype(np.float32)
+    b = (rng.normal(size=(64,)) * 0.5).astype(np.float32)
+    x = rn.crop_cast(img, crop, crop)                         # exact in bf16 (integers <= 255)
+    wr = bf16_round(w)
+    OH = crop // 2
+    imgd, wd, bd = dev(img), dev(w), dev(b)
+    pool = torch.full((B, OH, OH, 64), float("nan"), device="cuda")
+    arg = torch.full((B, OH, OH, 64), 255, dtype=torch.uint8, device="cuda")
+    conv = torch.full((B, crop, crop, 64), float("nan"), device="cuda")
+    _lib.check(lib.b200_conv1_pool_fwd_bf16(imgd.data_ptr(), wd.data_ptr(), bd.data_ptr(), pool.data_ptr(),
+                                            arg.data_ptr(), conv.data_ptr(), B, 32, 32, crop, crop, stream()))
+    torch.cuda.synchronize()
+    want_conv = np.maximum(rn.conv2d_same(x, wr) + b, 0)
+    assert relerr(conv.cpu().numpy(), want_conv) <= TIGHT
+    assert relerr(conv.cpu().numpy(), np.maximum(rn.conv2d_same(x, w.astype(np.float64)) + b, 0)) <= LOOSE
+    # the fused pool applies TF's rule to the kernel's OWN conv values: bit-exact values and argmax
+    wy, warg = rn.maxpool_3x3s2_same(conv.cpu().numpy())
+    np.testing.assert_array_equal(pool.cpu().numpy(), wy)
+    np.testing.assert_array_equal(arg.cpu().numpy(), warg)
+    # without the debug output the results are the same
+    pool2 = torch.empty_like(pool); arg2 = torch.empty_like(arg)
+    _lib.check(lib.b200_conv1_pool_fwd_bf16(imgd.data_ptr(), wd.data_ptr(), bd.data_ptr(), pool2.data_ptr(),
+                                            arg2.data_ptr(), None, B, 32, 32, crop, crop, stream()))
+    torch.cuda.synchronize()
+    assert torch.equal(pool, pool2) and torch.equal(arg, arg2)
+
+    # ---- gradient ----
+    dpool = (rng.normal(size=(B, OH, OH, 64)) * (rng.random(size=(B, OH, OH, 64)) < 0.5)).astype(np.float32)
+    nb = C.c_int64()
+    _lib.check(lib.b200_conv1_wgrad_bf16_scratch_bytes(B, C.byref(nb)))
+    scr = torch.empty(nb.value, dtype=torch.uint8, device="cuda")
+    dw = torch.full((5, 5, 3, 64), float("nan"), device="cuda")
+    db = torch.full((64,), float("nan"), device="cuda")
+    convn = conv.cpu().numpy().astype(np.float64)
+    dconv = rn.maxpool_3x3s2_same_grad(dpool.astype(np.float64), warg, (crop, crop)) * (convn > 0)
+    dconv_r = bf16_round(dconv)                                # the kernel rounds dY once, after summing windows
+    for _ in range(2):
+        _lib.check(lib.b200_conv1_wgrad_bf16(imgd.data_ptr(), dev(dpool).data_ptr(), pool.data_ptr(), arg.data_ptr(),
+                                             dw.data_ptr(), db.data_ptr(), scr.data_ptr(), nb.value, B, 32, 32, crop,
+                                             crop, stream()))
+        torch.cuda.synchronize()
+        assert relerr(dw.cpu().numpy(), rn.conv2d_same_grad_filter(x, dconv_r)) <= TIGHT
+        assert relerr(db.cpu().numpy(), dconv_r.sum((0, 1, 2))) <= TIGHT
+    assert relerr(dw.cpu().numpy(), rn.conv2d_same_grad_filter(x, dconv)) <= LOOSE
+    assert relerr(db.cpu().numpy(), dconv.sum((0, 1, 2))) <= LOOSE
