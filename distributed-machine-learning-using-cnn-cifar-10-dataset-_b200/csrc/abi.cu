@@ -42,6 +42,7 @@ struct b200_model {
   int64_t ws_bytes = 0;
   std::vector<Tensor> tensors;
   bool forward_done = false;
+  const uint8_t* last_images = nullptr;   // records of the last forward (the fused conv1 gradient re-reads them)
   // per-launch-site timing (b200_profile_step): events are created lazily, once
   bool profiling = false;
   std::vector<std::string> site_names;
@@ -120,6 +121,7 @@ int b200_create(const b200_config* c, b200_handle* out) {
   int64_t scratch = conv5x5_wgrad_scratch_bytes(c->batch, c->crop_h, c->crop_w, c->c_in, c->c1);
   scratch = std::max(scratch, conv5x5_wgrad_scratch_bytes(c->batch, h->h1, h->w1, c->c1, c->c2));
   scratch = std::max(scratch, colsum_scratch_bytes(c->batch, std::max(c->f1, std::max(c->f2, c->n_cls))));
+  scratch = std::max(scratch, conv1_wgrad_tc_scratch_bytes(c->batch));
   scratch = std::max(scratch, conv5x5_wgrad_tc_scratch_bytes(c->batch) +
                                   colsum_scratch_bytes(c->batch * h->h1 * h->w1, c->c2));
   h->add("scratch", scratch, 1);
@@ -208,9 +210,16 @@ int b200_forward(b200_handle h, const uint8_t* images, const int32_t* labels, vo
   float *conv1 = h->ptr<float>("conv1"), *pool1 = h->ptr<float>("pool1");
   float *conv2 = h->ptr<float>("conv2"), *pool2 = h->ptr<float>("pool2");
   float *full1 = h->ptr<float>("full1"), *full2 = h->ptr<float>("full2"), *logits = h->ptr<float>("logits");
-  SITE("crop_cast", crop_cast_f32(images, x, c.batch, c.img_h, c.img_w, c.crop_h, c.crop_w, c.c_in, st));
-  SITE("conv1_fwd", conv5x5_fwd_f32(x, h->P(P_W1), h->P(P_B1), conv1, c.batch, c.crop_h, c.crop_w, c.c_in, c.c1, 1, st));
-  SITE("pool1_fwd", maxpool_fwd_f32(conv1, pool1, h->ptr<uint8_t>("arg1"), c.batch, c.crop_h, c.crop_w, c.c1, st));
+  const bool fused1 = tc && conv1_tc_supported(c.crop_h, c.crop_w, c.c_in, c.c1);
+  h->last_images = images;
+  if (fused1) {
+    SITE("conv1_pool1_fwd", conv1_pool_fwd_tc(images, h->P(P_W1), h->P(P_B1), pool1, h->ptr<uint8_t>("arg1"), nullptr,
+                                              c.batch, c.img_h, c.img_w, c.crop_h, c.crop_w, st));
+  } else {
+    SITE("crop_cast", crop_cast_f32(images, x, c.batch, c.img_h, c.img_w, c.crop_h, c.crop_w, c.c_in, st));
+    SITE("conv1_fwd", conv5x5_fwd_f32(x, h->P(P_W1), h->P(P_B1), conv1, c.batch, c.crop_h, c.crop_w, c.c_in, c.c1, 1, st));
+    SITE("pool1_fwd", maxpool_fwd_f32(conv1, pool1, h->ptr<uint8_t>("arg1"), c.batch, c.crop_h, c.crop_w, c.c1, st));
+  }
   if (tc)
     SITE("conv2_fwd", conv5x5_fwd_tc(pool1, h->P(P_W2), h->P(P_B2), conv2, c.batch, h->h1, h->w1, c.c1, c.c2, 1, st));
   else
@@ -273,10 +282,16 @@ int b200_backward(b200_handle h, void* stream) {
     SITE("conv2_dgrad", conv5x5_fwd_f32(dconv2, h->ptr<float>("wrot"), nullptr, dpool1, c.batch, h->h1, h->w1, c.c2,
                                         c.c1, 0, st));
   }
-  SITE("pool1_bwd", maxpool_bwd_f32(dpool1, h->ptr<uint8_t>("arg1"), h->ptr<float>("conv1"), dconv1, c.batch, c.crop_h,
-                      c.crop_w, c.c1, 1, st));
-  SITE("conv1_wgrad", conv5x5_wgrad_f32(h->ptr<float>("x"), dconv1, h->G(P_W1), h->G(P_B1), scratch, c.batch, c.crop_h,
-                        c.crop_w, c.c_in, c.c1, st));
+  if (tc && conv1_tc_supported(c.crop_h, c.crop_w, c.c_in, c.c1)) {
+    SITE("conv1_wgrad", conv1_wgrad_tc(h->last_images, dpool1, h->ptr<float>("pool1"), h->ptr<uint8_t>("arg1"),
+                                       h->G(P_W1), h->G(P_B1), scratch, c.batch, c.img_h, c.img_w, c.crop_h, c.crop_w,
+                                       st));
+  } else {
+    SITE("pool1_bwd", maxpool_bwd_f32(dpool1, h->ptr<uint8_t>("arg1"), h->ptr<float>("conv1"), dconv1, c.batch,
+                                      c.crop_h, c.crop_w, c.c1, 1, st));
+    SITE("conv1_wgrad", conv5x5_wgrad_f32(h->ptr<float>("x"), dconv1, h->G(P_W1), h->G(P_B1), scratch, c.batch,
+                                          c.crop_h, c.crop_w, c.c_in, c.c1, st));
+  }
   return B200_OK;
 }
 
@@ -357,7 +372,10 @@ int b200_launches_per_step(b200_handle h, int32_t* n) {
   // forward 9; fc_bwd 3 x (dw, colsum x2, dx); pool bwd x2; conv wgrad 2 x (gemm, reduce, colsum x2);
   // dgrad (rot180 + gemm); sgd
   *n = 9 + 12 + 2 + 8 + 2 + 1;
-  if (h->cfg.mode == B200_MODE_BF16) *n = 9 + (4 + 4 + 4) + 2 + (2 + 2 + 1) + 4 + 1;
+  if (h->cfg.mode == B200_MODE_BF16) {
+    *n = 9 + (4 + 4 + 4) + 2 + (2 + 2 + 1) + 4 + 1;
+    if (conv1_tc_supported(h->cfg.crop_h, h->cfg.crop_w, h->cfg.c_in, h->cfg.c1)) *n -= 2 + 1 + 2;   // fused conv1 fwd / bwd
+  }
   return B200_OK;
 }
 

@@ -77,7 +77,8 @@ int b200_bind_workspace(b200_handle h, void* workspace, int64_t nbytes);
  * The crop/transposes/cast of read_cifar_files (:57-68) happen inside.  Results stay in the
  * workspace; b200_result_ptrs exposes them. */
 int b200_forward(b200_handle h, const uint8_t* images, const int32_t* labels, void* stream);
-/* the gradient graph built by minimize() (:162-163); fills the bound gradient buffer. */
+/* the gradient graph built by minimize() (:162-163); fills the bound gradient buffer.  The `images`
+ * buffer given to the last b200_forward must still be intact (the conv1 gradient re-reads the records). */
 int b200_backward(b200_handle h, void* stream);
 /* ApplyGradientDescent x10 (:162-163): params -= lr * grad_scale * grads.  grad_scale = 1 for a
  * single worker or a SUM allreduce, 1/world for a MEAN allreduce. */
