@@ -88,8 +88,8 @@ int b200_create(const b200_config* c, b200_handle* out) {
   B200_REQUIRE(c->n_cls > 0 && c->n_cls <= 16, "b200_create: n_cls must be in 1..16");
   B200_REQUIRE(c->mode == B200_MODE_FP32 || c->mode == B200_MODE_BF16, "b200_create: unknown mode %d", c->mode);
   if (c->mode == B200_MODE_BF16)
-    B200_REQUIRE(c->batch % 8 == 0 && c->c1 == 64 && c->c2 == 64 && c->f1 % 8 == 0 && c->f2 % 8 == 0,
-                 "b200_create: bf16 mode needs batch %% 8 == 0, 64/64 conv channels and FC widths %% 8 == 0");
+    B200_REQUIRE(c->batch % 8 == 0 && c->c1 == 64 && c->c2 == 64 && c->f1 % 32 == 0 && c->f2 % 8 == 0 && c->f2 <= 256,
+                 "b200_create: bf16 mode needs batch %% 8 == 0, 64/64 conv channels, f1 %% 32 == 0, f2 %% 8 == 0, f2 <= 256");
   b200_model* h = new (std::nothrow) b200_model();
   B200_REQUIRE(h, "b200_create: out of host memory");
   h->cfg = *c;
@@ -125,6 +125,8 @@ int b200_create(const b200_config* c, b200_handle* out) {
   scratch = std::max(scratch, conv5x5_wgrad_tc_scratch_bytes(c->batch) +
                                   colsum_scratch_bytes(c->batch * h->h1 * h->w1, c->c2));
   h->add("scratch", scratch, 1);
+  h->add("fc1_part", (int64_t)fc_fwd_tc_splits(c->batch, h->flat, c->f1) * B * c->f1, 4);
+  h->add("tail_scratch", fc_tail_scratch_bytes(c->batch, c->f1, c->f2, c->n_cls), 1);
   h->add("loss", 1, 4); h->add("n_correct", 1, 4); h->add("n_bad", 1, 4); h->add("pred", B, 4);
   h->add("stage_images", B * c->c_in * c->img_h * c->img_w, 1);
   h->add("stage_labels", B, 4);
@@ -226,15 +228,25 @@ int b200_forward(b200_handle h, const uint8_t* images, const int32_t* labels, vo
     SITE("conv2_fwd", conv5x5_fwd_f32(pool1, h->P(P_W2), h->P(P_B2), conv2, c.batch, h->h1, h->w1, c.c1, c.c2, 1, st));
   SITE("pool2_fwd", maxpool_fwd_f32(conv2, pool2, h->ptr<uint8_t>("arg2"), c.batch, h->h1, h->w1, c.c2, st));
   if (tc) {
-    SITE("full1_fwd", fc_fwd_tc(pool2, h->P(P_FW1), h->P(P_FB1), full1, c.batch, h->flat, c.f1, 1, st));
-    SITE("full2_fwd", fc_fwd_tc(full1, h->P(P_FW2), h->P(P_FB2), full2, c.batch, c.f1, c.f2, 1, st));
+    // FC1 as a split-K tensor-core product; the tail kernels add the partials, bias and ReLU, run
+    // FC2 / FC3 / loss / accuracy and already produce every gradient above FC1 (dfull1, dW2, db2, dW3,
+    // db3, db1) -- they depend on nothing else, so b200_backward starts at FC1's weight gradient.
+    // CTA 0 of the tail also clears conv2's bias gradient for the atomics of the pool2 backward.
+    float* part = h->ptr<float>("fc1_part");
+    SITE("full1_fwd", fc_fwd_tc_splitk(pool2, h->P(P_FW1), part, c.batch, h->flat, c.f1, st));
+    SITE("fc_tail", fc_tail(part, fc_fwd_tc_splits(c.batch, h->flat, c.f1), h->P(P_FB1), full1, h->P(P_FW2),
+                            h->P(P_FB2), h->P(P_FW3), h->P(P_FB3), labels, full2, logits, h->ptr<float>("dlogits"),
+                            h->ptr<float>("dfull2"), h->ptr<float>("dfull1"), h->ptr<int32_t>("pred"),
+                            h->ptr<float>("loss"), h->ptr<int32_t>("n_correct"), h->ptr<int32_t>("n_bad"),
+                            h->G(P_FW2), h->G(P_FB2), h->G(P_FW3), h->G(P_FB3), h->G(P_FB1),
+                            h->ptr<void>("tail_scratch"), h->G(P_B2), c.c2, c.batch, c.f1, c.f2, c.n_cls, st));
   } else {
     SITE("full1_fwd", fc_fwd_f32(pool2, h->P(P_FW1), h->P(P_FB1), full1, c.batch, h->flat, c.f1, 1, st));
     SITE("full2_fwd", fc_fwd_f32(full1, h->P(P_FW2), h->P(P_FB2), full2, c.batch, c.f1, c.f2, 1, st));
+    SITE("full3_fwd", fc_fwd_f32(full2, h->P(P_FW3), h->P(P_FB3), logits, c.batch, c.f2, c.n_cls, 1, st));
+    SITE("head", head_f32(logits, labels, h->ptr<float>("loss"), h->ptr<float>("dlogits"), h->ptr<int32_t>("pred"),
+                          h->ptr<int32_t>("n_correct"), h->ptr<int32_t>("n_bad"), c.batch, c.n_cls, st));
   }
-  SITE("full3_fwd", fc_fwd_f32(full2, h->P(P_FW3), h->P(P_FB3), logits, c.batch, c.f2, c.n_cls, 1, st));
-  SITE("head", head_f32(logits, labels, h->ptr<float>("loss"), h->ptr<float>("dlogits"), h->ptr<int32_t>("pred"),
-               h->ptr<int32_t>("n_correct"), h->ptr<int32_t>("n_bad"), c.batch, c.n_cls, st));
   h->forward_done = true;
   return B200_OK;
 }
@@ -252,28 +264,23 @@ int b200_backward(b200_handle h, void* stream) {
   float *dlogits = h->ptr<float>("dlogits"), *dfull2 = h->ptr<float>("dfull2"), *dfull1 = h->ptr<float>("dfull1");
   float *dpool2 = h->ptr<float>("dpool2"), *dconv2 = h->ptr<float>("dconv2");
   float *dpool1 = h->ptr<float>("dpool1"), *dconv1 = h->ptr<float>("dconv1");
-  SITE("full3_bwd", fc_bwd_f32(h->ptr<float>("full2"), h->P(P_FW3), dlogits, dfull2, h->G(P_FW3), h->G(P_FB3), scratch,
-                 c.batch, c.f2, c.n_cls, 1, st));
   if (tc) {
-    SITE("full2_bwd", fc_bwd_tc(h->ptr<float>("full1"), h->P(P_FW2), dfull2, dfull1, h->G(P_FW2), c.batch, c.f1, c.f2,
-                                1, st));
-    SITE("full2_bias", colsum_f32(dfull2, h->G(P_FB2), scratch, c.batch, c.f2, st));
     SITE("full1_bwd", fc_bwd_tc(h->ptr<float>("pool2"), h->P(P_FW1), dfull1, dpool2, h->G(P_FW1), c.batch, h->flat,
                                 c.f1, 0, st));
-    SITE("full1_bias", colsum_f32(dfull1, h->G(P_FB1), scratch, c.batch, c.f1, st));
   } else {
+    SITE("full3_bwd", fc_bwd_f32(h->ptr<float>("full2"), h->P(P_FW3), dlogits, dfull2, h->G(P_FW3), h->G(P_FB3),
+                                 scratch, c.batch, c.f2, c.n_cls, 1, st));
     SITE("full2_bwd", fc_bwd_f32(h->ptr<float>("full1"), h->P(P_FW2), dfull2, dfull1, h->G(P_FW2), h->G(P_FB2), scratch,
                                  c.batch, c.f1, c.f2, 1, st));
     SITE("full1_bwd", fc_bwd_f32(h->ptr<float>("pool2"), h->P(P_FW1), dfull1, dpool2, h->G(P_FW1), h->G(P_FB1), scratch,
                                  c.batch, h->flat, c.f1, 0, st));
   }
-  SITE("pool2_bwd", maxpool_bwd_f32(dpool2, h->ptr<uint8_t>("arg2"), h->ptr<float>("conv2"), dconv2, c.batch, h->h1, h->w1,
-                      c.c2, 1, st));
+  // bf16 mode: conv2's bias gradient rides along (atomics into the buffer the tail kernel cleared)
+  SITE("pool2_bwd", maxpool_bwd_f32(dpool2, h->ptr<uint8_t>("arg2"), h->ptr<float>("conv2"), dconv2, c.batch, h->h1,
+                                    h->w1, c.c2, 1, st, tc ? h->G(P_B2) : nullptr));
   if (tc) {
     SITE("conv2_wgrad", conv5x5_wgrad_tc(h->ptr<float>("pool1"), dconv2, h->G(P_W2), scratch, c.batch, h->h1, h->w1,
                                          c.c1, c.c2, st));
-    SITE("conv2_bias", colsum_f32(dconv2, h->G(P_B2), scratch + conv5x5_wgrad_tc_scratch_bytes(c.batch) / 4,
-                                  c.batch * h->h1 * h->w1, c.c2, st));
     SITE("conv2_dgrad", conv5x5_dgrad_tc(dconv2, h->P(P_W2), dpool1, c.batch, h->h1, h->w1, c.c1, c.c2, st));
   } else {
     SITE("conv2_wgrad", conv5x5_wgrad_f32(h->ptr<float>("pool1"), dconv2, h->G(P_W2), h->G(P_B2), scratch, c.batch,
@@ -373,8 +380,9 @@ int b200_launches_per_step(b200_handle h, int32_t* n) {
   // dgrad (rot180 + gemm); sgd
   *n = 9 + 12 + 2 + 8 + 2 + 1;
   if (h->cfg.mode == B200_MODE_BF16) {
-    *n = 9 + (4 + 4 + 4) + 2 + (2 + 2 + 1) + 4 + 1;
-    if (conv1_tc_supported(h->cfg.crop_h, h->cfg.crop_w, h->cfg.c_in, h->cfg.c1)) *n -= 2 + 1 + 2;   // fused conv1 fwd / bwd
+    // conv1 (3 or 1), conv2, pool2, FC1 split-K, tail x2 | FC1 bwd x2, pool2 bwd, conv2 wgrad x2, dgrad, conv1 wgrad (2 or 1+4), sgd
+    const bool f1 = conv1_tc_supported(h->cfg.crop_h, h->cfg.crop_w, h->cfg.c_in, h->cfg.c1);
+    *n = (f1 ? 1 : 3) + 1 + 1 + 1 + 2 + 2 + 1 + 2 + 1 + (f1 ? 2 : 5) + 1;
   }
   return B200_OK;
 }
@@ -492,6 +500,25 @@ int b200_fc_bwd_bf16(const float* x, const float* w, const float* dy, float* dx,
   B200_REQUIRE(!db || (scratch && scratch_bytes >= colsum_scratch_bytes(batch, n)), "scratch too small");
   TRY(fc_bwd_tc(x, w, dy, dx, dw, batch, k, n, mask_x, (cudaStream_t)stream));
   if (db) return colsum_f32(dy, db, (float*)scratch, batch, n, (cudaStream_t)stream);
+  return B200_OK;
+}
+int b200_fc_tail_f32(float* full1, const float* w2, const float* b2, const float* w3, const float* b3,
+                     const int32_t* labels, float* full2, float* logits, float* dlogits, float* dfull2, float* dfull1,
+                     int32_t* pred, float* loss, int32_t* n_correct, int32_t* n_bad, float* dw2, float* db2, float* dw3,
+                     float* db3, float* db1, void* scratch, int64_t scratch_bytes, int32_t batch, int32_t f1, int32_t f2,
+                     int32_t n_cls, void* stream) {
+  B200_REQUIRE(full1 && w2 && b2 && w3 && b3 && labels && full2 && logits && dlogits && dfull2 && dfull1 && pred &&
+                   loss && n_correct && n_bad && dw2 && db2 && dw3 && db3 && db1 && scratch,
+               "null pointer");
+  B200_REQUIRE(batch > 0 && f1 > 0 && f2 > 0 && n_cls > 0 && scratch_bytes >= fc_tail_scratch_bytes(batch, f1, f2, n_cls),
+               "scratch too small");
+  return fc_tail(nullptr, 0, nullptr, full1, w2, b2, w3, b3, labels, full2, logits, dlogits, dfull2, dfull1, pred, loss,
+                 n_correct, n_bad, dw2, db2, dw3, db3, db1, scratch, nullptr, 0, batch, f1, f2, n_cls,
+                 (cudaStream_t)stream);
+}
+int b200_fc_tail_scratch_bytes(int32_t batch, int32_t f1, int32_t f2, int32_t n_cls, int64_t* nbytes) {
+  B200_REQUIRE(nbytes && batch > 0 && f1 > 0 && f2 > 0 && n_cls > 0, "bad argument");
+  *nbytes = fc_tail_scratch_bytes(batch, f1, f2, n_cls);
   return B200_OK;
 }
 int b200_head_f32(const float* logits, const int32_t* labels, float* loss_mean, float* dlogits, int32_t* pred,

@@ -323,8 +323,10 @@ int maxpool_fwd_f32(const float* x, float* y, uint8_t* arg, int B, int H, int W,
 // tensor that was pooled.
 __global__ void maxpool_bwd_kernel(const float* __restrict__ dy, const uint8_t* __restrict__ arg,
                                    const float* __restrict__ x, float* __restrict__ dx, int B, int H, int W,
-                                   int C, int OH, int OW, int pbh, int pbw, int relu_mask) {
+                                   int C, int OH, int OW, int pbh, int pbw, int relu_mask,
+                                   float* __restrict__ colsum) {
   const int64_t total = (int64_t)B * H * W * C;
+  float csum = 0.f;   // with 256 % C == 0 a thread keeps one channel over the whole grid-stride loop
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
        i += (int64_t)gridDim.x * blockDim.x) {
     int c = (int)(i % C);
@@ -354,17 +356,29 @@ __global__ void maxpool_bwd_kernel(const float* __restrict__ dy, const uint8_t* 
       }
     }
     dx[i] = s;
+    csum += s;
+  }
+  if (colsum) {       // BiasAddGrad of the layer below, fused: per-CTA partial -> one atomic per channel
+    __shared__ float red[256];
+    red[threadIdx.x] = csum;
+    __syncthreads();
+    if ((int)threadIdx.x < C) {
+      float t = 0.f;
+      for (int j = threadIdx.x; j < 256; j += C) t += red[j];
+      atomicAdd(colsum + threadIdx.x, t);
+    }
   }
 }
 int maxpool_bwd_f32(const float* dy, const uint8_t* arg, const float* x, float* dx, int B, int H, int W,
-                    int C, int relu_mask, cudaStream_t st) {
+                    int C, int relu_mask, cudaStream_t st, float* colsum_atomic) {
+  B200_REQUIRE(!colsum_atomic || (256 % C) == 0, "maxpool_bwd: fused bias gradient needs C to divide 256");
   B200_REQUIRE(B > 0 && H > 1 && W > 1 && C > 0, "maxpool_bwd: bad shape");
   B200_REQUIRE(!relu_mask || x, "maxpool_bwd: relu_mask needs x");
   int OH, OW, pbh, pbw;
   pool_geom(H, W, OH, OW, pbh, pbw);
   int64_t total = (int64_t)B * H * W * C;
   int grid = (int)std::min<int64_t>((total + 255) / 256, kNumSMs * 16);
-  maxpool_bwd_kernel<<<grid, 256, 0, st>>>(dy, arg, x, dx, B, H, W, C, OH, OW, pbh, pbw, relu_mask);
+  maxpool_bwd_kernel<<<grid, 256, 0, st>>>(dy, arg, x, dx, B, H, W, C, OH, OW, pbh, pbw, relu_mask, colsum_atomic);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

@@ -14,8 +14,10 @@ int64_t conv5x5_wgrad_scratch_bytes(int B, int H, int W, int Cin, int Cout);
 int conv5x5_wgrad_f32(const float* x, const float* dy, float* dw, float* db, float* scratch, int B, int H,
                       int W, int Cin, int Cout, cudaStream_t st);
 int maxpool_fwd_f32(const float* x, float* y, uint8_t* arg, int B, int H, int W, int C, cudaStream_t st);
+// colsum_atomic (optional, must be zero on entry): += sum of dx over (B,H,W) per channel, i.e. the
+// BiasAddGrad of the layer that fed the pool
 int maxpool_bwd_f32(const float* dy, const uint8_t* arg, const float* x, float* dx, int B, int H, int W,
-                    int C, int relu_mask, cudaStream_t st);
+                    int C, int relu_mask, cudaStream_t st, float* colsum_atomic = nullptr);
 int fc_fwd_f32(const float* x, const float* w, const float* b, float* y, int B, int K, int N, int relu,
                cudaStream_t st);
 int64_t colsum_scratch_bytes(int rows, int cols);
@@ -39,6 +41,14 @@ int conv5x5_dgrad_tc(const float* dy, const float* w, float* dx, int B, int H, i
 int64_t conv5x5_wgrad_tc_scratch_bytes(int B);
 int conv5x5_wgrad_tc(const float* x, const float* dy, float* dw, float* scratch, int B, int H, int W, int Cin,
                      int Cout, cudaStream_t st);
+int fc_fwd_tc_splits(int B, int K, int N);
+int fc_fwd_tc_splitk(const float* x, const float* w, float* part, int B, int K, int N, cudaStream_t st);
+int64_t fc_tail_scratch_bytes(int B, int F1, int F2, int NC);
+int fc_tail(const float* fc1_part, int n_part, const float* b1, float* full1, const float* w2, const float* b2,
+            const float* w3, const float* b3, const int32_t* labels, float* full2, float* logits, float* dlogits,
+            float* dfull2, float* dfull1, int32_t* pred, float* loss, int32_t* n_correct, int32_t* n_bad, float* dw2,
+            float* db2, float* dw3, float* db3, float* db1, void* scratch, float* zero_ptr, int zero_n, int B, int F1,
+            int F2, int NC, cudaStream_t st);
 bool conv1_tc_supported(int H, int W, int c_in, int c1);
 int conv1_pool_fwd_tc(const uint8_t* img, const float* w, const float* bias, float* pool, uint8_t* arg,
                       float* conv_dbg, int B, int ih, int iw, int H, int W, cudaStream_t st);

@@ -29,6 +29,8 @@ struct GemmArgs {
   int relu;
   const float* mask; int64_t ldmask;
   float* colsum;           // optional: colsum[n] = sum_m C[m,n] (after mask), needs gridDim.y == 1
+  int k_per_split;         // multiple of BK; blockIdx.z covers K range [z*kps, (z+1)*kps)
+  int64_t split_stride;    // floats between the C outputs of consecutive splits
 };
 
 template <int BN>
@@ -54,7 +56,8 @@ __global__ void __launch_bounds__(160, 1) tc_gemm_kernel(GemmArgs g) {
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
-  const int nkb = (g.K + BK - 1) / BK;
+  const int kbeg = blockIdx.z * g.k_per_split, kend = min(g.K, kbeg + g.k_per_split);
+  const int nkb = (kend - kbeg + BK - 1) / BK;
 
   if (tid == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(smem_u32(full + s), LOADERS); mbar_init(smem_u32(empty + s), 1); }
@@ -77,42 +80,42 @@ __global__ void __launch_bounds__(160, 1) tc_gemm_kernel(GemmArgs g) {
       mbar_wait(smem_u32(empty + s), ph ^ 1);
       uint8_t* sa = smem + s * S::STAGE;
       uint8_t* sb = sa + S::A_BYTES;
-      const int k0 = kb * BK;
+      const int k0 = kbeg + kb * BK;
       if (!A_MN) {   // A(m,k) = A[m*lda + k]: 8 consecutive threads read one row's 8 chunks
-#pragma unroll 4
+#pragma unroll
         for (int q = tid; q < BM * 8; q += LOADERS) {
           int c = q & 7, r = q >> 3;
           int m = m0 + r, k = k0 + c * 8;
           uint4 v = make_uint4(0, 0, 0, 0);
-          if (m < g.M && k < g.K) v = load_chunk(A + (int64_t)m * g.lda + k);
+          if (m < g.M && k < kend) v = load_chunk(A + (int64_t)m * g.lda + k);
           *reinterpret_cast<uint4*>(sa + c * S::A_K_LBO + r * 16) = v;
         }
       } else {       // A(m,k) = A[k*lda + m]: consecutive threads read consecutive m-chunks of one k row
-#pragma unroll 4
+#pragma unroll
         for (int q = tid; q < BK * (BM / 8); q += LOADERS) {
           int gi = q % (BM / 8), kk = q / (BM / 8);
           int m = m0 + gi * 8, k = k0 + kk;
           uint4 v = make_uint4(0, 0, 0, 0);
-          if (m < g.M && k < g.K) v = load_chunk(A + (int64_t)k * g.lda + m);
+          if (m < g.M && k < kend) v = load_chunk(A + (int64_t)k * g.lda + m);
           *reinterpret_cast<uint4*>(sa + gi * S::A_MN_SBO + kk * 16) = v;
         }
       }
       if (!B_MN) {   // B(k,n) = B[n*ldb + k]
-#pragma unroll 4
+#pragma unroll
         for (int q = tid; q < BN * 8; q += LOADERS) {
           int c = q & 7, r = q >> 3;
           int n = n0 + r, k = k0 + c * 8;
           uint4 v = make_uint4(0, 0, 0, 0);
-          if (n < g.N && k < g.K) v = load_chunk(B + (int64_t)n * g.ldb + k);
+          if (n < g.N && k < kend) v = load_chunk(B + (int64_t)n * g.ldb + k);
           *reinterpret_cast<uint4*>(sb + c * S::B_K_LBO + r * 16) = v;
         }
       } else {       // B(k,n) = B[k*ldb + n]
-#pragma unroll 4
+#pragma unroll
         for (int q = tid; q < BK * (BN / 8); q += LOADERS) {
           int gi = q % (BN / 8), kk = q / (BN / 8);
           int n = n0 + gi * 8, k = k0 + kk;
           uint4 v = make_uint4(0, 0, 0, 0);
-          if (n < g.N && k < g.K) v = load_chunk(B + (int64_t)k * g.ldb + n);
+          if (n < g.N && k < kend) v = load_chunk(B + (int64_t)k * g.ldb + n);
           *reinterpret_cast<uint4*>(sb + gi * S::B_MN_SBO + kk * 16) = v;
         }
       }
@@ -146,7 +149,7 @@ __global__ void __launch_bounds__(160, 1) tc_gemm_kernel(GemmArgs g) {
           if (n0 + c0 + j < g.N && !(__ldg(mk + j) > 0.f)) o[j] = 0.f;
       }
       if (m < g.M) {
-        float* out = g.C + (int64_t)m * g.ldc + n0 + c0;
+        float* out = g.C + (int64_t)blockIdx.z * g.split_stride + (int64_t)m * g.ldc + n0 + c0;
         if (n0 + c0 + 32 <= g.N && ((g.ldc & 3) == 0)) {
 #pragma unroll
           for (int j = 0; j < 32; j += 4)
@@ -209,7 +212,7 @@ int launch(const GemmArgs& g, cudaStream_t st) {
     B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
     attr_done = true;
   }
-  dim3 grid(cdiv(g.N, BN), cdiv(g.M, BM));
+  dim3 grid(cdiv(g.N, BN), cdiv(g.M, BM), cdiv(g.K, g.k_per_split));
   kern<<<grid, 160, S::TOTAL, st>>>(g);
   B200_LAUNCH_CHECK();
   return B200_OK;
@@ -234,7 +237,24 @@ int check_align(const GemmArgs& g, bool a_mn, bool b_mn) {
 // y = relu?(x @ w + b): A = x [B,K] K-major, B = w [K,N] MN-major
 int fc_fwd_tc(const float* x, const float* w, const float* b, float* y, int Bt, int K, int N, int relu,
               cudaStream_t st) {
-  GemmArgs g{Bt, N, K, x, K, w, N, y, N, b, relu, nullptr, 0, nullptr};
+  GemmArgs g{Bt, N, K, x, K, w, N, y, N, b, relu, nullptr, 0, nullptr, (int)round_up(K, BK), 0};
+  int rc = check_align(g, false, true);
+  if (rc) return rc;
+  return dispatch<false, true>(g, st);
+}
+
+// split-K forward product without epilogue: part[s][B][N] = x[:, ks] @ w[ks, :]; the consumer
+// (fc_tail) adds the partials, the bias and the ReLU.  Returns the number of splits used.
+int fc_fwd_tc_splits(int Bt, int K, int N) {
+  int tiles = cdiv(N, 64) * cdiv(Bt, BM);
+  int s = std::max(1, std::min(K / (3 * BK), (kNumSMs + tiles - 1) / tiles));
+  int kps = (int)round_up(cdiv(K, s), BK);
+  return cdiv(K, kps);
+}
+int fc_fwd_tc_splitk(const float* x, const float* w, float* part, int Bt, int K, int N, cudaStream_t st) {
+  int s = fc_fwd_tc_splits(Bt, K, N);
+  int kps = (int)round_up(cdiv(K, s), BK);
+  GemmArgs g{Bt, N, K, x, K, w, N, part, N, nullptr, 0, nullptr, 0, nullptr, kps, (int64_t)Bt * N};
   int rc = check_align(g, false, true);
   if (rc) return rc;
   return dispatch<false, true>(g, st);
@@ -245,12 +265,12 @@ int fc_bwd_tc(const float* x, const float* w, const float* dy, float* dx, float*
               int mask_x, cudaStream_t st) {
   int rc;
   {  // dw[K,N] = x^T[K,Bt] dy[Bt,N]: A(m=k_feat, k=batch) = x[batch*K + m] MN-major; B(k=batch, n) = dy MN-major
-    GemmArgs g{K, N, Bt, x, K, dy, N, dw, N, nullptr, 0, nullptr, 0, nullptr};
+    GemmArgs g{K, N, Bt, x, K, dy, N, dw, N, nullptr, 0, nullptr, 0, nullptr, (int)round_up(Bt, BK), 0};
     if ((rc = check_align(g, true, true))) return rc;
     if ((rc = dispatch<true, true>(g, st))) return rc;
   }
   if (dx) {  // dx[Bt,K] = dy[Bt,N] w^T: A = dy K-major; B(k=n_out, n=k_feat) = w[n*N + k] K-major
-    GemmArgs g{Bt, K, N, dy, N, w, N, dx, K, nullptr, 0, mask_x ? x : nullptr, K, nullptr};
+    GemmArgs g{Bt, K, N, dy, N, w, N, dx, K, nullptr, 0, mask_x ? x : nullptr, K, nullptr, (int)round_up(N, BK), 0};
     if ((rc = check_align(g, false, false))) return rc;
     if ((rc = dispatch<false, false>(g, st))) return rc;
   }

@@ -188,6 +188,16 @@ int b200_fc_bwd_bf16(const float* x, const float* w, const float* dy, float* dx,
 #define B200_STATIC_SCRATCH_BYTES (1 << 20)
 int b200_fc_bwd_f32_static(const float* x, const float* w, const float* dy, float* dx, float* dw, float* db,
                            int32_t batch, int32_t k, int32_t n, int32_t mask_x, void* stream);
+/* Everything above full1 in two launches: full2 (:139), logits (:145), cifar_loss (:150-157),
+ * batch_accuracy (:166-176) and all their gradients (dfull1 = gradient w.r.t. full1 after its ReluGrad,
+ * dW2, db2, dW3, db3, db1 = colsum(dfull1)).  fp32; sums over the batch in a fixed order.  full1 is the
+ * [batch,f1] input (post-ReLU); f1 % 32 == 0, f2 % 4 == 0, f2 <= 256. */
+int b200_fc_tail_scratch_bytes(int32_t batch, int32_t f1, int32_t f2, int32_t n_cls, int64_t* nbytes);
+int b200_fc_tail_f32(float* full1, const float* w2, const float* b2, const float* w3, const float* b3,
+                     const int32_t* labels, float* full2, float* logits, float* dlogits, float* dfull2, float* dfull1,
+                     int32_t* pred, float* loss, int32_t* n_correct, int32_t* n_bad, float* dw2, float* db2, float* dw3,
+                     float* db3, float* db1, void* scratch, int64_t scratch_bytes, int32_t batch, int32_t f1, int32_t f2,
+                     int32_t n_cls, void* stream);
 /* cifar_loss (:150-157), batch_accuracy (:166-176) and the first backward step: dlogits =
  * (softmax - onehot)/batch * [logits > 0] (ReLU on the logits, :145).  Labels outside
  * [0,n_cls) set *n_bad (int32, device) > 0 and contribute nothing. */

@@ -396,3 +396,52 @@ def test_bad_inputs_raise():
     e2 = _engine(8)
     with pytest.raises(_lib.B200Error):
         e2.backward()                                  # backward before forward
+
+
+@pytest.mark.parametrize("B", [128, 6, 2048])
+def test_fc_tail_fused(lib, B):
+    """full2 / logits / loss / accuracy and every gradient above full1 in two launches."""
+    F1, F2, NC = 384, 192, 10
+    rng = np.random.default_rng(61)
+    full1 = np.maximum(rng.normal(size=(B, F1)), 0).astype(np.float32)
+    w2 = (rng.normal(size=(F1, F2)) * 0.05).astype(np.float32)
+    b2 = (rng.normal(size=(F2,)) * 0.1).astype(np.float32)
+    w3 = (rng.normal(size=(F2, NC)) * 0.1).astype(np.float32)
+    b3 = (rng.normal(size=(NC,)) * 0.1).astype(np.float32)
+    labels = rng.integers(0, NC, (B,)).astype(np.int32)
+    t = lambda *s, dt=torch.float32: torch.full(s, -7, dtype=dt, device="cuda")
+    full2, logits, dlogits, dfull2, dfull1 = t(B, F2), t(B, NC), t(B, NC), t(B, F2), t(B, F1)
+    pred, loss, nc, nbad = t(B, dt=torch.int32), t(1), t(1, dt=torch.int32), t(1, dt=torch.int32)
+    dw2, db2, dw3, db3, db1 = t(F1, F2), t(F2), t(F2, NC), t(NC), t(F1)
+    nb = C.c_int64()
+    ck(lib.b200_fc_tail_scratch_bytes(B, F1, F2, NC, C.byref(nb)))
+    scr = torch.empty(nb.value, dtype=torch.uint8, device="cuda")
+    f1d, w2d, b2d, w3d, b3d, labd = dev(full1), dev(w2), dev(b2), dev(w3), dev(b3), dev(labels)   # keep alive
+    ck(lib.b200_fc_tail_f32(f1d.data_ptr(), w2d.data_ptr(), b2d.data_ptr(), w3d.data_ptr(),
+                            b3d.data_ptr(), labd.data_ptr(), full2.data_ptr(), logits.data_ptr(),
+                            dlogits.data_ptr(), dfull2.data_ptr(), dfull1.data_ptr(), pred.data_ptr(), loss.data_ptr(),
+                            nc.data_ptr(), nbad.data_ptr(), dw2.data_ptr(), db2.data_ptr(), dw3.data_ptr(),
+                            db3.data_ptr(), db1.data_ptr(), scr.data_ptr(), nb.value, B, F1, F2, NC, stream()))
+    torch.cuda.synchronize()
+    x = full1.astype(np.float64)
+    # the kernel keeps W2 in shared memory rounded to bf16 (both products that read it); everything
+    # else is fp32, so against the oracle on the rounded W2 the usual fp32 tolerance holds
+    w2 = torch.as_tensor(w2).to(torch.bfloat16).to(torch.float64).numpy()
+    f2 = np.maximum(x @ w2 + b2, 0)
+    lg = np.maximum(f2 @ w3 + b3, 0)
+    wl, _, back = rn.softmax_xent(lg, labels)
+    _, wpred, wn = rn.batch_accuracy(lg, labels)
+    d = back / B * (lg > 0)
+    d2 = (d @ w3.T.astype(np.float64)) * (f2 > 0)
+    d1 = (d2 @ w2.T.astype(np.float64)) * (x > 0)
+    for got, want, name in ((full2, f2, "full2"), (logits, lg, "logits"), (dlogits, d, "dlogits"), (dfull2, d2, "dfull2"),
+                            (dfull1, d1, "dfull1"), (dw2, x.T @ d2, "dw2"), (db2, d2.sum(0), "db2"),
+                            (dw3, f2.T @ d, "dw3"), (db3, d.sum(0), "db3"), (db1, d1.sum(0), "db1")):
+        assert relerr(got.cpu().numpy(), want) <= RTOL_F32, name
+    assert abs(float(loss) - wl) <= RTOL_F32 * abs(wl)
+    srt = np.sort(lg, axis=1)
+    safe = ((srt[:, -1] - srt[:, -2]) > 1e-4) | (srt[:, -1] == 0)
+    np.testing.assert_array_equal(pred.cpu().numpy()[safe], wpred[safe])
+    if safe.all():
+        assert int(nc) == wn
+    assert int(nbad) == 0
