@@ -32,7 +32,7 @@ def _require_cuda():
 
 class TrainStepEngine:
     def __init__(self, batch=128, img_hw=(32, 32), crop_hw=(24, 24), c_in=3, c1=64, c2=64, f1=384,
-                 f2=192, n_cls=10, mode="fp32", device=None):
+                 f2=192, n_cls=10, mode="fp32", device=None, params=None):
         _require_cuda()
         self.lib = _lib.load()
         self.device = torch.device("cuda", torch.cuda.current_device() if device is None else device)
@@ -55,7 +55,12 @@ class TrainStepEngine:
         self.shapes = dict(zip(PARAM_NAMES, [
             (5, 5, c_in, c1), (c1,), (5, 5, c1, c2), (c2,), (h2 * w2 * c2, f1), (f1,), (f1, f2), (f2,),
             (f2, n_cls), (n_cls,)]))
-        self.params = torch.zeros(self.total, dtype=torch.float32, device=self.device)
+        if params is not None:      # a second tower sharing the variables (scope.reuse_variables(), :209)
+            if params.numel() != self.total or params.device != self.device or params.dtype != torch.float32:
+                raise ValueError("shared parameter buffer does not match this engine")
+            self.params = params
+        else:
+            self.params = torch.zeros(self.total, dtype=torch.float32, device=self.device)
         self.grads = torch.zeros(self.total, dtype=torch.float32, device=self.device)
         nb = C.c_int64()
         check(self.lib.b200_workspace_bytes(h, C.byref(nb)))
