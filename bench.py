@@ -396,7 +396,14 @@ def main():
                        "ms_per_step_graph_hot": ms_hot / K}, open(args.sites_json, "w"), indent=1)
         print(json.dumps(out))
     if world > 1:
-        dist.destroy_process_group()
+        # CUDA graphs that captured NCCL work are still alive here; tearing the communicator down under
+        # them can deadlock, so release them first and leave without running further destructors.
+        torch.cuda.synchronize()
+        dist.barrier()
+        del graph, host_graphs
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 if __name__ == "__main__":
