@@ -125,6 +125,7 @@ int b200_create(const b200_config* c, b200_handle* out) {
   scratch = std::max(scratch, conv5x5_wgrad_tc_scratch_bytes(c->batch) +
                                   colsum_scratch_bytes(c->batch * h->h1 * h->w1, c->c2));
   h->add("scratch", scratch, 1);
+  h->add("w2_packed", conv5x5_packed_bytes(c->c1, c->c2), 1);
   h->add("fc1_part", (int64_t)fc_fwd_tc_splits(c->batch, h->flat, c->f1) * B * c->f1, 4);
   h->add("tail_scratch", fc_tail_scratch_bytes(c->batch, c->f1, c->f2, c->n_cls), 1);
   h->add("loss", 1, 4); h->add("n_correct", 1, 4); h->add("n_bad", 1, 4); h->add("pred", B, 4);
@@ -222,8 +223,12 @@ int b200_forward(b200_handle h, const uint8_t* images, const int32_t* labels, vo
     SITE("conv1_fwd", conv5x5_fwd_f32(x, h->P(P_W1), h->P(P_B1), conv1, c.batch, c.crop_h, c.crop_w, c.c_in, c.c1, 1, st));
     SITE("pool1_fwd", maxpool_fwd_f32(conv1, pool1, h->ptr<uint8_t>("arg1"), c.batch, c.crop_h, c.crop_w, c.c1, st));
   }
-  if (tc)
-    SITE("conv2_fwd", conv5x5_fwd_tc(pool1, h->P(P_W2), h->P(P_B2), conv2, c.batch, h->h1, h->w1, c.c1, c.c2, 1, st));
+  if (tc) {
+    // the filter may have been changed by the caller or the last update: repack it every step (2 us)
+    SITE("conv2_pack", pack_conv_weights(h->P(P_W2), h->ptr<void>("w2_packed"), c.c1, c.c2, st));
+    SITE("conv2_fwd", conv5x5_fwd_tc(pool1, h->ptr<void>("w2_packed"), h->P(P_B2), conv2, c.batch, h->h1, h->w1, c.c1,
+                                     c.c2, 1, st));
+  }
   else
     SITE("conv2_fwd", conv5x5_fwd_f32(pool1, h->P(P_W2), h->P(P_B2), conv2, c.batch, h->h1, h->w1, c.c1, c.c2, 1, st));
   SITE("pool2_fwd", maxpool_fwd_f32(conv2, pool2, h->ptr<uint8_t>("arg2"), c.batch, h->h1, h->w1, c.c2, st));
@@ -281,7 +286,7 @@ int b200_backward(b200_handle h, void* stream) {
   if (tc) {
     SITE("conv2_wgrad", conv5x5_wgrad_tc(h->ptr<float>("pool1"), dconv2, h->G(P_W2), scratch, c.batch, h->h1, h->w1,
                                          c.c1, c.c2, st));
-    SITE("conv2_dgrad", conv5x5_dgrad_tc(dconv2, h->P(P_W2), dpool1, c.batch, h->h1, h->w1, c.c1, c.c2, st));
+    SITE("conv2_dgrad", conv5x5_dgrad_tc(dconv2, h->ptr<void>("w2_packed"), dpool1, c.batch, h->h1, h->w1, c.c1, c.c2, st));
   } else {
     SITE("conv2_wgrad", conv5x5_wgrad_f32(h->ptr<float>("pool1"), dconv2, h->G(P_W2), h->G(P_B2), scratch, c.batch,
                                           h->h1, h->w1, c.c1, c.c2, st));
@@ -382,7 +387,7 @@ int b200_launches_per_step(b200_handle h, int32_t* n) {
   if (h->cfg.mode == B200_MODE_BF16) {
     // conv1 (3 or 1), conv2, pool2, FC1 split-K, tail x2 | FC1 bwd x2, pool2 bwd, conv2 wgrad x2, dgrad, conv1 wgrad (2 or 1+4), sgd
     const bool f1 = conv1_tc_supported(h->cfg.crop_h, h->cfg.crop_w, h->cfg.c_in, h->cfg.c1);
-    *n = (f1 ? 1 : 3) + 1 + 1 + 1 + 2 + 2 + 1 + 2 + 1 + (f1 ? 2 : 5) + 1;
+    *n = (f1 ? 1 : 3) + 2 + 1 + 1 + 2 + 2 + 1 + 2 + 1 + (f1 ? 2 : 5) + 1;
   }
   return B200_OK;
 }
@@ -466,15 +471,24 @@ int b200_conv1_wgrad_bf16(const uint8_t* images, const float* dpool, const float
   return conv1_wgrad_tc(images, dpool, pool, arg, dw, db, (float*)scratch, batch, img_h, img_w, crop_h, crop_w,
                         (cudaStream_t)stream);
 }
-int b200_conv5x5_fwd_bf16(const float* x, const float* w, const float* bias, float* y, int32_t batch, int32_t h,
-                          int32_t wd, int32_t c_in, int32_t c_out, int32_t relu, void* stream) {
-  B200_REQUIRE(x && w && y, "null pointer");
-  return conv5x5_fwd_tc(x, w, bias, y, batch, h, wd, c_in, c_out, relu, (cudaStream_t)stream);
+int b200_conv5x5_packed_bytes(int32_t c_in, int32_t c_out, int64_t* nbytes) {
+  B200_REQUIRE(nbytes && c_in > 0 && c_out > 0, "bad argument");
+  *nbytes = conv5x5_packed_bytes(c_in, c_out);
+  return B200_OK;
 }
-int b200_conv5x5_dgrad_bf16(const float* dy, const float* w, float* dx, int32_t batch, int32_t h, int32_t wd,
+int b200_conv5x5_pack_weights(const float* w, void* w_packed, int32_t c_in, int32_t c_out, void* stream) {
+  B200_REQUIRE(w && w_packed, "null pointer");
+  return pack_conv_weights(w, w_packed, c_in, c_out, (cudaStream_t)stream);
+}
+int b200_conv5x5_fwd_bf16(const float* x, const void* w_packed, const float* bias, float* y, int32_t batch, int32_t h,
+                          int32_t wd, int32_t c_in, int32_t c_out, int32_t relu, void* stream) {
+  B200_REQUIRE(x && w_packed && y, "null pointer");
+  return conv5x5_fwd_tc(x, w_packed, bias, y, batch, h, wd, c_in, c_out, relu, (cudaStream_t)stream);
+}
+int b200_conv5x5_dgrad_bf16(const float* dy, const void* w_packed, float* dx, int32_t batch, int32_t h, int32_t wd,
                             int32_t c_in, int32_t c_out, void* stream) {
-  B200_REQUIRE(dy && w && dx, "null pointer");
-  return conv5x5_dgrad_tc(dy, w, dx, batch, h, wd, c_in, c_out, (cudaStream_t)stream);
+  B200_REQUIRE(dy && w_packed && dx, "null pointer");
+  return conv5x5_dgrad_tc(dy, w_packed, dx, batch, h, wd, c_in, c_out, (cudaStream_t)stream);
 }
 int b200_conv5x5_wgrad_bf16_scratch_bytes(int32_t batch, int64_t* nbytes) {
   B200_REQUIRE(nbytes && batch > 0, "bad argument");

@@ -34,9 +34,12 @@ int fc_fwd_tc(const float* x, const float* w, const float* b, float* y, int B, i
               cudaStream_t st);
 int fc_bwd_tc(const float* x, const float* w, const float* dy, float* dx, float* dw, int B, int K, int N,
               int mask_x, cudaStream_t st);
-int conv5x5_fwd_tc(const float* x, const float* w, const float* bias, float* y, int B, int H, int W, int Cin,
+// wp: the filter packed once per step by pack_conv_weights (conv5x5_packed_bytes bytes)
+int64_t conv5x5_packed_bytes(int Cin, int Cout);
+int pack_conv_weights(const float* w, void* wp, int Cin, int Cout, cudaStream_t st);
+int conv5x5_fwd_tc(const float* x, const void* wp, const float* bias, float* y, int B, int H, int W, int Cin,
                    int Cout, int relu, cudaStream_t st);
-int conv5x5_dgrad_tc(const float* dy, const float* w, float* dx, int B, int H, int W, int Cin, int Cout,
+int conv5x5_dgrad_tc(const float* dy, const void* wp, float* dx, int B, int H, int W, int Cin, int Cout,
                      cudaStream_t st);
 int64_t conv5x5_wgrad_tc_scratch_bytes(int B);
 int conv5x5_wgrad_tc(const float* x, const float* dy, float* dw, float* scratch, int B, int H, int W, int Cin,

@@ -76,7 +76,8 @@ __device__ __forceinline__ void fill_strip(uint8_t* strip, const float* __restri
 
 struct ConvArgs {
   const float* x;      // [B,H,W,KC]
-  const float* w;      // HWIO fp32: forward [25][KC][NC]; dgrad: the FORWARD filter [25][NC][KC]
+  const uint8_t* wp;   // filter packed by pack_conv_weights (bf16, ready-made shared-memory images per tap)
+  int cin_f, cout_f;   // the FORWARD filter's channel counts (packing geometry)
   const float* bias;   // [NC] or null
   float* y;            // [B,H,W,NC]
   int relu;
@@ -84,12 +85,14 @@ struct ConvArgs {
 };
 
 // ---------------------------------------------------------------------------------------------------
-// forward / input-gradient convolution.  grid = (ceil(B/ipc), NC/64), 160 threads.
+// forward / input-gradient convolution.  grid = (ceil(B/ipc), NC/64), 192 threads: warps 0-3 stage
+// the strip and run the epilogue, warp 4 issues MMAs, warp 5 streams the packed filter taps with bulk
+// (TMA) copies through a 6-stage ring.
 // DGRAD = false: y = conv(x, w)            B operand (kc,nc) = w[tap][kc][nc]     (MN-major)
 // DGRAD = true : y = conv(x, rot180(w)^T)  B operand (kc,nc) = w[24-tap][nc][kc]  (K-major)
 // ---------------------------------------------------------------------------------------------------
 template <bool DGRAD>
-__global__ void __launch_bounds__(160, 1) conv5x5_tc_kernel(ConvArgs a) {
+__global__ void __launch_bounds__(192, 1) conv5x5_tc_kernel(ConvArgs a) {
   constexpr int BN = 64;
   const ConvGeom& g = a.g;
   extern __shared__ __align__(128) uint8_t smem[];
@@ -113,7 +116,7 @@ __global__ void __launch_bounds__(160, 1) conv5x5_tc_kernel(ConvArgs a) {
   const int tmem_cols = g.tiles * BN <= 64 ? 64 : g.tiles * BN <= 128 ? 128 : g.tiles * BN <= 256 ? 256 : 512;
 
   if (tid == 0) {
-    for (int s = 0; s < WSTAGES; ++s) { mbar_init(smem_u32(wfull + s), LOADERS); mbar_init(smem_u32(wempty + s), 1); }
+    for (int s = 0; s < WSTAGES; ++s) { mbar_init(smem_u32(wfull + s), 1); mbar_init(smem_u32(wempty + s), 1); }
     mbar_init(smem_u32(strip_full), LOADERS);
     mbar_init(smem_u32(accum), 1);
     fence_mbar_init();
@@ -131,30 +134,6 @@ __global__ void __launch_bounds__(160, 1) conv5x5_tc_kernel(ConvArgs a) {
     fill_strip(strip, a.x, g, n_img0, g.KC, g.ch_stride, tid);
     fence_proxy_async();
     mbar_arrive(smem_u32(strip_full));
-    // ---- filter taps through the ring ------------------------------------------------------------
-    for (int tap = 0; tap < 25; ++tap) {
-      const int s = tap % WSTAGES;
-      const uint32_t ph = (tap / WSTAGES) & 1;
-      mbar_wait(smem_u32(wempty + s), ph ^ 1);
-      uint8_t* ws = wring + s * wstage;
-      if (!DGRAD) {
-        const float* wt = a.w + (int64_t)tap * g.KC * g.NC;
-        for (int q = tid; q < g.KC * (BN / 8); q += LOADERS) {
-          int gi = q & 7, k = q >> 3;
-          uint4 v = load_chunk(wt + (int64_t)k * g.NC + nc0 + gi * 8);
-          *reinterpret_cast<uint4*>(ws + gi * w_mn_sbo + k * 16) = v;
-        }
-      } else {
-        const float* wt = a.w + (int64_t)(24 - tap) * g.NC * g.KC;       // forward filter [tap][cin=NC][cout=KC]
-        for (int q = tid; q < BN * kchunks; q += LOADERS) {
-          int c = q % kchunks, n = q / kchunks;
-          uint4 v = load_chunk(wt + (int64_t)(nc0 + n) * g.KC + c * 8);
-          *reinterpret_cast<uint4*>(ws + c * w_k_lbo + n * 16) = v;
-        }
-      }
-      fence_proxy_async();
-      mbar_arrive(smem_u32(wfull + s));
-    }
     // ---- epilogue: TMEM -> registers -> (+bias, relu) -> dense NHWC fp32 ---------------------------
     mbar_wait(smem_u32(accum), 0);
     tc_fence_after();
@@ -187,7 +166,7 @@ __global__ void __launch_bounds__(160, 1) conv5x5_tc_kernel(ConvArgs a) {
       }
     }
     tc_fence_before();
-  } else {
+  } else if (warp == 4) {
     if (lane == 0) {
       const uint32_t idesc = make_idesc(128, BN, false, !DGRAD);
       mbar_wait(smem_u32(strip_full), 0);
@@ -213,11 +192,48 @@ __global__ void __launch_bounds__(160, 1) conv5x5_tc_kernel(ConvArgs a) {
       umma_commit(smem_u32(accum));
     }
     __syncwarp();
+  } else {
+    // ---- filter taps: one thread, bulk copies global -> shared, completion counted in bytes ----------
+    if (lane == 0) {
+      const int img = (a.cout_f / 8) * (a.cin_f * 16 + 16);             // bytes of one packed tap
+      for (int tap = 0; tap < 25; ++tap) {
+        const int s = tap % WSTAGES;
+        const uint32_t ph = (tap / WSTAGES) & 1;
+        mbar_wait(smem_u32(wempty + s), ph ^ 1);
+        const uint32_t ws = smem_u32(wring + s * wstage);
+        const uint32_t bar = smem_u32(wfull + s);
+        if (!DGRAD) {     // N-groups nc0/8 .. +8 of tap `tap` are contiguous: one copy
+          const uint32_t bytes = (BN / 8) * w_mn_sbo;
+          mbar_arrive_expect_tx(bar, bytes);
+          bulk_g2s(ws, a.wp + (size_t)tap * img + (size_t)(nc0 / 8) * w_mn_sbo, bytes, bar);
+        } else {          // tap 24-t read K-major: per k-chunk (forward cout group) the 64 rows nc0.. are contiguous
+          mbar_arrive_expect_tx(bar, (uint32_t)kchunks * BN * 16);
+          const uint8_t* src = a.wp + (size_t)(24 - tap) * img + (size_t)nc0 * 16;
+          for (int c = 0; c < kchunks; ++c) bulk_g2s(ws + c * w_k_lbo, src + (size_t)c * (a.cin_f * 16 + 16), BN * 16, bar);
+        }
+      }
+    }
+    __syncwarp();
   }
   __syncthreads();
   if (warp == 4) {
     tc_fence_after();
     tmem_dealloc(tmem, tmem_cols);
+  }
+}
+
+// fp32 HWIO filter [25][Cin][Cout] -> bf16 images: P[tap][g = cout/8][cin][cout%8], group stride
+// Cin*16+16 bytes.  Read MN-major (groups along N) it is the forward B operand of tap `tap`; read
+// K-major (groups along K) it is the input-gradient B operand of tap 24-tap.  One packed copy serves both.
+__global__ void pack_conv_weights_kernel(const float* __restrict__ w, uint8_t* __restrict__ wp, int Cin, int Cout) {
+  const int gstride = Cin * 16 + 16, img = (Cout / 8) * gstride;
+  const int total = 25 * Cin * (Cout / 8);
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int g = i % (Cout / 8);
+    const int t = i / (Cout / 8);
+    const int cin = t % Cin, tap = t / Cin;
+    *reinterpret_cast<uint4*>(wp + (size_t)tap * img + g * gstride + cin * 16) =
+        load_chunk(w + ((size_t)tap * Cin + cin) * Cout + g * 8);
   }
 }
 
@@ -234,12 +250,12 @@ int pick_ipc(int B, int H, int W, int KC) {
 }
 
 template <bool DGRAD>
-int launch_conv(const float* x, const float* w, const float* bias, float* y, int B, int H, int W, int KC, int NC,
+int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, int B, int H, int W, int KC, int NC,
                 int relu, cudaStream_t st) {
   B200_REQUIRE(B > 0 && H > 0 && W > 0, "conv5x5_tc: bad shape");
   B200_REQUIRE(KC % 16 == 0 && NC % 64 == 0, "conv5x5_tc: channels must be multiples of 16 (in) / 64 (out), got %d/%d",
                KC, NC);
-  B200_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)w & 15) == 0 && ((uintptr_t)y & 15) == 0,
+  B200_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)wp & 15) == 0 && ((uintptr_t)y & 15) == 0,
                "conv5x5_tc: pointers must be 16-byte aligned");
   int ipc = pick_ipc(B, H, W, KC);
   ConvGeom g = make_geom(B, H, W, KC, NC, ipc);
@@ -254,9 +270,9 @@ int launch_conv(const float* x, const float* w, const float* bias, float* y, int
     B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr = 227 * 1024;
   }
-  ConvArgs a{x, w, bias, y, relu, g};
+  ConvArgs a{x, wp, DGRAD ? NC : KC, DGRAD ? KC : NC, bias, y, relu, g};
   dim3 grid(cdiv(B, ipc), NC / 64);
-  kern<<<grid, 160, smem, st>>>(a);
+  kern<<<grid, 192, smem, st>>>(a);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
@@ -387,14 +403,23 @@ __global__ void reduce_partials_tc(const float* __restrict__ part, float* __rest
 int wgrad_splits_tc(int B) { return std::max(1, std::min(B, (kNumSMs + 4) / 5)); }
 }  // namespace
 
-int conv5x5_fwd_tc(const float* x, const float* w, const float* bias, float* y, int B, int H, int W, int Cin,
+int64_t conv5x5_packed_bytes(int Cin, int Cout) { return 25ll * (Cout / 8) * (Cin * 16 + 16); }
+int pack_conv_weights(const float* w, void* wp, int Cin, int Cout, cudaStream_t st) {
+  B200_REQUIRE(Cin % 8 == 0 && Cout % 8 == 0 && Cin > 0 && Cout > 0, "pack_conv_weights: channels must be multiples of 8");
+  B200_REQUIRE(((uintptr_t)w & 15) == 0 && ((uintptr_t)wp & 15) == 0, "pack_conv_weights: pointers must be 16-byte aligned");
+  const int total = 25 * Cin * (Cout / 8);
+  pack_conv_weights_kernel<<<std::min(cdiv(total, 256), 2 * kNumSMs), 256, 0, st>>>(w, (uint8_t*)wp, Cin, Cout);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+int conv5x5_fwd_tc(const float* x, const void* wp, const float* bias, float* y, int B, int H, int W, int Cin,
                    int Cout, int relu, cudaStream_t st) {
-  return launch_conv<false>(x, w, bias, y, B, H, W, Cin, Cout, relu, st);
+  return launch_conv<false>(x, (const uint8_t*)wp, bias, y, B, H, W, Cin, Cout, relu, st);
 }
 // dx = Conv2DBackpropInput(dy, w): contraction over the forward Cout, output the forward Cin
-int conv5x5_dgrad_tc(const float* dy, const float* w, float* dx, int B, int H, int W, int Cin, int Cout,
+int conv5x5_dgrad_tc(const float* dy, const void* wp, float* dx, int B, int H, int W, int Cin, int Cout,
                      cudaStream_t st) {
-  return launch_conv<true>(dy, w, nullptr, dx, B, H, W, Cout, Cin, 0, st);
+  return launch_conv<true>(dy, (const uint8_t*)wp, nullptr, dx, B, H, W, Cout, Cin, 0, st);
 }
 int64_t conv5x5_wgrad_tc_scratch_bytes(int B) { return (int64_t)wgrad_splits_tc(B) * 25 * 64 * 64 * 4; }
 int conv5x5_wgrad_tc(const float* x, const float* dy, float* dw, float* scratch, int B, int H, int W, int Cin,

@@ -160,10 +160,15 @@ int b200_conv1_wgrad_bf16(const uint8_t* images, const float* dpool, const float
 /* conv2d / Conv2DBackpropInput / Conv2DBackpropFilter of :118 on the tensor cores (tcgen05 implicit
  * GEMM over a zero-padded shared-memory strip; bf16 operands rounded from the fp32 tensors, fp32
  * accumulation).  c_in % 16 == 0 and c_out % 64 == 0 (wgrad: 64 -> 64 only).  The wgrad scratch
- * holds per-CTA partial sums that a second kernel adds in a fixed order. */
-int b200_conv5x5_fwd_bf16(const float* x, const float* w, const float* bias, float* y, int32_t batch, int32_t h,
+ * holds per-CTA partial sums that a second kernel adds in a fixed order.
+ * forward and dgrad take the filter PACKED: b200_conv5x5_pack_weights turns the fp32 HWIO tensor into
+ * bf16 shared-memory images (b200_conv5x5_packed_bytes bytes) that the kernels fetch with bulk copies;
+ * one packed copy serves both directions. */
+int b200_conv5x5_packed_bytes(int32_t c_in, int32_t c_out, int64_t* nbytes);
+int b200_conv5x5_pack_weights(const float* w, void* w_packed, int32_t c_in, int32_t c_out, void* stream);
+int b200_conv5x5_fwd_bf16(const float* x, const void* w_packed, const float* bias, float* y, int32_t batch, int32_t h,
                           int32_t wd, int32_t c_in, int32_t c_out, int32_t relu, void* stream);
-int b200_conv5x5_dgrad_bf16(const float* dy, const float* w, float* dx, int32_t batch, int32_t h, int32_t wd,
+int b200_conv5x5_dgrad_bf16(const float* dy, const void* w_packed, float* dx, int32_t batch, int32_t h, int32_t wd,
                             int32_t c_in, int32_t c_out, void* stream);
 int b200_conv5x5_wgrad_bf16_scratch_bytes(int32_t batch, int64_t* nbytes);
 int b200_conv5x5_wgrad_bf16(const float* x, const float* dy, float* dw, void* scratch, int64_t scratch_bytes,

@@ -42,6 +42,15 @@ def lib():
     return _lib.load()
 
 
+def pack_filter(lib, wd, cin, cout):
+    """fp32 HWIO filter on the device -> the packed bf16 images the tcgen05 conv kernels stream."""
+    nb = C.c_int64()
+    _lib.check(lib.b200_conv5x5_packed_bytes(cin, cout, C.byref(nb)))
+    wp = torch.full((nb.value,), 0x7f, dtype=torch.uint8, device="cuda")      # pad bytes = garbage on purpose
+    _lib.check(lib.b200_conv5x5_pack_weights(wd.data_ptr(), wp.data_ptr(), cin, cout, stream()))
+    return wp
+
+
 @pytest.mark.parametrize("B,K,N", [(128, 2304, 384), (128, 384, 192), (8, 2304, 384), (256, 384, 192),
                                    (136, 200, 72), (128, 192, 16)])
 def test_fc_tensorcore(lib, B, K, N):
@@ -97,17 +106,18 @@ def test_conv_tensorcore_fwd_dgrad_wgrad(lib, B, H, W):
     xd, wd, bd, dyd = dev(x), dev(w), dev(b), dev(dy)
     xr, wr, dyr = bf16_round(x), bf16_round(w), bf16_round(dy)
     y = torch.full((B, H, W, Cout), float("nan"), device="cuda")
-    _lib.check(lib.b200_conv5x5_fwd_bf16(xd.data_ptr(), wd.data_ptr(), bd.data_ptr(), y.data_ptr(), B, H, W, Cin, Cout,
+    wp = pack_filter(lib, wd, Cin, Cout)
+    _lib.check(lib.b200_conv5x5_fwd_bf16(xd.data_ptr(), wp.data_ptr(), bd.data_ptr(), y.data_ptr(), B, H, W, Cin, Cout,
                                          1, stream()))
     torch.cuda.synchronize()
     assert relerr(y.cpu().numpy(), np.maximum(rn.conv2d_same(xr, wr) + b, 0)) <= TIGHT
     assert relerr(y.cpu().numpy(), np.maximum(rn.conv2d_same(x.astype(np.float64), w.astype(np.float64)) + b, 0)) <= LOOSE
-    _lib.check(lib.b200_conv5x5_fwd_bf16(xd.data_ptr(), wd.data_ptr(), None, y.data_ptr(), B, H, W, Cin, Cout, 0,
+    _lib.check(lib.b200_conv5x5_fwd_bf16(xd.data_ptr(), wp.data_ptr(), None, y.data_ptr(), B, H, W, Cin, Cout, 0,
                                          stream()))
     torch.cuda.synchronize()
     assert relerr(y.cpu().numpy(), rn.conv2d_same(xr, wr)) <= TIGHT
     dx = torch.full((B, H, W, Cin), float("nan"), device="cuda")
-    _lib.check(lib.b200_conv5x5_dgrad_bf16(dyd.data_ptr(), wd.data_ptr(), dx.data_ptr(), B, H, W, Cin, Cout, stream()))
+    _lib.check(lib.b200_conv5x5_dgrad_bf16(dyd.data_ptr(), wp.data_ptr(), dx.data_ptr(), B, H, W, Cin, Cout, stream()))
     torch.cuda.synchronize()
     assert relerr(dx.cpu().numpy(), rn.conv2d_same_grad_input(dyr, wr)) <= TIGHT
     assert relerr(dx.cpu().numpy(), rn.conv2d_same_grad_input(dy.astype(np.float64), w.astype(np.float64))) <= LOOSE
@@ -135,10 +145,11 @@ def test_conv_tensorcore_rectangular_and_asymmetric_channels(lib):
     xd, wd, dyd = dev(x), dev(w), dev(dy)
     xr, wr, dyr = bf16_round(x), bf16_round(w), bf16_round(dy)
     y = torch.full((B, H, W, Cout), float("nan"), device="cuda")
-    _lib.check(lib.b200_conv5x5_fwd_bf16(xd.data_ptr(), wd.data_ptr(), None, y.data_ptr(), B, H, W, Cin, Cout, 0,
+    wp = pack_filter(lib, wd, Cin, Cout)
+    _lib.check(lib.b200_conv5x5_fwd_bf16(xd.data_ptr(), wp.data_ptr(), None, y.data_ptr(), B, H, W, Cin, Cout, 0,
                                          stream()))
     dx = torch.full((B, H, W, Cin), float("nan"), device="cuda")
-    assert lib.b200_conv5x5_dgrad_bf16(dyd.data_ptr(), wd.data_ptr(), dx.data_ptr(), B, H, W, Cin, Cout,
+    assert lib.b200_conv5x5_dgrad_bf16(dyd.data_ptr(), wp.data_ptr(), dx.data_ptr(), B, H, W, Cin, Cout,
                                        stream()) == _lib.E_INVALID      # output channels (Cin=32) not a multiple of 64
     torch.cuda.synchronize()
     assert relerr(y.cpu().numpy(), rn.conv2d_same(xr, wr)) <= TIGHT
@@ -146,7 +157,9 @@ def test_conv_tensorcore_rectangular_and_asymmetric_channels(lib):
     w = (rng.normal(size=(5, 5, Cin, Cout)) * 0.05).astype(np.float32)
     dy = rng.normal(size=(B, H, W, Cout)).astype(np.float32)
     dx = torch.full((B, H, W, Cin), float("nan"), device="cuda")
-    _lib.check(lib.b200_conv5x5_dgrad_bf16(dev(dy).data_ptr(), dev(w).data_ptr(), dx.data_ptr(), B, H, W, Cin, Cout,
+    dyd2, wd2 = dev(dy), dev(w)
+    wp2 = pack_filter(lib, wd2, Cin, Cout)
+    _lib.check(lib.b200_conv5x5_dgrad_bf16(dyd2.data_ptr(), wp2.data_ptr(), dx.data_ptr(), B, H, W, Cin, Cout,
                                            stream()))
     torch.cuda.synchronize()
     assert relerr(dx.cpu().numpy(), rn.conv2d_same_grad_input(bf16_round(dy), bf16_round(w))) <= TIGHT
