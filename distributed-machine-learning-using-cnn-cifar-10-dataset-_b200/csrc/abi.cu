@@ -471,6 +471,10 @@ int b200_conv1_wgrad_bf16(const uint8_t* images, const float* dpool, const float
   return conv1_wgrad_tc(images, dpool, pool, arg, dw, db, (float*)scratch, batch, img_h, img_w, crop_h, crop_w,
                         (cudaStream_t)stream);
 }
+int b200_debug_conv_timeline(int64_t* device_buf8) {
+  conv5x5_set_timeline(reinterpret_cast<long long*>(device_buf8));
+  return B200_OK;
+}
 int b200_conv5x5_packed_bytes(int32_t c_in, int32_t c_out, int64_t* nbytes) {
   B200_REQUIRE(nbytes && c_in > 0 && c_out > 0, "bad argument");
   *nbytes = conv5x5_packed_bytes(c_in, c_out);

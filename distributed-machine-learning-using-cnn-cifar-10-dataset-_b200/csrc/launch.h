@@ -35,6 +35,7 @@ int fc_fwd_tc(const float* x, const float* w, const float* b, float* y, int B, i
 int fc_bwd_tc(const float* x, const float* w, const float* dy, float* dx, float* dw, int B, int K, int N,
               int mask_x, cudaStream_t st);
 // wp: the filter packed once per step by pack_conv_weights (conv5x5_packed_bytes bytes)
+void conv5x5_set_timeline(long long* dev_buf);   // diagnostics: CTA 0 of conv5x5_tc_kernel stamps clock64 per phase
 int64_t conv5x5_packed_bytes(int Cin, int Cout);
 int pack_conv_weights(const float* w, void* wp, int Cin, int Cout, cudaStream_t st);
 int conv5x5_fwd_tc(const float* x, const void* wp, const float* bias, float* y, int B, int H, int W, int Cin,

@@ -92,10 +92,28 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes
   d |= (uint64_t)1 << 46;
   return d;
 }
+// The same descriptor split in two 32-bit words so that an MMA issue loop only ADDS to the low word:
+//   lo = start address (16-byte units, bits 0-13) | LBO (bits 16-29);   hi = SBO | version.
+// The single issuing thread is the pacing resource of a tcgen05 kernel with small tiles (one
+// M=128,N=64,K=16 MMA takes 48 cycles, measured), so per-MMA integer work must stay at a few adds.
+__device__ __forceinline__ uint32_t desc_lo(uint32_t saddr, uint32_t lbo_bytes) {
+  return ((saddr >> 4) & 0x3FFFu) | (((lbo_bytes >> 4) & 0x3FFFu) << 16);
+}
+__device__ __forceinline__ uint32_t desc_hi(uint32_t sbo_bytes) { return ((sbo_bytes >> 4) & 0x3FFFu) | (1u << 14); }
+__device__ __forceinline__ uint64_t desc_join(uint32_t lo, uint32_t hi) { return ((uint64_t)hi << 32) | lo; }
+
 // instruction descriptor for kind::f16: bf16 x bf16 -> f32, M in {64,128}, N % 8 == 0 (16 for M=128)
 __host__ __device__ constexpr uint32_t make_idesc(int M, int N, bool a_mn_major, bool b_mn_major) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((a_mn_major ? 1u : 0u) << 15) | ((b_mn_major ? 1u : 0u) << 16) |
          ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+// one lane of a fully converged warp (the tcgen05 issue pattern: the WHOLE warp walks the loop with
+// warp-uniform values, only the instruction itself is predicated on the elected lane -- a loop
+// entered by a single lane makes the compiler wrap every UTCHMMA in an elect/retry loop)
+__device__ __forceinline__ bool elect_one() {
+  uint32_t p;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(p));
+  return p != 0;
 }
 // D[tmem] (+)= A[smem] * B[smem]; issued by ONE thread
 __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,

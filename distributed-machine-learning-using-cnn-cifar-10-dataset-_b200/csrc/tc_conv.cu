@@ -82,21 +82,23 @@ struct ConvArgs {
   float* y;            // [B,H,W,NC]
   int relu;
   ConvGeom g;
+  long long* timeline;  // optional device buffer [8]: clock64 stamps of CTA 0's phases (diagnostics), else null
 };
 
 // ---------------------------------------------------------------------------------------------------
-// forward / input-gradient convolution.  grid = (ceil(B/ipc), NC/64), 192 threads: warps 0-3 stage
-// the strip and run the epilogue, warp 4 issues MMAs, warp 5 streams the packed filter taps with bulk
-// (TMA) copies through a 6-stage ring.
+// forward / input-gradient convolution.  grid = (ceil(B/ipc), NC/64), 288 threads: warps 0-3 stage
+// the strip and run the epilogue, warps 4-7 issue MMAs (one accumulator tile each), warp 8 streams the
+// packed filter taps with bulk (TMA) copies through a 6-stage ring.
 // DGRAD = false: y = conv(x, w)            B operand (kc,nc) = w[tap][kc][nc]     (MN-major)
 // DGRAD = true : y = conv(x, rot180(w)^T)  B operand (kc,nc) = w[24-tap][nc][kc]  (K-major)
 // ---------------------------------------------------------------------------------------------------
-template <bool DGRAD>
-__global__ void __launch_bounds__(192, 1) conv5x5_tc_kernel(ConvArgs a) {
+template <bool DGRAD, int KSTEPS>
+__global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
   constexpr int BN = 64;
+  constexpr int NISS = 4;                 // MMA-issuing warps (warps 4..7); warp 8 streams the filter
   const ConvGeom& g = a.g;
   extern __shared__ __align__(128) uint8_t smem[];
-  const int kchunks = g.KC >> 3;
+  const int kchunks = KSTEPS * 2;         // KC = 16 * KSTEPS
   const int strip_bytes = kchunks * g.ch_stride;
   // weight stage: MN-major [BN/8 groups][KC k][16B] (SBO = KC*16+16)  |  K-major [KC/8 chunks][BN rows][16B]
   const int w_mn_sbo = g.KC * 16 + 16, w_k_lbo = BN * 16 + 16;
@@ -116,9 +118,9 @@ __global__ void __launch_bounds__(192, 1) conv5x5_tc_kernel(ConvArgs a) {
   const int tmem_cols = g.tiles * BN <= 64 ? 64 : g.tiles * BN <= 128 ? 128 : g.tiles * BN <= 256 ? 256 : 512;
 
   if (tid == 0) {
-    for (int s = 0; s < WSTAGES; ++s) { mbar_init(smem_u32(wfull + s), 1); mbar_init(smem_u32(wempty + s), 1); }
+    for (int s = 0; s < WSTAGES; ++s) { mbar_init(smem_u32(wfull + s), 1); mbar_init(smem_u32(wempty + s), NISS); }
     mbar_init(smem_u32(strip_full), LOADERS);
-    mbar_init(smem_u32(accum), 1);
+    mbar_init(smem_u32(accum), NISS);
     fence_mbar_init();
   }
   if (warp == 4) tmem_alloc(smem_u32(tmem_slot), tmem_cols);
@@ -129,14 +131,18 @@ __global__ void __launch_bounds__(192, 1) conv5x5_tc_kernel(ConvArgs a) {
 
   if (warp < 4) {
     // ---- input strip --------------------------------------------------------------------------
+    if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) a.timeline[0] = clock64();
     zero_smem(strip, strip_bytes, tid);
     loaders_sync();
+    if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) a.timeline[1] = clock64();
     fill_strip(strip, a.x, g, n_img0, g.KC, g.ch_stride, tid);
     fence_proxy_async();
     mbar_arrive(smem_u32(strip_full));
+    if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) a.timeline[2] = clock64();
     // ---- epilogue: TMEM -> registers -> (+bias, relu) -> dense NHWC fp32 ---------------------------
     mbar_wait(smem_u32(accum), 0);
     tc_fence_after();
+    if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) a.timeline[5] = clock64();
     for (int t = 0; t < g.tiles; ++t) {
       const int p = t * 128 + warp * 32 + lane;
       const int r = p / g.P, c = p - r * g.P;
@@ -165,40 +171,58 @@ __global__ void __launch_bounds__(192, 1) conv5x5_tc_kernel(ConvArgs a) {
         }
       }
     }
+    if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) a.timeline[6] = clock64();
     tc_fence_before();
-  } else if (warp == 4) {
+  } else if (warp < 4 + NISS) {
+    // ---- MMA issue.  One M=128,N=64,K=16 MMA takes 48 cycles but a single thread needs ~65-130 cycles
+    // of scalar work to issue one (measured), so NISS warps issue in parallel, each feeding its own
+    // accumulator tiles; the k-steps of a tap are a compile-time unrolled group.
     if (lane == 0) {
+      const int w = warp - 4;
       const uint32_t idesc = make_idesc(128, BN, false, !DGRAD);
+      const uint32_t a_hi = desc_hi(128), b_hi = DGRAD ? desc_hi(128) : desc_hi(w_mn_sbo);
+      const uint32_t a_lo0 = desc_lo(smem_u32(strip) + g.lead * 16, g.ch_stride);
+      const uint32_t b_lo0 = DGRAD ? desc_lo(smem_u32(wring), w_k_lbo) : desc_lo(smem_u32(wring), 128);
+      const uint32_t a_kstep = 2 * (g.ch_stride >> 4), b_kstep = DGRAD ? 2 * (w_k_lbo >> 4) : 16;
       mbar_wait(smem_u32(strip_full), 0);
-      for (int tap = 0; tap < 25; ++tap) {
-        const int s = tap % WSTAGES;
-        const uint32_t ph = (tap / WSTAGES) & 1;
+      if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && w == 0) a.timeline[3] = clock64();
+      uint32_t acc = 0;
+      // Every CTA streams the same 25 filter taps out of L2; each walks them in its own rotation so
+      // that the CTAs do not all pull the same lines at once (the sum over taps is order-independent).
+      const int tap0 = (int)((blockIdx.x * 7u + blockIdx.y * 3u) % 25u);
+      int di = tap0 / 5, dj = tap0 - di * 5;
+      for (int i = 0; i < 25; ++i) {
+        const int s = i % WSTAGES;
+        const uint32_t ph = (i / WSTAGES) & 1;
         mbar_wait(smem_u32(wfull + s), ph);
         tc_fence_after();
-        const int di = tap / 5, dj = tap - di * 5;
-        const int slot0 = g.lead + (di - 2) * g.P + (dj - 2);
-        const uint32_t sa = smem_u32(strip) + slot0 * 16;
-        const uint32_t sb = smem_u32(wring + s * wstage);
-        for (int t = 0; t < g.tiles; ++t) {
-          for (int ks = 0; ks < (g.KC >> 4); ++ks) {
-            uint64_t da = make_desc(sa + t * 128 * 16 + ks * 2 * g.ch_stride, g.ch_stride, 128);
-            uint64_t db = DGRAD ? make_desc(sb + ks * 2 * w_k_lbo, w_k_lbo, 128)
-                                : make_desc(sb + ks * 256, 128, w_mn_sbo);
-            umma_bf16(tmem + t * BN, da, db, idesc, (tap | ks) ? 1u : 0u);
+        const uint32_t a_tap = a_lo0 + (uint32_t)((di - 2) * g.P + (dj - 2));      // a tap is a slot offset
+        const uint32_t b_tap = b_lo0 + (uint32_t)s * (wstage >> 4);
+        for (int t = w; t < g.tiles; t += NISS) {
+          uint32_t a_lo = a_tap + t * 128, b_lo = b_tap;
+          const uint32_t d = tmem + t * BN;
+#pragma unroll
+          for (int ks = 0; ks < KSTEPS; ++ks) {
+            umma_bf16(d, desc_join(a_lo, a_hi), desc_join(b_lo, b_hi), idesc, acc | (uint32_t)ks);
+            a_lo += a_kstep; b_lo += b_kstep;
           }
         }
-        umma_commit(smem_u32(wempty + s));
+        acc = 1;
+        umma_commit(smem_u32(wempty + s));        // arrives when this warp's MMAs on the stage are done
+        if (++dj == 5) { dj = 0; if (++di == 5) di = 0; }
       }
       umma_commit(smem_u32(accum));
+      if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && w == 0) a.timeline[4] = clock64();
     }
     __syncwarp();
   } else {
     // ---- filter taps: one thread, bulk copies global -> shared, completion counted in bytes ----------
     if (lane == 0) {
       const int img = (a.cout_f / 8) * (a.cin_f * 16 + 16);             // bytes of one packed tap
-      for (int tap = 0; tap < 25; ++tap) {
-        const int s = tap % WSTAGES;
-        const uint32_t ph = (tap / WSTAGES) & 1;
+      int tap = (int)((blockIdx.x * 7u + blockIdx.y * 3u) % 25u);      // same rotation as the MMA warp
+      for (int i = 0; i < 25; ++i, tap = (tap == 24 ? 0 : tap + 1)) {
+        const int s = i % WSTAGES;
+        const uint32_t ph = (i / WSTAGES) & 1;
         mbar_wait(smem_u32(wempty + s), ph ^ 1);
         const uint32_t ws = smem_u32(wring + s * wstage);
         const uint32_t bar = smem_u32(wfull + s);
@@ -249,6 +273,8 @@ int pick_ipc(int B, int H, int W, int KC) {
   return best;
 }
 
+long long* g_conv_timeline = nullptr;
+
 template <bool DGRAD>
 int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, int B, int H, int W, int KC, int NC,
                 int relu, cudaStream_t st) {
@@ -264,15 +290,18 @@ int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, 
   const int wstage = ((DGRAD ? kchunks * (64 * 16 + 16) : 8 * (KC * 16 + 16)) + 127) & ~127;
   const int smem = ((kchunks * g.ch_stride + 127) & ~127) + WSTAGES * wstage + 256;
   B200_REQUIRE(smem <= 227 * 1024, "conv5x5_tc: %d bytes of shared memory needed", smem);
-  auto kern = conv5x5_tc_kernel<DGRAD>;
-  static int attr = 0;
-  if (attr < smem) {
-    B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    attr = 227 * 1024;
+  void (*kern)(ConvArgs) = nullptr;
+  switch (KC / 16) {
+    case 2: kern = conv5x5_tc_kernel<DGRAD, 2>; break;
+    case 4: kern = conv5x5_tc_kernel<DGRAD, 4>; break;
+    case 8: kern = conv5x5_tc_kernel<DGRAD, 8>; break;
+    case 16: kern = conv5x5_tc_kernel<DGRAD, 16>; break;
+    default: B200_REQUIRE(false, "conv5x5_tc: contraction channels must be 32, 64, 128 or 256 (got %d)", KC);
   }
-  ConvArgs a{x, wp, DGRAD ? NC : KC, DGRAD ? KC : NC, bias, y, relu, g};
+  B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  ConvArgs a{x, wp, DGRAD ? NC : KC, DGRAD ? KC : NC, bias, y, relu, g, g_conv_timeline};
   dim3 grid(cdiv(B, ipc), NC / 64);
-  kern<<<grid, 192, smem, st>>>(a);
+  kern<<<grid, 288, smem, st>>>(a);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
@@ -292,7 +321,7 @@ struct WgradArgs {
   int nbuf;             // 2 = double-buffered strips, 1 when two pairs do not fit in shared memory
 };
 
-__global__ void __launch_bounds__(160, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
+__global__ void __launch_bounds__(288, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
   constexpr int C = 64;
   const ConvGeom& g = a.g;
   extern __shared__ __align__(128) uint8_t smem[];
@@ -311,8 +340,8 @@ __global__ void __launch_bounds__(160, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
   const int ksteps = (g.rows_per_img * g.P + 15) / 16;
 
   if (tid == 0) {
-    for (int s = 0; s < 2; ++s) { mbar_init(smem_u32(full + s), LOADERS); mbar_init(smem_u32(empty + s), 1); }
-    mbar_init(smem_u32(accum), 1);
+    for (int s = 0; s < 2; ++s) { mbar_init(smem_u32(full + s), LOADERS); mbar_init(smem_u32(empty + s), 5); }
+    mbar_init(smem_u32(accum), 5);
     fence_mbar_init();
   }
   if (warp == 4) tmem_alloc(smem_u32(tmem_slot), 512);
@@ -359,23 +388,29 @@ __global__ void __launch_bounds__(160, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
     }
     tc_fence_before();
   } else {
+    // warps 4..8: one issuing thread per filter tap dj of this CTA's filter row (own accumulator each)
     if (lane == 0) {
+      const int dj = warp - 4;
       const uint32_t idesc = make_idesc(64, C, true, true);
+      const uint32_t hi = desc_hi(g.ch_stride);                 // MN-major: SBO = channel-chunk stride, LBO = 128
+      const uint32_t d = tmem + dj * C;
+      uint32_t acc = 0;
       for (int it = 0; it < nimg; ++it) {
         const int b = it % a.nbuf;
         const uint32_t ph = (it / a.nbuf) & 1;
         mbar_wait(smem_u32(full + b), ph);
         tc_fence_after();
         const uint32_t xs = smem_u32(smem + (2 * b) * strip_bytes);
-        const uint32_t ds = xs + strip_bytes;
-        for (int dj = 0; dj < 5; ++dj) {
-          const int slot0 = g.lead + (di - 2) * g.P + (dj - 2);
-          for (int ks = 0; ks < ksteps; ++ks) {
-            uint64_t da = make_desc(xs + (slot0 + ks * 16) * 16, 128, g.ch_stride);
-            uint64_t db = make_desc(ds + (g.lead + ks * 16) * 16, 128, g.ch_stride);
-            umma_bf16(tmem + dj * C, da, db, idesc, (it | ks) ? 1u : 0u);
-          }
+        uint32_t x_lo = desc_lo(xs + (g.lead + (di - 2) * g.P - 2 + dj) * 16, 128);
+        uint32_t d_lo = desc_lo(xs + strip_bytes + g.lead * 16, 128);
+        int ks = 0;
+        for (; ks + 2 <= ksteps; ks += 2) {                      // 16 pixel slots = 16 x 16 bytes per k-step
+          umma_bf16(d, desc_join(x_lo, hi), desc_join(d_lo, hi), idesc, acc | (uint32_t)ks);
+          umma_bf16(d, desc_join(x_lo + 16, hi), desc_join(d_lo + 16, hi), idesc, 1u);
+          x_lo += 32; d_lo += 32;
         }
+        if (ks < ksteps) umma_bf16(d, desc_join(x_lo, hi), desc_join(d_lo, hi), idesc, acc | (uint32_t)ks);
+        acc = 1;
         umma_commit(smem_u32(empty + b));
       }
       umma_commit(smem_u32(accum));   // with nimg == 0 nothing was issued: the commit arrives at once
@@ -403,6 +438,7 @@ __global__ void reduce_partials_tc(const float* __restrict__ part, float* __rest
 int wgrad_splits_tc(int B) { return std::max(1, std::min(B, (kNumSMs + 4) / 5)); }
 }  // namespace
 
+void conv5x5_set_timeline(long long* dev_buf) { g_conv_timeline = dev_buf; }
 int64_t conv5x5_packed_bytes(int Cin, int Cout) { return 25ll * (Cout / 8) * (Cin * 16 + 16); }
 int pack_conv_weights(const float* w, void* wp, int Cin, int Cout, cudaStream_t st) {
   B200_REQUIRE(Cin % 8 == 0 && Cout % 8 == 0 && Cin > 0 && Cout > 0, "pack_conv_weights: channels must be multiples of 8");
@@ -441,7 +477,7 @@ int conv5x5_wgrad_tc(const float* x, const float* dy, float* dw, float* scratch,
   int per = cdiv(B, S);
   S = cdiv(B, per);
   WgradArgs a{x, dy, scratch, g, per, nbuf};
-  conv5x5_wgrad_tc_kernel<<<dim3(5, S), 160, smem, st>>>(a);
+  conv5x5_wgrad_tc_kernel<<<dim3(5, S), 288, smem, st>>>(a);
   B200_LAUNCH_CHECK();
   const int n = 25 * 64 * 64;
   reduce_partials_tc<<<cdiv(n / 4, 256), 256, 0, st>>>(scratch, dw, n, S);

@@ -179,17 +179,20 @@ __global__ void __launch_bounds__(288, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
       const uint32_t idesc = make_idesc(128, 64, false, false);
       mbar_wait(smem_u32(ready), 0);
       tc_fence_after();
-      const uint32_t sx = smem_u32(strip), sw = smem_u32(wB);
+      const uint32_t a_hi = desc_hi(128), b_hi = desc_hi(128);
+      const uint32_t a_base = ((smem_u32(strip) >> 4) + g.lead) & 0x3FFFu;      // address field of slot `lead`
+      uint32_t b_lo = desc_lo(smem_u32(wB), kWLbo);
+#pragma unroll
       for (int ks = 0; ks < 13; ++ks) {
-        const int t0 = 2 * ks, t1 = 2 * ks + 1;
+        const int t0 = 2 * ks, t1 = 2 * ks + 1;                                 // compile-time after unrolling
         const int off0 = (t0 / 5 - 2) * g.P + (t0 % 5 - 2);
         const int off1 = (t1 < 25) ? (t1 / 5 - 2) * g.P + (t1 % 5 - 2) : off0 + 1;   // dummy tap: zero weights
-        const uint32_t lbo = (uint32_t)(off1 - off0) * 16;
+        uint32_t a_lo = (a_base + (uint32_t)off0) | ((uint32_t)(off1 - off0) << 16);  // LBO = tap distance in slots
         for (int t = 0; t < g.tiles; ++t) {
-          uint64_t da = make_desc(sx + (g.lead + off0 + t * 128) * 16, lbo, 128);
-          uint64_t db = make_desc(sw + ks * 2 * kWLbo, kWLbo, 128);
-          umma_bf16(tmem + t * 64, da, db, idesc, ks ? 1u : 0u);
+          umma_bf16(tmem + t * 64, desc_join(a_lo, a_hi), desc_join(b_lo, b_hi), idesc, ks ? 1u : 0u);
+          a_lo += 128;
         }
+        b_lo += 2 * (kWLbo >> 4);
       }
       umma_commit(smem_u32(accum));
     }
@@ -361,18 +364,23 @@ __global__ void __launch_bounds__(288, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
   } else {
     if (lane == 0) {
       const uint32_t idesc = make_idesc(64, 40, true, true);
-      const uint32_t sx = smem_u32(xs), sd = smem_u32(ds);
+      const uint32_t d_hi = desc_hi(ch_stride), x_hi = desc_hi(16);     // x: N-group stride = one pixel slot
+      const uint32_t d_lo0 = desc_lo(smem_u32(ds) + g.lead * 16, 128);
+      const uint32_t x_lo0 = desc_lo(smem_u32(xs) + (g.lead - 2 * g.P - 2) * 16, 128);
+      uint32_t acc = 0;
       for (int it = 0; it < nimg; ++it) {
         mbar_wait(smem_u32(full), it & 1);
         tc_fence_after();
         for (int di = 0; di < 5; ++di) {
-          const int slot0 = g.lead + (di - 2) * g.P - 2;
+          uint32_t d_lo = d_lo0, x_lo = x_lo0 + di * g.P;
+          const uint32_t d = tmem + di * 64;
+#pragma unroll 2
           for (int ks = 0; ks < ksteps; ++ks) {
-            uint64_t da = make_desc(sd + (g.lead + ks * 16) * 16, 128, ch_stride);
-            uint64_t db = make_desc(sx + (slot0 + ks * 16) * 16, 128, 16);     // N-group stride = one pixel slot
-            umma_bf16(tmem + di * 64, da, db, idesc, (it | ks) ? 1u : 0u);
+            umma_bf16(d, desc_join(d_lo, d_hi), desc_join(x_lo, x_hi), idesc, acc | (uint32_t)ks);
+            d_lo += 16; x_lo += 16;
           }
         }
+        acc = 1;
         umma_commit(smem_u32(empty));
       }
       umma_commit(smem_u32(accum));

@@ -175,20 +175,20 @@ __global__ void __launch_bounds__(160, 1) tc_gemm_kernel(GemmArgs g) {
     // ------------------------------ MMA issue (one thread) -----------------------------------------
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc(BM, BN, A_MN, B_MN);
+      const uint32_t a_hi = A_MN ? desc_hi(S::A_MN_SBO) : desc_hi(128), b_hi = B_MN ? desc_hi(S::B_MN_SBO) : desc_hi(128);
+      const uint32_t a_lo0 = A_MN ? desc_lo(smem_u32(smem), 128) : desc_lo(smem_u32(smem), S::A_K_LBO);
+      const uint32_t b_lo0 = B_MN ? desc_lo(smem_u32(smem) + S::A_BYTES, 128) : desc_lo(smem_u32(smem) + S::A_BYTES, S::B_K_LBO);
       for (int kb = 0; kb < nkb; ++kb) {
         const int s = kb % STAGES;
         const uint32_t ph = (kb / STAGES) & 1;
         mbar_wait(smem_u32(full + s), ph);
         tc_fence_after();
-        const uint32_t sa = smem_u32(smem + s * S::STAGE);
-        const uint32_t sb = sa + S::A_BYTES;
+        uint32_t a_lo = a_lo0 + (uint32_t)s * (S::STAGE >> 4), b_lo = b_lo0 + (uint32_t)s * (S::STAGE >> 4);
 #pragma unroll
         for (int ks = 0; ks < BK / 16; ++ks) {
-          uint64_t da = A_MN ? make_desc(sa + ks * 256, 128, S::A_MN_SBO)
-                             : make_desc(sa + ks * 2 * S::A_K_LBO, S::A_K_LBO, 128);
-          uint64_t db = B_MN ? make_desc(sb + ks * 256, 128, S::B_MN_SBO)
-                             : make_desc(sb + ks * 2 * S::B_K_LBO, S::B_K_LBO, 128);
-          umma_bf16(tmem, da, db, idesc, (kb | ks) ? 1u : 0u);
+          umma_bf16(tmem, desc_join(a_lo, a_hi), desc_join(b_lo, b_hi), idesc, (kb | ks) ? 1u : 0u);
+          a_lo += A_MN ? 16 : 2 * (S::A_K_LBO >> 4);
+          b_lo += B_MN ? 16 : 2 * (S::B_K_LBO >> 4);
         }
         umma_commit(smem_u32(empty + s));
       }
