@@ -351,7 +351,8 @@ __global__ void maxpool_bwd_kernel(const float* __restrict__ dy, const uint8_t* 
           int ow = q >> 1;
           if (ow >= OW) continue;
           int64_t o = (((int64_t)b * OH + oh) * OW + ow) * C + c;
-          if (arg[o] == kh * 3 + kw) s += dy[o];
+          const float d = __ldg(dy + o);                 // unconditional: the (<= 4) loads stay independent
+          s += (__ldg(arg + o) == kh * 3 + kw) ? d : 0.f;
         }
       }
     }

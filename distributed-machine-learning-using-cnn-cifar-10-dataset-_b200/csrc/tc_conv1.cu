@@ -65,7 +65,7 @@ struct Conv1FwdArgs {
 constexpr int kWLbo = 64 * 16 + 16;      // B operand: [26 k-chunks][64 cout][16 B], chunk stride padded
 constexpr int kConvRow = 68;             // floats per conv-output row in smem (64 + 4: conflict-free STS.128)
 
-__global__ void __launch_bounds__(288, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) {
+__global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) {
   const C1Geom& g = a.g;
   extern __shared__ __align__(128) uint8_t smem[];
   const int strip_bytes = (g.npix * 16 + 127) & ~127;
@@ -83,7 +83,7 @@ __global__ void __launch_bounds__(288, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
 
   if (tid == 0) {
     mbar_init(smem_u32(ready), WORKERS);
-    mbar_init(smem_u32(accum), 1);
+    mbar_init(smem_u32(accum), 3);
     fence_mbar_init();
   }
   if (warp == 8) tmem_alloc(smem_u32(tmem_slot), tmem_cols);
@@ -175,24 +175,26 @@ __global__ void __launch_bounds__(288, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
       *reinterpret_cast<uchar4*>(a.arg + o) = make_uchar4(bi[0], bi[1], bi[2], bi[3]);
     }
   } else {
+    // warps 8..10: three issuing threads, tiles t = w, w+3, ... each (13 MMAs per tile)
     if (lane == 0) {
+      const int w = warp - 8;
       const uint32_t idesc = make_idesc(128, 64, false, false);
       mbar_wait(smem_u32(ready), 0);
       tc_fence_after();
       const uint32_t a_hi = desc_hi(128), b_hi = desc_hi(128);
       const uint32_t a_base = ((smem_u32(strip) >> 4) + g.lead) & 0x3FFFu;      // address field of slot `lead`
-      uint32_t b_lo = desc_lo(smem_u32(wB), kWLbo);
+      for (int t = w; t < g.tiles; t += 3) {
+        uint32_t b_lo = desc_lo(smem_u32(wB), kWLbo);
+        const uint32_t d = tmem + t * 64;
 #pragma unroll
-      for (int ks = 0; ks < 13; ++ks) {
-        const int t0 = 2 * ks, t1 = 2 * ks + 1;                                 // compile-time after unrolling
-        const int off0 = (t0 / 5 - 2) * g.P + (t0 % 5 - 2);
-        const int off1 = (t1 < 25) ? (t1 / 5 - 2) * g.P + (t1 % 5 - 2) : off0 + 1;   // dummy tap: zero weights
-        uint32_t a_lo = (a_base + (uint32_t)off0) | ((uint32_t)(off1 - off0) << 16);  // LBO = tap distance in slots
-        for (int t = 0; t < g.tiles; ++t) {
-          umma_bf16(tmem + t * 64, desc_join(a_lo, a_hi), desc_join(b_lo, b_hi), idesc, ks ? 1u : 0u);
-          a_lo += 128;
+        for (int ks = 0; ks < 13; ++ks) {
+          const int t0 = 2 * ks, t1 = 2 * ks + 1;                               // compile-time after unrolling
+          const int off0 = (t0 / 5 - 2) * g.P + (t0 % 5 - 2);
+          const int off1 = (t1 < 25) ? (t1 / 5 - 2) * g.P + (t1 % 5 - 2) : off0 + 1;   // dummy tap: zero weights
+          const uint32_t a_lo = (a_base + (uint32_t)(off0 + t * 128)) | ((uint32_t)(off1 - off0) << 16);   // LBO = tap distance
+          umma_bf16(d, desc_join(a_lo, a_hi), desc_join(b_lo, b_hi), idesc, ks ? 1u : 0u);
+          b_lo += 2 * (kWLbo >> 4);
         }
-        b_lo += 2 * (kWLbo >> 4);
       }
       umma_commit(smem_u32(accum));
     }
@@ -225,7 +227,7 @@ int conv1_pool_fwd_tc(const uint8_t* img, const float* w, const float* bias, flo
     attr = true;
   }
   Conv1FwdArgs a{img, w, bias, pool, arg, conv_dbg, g};
-  conv1_pool_fwd_kernel<<<B, 288, smem, st>>>(a);
+  conv1_pool_fwd_kernel<<<B, 352, smem, st>>>(a);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
@@ -247,7 +249,7 @@ struct Conv1WgradArgs {
   C1Geom g;
 };
 
-__global__ void __launch_bounds__(288, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
+__global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
   const C1Geom& g = a.g;
   extern __shared__ __align__(128) uint8_t smem[];
   const int xs_bytes = (g.npix * 16 + 127) & ~127;
@@ -269,8 +271,8 @@ __global__ void __launch_bounds__(288, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
 
   if (tid == 0) {
     mbar_init(smem_u32(full), WORKERS);
-    mbar_init(smem_u32(empty), 1);
-    mbar_init(smem_u32(accum), 1);
+    mbar_init(smem_u32(empty), 5);
+    mbar_init(smem_u32(accum), 5);
     fence_mbar_init();
   }
   if (warp == 8) tmem_alloc(smem_u32(tmem_slot), 512);
@@ -291,6 +293,7 @@ __global__ void __launch_bounds__(288, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
       const float4* dp4 = reinterpret_cast<const float4*>(a.dpool + (size_t)n * ncell * 64);
       const float4* pl4 = reinterpret_cast<const float4*>(a.pool + (size_t)n * ncell * 64);
       const uint32_t* ar4 = reinterpret_cast<const uint32_t*>(a.arg + (size_t)n * ncell * 64);
+#pragma unroll 3
       for (int q = tid; q < ncell * 16; q += WORKERS) {
         float4 d = __ldg(dp4 + q), p = __ldg(pl4 + q);
         d.x = p.x > 0.f ? d.x : 0.f; d.y = p.y > 0.f ? d.y : 0.f;
@@ -362,24 +365,26 @@ __global__ void __launch_bounds__(288, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
     }
     tc_fence_before();
   } else {
+    // warps 8..12: one issuing thread per filter row di (own accumulator each)
     if (lane == 0) {
+      const int di = warp - 8;
       const uint32_t idesc = make_idesc(64, 40, true, true);
       const uint32_t d_hi = desc_hi(ch_stride), x_hi = desc_hi(16);     // x: N-group stride = one pixel slot
       const uint32_t d_lo0 = desc_lo(smem_u32(ds) + g.lead * 16, 128);
-      const uint32_t x_lo0 = desc_lo(smem_u32(xs) + (g.lead - 2 * g.P - 2) * 16, 128);
+      const uint32_t x_lo0 = desc_lo(smem_u32(xs) + (g.lead + (di - 2) * g.P - 2) * 16, 128);
+      const uint32_t d = tmem + di * 64;
       uint32_t acc = 0;
       for (int it = 0; it < nimg; ++it) {
         mbar_wait(smem_u32(full), it & 1);
         tc_fence_after();
-        for (int di = 0; di < 5; ++di) {
-          uint32_t d_lo = d_lo0, x_lo = x_lo0 + di * g.P;
-          const uint32_t d = tmem + di * 64;
-#pragma unroll 2
-          for (int ks = 0; ks < ksteps; ++ks) {
-            umma_bf16(d, desc_join(d_lo, d_hi), desc_join(x_lo, x_hi), idesc, acc | (uint32_t)ks);
-            d_lo += 16; x_lo += 16;
-          }
+        uint32_t d_lo = d_lo0, x_lo = x_lo0;
+        int ks = 0;
+        for (; ks + 2 <= ksteps; ks += 2) {
+          umma_bf16(d, desc_join(d_lo, d_hi), desc_join(x_lo, x_hi), idesc, acc | (uint32_t)ks);
+          umma_bf16(d, desc_join(d_lo + 16, d_hi), desc_join(x_lo + 16, x_hi), idesc, 1u);
+          d_lo += 32; x_lo += 32;
         }
+        if (ks < ksteps) umma_bf16(d, desc_join(d_lo, d_hi), desc_join(x_lo, x_hi), idesc, acc | (uint32_t)ks);
         acc = 1;
         umma_commit(smem_u32(empty));
       }
@@ -407,7 +412,16 @@ __global__ void conv1_wgrad_finish(const float* __restrict__ part, float* __rest
     src = (2 * 64 + (i - 75 * 64)) * 40 + 2 * 8 + 3;
   }
   float s = 0.f;
-  for (int z = 0; z < S; ++z) s += __ldg(part + (size_t)z * 5 * 64 * 40 + src);
+  const float* p = part + src;
+  int z = 0;
+  for (; z + 8 <= S; z += 8) {          // 8 independent loads in flight; summation order is fixed
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = __ldg(p + (size_t)(z + j) * 5 * 64 * 40);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += v[j];
+  }
+  for (; z < S; ++z) s += __ldg(p + (size_t)z * 5 * 64 * 40);
   if (i < 75 * 64) dw[i] = s;
   else if (db) db[i - 75 * 64] = s;
 }
@@ -434,9 +448,9 @@ int conv1_wgrad_tc(const uint8_t* img, const float* dpool, const float* pool, co
   }
   const int S = conv1_wgrad_ctas(B);
   Conv1WgradArgs a{img, dpool, pool, arg, scratch, g};
-  conv1_wgrad_kernel<<<S, 288, smem, st>>>(a);
+  conv1_wgrad_kernel<<<S, 416, smem, st>>>(a);
   B200_LAUNCH_CHECK();
-  conv1_wgrad_finish<<<cdiv(75 * 64 + 64, 256), 256, 0, st>>>(scratch, dw, db, S);
+  conv1_wgrad_finish<<<cdiv(75 * 64 + 64, 64), 64, 0, st>>>(scratch, dw, db, S);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
