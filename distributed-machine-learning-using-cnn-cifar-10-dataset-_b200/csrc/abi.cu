@@ -387,7 +387,7 @@ int b200_launches_per_step(b200_handle h, int32_t* n) {
   if (h->cfg.mode == B200_MODE_BF16) {
     // conv1 (3 or 1), conv2, pool2, FC1 split-K, tail x2 | FC1 bwd x2, pool2 bwd, conv2 wgrad x2, dgrad, conv1 wgrad (2 or 1+4), sgd
     const bool f1 = conv1_tc_supported(h->cfg.crop_h, h->cfg.crop_w, h->cfg.c_in, h->cfg.c1);
-    *n = (f1 ? 1 : 3) + 2 + 1 + 1 + 2 + 2 + 1 + 2 + 1 + (f1 ? 2 : 5) + 1;
+    *n = (f1 ? 1 : 3) + 2 + 1 + 1 + 3 + 2 + 1 + 2 + 1 + (f1 ? 2 : 5) + 1;
   }
   return B200_OK;
 }
@@ -473,6 +473,7 @@ int b200_conv1_wgrad_bf16(const uint8_t* images, const float* dpool, const float
 }
 int b200_debug_conv_timeline(int64_t* device_buf8) {
   conv5x5_set_timeline(reinterpret_cast<long long*>(device_buf8));
+  fc_tail_set_timeline(device_buf8 ? reinterpret_cast<long long*>(device_buf8) + 16 : nullptr);
   return B200_OK;
 }
 int b200_conv5x5_packed_bytes(int32_t c_in, int32_t c_out, int64_t* nbytes) {

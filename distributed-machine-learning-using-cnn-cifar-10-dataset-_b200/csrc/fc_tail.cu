@@ -1,4 +1,5 @@
 // The small end of the network in two launches instead of ~25:
+//   (+ one tiny kernel that rounds W2 to a bf16 image the rows kernel bulk-copies into shared memory)
 //   rows kernel  (row-parallel):  full1 = relu(sum of FC1 split-K partials + b1)   [optional]
 //                                 full2 = relu(full1 W2 + b2)   (W2 rounded to bf16) cifar10cnn.py:139
 //                                 logits = relu(full2 W3 + b3)                      :145
@@ -17,6 +18,7 @@
 #include <cuda_bf16.h>
 
 #include "launch.h"
+#include "tc_common.cuh"
 
 namespace b200 {
 namespace {
@@ -44,11 +46,13 @@ struct TailArgs {
   const float* b1;
   float* full1;                    // [B,F1]  in (n_part == 0) or out
   const float *w2, *b2, *w3, *b3;
+  const __nv_bfloat16* w2b;        // W2 as the bf16 [F1][F2+2] image (w2_to_bf16_kernel)
   const int32_t* labels;
   float *full2, *logits, *dlogits, *dfull2, *dfull1;
   int32_t* pred;
   float* part;                     // [n_ctas][PV] per-CTA partial sums: db1 | db2 | db3(16) | dW3 | loss, ok, bad
   float* zero_ptr; int zero_n;     // small buffer CTA 0 clears for a later kernel's atomics (may be null)
+  long long* timeline;             // diagnostics: clock64 stamps of CTA 0's phases, or null
 };
 __host__ __device__ inline int part_len(int F1, int F2, int NC) { return F1 + F2 + 16 + F2 * NC + 4; }
 
@@ -58,47 +62,51 @@ __device__ __forceinline__ void stage_tile(float* dst, const float* src, int nfl
   cp_async_commit();
 }
 
+#define TL(i) do { if (a.timeline && blockIdx.x == 0 && threadIdx.x == 0) a.timeline[i] = clock64(); } while (0)
+
+// W2 fp32 [F1][F2] -> bf16 image [F1][F2+2] (row stride odd in 32-bit words: conflict-free when every
+// thread walks its own row), fetched by the rows kernel with bulk copies
+__global__ void w2_to_bf16_kernel(const float* __restrict__ w2, __nv_bfloat16* __restrict__ out, int F1, int F2) {
+  const int WS = F2 + 2;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < F1 * WS; i += gridDim.x * blockDim.x) {
+    const int k = i / WS, n = i - k * WS;
+    out[i] = __float2bfloat16(n < F2 ? __ldg(w2 + (size_t)k * F2 + n) : 0.f);
+  }
+}
+
 template <int R>
 __global__ void __launch_bounds__(RT) fc_tail_rows_kernel(TailArgs a) {
   extern __shared__ __align__(16) float sm[];
-  float* xs = sm;                       // [R][F1]   full1 rows
-  float* d1s = xs + R * a.F1;           // [R][F1]   dfull1 rows
+  const int WS = a.F2 + 2;
+  float* xsI = sm;                      // [F1][R]   full1 rows, row index innermost (one broadcast LDS.128 per k)
+  float* d1s = xsI + R * a.F1;          // [R][F1]   dfull1 rows
   float* f2s = d1s + R * a.F1;          // [R][F2]
-  float* d2s = f2s + R * a.F2;          // [R][F2]
-  float* lgs = d2s + R * a.F2;          // [R][16] logits
+  float* d2I = f2s + R * a.F2;          // [F2][R]   dfull2, row index innermost
+  float* lgs = d2I + R * a.F2;          // [R][16] logits
   float* dls = lgs + R * kMaxCls;       // [R][16] dlogits
   float* misc = dls + R * kMaxCls;      // [4] loss, ok, bad
-  __nv_bfloat16* wb = reinterpret_cast<__nv_bfloat16*>(misc + 4);   // [F1][F2] W2, bf16, resident for both passes
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  float* w3s = misc + 4;                // [F2][NC]
+  uint64_t* bar = reinterpret_cast<uint64_t*>(w3s + ((a.F2 * a.NC + 3) & ~3));
+  __nv_bfloat16* wb = reinterpret_cast<__nv_bfloat16*>(bar + 2);      // [F1][WS] W2 in bf16, resident for both passes
+  const int tid = threadIdx.x;
   const int r0 = blockIdx.x * R;
   const int nr = min(R, a.B - r0);
 
   if (blockIdx.x == 0 && a.zero_ptr)
     for (int i = tid; i < a.zero_n; i += RT) a.zero_ptr[i] = 0.f;
-
-  // W2 -> shared memory once, rounded to bf16 (147 KB for 384x192): both products below read it from
-  // there.  12 independent 16-byte loads per thread and round keep the L2 pipe full.
-  {
-    const float4* src = reinterpret_cast<const float4*>(a.w2);
-    uint2* dst = reinterpret_cast<uint2*>(wb);
-    const int n4 = a.F1 * a.F2 / 4;
-    for (int i0 = tid; i0 < n4; i0 += RT * 12) {
-      float4 v[12];
-#pragma unroll
-      for (int j = 0; j < 12; ++j) {
-        const int i = i0 + j * RT;
-        v[j] = i < n4 ? __ldg(src + i) : make_float4(0.f, 0.f, 0.f, 0.f);
-      }
-#pragma unroll
-      for (int j = 0; j < 12; ++j) {
-        const int i = i0 + j * RT;
-        if (i < n4) {
-          __nv_bfloat162 lo = __floats2bfloat162_rn(v[j].x, v[j].y), hi = __floats2bfloat162_rn(v[j].z, v[j].w);
-          dst[i] = make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
-        }
-      }
-    }
+  TL(0);
+  // ---- W2 (bf16 image, 149 KB) -> shared memory with bulk copies; lands while full1 is assembled ------
+  if (tid == 0) {
+    tc::mbar_init(tc::smem_u32(bar), 1);
+    tc::fence_mbar_init();
+    const uint32_t total = (uint32_t)a.F1 * WS * 2;
+    tc::mbar_arrive_expect_tx(tc::smem_u32(bar), total);
+    for (uint32_t off = 0; off < total; off += 32768)
+      tc::bulk_g2s(tc::smem_u32(wb) + off, reinterpret_cast<const uint8_t*>(a.w2b) + off, min(32768u, total - off),
+                   tc::smem_u32(bar));
   }
+  for (int i = tid; i < a.F2 * a.NC; i += RT) w3s[i] = __ldg(a.w3 + i);
+  TL(1);
   // ---- full1 rows: add the split-K partials of FC1, bias, ReLU ------------------------------------
   const int f14 = a.F1 / 4;
   for (int i = tid; i < R * f14; i += RT) {
@@ -121,22 +129,26 @@ __global__ void __launch_bounds__(RT) fc_tail_rows_kernel(TailArgs a) {
         v = *dst;
       }
     }
-    reinterpret_cast<float4*>(xs)[i] = v;
+    xsI[(4 * k4 + 0) * R + r] = v.x; xsI[(4 * k4 + 1) * R + r] = v.y;
+    xsI[(4 * k4 + 2) * R + r] = v.z; xsI[(4 * k4 + 3) * R + r] = v.w;
   }
-  // ---- pass 1 over W2: full2 = relu(x W2 + b2), thread <-> column n ------------------------------------
-  float acc[R];
-#pragma unroll
-  for (int r = 0; r < R; ++r) acc[r] = 0.f;
   __syncthreads();
+  tc::mbar_wait(tc::smem_u32(bar), 0);
+  TL(2);
+  // ---- pass 1 over W2: full2 = relu(x W2 + b2), thread <-> column n ------------------------------------
   if (tid < a.F2) {
+    float acc[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) acc[r] = 0.f;
 #pragma unroll 8
     for (int k = 0; k < a.F1; ++k) {
-      const float wv = __bfloat162float(wb[k * a.F2 + tid]);
+      const float wv = __bfloat162float(wb[k * WS + tid]);
+      float xr[R];
 #pragma unroll
-      for (int r = 0; r < R; ++r) acc[r] = fmaf(xs[r * a.F1 + k], wv, acc[r]);
+      for (int q = 0; q < R / 4; ++q) *reinterpret_cast<float4*>(xr + 4 * q) = *reinterpret_cast<const float4*>(xsI + k * R + 4 * q);
+#pragma unroll
+      for (int r = 0; r < R; ++r) acc[r] = fmaf(xr[r], wv, acc[r]);
     }
-  }
-  if (tid < a.F2) {
     const float b = __ldg(a.b2 + tid);
 #pragma unroll
     for (int r = 0; r < R; ++r) {
@@ -146,15 +158,20 @@ __global__ void __launch_bounds__(RT) fc_tail_rows_kernel(TailArgs a) {
     }
   }
   __syncthreads();
-  // ---- logits = relu(full2 W3 + b3): one warp per (row, class) ------------------------------------
-  for (int q = warp; q < R * a.NC; q += RT / 32) {
-    const int r = q / a.NC, c = q - r * a.NC;
-    float s = 0.f;
-    for (int k = lane; k < a.F2; k += 32) s = fmaf(f2s[r * a.F2 + k], __ldg(a.w3 + (size_t)k * a.NC + c), s);
-    s = warp_sum(s);
-    if (lane == 0) lgs[r * kMaxCls + c] = fmaxf(s + __ldg(a.b3 + c), 0.f);
+  TL(3);
+  // ---- logits = relu(full2 W3 + b3): one thread per (row, class), W3 from shared memory ---------------
+  if (tid < R * a.NC) {
+    const int r = tid / a.NC, c = tid - r * a.NC;
+    float s0 = 0.f, s1 = 0.f;
+    for (int k = 0; k + 1 < a.F2; k += 2) {
+      s0 = fmaf(f2s[r * a.F2 + k], w3s[k * a.NC + c], s0);
+      s1 = fmaf(f2s[r * a.F2 + k + 1], w3s[(k + 1) * a.NC + c], s1);
+    }
+    if (a.F2 & 1) s0 = fmaf(f2s[r * a.F2 + a.F2 - 1], w3s[(a.F2 - 1) * a.NC + c], s0);
+    lgs[r * kMaxCls + c] = fmaxf(s0 + s1 + __ldg(a.b3 + c), 0.f);
   }
   __syncthreads();
+  TL(4);
   // ---- softmax cross-entropy per row (R <= 32 rows: one lane each in warp 0) -----------------------------
   if (tid < 32) {
     const int r = tid;
@@ -194,56 +211,60 @@ __global__ void __launch_bounds__(RT) fc_tail_rows_kernel(TailArgs a) {
     if (tid == 0) { misc[0] = lossv; misc[1] = (float)okv; misc[2] = (float)badv; }
   }
   __syncthreads();
+  TL(5);
   // ---- dfull2 = (dlogits W3^T) * [full2 > 0] -----------------------------------------------------------
   if (tid < a.F2) {
     float w[kMaxCls];
 #pragma unroll
-    for (int c = 0; c < kMaxCls; ++c) w[c] = c < a.NC ? __ldg(a.w3 + (size_t)tid * a.NC + c) : 0.f;
+    for (int c = 0; c < kMaxCls; ++c) w[c] = c < a.NC ? w3s[tid * a.NC + c] : 0.f;
 #pragma unroll
     for (int r = 0; r < R; ++r) {
       float s = 0.f;
 #pragma unroll
       for (int c = 0; c < kMaxCls; ++c) s = fmaf(c < a.NC ? dls[r * kMaxCls + c] : 0.f, w[c], s);
       s = f2s[r * a.F2 + tid] > 0.f ? s : 0.f;
-      d2s[r * a.F2 + tid] = s;
+      d2I[tid * R + r] = s;
       if (r < nr) a.dfull2[(size_t)(r0 + r) * a.F2 + tid] = s;
     }
   }
   __syncthreads();
-  // ---- pass 2 over W2: dfull1 = (dfull2 W2^T) * [full1 > 0]; warp <-> k rows of the tile, lanes over n ---
-  for (int k = warp; k < a.F1; k += RT / 32) {
-    float s[R];
+  TL(6);
+  // ---- pass 2 over W2: dfull1 = (dfull2 W2^T) * [full1 > 0]; thread <-> its own W2 row k -----------------
+  for (int k = tid; k < a.F1; k += RT) {
+    float acc[R];
 #pragma unroll
-    for (int r = 0; r < R; ++r) s[r] = 0.f;
-    const __nv_bfloat162* wrow = reinterpret_cast<const __nv_bfloat162*>(wb + k * a.F2);
-    for (int n2 = lane; n2 < a.F2 / 2; n2 += 32) {
+    for (int r = 0; r < R; ++r) acc[r] = 0.f;
+    const __nv_bfloat162* wrow = reinterpret_cast<const __nv_bfloat162*>(wb + k * WS);
+#pragma unroll 4
+    for (int n2 = 0; n2 < a.F2 / 2; ++n2) {
       const float2 wv = __bfloat1622float2(wrow[n2]);
+      float d0[R], d1[R];
 #pragma unroll
-      for (int r = 0; r < R; ++r) {
-        const float2 d = *reinterpret_cast<const float2*>(d2s + r * a.F2 + 2 * n2);
-        s[r] = fmaf(d.x, wv.x, fmaf(d.y, wv.y, s[r]));
+      for (int q = 0; q < R / 4; ++q) {
+        *reinterpret_cast<float4*>(d0 + 4 * q) = *reinterpret_cast<const float4*>(d2I + (2 * n2) * R + 4 * q);
+        *reinterpret_cast<float4*>(d1 + 4 * q) = *reinterpret_cast<const float4*>(d2I + (2 * n2 + 1) * R + 4 * q);
       }
+#pragma unroll
+      for (int r = 0; r < R; ++r) acc[r] = fmaf(d0[r], wv.x, fmaf(d1[r], wv.y, acc[r]));
     }
 #pragma unroll
-    for (int r = 0; r < R; ++r) {
-      const float v = warp_sum(s[r]);
-      if (lane == 0) d1s[r * a.F1 + k] = xs[r * a.F1 + k] > 0.f ? v : 0.f;
-    }
+    for (int r = 0; r < R; ++r) d1s[r * a.F1 + k] = xsI[k * R + r] > 0.f ? acc[r] : 0.f;
   }
   __syncthreads();
+  TL(7);
   // ---- write dfull1 rows and this CTA's partial sums over its rows ---------------------------------------
   for (int i = tid; i < nr * a.F1; i += RT) a.dfull1[(size_t)r0 * a.F1 + i] = d1s[i];
   float* part = a.part + (size_t)blockIdx.x * part_len(a.F1, a.F2, a.NC);
   for (int k = tid; k < a.F1; k += RT) {
     float s = 0.f;
 #pragma unroll
-    for (int r = 0; r < R; ++r) s += d1s[r * a.F1 + k];     // rows >= nr are zero (dls = 0 -> d2s = 0 -> d1s = 0)
+    for (int r = 0; r < R; ++r) s += d1s[r * a.F1 + k];     // rows >= nr are zero (dls = 0 -> d2 = 0 -> d1 = 0)
     part[k] = s;
   }
   if (tid < a.F2) {
     float s = 0.f;
 #pragma unroll
-    for (int r = 0; r < R; ++r) s += d2s[r * a.F2 + tid];
+    for (int r = 0; r < R; ++r) s += d2I[tid * R + r];
     part[a.F1 + tid] = s;
     float* pw3 = part + a.F1 + a.F2 + 16 + tid * a.NC;
     for (int c = 0; c < a.NC; ++c) {
@@ -261,6 +282,7 @@ __global__ void __launch_bounds__(RT) fc_tail_rows_kernel(TailArgs a) {
     part[a.F1 + a.F2 + tid] = s;
   }
   if (tid < 4) part[a.F1 + a.F2 + 16 + a.F2 * a.NC + tid] = tid < 3 ? misc[tid] : 0.f;
+  TL(8);
 }
 
 struct TailGradArgs {
@@ -337,10 +359,17 @@ __global__ void __launch_bounds__(RT) fc_tail_grads_kernel(TailGradArgs a) {
 }
 
 int rows_per_cta(int B) { return B <= 1024 ? 4 : 8; }
+long long* g_tail_timeline = nullptr;
 }  // namespace
 
+void fc_tail_set_timeline(long long* dev_buf) { g_tail_timeline = dev_buf; }
+
+static int64_t part_bytes(int B, int F1, int F2, int NC) {
+  return round_up((int64_t)cdiv(B, rows_per_cta(B)) * part_len(F1, F2, NC) * 4, 256);
+}
+// per-CTA partial sums + the bf16 image of W2
 int64_t fc_tail_scratch_bytes(int B, int F1, int F2, int NC) {
-  return (int64_t)cdiv(B, rows_per_cta(B)) * part_len(F1, F2, NC) * 4;
+  return part_bytes(B, F1, F2, NC) + round_up((int64_t)F1 * (F2 + 2) * 2, 256);
 }
 
 int fc_tail(const float* fc1_part, int n_part, const float* b1, float* full1, const float* w2, const float* b2,
@@ -353,9 +382,13 @@ int fc_tail(const float* fc1_part, int n_part, const float* b1, float* full1, co
   const int R = rows_per_cta(B);
   const int nrc = cdiv(B, R);
   float* part = reinterpret_cast<float*>(scratch);
-  TailArgs a{B, F1, F2, NC, R, fc1_part, n_part, b1, full1, w2, b2, w3, b3, labels, full2, logits, dlogits, dfull2,
-             dfull1, pred, part, zero_ptr, zero_n};
-  const size_t smem = (size_t)(2 * R * F1 + 2 * R * F2 + 2 * R * kMaxCls + 4) * 4 + (size_t)F1 * F2 * 2;
+  __nv_bfloat16* w2b = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<char*>(scratch) + part_bytes(B, F1, F2, NC));
+  w2_to_bf16_kernel<<<cdiv(F1 * (F2 + 2), 256), 256, 0, st>>>(w2, w2b, F1, F2);
+  B200_LAUNCH_CHECK();
+  TailArgs a{B, F1, F2, NC, R, fc1_part, n_part, b1, full1, w2, b2, w3, b3, w2b, labels, full2, logits, dlogits,
+             dfull2, dfull1, pred, part, zero_ptr, zero_n, g_tail_timeline};
+  const size_t smem = (size_t)(2 * R * F1 + 2 * R * F2 + 2 * R * kMaxCls + 4 + ((F2 * NC + 3) & ~3) + 4) * 4 +
+                      (size_t)F1 * (F2 + 2) * 2;
   B200_REQUIRE(smem <= 200 * 1024, "fc_tail: layer widths too large (%zu bytes of shared memory)", smem);
   static bool attr = false;
   if (!attr) {

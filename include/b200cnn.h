@@ -164,10 +164,10 @@ int b200_conv1_wgrad_bf16(const uint8_t* images, const float* dpool, const float
  * forward and dgrad take the filter PACKED: b200_conv5x5_pack_weights turns the fp32 HWIO tensor into
  * bf16 shared-memory images (b200_conv5x5_packed_bytes bytes) that the kernels fetch with bulk copies;
  * one packed copy serves both directions. */
-/* diagnostics: when given a device buffer of 8 int64, CTA 0 of the conv2 forward / dgrad kernel stores
+/* diagnostics: when given a device buffer of 32 int64 (conv stamps in [0,8), FC-tail stamps in [16,25)), CTA 0 of the conv2 forward / dgrad kernel stores
  * clock64() at its phase boundaries (start, strip zeroed, strip filled, MMA start, MMA issued,
  * accumulators ready, epilogue done); NULL switches it off. */
-int b200_debug_conv_timeline(int64_t* device_buf8);
+int b200_debug_conv_timeline(int64_t* device_buf32);
 int b200_conv5x5_packed_bytes(int32_t c_in, int32_t c_out, int64_t* nbytes);
 int b200_conv5x5_pack_weights(const float* w, void* w_packed, int32_t c_in, int32_t c_out, void* stream);
 int b200_conv5x5_fwd_bf16(const float* x, const void* w_packed, const float* bias, float* y, int32_t batch, int32_t h,
