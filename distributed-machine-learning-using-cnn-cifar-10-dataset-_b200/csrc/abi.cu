@@ -42,6 +42,10 @@ struct b200_model {
   int64_t ws_bytes = 0;
   std::vector<Tensor> tensors;
   bool forward_done = false;
+  // side streams / events for the independent branches of the backward pass (created at the first
+  // bf16 backward, which must therefore run once eagerly before any stream capture)
+  cudaStream_t side[2] = {nullptr, nullptr};
+  cudaEvent_t ev_fork[2] = {nullptr, nullptr}, ev_join[2] = {nullptr, nullptr};
   const uint8_t* last_images = nullptr;   // records of the last forward (the fused conv1 gradient re-reads them)
   // per-launch-site timing (b200_profile_step): events are created lazily, once
   bool profiling = false;
@@ -125,6 +129,7 @@ int b200_create(const b200_config* c, b200_handle* out) {
   scratch = std::max(scratch, conv5x5_wgrad_tc_scratch_bytes(c->batch) +
                                   colsum_scratch_bytes(c->batch * h->h1 * h->w1, c->c2));
   h->add("scratch", scratch, 1);
+  h->add("scratch2", conv5x5_wgrad_tc_scratch_bytes(c->batch), 1);      // conv2 wgrad runs beside conv1 wgrad
   h->add("w2_packed", conv5x5_packed_bytes(c->c1, c->c2), 1);
   h->add("fc1_part", (int64_t)fc_fwd_tc_splits(c->batch, h->flat, c->f1) * B * c->f1, 4);
   h->add("tail_scratch", fc_tail_scratch_bytes(c->batch, c->f1, c->f2, c->n_cls), 1);
@@ -136,8 +141,14 @@ int b200_create(const b200_config* c, b200_handle* out) {
 }
 
 int b200_destroy(b200_handle h) {
-  if (h)
+  if (h) {
     for (cudaEvent_t ev : h->site_events) cudaEventDestroy(ev);
+    for (int i = 0; i < 2; ++i) {
+      if (h->ev_fork[i]) cudaEventDestroy(h->ev_fork[i]);
+      if (h->ev_join[i]) cudaEventDestroy(h->ev_join[i]);
+      if (h->side[i]) cudaStreamDestroy(h->side[i]);
+    }
+  }
   delete h;
   return B200_OK;
 }
@@ -270,40 +281,80 @@ int b200_backward(b200_handle h, void* stream) {
   float *dpool2 = h->ptr<float>("dpool2"), *dconv2 = h->ptr<float>("dconv2");
   float *dpool1 = h->ptr<float>("dpool1"), *dconv1 = h->ptr<float>("dconv1");
   if (tc) {
-    SITE("full1_bwd", fc_bwd_tc(h->ptr<float>("pool2"), h->P(P_FW1), dfull1, dpool2, h->G(P_FW1), c.batch, h->flat,
-                                c.f1, 0, st));
-  } else {
-    SITE("full3_bwd", fc_bwd_f32(h->ptr<float>("full2"), h->P(P_FW3), dlogits, dfull2, h->G(P_FW3), h->G(P_FB3),
-                                 scratch, c.batch, c.f2, c.n_cls, 1, st));
-    SITE("full2_bwd", fc_bwd_f32(h->ptr<float>("full1"), h->P(P_FW2), dfull2, dfull1, h->G(P_FW2), h->G(P_FB2), scratch,
-                                 c.batch, c.f1, c.f2, 1, st));
-    SITE("full1_bwd", fc_bwd_f32(h->ptr<float>("pool2"), h->P(P_FW1), dfull1, dpool2, h->G(P_FW1), h->G(P_FB1), scratch,
-                                 c.batch, h->flat, c.f1, 0, st));
+    // Dependency graph of the bf16 backward (dfull1 and everything above it came from fc_tail):
+    //   main : FC1 dX -> pool2 bwd -> conv2 dgrad -> conv1 wgrad
+    //   side0: FC1 dW                      (needs dfull1 only)
+    //   side1: conv2 wgrad                 (needs dconv2 only)
+    // The side branches are forked with events so they overlap the main chain, eagerly and inside a
+    // captured CUDA graph alike.  While profiling per site everything stays on one stream.
+    const bool fork = !h->profiling;
+    if (fork && !h->side[0]) {
+      for (int i = 0; i < 2; ++i) {
+        B200_CUDA_TRY(cudaStreamCreateWithFlags(&h->side[i], cudaStreamNonBlocking));
+        B200_CUDA_TRY(cudaEventCreateWithFlags(&h->ev_fork[i], cudaEventDisableTiming));
+        B200_CUDA_TRY(cudaEventCreateWithFlags(&h->ev_join[i], cudaEventDisableTiming));
+      }
+    }
+    cudaStream_t s0 = fork ? h->side[0] : st, s1 = fork ? h->side[1] : st;
+    const bool fused1 = conv1_tc_supported(c.crop_h, c.crop_w, c.c_in, c.c1);
+    if (fork) {
+      B200_CUDA_TRY(cudaEventRecord(h->ev_fork[0], st));
+      B200_CUDA_TRY(cudaStreamWaitEvent(s0, h->ev_fork[0], 0));
+    }
+    {
+      cudaStream_t st = s0;   // SITE() launches on `st`
+      SITE("full1_dw", fc_dw_tc(h->ptr<float>("pool2"), dfull1, h->G(P_FW1), c.batch, h->flat, c.f1, st));
+    }
+    SITE("full1_dx", fc_dx_tc(h->ptr<float>("pool2"), h->P(P_FW1), dfull1, dpool2, c.batch, h->flat, c.f1, 0, st));
+    // conv2's bias gradient rides along (atomics into the buffer the tail kernel cleared)
+    SITE("pool2_bwd", maxpool_bwd_f32(dpool2, h->ptr<uint8_t>("arg2"), h->ptr<float>("conv2"), dconv2, c.batch, h->h1,
+                                      h->w1, c.c2, 1, st, h->G(P_B2)));
+    if (fork) {
+      B200_CUDA_TRY(cudaEventRecord(h->ev_fork[1], st));
+      B200_CUDA_TRY(cudaStreamWaitEvent(s1, h->ev_fork[1], 0));
+    }
+    {
+      cudaStream_t st = s1;
+      SITE("conv2_wgrad", conv5x5_wgrad_tc(h->ptr<float>("pool1"), dconv2, h->G(P_W2), h->ptr<float>("scratch2"),
+                                           c.batch, h->h1, h->w1, c.c1, c.c2, st));
+    }
+    SITE("conv2_dgrad", conv5x5_dgrad_tc(dconv2, h->ptr<void>("w2_packed"), dpool1, c.batch, h->h1, h->w1, c.c1, c.c2,
+                                         st));
+    if (fused1) {
+      SITE("conv1_wgrad", conv1_wgrad_tc(h->last_images, dpool1, h->ptr<float>("pool1"), h->ptr<uint8_t>("arg1"),
+                                         h->G(P_W1), h->G(P_B1), scratch, c.batch, c.img_h, c.img_w, c.crop_h,
+                                         c.crop_w, st));
+    } else {
+      SITE("pool1_bwd", maxpool_bwd_f32(dpool1, h->ptr<uint8_t>("arg1"), h->ptr<float>("conv1"), dconv1, c.batch,
+                                        c.crop_h, c.crop_w, c.c1, 1, st));
+      SITE("conv1_wgrad", conv5x5_wgrad_f32(h->ptr<float>("x"), dconv1, h->G(P_W1), h->G(P_B1), scratch, c.batch,
+                                            c.crop_h, c.crop_w, c.c_in, c.c1, st));
+    }
+    if (fork) {
+      for (int i = 0; i < 2; ++i) {
+        B200_CUDA_TRY(cudaEventRecord(h->ev_join[i], h->side[i]));
+        B200_CUDA_TRY(cudaStreamWaitEvent(st, h->ev_join[i], 0));
+      }
+    }
+    return B200_OK;
   }
-  // bf16 mode: conv2's bias gradient rides along (atomics into the buffer the tail kernel cleared)
+  SITE("full3_bwd", fc_bwd_f32(h->ptr<float>("full2"), h->P(P_FW3), dlogits, dfull2, h->G(P_FW3), h->G(P_FB3),
+                               scratch, c.batch, c.f2, c.n_cls, 1, st));
+  SITE("full2_bwd", fc_bwd_f32(h->ptr<float>("full1"), h->P(P_FW2), dfull2, dfull1, h->G(P_FW2), h->G(P_FB2), scratch,
+                               c.batch, c.f1, c.f2, 1, st));
+  SITE("full1_bwd", fc_bwd_f32(h->ptr<float>("pool2"), h->P(P_FW1), dfull1, dpool2, h->G(P_FW1), h->G(P_FB1), scratch,
+                               c.batch, h->flat, c.f1, 0, st));
   SITE("pool2_bwd", maxpool_bwd_f32(dpool2, h->ptr<uint8_t>("arg2"), h->ptr<float>("conv2"), dconv2, c.batch, h->h1,
-                                    h->w1, c.c2, 1, st, tc ? h->G(P_B2) : nullptr));
-  if (tc) {
-    SITE("conv2_wgrad", conv5x5_wgrad_tc(h->ptr<float>("pool1"), dconv2, h->G(P_W2), scratch, c.batch, h->h1, h->w1,
-                                         c.c1, c.c2, st));
-    SITE("conv2_dgrad", conv5x5_dgrad_tc(dconv2, h->ptr<void>("w2_packed"), dpool1, c.batch, h->h1, h->w1, c.c1, c.c2, st));
-  } else {
-    SITE("conv2_wgrad", conv5x5_wgrad_f32(h->ptr<float>("pool1"), dconv2, h->G(P_W2), h->G(P_B2), scratch, c.batch,
-                                          h->h1, h->w1, c.c1, c.c2, st));
-    SITE("conv2_dgrad_prep", conv5x5_rot180_f32(h->P(P_W2), h->ptr<float>("wrot"), c.c1, c.c2, st));
-    SITE("conv2_dgrad", conv5x5_fwd_f32(dconv2, h->ptr<float>("wrot"), nullptr, dpool1, c.batch, h->h1, h->w1, c.c2,
-                                        c.c1, 0, st));
-  }
-  if (tc && conv1_tc_supported(c.crop_h, c.crop_w, c.c_in, c.c1)) {
-    SITE("conv1_wgrad", conv1_wgrad_tc(h->last_images, dpool1, h->ptr<float>("pool1"), h->ptr<uint8_t>("arg1"),
-                                       h->G(P_W1), h->G(P_B1), scratch, c.batch, c.img_h, c.img_w, c.crop_h, c.crop_w,
-                                       st));
-  } else {
-    SITE("pool1_bwd", maxpool_bwd_f32(dpool1, h->ptr<uint8_t>("arg1"), h->ptr<float>("conv1"), dconv1, c.batch,
-                                      c.crop_h, c.crop_w, c.c1, 1, st));
-    SITE("conv1_wgrad", conv5x5_wgrad_f32(h->ptr<float>("x"), dconv1, h->G(P_W1), h->G(P_B1), scratch, c.batch,
-                                          c.crop_h, c.crop_w, c.c_in, c.c1, st));
-  }
+                                    h->w1, c.c2, 1, st));
+  SITE("conv2_wgrad", conv5x5_wgrad_f32(h->ptr<float>("pool1"), dconv2, h->G(P_W2), h->G(P_B2), scratch, c.batch,
+                                        h->h1, h->w1, c.c1, c.c2, st));
+  SITE("conv2_dgrad_prep", conv5x5_rot180_f32(h->P(P_W2), h->ptr<float>("wrot"), c.c1, c.c2, st));
+  SITE("conv2_dgrad", conv5x5_fwd_f32(dconv2, h->ptr<float>("wrot"), nullptr, dpool1, c.batch, h->h1, h->w1, c.c2,
+                                      c.c1, 0, st));
+  SITE("pool1_bwd", maxpool_bwd_f32(dpool1, h->ptr<uint8_t>("arg1"), h->ptr<float>("conv1"), dconv1, c.batch,
+                                    c.crop_h, c.crop_w, c.c1, 1, st));
+  SITE("conv1_wgrad", conv5x5_wgrad_f32(h->ptr<float>("x"), dconv1, h->G(P_W1), h->G(P_B1), scratch, c.batch,
+                                        c.crop_h, c.crop_w, c.c_in, c.c1, st));
   return B200_OK;
 }
 

@@ -34,6 +34,9 @@ int fc_fwd_tc(const float* x, const float* w, const float* b, float* y, int B, i
               cudaStream_t st);
 int fc_bwd_tc(const float* x, const float* w, const float* dy, float* dx, float* dw, int B, int K, int N,
               int mask_x, cudaStream_t st);
+int fc_dw_tc(const float* x, const float* dy, float* dw, int B, int K, int N, cudaStream_t st);
+int fc_dx_tc(const float* x, const float* w, const float* dy, float* dx, int B, int K, int N, int mask_x,
+             cudaStream_t st);
 // wp: the filter packed once per step by pack_conv_weights (conv5x5_packed_bytes bytes)
 void conv5x5_set_timeline(long long* dev_buf);   // diagnostics: CTA 0 of conv5x5_tc_kernel stamps clock64 per phase
 int64_t conv5x5_packed_bytes(int Cin, int Cout);

@@ -260,21 +260,27 @@ int fc_fwd_tc_splitk(const float* x, const float* w, float* part, int Bt, int K,
   return dispatch<false, true>(g, st);
 }
 
-// dw = x^T dy, dx = (dy w^T) * [x > 0]?   (bias gradient: colsum_f32)
+// dw[K,N] = x^T[K,Bt] dy[Bt,N]: A(m=k_feat, k=batch) = x[batch*K + m] MN-major; B(k=batch, n) = dy MN-major
+int fc_dw_tc(const float* x, const float* dy, float* dw, int Bt, int K, int N, cudaStream_t st) {
+  GemmArgs g{K, N, Bt, x, K, dy, N, dw, N, nullptr, 0, nullptr, 0, nullptr, (int)round_up(Bt, BK), 0};
+  int rc = check_align(g, true, true);
+  if (rc) return rc;
+  return dispatch<true, true>(g, st);
+}
+// dx[Bt,K] = (dy[Bt,N] w^T) * [x > 0]?: A = dy K-major; B(k=n_out, n=k_feat) = w[n*N + k] K-major
+int fc_dx_tc(const float* x, const float* w, const float* dy, float* dx, int Bt, int K, int N, int mask_x,
+             cudaStream_t st) {
+  GemmArgs g{Bt, K, N, dy, N, w, N, dx, K, nullptr, 0, mask_x ? x : nullptr, K, nullptr, (int)round_up(N, BK), 0};
+  int rc = check_align(g, false, false);
+  if (rc) return rc;
+  return dispatch<false, false>(g, st);
+}
+// both gradients of one FC layer (bias gradient: colsum_f32 / fc_tail)
 int fc_bwd_tc(const float* x, const float* w, const float* dy, float* dx, float* dw, int Bt, int K, int N,
               int mask_x, cudaStream_t st) {
-  int rc;
-  {  // dw[K,N] = x^T[K,Bt] dy[Bt,N]: A(m=k_feat, k=batch) = x[batch*K + m] MN-major; B(k=batch, n) = dy MN-major
-    GemmArgs g{K, N, Bt, x, K, dy, N, dw, N, nullptr, 0, nullptr, 0, nullptr, (int)round_up(Bt, BK), 0};
-    if ((rc = check_align(g, true, true))) return rc;
-    if ((rc = dispatch<true, true>(g, st))) return rc;
-  }
-  if (dx) {  // dx[Bt,K] = dy[Bt,N] w^T: A = dy K-major; B(k=n_out, n=k_feat) = w[n*N + k] K-major
-    GemmArgs g{Bt, K, N, dy, N, w, N, dx, K, nullptr, 0, mask_x ? x : nullptr, K, nullptr, (int)round_up(N, BK), 0};
-    if ((rc = check_align(g, false, false))) return rc;
-    if ((rc = dispatch<false, false>(g, st))) return rc;
-  }
-  return B200_OK;
+  int rc = fc_dw_tc(x, dy, dw, Bt, K, N, st);
+  if (rc || !dx) return rc;
+  return fc_dx_tc(x, w, dy, dx, Bt, K, N, mask_x, st);
 }
 
 }  // namespace b200

@@ -78,7 +78,9 @@ int b200_bind_workspace(b200_handle h, void* workspace, int64_t nbytes);
  * workspace; b200_result_ptrs exposes them. */
 int b200_forward(b200_handle h, const uint8_t* images, const int32_t* labels, void* stream);
 /* the gradient graph built by minimize() (:162-163); fills the bound gradient buffer.  The `images`
- * buffer given to the last b200_forward must still be intact (the conv1 gradient re-reads the records). */
+ * buffer given to the last b200_forward must still be intact (the conv1 gradient re-reads the records).
+ * In bf16 mode independent branches run on two internal side streams forked from / joined to `stream` with
+ * events; those streams are created by the first call, which must therefore happen before any capture. */
 int b200_backward(b200_handle h, void* stream);
 /* ApplyGradientDescent x10 (:162-163): params -= lr * grad_scale * grads.  grad_scale = 1 for a
  * single worker or a SUM allreduce, 1/world for a MEAN allreduce. */
