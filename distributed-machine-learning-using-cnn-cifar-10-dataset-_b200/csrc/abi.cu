@@ -196,6 +196,17 @@ int b200_bind_workspace(b200_handle h, void* ws, int64_t nbytes) {
   } while (0)
 #define TRY(expr) do { int rc__ = (expr); if (rc__) return rc__; } while (0)
 
+// side streams / events for the independent branches of a bf16 step (lazily, at the first eager call)
+static int ensure_side_streams(b200_model* h) {
+  if (h->side[0]) return B200_OK;
+  for (int i = 0; i < 2; ++i) {
+    B200_CUDA_TRY(cudaStreamCreateWithFlags(&h->side[i], cudaStreamNonBlocking));
+    B200_CUDA_TRY(cudaEventCreateWithFlags(&h->ev_fork[i], cudaEventDisableTiming));
+    B200_CUDA_TRY(cudaEventCreateWithFlags(&h->ev_join[i], cudaEventDisableTiming));
+  }
+  return B200_OK;
+}
+
 // A launch site: one logical kernel group of the step.  When b200_profile_step is active an
 // event is recorded on the stream before each site (and one after the last).
 static int site_mark(b200_model* h, const char* name, cudaStream_t st) {
@@ -226,6 +237,21 @@ int b200_forward(b200_handle h, const uint8_t* images, const int32_t* labels, vo
   float *full1 = h->ptr<float>("full1"), *full2 = h->ptr<float>("full2"), *logits = h->ptr<float>("logits");
   const bool fused1 = tc && conv1_tc_supported(c.crop_h, c.crop_w, c.c_in, c.c1);
   h->last_images = images;
+  // bf16 mode: the weight images the tensor-core kernels stream (conv2 filter, W2) depend only on the
+  // parameters, so they are rebuilt on a side stream while conv1 runs (every step: the caller or the
+  // last update may have changed the parameters).
+  const bool fork = tc && !h->profiling;
+  if (tc) {
+    if (fork) {
+      TRY(ensure_side_streams(h));
+      B200_CUDA_TRY(cudaEventRecord(h->ev_fork[0], st));
+      B200_CUDA_TRY(cudaStreamWaitEvent(h->side[0], h->ev_fork[0], 0));
+    }
+    cudaStream_t st = fork ? h->side[0] : (cudaStream_t)stream;
+    SITE("weights_prep", pack_conv_weights(h->P(P_W2), h->ptr<void>("w2_packed"), c.c1, c.c2, st));
+    TRY(fc_tail_prepare_w2(h->P(P_FW2), h->ptr<void>("tail_scratch"), c.batch, c.f1, c.f2, c.n_cls, st));
+    if (fork) B200_CUDA_TRY(cudaEventRecord(h->ev_join[0], st));
+  }
   if (fused1) {
     SITE("conv1_pool1_fwd", conv1_pool_fwd_tc(images, h->P(P_W1), h->P(P_B1), pool1, h->ptr<uint8_t>("arg1"), nullptr,
                                               c.batch, c.img_h, c.img_w, c.crop_h, c.crop_w, st));
@@ -235,8 +261,7 @@ int b200_forward(b200_handle h, const uint8_t* images, const int32_t* labels, vo
     SITE("pool1_fwd", maxpool_fwd_f32(conv1, pool1, h->ptr<uint8_t>("arg1"), c.batch, c.crop_h, c.crop_w, c.c1, st));
   }
   if (tc) {
-    // the filter may have been changed by the caller or the last update: repack it every step (2 us)
-    SITE("conv2_pack", pack_conv_weights(h->P(P_W2), h->ptr<void>("w2_packed"), c.c1, c.c2, st));
+    if (fork) B200_CUDA_TRY(cudaStreamWaitEvent(st, h->ev_join[0], 0));
     SITE("conv2_fwd", conv5x5_fwd_tc(pool1, h->ptr<void>("w2_packed"), h->P(P_B2), conv2, c.batch, h->h1, h->w1, c.c1,
                                      c.c2, 1, st));
   }
@@ -255,7 +280,7 @@ int b200_forward(b200_handle h, const uint8_t* images, const int32_t* labels, vo
                             h->ptr<float>("dfull2"), h->ptr<float>("dfull1"), h->ptr<int32_t>("pred"),
                             h->ptr<float>("loss"), h->ptr<int32_t>("n_correct"), h->ptr<int32_t>("n_bad"),
                             h->G(P_FW2), h->G(P_FB2), h->G(P_FW3), h->G(P_FB3), h->G(P_FB1),
-                            h->ptr<void>("tail_scratch"), h->G(P_B2), c.c2, c.batch, c.f1, c.f2, c.n_cls, st));
+                            h->ptr<void>("tail_scratch"), h->G(P_B2), c.c2, c.batch, c.f1, c.f2, c.n_cls, st, true));
   } else {
     SITE("full1_fwd", fc_fwd_f32(pool2, h->P(P_FW1), h->P(P_FB1), full1, c.batch, h->flat, c.f1, 1, st));
     SITE("full2_fwd", fc_fwd_f32(full1, h->P(P_FW2), h->P(P_FB2), full2, c.batch, c.f1, c.f2, 1, st));
@@ -288,13 +313,7 @@ int b200_backward(b200_handle h, void* stream) {
     // The side branches are forked with events so they overlap the main chain, eagerly and inside a
     // captured CUDA graph alike.  While profiling per site everything stays on one stream.
     const bool fork = !h->profiling;
-    if (fork && !h->side[0]) {
-      for (int i = 0; i < 2; ++i) {
-        B200_CUDA_TRY(cudaStreamCreateWithFlags(&h->side[i], cudaStreamNonBlocking));
-        B200_CUDA_TRY(cudaEventCreateWithFlags(&h->ev_fork[i], cudaEventDisableTiming));
-        B200_CUDA_TRY(cudaEventCreateWithFlags(&h->ev_join[i], cudaEventDisableTiming));
-      }
-    }
+    if (fork) TRY(ensure_side_streams(h));
     cudaStream_t s0 = fork ? h->side[0] : st, s1 = fork ? h->side[1] : st;
     const bool fused1 = conv1_tc_supported(c.crop_h, c.crop_w, c.c_in, c.c1);
     if (fork) {

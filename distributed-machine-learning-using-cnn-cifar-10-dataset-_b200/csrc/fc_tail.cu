@@ -372,19 +372,30 @@ int64_t fc_tail_scratch_bytes(int B, int F1, int F2, int NC) {
   return part_bytes(B, F1, F2, NC) + round_up((int64_t)F1 * (F2 + 2) * 2, 256);
 }
 
+// the bf16 image of W2 inside `scratch` (same layout fc_tail expects); lets a caller build it early, off
+// the critical path, and then call fc_tail(..., w2_image_ready = true)
+int fc_tail_prepare_w2(const float* w2, void* scratch, int B, int F1, int F2, int NC, cudaStream_t st) {
+  __nv_bfloat16* w2b = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<char*>(scratch) + part_bytes(B, F1, F2, NC));
+  w2_to_bf16_kernel<<<cdiv(F1 * (F2 + 2), 256), 256, 0, st>>>(w2, w2b, F1, F2);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
 int fc_tail(const float* fc1_part, int n_part, const float* b1, float* full1, const float* w2, const float* b2,
             const float* w3, const float* b3, const int32_t* labels, float* full2, float* logits, float* dlogits,
             float* dfull2, float* dfull1, int32_t* pred, float* loss, int32_t* n_correct, int32_t* n_bad, float* dw2,
             float* db2, float* dw3, float* db3, float* db1, void* scratch, float* zero_ptr, int zero_n, int B, int F1,
-            int F2, int NC, cudaStream_t st) {
+            int F2, int NC, cudaStream_t st, bool w2_image_ready) {
   B200_REQUIRE(B > 0 && NC > 0 && NC <= kMaxCls, "fc_tail: bad shape");
   B200_REQUIRE(F1 % KT == 0 && F2 % 4 == 0 && F2 <= RT && F2 > 0, "fc_tail: needs f1 %% 32 == 0, f2 %% 4 == 0, f2 <= 256");
   const int R = rows_per_cta(B);
   const int nrc = cdiv(B, R);
   float* part = reinterpret_cast<float*>(scratch);
   __nv_bfloat16* w2b = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<char*>(scratch) + part_bytes(B, F1, F2, NC));
-  w2_to_bf16_kernel<<<cdiv(F1 * (F2 + 2), 256), 256, 0, st>>>(w2, w2b, F1, F2);
-  B200_LAUNCH_CHECK();
+  if (!w2_image_ready) {
+    w2_to_bf16_kernel<<<cdiv(F1 * (F2 + 2), 256), 256, 0, st>>>(w2, w2b, F1, F2);
+    B200_LAUNCH_CHECK();
+  }
   TailArgs a{B, F1, F2, NC, R, fc1_part, n_part, b1, full1, w2, b2, w3, b3, w2b, labels, full2, logits, dlogits,
              dfull2, dfull1, pred, part, zero_ptr, zero_n, g_tail_timeline};
   const size_t smem = (size_t)(2 * R * F1 + 2 * R * F2 + 2 * R * kMaxCls + 4 + ((F2 * NC + 3) & ~3) + 4) * 4 +
