@@ -325,9 +325,12 @@ int b200_backward(b200_handle h, void* stream) {
       SITE("full1_dw", fc_dw_tc(h->ptr<float>("pool2"), dfull1, h->G(P_FW1), c.batch, h->flat, c.f1, st));
     }
     SITE("full1_dx", fc_dx_tc(h->ptr<float>("pool2"), h->P(P_FW1), dfull1, dpool2, c.batch, h->flat, c.f1, 0, st));
-    // conv2's bias gradient rides along (atomics into the buffer the tail kernel cleared)
-    SITE("pool2_bwd", maxpool_bwd_f32(dpool2, h->ptr<uint8_t>("arg2"), h->ptr<float>("conv2"), dconv2, c.batch, h->h1,
-                                      h->w1, c.c2, 1, st, h->G(P_B2)));
+    // pool2's backward is not a kernel of its own: conv2's dgrad gathers MaxPoolGrad * ReluGrad from (dpool2,
+    // pool2, arg2) while it builds its strip, adds the bias gradient (atomics into the buffer the tail kernel
+    // cleared) and leaves dconv2 behind for the filter gradient, which then overlaps conv1's gradient.
+    SITE("conv2_dgrad", conv5x5_dgrad_pool_tc(dpool2, h->ptr<float>("pool2"), h->ptr<uint8_t>("arg2"),
+                                              h->ptr<void>("w2_packed"), dpool1, h->G(P_B2), dconv2, c.batch, h->h1,
+                                              h->w1, c.c1, c.c2, st));
     if (fork) {
       B200_CUDA_TRY(cudaEventRecord(h->ev_fork[1], st));
       B200_CUDA_TRY(cudaStreamWaitEvent(s1, h->ev_fork[1], 0));
@@ -337,8 +340,6 @@ int b200_backward(b200_handle h, void* stream) {
       SITE("conv2_wgrad", conv5x5_wgrad_tc(h->ptr<float>("pool1"), dconv2, h->G(P_W2), h->ptr<float>("scratch2"),
                                            c.batch, h->h1, h->w1, c.c1, c.c2, st));
     }
-    SITE("conv2_dgrad", conv5x5_dgrad_tc(dconv2, h->ptr<void>("w2_packed"), dpool1, c.batch, h->h1, h->w1, c.c1, c.c2,
-                                         st));
     if (fused1) {
       SITE("conv1_wgrad", conv1_wgrad_tc(h->last_images, dpool1, h->ptr<float>("pool1"), h->ptr<uint8_t>("arg1"),
                                          h->G(P_W1), h->G(P_B1), scratch, c.batch, c.img_h, c.img_w, c.crop_h,
@@ -457,7 +458,7 @@ int b200_launches_per_step(b200_handle h, int32_t* n) {
   if (h->cfg.mode == B200_MODE_BF16) {
     // conv1 (3 or 1), conv2, pool2, FC1 split-K, tail x2 | FC1 bwd x2, pool2 bwd, conv2 wgrad x2, dgrad, conv1 wgrad (2 or 1+4), sgd
     const bool f1 = conv1_tc_supported(h->cfg.crop_h, h->cfg.crop_w, h->cfg.c_in, h->cfg.c1);
-    *n = (f1 ? 1 : 3) + 2 + 1 + 1 + 3 + 2 + 1 + 2 + 1 + (f1 ? 2 : 5) + 1;
+    *n = (f1 ? 1 : 3) + 2 + 1 + 1 + 3 + 2 + 2 + 1 + (f1 ? 2 : 5) + 1;
   }
   return B200_OK;
 }
@@ -575,6 +576,21 @@ int b200_conv5x5_wgrad_bf16(const float* x, const float* dy, float* dw, void* sc
   B200_REQUIRE(x && dy && dw && scratch, "null pointer");
   B200_REQUIRE(batch > 0 && scratch_bytes >= conv5x5_wgrad_tc_scratch_bytes(batch), "scratch too small");
   return conv5x5_wgrad_tc(x, dy, dw, (float*)scratch, batch, h, wd, c_in, c_out, (cudaStream_t)stream);
+}
+int b200_conv5x5_dgrad_pool_bf16(const float* dpool, const float* pool, const uint8_t* arg, const void* w_packed,
+                                 float* dx, float* dbias, int32_t batch, int32_t h, int32_t wd, int32_t c_in,
+                                 int32_t c_out, void* stream) {
+  B200_REQUIRE(dpool && pool && arg && w_packed && dx, "null pointer");
+  return conv5x5_dgrad_pool_tc(dpool, pool, arg, w_packed, dx, dbias, nullptr, batch, h, wd, c_in, c_out,
+                               (cudaStream_t)stream);
+}
+int b200_conv5x5_wgrad_pool_bf16(const float* x, const float* dpool, const float* pool, const uint8_t* arg, float* dw,
+                                 void* scratch, int64_t scratch_bytes, int32_t batch, int32_t h, int32_t wd,
+                                 int32_t c_in, int32_t c_out, void* stream) {
+  B200_REQUIRE(x && dpool && pool && arg && dw && scratch, "null pointer");
+  B200_REQUIRE(batch > 0 && scratch_bytes >= conv5x5_wgrad_tc_scratch_bytes(batch), "scratch too small");
+  return conv5x5_wgrad_pool_tc(x, dpool, pool, arg, dw, (float*)scratch, batch, h, wd, c_in, c_out,
+                               (cudaStream_t)stream);
 }
 int b200_fc_fwd_bf16(const float* x, const float* w, const float* b, float* y, int32_t batch, int32_t k, int32_t n,
                      int32_t relu, void* stream) {

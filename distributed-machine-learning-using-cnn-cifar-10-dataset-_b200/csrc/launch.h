@@ -45,6 +45,13 @@ int conv5x5_fwd_tc(const float* x, const void* wp, const float* bias, float* y, 
                    int Cout, int relu, cudaStream_t st);
 int conv5x5_dgrad_tc(const float* dy, const void* wp, float* dx, int B, int H, int W, int Cin, int Cout,
                      cudaStream_t st);
+// the same two gradients fed by the POOLED gradient: dconv = MaxPoolGrad(dpool, arg) * [pool > 0] is gathered
+// inside the kernels (64 channels); dbias (optional, zero on entry) receives sum(dconv) through atomics;
+// dconv_out (optional) receives dconv as a dense [B,H,W,64] fp32 tensor
+int conv5x5_dgrad_pool_tc(const float* dpool, const float* pool, const uint8_t* arg, const void* wp, float* dx,
+                          float* dbias, float* dconv_out, int B, int H, int W, int Cin, int Cout, cudaStream_t st);
+int conv5x5_wgrad_pool_tc(const float* x, const float* dpool, const float* pool, const uint8_t* arg, float* dw,
+                          float* scratch, int B, int H, int W, int Cin, int Cout, cudaStream_t st);
 int64_t conv5x5_wgrad_tc_scratch_bytes(int B);
 int conv5x5_wgrad_tc(const float* x, const float* dy, float* dw, float* scratch, int B, int H, int W, int Cin,
                      int Cout, cudaStream_t st);

@@ -74,6 +74,72 @@ __device__ __forceinline__ void fill_strip(uint8_t* strip, const float* __restri
   }
 }
 
+// ---- a dY strip built straight from the pooled gradient -------------------------------------------
+// dconv = MaxPoolGrad(dpool, arg) * ReluGrad, the gradient w.r.t. the conv output that fed a 3x3/2 SAME
+// max-pool (cifar10cnn.py:123), never materialised in HBM: the pooled gradient (masked by pool > 0, the
+// ReluGrad of the selected cell) and the argmax of one image are staged in shared memory and every strip
+// pixel gathers the <= 4 windows that cover it.  64 channels.
+struct PoolGradSrc {
+  const float* dpool;     // [B,OH,OW,64]
+  const float* pool;      // [B,OH,OW,64]
+  const uint8_t* arg;     // [B,OH,OW,64]
+  int OH, OW, pbh, pbw;
+};
+__device__ __forceinline__ void stage_pool_grad(float* dpm, uint8_t* argb, const PoolGradSrc& p, int n, int tid) {
+  const int ncell = p.OH * p.OW;
+  const float4* dp4 = reinterpret_cast<const float4*>(p.dpool + (size_t)n * ncell * 64);
+  const float4* pl4 = reinterpret_cast<const float4*>(p.pool + (size_t)n * ncell * 64);
+  const uint32_t* ar4 = reinterpret_cast<const uint32_t*>(p.arg + (size_t)n * ncell * 64);
+#pragma unroll 3
+  for (int q = tid; q < ncell * 16; q += LOADERS) {
+    float4 d = __ldg(dp4 + q), v = __ldg(pl4 + q);
+    d.x = v.x > 0.f ? d.x : 0.f; d.y = v.y > 0.f ? d.y : 0.f;
+    d.z = v.z > 0.f ? d.z : 0.f; d.w = v.w > 0.f ? d.w : 0.f;
+    reinterpret_cast<float4*>(dpm)[q] = d;
+    reinterpret_cast<uint32_t*>(argb)[q] = __ldg(ar4 + q);
+  }
+}
+// gathers image slot `img` of the strip; bsum accumulates this thread's channel chunk (tid & 7) for the bias gradient
+__device__ __forceinline__ void fill_strip_from_pool(uint8_t* strip, const float* dpm, const uint8_t* argb,
+                                                     const ConvGeom& g, const PoolGradSrc& p, int img, int ch_stride,
+                                                     int tid, float (&bsum)[8], float* __restrict__ dense_out = nullptr) {
+  for (int q = tid; q < g.H * g.W * 8; q += LOADERS) {
+    const int c8 = q & 7, pix = q >> 3;
+    const int i = pix / g.W, j = pix - i * g.W;
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh) {
+      const int r = i + p.pbh - kh;
+      if (r < 0 || (r & 1) || (r >> 1) >= p.OH) continue;
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) {
+        const int cc = j + p.pbw - kw;
+        if (cc < 0 || (cc & 1) || (cc >> 1) >= p.OW) continue;
+        const int cell = (r >> 1) * p.OW + (cc >> 1);
+        const uint2 ab = *reinterpret_cast<const uint2*>(argb + cell * 64 + c8 * 8);
+        const float4 d0 = *reinterpret_cast<const float4*>(dpm + cell * 64 + c8 * 8);
+        const float4 d1 = *reinterpret_cast<const float4*>(dpm + cell * 64 + c8 * 8 + 4);
+        const uint32_t code = kh * 3 + kw;
+        const float dv[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const uint32_t ae = ((e < 4 ? ab.x : ab.y) >> (8 * (e & 3))) & 0xffu;
+          if (ae == code) acc[e] += dv[e];
+        }
+      }
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) bsum[e] += acc[e];
+    const int slot = g.lead + (img * g.rows_per_img + i) * g.P + j;
+    *reinterpret_cast<uint4*>(strip + c8 * ch_stride + slot * 16) = pack8(acc);
+    if (dense_out) {          // dense NHWC fp32 copy for a consumer that runs later (8 lanes = one pixel's 256 B)
+      float4* o = reinterpret_cast<float4*>(dense_out + (size_t)pix * 64 + c8 * 8);
+      o[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+      o[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+    }
+  }
+}
+
 struct ConvArgs {
   const float* x;      // [B,H,W,KC]
   const uint8_t* wp;   // filter packed by pack_conv_weights (bf16, ready-made shared-memory images per tap)
@@ -83,6 +149,9 @@ struct ConvArgs {
   int relu;
   ConvGeom g;
   long long* timeline;  // optional device buffer [8]: clock64 stamps of CTA 0's phases (diagnostics), else null
+  PoolGradSrc pg;       // POOL variant: x is unused, the strip is gathered from the pooled gradient
+  float* dbias;         // POOL variant: += sum of dconv over pixels per channel (atomics; zero on entry), or null
+  float* dconv_out;     // POOL variant: also store dconv as dense [B,H,W,64] fp32 (for the filter gradient), or null
 };
 
 // ---------------------------------------------------------------------------------------------------
@@ -92,7 +161,7 @@ struct ConvArgs {
 // DGRAD = false: y = conv(x, w)            B operand (kc,nc) = w[tap][kc][nc]     (MN-major)
 // DGRAD = true : y = conv(x, rot180(w)^T)  B operand (kc,nc) = w[24-tap][nc][kc]  (K-major)
 // ---------------------------------------------------------------------------------------------------
-template <bool DGRAD, int KSTEPS>
+template <bool DGRAD, int KSTEPS, bool POOL = false>
 __global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
   constexpr int BN = 64;
   constexpr int NISS = 4;                 // MMA-issuing warps (warps 4..7); warp 8 streams the filter
@@ -111,6 +180,9 @@ __global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
   uint64_t* strip_full = wempty + WSTAGES;
   uint64_t* accum = strip_full + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum + 1);
+  float* dpm = reinterpret_cast<float*>(ctrl + 256);                  // POOL: [OH*OW][64] masked pooled gradient
+  uint8_t* argb = reinterpret_cast<uint8_t*>(dpm + (POOL ? a.pg.OH * a.pg.OW * 64 : 0));
+  float* bred = reinterpret_cast<float*>(argb + (POOL ? ((a.pg.OH * a.pg.OW * 64 + 15) & ~15) : 0));   // [64]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int n_img0 = blockIdx.x * g.ipc;
@@ -135,9 +207,29 @@ __global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
     zero_smem(strip, strip_bytes, tid);
     loaders_sync();
     if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) a.timeline[1] = clock64();
-    fill_strip(strip, a.x, g, n_img0, g.KC, g.ch_stride, tid);
+    if (POOL) {
+      float bsum[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      if (tid < 64) bred[tid] = 0.f;
+      for (int img = 0; img < g.ipc && n_img0 + img < g.B; ++img) {
+        stage_pool_grad(dpm, argb, a.pg, n_img0 + img, tid);
+        loaders_sync();
+        fill_strip_from_pool(strip, dpm, argb, g, a.pg, img, g.ch_stride, tid, bsum,
+                             (a.dconv_out && blockIdx.y == 0) ? a.dconv_out + (size_t)(n_img0 + img) * g.H * g.W * 64 : nullptr);
+        loaders_sync();
+      }
+      if (a.dbias && blockIdx.y == 0) {        // BiasAddGrad of the conv layer: chunk tid&7, 16 threads share it
+#pragma unroll
+        for (int e = 0; e < 8; ++e) atomicAdd(bred + (tid & 7) * 8 + e, bsum[e]);
+      }
+    } else {
+      fill_strip(strip, a.x, g, n_img0, g.KC, g.ch_stride, tid);
+    }
     fence_proxy_async();
     mbar_arrive(smem_u32(strip_full));
+    if (POOL && a.dbias && blockIdx.y == 0) {
+      loaders_sync();
+      if (tid < 64) atomicAdd(a.dbias + tid, bred[tid]);
+    }
     if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) a.timeline[2] = clock64();
     // ---- epilogue: TMEM -> registers -> (+bias, relu) -> dense NHWC fp32 ---------------------------
     mbar_wait(smem_u32(accum), 0);
@@ -277,20 +369,26 @@ long long* g_conv_timeline = nullptr;
 
 template <bool DGRAD>
 int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, int B, int H, int W, int KC, int NC,
-                int relu, cudaStream_t st) {
+                int relu, cudaStream_t st, const PoolGradSrc* pg = nullptr, float* dbias = nullptr,
+                float* dconv_out = nullptr) {
   B200_REQUIRE(B > 0 && H > 0 && W > 0, "conv5x5_tc: bad shape");
   B200_REQUIRE(KC % 16 == 0 && NC % 64 == 0, "conv5x5_tc: channels must be multiples of 16 (in) / 64 (out), got %d/%d",
                KC, NC);
-  B200_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)wp & 15) == 0 && ((uintptr_t)y & 15) == 0,
+  B200_REQUIRE((pg || ((uintptr_t)x & 15) == 0) && ((uintptr_t)wp & 15) == 0 && ((uintptr_t)y & 15) == 0,
                "conv5x5_tc: pointers must be 16-byte aligned");
   int ipc = pick_ipc(B, H, W, KC);
   ConvGeom g = make_geom(B, H, W, KC, NC, ipc);
   B200_REQUIRE(g.tiles * 64 <= 512, "conv5x5_tc: image %dx%d too large for one CTA's TMEM", H, W);
   const int kchunks = KC / 8;
   const int wstage = ((DGRAD ? kchunks * (64 * 16 + 16) : 8 * (KC * 16 + 16)) + 127) & ~127;
-  const int smem = ((kchunks * g.ch_stride + 127) & ~127) + WSTAGES * wstage + 256;
+  int smem = ((kchunks * g.ch_stride + 127) & ~127) + WSTAGES * wstage + 256;
+  if (pg) smem += pg->OH * pg->OW * 64 * 5 + 16 + 256;
   B200_REQUIRE(smem <= 227 * 1024, "conv5x5_tc: %d bytes of shared memory needed", smem);
   void (*kern)(ConvArgs) = nullptr;
+  if (pg) {
+    B200_REQUIRE(DGRAD && KC == 64, "conv5x5_tc: the pooled-gradient source needs 64 channels");
+    kern = conv5x5_tc_kernel<true, 4, true>;
+  } else
   switch (KC / 16) {
     case 2: kern = conv5x5_tc_kernel<DGRAD, 2>; break;
     case 4: kern = conv5x5_tc_kernel<DGRAD, 4>; break;
@@ -299,7 +397,7 @@ int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, 
     default: B200_REQUIRE(false, "conv5x5_tc: contraction channels must be 32, 64, 128 or 256 (got %d)", KC);
   }
   B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-  ConvArgs a{x, wp, DGRAD ? NC : KC, DGRAD ? KC : NC, bias, y, relu, g, g_conv_timeline};
+  ConvArgs a{x, wp, DGRAD ? NC : KC, DGRAD ? KC : NC, bias, y, relu, g, g_conv_timeline, pg ? *pg : PoolGradSrc{}, dbias, dconv_out};
   dim3 grid(cdiv(B, ipc), NC / 64);
   kern<<<grid, 288, smem, st>>>(a);
   B200_LAUNCH_CHECK();
@@ -319,6 +417,7 @@ struct WgradArgs {
   ConvGeom g;          // ipc = 1
   int imgs_per_cta;
   int nbuf;             // 2 = double-buffered strips, 1 when two pairs do not fit in shared memory
+  PoolGradSrc pg;       // when pg.dpool != null, dy is unused and the dY strip is gathered from the pooled gradient
 };
 
 __global__ void __launch_bounds__(288, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
@@ -331,6 +430,8 @@ __global__ void __launch_bounds__(288, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
   uint64_t* empty = full + 2;
   uint64_t* accum = empty + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum + 1);
+  float* dpm = reinterpret_cast<float*>(ctrl + 256);
+  uint8_t* argb = reinterpret_cast<uint8_t*>(dpm + (a.pg.dpool ? a.pg.OH * a.pg.OW * 64 : 0));
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int di = blockIdx.x;
@@ -360,7 +461,15 @@ __global__ void __launch_bounds__(288, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
       uint8_t* xs = smem + (2 * b) * strip_bytes;
       uint8_t* ds = xs + strip_bytes;
       fill_strip(xs, a.x, g, img_beg + it, C, g.ch_stride, tid);
-      fill_strip(ds, a.dy, g, img_beg + it, C, g.ch_stride, tid);
+      if (a.pg.dpool) {
+        float unused[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        stage_pool_grad(dpm, argb, a.pg, img_beg + it, tid);
+        loaders_sync();
+        fill_strip_from_pool(ds, dpm, argb, g, a.pg, 0, g.ch_stride, tid, unused);
+        loaders_sync();                       // nobody restages dpm while a slower loader still gathers from it
+      } else {
+        fill_strip(ds, a.dy, g, img_beg + it, C, g.ch_stride, tid);
+      }
       fence_proxy_async();
       mbar_arrive(smem_u32(full + b));
     }
@@ -465,15 +574,42 @@ int conv5x5_dgrad_tc(const float* dy, const void* wp, float* dx, int B, int H, i
                      cudaStream_t st) {
   return launch_conv<true>(dy, (const uint8_t*)wp, nullptr, dx, B, H, W, Cout, Cin, 0, st);
 }
+static PoolGradSrc make_pool_src(const float* dpool, const float* pool, const uint8_t* arg, int H, int W) {
+  PoolGradSrc p{dpool, pool, arg, (H + 1) / 2, (W + 1) / 2, 0, 0};
+  p.pbh = std::max((p.OH - 1) * 2 + 3 - H, 0) / 2;
+  p.pbw = std::max((p.OW - 1) * 2 + 3 - W, 0) / 2;
+  return p;
+}
+// dx = Conv2DBackpropInput(dconv, w) with dconv = MaxPoolGrad(dpool, arg) * [pool > 0] gathered on the fly;
+// dbias (optional, zero on entry) += sum of dconv over (B,H,W)
+int conv5x5_dgrad_pool_tc(const float* dpool, const float* pool, const uint8_t* arg, const void* wp, float* dx,
+                          float* dbias, float* dconv_out, int B, int H, int W, int Cin, int Cout, cudaStream_t st) {
+  B200_REQUIRE(Cin % 64 == 0 && Cout == 64, "conv5x5_dgrad_pool_tc: needs Cout == 64 (got %d -> %d)", Cin, Cout);
+  PoolGradSrc p = make_pool_src(dpool, pool, arg, H, W);
+  return launch_conv<true>(nullptr, (const uint8_t*)wp, nullptr, dx, B, H, W, Cout, Cin, 0, st, &p, dbias, dconv_out);
+}
 int64_t conv5x5_wgrad_tc_scratch_bytes(int B) { return (int64_t)wgrad_splits_tc(B) * 25 * 64 * 64 * 4; }
+static int launch_wgrad(const float* x, const float* dy, const PoolGradSrc* pg, float* dw, float* scratch, int B, int H,
+                        int W, int Cin, int Cout, cudaStream_t st);
 int conv5x5_wgrad_tc(const float* x, const float* dy, float* dw, float* scratch, int B, int H, int W, int Cin,
                      int Cout, cudaStream_t st) {
+  return launch_wgrad(x, dy, nullptr, dw, scratch, B, H, W, Cin, Cout, st);
+}
+// filter gradient with dY = MaxPoolGrad(dpool, arg) * [pool > 0] gathered on the fly
+int conv5x5_wgrad_pool_tc(const float* x, const float* dpool, const float* pool, const uint8_t* arg, float* dw,
+                          float* scratch, int B, int H, int W, int Cin, int Cout, cudaStream_t st) {
+  PoolGradSrc p = make_pool_src(dpool, pool, arg, H, W);
+  return launch_wgrad(x, nullptr, &p, dw, scratch, B, H, W, Cin, Cout, st);
+}
+static int launch_wgrad(const float* x, const float* dy, const PoolGradSrc* pg, float* dw, float* scratch, int B, int H,
+                        int W, int Cin, int Cout, cudaStream_t st) {
   B200_REQUIRE(Cin == 64 && Cout == 64, "conv5x5_wgrad_tc: only 64 -> 64 channels (got %d -> %d)", Cin, Cout);
   B200_REQUIRE(B > 0 && H > 0 && W > 0, "conv5x5_wgrad_tc: bad shape");
   ConvGeom g = make_geom(B, H, W, 64, 64, 1);
   const int strip_bytes = ((8 * g.ch_stride) + 127) & ~127;
-  const int nbuf = (4 * strip_bytes + 256 <= 227 * 1024) ? 2 : 1;
-  const int smem = 2 * nbuf * strip_bytes + 256;
+  const int extra = pg ? pg->OH * pg->OW * 64 * 5 + 16 : 0;
+  const int nbuf = (4 * strip_bytes + 256 + extra <= 227 * 1024) ? 2 : 1;
+  const int smem = 2 * nbuf * strip_bytes + 256 + extra;
   B200_REQUIRE(smem <= 227 * 1024, "conv5x5_wgrad_tc: image %dx%d needs %d bytes of shared memory", H, W, smem);
   static bool attr = false;
   if (!attr) {
@@ -484,7 +620,7 @@ int conv5x5_wgrad_tc(const float* x, const float* dy, float* dw, float* scratch,
   int S = wgrad_splits_tc(B);
   int per = cdiv(B, S);
   S = cdiv(B, per);
-  WgradArgs a{x, dy, scratch, g, per, nbuf};
+  WgradArgs a{x, dy, scratch, g, per, nbuf, pg ? *pg : PoolGradSrc{}};
   conv5x5_wgrad_tc_kernel<<<dim3(5, S), 288, smem, st>>>(a);
   B200_LAUNCH_CHECK();
   const int n = 25 * 64 * 64;

@@ -179,6 +179,16 @@ int b200_conv5x5_dgrad_bf16(const float* dy, const void* w_packed, float* dx, in
 int b200_conv5x5_wgrad_bf16_scratch_bytes(int32_t batch, int64_t* nbytes);
 int b200_conv5x5_wgrad_bf16(const float* x, const float* dy, float* dw, void* scratch, int64_t scratch_bytes,
                             int32_t batch, int32_t h, int32_t wd, int32_t c_in, int32_t c_out, void* stream);
+/* Conv2DBackpropInput / Conv2DBackpropFilter fed by the POOLED gradient: MaxPoolGrad (:123) and the ReluGrad
+ * of :121 are applied while the kernels build their shared-memory strips, so the gradient w.r.t. the conv
+ * output never exists in HBM.  pool / arg are the forward pool output and argmax, dpool its gradient, all
+ * [batch, ceil(h/2), ceil(wd/2), 64].  dbias (optional, must be zero on entry) receives BiasAddGrad (:120). */
+int b200_conv5x5_dgrad_pool_bf16(const float* dpool, const float* pool, const uint8_t* arg, const void* w_packed,
+                                 float* dx, float* dbias, int32_t batch, int32_t h, int32_t wd, int32_t c_in,
+                                 int32_t c_out, void* stream);
+int b200_conv5x5_wgrad_pool_bf16(const float* x, const float* dpool, const float* pool, const uint8_t* arg, float* dw,
+                                 void* scratch, int64_t scratch_bytes, int32_t batch, int32_t h, int32_t wd,
+                                 int32_t c_in, int32_t c_out, void* stream);
 /* The same two products on the tensor cores (tcgen05, bf16 operands rounded from the fp32 tensors
  * on the fly, fp32 accumulation in TMEM).  batch, k and n must be multiples of 8. */
 int b200_fc_fwd_bf16(const float* x, const float* w, const float* b, float* y, int32_t batch, int32_t k, int32_t n,

@@ -252,3 +252,41 @@ def test_conv1_pool_fused_fwd_and_wgrad(lib, B, crop):
         assert relerr(db.cpu().numpy(), dconv_r.sum((0, 1, 2))) <= TIGHT
     assert relerr(dw.cpu().numpy(), rn.conv2d_same_grad_filter(x, dconv)) <= LOOSE
     assert relerr(db.cpu().numpy(), dconv.sum((0, 1, 2))) <= LOOSE
+
+
+@pytest.mark.parametrize("B", [3, 128])
+def test_conv2_gradients_from_pooled_gradient(lib, B):
+    """dgrad / wgrad / bias grad of conv2 with MaxPoolGrad + ReluGrad of pool2 gathered inside the
+    kernels (no dconv2 tensor in HBM), against the oracle's explicit chain."""
+    H = W = 12
+    Cc = 64
+    rng = np.random.default_rng(71)
+    conv = np.maximum(rng.normal(size=(B, H, W, Cc)), 0).astype(np.float32)          # post-ReLU conv2 output
+    pool, arg = rn.maxpool_3x3s2_same(conv)
+    dpool = rng.normal(size=pool.shape).astype(np.float32)
+    x = np.maximum(rng.normal(size=(B, H, W, Cc)), 0).astype(np.float32)             # pool1
+    w = (rng.normal(size=(5, 5, Cc, Cc)) * 0.05).astype(np.float32)
+    dconv = rn.maxpool_3x3s2_same_grad(dpool.astype(np.float64), arg, (H, W)) * (conv > 0)
+    # the kernel adds the (<= 4) window contributions in fp32, in (kh,kw) order, and rounds once to bf16;
+    # the oracle run in fp32 adds in the same order, so the rounded operands agree bit for bit
+    dconv32 = rn.maxpool_3x3s2_same_grad(dpool, arg, (H, W)) * (conv > 0)
+    dconv_r, xr, wr = bf16_round(dconv32), bf16_round(x), bf16_round(w)
+    wd = dev(w)
+    wp = pack_filter(lib, wd, Cc, Cc)
+    dpd, pld, ard, xd = dev(dpool), dev(pool.astype(np.float32)), dev(arg), dev(x)
+    dx = torch.full((B, H, W, Cc), float("nan"), device="cuda")
+    db = torch.zeros(Cc, device="cuda")
+    _lib.check(lib.b200_conv5x5_dgrad_pool_bf16(dpd.data_ptr(), pld.data_ptr(), ard.data_ptr(), wp.data_ptr(),
+                                                dx.data_ptr(), db.data_ptr(), B, H, W, Cc, Cc, stream()))
+    torch.cuda.synchronize()
+    assert relerr(dx.cpu().numpy(), rn.conv2d_same_grad_input(dconv_r, wr)) <= TIGHT
+    assert relerr(db.cpu().numpy(), dconv.sum((0, 1, 2))) <= 1e-5                    # summed in fp32 before rounding
+    nb = C.c_int64()
+    _lib.check(lib.b200_conv5x5_wgrad_bf16_scratch_bytes(B, C.byref(nb)))
+    scr = torch.empty(nb.value, dtype=torch.uint8, device="cuda")
+    dw = torch.full((5, 5, Cc, Cc), float("nan"), device="cuda")
+    _lib.check(lib.b200_conv5x5_wgrad_pool_bf16(xd.data_ptr(), dpd.data_ptr(), pld.data_ptr(), ard.data_ptr(),
+                                                dw.data_ptr(), scr.data_ptr(), nb.value, B, H, W, Cc, Cc, stream()))
+    torch.cuda.synchronize()
+    assert relerr(dw.cpu().numpy(), rn.conv2d_same_grad_filter(xr, dconv_r)) <= TIGHT
+    assert relerr(dw.cpu().numpy(), rn.conv2d_same_grad_filter(x.astype(np.float64), dconv)) <= LOOSE
