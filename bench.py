@@ -160,6 +160,9 @@ def site_work(mode):
         "conv2_fwd": ("tensor", 14_745_600), "conv2_dgrad": ("tensor", 14_745_600),
         "conv2_wgrad": ("tensor", 14_745_600),
         "full1_fwd": ("tensor", 884_736), "full1_bwd": ("tensor", 2 * 884_736),
+        "full1_dw": ("tensor", 884_736), "full1_dx": ("tensor", 884_736),
+        "conv1_pool1_fwd": ("tensor", 2_764_800), "fc_tail": ("tensor", 3 * (73_728 + 1_920)),
+        "weights_prep": ("hbm", 0, 102400 * 6 + 73728 * 6),
         "full2_fwd": ("tensor", 73_728), "full2_bwd": ("tensor", 2 * 73_728),
         "full3_fwd": ("tensor", 1_920), "full3_bwd": ("tensor", 2 * 1_920),
         "crop_cast": ("hbm", 3072 + 1728 * act, 0),
@@ -344,13 +347,17 @@ def main():
         table.append(row)
     table.sort(key=lambda r: -r["ms"])
     dom = table[0]
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):          # dram__bytes_read+write per launch from the committed ncu --set full capture
+        traffic = json.load(open(tpath)).get(dom["site"], {}).get("dram_bytes_per_launch")
     if dom.get("bound") == "tensor":
         roof = {"bound": "tensor", "kernel": dom["site"], "achieved": dom["tflops"], "peak": peaks["tflops_burst"],
-                "unit": "TFLOP/s", "frac": dom["tflops"] / peaks["tflops_burst"], "traffic": None,
+                "unit": "TFLOP/s", "frac": dom["tflops"] / peaks["tflops_burst"], "traffic": traffic,
                 "peak_source": peaks["source"] + " (burst: kernel timed alone)", "kernel_ms": dom["ms"]}
     else:
         roof = {"bound": "hbm", "kernel": dom["site"], "achieved": dom.get("gbs"), "peak": peaks["hbm_gbs"],
-                "unit": "GB/s", "frac": (dom.get("gbs") or 0) / peaks["hbm_gbs"], "traffic": None,
+                "unit": "GB/s", "frac": (dom.get("gbs") or 0) / peaks["hbm_gbs"], "traffic": traffic,
                 "peak_source": peaks["source"], "kernel_ms": dom["ms"]}
 
     # max over ranks
