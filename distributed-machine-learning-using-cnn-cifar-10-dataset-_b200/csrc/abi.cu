@@ -262,12 +262,14 @@ int b200_forward(b200_handle h, const uint8_t* images, const int32_t* labels, vo
   }
   if (tc) {
     if (fork) B200_CUDA_TRY(cudaStreamWaitEvent(st, h->ev_join[0], 0));
-    SITE("conv2_fwd", conv5x5_fwd_tc(pool1, h->ptr<void>("w2_packed"), h->P(P_B2), conv2, c.batch, h->h1, h->w1, c.c1,
-                                     c.c2, 1, st));
+    // conv2 + bias + ReLU + pool2 in one kernel; the un-pooled activations are not needed again (the
+    // backward gathers through pool2 / arg2)
+    SITE("conv2_pool2_fwd", conv5x5_pool_fwd_tc(pool1, h->ptr<void>("w2_packed"), h->P(P_B2), nullptr, pool2,
+                                                h->ptr<uint8_t>("arg2"), c.batch, h->h1, h->w1, c.c1, c.c2, st));
   }
   else
     SITE("conv2_fwd", conv5x5_fwd_f32(pool1, h->P(P_W2), h->P(P_B2), conv2, c.batch, h->h1, h->w1, c.c1, c.c2, 1, st));
-  SITE("pool2_fwd", maxpool_fwd_f32(conv2, pool2, h->ptr<uint8_t>("arg2"), c.batch, h->h1, h->w1, c.c2, st));
+  if (!tc) SITE("pool2_fwd", maxpool_fwd_f32(conv2, pool2, h->ptr<uint8_t>("arg2"), c.batch, h->h1, h->w1, c.c2, st));
   if (tc) {
     // FC1 as a split-K tensor-core product; the tail kernels add the partials, bias and ReLU, run
     // FC2 / FC3 / loss / accuracy and already produce every gradient above FC1 (dfull1, dW2, db2, dW3,
@@ -458,7 +460,7 @@ int b200_launches_per_step(b200_handle h, int32_t* n) {
   if (h->cfg.mode == B200_MODE_BF16) {
     // conv1 (3 or 1), conv2, pool2, FC1 split-K, tail x2 | FC1 bwd x2, pool2 bwd, conv2 wgrad x2, dgrad, conv1 wgrad (2 or 1+4), sgd
     const bool f1 = conv1_tc_supported(h->cfg.crop_h, h->cfg.crop_w, h->cfg.c_in, h->cfg.c1);
-    *n = (f1 ? 1 : 3) + 2 + 1 + 1 + 3 + 2 + 2 + 1 + (f1 ? 2 : 5) + 1;
+    *n = (f1 ? 1 : 3) + 2 + 1 + 3 + 2 + 2 + 1 + (f1 ? 2 : 5) + 1;
   }
   return B200_OK;
 }
@@ -560,6 +562,12 @@ int b200_conv5x5_fwd_bf16(const float* x, const void* w_packed, const float* bia
                           int32_t wd, int32_t c_in, int32_t c_out, int32_t relu, void* stream) {
   B200_REQUIRE(x && w_packed && y, "null pointer");
   return conv5x5_fwd_tc(x, w_packed, bias, y, batch, h, wd, c_in, c_out, relu, (cudaStream_t)stream);
+}
+int b200_conv5x5_pool_fwd_bf16(const float* x, const void* w_packed, const float* bias, float* y, float* pool,
+                               uint8_t* arg, int32_t batch, int32_t h, int32_t wd, int32_t c_in, int32_t c_out,
+                               void* stream) {
+  B200_REQUIRE(x && w_packed && bias && pool && arg, "null pointer");
+  return conv5x5_pool_fwd_tc(x, w_packed, bias, y, pool, arg, batch, h, wd, c_in, c_out, (cudaStream_t)stream);
 }
 int b200_conv5x5_dgrad_bf16(const float* dy, const void* w_packed, float* dx, int32_t batch, int32_t h, int32_t wd,
                             int32_t c_in, int32_t c_out, void* stream) {

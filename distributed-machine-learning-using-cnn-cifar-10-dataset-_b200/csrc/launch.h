@@ -43,6 +43,8 @@ int64_t conv5x5_packed_bytes(int Cin, int Cout);
 int pack_conv_weights(const float* w, void* wp, int Cin, int Cout, cudaStream_t st);
 int conv5x5_fwd_tc(const float* x, const void* wp, const float* bias, float* y, int B, int H, int W, int Cin,
                    int Cout, int relu, cudaStream_t st);
+int conv5x5_pool_fwd_tc(const float* x, const void* wp, const float* bias, float* y, float* pool, uint8_t* arg, int B,
+                        int H, int W, int Cin, int Cout, cudaStream_t st);
 int conv5x5_dgrad_tc(const float* dy, const void* wp, float* dx, int B, int H, int W, int Cin, int Cout,
                      cudaStream_t st);
 // the same two gradients fed by the POOLED gradient: dconv = MaxPoolGrad(dpool, arg) * [pool > 0] is gathered

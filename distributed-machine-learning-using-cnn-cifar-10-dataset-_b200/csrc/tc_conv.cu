@@ -152,6 +152,8 @@ struct ConvArgs {
   PoolGradSrc pg;       // POOL variant: x is unused, the strip is gathered from the pooled gradient
   float* dbias;         // POOL variant: += sum of dconv over pixels per channel (atomics; zero on entry), or null
   float* dconv_out;     // POOL variant: also store dconv as dense [B,H,W,64] fp32 (for the filter gradient), or null
+  float* pool_out;      // forward, ipc == 1, NC == 64: fused 3x3/2 SAME max-pool of the output [B,OH,OW,64] (or null)
+  uint8_t* arg_out;     //   ... and its argmax; y may then be null
 };
 
 // ---------------------------------------------------------------------------------------------------
@@ -241,7 +243,10 @@ __global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
       const int img = r / g.rows_per_img, i = r - img * g.rows_per_img;
       const int n = n_img0 + img;
       const bool valid = (img < g.ipc) && (n < g.B) && (i < g.H) && (c < g.W);
-      float* out = a.y + (((int64_t)n * g.H + i) * g.W + c) * g.NC + nc0;
+      float* out = a.y ? a.y + (((int64_t)n * g.H + i) * g.W + c) * g.NC + nc0 : nullptr;
+      // fused pool: the finished MMAs no longer need the strip, so the fp32 conv tile of the (single) image
+      // goes where the strip was, rows of 68 floats (conflict-free 16-byte stores)
+      float* trow = a.pool_out ? reinterpret_cast<float*>(strip) + (size_t)(i * g.W + c) * 68 : nullptr;
 #pragma unroll 1
       for (int c0 = 0; c0 < BN; c0 += 32) {
         uint32_t v[32];
@@ -258,9 +263,43 @@ __global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
               if (a.relu) xv = fmaxf(xv, 0.f);
               o[e] = xv;
             }
-            *reinterpret_cast<float4*>(out + c0 + j) = make_float4(o[0], o[1], o[2], o[3]);
+            if (out) *reinterpret_cast<float4*>(out + c0 + j) = make_float4(o[0], o[1], o[2], o[3]);
+            if (trow) *reinterpret_cast<float4*>(trow + c0 + j) = make_float4(o[0], o[1], o[2], o[3]);
           }
         }
+      }
+    }
+    if (a.pool_out && n_img0 < g.B) {
+      // ---- 3x3/2 SAME max-pool (pad 0 before / rest after), first max in (h,w) scan order (:123) ------
+      loaders_sync();
+      const float* tile = reinterpret_cast<const float*>(strip);
+      const int OH = (g.H + 1) / 2, OW = (g.W + 1) / 2;
+      const int pbh = max((OH - 1) * 2 + 3 - g.H, 0) / 2, pbw = max((OW - 1) * 2 + 3 - g.W, 0) / 2;
+      for (int q = tid; q < OH * OW * 16; q += LOADERS) {
+        const int cq = q & 15, cell = q >> 4;
+        const int oh = cell / OW, ow = cell - oh * OW;
+        float best[4];
+        int bi[4] = {0, 0, 0, 0};
+        bool any = false;
+#pragma unroll
+        for (int kh = 0; kh < 3; ++kh) {
+          const int hh = 2 * oh + kh - pbh;
+          if ((unsigned)hh >= (unsigned)g.H) continue;
+#pragma unroll
+          for (int kw = 0; kw < 3; ++kw) {
+            const int ww = 2 * ow + kw - pbw;
+            if ((unsigned)ww >= (unsigned)g.W) continue;
+            const float4 v = *reinterpret_cast<const float4*>(tile + (size_t)(hh * g.W + ww) * 68 + cq * 4);
+            const float vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+              if (!any || vv[e] > best[e]) { best[e] = vv[e]; bi[e] = kh * 3 + kw; }
+            any = true;
+          }
+        }
+        const size_t o = ((size_t)n_img0 * OH * OW + cell) * 64 + cq * 4;
+        *reinterpret_cast<float4*>(a.pool_out + o) = make_float4(best[0], best[1], best[2], best[3]);
+        *reinterpret_cast<uchar4*>(a.arg_out + o) = make_uchar4(bi[0], bi[1], bi[2], bi[3]);
       }
     }
     if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) a.timeline[6] = clock64();
@@ -370,14 +409,19 @@ long long* g_conv_timeline = nullptr;
 template <bool DGRAD>
 int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, int B, int H, int W, int KC, int NC,
                 int relu, cudaStream_t st, const PoolGradSrc* pg = nullptr, float* dbias = nullptr,
-                float* dconv_out = nullptr) {
+                float* dconv_out = nullptr, float* pool_out = nullptr, uint8_t* arg_out = nullptr) {
   B200_REQUIRE(B > 0 && H > 0 && W > 0, "conv5x5_tc: bad shape");
   B200_REQUIRE(KC % 16 == 0 && NC % 64 == 0, "conv5x5_tc: channels must be multiples of 16 (in) / 64 (out), got %d/%d",
                KC, NC);
+  B200_REQUIRE(y || pool_out, "conv5x5_tc: no output");
   B200_REQUIRE((pg || ((uintptr_t)x & 15) == 0) && ((uintptr_t)wp & 15) == 0 && ((uintptr_t)y & 15) == 0,
                "conv5x5_tc: pointers must be 16-byte aligned");
-  int ipc = pick_ipc(B, H, W, KC);
+  int ipc = pool_out ? 1 : pick_ipc(B, H, W, KC);       // the fused pool works on one image per CTA
   ConvGeom g = make_geom(B, H, W, KC, NC, ipc);
+  if (pool_out) {
+    B200_REQUIRE(!DGRAD && NC == 64 && arg_out, "conv5x5_tc: fused pool needs the forward kernel with 64 output channels");
+    B200_REQUIRE((int64_t)H * W * 68 * 4 <= (int64_t)(KC / 8) * g.ch_stride, "conv5x5_tc: conv tile does not fit the strip");
+  }
   B200_REQUIRE(g.tiles * 64 <= 512, "conv5x5_tc: image %dx%d too large for one CTA's TMEM", H, W);
   const int kchunks = KC / 8;
   const int wstage = ((DGRAD ? kchunks * (64 * 16 + 16) : 8 * (KC * 16 + 16)) + 127) & ~127;
@@ -397,7 +441,7 @@ int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, 
     default: B200_REQUIRE(false, "conv5x5_tc: contraction channels must be 32, 64, 128 or 256 (got %d)", KC);
   }
   B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-  ConvArgs a{x, wp, DGRAD ? NC : KC, DGRAD ? KC : NC, bias, y, relu, g, g_conv_timeline, pg ? *pg : PoolGradSrc{}, dbias, dconv_out};
+  ConvArgs a{x, wp, DGRAD ? NC : KC, DGRAD ? KC : NC, bias, y, relu, g, g_conv_timeline, pg ? *pg : PoolGradSrc{}, dbias, dconv_out, pool_out, arg_out};
   dim3 grid(cdiv(B, ipc), NC / 64);
   kern<<<grid, 288, smem, st>>>(a);
   B200_LAUNCH_CHECK();
@@ -568,6 +612,11 @@ int pack_conv_weights(const float* w, void* wp, int Cin, int Cout, cudaStream_t 
 int conv5x5_fwd_tc(const float* x, const void* wp, const float* bias, float* y, int B, int H, int W, int Cin,
                    int Cout, int relu, cudaStream_t st) {
   return launch_conv<false>(x, (const uint8_t*)wp, bias, y, B, H, W, Cin, Cout, relu, st);
+}
+// conv + bias + ReLU + 3x3/2 SAME max-pool in one kernel; y (the un-pooled activations) is optional
+int conv5x5_pool_fwd_tc(const float* x, const void* wp, const float* bias, float* y, float* pool, uint8_t* arg, int B,
+                        int H, int W, int Cin, int Cout, cudaStream_t st) {
+  return launch_conv<false>(x, (const uint8_t*)wp, bias, y, B, H, W, Cin, Cout, 1, st, nullptr, nullptr, nullptr, pool, arg);
 }
 // dx = Conv2DBackpropInput(dy, w): contraction over the forward Cout, output the forward Cin
 int conv5x5_dgrad_tc(const float* dy, const void* wp, float* dx, int B, int H, int W, int Cin, int Cout,

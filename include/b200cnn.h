@@ -174,6 +174,11 @@ int b200_conv5x5_packed_bytes(int32_t c_in, int32_t c_out, int64_t* nbytes);
 int b200_conv5x5_pack_weights(const float* w, void* w_packed, int32_t c_in, int32_t c_out, void* stream);
 int b200_conv5x5_fwd_bf16(const float* x, const void* w_packed, const float* bias, float* y, int32_t batch, int32_t h,
                           int32_t wd, int32_t c_in, int32_t c_out, int32_t relu, void* stream);
+/* conv + bias + ReLU (:118-121) fused with the 3x3/2 SAME max-pool that follows (:123): pool [batch,ceil(h/2),
+ * ceil(wd/2),64] and its argmax; y (un-pooled) may be NULL.  64 output channels, one image per CTA. */
+int b200_conv5x5_pool_fwd_bf16(const float* x, const void* w_packed, const float* bias, float* y, float* pool,
+                               uint8_t* arg, int32_t batch, int32_t h, int32_t wd, int32_t c_in, int32_t c_out,
+                               void* stream);
 int b200_conv5x5_dgrad_bf16(const float* dy, const void* w_packed, float* dx, int32_t batch, int32_t h, int32_t wd,
                             int32_t c_in, int32_t c_out, void* stream);
 int b200_conv5x5_wgrad_bf16_scratch_bytes(int32_t batch, int64_t* nbytes);

@@ -203,16 +203,18 @@ def _oracle_backward_on_gpu_forward(e, params, labels, a_ref, fused_conv1=False)
     (2) the GPU's argmax is exactly the first-max of the GPU's own conv output (checked here,
     bit-exact), (3) gradients match the oracle's backward evaluated on the GPU's forward tensors."""
     a = {"x": a_ref["x"]}
-    names = ("pool1", "conv2", "pool2", "full1", "full2", "logits") if fused_conv1 else \
+    names = ("pool1", "pool2", "full1", "full2", "logits") if fused_conv1 else \
         ("conv1", "pool1", "conv2", "pool2", "full1", "full2", "logits")
     for name in names:
         a[name] = e.tensor(name).cpu().numpy().astype(np.float64).reshape(a_ref[name].shape)
     if fused_conv1:
         # conv1 never reaches HBM in the fused kernel (its own test checks the pool rule on a debug
         # copy); backward only needs its sign at the selected cells, which is the sign of pool1
-        a["arg1"] = e.tensor("arg1").cpu().numpy().reshape(a_ref["arg1"].shape)
-        a["conv1"] = rn.maxpool_3x3s2_same_grad(a["pool1"], a["arg1"], a_ref["conv1"].shape[1:3])
-    for name, src in (("arg2", "conv2"),) if fused_conv1 else (("arg1", "conv1"), ("arg2", "conv2")):
+        # (the same holds for conv2, fused with pool2)
+        for k in ("1", "2"):
+            a["arg" + k] = e.tensor("arg" + k).cpu().numpy().reshape(a_ref["arg" + k].shape)
+            a["conv" + k] = rn.maxpool_3x3s2_same_grad(a["pool" + k], a["arg" + k], a_ref["conv" + k].shape[1:3])
+    for name, src in () if fused_conv1 else (("arg1", "conv1"), ("arg2", "conv2")):
         a[name] = e.tensor(name).cpu().numpy().reshape(a_ref[name].shape)
         y, arg = rn.maxpool_3x3s2_same(a[src])
         np.testing.assert_array_equal(a[name], arg)                   # first-max rule on its own values

@@ -188,7 +188,7 @@ def test_full_step_bf16_mode_b128(kind):
     e.forward(dev(img), dev(lab.reshape(-1)))
     e.backward()
     torch.cuda.synchronize()
-    for name in ("pool1", "conv2", "pool2", "full1", "full2", "logits"):
+    for name in ("pool1", "pool2", "full1", "full2", "logits"):
         assert relerr(e.tensor(name).cpu().numpy().reshape(a[name].shape), a[name]) <= LOOSE, name
     assert abs(float(e.loss()) - loss) <= 2e-2 * abs(loss)
     srt = np.sort(a["logits"], axis=1)
@@ -290,3 +290,32 @@ def test_conv2_gradients_from_pooled_gradient(lib, B):
     torch.cuda.synchronize()
     assert relerr(dw.cpu().numpy(), rn.conv2d_same_grad_filter(xr, dconv_r)) <= TIGHT
     assert relerr(dw.cpu().numpy(), rn.conv2d_same_grad_filter(x.astype(np.float64), dconv)) <= LOOSE
+
+
+@pytest.mark.parametrize("B", [2, 128, 300])
+def test_conv2_pool2_fused_forward(lib, B):
+    """conv2 + bias + ReLU + pool2 (cifar10cnn.py:118-123) in one kernel: the conv values against the
+    oracle, and TF's pooling rule applied bit-exactly to the kernel's own conv values."""
+    H = W = 12
+    Cc = 64
+    rng = np.random.default_rng(81)
+    x = np.maximum(rng.normal(size=(B, H, W, Cc)), 0).astype(np.float32)
+    w = (rng.normal(size=(5, 5, Cc, Cc)) * 0.05).astype(np.float32)
+    b = (rng.normal(size=(Cc,)) * 0.3).astype(np.float32)
+    xd, wd, bd = dev(x), dev(w), dev(b)
+    wp = pack_filter(lib, wd, Cc, Cc)
+    y = torch.full((B, H, W, Cc), float("nan"), device="cuda")
+    pool = torch.full((B, 6, 6, Cc), float("nan"), device="cuda")
+    arg = torch.full((B, 6, 6, Cc), 255, dtype=torch.uint8, device="cuda")
+    _lib.check(lib.b200_conv5x5_pool_fwd_bf16(xd.data_ptr(), wp.data_ptr(), bd.data_ptr(), y.data_ptr(), pool.data_ptr(),
+                                              arg.data_ptr(), B, H, W, Cc, Cc, stream()))
+    torch.cuda.synchronize()
+    assert relerr(y.cpu().numpy(), np.maximum(rn.conv2d_same(bf16_round(x), bf16_round(w)) + b, 0)) <= TIGHT
+    wy, warg = rn.maxpool_3x3s2_same(y.cpu().numpy())
+    np.testing.assert_array_equal(pool.cpu().numpy(), wy)
+    np.testing.assert_array_equal(arg.cpu().numpy(), warg)
+    pool2 = torch.empty_like(pool); arg2 = torch.empty_like(arg)
+    _lib.check(lib.b200_conv5x5_pool_fwd_bf16(xd.data_ptr(), wp.data_ptr(), bd.data_ptr(), None, pool2.data_ptr(),
+                                              arg2.data_ptr(), B, H, W, Cc, Cc, stream()))
+    torch.cuda.synchronize()
+    assert torch.equal(pool, pool2) and torch.equal(arg, arg2)
