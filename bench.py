@@ -182,6 +182,8 @@ def main():
     ap.add_argument("--batch", type=int, default=128)
     ap.add_argument("--mode", default=os.environ.get("B200CNN_MODE", "auto"), choices=["auto", "fp32", "bf16"])
     ap.add_argument("--reduce", default="sum", choices=["sum", "mean"])
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
+                    help="N>1: fused peer-memory allreduce+SGD kernel (default) or NCCL allreduce + SGD kernel")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--sites-json", default=None, help="also write the per-site timing table here")
@@ -211,10 +213,24 @@ def main():
     lr = 0.1
     peaks = load_peaks()
 
-    eng = b200cnn.TrainStepEngine(batch=B, mode=mode, device=local)
+    ex, exchange = None, "none"
+    if world > 1 and args.exchange == "p2p":
+        try:
+            total = b200cnn.TrainStepEngine(batch=8, mode="fp32", device=local).total
+            ex = b200cnn.P2PExchange(total, torch.device("cuda", local), reduce=args.reduce)
+            exchange = "p2p-fused" + ("-nvls" if ex.multicast else "")
+        except Exception as e:          # no symmetric memory on this box: fall back to NCCL (still all CUDA)
+            if rank == 0:
+                print(f"P2P exchange unavailable ({type(e).__name__}: {e}); using NCCL", file=sys.stderr)
+            ex = None
+    if ex is None:
+        ex = b200cnn.GradientExchange(reduce=args.reduce)
+        exchange = "nccl" if world > 1 else "none"
+    fused = isinstance(ex, b200cnn.P2PExchange)
+    eng = b200cnn.TrainStepEngine(batch=B, mode=mode, device=local, params=ex.params if fused else None,
+                                  grads=ex.grads if fused else None)
     eng.init_params(0)
     params0 = eng.params.clone()
-    ex = b200cnn.GradientExchange(reduce=args.reduce)
     ex.broadcast_params_(eng.params)
 
     rng = np.random.default_rng(1234 + rank)
@@ -237,6 +253,12 @@ def main():
         else:
             eng.forward(s_img, s_lab)
             eng.backward()
+            exchange_and_update()
+
+    def exchange_and_update():
+        if fused:
+            ex.apply_(eng, lr)                       # one kernel: allreduce over peer memory + SGD
+        else:
             ex.allreduce_(eng.grads)
             eng.sgd_apply(lr, ex.grad_scale)
 
@@ -249,8 +271,7 @@ def main():
                 s_lab.copy_(lab, non_blocking=True)
                 eng.forward(s_img, s_lab)
                 eng.backward()
-                ex.allreduce_(eng.grads)
-                eng.sgd_apply(lr, ex.grad_scale)
+                exchange_and_update()
                 out.copy_(eng.loss(), non_blocking=True)
         return fn
 
@@ -378,7 +399,7 @@ def main():
             "warmup": W, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32" if mode == "fp32" else "bf16", "data": "synthetic",
             "config": {"workload": workload_name(args), "batch_per_gpu": B, "global_batch": B * world,
-                       "mode": mode, "parallelism": f"dp{world}", "reduce": args.reduce,
+                       "mode": mode, "parallelism": f"dp{world}", "reduce": args.reduce, "exchange": exchange,
                        "l2": "flushed between timed steps (256 MiB memset, untimed); per-step CUDA events summed",
                        "cuda_graph": True},
             "value_hot_l2": imgs / (ms_hot * 1e-3),

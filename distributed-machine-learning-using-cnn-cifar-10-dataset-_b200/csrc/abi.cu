@@ -387,6 +387,19 @@ int b200_sgd_apply(b200_handle h, float lr, float grad_scale, void* stream) {
   return B200_OK;
 }
 
+int b200_p2p_sgd_apply(b200_handle h, const void* const* peer_grads, void* const* peer_params, void* const* peer_pads,
+                       const void* mc_grads, void* mc_params, uint32_t* state, int32_t rank, int32_t world, float lr,
+                       float grad_scale, void* stream) {
+  B200_READY(h);
+  B200_REQUIRE(peer_grads && peer_params && rank >= 0 && rank < world && world <= 8, "p2p_sgd_apply: bad argument");
+  B200_REQUIRE(peer_grads[rank] == h->grads && peer_params[rank] == h->params,
+               "p2p_sgd_apply: entry `rank` of the peer tables must be the buffers bound to this handle");
+  cudaStream_t st = (cudaStream_t)stream;
+  SITE("p2p_sgd_apply", p2p_allreduce_sgd(peer_grads, peer_params, peer_pads, mc_grads, mc_params, state, rank, world,
+                                          h->p_total, lr, grad_scale, st));
+  return B200_OK;
+}
+
 int b200_train_step(b200_handle h, const uint8_t* images, const int32_t* labels, float lr, void* stream) {
   TRY(b200_forward(h, images, labels, stream));
   TRY(b200_backward(h, stream));

@@ -67,6 +67,10 @@ int fc_tail(const float* fc1_part, int n_part, const float* b1, float* full1, co
             float* db2, float* dw3, float* db3, float* db1, void* scratch, float* zero_ptr, int zero_n, int B, int F1,
             int F2, int NC, cudaStream_t st, bool w2_image_ready = false);
 int fc_tail_prepare_w2(const float* w2, void* scratch, int B, int F1, int F2, int NC, cudaStream_t st);
+// allreduce + SGD in one kernel over NVLink peer memory (p2p_update.cu)
+int p2p_allreduce_sgd(const void* const* peer_grads, void* const* peer_params, void* const* peer_pads,
+                      const void* mc_grads, void* mc_params, uint32_t* state, int rank, int world, int64_t total,
+                      float lr, float scale, cudaStream_t st);
 bool conv1_tc_supported(int H, int W, int c_in, int c1);
 int conv1_pool_fwd_tc(const uint8_t* img, const float* w, const float* bias, float* pool, uint8_t* arg,
                       float* conv_dbg, int B, int ih, int iw, int H, int W, cudaStream_t st);

@@ -1,0 +1,152 @@
+// The parameter-server push/apply of cifar10cnn.py (:162-163 executed on /job:ps, :195-196) as ONE kernel per
+// GPU over NVLink peer memory: all-reduce of the flat gradient buffer fused with the SGD update.
+//
+// Every rank owns the shard [rank*S, (rank+1)*S) of the flat parameter vector.  Its kernel
+//   A. waits until every peer has published "my gradients of this step are complete",
+//   1. sums the shard's gradients over all ranks   -- direct NVLink loads from the peers' buffers, or one
+//      multimem.ld_reduce per 16 bytes when the buffers have an NVSwitch multicast mapping (the switch adds),
+//   2. applies  w -= lr * scale * sum  to its shard (fp32 master weights),
+//   3. writes the updated shard into EVERY rank's parameter buffer (peer stores, or one multimem.st),
+//   B. publishes "done" and waits for every peer's "done": after that all gradients may be overwritten and
+//      all parameter buffers are complete and identical.
+// Transfers per rank: 2*(N-1)/N of 4.27 MB (NVLS: 2/N), two flag round trips; no separate update launch, no
+// NCCL call.  Flags live in each rank's signal pad (symmetric memory); the step number is a device-side
+// epoch counter, so the launch is identical every step and can sit in a CUDA graph.
+//
+// Buffers (gradients, parameters, pads) must be peer-mapped symmetric allocations of the same size on all
+// ranks; torch.distributed._symmetric_memory provides them (plumbing), see exchange.P2PExchange.
+#include <algorithm>
+
+#include "launch.h"
+
+namespace b200 {
+namespace {
+constexpr int kMaxRanks = 8;
+
+struct P2PArgs {
+  const float* grads[kMaxRanks];    // every rank's flat gradient buffer (index = rank)
+  float* params[kMaxRanks];         // every rank's flat parameter buffer
+  uint32_t* pads[kMaxRanks];        // every rank's flag pad: [0,8) "ready" slots, [8,16) "done" slots
+  const float* mc_grads;            // multicast mapping of the gradient buffers, or null
+  float* mc_params;                 // multicast mapping of the parameter buffers, or null
+  uint32_t* state;                  // local: [0] epoch, [1] CTA arrival counter
+  int rank, world;
+  int64_t total;                    // floats, divisible by 4 * world
+  float step;                       // lr * scale
+};
+
+__device__ __forceinline__ void st_flag(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_flag(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+// bounded: a lost peer must fault this launch, not hang the GPU
+__device__ __forceinline__ void wait_flag(const uint32_t* p, uint32_t epoch) {
+  const long long t0 = clock64();
+  while ((int32_t)(ld_flag(p) - epoch) < 0) {
+    if (clock64() - t0 > 8000000000ll) {
+      printf("b200cnn: peer flag wait timed out (block %d thread %d)\n", (int)blockIdx.x, (int)threadIdx.x);
+      __trap();
+    }
+  }
+}
+__device__ __forceinline__ float4 mc_ld_reduce(const float* p) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void mc_st(float* p, const float4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z),
+               "f"(v.w)
+               : "memory");
+}
+
+__global__ void __launch_bounds__(512) p2p_allreduce_sgd_kernel(P2PArgs a) {
+  const int tid = threadIdx.x;
+  const uint32_t epoch = a.state[0] + 1;          // read by everyone before the last CTA bumps it at the very end
+  // ---- A: gradients of all ranks complete ------------------------------------------------------------
+  if (blockIdx.x == 0 && tid < a.world) {
+    __threadfence_system();
+    st_flag(a.pads[tid] + a.rank, epoch);         // "rank `a.rank` is ready", written into peer tid's pad
+  }
+  if (tid < a.world) wait_flag(a.pads[a.rank] + tid, epoch);
+  __syncthreads();
+  // ---- 1-3: reduce my shard, update, broadcast -----------------------------------------------------------
+  const int64_t shard4 = a.total / 4 / a.world;
+  const int64_t beg4 = (int64_t)a.rank * shard4;
+  const bool nvls = a.mc_grads != nullptr && a.mc_params != nullptr;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + tid; i < shard4; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t o = (beg4 + i) * 4;
+    float4 g;
+    if (nvls) {
+      g = mc_ld_reduce(a.mc_grads + o);
+    } else {
+      float4 v[kMaxRanks];
+#pragma unroll
+      for (int p = 0; p < kMaxRanks; ++p)
+        if (p < a.world) v[p] = *reinterpret_cast<const float4*>(a.grads[p] + o);     // all peer loads in flight
+      g = v[0];
+#pragma unroll
+      for (int p = 1; p < kMaxRanks; ++p)
+        if (p < a.world) { g.x += v[p].x; g.y += v[p].y; g.z += v[p].z; g.w += v[p].w; }   // rank order: same on all ranks
+    }
+    float4 w = *reinterpret_cast<const float4*>(a.params[a.rank] + o);
+    w.x = fmaf(-a.step, g.x, w.x); w.y = fmaf(-a.step, g.y, w.y);
+    w.z = fmaf(-a.step, g.z, w.z); w.w = fmaf(-a.step, g.w, w.w);
+    if (nvls) {
+      mc_st(a.mc_params + o, w);
+    } else {
+#pragma unroll
+      for (int p = 0; p < kMaxRanks; ++p)
+        if (p < a.world) *reinterpret_cast<float4*>(a.params[p] + o) = w;
+    }
+  }
+  // ---- B: everybody done ------------------------------------------------------------------------------------
+  __threadfence_system();
+  __syncthreads();
+  __shared__ bool last;
+  if (tid == 0) last = atomicAdd(a.state + 1, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (last) {
+    if (tid < a.world) {
+      __threadfence_system();
+      st_flag(a.pads[tid] + 8 + a.rank, epoch);
+      wait_flag(a.pads[a.rank] + 8 + tid, epoch);
+    }
+    __syncthreads();
+    if (tid == 0) { a.state[1] = 0; a.state[0] = epoch; }
+  }
+}
+}  // namespace
+
+int p2p_allreduce_sgd(const void* const* peer_grads, void* const* peer_params, void* const* peer_pads,
+                      const void* mc_grads, void* mc_params, uint32_t* state, int rank, int world, int64_t total,
+                      float lr, float scale, cudaStream_t st) {
+  B200_REQUIRE(world >= 1 && world <= kMaxRanks && rank >= 0 && rank < world, "p2p_allreduce_sgd: bad rank %d / world %d",
+               rank, world);
+  B200_REQUIRE(total > 0 && total % (4 * world) == 0, "p2p_allreduce_sgd: %lld floats do not split into %d 16-byte shards",
+               (long long)total, world);
+  B200_REQUIRE(peer_grads && peer_params && peer_pads && state, "p2p_allreduce_sgd: null argument");
+  P2PArgs a{};
+  for (int p = 0; p < world; ++p) {
+    B200_REQUIRE(peer_grads[p] && peer_params[p] && peer_pads[p], "p2p_allreduce_sgd: null peer pointer for rank %d", p);
+    a.grads[p] = (const float*)peer_grads[p];
+    a.params[p] = (float*)peer_params[p];
+    a.pads[p] = (uint32_t*)peer_pads[p];
+  }
+  a.mc_grads = (const float*)mc_grads; a.mc_params = (float*)mc_params;
+  a.state = state; a.rank = rank; a.world = world; a.total = total; a.step = lr * scale;
+  const int64_t shard4 = total / 4 / world;
+  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(kNumSMs, (shard4 + 511) / 512));
+  p2p_allreduce_sgd_kernel<<<grid, 512, 0, st>>>(a);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+}  // namespace b200

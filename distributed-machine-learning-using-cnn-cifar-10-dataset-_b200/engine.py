@@ -32,7 +32,7 @@ def _require_cuda():
 
 class TrainStepEngine:
     def __init__(self, batch=128, img_hw=(32, 32), crop_hw=(24, 24), c_in=3, c1=64, c2=64, f1=384,
-                 f2=192, n_cls=10, mode="fp32", device=None, params=None):
+                 f2=192, n_cls=10, mode="fp32", device=None, params=None, grads=None):
         _require_cuda()
         self.lib = _lib.load()
         self.device = torch.device("cuda", torch.cuda.current_device() if device is None else device)
@@ -61,7 +61,12 @@ class TrainStepEngine:
             self.params = params
         else:
             self.params = torch.zeros(self.total, dtype=torch.float32, device=self.device)
-        self.grads = torch.zeros(self.total, dtype=torch.float32, device=self.device)
+        if grads is not None:       # e.g. a peer-mapped symmetric buffer (exchange.P2PExchange)
+            if grads.numel() != self.total or grads.device != self.device or grads.dtype != torch.float32:
+                raise ValueError("gradient buffer does not match this engine")
+            self.grads = grads
+        else:
+            self.grads = torch.zeros(self.total, dtype=torch.float32, device=self.device)
         nb = C.c_int64()
         check(self.lib.b200_workspace_bytes(h, C.byref(nb)))
         self.workspace = torch.zeros(nb.value + 256, dtype=torch.uint8, device=self.device)

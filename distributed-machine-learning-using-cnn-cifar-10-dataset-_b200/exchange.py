@@ -58,3 +58,54 @@ class GradientExchange:
         dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=self.group)
         dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=self.group)
         return bool((lo == hi).all())
+
+
+class P2PExchange(GradientExchange):
+    """The same exchange as ONE kernel per GPU over NVLink peer memory (csrc/p2p_update.cu): the all-reduce
+    of the flat gradient buffer is fused with the SGD update and the updated shard is written straight into
+    every worker's parameter buffer -- no NCCL call, no separate update launch.  With an NVSwitch multicast
+    mapping the switch does the additions (multimem.ld_reduce / multimem.st).
+
+    torch.distributed._symmetric_memory is the plumbing: it allocates the peer-mapped gradient / parameter
+    buffers and exchanges their addresses.  Usage: create it first, build the engine on `self.params` /
+    `self.grads` (TrainStepEngine(params=..., grads=...)), then call apply_(engine, lr) once per step on
+    every worker."""
+
+    def __init__(self, total_floats, device, reduce="sum", group=None, use_multicast=True):
+        super().__init__(reduce=reduce, group=group)
+        if self.world < 2:
+            raise ValueError("P2PExchange needs an initialised process group with at least 2 workers")
+        if self.world > 8 or total_floats % (4 * self.world):
+            raise ValueError("P2PExchange supports 2..8 workers and sizes divisible by 4*world")
+        import ctypes as C
+        import torch.distributed._symmetric_memory as symm_mem
+        grp = group if group is not None else dist.group.WORLD
+        self.grads = symm_mem.empty(total_floats, dtype=torch.float32, device=device)
+        self.params = symm_mem.empty(total_floats, dtype=torch.float32, device=device)
+        self.grads.zero_()
+        self.params.zero_()
+        self._hg = symm_mem.rendezvous(self.grads, grp)
+        self._hp = symm_mem.rendezvous(self.params, grp)
+        n = self.world
+        arr = C.c_void_p * n
+        self._peer_grads = arr(*[int(x) for x in self._hg.buffer_ptrs])
+        self._peer_params = arr(*[int(x) for x in self._hp.buffer_ptrs])
+        # flags: a private corner of the gradient handle's signal pads (torch's own barrier uses the start)
+        off = 2048
+        if self._hg.signal_pad_size < off + 64:
+            raise RuntimeError("signal pad too small")
+        self._peer_pads = arr(*[int(x) + off for x in self._hg.signal_pad_ptrs])
+        mc_ok = use_multicast and self._hg.has_multicast_support and self._hp.has_multicast_support
+        self.multicast = bool(mc_ok and self._hg.multicast_ptr and self._hp.multicast_ptr)
+        self._mc_grads = int(self._hg.multicast_ptr) if self.multicast else None
+        self._mc_params = int(self._hp.multicast_ptr) if self.multicast else None
+        self._state = torch.zeros(2, dtype=torch.int32, device=device)
+        torch.cuda.synchronize(device)
+        dist.barrier(group=group)
+
+    def apply_(self, engine, lr):
+        """allreduce + update in one launch on the current stream (replaces allreduce_ + engine.sgd_apply)."""
+        from ._lib import check
+        check(engine.lib.b200_p2p_sgd_apply(engine.h, self._peer_grads, self._peer_params, self._peer_pads,
+                                            self._mc_grads, self._mc_params, self._state.data_ptr(), self.rank,
+                                            self.world, lr, self.grad_scale, torch.cuda.current_stream().cuda_stream))

@@ -85,6 +85,17 @@ int b200_backward(b200_handle h, void* stream);
 /* ApplyGradientDescent x10 (:162-163): params -= lr * grad_scale * grads.  grad_scale = 1 for a
  * single worker or a SUM allreduce, 1/world for a MEAN allreduce. */
 int b200_sgd_apply(b200_handle h, float lr, float grad_scale, void* stream);
+/* The ps push/apply for world > 1 as ONE kernel per GPU over NVLink peer memory: all-reduce (sum) of the flat
+ * gradient buffers of all workers fused with the update params -= lr * grad_scale * sum, written into every
+ * worker's parameter buffer.  peer_grads / peer_params / peer_pads: host arrays of `world` device pointers
+ * (entry i = worker i; entry `rank` = the buffers bound to this handle); all must be peer-mapped symmetric
+ * allocations of the padded parameter size (pads: >= 64 B of zero-initialised uint32 flags per worker).
+ * mc_grads / mc_params: NVSwitch multicast mappings of the same buffers, or NULL (then plain peer loads /
+ * stores).  state: 8 zero-initialised bytes of local device memory.  Every worker must launch it once per
+ * step; the kernels wait for one another (bounded), so all `world` GPUs must be running. */
+int b200_p2p_sgd_apply(b200_handle h, const void* const* peer_grads, void* const* peer_params, void* const* peer_pads,
+                       const void* mc_grads, void* mc_params, uint32_t* state, int32_t rank, int32_t world, float lr,
+                       float grad_scale, void* stream);
 /* forward + backward + sgd_apply: one `mon_sess.run([train_op, loss])` (:230) for world == 1. */
 int b200_train_step(b200_handle h, const uint8_t* images, const int32_t* labels, float lr, void* stream);
 /* The same call with HOST (pinned) inputs and a host loss: copies the records and labels to
