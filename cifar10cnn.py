@@ -114,11 +114,13 @@ def run_worker(flags, ps_hosts, worker_hosts):
     train_op = train_step(loss, generation_num)
 
     with session.MonitoredTrainingSession(is_chief=(flags.task_index == 0), last_step=flags.max_steps,
-                                          reduce=flags.reduce) as mon_sess:
+                                          reduce=flags.reduce, checkpoint_dir=flags.log_dir) as mon_sess:
         i = 0
         print('Starting Training')
         while not mon_sess.should_stop():
             _, loss_value = mon_sess.run([train_op, loss])
+            if loss_value is None:          # restored checkpoint already at the last step
+                break
             if (i + 1) % OUTPUT_EVERY == 0:
                 print('global_step %s, task:%d_step %d, training accuracy %g'
                       % (mon_sess.global_step, flags.task_index, i, mon_sess.run([accuracy_train])[0]))

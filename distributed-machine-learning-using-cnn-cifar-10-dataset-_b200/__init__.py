@@ -11,4 +11,4 @@ SMOKE_MODES = (("fp32", 2e-5), ("bf16", 5e-2))
 from .exchange import GradientExchange, P2PExchange  # noqa: E402,F401
 # mode bench.py and the CLI use unless told otherwise
 DEFAULT_MODE = "bf16"
-from . import data, roles, session  # noqa: E402,F401
+from . import checkpoint, data, roles, session  # noqa: E402,F401

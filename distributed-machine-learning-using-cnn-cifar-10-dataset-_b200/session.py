@@ -8,6 +8,7 @@ from __future__ import annotations
 import numpy as np
 import torch
 
+from . import checkpoint
 from .data import BatchSource
 from .engine import TrainStepEngine
 from .exchange import GradientExchange
@@ -88,18 +89,38 @@ class MonitoredTrainingSession:
     counts WORKER updates like the reference's shared counter: one allreduce round applies
     `world` of them."""
 
-    def __init__(self, is_chief=True, last_step=20000, reduce="sum"):
+    def __init__(self, is_chief=True, last_step=20000, reduce="sum", checkpoint_dir=None, save_secs=600.0):
         self.is_chief = is_chief
         self.last_step = last_step
         self.exchange = GradientExchange(reduce=reduce)
         self.global_step = 0
         self._synced = False
+        self._engine = None
+        self._saver = checkpoint.Saver(checkpoint_dir, save_secs) if (is_chief and checkpoint_dir) else None
+        self._restore_from = checkpoint.latest(checkpoint_dir) if (is_chief and checkpoint_dir) else None
 
     def __enter__(self):
         return self
 
-    def __exit__(self, *exc):
+    def __exit__(self, exc_type, *exc):
+        if exc_type is None and self._saver and self._engine is not None:
+            self._saver.maybe_save(self._engine, self.global_step, force=True)       # final checkpoint, like TF
         return False
+
+    def _first_sync(self, eng):
+        """chief restores the newest checkpoint (or keeps its fresh init) and publishes variables and
+        global_step to the other workers (:222)."""
+        if self._restore_from:
+            params, step = checkpoint.load(self._restore_from)
+            eng.load_params(params)
+            self.global_step = step
+        self.exchange.broadcast_params_(eng.params)
+        gs = torch.tensor([self.global_step], dtype=torch.int64, device=eng.params.device)
+        if self.exchange.world > 1:
+            import torch.distributed as dist
+            dist.broadcast(gs, src=0)
+        self.global_step = int(gs.item())
+        self._synced = True
 
     def should_stop(self):
         return self.global_step >= self.last_step
@@ -120,15 +141,19 @@ class MonitoredTrainingSession:
         if train:
             op = train[0]
             eng = op.loss.logits.engine
+            self._engine = eng
             if not self._synced:
-                self.exchange.broadcast_params_(eng.params)      # chief publishes the initial variables (:222)
-                self._synced = True
+                self._first_sync(eng)
+                if self.should_stop():
+                    return None if single else [None] * len(items)
             self._forward(op.loss.logits, op.loss.labels)
             eng.backward()
             self.exchange.allreduce_(eng.grads)
             eng.sgd_apply(op.learning_rate(), self.exchange.grad_scale)
             self.global_step += self.exchange.global_step_increment
             done[id(op.loss.logits)] = eng
+            if self._saver:
+                self._saver.maybe_save(eng, self.global_step)
         for i, f in enumerate(items):
             if isinstance(f, TrainOp):
                 continue

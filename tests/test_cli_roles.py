@@ -144,3 +144,24 @@ def test_two_workers_and_ps_over_gloo(reduce):
             np.testing.assert_allclose(got[k], want[k], rtol=1e-12, atol=1e-14)
         assert r[3] is True and r[4] == 2                        # replicas identical; global_step += world
     np.testing.assert_array_equal(res[0][2], res[1][2])
+
+
+def test_checkpoint_names_and_roundtrip(tmp_path):
+    """--log_dir contract (cifar10cnn.py:222): files keyed by the TF variable names, newest one restored."""
+    from b200cnn import checkpoint
+    from oracle import ref_numpy as rn
+    names = checkpoint.variable_names()
+    assert names[0] == "model_definition/conv1/conv1_kernel" and names[4] == "model_definition/full1/full_weight_1"
+    assert names[-1] == "model_definition/full3/full_bias_3" and len(names) == 10
+    p = rn.init_params(0)
+    assert checkpoint.latest(str(tmp_path)) is None
+    checkpoint.save(str(tmp_path), p, 200)
+    p2 = {k: v + 1 for k, v in p.items()}
+    path = checkpoint.save(str(tmp_path), p2, 1400)
+    assert checkpoint.latest(str(tmp_path)) == path
+    got, step = checkpoint.load(path)
+    assert step == 1400
+    for k in rn.PARAM_NAMES:
+        np.testing.assert_array_equal(got[k], p2[k])
+    z = np.load(path)
+    assert z["model_definition/conv2/conv2_kernel"].shape == (5, 5, 64, 64) and int(z["Variable"]) == 0

@@ -13,13 +13,30 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 def test_single_worker_cli_runs_and_prints_the_reference_lines():
     r = subprocess.run([sys.executable, os.path.join(ROOT, "cifar10cnn.py"), "--job_name=worker",
-                        "--worker_hosts=localhost:2223", "--ps_hosts=localhost:2222", "--max_steps=500"],
+                        "--worker_hosts=localhost:2223", "--ps_hosts=localhost:2222", "--max_steps=500",
+                        "--log_dir="],
                        capture_output=True, text=True, timeout=300, cwd=ROOT)
     assert r.returncode == 0, r.stderr[-2000:]
     lines = r.stdout.strip().splitlines()
     assert lines[0] == "Starting Training"
     assert any(l.startswith("global_step 200, task:0_step 199, training accuracy ") for l in lines)
     assert any(l.startswith(" --- Test Accuracy = ") and l.endswith("%.") for l in lines)   # Q3 fixed: no crash
+
+
+def test_cli_checkpoint_and_resume(tmp_path):
+    """chief writes model.ckpt-<step>.npz into --log_dir at the end and a second run resumes from it."""
+    from b200cnn import checkpoint
+    cmd = [sys.executable, os.path.join(ROOT, "cifar10cnn.py"), "--job_name=worker", "--worker_hosts=localhost:2223",
+           f"--log_dir={tmp_path}", "--mode=fp32"]
+    r = subprocess.run(cmd + ["--max_steps=3"], capture_output=True, text=True, timeout=300, cwd=ROOT)
+    assert r.returncode == 0, r.stderr[-2000:]
+    first = checkpoint.latest(str(tmp_path))
+    assert first and first.endswith("model.ckpt-3.npz")
+    r = subprocess.run(cmd + ["--max_steps=5"], capture_output=True, text=True, timeout=300, cwd=ROOT)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert checkpoint.latest(str(tmp_path)).endswith("model.ckpt-5.npz")          # resumed at 3, ran 2 more
+    r = subprocess.run(cmd + ["--max_steps=5"], capture_output=True, text=True, timeout=300, cwd=ROOT)
+    assert r.returncode == 0 and "Starting Training" in r.stdout                       # already done: no step
 
 
 def test_session_towers_share_variables_and_step_matches_engine():
