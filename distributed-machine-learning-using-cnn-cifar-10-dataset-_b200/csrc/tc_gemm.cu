@@ -4,9 +4,9 @@
 // Either operand may be K-major or MN-major in global memory, so forward (x W), dX (dY W^T) and
 // dW (X^T dY) all read the row-major tensors of the TF layouts directly -- no transposes.
 //
-// CTA = 128 x BN output tile, 5 warps: warps 0-3 stage operands (LDG -> bf16 -> STS in the
+// CTA = 128 x BN output tile, 9 warps: warps 0-7 stage operands (LDG -> bf16 -> STS in the
 // no-swizzle canonical layout, chunk stride padded by 16 B so the stores are conflict-free) and
-// later run the epilogue (warp w owns TMEM lanes 32w..32w+31); warp 4 allocates TMEM and issues
+// later warps 0-3 run the epilogue (warp w owns TMEM lanes 32w..32w+31); warp 8 allocates TMEM and issues
 // the MMAs from one thread.  4-stage ring, full/empty mbarriers; tcgen05.commit frees a stage.
 #include <algorithm>
 
@@ -18,7 +18,7 @@ using namespace tc;
 
 namespace {
 constexpr int BM = 128, BK = 64, STAGES = 4;
-constexpr int LOADERS = 128;
+constexpr int LOADERS = 256;     // 8 staging warps (warps 0-3 also run the epilogue); warp 8 issues the MMAs
 
 struct GemmArgs {
   int M, N, K;
@@ -45,7 +45,7 @@ struct Smem {
 };
 
 template <int BN, bool A_MN, bool B_MN, typename TA, typename TB>
-__global__ void __launch_bounds__(160, 1) tc_gemm_kernel(GemmArgs g) {
+__global__ void __launch_bounds__(288, 1) tc_gemm_kernel(GemmArgs g) {
   using S = Smem<BN>;
   extern __shared__ __align__(128) uint8_t smem[];
   uint8_t* ctrl = smem + STAGES * S::STAGE;
@@ -64,13 +64,13 @@ __global__ void __launch_bounds__(160, 1) tc_gemm_kernel(GemmArgs g) {
     mbar_init(smem_u32(accum), 1);
     fence_mbar_init();
   }
-  if (warp == 4) tmem_alloc(smem_u32(tmem_slot), BN < 32 ? 32 : BN);
+  if (warp == 8) tmem_alloc(smem_u32(tmem_slot), BN < 32 ? 32 : BN);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
 
-  if (warp < 4) {
+  if (warp < 8) {
     // ------------------------------ operand staging ------------------------------------------
     const TA* A = reinterpret_cast<const TA*>(g.A);
     const TB* B = reinterpret_cast<const TB*>(g.B);
@@ -122,7 +122,8 @@ __global__ void __launch_bounds__(160, 1) tc_gemm_kernel(GemmArgs g) {
       fence_proxy_async();
       mbar_arrive(smem_u32(full + s));
     }
-    // ------------------------------ epilogue ------------------------------------------------------
+    // ------------------------------ epilogue (warps 0-3: one TMEM lane quarter each) -----------------
+    if (warp < 4) {
     mbar_wait(smem_u32(accum), 0);
     tc_fence_after();
     const int m = m0 + warp * 32 + lane;
@@ -170,6 +171,7 @@ __global__ void __launch_bounds__(160, 1) tc_gemm_kernel(GemmArgs g) {
         }
       }
     }
+    }
     tc_fence_before();
   } else {
     // ------------------------------ MMA issue (one thread) -----------------------------------------
@@ -197,7 +199,7 @@ __global__ void __launch_bounds__(160, 1) tc_gemm_kernel(GemmArgs g) {
     __syncwarp();
   }
   __syncthreads();
-  if (warp == 4) {
+  if (warp == 8) {
     tc_fence_after();
     tmem_dealloc(tmem, BN < 32 ? 32 : BN);
   }
@@ -213,7 +215,7 @@ int launch(const GemmArgs& g, cudaStream_t st) {
     attr_done = true;
   }
   dim3 grid(cdiv(g.N, BN), cdiv(g.M, BM), cdiv(g.K, g.k_per_split));
-  kern<<<grid, 160, S::TOTAL, st>>>(g);
+  kern<<<grid, 288, S::TOTAL, st>>>(g);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
