@@ -274,7 +274,8 @@ int b200_forward(b200_handle h, const uint8_t* images, const int32_t* labels, vo
     // FC1 as a split-K tensor-core product; the tail kernels add the partials, bias and ReLU, run
     // FC2 / FC3 / loss / accuracy and already produce every gradient above FC1 (dfull1, dW2, db2, dW3,
     // db3, db1) -- they depend on nothing else, so b200_backward starts at FC1's weight gradient.
-    // CTA 0 of the tail also clears conv2's bias gradient for the atomics of the pool2 backward.
+    // The tail also clears the conv gradients (first four tensors of the flat buffer): conv1's filter / bias
+    // gradient and conv2's bias gradient are accumulated with atomics further down.
     float* part = h->ptr<float>("fc1_part");
     SITE("full1_fwd", fc_fwd_tc_splitk(pool2, h->P(P_FW1), part, c.batch, h->flat, c.f1, st));
     SITE("fc_tail", fc_tail(part, fc_fwd_tc_splits(c.batch, h->flat, c.f1), h->P(P_FB1), full1, h->P(P_FW2),
@@ -282,7 +283,8 @@ int b200_forward(b200_handle h, const uint8_t* images, const int32_t* labels, vo
                             h->ptr<float>("dfull2"), h->ptr<float>("dfull1"), h->ptr<int32_t>("pred"),
                             h->ptr<float>("loss"), h->ptr<int32_t>("n_correct"), h->ptr<int32_t>("n_bad"),
                             h->G(P_FW2), h->G(P_FB2), h->G(P_FW3), h->G(P_FB3), h->G(P_FB1),
-                            h->ptr<void>("tail_scratch"), h->G(P_B2), c.c2, c.batch, c.f1, c.f2, c.n_cls, st, true));
+                            h->ptr<void>("tail_scratch"), h->grads, (int)(h->p_off[P_B2] + h->p_size[P_B2]), c.batch, c.f1, c.f2,
+                            c.n_cls, st, true));
   } else {
     SITE("full1_fwd", fc_fwd_f32(pool2, h->P(P_FW1), h->P(P_FB1), full1, c.batch, h->flat, c.f1, 1, st));
     SITE("full2_fwd", fc_fwd_f32(full1, h->P(P_FW2), h->P(P_FB2), full2, c.batch, c.f1, c.f2, 1, st));
@@ -345,7 +347,7 @@ int b200_backward(b200_handle h, void* stream) {
     if (fused1) {
       SITE("conv1_wgrad", conv1_wgrad_tc(h->last_images, dpool1, h->ptr<float>("pool1"), h->ptr<uint8_t>("arg1"),
                                          h->G(P_W1), h->G(P_B1), scratch, c.batch, c.img_h, c.img_w, c.crop_h,
-                                         c.crop_w, st));
+                                         c.crop_w, st, true));
     } else {
       SITE("pool1_bwd", maxpool_bwd_f32(dpool1, h->ptr<uint8_t>("arg1"), h->ptr<float>("conv1"), dconv1, c.batch,
                                         c.crop_h, c.crop_w, c.c1, 1, st));
@@ -473,7 +475,7 @@ int b200_launches_per_step(b200_handle h, int32_t* n) {
   if (h->cfg.mode == B200_MODE_BF16) {
     // conv1 (3 or 1), conv2, pool2, FC1 split-K, tail x2 | FC1 bwd x2, pool2 bwd, conv2 wgrad x2, dgrad, conv1 wgrad (2 or 1+4), sgd
     const bool f1 = conv1_tc_supported(h->cfg.crop_h, h->cfg.crop_w, h->cfg.c_in, h->cfg.c1);
-    *n = (f1 ? 1 : 3) + 2 + 1 + 3 + 2 + 2 + 1 + (f1 ? 2 : 5) + 1;
+    *n = (f1 ? 1 : 3) + 2 + 1 + 3 + 2 + 2 + 1 + (f1 ? 1 : 5) + 1;
   }
   return B200_OK;
 }

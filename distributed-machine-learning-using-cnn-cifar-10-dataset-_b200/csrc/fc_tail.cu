@@ -51,7 +51,7 @@ struct TailArgs {
   float *full2, *logits, *dlogits, *dfull2, *dfull1;
   int32_t* pred;
   float* part;                     // [n_ctas][PV] per-CTA partial sums: db1 | db2 | db3(16) | dW3 | loss, ok, bad
-  float* zero_ptr; int zero_n;     // small buffer CTA 0 clears for a later kernel's atomics (may be null)
+  float* zero_ptr; int zero_n;     // buffer cleared here for later kernels' atomics (may be null)
   long long* timeline;             // diagnostics: clock64 stamps of CTA 0's phases, or null
 };
 __host__ __device__ inline int part_len(int F1, int F2, int NC) { return F1 + F2 + 16 + F2 * NC + 4; }
@@ -92,8 +92,8 @@ __global__ void __launch_bounds__(RT) fc_tail_rows_kernel(TailArgs a) {
   const int r0 = blockIdx.x * R;
   const int nr = min(R, a.B - r0);
 
-  if (blockIdx.x == 0 && a.zero_ptr)
-    for (int i = tid; i < a.zero_n; i += RT) a.zero_ptr[i] = 0.f;
+  if (a.zero_ptr)     // every CTA clears its slice of the buffer a later kernel accumulates into
+    for (int i = blockIdx.x * RT + tid; i < a.zero_n; i += gridDim.x * RT) a.zero_ptr[i] = 0.f;
   TL(0);
   // ---- W2 (bf16 image, 149 KB) -> shared memory with bulk copies; lands while full1 is assembled ------
   if (tid == 0) {

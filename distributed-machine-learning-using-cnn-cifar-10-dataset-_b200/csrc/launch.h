@@ -76,6 +76,6 @@ int conv1_pool_fwd_tc(const uint8_t* img, const float* w, const float* bias, flo
                       float* conv_dbg, int B, int ih, int iw, int H, int W, cudaStream_t st);
 int64_t conv1_wgrad_tc_scratch_bytes(int B);
 int conv1_wgrad_tc(const uint8_t* img, const float* dpool, const float* pool, const uint8_t* arg, float* dw, float* db,
-                   float* scratch, int B, int ih, int iw, int H, int W, cudaStream_t st);
+                   float* scratch, int B, int ih, int iw, int H, int W, cudaStream_t st, bool prezeroed = false);
 
 }  // namespace b200

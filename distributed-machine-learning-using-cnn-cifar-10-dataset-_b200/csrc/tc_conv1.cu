@@ -245,7 +245,8 @@ struct Conv1WgradArgs {
   const float* dpool;     // [B,OH,OW,64]  gradient w.r.t. pool1
   const float* pool;      // [B,OH,OW,64]  pool1 itself (ReluGrad mask: the selected cell is > 0 iff pool1 > 0)
   const uint8_t* arg;     // [B,OH,OW,64]
-  float* partial;         // [gridDim.x][5][64][40]
+  float* dw;              // [25][3][64]  += (atomics; zero on entry)
+  float* db;              // [64]         += (atomics; zero on entry), may be null
   C1Geom g;
 };
 
@@ -346,8 +347,10 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
     // ---- epilogue: D_di[cout][dj*8 + c] (M = 64: lanes 0-15 of each subpartition) -> partial --------
     mbar_wait(smem_u32(accum), 0);
     tc_fence_after();
-    if (warp < 4) {
-      float* part = a.partial + (size_t)blockIdx.x * 5 * 64 * 40;
+    if (warp < 4 && nimg > 0) {
+      // D_di[cout][dj*8 + c] -> dW1[(di*5+dj)][c][cout]: 16 adjacent couts per warp instruction, summed across
+      // CTAs with fp32 atomics (the 128 per-image partials would otherwise need a reduction kernel of their own)
+      const int cout = warp * 16 + lane;
       for (int di = 0; di < 5; ++di) {
 #pragma unroll 1
         for (int c0 = 0; c0 < 64; c0 += 32) {
@@ -355,10 +358,12 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
           tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + di * 64 + c0, v);
           tmem_ld_wait();
           if (lane < 16) {
-            float* out = part + ((size_t)di * 64 + warp * 16 + lane) * 40 + c0;
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (c0 + j < 40) out[j] = nimg > 0 ? __uint_as_float(v[j]) : 0.f;
+            for (int j = 0; j < 32; ++j) {
+              const int col = c0 + j, dj = col >> 3, c = col & 7;
+              if (col < 40 && c < 3) atomicAdd(a.dw + ((di * 5 + dj) * 3 + c) * 64 + cout, __uint_as_float(v[j]));
+              if (a.db && di == 2 && col == 2 * 8 + 3) atomicAdd(a.db + cout, __uint_as_float(v[j]));   // constant-1 channel
+            }
           }
         }
       }
@@ -399,33 +404,6 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
   }
 }
 
-// dW1[tap][c][cout] = sum_s part[s][di][cout][dj*8+c];  db1[cout] = sum_s part[s][2][cout][2*8+3]
-__global__ void conv1_wgrad_finish(const float* __restrict__ part, float* __restrict__ dw, float* __restrict__ db, int S) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= 75 * 64 + 64) return;
-  int src;
-  if (i < 75 * 64) {
-    const int cout = i & 63, tc3 = i >> 6;
-    const int c = tc3 % 3, tap = tc3 / 3;
-    src = ((tap / 5) * 64 + cout) * 40 + (tap % 5) * 8 + c;
-  } else {
-    src = (2 * 64 + (i - 75 * 64)) * 40 + 2 * 8 + 3;
-  }
-  float s = 0.f;
-  const float* p = part + src;
-  int z = 0;
-  for (; z + 8 <= S; z += 8) {          // 8 independent loads in flight; summation order is fixed
-    float v[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] = __ldg(p + (size_t)(z + j) * 5 * 64 * 40);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) s += v[j];
-  }
-  for (; z < S; ++z) s += __ldg(p + (size_t)z * 5 * 64 * 40);
-  if (i < 75 * 64) dw[i] = s;
-  else if (db) db[i - 75 * 64] = s;
-}
-
 int conv1_wgrad_ctas(int B) { return std::min(B, kNumSMs); }
 size_t conv1_wgrad_smem(const C1Geom& g) {
   size_t xs = (g.npix * 16 + 127) & ~127, ch = g.npix * 16 + 16;
@@ -433,10 +411,11 @@ size_t conv1_wgrad_smem(const C1Geom& g) {
 }
 }  // namespace
 
-int64_t conv1_wgrad_tc_scratch_bytes(int B) { return (int64_t)conv1_wgrad_ctas(B) * 5 * 64 * 40 * 4; }
+int64_t conv1_wgrad_tc_scratch_bytes(int B) { (void)B; return 256; }   // none needed any more (kept for the ABI)
 
 int conv1_wgrad_tc(const uint8_t* img, const float* dpool, const float* pool, const uint8_t* arg, float* dw, float* db,
-                   float* scratch, int B, int ih, int iw, int H, int W, cudaStream_t st) {
+                   float* scratch, int B, int ih, int iw, int H, int W, cudaStream_t st, bool prezeroed) {
+  (void)scratch;
   B200_REQUIRE(B > 0 && H <= ih && W <= iw && H >= 4 && W >= 4, "conv1_wgrad_tc: bad shape");
   C1Geom g = make_c1geom(B, ih, iw, H, W);
   const size_t smem = conv1_wgrad_smem(g);
@@ -447,10 +426,12 @@ int conv1_wgrad_tc(const uint8_t* img, const float* dpool, const float* pool, co
     attr = true;
   }
   const int S = conv1_wgrad_ctas(B);
-  Conv1WgradArgs a{img, dpool, pool, arg, scratch, g};
+  if (!prezeroed) {       // the kernel accumulates with atomics
+    B200_CUDA_TRY(cudaMemsetAsync(dw, 0, 75 * 64 * sizeof(float), st));
+    if (db) B200_CUDA_TRY(cudaMemsetAsync(db, 0, 64 * sizeof(float), st));
+  }
+  Conv1WgradArgs a{img, dpool, pool, arg, dw, db, g};
   conv1_wgrad_kernel<<<S, 416, smem, st>>>(a);
-  B200_LAUNCH_CHECK();
-  conv1_wgrad_finish<<<cdiv(75 * 64 + 64, 64), 64, 0, st>>>(scratch, dw, db, S);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
