@@ -26,7 +26,7 @@ using namespace tc;
 
 namespace {
 constexpr int LOADERS = 128;
-constexpr int WSTAGES = 6;
+constexpr int WSTAGES = 2;      // filter stages in shared memory; one stage = the five taps of one filter row
 
 struct ConvGeom {
   int B, H, W, KC, NC;      // batch, image size, contraction channels, output channels
@@ -173,7 +173,8 @@ __global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
   const int strip_bytes = kchunks * g.ch_stride;
   // weight stage: MN-major [BN/8 groups][KC k][16B] (SBO = KC*16+16)  |  K-major [KC/8 chunks][BN rows][16B]
   const int w_mn_sbo = g.KC * 16 + 16, w_k_lbo = BN * 16 + 16;
-  const int wstage = ((DGRAD ? kchunks * w_k_lbo : (BN / 8) * w_mn_sbo) + 127) & ~127;
+  const int wtap = ((DGRAD ? kchunks * w_k_lbo : (BN / 8) * w_mn_sbo) + 127) & ~127;   // one tap's operand image
+  const int wstage = 5 * wtap;
   uint8_t* strip = smem;
   uint8_t* wring = smem + ((strip_bytes + 127) & ~127);
   uint8_t* ctrl = wring + WSTAGES * wstage;
@@ -320,27 +321,31 @@ __global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
       uint32_t acc = 0;
       // Every CTA streams the same 25 filter taps out of L2; each walks them in its own rotation so
       // that the CTAs do not all pull the same lines at once (the sum over taps is order-independent).
-      const int tap0 = (int)((blockIdx.x * 7u + blockIdx.y * 3u) % 25u);
-      int di = tap0 / 5, dj = tap0 - di * 5;
-      for (int i = 0; i < 25; ++i) {
-        const int s = i % WSTAGES;
-        const uint32_t ph = (i / WSTAGES) & 1;
-        mbar_wait(smem_u32(wfull + s), ph);
-        tc_fence_after();
-        const uint32_t a_tap = a_lo0 + (uint32_t)((di - 2) * g.P + (dj - 2));      // a tap is a slot offset
-        const uint32_t b_tap = b_lo0 + (uint32_t)s * (wstage >> 4);
-        for (int t = w; t < g.tiles; t += NISS) {
-          uint32_t a_lo = a_tap + t * 128, b_lo = b_tap;
-          const uint32_t d = tmem + t * BN;
+      int di = (int)((blockIdx.x + blockIdx.y) % 5u);       // filter-row rotation (same in the producer warp)
+      for (int r = 0; r < 5; ++r) {
+        const int s = r % WSTAGES;
+        const uint32_t ph = (r / WSTAGES) & 1;
+        mbar_wait(smem_u32(wfull + s), ph);               // one wait and one commit per filter ROW: both cost
+        tc_fence_after();                                 // ~100 cycles of the issuing thread (measured)
+        const uint32_t b_row = b_lo0 + (uint32_t)s * (wstage >> 4);
 #pragma unroll
-          for (int ks = 0; ks < KSTEPS; ++ks) {
-            umma_bf16(d, desc_join(a_lo, a_hi), desc_join(b_lo, b_hi), idesc, acc | (uint32_t)ks);
-            a_lo += a_kstep; b_lo += b_kstep;
+        for (int dj = 0; dj < 5; ++dj) {
+          const uint32_t a_tap = a_lo0 + (uint32_t)((di - 2) * g.P + (dj - 2));    // a tap is a slot offset
+          // dgrad correlates with the filter rotated by 180 degrees: the stage holds forward row 4-di, read backwards
+          const uint32_t b_tap = b_row + (uint32_t)(DGRAD ? 4 - dj : dj) * (wtap >> 4);
+          for (int t = w; t < g.tiles; t += NISS) {
+            uint32_t a_lo = a_tap + t * 128, b_lo = b_tap;
+            const uint32_t d = tmem + t * BN;
+#pragma unroll
+            for (int ks = 0; ks < KSTEPS; ++ks) {
+              umma_bf16(d, desc_join(a_lo, a_hi), desc_join(b_lo, b_hi), idesc, acc | (uint32_t)(dj | ks));
+              a_lo += a_kstep; b_lo += b_kstep;
+            }
           }
         }
         acc = 1;
         umma_commit(smem_u32(wempty + s));        // arrives when this warp's MMAs on the stage are done
-        if (++dj == 5) { dj = 0; if (++di == 5) di = 0; }
+        if (++di == 5) di = 0;
       }
       umma_commit(smem_u32(accum));
       if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && w == 0) a.timeline[4] = clock64();
@@ -350,21 +355,26 @@ __global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
     // ---- filter taps: one thread, bulk copies global -> shared, completion counted in bytes ----------
     if (lane == 0) {
       const int img = (a.cout_f / 8) * (a.cin_f * 16 + 16);             // bytes of one packed tap
-      int tap = (int)((blockIdx.x * 7u + blockIdx.y * 3u) % 25u);      // same rotation as the MMA warp
-      for (int i = 0; i < 25; ++i, tap = (tap == 24 ? 0 : tap + 1)) {
-        const int s = i % WSTAGES;
-        const uint32_t ph = (i / WSTAGES) & 1;
+      int di = (int)((blockIdx.x + blockIdx.y) % 5u);                  // same rotation as the MMA warps
+      for (int r = 0; r < 5; ++r, di = (di == 4 ? 0 : di + 1)) {
+        const int s = r % WSTAGES;
+        const uint32_t ph = (r / WSTAGES) & 1;
         mbar_wait(smem_u32(wempty + s), ph ^ 1);
-        const uint32_t ws = smem_u32(wring + s * wstage);
         const uint32_t bar = smem_u32(wfull + s);
-        if (!DGRAD) {     // N-groups nc0/8 .. +8 of tap `tap` are contiguous: one copy
+        const int prow = DGRAD ? 4 - di : di;                            // packed (forward) filter row to fetch
+        if (!DGRAD) {     // N-groups nc0/8 .. +8 of a tap are contiguous: one copy per tap
           const uint32_t bytes = (BN / 8) * w_mn_sbo;
-          mbar_arrive_expect_tx(bar, bytes);
-          bulk_g2s(ws, a.wp + (size_t)tap * img + (size_t)(nc0 / 8) * w_mn_sbo, bytes, bar);
-        } else {          // tap 24-t read K-major: per k-chunk (forward cout group) the 64 rows nc0.. are contiguous
-          mbar_arrive_expect_tx(bar, (uint32_t)kchunks * BN * 16);
-          const uint8_t* src = a.wp + (size_t)(24 - tap) * img + (size_t)nc0 * 16;
-          for (int c = 0; c < kchunks; ++c) bulk_g2s(ws + c * w_k_lbo, src + (size_t)c * (a.cin_f * 16 + 16), BN * 16, bar);
+          mbar_arrive_expect_tx(bar, 5 * bytes);
+          for (int j = 0; j < 5; ++j)
+            bulk_g2s(smem_u32(wring + s * wstage + j * wtap),
+                     a.wp + (size_t)(prow * 5 + j) * img + (size_t)(nc0 / 8) * w_mn_sbo, bytes, bar);
+        } else {          // read K-major: per k-chunk (forward cout group) the 64 rows nc0.. are contiguous
+          mbar_arrive_expect_tx(bar, 5u * kchunks * BN * 16);
+          for (int j = 0; j < 5; ++j) {
+            const uint8_t* src = a.wp + (size_t)(prow * 5 + j) * img + (size_t)nc0 * 16;
+            const uint32_t ws = smem_u32(wring + s * wstage + j * wtap);
+            for (int c = 0; c < kchunks; ++c) bulk_g2s(ws + c * w_k_lbo, src + (size_t)c * (a.cin_f * 16 + 16), BN * 16, bar);
+          }
         }
       }
     }
@@ -398,7 +408,7 @@ int pick_ipc(int B, int H, int W, int KC) {
   int best = 1;
   for (int ipc : {2, 4}) {
     ConvGeom g = make_geom(B, H, W, KC, 64, ipc);
-    int64_t smem = (int64_t)(KC / 8) * g.ch_stride + WSTAGES * 9000 + 1024;
+    int64_t smem = (int64_t)(KC / 8) * g.ch_stride + WSTAGES * 5 * (int64_t)std::max((KC / 8) * 1040, 8 * (KC * 16 + 16)) + 1024;
     if (g.tiles * 64 <= 512 && smem <= 200 * 1024 && (B + ipc - 1) / ipc >= 2 * kNumSMs) best = ipc;
   }
   return best;
@@ -424,7 +434,7 @@ int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, 
   }
   B200_REQUIRE(g.tiles * 64 <= 512, "conv5x5_tc: image %dx%d too large for one CTA's TMEM", H, W);
   const int kchunks = KC / 8;
-  const int wstage = ((DGRAD ? kchunks * (64 * 16 + 16) : 8 * (KC * 16 + 16)) + 127) & ~127;
+  const int wstage = 5 * (((DGRAD ? kchunks * (64 * 16 + 16) : 8 * (KC * 16 + 16)) + 127) & ~127);
   int smem = ((kchunks * g.ch_stride + 127) & ~127) + WSTAGES * wstage + 256;
   if (pg) smem += pg->OH * pg->OW * 64 * 5 + 16 + 256;
   B200_REQUIRE(smem <= 227 * 1024, "conv5x5_tc: %d bytes of shared memory needed", smem);
