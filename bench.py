@@ -251,8 +251,7 @@ def main():
         if world == 1:
             eng.train_step(s_img, s_lab, lr)
         else:
-            eng.forward(s_img, s_lab)
-            eng.backward()
+            eng.forward_backward(s_img, s_lab)
             exchange_and_update()
 
     def exchange_and_update():
@@ -269,8 +268,7 @@ def main():
             else:
                 s_img.copy_(img, non_blocking=True)
                 s_lab.copy_(lab, non_blocking=True)
-                eng.forward(s_img, s_lab)
-                eng.backward()
+                eng.forward_backward(s_img, s_lab)
                 exchange_and_update()
                 out.copy_(eng.loss(), non_blocking=True)
         return fn

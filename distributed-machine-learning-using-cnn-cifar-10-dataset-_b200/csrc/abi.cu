@@ -225,7 +225,9 @@ static int site_mark(b200_model* h, const char* name, cudaStream_t st) {
 }
 #define SITE(name, expr) do { TRY(site_mark(h, name, st)); TRY(expr); } while (0)
 
-int b200_forward(b200_handle h, const uint8_t* images, const int32_t* labels, void* stream) {
+// defer_tail: the caller runs b200_backward right after on the same stream, so the tail's parameter-gradient
+// kernel (which also writes loss / n_correct) may stay on side stream 0 and be joined by the backward's final join
+static int forward_impl(b200_handle h, const uint8_t* images, const int32_t* labels, void* stream, bool defer_tail) {
   B200_READY(h);
   B200_REQUIRE(images && labels, "forward: null input");
   cudaStream_t st = (cudaStream_t)stream;
@@ -284,7 +286,11 @@ int b200_forward(b200_handle h, const uint8_t* images, const int32_t* labels, vo
                             h->ptr<float>("loss"), h->ptr<int32_t>("n_correct"), h->ptr<int32_t>("n_bad"),
                             h->G(P_FW2), h->G(P_FB2), h->G(P_FW3), h->G(P_FB3), h->G(P_FB1),
                             h->ptr<void>("tail_scratch"), h->grads, (int)(h->p_off[P_B2] + h->p_size[P_B2]), c.batch, c.f1, c.f2,
-                            c.n_cls, st, true));
+                            c.n_cls, st, true, fork ? h->side[0] : nullptr, h->ev_fork[0]));
+    if (fork && !defer_tail) {
+      B200_CUDA_TRY(cudaEventRecord(h->ev_join[0], h->side[0]));
+      B200_CUDA_TRY(cudaStreamWaitEvent(st, h->ev_join[0], 0));
+    }
   } else {
     SITE("full1_fwd", fc_fwd_f32(pool2, h->P(P_FW1), h->P(P_FB1), full1, c.batch, h->flat, c.f1, 1, st));
     SITE("full2_fwd", fc_fwd_f32(full1, h->P(P_FW2), h->P(P_FB2), full2, c.batch, c.f1, c.f2, 1, st));
@@ -294,6 +300,15 @@ int b200_forward(b200_handle h, const uint8_t* images, const int32_t* labels, vo
   }
   h->forward_done = true;
   return B200_OK;
+}
+
+int b200_forward(b200_handle h, const uint8_t* images, const int32_t* labels, void* stream) {
+  return forward_impl(h, images, labels, stream, false);
+}
+
+int b200_forward_backward(b200_handle h, const uint8_t* images, const int32_t* labels, void* stream) {
+  TRY(forward_impl(h, images, labels, stream, true));
+  return b200_backward(h, stream);
 }
 
 int b200_backward(b200_handle h, void* stream) {
@@ -403,8 +418,7 @@ int b200_p2p_sgd_apply(b200_handle h, const void* const* peer_grads, void* const
 }
 
 int b200_train_step(b200_handle h, const uint8_t* images, const int32_t* labels, float lr, void* stream) {
-  TRY(b200_forward(h, images, labels, stream));
-  TRY(b200_backward(h, stream));
+  TRY(b200_forward_backward(h, images, labels, stream));
   return b200_sgd_apply(h, lr, 1.f, stream);
 }
 

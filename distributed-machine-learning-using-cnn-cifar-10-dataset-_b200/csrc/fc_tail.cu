@@ -385,7 +385,7 @@ int fc_tail(const float* fc1_part, int n_part, const float* b1, float* full1, co
             const float* w3, const float* b3, const int32_t* labels, float* full2, float* logits, float* dlogits,
             float* dfull2, float* dfull1, int32_t* pred, float* loss, int32_t* n_correct, int32_t* n_bad, float* dw2,
             float* db2, float* dw3, float* db3, float* db1, void* scratch, float* zero_ptr, int zero_n, int B, int F1,
-            int F2, int NC, cudaStream_t st, bool w2_image_ready) {
+            int F2, int NC, cudaStream_t st, bool w2_image_ready, cudaStream_t grads_stream, cudaEvent_t rows_done) {
   B200_REQUIRE(B > 0 && NC > 0 && NC <= kMaxCls, "fc_tail: bad shape");
   B200_REQUIRE(F1 % KT == 0 && F2 % 4 == 0 && F2 <= RT && F2 > 0, "fc_tail: needs f1 %% 32 == 0, f2 %% 4 == 0, f2 <= 256");
   const int R = rows_per_cta(B);
@@ -413,6 +413,11 @@ int fc_tail(const float* fc1_part, int n_part, const float* b1, float* full1, co
   B200_LAUNCH_CHECK();
   TailGradArgs ga{B, F1, F2, NC, nrc, full1, dfull2, part, dw2, db2, dw3, db3, db1, loss, n_correct, n_bad};
   const size_t gsmem = (size_t)(2 * KT * F2 + 2 * KT * 4) * 4;
+  if (grads_stream && grads_stream != st) {       // the parameter gradients do not gate dfull1's consumer: let them overlap it
+    B200_CUDA_TRY(cudaEventRecord(rows_done, st));
+    B200_CUDA_TRY(cudaStreamWaitEvent(grads_stream, rows_done, 0));
+    st = grads_stream;
+  }
   fc_tail_grads_kernel<<<F1 / 4 + cdiv(part_len(F1, F2, NC), RT), RT, gsmem, st>>>(ga);
   B200_LAUNCH_CHECK();
   return B200_OK;

@@ -472,9 +472,48 @@ struct WgradArgs {
   int imgs_per_cta;
   int nbuf;             // 2 = double-buffered strips, 1 when two pairs do not fit in shared memory
   PoolGradSrc pg;       // when pg.dpool != null, dy is unused and the dY strip is gathered from the pooled gradient
+  long long* timeline;  // optional clock64 stamps of CTA (0,0) in slots [8,14) of the diagnostics buffer, else null
 };
 
-__global__ void __launch_bounds__(288, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
+constexpr int WG_LOADERS = 256;     // the filter-gradient kernel is bound by its strip fills: eight loader warps
+__device__ __forceinline__ void wg_loaders_sync() { asm volatile("bar.sync 2, 256;" ::: "memory"); }
+// x and dY strips of one image (64 channels each) filled together: every thread has its whole share of both
+// tensors (<= 5 + 5 chunks of 32 bytes) in flight before the first conversion, one memory round trip per image
+__device__ __forceinline__ void fill_strip_pair(uint8_t* xs, uint8_t* ds, const float* __restrict__ x,
+                                                const float* __restrict__ dy, const ConvGeom& g, int n, int tid) {
+  constexpr int U = 5;
+  const int per_img = g.H * g.W * 8;
+  const float* sx = x + (int64_t)n * per_img * 8;
+  const float* sd = dy + (int64_t)n * per_img * 8;
+  for (int q0 = tid; q0 < per_img; q0 += WG_LOADERS * U) {
+    float4 vx[U][2], vd[U][2];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int q = q0 + u * WG_LOADERS;
+      if (q < per_img) {
+        vx[u][0] = __ldg(reinterpret_cast<const float4*>(sx + q * 8));
+        vx[u][1] = __ldg(reinterpret_cast<const float4*>(sx + q * 8) + 1);
+        vd[u][0] = __ldg(reinterpret_cast<const float4*>(sd + q * 8));
+        vd[u][1] = __ldg(reinterpret_cast<const float4*>(sd + q * 8) + 1);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int q = q0 + u * WG_LOADERS;
+      if (q < per_img) {
+        const int c = q & 7, pix = q >> 3;
+        const int i = pix / g.W, j = pix - i * g.W;
+        const int off = c * g.ch_stride + (g.lead + i * g.P + j) * 16;
+        const float fx[8] = {vx[u][0].x, vx[u][0].y, vx[u][0].z, vx[u][0].w, vx[u][1].x, vx[u][1].y, vx[u][1].z, vx[u][1].w};
+        const float fd[8] = {vd[u][0].x, vd[u][0].y, vd[u][0].z, vd[u][0].w, vd[u][1].x, vd[u][1].y, vd[u][1].z, vd[u][1].w};
+        *reinterpret_cast<uint4*>(xs + off) = pack8(fx);
+        *reinterpret_cast<uint4*>(ds + off) = pack8(fd);
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(416, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
   constexpr int C = 64;
   const ConvGeom& g = a.g;
   extern __shared__ __align__(128) uint8_t smem[];
@@ -495,65 +534,74 @@ __global__ void __launch_bounds__(288, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
   const int ksteps = (g.rows_per_img * g.P + 15) / 16;
 
   if (tid == 0) {
-    for (int s = 0; s < 2; ++s) { mbar_init(smem_u32(full + s), LOADERS); mbar_init(smem_u32(empty + s), 5); }
+    for (int s = 0; s < 2; ++s) { mbar_init(smem_u32(full + s), WG_LOADERS); mbar_init(smem_u32(empty + s), 5); }
     mbar_init(smem_u32(accum), 5);
     fence_mbar_init();
   }
-  if (warp == 4) tmem_alloc(smem_u32(tmem_slot), 512);
+  if (warp == 8) tmem_alloc(smem_u32(tmem_slot), 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
 
-  if (warp < 4) {
-    zero_smem(smem, 2 * a.nbuf * strip_bytes, tid);      // pads stay zero for every image: fills touch valid pixels only
-    loaders_sync();
+  const bool stamp = a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0;
+  if (warp < 8) {
+    if (stamp) a.timeline[8] = clock64();
+    // pads stay zero for every image: fills touch valid pixels only
+    for (int o = tid * 16; o < 2 * a.nbuf * strip_bytes; o += WG_LOADERS * 16) *reinterpret_cast<uint4*>(smem + o) = make_uint4(0, 0, 0, 0);
+    wg_loaders_sync();
+    if (stamp) a.timeline[9] = clock64();
     for (int it = 0; it < nimg; ++it) {
       const int b = it % a.nbuf;
       const uint32_t ph = (it / a.nbuf) & 1;
       mbar_wait(smem_u32(empty + b), ph ^ 1);
       uint8_t* xs = smem + (2 * b) * strip_bytes;
       uint8_t* ds = xs + strip_bytes;
-      fill_strip(xs, a.x, g, img_beg + it, C, g.ch_stride, tid);
-      if (a.pg.dpool) {
-        float unused[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        stage_pool_grad(dpm, argb, a.pg, img_beg + it, tid);
-        loaders_sync();
-        fill_strip_from_pool(ds, dpm, argb, g, a.pg, 0, g.ch_stride, tid, unused);
-        loaders_sync();                       // nobody restages dpm while a slower loader still gathers from it
+      if (a.pg.dpool) {                       // the pooled-gradient gather keeps its 128-thread helpers (warps 0-3)
+        if (warp < 4) {
+          float unused[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+          fill_strip(xs, a.x, g, img_beg + it, C, g.ch_stride, tid);
+          stage_pool_grad(dpm, argb, a.pg, img_beg + it, tid);
+          loaders_sync();
+          fill_strip_from_pool(ds, dpm, argb, g, a.pg, 0, g.ch_stride, tid, unused);
+          loaders_sync();                     // nobody restages dpm while a slower loader still gathers from it
+        }
       } else {
-        fill_strip(ds, a.dy, g, img_beg + it, C, g.ch_stride, tid);
+        fill_strip_pair(xs, ds, a.x, a.dy, g, img_beg + it, tid);
       }
       fence_proxy_async();
       mbar_arrive(smem_u32(full + b));
+      if (stamp && it == 0) a.timeline[10] = clock64();
     }
+    if (stamp) a.timeline[11] = clock64();
     // ---- epilogue: M = 64 accumulators live in lanes 0-15 of each 32-lane subpartition --------------
     mbar_wait(smem_u32(accum), 0);
     tc_fence_after();
+    if (stamp) a.timeline[12] = clock64();
     float* part = a.partial + (int64_t)blockIdx.y * 25 * C * C;
-    for (int dj = 0; dj < 5; ++dj) {
+    const int q4 = warp & 3, c0 = (warp >> 2) * 32;       // TMEM lane quarter, column half of each tap
 #pragma unroll 1
-      for (int c0 = 0; c0 < C; c0 += 32) {
-        uint32_t v[32];
-        tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + dj * C + c0, v);
-        tmem_ld_wait();
-        if (lane < 16) {
-          const int cin = warp * 16 + lane;
-          float* out = part + ((int64_t)(di * 5 + dj) * C + cin) * C + c0;
+    for (int dj = 0; dj < 5; ++dj) {
+      uint32_t v[32];
+      tmem_ld32(tmem + ((uint32_t)(q4 * 32) << 16) + dj * C + c0, v);
+      tmem_ld_wait();
+      if (lane < 16) {
+        const int cin = q4 * 16 + lane;
+        float* out = part + ((int64_t)(di * 5 + dj) * C + cin) * C + c0;
 #pragma unroll
-          for (int j = 0; j < 32; j += 4)
-            *reinterpret_cast<float4*>(out + j) =
-                (nimg > 0) ? make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]),
-                                         __uint_as_float(v[j + 3]))
-                           : make_float4(0.f, 0.f, 0.f, 0.f);
-        }
+        for (int j = 0; j < 32; j += 4)
+          *reinterpret_cast<float4*>(out + j) =
+              (nimg > 0) ? make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]),
+                                       __uint_as_float(v[j + 3]))
+                         : make_float4(0.f, 0.f, 0.f, 0.f);
       }
     }
     tc_fence_before();
+    if (stamp) a.timeline[13] = clock64();
   } else {
-    // warps 4..8: one issuing thread per filter tap dj of this CTA's filter row (own accumulator each)
+    // warps 8..12: one issuing thread per filter tap dj of this CTA's filter row (own accumulator each)
     if (lane == 0) {
-      const int dj = warp - 4;
+      const int dj = warp - 8;
       const uint32_t idesc = make_idesc(64, C, true, true);
       const uint32_t hi = desc_hi(g.ch_stride);                 // MN-major: SBO = channel-chunk stride, LBO = 128
       const uint32_t d = tmem + dj * C;
@@ -581,29 +629,35 @@ __global__ void __launch_bounds__(288, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
     __syncwarp();
   }
   __syncthreads();
-  if (warp == 4) {
+  if (warp == 8) {
     tc_fence_after();
     tmem_dealloc(tmem, 512);
   }
 }
 
+// sums the S partials of every 4-float group: four neighbouring lanes take every fourth partial each (all of a
+// lane's loads in flight together) and combine with two shuffles -- a fixed order, so the result is deterministic
 __global__ void reduce_partials_tc(const float* __restrict__ part, float* __restrict__ out, int n, int S) {
-  int i = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
-  if (i >= n) return;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int sub = t & 3;
+  const int i = min((t >> 2) * 4, n - 4);                 // surplus threads redo the last group (shuffles stay full-warp)
   float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-  int z = 0;
-  for (; z + 6 <= S; z += 6) {            // six independent 16-byte loads in flight; fixed summation order
-    float4 v[6];
+  for (int z0 = sub; z0 < S; z0 += 32) {
+    float4 v[8];
 #pragma unroll
-    for (int j = 0; j < 6; ++j) v[j] = __ldg(reinterpret_cast<const float4*>(part + (int64_t)(z + j) * n + i));
+    for (int j = 0; j < 8; ++j) {
+      const int z = z0 + 4 * j;
+      v[j] = z < S ? __ldg(reinterpret_cast<const float4*>(part + (int64_t)z * n + i)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
 #pragma unroll
-    for (int j = 0; j < 6; ++j) { s.x += v[j].x; s.y += v[j].y; s.z += v[j].z; s.w += v[j].w; }
+    for (int j = 0; j < 8; ++j) { s.x += v[j].x; s.y += v[j].y; s.z += v[j].z; s.w += v[j].w; }
   }
-  for (; z < S; ++z) {
-    float4 v = __ldg(reinterpret_cast<const float4*>(part + (int64_t)z * n + i));
-    s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+#pragma unroll
+  for (int m = 1; m <= 2; m <<= 1) {
+    s.x += __shfl_xor_sync(0xffffffffu, s.x, m); s.y += __shfl_xor_sync(0xffffffffu, s.y, m);
+    s.z += __shfl_xor_sync(0xffffffffu, s.z, m); s.w += __shfl_xor_sync(0xffffffffu, s.w, m);
   }
-  *reinterpret_cast<float4*>(out + i) = s;
+  if (sub == 0 && (t >> 2) * 4 < n) *reinterpret_cast<float4*>(out + i) = s;
 }
 
 int wgrad_splits_tc(int B) { return std::max(1, std::min(B, (kNumSMs + 4) / 5)); }
@@ -679,11 +733,11 @@ static int launch_wgrad(const float* x, const float* dy, const PoolGradSrc* pg, 
   int S = wgrad_splits_tc(B);
   int per = cdiv(B, S);
   S = cdiv(B, per);
-  WgradArgs a{x, dy, scratch, g, per, nbuf, pg ? *pg : PoolGradSrc{}};
-  conv5x5_wgrad_tc_kernel<<<dim3(5, S), 288, smem, st>>>(a);
+  WgradArgs a{x, dy, scratch, g, per, nbuf, pg ? *pg : PoolGradSrc{}, g_conv_timeline};
+  conv5x5_wgrad_tc_kernel<<<dim3(5, S), 416, smem, st>>>(a);
   B200_LAUNCH_CHECK();
   const int n = 25 * 64 * 64;
-  reduce_partials_tc<<<cdiv(n / 4, 64), 64, 0, st>>>(scratch, dw, n, S);
+  reduce_partials_tc<<<cdiv(n, 128), 128, 0, st>>>(scratch, dw, n, S);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

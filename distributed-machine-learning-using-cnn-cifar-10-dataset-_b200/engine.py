@@ -150,6 +150,11 @@ class TrainStepEngine:
         self._check_inputs(images, labels)
         check(self.lib.b200_forward(self.h, images.data_ptr(), labels.data_ptr(), self._stream()))
 
+    def forward_backward(self, images, labels):
+        """forward + backward in one call (lets independent gradient kernels overlap); same results."""
+        self._check_inputs(images, labels)
+        check(self.lib.b200_forward_backward(self.h, images.data_ptr(), labels.data_ptr(), self._stream()))
+
     def backward(self):
         check(self.lib.b200_backward(self.h, self._stream()))
 

@@ -82,6 +82,11 @@ int b200_forward(b200_handle h, const uint8_t* images, const int32_t* labels, vo
  * In bf16 mode independent branches run on two internal side streams forked from / joined to `stream` with
  * events; those streams are created by the first call, which must therefore happen before any capture. */
 int b200_backward(b200_handle h, void* stream);
+/* b200_forward + b200_backward as one call -- what sess.run(train_op) makes of :147-163 before the update.  Same
+ * results as the two calls; knowing that the backward follows lets the bf16 path leave the FC2/FC3 parameter
+ * gradients (and the loss / accuracy sums) on a side stream until the backward's final join, so they overlap FC1's
+ * input gradient.  Everything is complete on `stream` when the call's work is. */
+int b200_forward_backward(b200_handle h, const uint8_t* images, const int32_t* labels, void* stream);
 /* ApplyGradientDescent x10 (:162-163): params -= lr * grad_scale * grads.  grad_scale = 1 for a
  * single worker or a SUM allreduce, 1/world for a MEAN allreduce. */
 int b200_sgd_apply(b200_handle h, float lr, float grad_scale, void* stream);

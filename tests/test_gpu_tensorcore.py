@@ -13,6 +13,7 @@ import numpy as np
 import pytest
 import torch
 
+import b200cnn
 from b200cnn import _lib
 from oracle import ref_numpy as rn
 
@@ -319,3 +320,29 @@ def test_conv2_pool2_fused_forward(lib, B):
                                               arg2.data_ptr(), B, H, W, Cc, Cc, stream()))
     torch.cuda.synchronize()
     assert torch.equal(pool, pool2) and torch.equal(arg, arg2)
+
+
+def test_forward_backward_one_call_equals_two_calls():
+    """b200_forward_backward overlaps the FC2/FC3 parameter gradients with FC1's input gradient (side stream);
+    loss, accuracy and every gradient must match the two separate calls -- eagerly and replayed from a CUDA graph.
+    Gradients accumulated with atomics (conv1 filter, conv biases) may differ in the last bits between runs."""
+    rng = np.random.default_rng(77)
+    B = 128
+    img = dev(np.clip(np.rint(rng.normal(8.0, 2.5, (B, 3, 32, 32))), 0, 255).astype(np.uint8))
+    lab = dev(rng.integers(0, 10, (B,)).astype(np.int32))
+    params = rn.init_params(3)
+    e1, e2, e3 = (b200cnn.TrainStepEngine(batch=B, mode="bf16") for _ in range(3))
+    for e in (e1, e2, e3):
+        e.load_params(params)
+    e1.forward(img, lab); e1.backward()
+    e2.forward_backward(img, lab)
+    e3.forward_backward(img, lab)          # first call eager: creates the side streams
+    g = e3.capture(lambda: e3.forward_backward(img, lab))
+    e3.grads.zero_()
+    g.replay()
+    torch.cuda.synchronize()
+    for e in (e2, e3):
+        assert torch.equal(e1.loss(), e.loss()) and torch.equal(e1.n_correct(), e.n_correct())
+        assert relerr(e.grads.cpu().numpy(), e1.grads.cpu().numpy()) <= 1e-6
+        for name in ("full_weight_2", "full_weight_3", "full_weight_1", "conv2_kernel"):
+            assert torch.equal(e.grad(name), e1.grad(name)), name
