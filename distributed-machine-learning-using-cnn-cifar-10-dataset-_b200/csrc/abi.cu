@@ -286,7 +286,7 @@ static int forward_impl(b200_handle h, const uint8_t* images, const int32_t* lab
                             h->ptr<float>("loss"), h->ptr<int32_t>("n_correct"), h->ptr<int32_t>("n_bad"),
                             h->G(P_FW2), h->G(P_FB2), h->G(P_FW3), h->G(P_FB3), h->G(P_FB1),
                             h->ptr<void>("tail_scratch"), h->grads, (int)(h->p_off[P_B2] + h->p_size[P_B2]), c.batch, c.f1, c.f2,
-                            c.n_cls, st, true, fork ? h->side[0] : nullptr, h->ev_fork[0]));
+                            c.n_cls, st, true, fork ? h->side[0] : nullptr, h->ev_fork[0], !h->profiling));
     if (fork && !defer_tail) {
       B200_CUDA_TRY(cudaEventRecord(h->ev_join[0], h->side[0]));
       B200_CUDA_TRY(cudaStreamWaitEvent(st, h->ev_join[0], 0));

@@ -10,9 +10,11 @@
 //   grads kernel (output-parallel, deterministic sums over the batch):
 //                                 dW2 = full1^T dfull2, db2, dW3 = full2^T dlogits, db3,
 //                                 db1 = colsum(dfull1), loss = mean, n_correct, n_bad
-// SIMT with fp32 accumulation: 28 MFLOP per 128 images is nowhere near worth a tensor-core pipeline.
-// W2 is held in shared memory as bf16 (it is read by two products; fp32 would not fit); activations,
-// softmax, loss and every sum stay fp32.
+// The rows kernel is row-parallel for latency: 8 (16 for large batches) batch rows per CTA, so 128 images
+// spread over 16 SMs.  Its two products with W2 (FC2 forward and dfull1) run on warp-level bf16 MMAs
+// (m16n8k16, fp32 accumulate) out of a bf16 image of W2 resident in shared memory -- rows this few are far
+// below a tcgen05 tile (M >= 64).  Operands of those two products (full1, dfull2, W2) are rounded to bf16
+// like every other tensor-core operand of the bf16 mode; FC3, softmax, loss and every sum stay fp32.
 #include <algorithm>
 
 #include <cuda_bf16.h>
@@ -46,7 +48,7 @@ struct TailArgs {
   const float* b1;
   float* full1;                    // [B,F1]  in (n_part == 0) or out
   const float *w2, *b2, *w3, *b3;
-  const __nv_bfloat16* w2b;        // W2 as the bf16 [F1][F2+2] image (w2_to_bf16_kernel)
+  const __nv_bfloat16* w2b;        // W2 as the bf16 [F1][F2+8] image (w2_to_bf16_kernel)
   const int32_t* labels;
   float *full2, *logits, *dlogits, *dfull2, *dfull1;
   int32_t* pred;
@@ -64,38 +66,76 @@ __device__ __forceinline__ void stage_tile(float* dst, const float* src, int nfl
 
 #define TL(i) do { if (a.timeline && blockIdx.x == 0 && threadIdx.x == 0) a.timeline[i] = clock64(); } while (0)
 
-// W2 fp32 [F1][F2] -> bf16 image [F1][F2+2] (row stride odd in 32-bit words: conflict-free when every
-// thread walks its own row), fetched by the rows kernel with bulk copies
+// W2 fp32 [F1][F2] -> bf16 image [F1][F2+8]: rows stay 16-byte aligned (ldmatrix) and shift by four banks per
+// row (conflict-free fragment loads); fetched by the rows kernel with bulk copies
 __global__ void w2_to_bf16_kernel(const float* __restrict__ w2, __nv_bfloat16* __restrict__ out, int F1, int F2) {
-  const int WS = F2 + 2;
+  const int WS = F2 + 8;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < F1 * WS; i += gridDim.x * blockDim.x) {
     const int k = i / WS, n = i - k * WS;
     out[i] = __float2bfloat16(n < F2 ? __ldg(w2 + (size_t)k * F2 + n) : 0.f);
   }
 }
 
-template <int R>
+// warp-level bf16 MMA, D[16x8] += A[16x16] B[16x8], fp32 accumulate.  The tail is row-parallel over many SMs
+// for latency (8 or 16 batch rows per CTA), far below the 64-row minimum of a tcgen05 tile.
+__device__ __forceinline__ void mma16816(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                         uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+// two 8x8 bf16 matrices, transposed on the way in: lanes 0-7 / 8-15 give the row addresses of matrix 0 / 1
+__device__ __forceinline__ void ldmatrix_x2_trans(uint32_t& r0, uint32_t& r1, uint32_t saddr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x2.trans.shared.b16 {%0,%1}, [%2];" : "=r"(r0), "=r"(r1) : "r"(saddr));
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+struct TailSmem {          // byte offsets into dynamic shared memory
+  int wb, xb, d2b, f2s, w3s, w3t, dls, stat, total;
+};
+__host__ __device__ inline TailSmem tail_smem(int RM, int F1, int F2, int NC) {
+  TailSmem s;
+  int o = 16;                                   // mbarrier first
+  s.wb = o;  o += F1 * (F2 + 8) * 2;            // bf16 W2 image
+  s.xb = o;  o += 16 * (F1 + 8) * 2;            // bf16 full1 rows (A operand of FC2); rows >= RM stay zero
+  s.d2b = o; o += 16 * (F2 + 8) * 2;            // bf16 dfull2 rows (A operand of the dfull1 product)
+  s.f2s = o; o += RM * F2 * 4;                  // fp32 full2 rows
+  s.w3s = o; o += ((F2 * NC + 3) & ~3) * 4;     // W3
+  s.w3t = o; o += ((F2 * NC + 3) & ~3) * 4;     // W3 transposed [class][k]
+  s.dls = o; o += RM * kMaxCls * 4;             // dlogits
+  s.stat = o; o += RM * 4 * 4;                  // per row: loss, correct, bad label
+  s.total = o;
+  return s;
+}
+
+// RM: rows of the MMA tile that can hold batch rows (8: the upper half of the 16-row tile is zero; 16).  The CTA
+// handles a.R <= RM batch rows.  T1: 8-column tiles of full2 per warp (F2 <= 64 * T1).
+template <int RM, int T1>
 __global__ void __launch_bounds__(RT) fc_tail_rows_kernel(TailArgs a) {
-  extern __shared__ __align__(16) float sm[];
-  const int WS = a.F2 + 2;
-  float* xsI = sm;                      // [F1][R]   full1 rows, row index innermost (one broadcast LDS.128 per k)
-  float* d1s = xsI + R * a.F1;          // [R][F1]   dfull1 rows
-  float* f2s = d1s + R * a.F1;          // [R][F2]
-  float* d2I = f2s + R * a.F2;          // [F2][R]   dfull2, row index innermost
-  float* lgs = d2I + R * a.F2;          // [R][16] logits
-  float* dls = lgs + R * kMaxCls;       // [R][16] dlogits
-  float* misc = dls + R * kMaxCls;      // [4] loss, ok, bad
-  float* w3s = misc + 4;                // [F2][NC]
-  uint64_t* bar = reinterpret_cast<uint64_t*>(w3s + ((a.F2 * a.NC + 3) & ~3));
-  __nv_bfloat16* wb = reinterpret_cast<__nv_bfloat16*>(bar + 2);      // [F1][WS] W2 in bf16, resident for both passes
-  const int tid = threadIdx.x;
-  const int r0 = blockIdx.x * R;
-  const int nr = min(R, a.B - r0);
+  extern __shared__ __align__(16) uint8_t smraw[];
+  const TailSmem L = tail_smem(RM, a.F1, a.F2, a.NC);
+  const int WS = a.F2 + 8, XS = a.F1 + 8, DS = a.F2 + 8;      // pitches in bf16 elements
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smraw);
+  __nv_bfloat16* wb = reinterpret_cast<__nv_bfloat16*>(smraw + L.wb);
+  __nv_bfloat16* xb = reinterpret_cast<__nv_bfloat16*>(smraw + L.xb);
+  __nv_bfloat16* d2b = reinterpret_cast<__nv_bfloat16*>(smraw + L.d2b);
+  float* f2s = reinterpret_cast<float*>(smraw + L.f2s);
+  float* w3s = reinterpret_cast<float*>(smraw + L.w3s);
+  float* w3t = reinterpret_cast<float*>(smraw + L.w3t);
+  float* dls = reinterpret_cast<float*>(smraw + L.dls);
+  float* stat = reinterpret_cast<float*>(smraw + L.stat);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+  const int r0 = blockIdx.x * a.R;
+  const int nr = min(a.R, a.B - r0);
+  float* part = a.part + (size_t)blockIdx.x * part_len(a.F1, a.F2, a.NC);
 
   if (a.zero_ptr)     // every CTA clears its slice of the buffer a later kernel accumulates into
     for (int i = blockIdx.x * RT + tid; i < a.zero_n; i += gridDim.x * RT) a.zero_ptr[i] = 0.f;
   TL(0);
-  // ---- W2 (bf16 image, 149 KB) -> shared memory with bulk copies; lands while full1 is assembled ------
+  // ---- W2 (bf16 image, 150 KB) -> shared memory with bulk copies; lands while full1 is assembled ------
   if (tid == 0) {
     tc::mbar_init(tc::smem_u32(bar), 1);
     tc::fence_mbar_init();
@@ -105,183 +145,312 @@ __global__ void __launch_bounds__(RT) fc_tail_rows_kernel(TailArgs a) {
       tc::bulk_g2s(tc::smem_u32(wb) + off, reinterpret_cast<const uint8_t*>(a.w2b) + off, min(32768u, total - off),
                    tc::smem_u32(bar));
   }
-  for (int i = tid; i < a.F2 * a.NC; i += RT) w3s[i] = __ldg(a.w3 + i);
+  // small operands used much later are requested now (nothing waits on them here)
+  const float b3v = lane < a.NC ? __ldg(a.b3 + lane) : 0.f;
+  int ylab[RM / 8];
+#pragma unroll
+  for (int q = 0; q < RM / 8; ++q) ylab[q] = warp + 8 * q < nr ? __ldg(a.labels + r0 + warp + 8 * q) : 0;
+  float2 bias2[T1];
+#pragma unroll
+  for (int i = 0; i < T1; ++i)
+    bias2[i] = __ldg(reinterpret_cast<const float2*>(a.b2 + min(warp + 8 * i, a.F2 / 8 - 1) * 8 + 2 * t));
+  constexpr int W3B = 8;
+  float w3v[W3B];
+  const int n3 = a.F2 * a.NC;
+#pragma unroll
+  for (int u = 0; u < W3B; ++u) w3v[u] = tid + u * RT < n3 ? __ldg(a.w3 + tid + u * RT) : 0.f;
   TL(1);
-  // ---- full1 rows: add the split-K partials of FC1, bias, ReLU ------------------------------------
+  // ---- full1 rows: add the split-K partials of FC1, bias, ReLU; keep a bf16 copy as the MMA operand.  Three
+  //      slots per thread at a time, the loads of all their splits in flight together ----------------------------
   const int f14 = a.F1 / 4;
-  for (int i = tid; i < R * f14; i += RT) {
-    const int r = i / f14, k4 = i - r * f14;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (r < nr) {
-      float4* dst = reinterpret_cast<float4*>(a.full1 + (size_t)(r0 + r) * a.F1) + k4;
+  // launched with programmatic stream serialization, everything above ran while the producer of fc1_part (FC1)
+  // was still executing; from here on its output is needed (no-op for an ordinary launch)
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (RM == 8)      // upper half of the A tile
+    for (int i = tid; i < XS; i += RT) reinterpret_cast<uint4*>(xb + 8 * XS)[i] = make_uint4(0, 0, 0, 0);
+  for (int i0 = tid; i0 < RM * f14; i0 += 3 * RT) {
+    // slots past the end / rows past the batch read a valid address and are not stored: no branch around the loads
+    float4 v[3];
+    const float4* p[3];
+    int rr[3], kk[3];
+    bool on[3];
+#pragma unroll
+    for (int u = 0; u < 3; ++u) {
+      const int i = min(i0 + u * RT, RM * f14 - 1);
+      rr[u] = i / f14; kk[u] = i - rr[u] * f14;
+      on[u] = i0 + u * RT < RM * f14;
+      const int row = r0 + min(rr[u], nr - 1);
       if (a.n_part > 0) {
-        v = __ldg(reinterpret_cast<const float4*>(a.b1) + k4);
-        const float4* p = reinterpret_cast<const float4*>(a.fc1_part + (size_t)(r0 + r) * a.F1) + k4;
-        const size_t stride4 = (size_t)a.B * a.F1 / 4;
-#pragma unroll 4
-        for (int s = 0; s < a.n_part; ++s) {          // loads are independent: several splits in flight
-          const float4 t = __ldg(p + s * stride4);
-          v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
-        }
-        v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f);
-        *dst = v;
+        p[u] = reinterpret_cast<const float4*>(a.fc1_part) + (size_t)row * f14 + kk[u];
+        v[u] = __ldg(reinterpret_cast<const float4*>(a.b1) + kk[u]);
       } else {
-        v = *dst;
+        p[u] = reinterpret_cast<const float4*>(a.full1) + (size_t)row * f14 + kk[u];
+        v[u] = *p[u];
       }
     }
-    xsI[(4 * k4 + 0) * R + r] = v.x; xsI[(4 * k4 + 1) * R + r] = v.y;
-    xsI[(4 * k4 + 2) * R + r] = v.z; xsI[(4 * k4 + 3) * R + r] = v.w;
+    if (a.n_part > 0) {
+      const size_t stride4 = (size_t)a.B * f14;
+#pragma unroll 4
+      for (int s = 0; s < a.n_part; ++s) {
+#pragma unroll
+        for (int u = 0; u < 3; ++u) {
+          const float4 q = __ldg(p[u] + s * stride4);
+          v[u].x += q.x; v[u].y += q.y; v[u].z += q.z; v[u].w += q.w;
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 3; ++u) {
+      if (on[u]) {
+        if (rr[u] < nr) {
+          if (a.n_part > 0) {
+            v[u].x = fmaxf(v[u].x, 0.f); v[u].y = fmaxf(v[u].y, 0.f); v[u].z = fmaxf(v[u].z, 0.f); v[u].w = fmaxf(v[u].w, 0.f);
+            reinterpret_cast<float4*>(a.full1 + (size_t)(r0 + rr[u]) * a.F1)[kk[u]] = v[u];
+          }
+        } else {
+          v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        *reinterpret_cast<uint2*>(xb + rr[u] * XS + 4 * kk[u]) =
+            make_uint2(pack_bf16x2(v[u].x, v[u].y), pack_bf16x2(v[u].z, v[u].w));
+      }
+    }
+  }
+  // W3 in both orientations: [k][class] for the dfull2 product, [class][k] for the logits
+#pragma unroll
+  for (int u = 0; u < W3B; ++u) {
+    const int i = tid + u * RT;
+    if (i < n3) { const int k = i / a.NC; w3s[i] = w3v[u]; w3t[(i - k * a.NC) * a.F2 + k] = w3v[u]; }
+  }
+  for (int i = tid + W3B * RT; i < n3; i += RT) {        // wider layers than the reference's: the rest, unhurried
+    const float v = __ldg(a.w3 + i);
+    const int k = i / a.NC;
+    w3s[i] = v; w3t[(i - k * a.NC) * a.F2 + k] = v;
   }
   __syncthreads();
   tc::mbar_wait(tc::smem_u32(bar), 0);
   TL(2);
-  // ---- pass 1 over W2: full2 = relu(x W2 + b2), thread <-> column n ------------------------------------
-  if (tid < a.F2) {
-    float acc[R];
+  // ---- full2 = relu(full1 W2 + b2): warp w owns the 8-column tiles w, w+8, ...  (a tile index past the end is
+  //      clamped: computed again, never stored).  Fragments of the next k-step are fetched before the MMAs of
+  //      the current one ------------------------------------------------------------------------------------
+  {
+    const int nt = a.F2 / 8;
+    float c[T1][4];
+    uint32_t wrow[T1];
+    const uint32_t* xr0 = reinterpret_cast<const uint32_t*>(xb) + g * (XS / 2) + t;
+    const uint32_t* xr1 = xr0 + 8 * (XS / 2);
 #pragma unroll
-    for (int r = 0; r < R; ++r) acc[r] = 0.f;
-#pragma unroll 8
-    for (int k = 0; k < a.F1; ++k) {
-      const float wv = __bfloat162float(wb[k * WS + tid]);
-      float xr[R];
-#pragma unroll
-      for (int q = 0; q < R / 4; ++q) *reinterpret_cast<float4*>(xr + 4 * q) = *reinterpret_cast<const float4*>(xsI + k * R + 4 * q);
-#pragma unroll
-      for (int r = 0; r < R; ++r) acc[r] = fmaf(xr[r], wv, acc[r]);
+    for (int i = 0; i < T1; ++i) {
+      c[i][0] = c[i][1] = c[i][2] = c[i][3] = 0.f;
+      wrow[i] = tc::smem_u32(wb) + (uint32_t)((lane & 15) * WS + min(warp + 8 * i, nt - 1) * 8) * 2;
     }
-    const float b = __ldg(a.b2 + tid);
+    const uint32_t kstep = (uint32_t)(16 * WS) * 2;
+    uint32_t af0[4], af1[4], bf0[T1][2], bf1[T1][2];
+    auto load = [&](int ks, uint32_t (&af)[4], uint32_t (&bf)[T1][2]) {
+      af[0] = xr0[ks * 8]; af[2] = xr0[ks * 8 + 4];
+      af[1] = RM == 16 ? xr1[ks * 8] : 0u; af[3] = RM == 16 ? xr1[ks * 8 + 4] : 0u;
 #pragma unroll
-    for (int r = 0; r < R; ++r) {
-      const float v = fmaxf(acc[r] + b, 0.f);
-      f2s[r * a.F2 + tid] = v;
-      if (r < nr) a.full2[(size_t)(r0 + r) * a.F2 + tid] = v;
+      for (int i = 0; i < T1; ++i) ldmatrix_x2_trans(bf[i][0], bf[i][1], wrow[i] + ks * kstep);
+    };
+    auto mmas = [&](const uint32_t (&af)[4], const uint32_t (&bf)[T1][2]) {
+#pragma unroll
+      for (int i = 0; i < T1; ++i) mma16816(c[i], af[0], af[1], af[2], af[3], bf[i][0], bf[i][1]);
+    };
+    const int nks = a.F1 / 16;                        // even: F1 % 32 == 0
+    load(0, af0, bf0);
+#pragma unroll 1
+    for (int ks = 0; ks < nks; ks += 2) {
+      load(ks + 1, af1, bf1);
+      mmas(af0, bf0);
+      if (ks + 2 < nks) load(ks + 2, af0, bf0);
+      mmas(af1, bf1);
+    }
+#pragma unroll
+    for (int i = 0; i < T1; ++i) {
+      const int j = warp + 8 * i;
+      if (j < nt) {
+        const int n = j * 8 + 2 * t;
+        const float2 v0 = make_float2(fmaxf(c[i][0] + bias2[i].x, 0.f), fmaxf(c[i][1] + bias2[i].y, 0.f));
+        *reinterpret_cast<float2*>(f2s + g * a.F2 + n) = v0;
+        if (g < nr) *reinterpret_cast<float2*>(a.full2 + (size_t)(r0 + g) * a.F2 + n) = v0;
+        if (RM == 16) {
+          const float2 v1 = make_float2(fmaxf(c[i][2] + bias2[i].x, 0.f), fmaxf(c[i][3] + bias2[i].y, 0.f));
+          *reinterpret_cast<float2*>(f2s + (g + 8) * a.F2 + n) = v1;
+          if (g + 8 < nr) *reinterpret_cast<float2*>(a.full2 + (size_t)(r0 + g + 8) * a.F2 + n) = v1;
+        }
+      }
     }
   }
   __syncthreads();
   TL(3);
-  // ---- logits = relu(full2 W3 + b3): one thread per (row, class), W3 from shared memory ---------------
-  if (tid < R * a.NC) {
-    const int r = tid / a.NC, c = tid - r * a.NC;
-    float s0 = 0.f, s1 = 0.f;
-    for (int k = 0; k + 1 < a.F2; k += 2) {
-      s0 = fmaf(f2s[r * a.F2 + k], w3s[k * a.NC + c], s0);
-      s1 = fmaf(f2s[r * a.F2 + k + 1], w3s[(k + 1) * a.NC + c], s1);
+  // ---- logits = relu(full2 W3 + b3) and the softmax cross-entropy of a row, all inside one warp: lanes split K,
+  //      a butterfly leaves every class sum in every lane, lane c then owns class c -----------------------------
+#pragma unroll
+  for (int q = 0; q < RM / 8; ++q) {
+    const int r = warp + 8 * q;
+    float acc[kMaxCls];
+#pragma unroll
+    for (int c = 0; c < kMaxCls; ++c) acc[c] = 0.f;
+    for (int k = lane; k < a.F2; k += 32) {
+      const float f = f2s[r * a.F2 + k];
+#pragma unroll
+      for (int c = 0; c < kMaxCls; ++c)
+        if (c < a.NC) acc[c] = fmaf(f, w3t[c * a.F2 + k], acc[c]);
     }
-    if (a.F2 & 1) s0 = fmaf(f2s[r * a.F2 + a.F2 - 1], w3s[(a.F2 - 1) * a.NC + c], s0);
-    lgs[r * kMaxCls + c] = fmaxf(s0 + s1 + __ldg(a.b3 + c), 0.f);
+    float z = 0.f;
+#pragma unroll
+    for (int c = 0; c < kMaxCls; ++c) {
+      if (c < a.NC) {
+        const float s = warp_sum(acc[c]);
+        if (lane == c) z = s;
+      }
+    }
+    const bool act = lane < a.NC;
+    z = act ? fmaxf(z + b3v, 0.f) : 0.f;
+    float m = act ? z : -INFINITY;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    const int am = __ffs(__ballot_sync(0xffffffffu, act && z == m)) - 1;     // first maximal index (:173)
+    const float e = act ? expf(z - m) : 0.f;
+    const float s = warp_sum(e);
+    const int y = ylab[q];
+    const bool valid = (unsigned)y < (unsigned)a.NC;
+    const float zy = __shfl_sync(0xffffffffu, z, valid ? y : 0);
+    float d = 0.f;
+    if (r < nr) {
+      if (act) {
+        d = (valid && z > 0.f) ? (e / s - (lane == y ? 1.f : 0.f)) / (float)a.B : 0.f;
+        a.logits[(size_t)(r0 + r) * a.NC + lane] = z;
+        a.dlogits[(size_t)(r0 + r) * a.NC + lane] = d;
+      }
+      if (lane == 0) {
+        stat[r * 4 + 0] = valid ? logf(s) - (zy - m) : 0.f;
+        stat[r * 4 + 1] = (valid && am == y) ? 1.f : 0.f;
+        stat[r * 4 + 2] = valid ? 0.f : 1.f;
+        a.pred[r0 + r] = am;
+      }
+    } else if (lane == 0) {
+      stat[r * 4 + 0] = stat[r * 4 + 1] = stat[r * 4 + 2] = 0.f;
+    }
+    if (lane < kMaxCls) dls[r * kMaxCls + lane] = d;       // zero for classes >= NC and rows >= nr
   }
   __syncthreads();
   TL(4);
-  // ---- softmax cross-entropy per row (R <= 32 rows: one lane each in warp 0) -----------------------------
-  if (tid < 32) {
-    const int r = tid;
-    float lossv = 0.f;
-    int okv = 0, badv = 0;
-    if (r < nr) {
-      float m = -INFINITY;
-      int am = 0;
-      for (int c = 0; c < a.NC; ++c) {
-        const float z = lgs[r * kMaxCls + c];
-        if (z > m) { m = z; am = c; }                    // strict '>' = first maximal index (:173)
-      }
-      float s = 0.f;
-      for (int c = 0; c < a.NC; ++c) s += expf(lgs[r * kMaxCls + c] - m);
-      const int y = a.labels[r0 + r];
-      const bool valid = (unsigned)y < (unsigned)a.NC;
-      const float inv = 1.f / s, invB = 1.f / (float)a.B;
-      for (int c = 0; c < a.NC; ++c) {
-        const float lg = lgs[r * kMaxCls + c];
-        const float d = (valid && lg > 0.f) ? (expf(lg - m) * inv - (c == y ? 1.f : 0.f)) * invB : 0.f;
-        dls[r * kMaxCls + c] = d;
-        a.logits[(size_t)(r0 + r) * a.NC + c] = lg;
-        a.dlogits[(size_t)(r0 + r) * a.NC + c] = d;
-      }
-      if (valid) lossv = logf(s) - (lgs[r * kMaxCls + y] - m);
-      else badv = 1;
-      okv = (valid && am == y) ? 1 : 0;
-      a.pred[r0 + r] = am;
-    } else if (r < R) {
-      for (int c = 0; c < a.NC; ++c) dls[r * kMaxCls + c] = 0.f;
-    }
-    lossv = warp_sum(lossv);
-    for (int o = 16; o > 0; o >>= 1) {
-      okv += __shfl_xor_sync(0xffffffffu, okv, o);
-      badv += __shfl_xor_sync(0xffffffffu, badv, o);
-    }
-    if (tid == 0) { misc[0] = lossv; misc[1] = (float)okv; misc[2] = (float)badv; }
-  }
-  __syncthreads();
   TL(5);
-  // ---- dfull2 = (dlogits W3^T) * [full2 > 0] -----------------------------------------------------------
+  // ---- dfull2 = (dlogits W3^T) * [full2 > 0]; thread <-> column n; also this CTA's db2 / dW3 / db3 sums ------
   if (tid < a.F2) {
-    float w[kMaxCls];
+    float w[kMaxCls], t3[kMaxCls];
 #pragma unroll
-    for (int c = 0; c < kMaxCls; ++c) w[c] = c < a.NC ? w3s[tid * a.NC + c] : 0.f;
+    for (int c = 0; c < kMaxCls; ++c) { w[c] = c < a.NC ? w3s[tid * a.NC + c] : 0.f; t3[c] = 0.f; }
+    float colsum = 0.f;
 #pragma unroll
-    for (int r = 0; r < R; ++r) {
+    for (int r = 0; r < RM; ++r) {
+      const float f2v = f2s[r * a.F2 + tid];
+      float dv[kMaxCls];
+#pragma unroll
+      for (int c4 = 0; c4 < kMaxCls / 4; ++c4)
+        *reinterpret_cast<float4*>(dv + 4 * c4) = *reinterpret_cast<const float4*>(dls + r * kMaxCls + 4 * c4);
       float s = 0.f;
 #pragma unroll
-      for (int c = 0; c < kMaxCls; ++c) s = fmaf(c < a.NC ? dls[r * kMaxCls + c] : 0.f, w[c], s);
-      s = f2s[r * a.F2 + tid] > 0.f ? s : 0.f;
-      d2I[tid * R + r] = s;
-      if (r < nr) a.dfull2[(size_t)(r0 + r) * a.F2 + tid] = s;
-    }
-  }
-  __syncthreads();
-  TL(6);
-  // ---- pass 2 over W2: dfull1 = (dfull2 W2^T) * [full1 > 0]; thread <-> its own W2 row k -----------------
-  for (int k = tid; k < a.F1; k += RT) {
-    float acc[R];
-#pragma unroll
-    for (int r = 0; r < R; ++r) acc[r] = 0.f;
-    const __nv_bfloat162* wrow = reinterpret_cast<const __nv_bfloat162*>(wb + k * WS);
-#pragma unroll 4
-    for (int n2 = 0; n2 < a.F2 / 2; ++n2) {
-      const float2 wv = __bfloat1622float2(wrow[n2]);
-      float d0[R], d1[R];
-#pragma unroll
-      for (int q = 0; q < R / 4; ++q) {
-        *reinterpret_cast<float4*>(d0 + 4 * q) = *reinterpret_cast<const float4*>(d2I + (2 * n2) * R + 4 * q);
-        *reinterpret_cast<float4*>(d1 + 4 * q) = *reinterpret_cast<const float4*>(d2I + (2 * n2 + 1) * R + 4 * q);
+      for (int c = 0; c < kMaxCls; ++c) {
+        s = fmaf(dv[c], w[c], s);
+        t3[c] = fmaf(f2v, dv[c], t3[c]);
       }
-#pragma unroll
-      for (int r = 0; r < R; ++r) acc[r] = fmaf(d0[r], wv.x, fmaf(d1[r], wv.y, acc[r]));
+      s = f2v > 0.f ? s : 0.f;
+      d2b[r * DS + tid] = __float2bfloat16(s);
+      if (r < nr) a.dfull2[(size_t)(r0 + r) * a.F2 + tid] = s;
+      colsum += s;
     }
+    if (RM == 8)
 #pragma unroll
-    for (int r = 0; r < R; ++r) d1s[r * a.F1 + k] = xsI[k * R + r] > 0.f ? acc[r] : 0.f;
-  }
-  __syncthreads();
-  TL(7);
-  // ---- write dfull1 rows and this CTA's partial sums over its rows ---------------------------------------
-  for (int i = tid; i < nr * a.F1; i += RT) a.dfull1[(size_t)r0 * a.F1 + i] = d1s[i];
-  float* part = a.part + (size_t)blockIdx.x * part_len(a.F1, a.F2, a.NC);
-  for (int k = tid; k < a.F1; k += RT) {
-    float s = 0.f;
-#pragma unroll
-    for (int r = 0; r < R; ++r) s += d1s[r * a.F1 + k];     // rows >= nr are zero (dls = 0 -> d2 = 0 -> d1 = 0)
-    part[k] = s;
-  }
-  if (tid < a.F2) {
-    float s = 0.f;
-#pragma unroll
-    for (int r = 0; r < R; ++r) s += d2I[tid * R + r];
-    part[a.F1 + tid] = s;
+      for (int r = 8; r < 16; ++r) d2b[r * DS + tid] = __float2bfloat16(0.f);
+    part[a.F1 + tid] = colsum;
     float* pw3 = part + a.F1 + a.F2 + 16 + tid * a.NC;
-    for (int c = 0; c < a.NC; ++c) {
-      float t3 = 0.f;
 #pragma unroll
-      for (int r = 0; r < R; ++r) t3 = fmaf(f2s[r * a.F2 + tid], dls[r * kMaxCls + c], t3);
-      pw3[c] = t3;
-    }
+    for (int c = 0; c < kMaxCls; ++c)
+      if (c < a.NC) pw3[c] = t3[c];
   }
   if (tid < 16) {
     float s = 0.f;
     if (tid < a.NC)
 #pragma unroll
-      for (int r = 0; r < R; ++r) s += dls[r * kMaxCls + tid];
+      for (int r = 0; r < RM; ++r) s += dls[r * kMaxCls + tid];
     part[a.F1 + a.F2 + tid] = s;
   }
-  if (tid < 4) part[a.F1 + a.F2 + 16 + a.F2 * a.NC + tid] = tid < 3 ? misc[tid] : 0.f;
+  if (tid >= 32 && tid < 36) {
+    float s = 0.f;
+    if (tid < 35)
+#pragma unroll
+      for (int r = 0; r < RM; ++r) s += stat[r * 4 + (tid - 32)];
+    part[a.F1 + a.F2 + 16 + a.F2 * a.NC + (tid - 32)] = s;
+  }
+  __syncthreads();
+  TL(6);
+  // ---- dfull1 = (dfull2 W2^T) * [full1 > 0]: warp w owns the 8-column tiles w, w+8, ... of each 48-tile round
+  //      (tile indices past the end are clamped: computed again, never stored); the column sums over this CTA's
+  //      rows (db1 partial) come out of the accumulator fragments --------------------------------------------------
+  {
+    constexpr int T2 = 6;
+    const int nt = a.F1 / 8;
+    const uint32_t* dr0 = reinterpret_cast<const uint32_t*>(d2b) + g * (DS / 2) + t;
+    const uint32_t* dr1 = dr0 + 8 * (DS / 2);
+    const int nks = a.F2 / 16;
+    for (int jb = 0; jb < nt; jb += 8 * T2) {
+      float c[T2][4];
+      float2 m0[T2], m1[T2];
+      const uint32_t* wr[T2];
+#pragma unroll
+      for (int i = 0; i < T2; ++i) {
+        c[i][0] = c[i][1] = c[i][2] = c[i][3] = 0.f;
+        const int j = min(jb + warp + 8 * i, nt - 1);
+        wr[i] = reinterpret_cast<const uint32_t*>(wb) + (j * 8 + g) * (WS / 2) + t;
+        // the ReLU mask: full1 as this CTA wrote it above (ordinary loads, ordered by the barriers)
+        m0[i] = m1[i] = make_float2(0.f, 0.f);
+        if (g < nr) m0[i] = *reinterpret_cast<const float2*>(a.full1 + (size_t)(r0 + g) * a.F1 + j * 8 + 2 * t);
+        if (RM == 16 && g + 8 < nr)
+          m1[i] = *reinterpret_cast<const float2*>(a.full1 + (size_t)(r0 + g + 8) * a.F1 + j * 8 + 2 * t);
+      }
+      uint32_t af0[4], af1[4], bf0[T2][2], bf1[T2][2];
+      auto load = [&](int ks, uint32_t (&af)[4], uint32_t (&bf)[T2][2]) {
+        af[0] = dr0[ks * 8]; af[2] = dr0[ks * 8 + 4];
+        af[1] = RM == 16 ? dr1[ks * 8] : 0u; af[3] = RM == 16 ? dr1[ks * 8 + 4] : 0u;
+#pragma unroll
+        for (int i = 0; i < T2; ++i) { bf[i][0] = wr[i][ks * 8]; bf[i][1] = wr[i][ks * 8 + 4]; }
+      };
+      auto mmas = [&](const uint32_t (&af)[4], const uint32_t (&bf)[T2][2]) {
+#pragma unroll
+        for (int i = 0; i < T2; ++i) mma16816(c[i], af[0], af[1], af[2], af[3], bf[i][0], bf[i][1]);
+      };
+      load(0, af0, bf0);
+#pragma unroll 1
+      for (int ks = 0; ks < nks; ks += 2) {
+        const bool two = ks + 1 < nks;
+        if (two) load(ks + 1, af1, bf1);
+        mmas(af0, bf0);
+        if (ks + 2 < nks) load(ks + 2, af0, bf0);
+        if (two) mmas(af1, bf1);
+      }
+#pragma unroll
+      for (int i = 0; i < T2; ++i) {
+        const int j = jb + warp + 8 * i;
+        const int col = min(j, nt - 1) * 8 + 2 * t;
+        const float2 v0 = make_float2(m0[i].x > 0.f ? c[i][0] : 0.f, m0[i].y > 0.f ? c[i][1] : 0.f);
+        float s0 = v0.x, s1 = v0.y;
+        if (j < nt && g < nr) *reinterpret_cast<float2*>(a.dfull1 + (size_t)(r0 + g) * a.F1 + col) = v0;
+        if (RM == 16) {
+          const float2 v1 = make_float2(m1[i].x > 0.f ? c[i][2] : 0.f, m1[i].y > 0.f ? c[i][3] : 0.f);
+          if (j < nt && g + 8 < nr) *reinterpret_cast<float2*>(a.dfull1 + (size_t)(r0 + g + 8) * a.F1 + col) = v1;
+          s0 += v1.x; s1 += v1.y;
+        }
+#pragma unroll
+        for (int o = 4; o < 32; o <<= 1) {
+          s0 += __shfl_xor_sync(0xffffffffu, s0, o);
+          s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+        }
+        if (j < nt && g == 0) *reinterpret_cast<float2*>(part + col) = make_float2(s0, s1);
+      }
+    }
+  }
+  TL(7);
   TL(8);
 }
 
@@ -358,7 +527,7 @@ __global__ void __launch_bounds__(RT) fc_tail_grads_kernel(TailGradArgs a) {
   else if (v == o4 + 2) *a.n_bad = (int)(s + 0.5f);
 }
 
-int rows_per_cta(int B) { return B <= 1024 ? 4 : 8; }
+int rows_per_cta(int B) { return B <= 1024 ? 8 : 16; }
 long long* g_tail_timeline = nullptr;
 }  // namespace
 
@@ -369,14 +538,14 @@ static int64_t part_bytes(int B, int F1, int F2, int NC) {
 }
 // per-CTA partial sums + the bf16 image of W2
 int64_t fc_tail_scratch_bytes(int B, int F1, int F2, int NC) {
-  return part_bytes(B, F1, F2, NC) + round_up((int64_t)F1 * (F2 + 2) * 2, 256);
+  return part_bytes(B, F1, F2, NC) + round_up((int64_t)F1 * (F2 + 8) * 2, 256);
 }
 
 // the bf16 image of W2 inside `scratch` (same layout fc_tail expects); lets a caller build it early, off
 // the critical path, and then call fc_tail(..., w2_image_ready = true)
 int fc_tail_prepare_w2(const float* w2, void* scratch, int B, int F1, int F2, int NC, cudaStream_t st) {
   __nv_bfloat16* w2b = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<char*>(scratch) + part_bytes(B, F1, F2, NC));
-  w2_to_bf16_kernel<<<cdiv(F1 * (F2 + 2), 256), 256, 0, st>>>(w2, w2b, F1, F2);
+  w2_to_bf16_kernel<<<cdiv(F1 * (F2 + 8), 256), 256, 0, st>>>(w2, w2b, F1, F2);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
@@ -385,31 +554,62 @@ int fc_tail(const float* fc1_part, int n_part, const float* b1, float* full1, co
             const float* w3, const float* b3, const int32_t* labels, float* full2, float* logits, float* dlogits,
             float* dfull2, float* dfull1, int32_t* pred, float* loss, int32_t* n_correct, int32_t* n_bad, float* dw2,
             float* db2, float* dw3, float* db3, float* db1, void* scratch, float* zero_ptr, int zero_n, int B, int F1,
-            int F2, int NC, cudaStream_t st, bool w2_image_ready, cudaStream_t grads_stream, cudaEvent_t rows_done) {
+            int F2, int NC, cudaStream_t st, bool w2_image_ready, cudaStream_t grads_stream, cudaEvent_t rows_done,
+            bool overlap_producer) {
   B200_REQUIRE(B > 0 && NC > 0 && NC <= kMaxCls, "fc_tail: bad shape");
-  B200_REQUIRE(F1 % KT == 0 && F2 % 4 == 0 && F2 <= RT && F2 > 0, "fc_tail: needs f1 %% 32 == 0, f2 %% 4 == 0, f2 <= 256");
+  B200_REQUIRE(F1 % KT == 0 && F2 % 16 == 0 && F2 <= RT && F2 > 0, "fc_tail: needs f1 %% 32 == 0, f2 %% 16 == 0, f2 <= 256");
   const int R = rows_per_cta(B);
   const int nrc = cdiv(B, R);
   float* part = reinterpret_cast<float*>(scratch);
   __nv_bfloat16* w2b = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<char*>(scratch) + part_bytes(B, F1, F2, NC));
   if (!w2_image_ready) {
-    w2_to_bf16_kernel<<<cdiv(F1 * (F2 + 2), 256), 256, 0, st>>>(w2, w2b, F1, F2);
+    w2_to_bf16_kernel<<<cdiv(F1 * (F2 + 8), 256), 256, 0, st>>>(w2, w2b, F1, F2);
     B200_LAUNCH_CHECK();
   }
   TailArgs a{B, F1, F2, NC, R, fc1_part, n_part, b1, full1, w2, b2, w3, b3, w2b, labels, full2, logits, dlogits,
              dfull2, dfull1, pred, part, zero_ptr, zero_n, g_tail_timeline};
-  const size_t smem = (size_t)(2 * R * F1 + 2 * R * F2 + 2 * R * kMaxCls + 4 + ((F2 * NC + 3) & ~3) + 4) * 4 +
-                      (size_t)F1 * (F2 + 2) * 2;
-  B200_REQUIRE(smem <= 200 * 1024, "fc_tail: layer widths too large (%zu bytes of shared memory)", smem);
-  static bool attr = false;
-  if (!attr) {
-    B200_CUDA_TRY(cudaFuncSetAttribute(fc_tail_rows_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    B200_CUDA_TRY(cudaFuncSetAttribute(fc_tail_rows_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  const int RM = R <= 8 ? 8 : 16;              // rows of the MMA tile that carry batch rows
+  const size_t smem = (size_t)tail_smem(RM, F1, F2, NC).total;
+  B200_REQUIRE(smem <= 220 * 1024, "fc_tail: layer widths too large (%zu bytes of shared memory)", smem);
+  static bool grads_attr = false, rows_attr[2][5] = {};
+  if (!grads_attr) {
     B200_CUDA_TRY(cudaFuncSetAttribute(fc_tail_grads_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-    attr = true;
+    grads_attr = true;
   }
-  if (R == 4) fc_tail_rows_kernel<4><<<nrc, RT, smem, st>>>(a);
-  else fc_tail_rows_kernel<8><<<nrc, RT, smem, st>>>(a);
+  const int t1 = cdiv(F2, 64);
+  // overlap_producer: the kernel in front of this one on `st` produced fc1_part and allows its dependents to start
+  // early (griddepcontrol.launch_dependents); the rows kernel then fetches W2 / W3 / labels while it still runs
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(nrc); cfg.blockDim = dim3(RT); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = overlap_producer ? 1 : 0;
+#define B200_TAIL_LAUNCH(RM_, T1_)                                                                                   \
+  do {                                                                                                                 \
+    if (!rows_attr[RM_ / 16][T1_]) {                                                                                   \
+      B200_CUDA_TRY(cudaFuncSetAttribute(fc_tail_rows_kernel<RM_, T1_>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
+                                         220 * 1024));                                                                 \
+      rows_attr[RM_ / 16][T1_] = true;                                                                                 \
+    }                                                                                                                  \
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, fc_tail_rows_kernel<RM_, T1_>, a));                                         \
+  } while (0)
+  if (RM == 8) {
+    switch (t1) {
+      case 1: B200_TAIL_LAUNCH(8, 1); break;
+      case 2: B200_TAIL_LAUNCH(8, 2); break;
+      case 3: B200_TAIL_LAUNCH(8, 3); break;
+      default: B200_TAIL_LAUNCH(8, 4); break;
+    }
+  } else {
+    switch (t1) {
+      case 1: B200_TAIL_LAUNCH(16, 1); break;
+      case 2: B200_TAIL_LAUNCH(16, 2); break;
+      case 3: B200_TAIL_LAUNCH(16, 3); break;
+      default: B200_TAIL_LAUNCH(16, 4); break;
+    }
+  }
+#undef B200_TAIL_LAUNCH
   B200_LAUNCH_CHECK();
   TailGradArgs ga{B, F1, F2, NC, nrc, full1, dfull2, part, dw2, db2, dw3, db3, db1, loss, n_correct, n_bad};
   const size_t gsmem = (size_t)(2 * KT * F2 + 2 * KT * 4) * 4;

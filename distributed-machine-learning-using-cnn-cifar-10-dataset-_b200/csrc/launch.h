@@ -66,7 +66,7 @@ int fc_tail(const float* fc1_part, int n_part, const float* b1, float* full1, co
             float* dfull2, float* dfull1, int32_t* pred, float* loss, int32_t* n_correct, int32_t* n_bad, float* dw2,
             float* db2, float* dw3, float* db3, float* db1, void* scratch, float* zero_ptr, int zero_n, int B, int F1,
             int F2, int NC, cudaStream_t st, bool w2_image_ready = false, cudaStream_t grads_stream = nullptr,
-            cudaEvent_t rows_done = nullptr);
+            cudaEvent_t rows_done = nullptr, bool overlap_producer = false);
 int fc_tail_prepare_w2(const float* w2, void* scratch, int B, int F1, int F2, int NC, cudaStream_t st);
 // allreduce + SGD in one kernel over NVLink peer memory (p2p_update.cu)
 int p2p_allreduce_sgd(const void* const* peer_grads, void* const* peer_params, void* const* peer_pads,

@@ -46,6 +46,9 @@ struct Smem {
 
 template <int BN, bool A_MN, bool B_MN, typename TA, typename TB>
 __global__ void __launch_bounds__(288, 1) tc_gemm_kernel(GemmArgs g) {
+  // a consumer launched with programmatic stream serialization (the FC tail after FC1) may start its own
+  // input-independent prologue now; it still waits for this whole grid before it reads our output
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   using S = Smem<BN>;
   extern __shared__ __align__(128) uint8_t smem[];
   uint8_t* ctrl = smem + STAGES * S::STAGE;

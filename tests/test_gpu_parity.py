@@ -426,16 +426,20 @@ def test_fc_tail_fused(lib, B):
                             db3.data_ptr(), db1.data_ptr(), scr.data_ptr(), nb.value, B, F1, F2, NC, stream()))
     torch.cuda.synchronize()
     x = full1.astype(np.float64)
-    # the kernel keeps W2 in shared memory rounded to bf16 (both products that read it); everything
-    # else is fp32, so against the oracle on the rounded W2 the usual fp32 tolerance holds
-    w2 = torch.as_tensor(w2).to(torch.bfloat16).to(torch.float64).numpy()
-    f2 = np.maximum(x @ w2 + b2, 0)
+    # the two products with W2 (full2 and dfull1) run on bf16 tensor-core MMAs: their operands (W2, full1, dfull2)
+    # are rounded to bf16, accumulation and everything else is fp32 -- so against the oracle on the rounded
+    # operands the usual fp32 tolerance holds
+    bf = lambda v: torch.as_tensor(np.asarray(v, dtype=np.float32)).to(torch.bfloat16).to(torch.float64).numpy()
+    w2 = bf(w2)
+    f2 = np.maximum(bf(x) @ w2 + b2, 0)
     lg = np.maximum(f2 @ w3 + b3, 0)
     wl, _, back = rn.softmax_xent(lg, labels)
     _, wpred, wn = rn.batch_accuracy(lg, labels)
     d = back / B * (lg > 0)
     d2 = (d @ w3.T.astype(np.float64)) * (f2 > 0)
-    d1 = (d2 @ w2.T.astype(np.float64)) * (x > 0)
+    # dfull1's oracle starts from the GPU's own dfull2 (checked against d2 below): a last-bit difference in an fp32
+    # value that sits on a bf16 rounding boundary would otherwise flip the operand the MMA sees
+    d1 = (bf(dfull2.cpu().numpy()) @ w2.T.astype(np.float64)) * (x > 0)
     for got, want, name in ((full2, f2, "full2"), (logits, lg, "logits"), (dlogits, d, "dlogits"), (dfull2, d2, "dfull2"),
                             (dfull1, d1, "dfull1"), (dw2, x.T @ d2, "dw2"), (db2, d2.sum(0), "db2"),
                             (dw3, f2.T @ d, "dw3"), (db3, d.sum(0), "db3"), (db1, d1.sum(0), "db1")):
