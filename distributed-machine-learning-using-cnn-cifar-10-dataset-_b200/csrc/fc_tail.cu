@@ -88,6 +88,15 @@ __device__ __forceinline__ void mma16816(float (&c)[4], uint32_t a0, uint32_t a1
 __device__ __forceinline__ void ldmatrix_x2_trans(uint32_t& r0, uint32_t& r1, uint32_t saddr) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x2.trans.shared.b16 {%0,%1}, [%2];" : "=r"(r0), "=r"(r1) : "r"(saddr));
 }
+// four 8x8 bf16 matrices; lane l gives the address of row l % 8 of matrix l / 8
+__device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], uint32_t saddr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(saddr));
+}
+__device__ __forceinline__ void ldmatrix_x4_trans(uint32_t (&r)[4], uint32_t saddr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(saddr));
+}
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
@@ -104,7 +113,7 @@ __host__ __device__ inline TailSmem tail_smem(int RM, int F1, int F2, int NC) {
   s.d2b = o; o += 16 * (F2 + 8) * 2;            // bf16 dfull2 rows (A operand of the dfull1 product)
   s.f2s = o; o += RM * F2 * 4;                  // fp32 full2 rows
   s.w3s = o; o += ((F2 * NC + 3) & ~3) * 4;     // W3
-  s.w3t = o; o += ((F2 * NC + 3) & ~3) * 4;     // W3 transposed [class][k]
+  s.w3t = o; o += kMaxCls * F2 * 4;             // W3 transposed [16][k], rows >= NC zero
   s.dls = o; o += RM * kMaxCls * 4;             // dlogits
   s.stat = o; o += RM * 4 * 4;                  // per row: loss, correct, bad label
   s.total = o;
@@ -221,6 +230,7 @@ __global__ void __launch_bounds__(RT) fc_tail_rows_kernel(TailArgs a) {
     const int i = tid + u * RT;
     if (i < n3) { const int k = i / a.NC; w3s[i] = w3v[u]; w3t[(i - k * a.NC) * a.F2 + k] = w3v[u]; }
   }
+  for (int i = a.NC * a.F2 + tid; i < kMaxCls * a.F2; i += RT) w3t[i] = 0.f;
   for (int i = tid + W3B * RT; i < n3; i += RT) {        // wider layers than the reference's: the rest, unhurried
     const float v = __ldg(a.w3 + i);
     const int k = i / a.NC;
@@ -236,33 +246,36 @@ __global__ void __launch_bounds__(RT) fc_tail_rows_kernel(TailArgs a) {
     const int nt = a.F2 / 8;
     float c[T1][4];
     uint32_t wrow[T1];
-    const uint32_t* xr0 = reinterpret_cast<const uint32_t*>(xb) + g * (XS / 2) + t;
-    const uint32_t* xr1 = xr0 + 8 * (XS / 2);
+    // A fragments (16 x 16, both halves of the row tile: rows >= RM are zero in shared memory) and B fragments
+    // come in with one ldmatrix.x4 per 32 k: lane l addresses row l % 8 of 8x8 matrix l / 8
+    const uint32_t xrow = tc::smem_u32(xb) + (uint32_t)(((lane & 7) + ((lane >> 3) & 1) * 8) * XS + (lane >> 4) * 8) * 2;
 #pragma unroll
     for (int i = 0; i < T1; ++i) {
       c[i][0] = c[i][1] = c[i][2] = c[i][3] = 0.f;
-      wrow[i] = tc::smem_u32(wb) + (uint32_t)((lane & 15) * WS + min(warp + 8 * i, nt - 1) * 8) * 2;
+      wrow[i] = tc::smem_u32(wb) + (uint32_t)(lane * WS + min(warp + 8 * i, nt - 1) * 8) * 2;
     }
-    const uint32_t kstep = (uint32_t)(16 * WS) * 2;
-    uint32_t af0[4], af1[4], bf0[T1][2], bf1[T1][2];
-    auto load = [&](int ks, uint32_t (&af)[4], uint32_t (&bf)[T1][2]) {
-      af[0] = xr0[ks * 8]; af[2] = xr0[ks * 8 + 4];
-      af[1] = RM == 16 ? xr1[ks * 8] : 0u; af[3] = RM == 16 ? xr1[ks * 8 + 4] : 0u;
+    const uint32_t kstep = (uint32_t)(32 * WS) * 2;
+    uint32_t al0[4], ah0[4], al1[4], ah1[4], b0[T1][4], b1[T1][4];
+    auto load = [&](int kk, uint32_t (&al)[4], uint32_t (&ah)[4], uint32_t (&b)[T1][4]) {     // kk: index of the 32-k block
+      ldmatrix_x4(al, xrow + kk * 64);
+      ldmatrix_x4(ah, xrow + kk * 64 + 32);
 #pragma unroll
-      for (int i = 0; i < T1; ++i) ldmatrix_x2_trans(bf[i][0], bf[i][1], wrow[i] + ks * kstep);
+      for (int i = 0; i < T1; ++i) ldmatrix_x4_trans(b[i], wrow[i] + kk * kstep);
     };
-    auto mmas = [&](const uint32_t (&af)[4], const uint32_t (&bf)[T1][2]) {
+    auto mmas = [&](const uint32_t (&al)[4], const uint32_t (&ah)[4], const uint32_t (&b)[T1][4]) {
 #pragma unroll
-      for (int i = 0; i < T1; ++i) mma16816(c[i], af[0], af[1], af[2], af[3], bf[i][0], bf[i][1]);
+      for (int i = 0; i < T1; ++i) mma16816(c[i], al[0], al[1], al[2], al[3], b[i][0], b[i][1]);
+#pragma unroll
+      for (int i = 0; i < T1; ++i) mma16816(c[i], ah[0], ah[1], ah[2], ah[3], b[i][2], b[i][3]);
     };
-    const int nks = a.F1 / 16;                        // even: F1 % 32 == 0
-    load(0, af0, bf0);
+    const int nkb = a.F1 / 32;
+    load(0, al0, ah0, b0);
 #pragma unroll 1
-    for (int ks = 0; ks < nks; ks += 2) {
-      load(ks + 1, af1, bf1);
-      mmas(af0, bf0);
-      if (ks + 2 < nks) load(ks + 2, af0, bf0);
-      mmas(af1, bf1);
+    for (int kk = 0; kk < nkb; kk += 2) {
+      if (kk + 1 < nkb) load(kk + 1, al1, ah1, b1);
+      mmas(al0, ah0, b0);
+      if (kk + 2 < nkb) load(kk + 2, al0, ah0, b0);
+      if (kk + 1 < nkb) mmas(al1, ah1, b1);
     }
 #pragma unroll
     for (int i = 0; i < T1; ++i) {
@@ -290,20 +303,26 @@ __global__ void __launch_bounds__(RT) fc_tail_rows_kernel(TailArgs a) {
     float acc[kMaxCls];
 #pragma unroll
     for (int c = 0; c < kMaxCls; ++c) acc[c] = 0.f;
+#pragma unroll 2
     for (int k = lane; k < a.F2; k += 32) {
       const float f = f2s[r * a.F2 + k];
 #pragma unroll
-      for (int c = 0; c < kMaxCls; ++c)
-        if (c < a.NC) acc[c] = fmaf(f, w3t[c * a.F2 + k], acc[c]);
+      for (int c = 0; c < kMaxCls; ++c) acc[c] = fmaf(f, w3t[c * a.F2 + k], acc[c]);
     }
-    float z = 0.f;
+    // transposing butterfly: each step adds the partner's half of the remaining classes, so 8+4+2+1 (+1) shuffles
+    // leave the complete sum of class c in lanes 2c and 2c+1
 #pragma unroll
-    for (int c = 0; c < kMaxCls; ++c) {
-      if (c < a.NC) {
-        const float s = warp_sum(acc[c]);
-        if (lane == c) z = s;
+    for (int h = kMaxCls / 2, o = 16; h >= 1; h >>= 1, o >>= 1) {
+      const bool up = (lane & o) != 0;
+#pragma unroll
+      for (int i = 0; i < h; ++i) {
+        const float send = up ? acc[i] : acc[i + h];
+        const float keep = up ? acc[i + h] : acc[i];
+        acc[i] = keep + __shfl_xor_sync(0xffffffffu, send, o);
       }
     }
+    acc[0] += __shfl_xor_sync(0xffffffffu, acc[0], 1);
+    float z = __shfl_sync(0xffffffffu, acc[0], (lane & 15) << 1);        // lane c <- class c
     const bool act = lane < a.NC;
     z = act ? fmaxf(z + b3v, 0.f) : 0.f;
     float m = act ? z : -INFINITY;
@@ -391,43 +410,44 @@ __global__ void __launch_bounds__(RT) fc_tail_rows_kernel(TailArgs a) {
   {
     constexpr int T2 = 6;
     const int nt = a.F1 / 8;
-    const uint32_t* dr0 = reinterpret_cast<const uint32_t*>(d2b) + g * (DS / 2) + t;
-    const uint32_t* dr1 = dr0 + 8 * (DS / 2);
-    const int nks = a.F2 / 16;
+    const uint32_t drow = tc::smem_u32(d2b) + (uint32_t)(((lane & 7) + ((lane >> 3) & 1) * 8) * DS + (lane >> 4) * 8) * 2;
+    const int nkb = a.F2 / 32;
     for (int jb = 0; jb < nt; jb += 8 * T2) {
       float c[T2][4];
       float2 m0[T2], m1[T2];
-      const uint32_t* wr[T2];
+      uint32_t wr[T2];
 #pragma unroll
       for (int i = 0; i < T2; ++i) {
         c[i][0] = c[i][1] = c[i][2] = c[i][3] = 0.f;
         const int j = min(jb + warp + 8 * i, nt - 1);
-        wr[i] = reinterpret_cast<const uint32_t*>(wb) + (j * 8 + g) * (WS / 2) + t;
+        // B[k = n2][n = k1] = W2[k1][n2]: rows k1 of the image, 8 consecutive n2 per 16-byte row piece
+        wr[i] = tc::smem_u32(wb) + (uint32_t)((j * 8 + (lane & 7)) * WS + (lane >> 3) * 8) * 2;
         // the ReLU mask: full1 as this CTA wrote it above (ordinary loads, ordered by the barriers)
         m0[i] = m1[i] = make_float2(0.f, 0.f);
         if (g < nr) m0[i] = *reinterpret_cast<const float2*>(a.full1 + (size_t)(r0 + g) * a.F1 + j * 8 + 2 * t);
         if (RM == 16 && g + 8 < nr)
           m1[i] = *reinterpret_cast<const float2*>(a.full1 + (size_t)(r0 + g + 8) * a.F1 + j * 8 + 2 * t);
       }
-      uint32_t af0[4], af1[4], bf0[T2][2], bf1[T2][2];
-      auto load = [&](int ks, uint32_t (&af)[4], uint32_t (&bf)[T2][2]) {
-        af[0] = dr0[ks * 8]; af[2] = dr0[ks * 8 + 4];
-        af[1] = RM == 16 ? dr1[ks * 8] : 0u; af[3] = RM == 16 ? dr1[ks * 8 + 4] : 0u;
+      uint32_t al0[4], ah0[4], al1[4], ah1[4], b0[T2][4], b1[T2][4];
+      auto load = [&](int kk, uint32_t (&al)[4], uint32_t (&ah)[4], uint32_t (&b)[T2][4]) {
+        ldmatrix_x4(al, drow + kk * 64);
+        ldmatrix_x4(ah, drow + kk * 64 + 32);
 #pragma unroll
-        for (int i = 0; i < T2; ++i) { bf[i][0] = wr[i][ks * 8]; bf[i][1] = wr[i][ks * 8 + 4]; }
+        for (int i = 0; i < T2; ++i) ldmatrix_x4(b[i], wr[i] + kk * 64);
       };
-      auto mmas = [&](const uint32_t (&af)[4], const uint32_t (&bf)[T2][2]) {
+      auto mmas = [&](const uint32_t (&al)[4], const uint32_t (&ah)[4], const uint32_t (&b)[T2][4]) {
 #pragma unroll
-        for (int i = 0; i < T2; ++i) mma16816(c[i], af[0], af[1], af[2], af[3], bf[i][0], bf[i][1]);
+        for (int i = 0; i < T2; ++i) mma16816(c[i], al[0], al[1], al[2], al[3], b[i][0], b[i][1]);
+#pragma unroll
+        for (int i = 0; i < T2; ++i) mma16816(c[i], ah[0], ah[1], ah[2], ah[3], b[i][2], b[i][3]);
       };
-      load(0, af0, bf0);
+      load(0, al0, ah0, b0);
 #pragma unroll 1
-      for (int ks = 0; ks < nks; ks += 2) {
-        const bool two = ks + 1 < nks;
-        if (two) load(ks + 1, af1, bf1);
-        mmas(af0, bf0);
-        if (ks + 2 < nks) load(ks + 2, af0, bf0);
-        if (two) mmas(af1, bf1);
+      for (int kk = 0; kk < nkb; kk += 2) {
+        if (kk + 1 < nkb) load(kk + 1, al1, ah1, b1);
+        mmas(al0, ah0, b0);
+        if (kk + 2 < nkb) load(kk + 2, al0, ah0, b0);
+        if (kk + 1 < nkb) mmas(al1, ah1, b1);
       }
 #pragma unroll
       for (int i = 0; i < T2; ++i) {
@@ -557,7 +577,7 @@ int fc_tail(const float* fc1_part, int n_part, const float* b1, float* full1, co
             int F2, int NC, cudaStream_t st, bool w2_image_ready, cudaStream_t grads_stream, cudaEvent_t rows_done,
             bool overlap_producer) {
   B200_REQUIRE(B > 0 && NC > 0 && NC <= kMaxCls, "fc_tail: bad shape");
-  B200_REQUIRE(F1 % KT == 0 && F2 % 16 == 0 && F2 <= RT && F2 > 0, "fc_tail: needs f1 %% 32 == 0, f2 %% 16 == 0, f2 <= 256");
+  B200_REQUIRE(F1 % KT == 0 && F2 % 32 == 0 && F2 <= RT && F2 > 0, "fc_tail: needs f1 %% 32 == 0, f2 %% 32 == 0, f2 <= 256");
   const int R = rows_per_cta(B);
   const int nrc = cdiv(B, R);
   float* part = reinterpret_cast<float*>(scratch);
