@@ -14,6 +14,8 @@ NVCC_FLAGS = [
     "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
     "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-Xptxas", "-v",
 ]
+if os.environ.get("B200_TRACE") == "1":      # diagnostics build: kernels stamp %globaltimer (see b200_debug_trace)
+    NVCC_FLAGS.append("-DB200_TRACE")
 
 
 def sources():

@@ -12,6 +12,7 @@
 #include "launch.h"
 
 namespace b200 {
+thread_local bool g_pdl_next = false;
 
 static thread_local char g_err[512] = "";
 void set_error(const char* fmt, ...) {
@@ -224,6 +225,19 @@ static int site_mark(b200_model* h, const char* name, cudaStream_t st) {
   return B200_OK;
 }
 #define SITE(name, expr) do { TRY(site_mark(h, name, st)); TRY(expr); } while (0)
+// a site whose (first) kernel follows its producer on the same stream: launched with programmatic stream
+// serialization so its prologue overlaps the producer's tail (see common.cuh); ordinary while profiling per site.
+// Used where the early-resident consumer does not take SMs away from a side-stream kernel: conv2's dgrad and
+// conv1's wgrad (128 CTAs each) stay ordinary launches -- resident and waiting they starved FC1's dW and conv2's
+// wgrad on the side streams (measured with the B200_TRACE schedule).
+#define PSITE(name, expr)                    \
+  do {                                       \
+    TRY(site_mark(h, name, st));             \
+    g_pdl_next = !h->profiling;              \
+    const int rc__ = (expr);                 \
+    g_pdl_next = false;                      \
+    if (rc__) return rc__;                   \
+  } while (0)
 
 // defer_tail: the caller runs b200_backward right after on the same stream, so the tail's parameter-gradient
 // kernel (which also writes loss / n_correct) may stay on side stream 0 and be joined by the backward's final join
@@ -279,7 +293,7 @@ static int forward_impl(b200_handle h, const uint8_t* images, const int32_t* lab
     // The tail also clears the conv gradients (first four tensors of the flat buffer): conv1's filter / bias
     // gradient and conv2's bias gradient are accumulated with atomics further down.
     float* part = h->ptr<float>("fc1_part");
-    SITE("full1_fwd", fc_fwd_tc_splitk(pool2, h->P(P_FW1), part, c.batch, h->flat, c.f1, st));
+    PSITE("full1_fwd", fc_fwd_tc_splitk(pool2, h->P(P_FW1), part, c.batch, h->flat, c.f1, st));
     SITE("fc_tail", fc_tail(part, fc_fwd_tc_splits(c.batch, h->flat, c.f1), h->P(P_FB1), full1, h->P(P_FW2),
                             h->P(P_FB2), h->P(P_FW3), h->P(P_FB3), labels, full2, logits, h->ptr<float>("dlogits"),
                             h->ptr<float>("dfull2"), h->ptr<float>("dfull1"), h->ptr<int32_t>("pred"),
@@ -292,7 +306,7 @@ static int forward_impl(b200_handle h, const uint8_t* images, const int32_t* lab
       B200_CUDA_TRY(cudaStreamWaitEvent(st, h->ev_join[0], 0));
     }
   } else {
-    SITE("full1_fwd", fc_fwd_f32(pool2, h->P(P_FW1), h->P(P_FB1), full1, c.batch, h->flat, c.f1, 1, st));
+    PSITE("full1_fwd", fc_fwd_f32(pool2, h->P(P_FW1), h->P(P_FB1), full1, c.batch, h->flat, c.f1, 1, st));
     SITE("full2_fwd", fc_fwd_f32(full1, h->P(P_FW2), h->P(P_FB2), full2, c.batch, c.f1, c.f2, 1, st));
     SITE("full3_fwd", fc_fwd_f32(full2, h->P(P_FW3), h->P(P_FB3), logits, c.batch, c.f2, c.n_cls, 1, st));
     SITE("head", head_f32(logits, labels, h->ptr<float>("loss"), h->ptr<float>("dlogits"), h->ptr<int32_t>("pred"),
@@ -343,7 +357,7 @@ int b200_backward(b200_handle h, void* stream) {
       cudaStream_t st = s0;   // SITE() launches on `st`
       SITE("full1_dw", fc_dw_tc(h->ptr<float>("pool2"), dfull1, h->G(P_FW1), c.batch, h->flat, c.f1, st));
     }
-    SITE("full1_dx", fc_dx_tc(h->ptr<float>("pool2"), h->P(P_FW1), dfull1, dpool2, c.batch, h->flat, c.f1, 0, st));
+    PSITE("full1_dx", fc_dx_tc(h->ptr<float>("pool2"), h->P(P_FW1), dfull1, dpool2, c.batch, h->flat, c.f1, 0, st));
     // pool2's backward is not a kernel of its own: conv2's dgrad gathers MaxPoolGrad * ReluGrad from (dpool2,
     // pool2, arg2) while it builds its strip, adds the bias gradient (atomics into the buffer the tail kernel
     // cleared) and leaves dconv2 behind for the filter gradient, which then overlaps conv1's gradient.
@@ -356,7 +370,7 @@ int b200_backward(b200_handle h, void* stream) {
     }
     {
       cudaStream_t st = s1;
-      SITE("conv2_wgrad", conv5x5_wgrad_tc(h->ptr<float>("pool1"), dconv2, h->G(P_W2), h->ptr<float>("scratch2"),
+      PSITE("conv2_wgrad", conv5x5_wgrad_tc(h->ptr<float>("pool1"), dconv2, h->G(P_W2), h->ptr<float>("scratch2"),
                                            c.batch, h->h1, h->w1, c.c1, c.c2, st));
     }
     if (fused1) {
@@ -385,7 +399,7 @@ int b200_backward(b200_handle h, void* stream) {
                                c.batch, h->flat, c.f1, 0, st));
   SITE("pool2_bwd", maxpool_bwd_f32(dpool2, h->ptr<uint8_t>("arg2"), h->ptr<float>("conv2"), dconv2, c.batch, h->h1,
                                     h->w1, c.c2, 1, st));
-  SITE("conv2_wgrad", conv5x5_wgrad_f32(h->ptr<float>("pool1"), dconv2, h->G(P_W2), h->G(P_B2), scratch, c.batch,
+  PSITE("conv2_wgrad", conv5x5_wgrad_f32(h->ptr<float>("pool1"), dconv2, h->G(P_W2), h->G(P_B2), scratch, c.batch,
                                         h->h1, h->w1, c.c1, c.c2, st));
   SITE("conv2_dgrad_prep", conv5x5_rot180_f32(h->P(P_W2), h->ptr<float>("wrot"), c.c1, c.c2, st));
   SITE("conv2_dgrad", conv5x5_fwd_f32(dconv2, h->ptr<float>("wrot"), nullptr, dpool1, c.batch, h->h1, h->w1, c.c2,
@@ -400,7 +414,7 @@ int b200_backward(b200_handle h, void* stream) {
 int b200_sgd_apply(b200_handle h, float lr, float grad_scale, void* stream) {
   B200_READY(h);
   cudaStream_t st = (cudaStream_t)stream;
-  SITE("sgd_apply", sgd_apply_f32(h->params, h->grads, h->p_total, lr, grad_scale, st));
+  PSITE("sgd_apply", sgd_apply_f32(h->params, h->grads, h->p_total, lr, grad_scale, st));
   return B200_OK;
 }
 
@@ -577,6 +591,18 @@ int b200_debug_conv_timeline(int64_t* device_buf8) {
   conv5x5_set_timeline(reinterpret_cast<long long*>(device_buf8));
   fc_tail_set_timeline(device_buf8 ? reinterpret_cast<long long*>(device_buf8) + 16 : nullptr);
   return B200_OK;
+}
+int b200_debug_trace(uint64_t* device_buf) {
+#ifdef B200_TRACE
+  unsigned long long* p = reinterpret_cast<unsigned long long*>(device_buf);
+  trace_set_fc_tail(p); trace_set_tc_conv(p); trace_set_tc_conv1(p); trace_set_tc_gemm(p); trace_set_f32(p);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+#else
+  (void)device_buf;
+  set_error("b200_debug_trace: this library was built without B200_TRACE");
+  return B200_E_STATE;
+#endif
 }
 int b200_conv5x5_packed_bytes(int32_t c_in, int32_t c_out, int64_t* nbytes) {
   B200_REQUIRE(nbytes && c_in > 0 && c_out > 0, "bad argument");

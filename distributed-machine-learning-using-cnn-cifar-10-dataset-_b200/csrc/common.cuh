@@ -32,6 +32,64 @@ void set_error(const char* fmt, ...);
 static inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
 static inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 
+// ---- programmatic dependent launch ----------------------------------------------------------------------------
+// Kernels of the bf16 step call pdl_launch_dependents() at their start: a consumer launched right behind them with
+// programmatic stream serialization may then become resident and run its input-independent prologue (barrier /
+// TMEM set-up, shared-memory clears, weight fetches) while the producer still executes.  Every thread of such a
+// consumer calls pdl_wait() before it reads the producer's output or writes global memory; the wait returns when
+// the whole producer grid has completed.  Both instructions do nothing in an ordinary launch.
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+#endif
+// The next launch through launch_kernel() on this host thread is made with programmatic stream serialization when
+// this flag is set (the step driver in abi.cu sets it in front of the launches it wants overlapped); it resets itself.
+extern thread_local bool g_pdl_next;
+#ifdef __CUDACC__
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                 Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = g_pdl_next ? 1 : 0;
+  g_pdl_next = false;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#endif
+
+// ---- kernel-schedule trace (diagnostics build only: B200_TRACE=1 python build.py) -----------------------------
+// Every instrumented kernel stamps %globaltimer when its first CTA starts and when its last CTA ends into
+// buf[2*id], buf[2*id+1]; b200_debug_trace() hands the buffer to every translation unit.  Compiled out otherwise.
+#ifdef B200_TRACE
+static __device__ unsigned long long* b200_trace_buf;
+struct TraceScope {
+  int id;
+  static __device__ __forceinline__ unsigned long long now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+  }
+  __device__ __forceinline__ explicit TraceScope(int i) : id(i) {
+    if (threadIdx.x == 0 && b200_trace_buf) atomicMin(b200_trace_buf + 2 * id, now());
+  }
+  __device__ __forceinline__ ~TraceScope() {
+    if (threadIdx.x == 0 && b200_trace_buf) atomicMax(b200_trace_buf + 2 * id + 1, now());
+  }
+};
+#define B200_TRACE_SCOPE(id) ::b200::TraceScope trace_scope__(id)
+#define B200_TRACE_SETTER(name) \
+  void name(unsigned long long* p) { cudaMemcpyToSymbol(b200_trace_buf, &p, sizeof(p)); }
+#else
+#define B200_TRACE_SCOPE(id) do { } while (0)
+#define B200_TRACE_SETTER(name) \
+  void name(unsigned long long*) {}
+#endif
+enum TraceId { TR_PACK = 0, TR_W2IMG, TR_CONV1_FWD, TR_CONV2_FWD, TR_FC1_FWD, TR_TAIL_ROWS, TR_TAIL_GRADS, TR_FC1_DW,
+               TR_FC1_DX, TR_CONV2_DGRAD, TR_CONV2_WGRAD, TR_CONV2_REDUCE, TR_CONV1_WGRAD, TR_SGD, TR_COUNT };
+
 constexpr int kNumSMs = 148;   // B200: 2 dies x 74 SMs; grids below are sized in multiples of it
 
 }  // namespace b200

@@ -503,6 +503,8 @@ int head_f32(const float* logits, const int32_t* labels, float* loss_mean, float
 // ApplyGradientDescent (cifar10cnn.py:162-163): p -= lr * scale * g
 // ------------------------------------------------------------------------------------------
 __global__ void sgd_kernel(float* __restrict__ p, const float* __restrict__ g, int64_t n, float step) {
+  B200_TRACE_SCOPE(TR_SGD);
+  pdl_wait();
   int64_t n4 = n >> 2;
   float4* p4 = reinterpret_cast<float4*>(p);
   const float4* g4 = reinterpret_cast<const float4*>(g);
@@ -522,9 +524,11 @@ int sgd_apply_f32(float* p, const float* g, int64_t n, float lr, float scale, cu
   B200_REQUIRE(((uintptr_t)p & 15) == 0 && ((uintptr_t)g & 15) == 0, "sgd_apply: pointers must be 16-byte aligned");
   if (n == 0) return B200_OK;
   int grid = (int)std::min<int64_t>((n / 4 + 255) / 256 + 1, kNumSMs * 4);
-  sgd_kernel<<<grid, 256, 0, st>>>(p, g, n, lr * scale);
+  B200_CUDA_TRY(launch_kernel(sgd_kernel, dim3(grid), dim3(256), 0, st, p, g, n, lr * scale));
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
+
+B200_TRACE_SETTER(trace_set_f32)
 
 }  // namespace b200

@@ -69,6 +69,7 @@ __device__ __forceinline__ void stage_tile(float* dst, const float* src, int nfl
 // W2 fp32 [F1][F2] -> bf16 image [F1][F2+8]: rows stay 16-byte aligned (ldmatrix) and shift by four banks per
 // row (conflict-free fragment loads); fetched by the rows kernel with bulk copies
 __global__ void w2_to_bf16_kernel(const float* __restrict__ w2, __nv_bfloat16* __restrict__ out, int F1, int F2) {
+  B200_TRACE_SCOPE(TR_W2IMG);
   const int WS = F2 + 8;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < F1 * WS; i += gridDim.x * blockDim.x) {
     const int k = i / WS, n = i - k * WS;
@@ -124,6 +125,7 @@ __host__ __device__ inline TailSmem tail_smem(int RM, int F1, int F2, int NC) {
 // handles a.R <= RM batch rows.  T1: 8-column tiles of full2 per warp (F2 <= 64 * T1).
 template <int RM, int T1>
 __global__ void __launch_bounds__(RT) fc_tail_rows_kernel(TailArgs a) {
+  B200_TRACE_SCOPE(TR_TAIL_ROWS);
   extern __shared__ __align__(16) uint8_t smraw[];
   const TailSmem L = tail_smem(RM, a.F1, a.F2, a.NC);
   const int WS = a.F2 + 8, XS = a.F1 + 8, DS = a.F2 + 8;      // pitches in bf16 elements
@@ -174,7 +176,8 @@ __global__ void __launch_bounds__(RT) fc_tail_rows_kernel(TailArgs a) {
   const int f14 = a.F1 / 4;
   // launched with programmatic stream serialization, everything above ran while the producer of fc1_part (FC1)
   // was still executing; from here on its output is needed (no-op for an ordinary launch)
-  asm volatile("griddepcontrol.wait;" ::: "memory");
+  pdl_wait();
+  pdl_launch_dependents();
   if (RM == 8)      // upper half of the A tile
     for (int i = tid; i < XS; i += RT) reinterpret_cast<uint4*>(xb + 8 * XS)[i] = make_uint4(0, 0, 0, 0);
   for (int i0 = tid; i0 < RM * f14; i0 += 3 * RT) {
@@ -484,6 +487,9 @@ struct TailGradArgs {
 // CTAs [0, F1/4): dW2 rows k0..k0+3 = full1[:, k0..k0+3]^T dfull2, batch staged through shared memory.
 // Remaining CTAs: fixed-order sums of the row-kernel partials (db1, db2, db3, dW3, loss, counts).
 __global__ void __launch_bounds__(RT) fc_tail_grads_kernel(TailGradArgs a) {
+  B200_TRACE_SCOPE(TR_TAIL_GRADS);
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ __align__(16) float sm[];
   const int tid = threadIdx.x;
   const int n_dw2 = a.F1 / 4;
@@ -552,6 +558,7 @@ long long* g_tail_timeline = nullptr;
 }  // namespace
 
 void fc_tail_set_timeline(long long* dev_buf) { g_tail_timeline = dev_buf; }
+B200_TRACE_SETTER(trace_set_fc_tail)
 
 static int64_t part_bytes(int B, int F1, int F2, int NC) {
   return round_up((int64_t)cdiv(B, rows_per_cta(B)) * part_len(F1, F2, NC) * 4, 256);

@@ -59,7 +59,13 @@ int conv5x5_wgrad_tc(const float* x, const float* dy, float* dw, float* scratch,
                      int Cout, cudaStream_t st);
 int fc_fwd_tc_splits(int B, int K, int N);
 int fc_fwd_tc_splitk(const float* x, const float* w, float* part, int B, int K, int N, cudaStream_t st);
-void fc_tail_set_timeline(long long* dev_buf);   // diagnostics (see conv5x5_set_timeline)
+void fc_tail_set_timeline(long long* dev_buf);
+// diagnostics build (B200_TRACE): hand the %globaltimer trace buffer to each translation unit
+void trace_set_fc_tail(unsigned long long*);
+void trace_set_tc_conv(unsigned long long*);
+void trace_set_tc_conv1(unsigned long long*);
+void trace_set_tc_gemm(unsigned long long*);
+void trace_set_f32(unsigned long long*);   // diagnostics (see conv5x5_set_timeline)
 int64_t fc_tail_scratch_bytes(int B, int F1, int F2, int NC);
 int fc_tail(const float* fc1_part, int n_part, const float* b1, float* full1, const float* w2, const float* b2,
             const float* w3, const float* b3, const int32_t* labels, float* full2, float* logits, float* dlogits,

@@ -165,6 +165,7 @@ struct ConvArgs {
 // ---------------------------------------------------------------------------------------------------
 template <bool DGRAD, int KSTEPS, bool POOL = false>
 __global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
+  B200_TRACE_SCOPE(DGRAD ? TR_CONV2_DGRAD : TR_CONV2_FWD);
   constexpr int BN = 64;
   constexpr int NISS = 4;                 // MMA-issuing warps (warps 4..7); warp 8 streams the filter
   const ConvGeom& g = a.g;
@@ -209,6 +210,8 @@ __global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
     if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) a.timeline[0] = clock64();
     zero_smem(strip, strip_bytes, tid);
     loaders_sync();
+    pdl_wait();      // these warps are the only ones that touch global memory besides the filter fetch (TMA warp)
+    pdl_launch_dependents();   // after our own wait: a dependent overlaps this kernel only, never our producer
     if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) a.timeline[1] = clock64();
     if (POOL) {
       float bsum[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -391,6 +394,7 @@ __global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
 // Cin*16+16 bytes.  Read MN-major (groups along N) it is the forward B operand of tap `tap`; read
 // K-major (groups along K) it is the input-gradient B operand of tap 24-tap.  One packed copy serves both.
 __global__ void pack_conv_weights_kernel(const float* __restrict__ w, uint8_t* __restrict__ wp, int Cin, int Cout) {
+  B200_TRACE_SCOPE(TR_PACK);
   const int gstride = Cin * 16 + 16, img = (Cout / 8) * gstride;
   const int total = 25 * Cin * (Cout / 8);
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
@@ -453,8 +457,7 @@ int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, 
   B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   ConvArgs a{x, wp, DGRAD ? NC : KC, DGRAD ? KC : NC, bias, y, relu, g, g_conv_timeline, pg ? *pg : PoolGradSrc{}, dbias, dconv_out, pool_out, arg_out};
   dim3 grid(cdiv(B, ipc), NC / 64);
-  kern<<<grid, 288, smem, st>>>(a);
-  B200_LAUNCH_CHECK();
+  B200_CUDA_TRY(launch_kernel(kern, grid, dim3(288), (size_t)smem, st, a));
   return B200_OK;
 }
 
@@ -514,6 +517,8 @@ __device__ __forceinline__ void fill_strip_pair(uint8_t* xs, uint8_t* ds, const 
 }
 
 __global__ void __launch_bounds__(416, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
+  B200_TRACE_SCOPE(TR_CONV2_WGRAD);
+  pdl_launch_dependents();
   constexpr int C = 64;
   const ConvGeom& g = a.g;
   extern __shared__ __align__(128) uint8_t smem[];
@@ -550,6 +555,7 @@ __global__ void __launch_bounds__(416, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
     // pads stay zero for every image: fills touch valid pixels only
     for (int o = tid * 16; o < 2 * a.nbuf * strip_bytes; o += WG_LOADERS * 16) *reinterpret_cast<uint4*>(smem + o) = make_uint4(0, 0, 0, 0);
     wg_loaders_sync();
+    pdl_wait();
     if (stamp) a.timeline[9] = clock64();
     for (int it = 0; it < nimg; ++it) {
       const int b = it % a.nbuf;
@@ -638,6 +644,8 @@ __global__ void __launch_bounds__(416, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
 // sums the S partials of every 4-float group: four neighbouring lanes take every fourth partial each (all of a
 // lane's loads in flight together) and combine with two shuffles -- a fixed order, so the result is deterministic
 __global__ void reduce_partials_tc(const float* __restrict__ part, float* __restrict__ out, int n, int S) {
+  B200_TRACE_SCOPE(TR_CONV2_REDUCE);
+  pdl_wait();
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   const int sub = t & 3;
   const int i = min((t >> 2) * 4, n - 4);                 // surplus threads redo the last group (shuffles stay full-warp)
@@ -664,6 +672,7 @@ int wgrad_splits_tc(int B) { return std::max(1, std::min(B, (kNumSMs + 4) / 5));
 }  // namespace
 
 void conv5x5_set_timeline(long long* dev_buf) { g_conv_timeline = dev_buf; }
+B200_TRACE_SETTER(trace_set_tc_conv)
 int64_t conv5x5_packed_bytes(int Cin, int Cout) { return 25ll * (Cout / 8) * (Cin * 16 + 16); }
 int pack_conv_weights(const float* w, void* wp, int Cin, int Cout, cudaStream_t st) {
   B200_REQUIRE(Cin % 8 == 0 && Cout % 8 == 0 && Cin > 0 && Cout > 0, "pack_conv_weights: channels must be multiples of 8");
@@ -734,11 +743,12 @@ static int launch_wgrad(const float* x, const float* dy, const PoolGradSrc* pg, 
   int per = cdiv(B, S);
   S = cdiv(B, per);
   WgradArgs a{x, dy, scratch, g, per, nbuf, pg ? *pg : PoolGradSrc{}, g_conv_timeline};
-  conv5x5_wgrad_tc_kernel<<<dim3(5, S), 416, smem, st>>>(a);
-  B200_LAUNCH_CHECK();
+  const bool overlap = g_pdl_next;           // the step driver asked for overlapped launches: only the reduction is
+  g_pdl_next = false;                        // programmatic (the kernel in front of this one is on another stream)
+  B200_CUDA_TRY(launch_kernel(conv5x5_wgrad_tc_kernel, dim3(5, S), dim3(416), (size_t)smem, st, a));
   const int n = 25 * 64 * 64;
-  reduce_partials_tc<<<cdiv(n, 128), 128, 0, st>>>(scratch, dw, n, S);
-  B200_LAUNCH_CHECK();
+  g_pdl_next = overlap;
+  B200_CUDA_TRY(launch_kernel(reduce_partials_tc, dim3(cdiv(n, 128)), dim3(128), 0, st, (const float*)scratch, dw, n, S));
   return B200_OK;
 }
 

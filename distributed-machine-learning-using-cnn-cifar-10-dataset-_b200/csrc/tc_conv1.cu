@@ -66,6 +66,8 @@ constexpr int kWLbo = 64 * 16 + 16;      // B operand: [26 k-chunks][64 cout][16
 constexpr int kConvRow = 68;             // floats per conv-output row in smem (64 + 4: conflict-free STS.128)
 
 __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) {
+  B200_TRACE_SCOPE(TR_CONV1_FWD);
+  pdl_launch_dependents();
   const C1Geom& g = a.g;
   extern __shared__ __align__(128) uint8_t smem[];
   const int strip_bytes = (g.npix * 16 + 127) & ~127;
@@ -251,6 +253,7 @@ struct Conv1WgradArgs {
 };
 
 __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
+  B200_TRACE_SCOPE(TR_CONV1_WGRAD);
   const C1Geom& g = a.g;
   extern __shared__ __align__(128) uint8_t smem[];
   const int xs_bytes = (g.npix * 16 + 127) & ~127;
@@ -290,6 +293,18 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
     for (int it = 0; it < nimg; ++it) {
       const int n = blockIdx.x + it * gridDim.x;
       mbar_wait(smem_u32(empty), (it & 1) ^ 1);          // MMAs of the previous image are done with the strips
+      // x strip: channels 0..2 = pixel bytes (0 in the pads), channel 3 = 1 in EVERY slot
+      const uint8_t* rec = a.img + (size_t)n * 3 * g.ih * g.iw;
+      for (int s = tid; s < g.npix; s += WORKERS) {
+        const int p = s - g.lead;
+        const int i = p >= 0 ? p / g.P : -1, j = p >= 0 ? p - i * g.P : 0;
+        uint4 v;
+        if (p >= 0 && i < g.H && j < g.W) v = pixel_chunk(rec, g.ih, g.iw, i + oy, j + ox, 1.f);
+        else { float f[8] = {0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 0.f}; v = pack8(f); }
+        *reinterpret_cast<uint4*>(xs + s * 16) = v;
+      }
+      pdl_wait();     // the records above do not depend on the producer of dpool (conv2's dgrad); from here on we do
+      pdl_launch_dependents();
       // masked pool gradient and argmax of this image -> shared memory (coalesced)
       const float4* dp4 = reinterpret_cast<const float4*>(a.dpool + (size_t)n * ncell * 64);
       const float4* pl4 = reinterpret_cast<const float4*>(a.pool + (size_t)n * ncell * 64);
@@ -301,16 +316,6 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
         d.z = p.z > 0.f ? d.z : 0.f; d.w = p.w > 0.f ? d.w : 0.f;
         reinterpret_cast<float4*>(dpm)[q] = d;
         reinterpret_cast<uint32_t*>(argb)[q] = __ldg(ar4 + q);
-      }
-      // x strip: channels 0..2 = pixel bytes (0 in the pads), channel 3 = 1 in EVERY slot
-      const uint8_t* rec = a.img + (size_t)n * 3 * g.ih * g.iw;
-      for (int s = tid; s < g.npix; s += WORKERS) {
-        const int p = s - g.lead;
-        const int i = p >= 0 ? p / g.P : -1, j = p >= 0 ? p - i * g.P : 0;
-        uint4 v;
-        if (p >= 0 && i < g.H && j < g.W) v = pixel_chunk(rec, g.ih, g.iw, i + oy, j + ox, 1.f);
-        else { float f[8] = {0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 0.f}; v = pack8(f); }
-        *reinterpret_cast<uint4*>(xs + s * 16) = v;
       }
       workers_sync();
       // dY strip: MaxPoolGrad (gather over the <= 4 windows covering a cell) of the masked gradient
@@ -431,9 +436,10 @@ int conv1_wgrad_tc(const uint8_t* img, const float* dpool, const float* pool, co
     if (db) B200_CUDA_TRY(cudaMemsetAsync(db, 0, 64 * sizeof(float), st));
   }
   Conv1WgradArgs a{img, dpool, pool, arg, dw, db, g};
-  conv1_wgrad_kernel<<<S, 416, smem, st>>>(a);
-  B200_LAUNCH_CHECK();
+  B200_CUDA_TRY(launch_kernel(conv1_wgrad_kernel, dim3(S), dim3(416), smem, st, a));
   return B200_OK;
 }
+
+B200_TRACE_SETTER(trace_set_tc_conv1)
 
 }  // namespace b200

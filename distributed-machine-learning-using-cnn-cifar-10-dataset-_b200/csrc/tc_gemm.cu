@@ -31,6 +31,7 @@ struct GemmArgs {
   float* colsum;           // optional: colsum[n] = sum_m C[m,n] (after mask), needs gridDim.y == 1
   int k_per_split;         // multiple of BK; blockIdx.z covers K range [z*kps, (z+1)*kps)
   int64_t split_stride;    // floats between the C outputs of consecutive splits
+  int trace_id;            // TraceId of this launch (diagnostics build)
 };
 
 template <int BN>
@@ -46,9 +47,7 @@ struct Smem {
 
 template <int BN, bool A_MN, bool B_MN, typename TA, typename TB>
 __global__ void __launch_bounds__(288, 1) tc_gemm_kernel(GemmArgs g) {
-  // a consumer launched with programmatic stream serialization (the FC tail after FC1) may start its own
-  // input-independent prologue now; it still waits for this whole grid before it reads our output
-  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  B200_TRACE_SCOPE(g.trace_id);
   using S = Smem<BN>;
   extern __shared__ __align__(128) uint8_t smem[];
   uint8_t* ctrl = smem + STAGES * S::STAGE;
@@ -75,6 +74,8 @@ __global__ void __launch_bounds__(288, 1) tc_gemm_kernel(GemmArgs g) {
 
   if (warp < 8) {
     // ------------------------------ operand staging ------------------------------------------
+    pdl_wait();      // barrier / TMEM set-up above overlapped the producer; the operands are its output
+    pdl_launch_dependents();   // after our own wait: a dependent overlaps this kernel only, never our producer
     const TA* A = reinterpret_cast<const TA*>(g.A);
     const TB* B = reinterpret_cast<const TB*>(g.B);
     for (int kb = 0; kb < nkb; ++kb) {
@@ -218,7 +219,7 @@ int launch(const GemmArgs& g, cudaStream_t st) {
     attr_done = true;
   }
   dim3 grid(cdiv(g.N, BN), cdiv(g.M, BM), cdiv(g.K, g.k_per_split));
-  kern<<<grid, 288, S::TOTAL, st>>>(g);
+  B200_CUDA_TRY(launch_kernel(kern, grid, dim3(288), (size_t)S::TOTAL, st, g));
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
@@ -242,7 +243,7 @@ int check_align(const GemmArgs& g, bool a_mn, bool b_mn) {
 // y = relu?(x @ w + b): A = x [B,K] K-major, B = w [K,N] MN-major
 int fc_fwd_tc(const float* x, const float* w, const float* b, float* y, int Bt, int K, int N, int relu,
               cudaStream_t st) {
-  GemmArgs g{Bt, N, K, x, K, w, N, y, N, b, relu, nullptr, 0, nullptr, (int)round_up(K, BK), 0};
+  GemmArgs g{Bt, N, K, x, K, w, N, y, N, b, relu, nullptr, 0, nullptr, (int)round_up(K, BK), 0, TR_FC1_FWD};
   int rc = check_align(g, false, true);
   if (rc) return rc;
   return dispatch<false, true>(g, st);
@@ -259,7 +260,7 @@ int fc_fwd_tc_splits(int Bt, int K, int N) {
 int fc_fwd_tc_splitk(const float* x, const float* w, float* part, int Bt, int K, int N, cudaStream_t st) {
   int s = fc_fwd_tc_splits(Bt, K, N);
   int kps = (int)round_up(cdiv(K, s), BK);
-  GemmArgs g{Bt, N, K, x, K, w, N, part, N, nullptr, 0, nullptr, 0, nullptr, kps, (int64_t)Bt * N};
+  GemmArgs g{Bt, N, K, x, K, w, N, part, N, nullptr, 0, nullptr, 0, nullptr, kps, (int64_t)Bt * N, TR_FC1_FWD};
   int rc = check_align(g, false, true);
   if (rc) return rc;
   return dispatch<false, true>(g, st);
@@ -267,7 +268,7 @@ int fc_fwd_tc_splitk(const float* x, const float* w, float* part, int Bt, int K,
 
 // dw[K,N] = x^T[K,Bt] dy[Bt,N]: A(m=k_feat, k=batch) = x[batch*K + m] MN-major; B(k=batch, n) = dy MN-major
 int fc_dw_tc(const float* x, const float* dy, float* dw, int Bt, int K, int N, cudaStream_t st) {
-  GemmArgs g{K, N, Bt, x, K, dy, N, dw, N, nullptr, 0, nullptr, 0, nullptr, (int)round_up(Bt, BK), 0};
+  GemmArgs g{K, N, Bt, x, K, dy, N, dw, N, nullptr, 0, nullptr, 0, nullptr, (int)round_up(Bt, BK), 0, TR_FC1_DW};
   int rc = check_align(g, true, true);
   if (rc) return rc;
   return dispatch<true, true>(g, st);
@@ -275,7 +276,7 @@ int fc_dw_tc(const float* x, const float* dy, float* dw, int Bt, int K, int N, c
 // dx[Bt,K] = (dy[Bt,N] w^T) * [x > 0]?: A = dy K-major; B(k=n_out, n=k_feat) = w[n*N + k] K-major
 int fc_dx_tc(const float* x, const float* w, const float* dy, float* dx, int Bt, int K, int N, int mask_x,
              cudaStream_t st) {
-  GemmArgs g{Bt, K, N, dy, N, w, N, dx, K, nullptr, 0, mask_x ? x : nullptr, K, nullptr, (int)round_up(N, BK), 0};
+  GemmArgs g{Bt, K, N, dy, N, w, N, dx, K, nullptr, 0, mask_x ? x : nullptr, K, nullptr, (int)round_up(N, BK), 0, TR_FC1_DX};
   int rc = check_align(g, false, false);
   if (rc) return rc;
   return dispatch<false, false>(g, st);
@@ -287,5 +288,7 @@ int fc_bwd_tc(const float* x, const float* w, const float* dy, float* dx, float*
   if (rc || !dx) return rc;
   return fc_dx_tc(x, w, dy, dx, Bt, K, N, mask_x, st);
 }
+
+B200_TRACE_SETTER(trace_set_tc_gemm)
 
 }  // namespace b200

@@ -186,6 +186,11 @@ int b200_conv1_wgrad_bf16(const uint8_t* images, const float* dpool, const float
  * clock64() at its phase boundaries (start, strip zeroed, strip filled, MMA start, MMA issued,
  * accumulators ready, epilogue done); NULL switches it off. */
 int b200_debug_conv_timeline(int64_t* device_buf32);
+/* diagnostics, only in a library built with B200_TRACE=1 (else B200_E_STATE): every kernel of the bf16 step stores
+ * %globaltimer (ns) of its first CTA's start / last CTA's end into device_buf[2*k], device_buf[2*k+1] (atomic min /
+ * max: preset them to ~0 / 0), k = pack, W2 image, conv1 fwd, conv2 fwd, FC1 fwd, tail rows, tail grads, FC1 dW,
+ * FC1 dX, conv2 dgrad, conv2 wgrad, wgrad reduce, conv1 wgrad, SGD.  No counterpart in the reference. */
+int b200_debug_trace(uint64_t* device_buf);
 int b200_conv5x5_packed_bytes(int32_t c_in, int32_t c_out, int64_t* nbytes);
 int b200_conv5x5_pack_weights(const float* w, void* w_packed, int32_t c_in, int32_t c_out, void* stream);
 int b200_conv5x5_fwd_bf16(const float* x, const void* w_packed, const float* bias, float* y, int32_t batch, int32_t h,

@@ -1,0 +1,38 @@
+"""Kernel schedule of one captured bf16 train step (needs a B200_TRACE=1 build): start / end of every kernel in us
+relative to the first kernel's start, from %globaltimer stamps."""
+import sys, ctypes as C, numpy as np, torch
+sys.path.insert(0, '.')
+import b200cnn
+from b200cnn import _lib
+lib = _lib.load()
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 128
+names = ["pack", "w2img", "conv1_fwd", "conv2_fwd", "fc1_fwd", "tail_rows", "tail_grads", "fc1_dw", "fc1_dx",
+         "conv2_dgrad", "conv2_wgrad", "wgrad_reduce", "conv1_wgrad", "sgd"]
+e = b200cnn.TrainStepEngine(batch=B, mode="bf16"); e.init_params(0)
+rng = np.random.default_rng(0)
+img = torch.as_tensor(rng.integers(0, 256, (B, 3, 32, 32), dtype=np.uint8)).cuda()
+lab = torch.as_tensor(rng.integers(0, 10, (B,)).astype(np.int32)).cuda()
+buf = torch.zeros(2 * len(names), dtype=torch.int64, device='cuda')
+_lib.check(lib.b200_debug_trace(buf.data_ptr()))
+def reset():
+    buf[0::2] = torch.iinfo(torch.int64).max; buf[1::2] = 0      # stamps are < 2^63: signed view orders the same
+e.train_step(img, lab, 0.1); torch.cuda.synchronize()
+g = e.capture(lambda: e.train_step(img, lab, 0.1))
+flush = torch.empty(256 << 20, dtype=torch.uint8, device='cuda')
+for cold in (0, 1):
+    for _ in range(5):
+        if cold: flush.zero_()
+        reset(); torch.cuda.synchronize(); g.replay(); torch.cuda.synchronize()
+    t = buf.cpu().numpy().reshape(-1, 2).astype(np.float64)
+    t0 = t[:, 0].min()
+    print("cold" if cold else "hot", "step: %.1f us from first start to last end" % ((t[:, 1].max() - t0) / 1e3))
+    for i in np.argsort(t[:, 0]):
+        print("  %-13s start %7.1f  end %7.1f  (%5.1f us)" % (names[i], (t[i, 0] - t0) / 1e3, (t[i, 1] - t0) / 1e3, (t[i, 1] - t[i, 0]) / 1e3))
+# phase stamps (clock64) of CTA 0 of the LAST conv5x5 kernel that ran (the dgrad of the step) and of the tail rows kernel
+tl = torch.zeros(32, dtype=torch.int64, device='cuda')
+lib.b200_debug_conv_timeline(C.cast(tl.data_ptr(), C.POINTER(C.c_int64)))
+g.replay(); torch.cuda.synchronize()
+t = tl.cpu().numpy()
+print("conv2 dgrad CTA0 cycles since start: zeroed %d filled %d mma_start %d mma_issued %d accum_ready %d epilogue_done %d" % tuple(t[1:7] - t[0]))
+print("conv2 wgrad CTA0 cycles since start: zeroed %d img0 %d all_filled %d accum_ready %d epilogue_done %d" % tuple(t[9:14] - t[8]))
+print("tail rows phases:", (t[17:25] - t[16:24]).tolist())
