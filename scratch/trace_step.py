@@ -16,6 +16,8 @@ buf = torch.zeros(2 * len(names), dtype=torch.int64, device='cuda')
 _lib.check(lib.b200_debug_trace(buf.data_ptr()))
 def reset():
     buf[0::2] = torch.iinfo(torch.int64).max; buf[1::2] = 0      # stamps are < 2^63: signed view orders the same
+tl = torch.zeros(32, dtype=torch.int64, device='cuda')
+lib.b200_debug_conv_timeline(C.cast(tl.data_ptr(), C.POINTER(C.c_int64)))
 e.train_step(img, lab, 0.1); torch.cuda.synchronize()
 g = e.capture(lambda: e.train_step(img, lab, 0.1))
 flush = torch.empty(256 << 20, dtype=torch.uint8, device='cuda')
@@ -29,8 +31,6 @@ for cold in (0, 1):
     for i in np.argsort(t[:, 0]):
         print("  %-13s start %7.1f  end %7.1f  (%5.1f us)" % (names[i], (t[i, 0] - t0) / 1e3, (t[i, 1] - t0) / 1e3, (t[i, 1] - t[i, 0]) / 1e3))
 # phase stamps (clock64) of CTA 0 of the LAST conv5x5 kernel that ran (the dgrad of the step) and of the tail rows kernel
-tl = torch.zeros(32, dtype=torch.int64, device='cuda')
-lib.b200_debug_conv_timeline(C.cast(tl.data_ptr(), C.POINTER(C.c_int64)))
 g.replay(); torch.cuda.synchronize()
 t = tl.cpu().numpy()
 print("conv2 dgrad CTA0 cycles since start: zeroed %d filled %d mma_start %d mma_issued %d accum_ready %d epilogue_done %d" % tuple(t[1:7] - t[0]))
