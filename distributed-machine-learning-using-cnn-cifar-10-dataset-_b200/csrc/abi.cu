@@ -300,10 +300,12 @@ static int forward_impl(b200_handle h, const uint8_t* images, const int32_t* lab
                             h->ptr<float>("loss"), h->ptr<int32_t>("n_correct"), h->ptr<int32_t>("n_bad"),
                             h->G(P_FW2), h->G(P_FB2), h->G(P_FW3), h->G(P_FB3), h->G(P_FB1),
                             h->ptr<void>("tail_scratch"), h->grads, (int)(h->p_off[P_B2] + h->p_size[P_B2]), c.batch, c.f1, c.f2,
-                            c.n_cls, st, true, fork ? h->side[0] : nullptr, h->ev_fork[0], !h->profiling));
+                            c.n_cls, st, true, fork ? h->side[1] : nullptr, h->ev_fork[1], !h->profiling));
+    // (side stream 1, not 0: the backward puts FC1's dW on stream 0 and wants it to start with FC1's dX, not behind
+    //  this kernel -- 36 + 108 CTAs fit the machine together)
     if (fork && !defer_tail) {
-      B200_CUDA_TRY(cudaEventRecord(h->ev_join[0], h->side[0]));
-      B200_CUDA_TRY(cudaStreamWaitEvent(st, h->ev_join[0], 0));
+      B200_CUDA_TRY(cudaEventRecord(h->ev_join[1], h->side[1]));
+      B200_CUDA_TRY(cudaStreamWaitEvent(st, h->ev_join[1], 0));
     }
   } else {
     PSITE("full1_fwd", fc_fwd_f32(pool2, h->P(P_FW1), h->P(P_FB1), full1, c.batch, h->flat, c.f1, 1, st));
@@ -590,6 +592,7 @@ int b200_conv1_wgrad_bf16(const uint8_t* images, const float* dpool, const float
 int b200_debug_conv_timeline(int64_t* device_buf8) {
   conv5x5_set_timeline(reinterpret_cast<long long*>(device_buf8));
   fc_tail_set_timeline(device_buf8 ? reinterpret_cast<long long*>(device_buf8) + 16 : nullptr);
+  conv1_set_timeline(reinterpret_cast<long long*>(device_buf8));
   return B200_OK;
 }
 int b200_debug_trace(uint64_t* device_buf) {

@@ -63,6 +63,8 @@ inline cudaError_t launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block
 // ---- kernel-schedule trace (diagnostics build only: B200_TRACE=1 python build.py) -----------------------------
 // Every instrumented kernel stamps %globaltimer when its first CTA starts and when its last CTA ends into
 // buf[2*id], buf[2*id+1]; b200_debug_trace() hands the buffer to every translation unit.  Compiled out otherwise.
+enum TraceId { TR_PACK = 0, TR_W2IMG, TR_CONV1_FWD, TR_CONV2_FWD, TR_FC1_FWD, TR_TAIL_ROWS, TR_TAIL_GRADS, TR_FC1_DW,
+               TR_FC1_DX, TR_CONV2_DGRAD, TR_CONV2_WGRAD, TR_CONV2_REDUCE, TR_CONV1_WGRAD, TR_SGD, TR_COUNT };
 #ifdef B200_TRACE
 static __device__ unsigned long long* b200_trace_buf;
 struct TraceScope {
@@ -72,11 +74,28 @@ struct TraceScope {
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     return t;
   }
+  // buf[2*TR_COUNT] = id of one kernel whose CTAs also log their own start / end / SM at buf[64 + 3*cta ...]
   __device__ __forceinline__ explicit TraceScope(int i) : id(i) {
-    if (threadIdx.x == 0 && b200_trace_buf) atomicMin(b200_trace_buf + 2 * id, now());
+    if (threadIdx.x == 0 && b200_trace_buf) {
+      const unsigned long long t = now();
+      atomicMin(b200_trace_buf + 2 * id, t);
+      if (b200_trace_buf[2 * TR_COUNT] == (unsigned long long)id) {
+        const int cta = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+        unsigned sm;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
+        if (cta < 512) { b200_trace_buf[64 + 3 * cta] = t; b200_trace_buf[64 + 3 * cta + 2] = sm; }
+      }
+    }
   }
   __device__ __forceinline__ ~TraceScope() {
-    if (threadIdx.x == 0 && b200_trace_buf) atomicMax(b200_trace_buf + 2 * id + 1, now());
+    if (threadIdx.x == 0 && b200_trace_buf) {
+      const unsigned long long t = now();
+      atomicMax(b200_trace_buf + 2 * id + 1, t);
+      if (b200_trace_buf[2 * TR_COUNT] == (unsigned long long)id) {
+        const int cta = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+        if (cta < 512) b200_trace_buf[64 + 3 * cta + 1] = t;
+      }
+    }
   }
 };
 #define B200_TRACE_SCOPE(id) ::b200::TraceScope trace_scope__(id)
@@ -87,8 +106,6 @@ struct TraceScope {
 #define B200_TRACE_SETTER(name) \
   void name(unsigned long long*) {}
 #endif
-enum TraceId { TR_PACK = 0, TR_W2IMG, TR_CONV1_FWD, TR_CONV2_FWD, TR_FC1_FWD, TR_TAIL_ROWS, TR_TAIL_GRADS, TR_FC1_DW,
-               TR_FC1_DX, TR_CONV2_DGRAD, TR_CONV2_WGRAD, TR_CONV2_REDUCE, TR_CONV1_WGRAD, TR_SGD, TR_COUNT };
 
 constexpr int kNumSMs = 148;   // B200: 2 dies x 74 SMs; grids below are sized in multiples of it
 

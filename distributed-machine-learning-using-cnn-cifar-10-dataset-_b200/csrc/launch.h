@@ -60,6 +60,7 @@ int conv5x5_wgrad_tc(const float* x, const float* dy, float* dw, float* scratch,
 int fc_fwd_tc_splits(int B, int K, int N);
 int fc_fwd_tc_splitk(const float* x, const float* w, float* part, int B, int K, int N, cudaStream_t st);
 void fc_tail_set_timeline(long long* dev_buf);
+void conv1_set_timeline(long long* dev_buf);
 // diagnostics build (B200_TRACE): hand the %globaltimer trace buffer to each translation unit
 void trace_set_fc_tail(unsigned long long*);
 void trace_set_tc_conv(unsigned long long*);

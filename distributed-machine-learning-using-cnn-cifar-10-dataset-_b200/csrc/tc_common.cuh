@@ -162,5 +162,74 @@ __device__ __forceinline__ uint4 load_chunk(const float* p) {
 }
 __device__ __forceinline__ uint4 load_chunk(const __nv_bfloat16* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
 
+
+// ---- MaxPoolGrad by parity-aware gather ---------------------------------------------------------------------------
+// 3x3 / stride-2 max-pool with (pbh, pbw) rows / columns of padding in front: conv pixel (i, j) lies in the windows
+// (oh, kh) with 2*oh - pbh + kh = i -- ONE window row when i + pbh is odd (kh = 1), TWO when it is even (kh = 0, and
+// kh = 2 of the window row above); columns alike.  A pixel's chunk of 8 channels is the sum, over those <= 4
+// windows, of the masked pooled gradient of every channel whose argmax code (kh*3 + kw) points at the pixel.
+// dpm: masked pooled gradient, fp32, per cell 16 float4 laid out [half][chunk] (channels 8*chunk + 4*half .. +3: the
+// eight lanes of a pixel read 128 contiguous bytes), argb: [cells][64] argmax codes, both in shared memory.
+template <int NA, int NB>       // window rows / columns covering the pixel (fixed by the parities of i+pbh, j+pbw)
+__device__ __forceinline__ void pool_grad_px(const float* dpm, const uint8_t* argb, int OH, int OW, int oh0, int ow0,
+                                             int c8, float (&acc)[8]) {
+#pragma unroll
+  for (int a = 0; a < NA; ++a) {
+    const int oh = oh0 - a, kh = a ? 2 : (NA == 2 ? 0 : 1);
+    const bool va = a ? oh >= 0 : oh < OH;
+#pragma unroll
+    for (int b = 0; b < NB; ++b) {
+      const int ow = ow0 - b, kw = b ? 2 : (NB == 2 ? 0 : 1);
+      const bool v = va && (b ? ow >= 0 : ow < OW);
+      const int cell = v ? oh * OW + ow : 0;
+      const uint32_t code = v ? (uint32_t)(kh * 3 + kw) * 0x01010101u : 0xffffffffu;     // 0xff matches no code
+      const uint2 ab = *reinterpret_cast<const uint2*>(argb + cell * 64 + c8 * 8);
+      const float4 d0 = reinterpret_cast<const float4*>(dpm)[cell * 16 + c8];          // channels 8*c8 .. +3
+      const float4 d1 = reinterpret_cast<const float4*>(dpm)[cell * 16 + 8 + c8];      // channels 8*c8+4 .. +7
+      const uint32_t m0 = __vcmpeq4(ab.x, code), m1 = __vcmpeq4(ab.y, code);             // 0xff per matching byte
+      acc[0] += __uint_as_float(__float_as_uint(d0.x) & __byte_perm(m0, 0, 0x0000));
+      acc[1] += __uint_as_float(__float_as_uint(d0.y) & __byte_perm(m0, 0, 0x1111));
+      acc[2] += __uint_as_float(__float_as_uint(d0.z) & __byte_perm(m0, 0, 0x2222));
+      acc[3] += __uint_as_float(__float_as_uint(d0.w) & __byte_perm(m0, 0, 0x3333));
+      acc[4] += __uint_as_float(__float_as_uint(d1.x) & __byte_perm(m1, 0, 0x0000));
+      acc[5] += __uint_as_float(__float_as_uint(d1.y) & __byte_perm(m1, 0, 0x1111));
+      acc[6] += __uint_as_float(__float_as_uint(d1.z) & __byte_perm(m1, 0, 0x2222));
+      acc[7] += __uint_as_float(__float_as_uint(d1.w) & __byte_perm(m1, 0, 0x3333));
+    }
+  }
+}
+// all 8-channel chunks of image rows [row0, row0 + rows): emit(i, j, c8, acc) is called once per chunk.  NT threads
+// (a multiple of 8, so a thread keeps the chunk index tid & 7); pixels are visited parity class by parity class so
+// that the window counts above are compile-time constants.
+template <int NT, typename Emit>
+__device__ __forceinline__ void pool_grad_rows(const float* dpm, const uint8_t* argb, int W, int OH, int OW, int pbh,
+                                               int pbw, int row0, int rows, int tid, Emit emit) {
+#pragma unroll
+  for (int cls = 0; cls < 4; ++cls) {
+    const int pi = cls >> 1, pj = cls & 1;                       // parities of i + pbh, j + pbw
+    const int i_first = row0 + ((((row0 + pbh) & 1) != pi) ? 1 : 0);
+    const int ni = i_first < row0 + rows ? ((row0 + rows - 1 - i_first) >> 1) + 1 : 0;
+    const int j_first = ((pbw & 1) != pj) ? 1 : 0;
+    const int nj = j_first < W ? ((W - 1 - j_first) >> 1) + 1 : 0;
+    const uint32_t magic = nj > 1 ? 0xffffffffu / (uint32_t)nj + 1u : 0u;      // pq / nj = umulhi(pq, magic), small pq
+#pragma unroll 2
+    for (int q = tid; q < ni * nj * 8; q += NT) {
+      const int c8 = q & 7, pq = q >> 3;
+      const int ii = nj > 1 ? (int)__umulhi((uint32_t)pq, magic) : pq, jj = pq - ii * nj;
+      const int i = i_first + 2 * ii, j = j_first + 2 * jj;
+      const int oh0 = (i + pbh) >> 1, ow0 = (j + pbw) >> 1;
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      if (pi == 0) {
+        if (pj == 0) pool_grad_px<2, 2>(dpm, argb, OH, OW, oh0, ow0, c8, acc);
+        else pool_grad_px<2, 1>(dpm, argb, OH, OW, oh0, ow0, c8, acc);
+      } else {
+        if (pj == 0) pool_grad_px<1, 2>(dpm, argb, OH, OW, oh0, ow0, c8, acc);
+        else pool_grad_px<1, 1>(dpm, argb, OH, OW, oh0, ow0, c8, acc);
+      }
+      emit(i, j, c8, acc);
+    }
+  }
+}
+
 }  // namespace tc
 }  // namespace b200

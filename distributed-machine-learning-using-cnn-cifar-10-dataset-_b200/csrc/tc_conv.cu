@@ -26,7 +26,7 @@ using namespace tc;
 
 namespace {
 constexpr int LOADERS = 128;
-constexpr int WSTAGES = 2;      // filter stages in shared memory; one stage = the five taps of one filter row
+constexpr int WSTAGES = 3;      // filter stages in shared memory; one stage = the five taps of one filter row
 
 struct ConvGeom {
   int B, H, W, KC, NC;      // batch, image size, contraction channels, output channels
@@ -140,18 +140,12 @@ __device__ __forceinline__ void fill_strip_from_pool(uint8_t* strip, const float
   }
 }
 
-// ---- the same dY strip built by SCATTER (conv2's dgrad): every pooled cell adds its masked gradient to the one
-// conv pixel its argmax selected, in an fp32 tile in shared memory; the tile is then rounded into the strip.  A
-// quarter of the work of the gather above (one add per pooled value instead of <= 4 window tests per conv value).
-// Windows whose (row, column) parities agree are disjoint (3x3, stride 2), so four passes of plain read-add-write
-// need no atomics and add in a fixed order.  NT threads (a multiple of 64), named barrier 3.
+// stage_pool_grad with NT threads and named barrier 3 (conv2's dgrad uses all eight non-TMA warps for its strip)
 template <int NT>
 __device__ __forceinline__ void nt_sync() { asm volatile("bar.sync 3, %0;" ::"n"(NT) : "memory"); }
 template <int NT>
-__device__ __forceinline__ void scatter_pool_grad(uint8_t* strip, float* tile, float* dpm, uint8_t* argb,
-                                                  const ConvGeom& g, const PoolGradSrc& p, int n, int img, int tid,
-                                                  float (&bsum)[8], float* __restrict__ dense_out) {
-  const int ncell = p.OH * p.OW, npx = g.H * g.W;
+__device__ __forceinline__ void stage_pool_grad_nt(float* dpm, uint8_t* argb, const PoolGradSrc& p, int n, int tid) {
+  const int ncell = p.OH * p.OW;
   const float4* dp4 = reinterpret_cast<const float4*>(p.dpool + (size_t)n * ncell * 64);
   const float4* pl4 = reinterpret_cast<const float4*>(p.pool + (size_t)n * ncell * 64);
   const uint32_t* ar4 = reinterpret_cast<const uint32_t*>(p.arg + (size_t)n * ncell * 64);
@@ -160,43 +154,9 @@ __device__ __forceinline__ void scatter_pool_grad(uint8_t* strip, float* tile, f
     float4 d = __ldg(dp4 + q), v = __ldg(pl4 + q);
     d.x = v.x > 0.f ? d.x : 0.f; d.y = v.y > 0.f ? d.y : 0.f;
     d.z = v.z > 0.f ? d.z : 0.f; d.w = v.w > 0.f ? d.w : 0.f;
-    reinterpret_cast<float4*>(dpm)[q] = d;
+    reinterpret_cast<float4*>(dpm)[(q & ~15) + (q & 1) * 8 + ((q & 15) >> 1)] = d;      // layout of pool_grad_px
     reinterpret_cast<uint32_t*>(argb)[q] = __ldg(ar4 + q);
   }
-  for (int q = tid; q < npx * 16; q += NT) reinterpret_cast<float4*>(tile)[q] = make_float4(0.f, 0.f, 0.f, 0.f);
-  nt_sync<NT>();
-#pragma unroll 1
-  for (int pc = 0; pc < 4; ++pc) {
-    const int ph = pc >> 1, pw = pc & 1;
-    const int nh = (p.OH - ph + 1) >> 1, nw = (p.OW - pw + 1) >> 1;
-    for (int q = tid; q < nh * nw * 64; q += NT) {
-      const int ch = q & 63, cq = q >> 6;
-      const int ohh = cq / nw, oh = 2 * ohh + ph, ow = 2 * (cq - ohh * nw) + pw;
-      const int cell = oh * p.OW + ow;
-      const float d = dpm[cell * 64 + ch];
-      const int code = argb[cell * 64 + ch];
-      const int kh = (code * 11) >> 5, kw = code - 3 * kh;            // code = kh*3 + kw in [0, 9)
-      const int r = 2 * oh - p.pbh + kh, c = 2 * ow - p.pbw + kw;     // the argmax is a cell inside the image
-      if (d != 0.f) tile[(r * g.W + c) * 64 + ch] += d;
-    }
-    nt_sync<NT>();
-  }
-  for (int q = tid; q < npx * 8; q += NT) {
-    const int c8 = q & 7, pix = q >> 3;
-    const int i = pix / g.W, j = pix - i * g.W;
-    const float4 a0 = reinterpret_cast<const float4*>(tile)[pix * 16 + c8 * 2];
-    const float4 a1 = reinterpret_cast<const float4*>(tile)[pix * 16 + c8 * 2 + 1];
-    const float acc[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-#pragma unroll
-    for (int e = 0; e < 8; ++e) bsum[e] += acc[e];
-    const int slot = g.lead + (img * g.rows_per_img + i) * g.P + j;
-    *reinterpret_cast<uint4*>(strip + c8 * g.ch_stride + slot * 16) = pack8(acc);
-    if (dense_out) {          // dense NHWC fp32 copy for a consumer that runs later (8 lanes = one pixel's 256 B)
-      float4* o = reinterpret_cast<float4*>(dense_out + (size_t)pix * 64 + c8 * 8);
-      o[0] = a0; o[1] = a1;
-    }
-  }
-  nt_sync<NT>();      // the tile / staging buffers are free again
 }
 
 struct ConvArgs {
@@ -246,7 +206,6 @@ __global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
   float* dpm = reinterpret_cast<float*>(ctrl + 256);                  // POOL: [OH*OW][64] masked pooled gradient
   uint8_t* argb = reinterpret_cast<uint8_t*>(dpm + (POOL ? a.pg.OH * a.pg.OW * 64 : 0));
   float* bred = reinterpret_cast<float*>(argb + (POOL ? ((a.pg.OH * a.pg.OW * 64 + 15) & ~15) : 0));   // [64]
-  float* tile = bred + 64;                                            // POOL: [H*W][64] fp32 scatter target
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int n_img0 = blockIdx.x * g.ipc;
@@ -274,9 +233,25 @@ __global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
     pdl_launch_dependents();
     if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) a.timeline[1] = clock64();
     float bsum[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    for (int img = 0; img < g.ipc && n_img0 + img < g.B; ++img)      // (the first barrier inside also orders the clears)
-      scatter_pool_grad<256>(strip, tile, dpm, argb, g, a.pg, n_img0 + img, img, tid, bsum,
-                             (a.dconv_out && blockIdx.y == 0) ? a.dconv_out + (size_t)(n_img0 + img) * g.H * g.W * 64 : nullptr);
+    for (int img = 0; img < g.ipc && n_img0 + img < g.B; ++img) {
+      const int n = n_img0 + img;
+      if (img) nt_sync<256>();                       // the staging buffers are free again
+      stage_pool_grad_nt<256>(dpm, argb, a.pg, n, tid);
+      nt_sync<256>();                                // (also orders the clears above)
+      float* dense = (a.dconv_out && blockIdx.y == 0) ? a.dconv_out + (size_t)n * g.H * g.W * 64 : nullptr;
+      pool_grad_rows<256>(dpm, argb, g.W, a.pg.OH, a.pg.OW, a.pg.pbh, a.pg.pbw, 0, g.H, tid,
+                          [&](int i, int j, int c8, const float (&acc)[8]) {
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) bsum[e] += acc[e];
+                            const int slot = g.lead + (img * g.rows_per_img + i) * g.P + j;
+                            *reinterpret_cast<uint4*>(strip + c8 * g.ch_stride + slot * 16) = pack8(acc);
+                            if (dense) {     // dense NHWC fp32 copy for the filter gradient, which runs later
+                              float4* o = reinterpret_cast<float4*>(dense + (size_t)(i * g.W + j) * 64 + c8 * 8);
+                              o[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+                              o[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+                            }
+                          });
+    }
     fence_proxy_async();
     mbar_arrive(smem_u32(strip_full));
     if (a.dbias && blockIdx.y == 0) {        // BiasAddGrad of the conv layer: thread <-> channel chunk tid & 7
@@ -513,7 +488,7 @@ int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, 
   const int kchunks = KC / 8;
   const int wstage = 5 * (((DGRAD ? kchunks * (64 * 16 + 16) : 8 * (KC * 16 + 16)) + 127) & ~127);
   int smem = ((kchunks * g.ch_stride + 127) & ~127) + WSTAGES * wstage + 256;
-  if (pg) smem += pg->OH * pg->OW * 64 * 5 + 16 + 256 + H * W * 64 * 4;
+  if (pg) smem += pg->OH * pg->OW * 64 * 5 + 16 + 256;
   B200_REQUIRE(smem <= 227 * 1024, "conv5x5_tc: %d bytes of shared memory needed", smem);
   void (*kern)(ConvArgs) = nullptr;
   if (pg) {

@@ -242,6 +242,9 @@ int conv1_pool_fwd_tc(const uint8_t* img, const float* w, const float* bias, flo
 namespace b200 {
 namespace {
 
+constexpr int C1W_BR = 12;     // image rows per band of the dY strip
+constexpr int C1W_MAXB = 8;    // bands per image the barrier array allows (crops up to 96 rows)
+
 struct Conv1WgradArgs {
   const uint8_t* img;     // [B,3,ih,iw]
   const float* dpool;     // [B,OH,OW,64]  gradient w.r.t. pool1
@@ -250,6 +253,7 @@ struct Conv1WgradArgs {
   float* dw;              // [25][3][64]  += (atomics; zero on entry)
   float* db;              // [64]         += (atomics; zero on entry), may be null
   C1Geom g;
+  long long* timeline;    // diagnostics: clock64 stamps of CTA 0 in slots [25,31) of the timeline buffer, or null
 };
 
 __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
@@ -264,17 +268,18 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
   float* dpm = reinterpret_cast<float*>(ds + ((8 * ch_stride + 127) & ~127));
   uint8_t* argb = reinterpret_cast<uint8_t*>(dpm + (size_t)ncell * 64);
   uint8_t* ctrl = argb + (((size_t)ncell * 64 + 127) & ~127);
-  uint64_t* full = reinterpret_cast<uint64_t*>(ctrl);
-  uint64_t* empty = full + 1;
+  uint64_t* full = reinterpret_cast<uint64_t*>(ctrl);       // one per row band
+  uint64_t* empty = full + C1W_MAXB;
   uint64_t* accum = empty + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum + 1);
+  const int nband = (g.H + C1W_BR - 1) / C1W_BR;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int nimg = (g.B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
   const int ksteps = (g.H * g.P + 15) / 16;
 
   if (tid == 0) {
-    mbar_init(smem_u32(full), WORKERS);
+    for (int b = 0; b < C1W_MAXB; ++b) mbar_init(smem_u32(full + b), WORKERS);
     mbar_init(smem_u32(empty), 5);
     mbar_init(smem_u32(accum), 5);
     fence_mbar_init();
@@ -285,7 +290,9 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
 
+  const bool stamp = a.timeline && blockIdx.x == 0 && tid == 0;
   if (warp < 8) {
+    if (stamp) a.timeline[25] = clock64();
     for (int o = tid * 16; o < 8 * ch_stride; o += WORKERS * 16) *reinterpret_cast<uint4*>(ds + o) = make_uint4(0, 0, 0, 0);
     const int pth = max((g.OH - 1) * 2 + 3 - g.H, 0), ptw = max((g.OW - 1) * 2 + 3 - g.W, 0);
     const int pbh = pth / 2, pbw = ptw / 2;
@@ -309,49 +316,33 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
       const float4* dp4 = reinterpret_cast<const float4*>(a.dpool + (size_t)n * ncell * 64);
       const float4* pl4 = reinterpret_cast<const float4*>(a.pool + (size_t)n * ncell * 64);
       const uint32_t* ar4 = reinterpret_cast<const uint32_t*>(a.arg + (size_t)n * ncell * 64);
-#pragma unroll 3
+#pragma unroll 5
       for (int q = tid; q < ncell * 16; q += WORKERS) {
         float4 d = __ldg(dp4 + q), p = __ldg(pl4 + q);
         d.x = p.x > 0.f ? d.x : 0.f; d.y = p.y > 0.f ? d.y : 0.f;
         d.z = p.z > 0.f ? d.z : 0.f; d.w = p.w > 0.f ? d.w : 0.f;
-        reinterpret_cast<float4*>(dpm)[q] = d;
+        reinterpret_cast<float4*>(dpm)[(q & ~15) + (q & 1) * 8 + ((q & 15) >> 1)] = d;      // layout of pool_grad_px
         reinterpret_cast<uint32_t*>(argb)[q] = __ldg(ar4 + q);
       }
       workers_sync();
-      // dY strip: MaxPoolGrad (gather over the <= 4 windows covering a cell) of the masked gradient
-      for (int q = tid; q < g.H * g.W * 8; q += WORKERS) {
-        const int c8 = q & 7, cellq = q >> 3;
-        const int i = cellq / g.W, j = cellq - i * g.W;
-        float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-        for (int kh = 0; kh < 3; ++kh) {
-          const int r = i + pbh - kh;
-          if (r < 0 || (r & 1) || (r >> 1) >= g.OH) continue;
-#pragma unroll
-          for (int kw = 0; kw < 3; ++kw) {
-            const int cc = j + pbw - kw;
-            if (cc < 0 || (cc & 1) || (cc >> 1) >= g.OW) continue;
-            const int cell = (r >> 1) * g.OW + (cc >> 1);
-            const uint2 ab = *reinterpret_cast<const uint2*>(argb + cell * 64 + c8 * 8);
-            const float4 d0 = *reinterpret_cast<const float4*>(dpm + cell * 64 + c8 * 8);
-            const float4 d1 = *reinterpret_cast<const float4*>(dpm + cell * 64 + c8 * 8 + 4);
-            const uint32_t code = kh * 3 + kw;
-            const float dv[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
-#pragma unroll
-            for (int e = 0; e < 8; ++e) {
-              const uint32_t ae = ((e < 4 ? ab.x : ab.y) >> (8 * (e & 3))) & 0xffu;
-              if (ae == code) acc[e] += dv[e];
-            }
-          }
-        }
-        *reinterpret_cast<uint4*>(ds + c8 * ch_stride + (g.lead + i * g.P + j) * 16) = pack8(acc);
+      if (stamp) a.timeline[26] = clock64();
+      // dY strip = MaxPoolGrad of the masked gradient (parity-aware gather, tc_common.cuh) in bands of C1W_BR image
+      // rows: each finished band is released to the MMA warps while the next one is built
+      for (int b = 0; b < nband; ++b) {
+        const int row0 = b * C1W_BR, rows = min(C1W_BR, g.H - row0);
+        pool_grad_rows<WORKERS>(dpm, argb, g.W, g.OH, g.OW, pbh, pbw, row0, rows, tid,
+                                [&](int i, int j, int c8, const float (&acc)[8]) {
+                                  *reinterpret_cast<uint4*>(ds + c8 * ch_stride + (g.lead + i * g.P + j) * 16) = pack8(acc);
+                                });
+        fence_proxy_async();
+        mbar_arrive(smem_u32(full + b));
       }
-      fence_proxy_async();
-      mbar_arrive(smem_u32(full));
+      if (stamp) a.timeline[27] = clock64();
     }
     // ---- epilogue: D_di[cout][dj*8 + c] (M = 64: lanes 0-15 of each subpartition) -> partial --------
     mbar_wait(smem_u32(accum), 0);
     tc_fence_after();
+    if (stamp) a.timeline[28] = clock64();
     if (warp < 4 && nimg > 0) {
       // D_di[cout][dj*8 + c] -> dW1[(di*5+dj)][c][cout]: 16 adjacent couts per warp instruction, summed across
       // CTAs with fp32 atomics (the 128 per-image partials would otherwise need a reduction kernel of their own)
@@ -374,6 +365,7 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
       }
     }
     tc_fence_before();
+    if (stamp) a.timeline[29] = clock64();
   } else {
     // warps 8..12: one issuing thread per filter row di (own accumulator each)
     if (lane == 0) {
@@ -385,16 +377,18 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
       const uint32_t d = tmem + di * 64;
       uint32_t acc = 0;
       for (int it = 0; it < nimg; ++it) {
-        mbar_wait(smem_u32(full), it & 1);
-        tc_fence_after();
         uint32_t d_lo = d_lo0, x_lo = x_lo0;
         int ks = 0;
-        for (; ks + 2 <= ksteps; ks += 2) {
-          umma_bf16(d, desc_join(d_lo, d_hi), desc_join(x_lo, x_hi), idesc, acc | (uint32_t)ks);
-          umma_bf16(d, desc_join(d_lo + 16, d_hi), desc_join(x_lo + 16, x_hi), idesc, 1u);
-          d_lo += 32; x_lo += 32;
+        for (int b = 0; b < nband; ++b) {
+          mbar_wait(smem_u32(full + b), it & 1);
+          tc_fence_after();
+          // k-steps (16 pixel slots each) that lie completely inside the rows finished so far
+          const int kend = (b == nband - 1) ? ksteps : (min(g.H, (b + 1) * C1W_BR) * g.P) / 16;
+          for (; ks < kend; ++ks) {
+            umma_bf16(d, desc_join(d_lo, d_hi), desc_join(x_lo, x_hi), idesc, acc | (uint32_t)ks);
+            d_lo += 16; x_lo += 16;
+          }
         }
-        if (ks < ksteps) umma_bf16(d, desc_join(d_lo, d_hi), desc_join(x_lo, x_hi), idesc, acc | (uint32_t)ks);
         acc = 1;
         umma_commit(smem_u32(empty));
       }
@@ -410,9 +404,11 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
 }
 
 int conv1_wgrad_ctas(int B) { return std::min(B, kNumSMs); }
+long long* g_conv1_timeline = nullptr;
 size_t conv1_wgrad_smem(const C1Geom& g) {
   size_t xs = (g.npix * 16 + 127) & ~127, ch = g.npix * 16 + 16;
-  return xs + ((8 * ch + 127) & ~127) + (size_t)g.OH * g.OW * 64 * 4 + (((size_t)g.OH * g.OW * 64 + 127) & ~127) + 256;
+  return xs + ((8 * ch + 127) & ~127) + (size_t)g.OH * g.OW * 64 * 4 + (((size_t)g.OH * g.OW * 64 + 127) & ~127) +
+         256;
 }
 }  // namespace
 
@@ -435,11 +431,12 @@ int conv1_wgrad_tc(const uint8_t* img, const float* dpool, const float* pool, co
     B200_CUDA_TRY(cudaMemsetAsync(dw, 0, 75 * 64 * sizeof(float), st));
     if (db) B200_CUDA_TRY(cudaMemsetAsync(db, 0, 64 * sizeof(float), st));
   }
-  Conv1WgradArgs a{img, dpool, pool, arg, dw, db, g};
+  Conv1WgradArgs a{img, dpool, pool, arg, dw, db, g, g_conv1_timeline};
   B200_CUDA_TRY(launch_kernel(conv1_wgrad_kernel, dim3(S), dim3(416), smem, st, a));
   return B200_OK;
 }
 
+void conv1_set_timeline(long long* dev_buf) { g_conv1_timeline = dev_buf; }
 B200_TRACE_SETTER(trace_set_tc_conv1)
 
 }  // namespace b200

@@ -12,10 +12,11 @@ e = b200cnn.TrainStepEngine(batch=B, mode="bf16"); e.init_params(0)
 rng = np.random.default_rng(0)
 img = torch.as_tensor(rng.integers(0, 256, (B, 3, 32, 32), dtype=np.uint8)).cuda()
 lab = torch.as_tensor(rng.integers(0, 10, (B,)).astype(np.int32)).cuda()
-buf = torch.zeros(2 * len(names), dtype=torch.int64, device='cuda')
+buf = torch.zeros(64 + 3 * 512, dtype=torch.int64, device='cuda')
+sel = int(sys.argv[2]) if len(sys.argv) > 2 else -1      # kernel whose CTAs log individually
 _lib.check(lib.b200_debug_trace(buf.data_ptr()))
 def reset():
-    buf[0::2] = torch.iinfo(torch.int64).max; buf[1::2] = 0      # stamps are < 2^63: signed view orders the same
+    buf[0:28:2] = torch.iinfo(torch.int64).max; buf[1:28:2] = 0; buf[28] = sel; buf[64:] = 0      # stamps are < 2^63: signed view orders the same
 tl = torch.zeros(32, dtype=torch.int64, device='cuda')
 lib.b200_debug_conv_timeline(C.cast(tl.data_ptr(), C.POINTER(C.c_int64)))
 e.train_step(img, lab, 0.1); torch.cuda.synchronize()
@@ -25,7 +26,8 @@ for cold in (0, 1):
     for _ in range(5):
         if cold: flush.zero_()
         reset(); torch.cuda.synchronize(); g.replay(); torch.cuda.synchronize()
-    t = buf.cpu().numpy().reshape(-1, 2).astype(np.float64)
+    raw = buf.cpu().numpy()
+    t = raw[:28].reshape(-1, 2).astype(np.float64)
     t0 = t[:, 0].min()
     print("cold" if cold else "hot", "step: %.1f us from first start to last end" % ((t[:, 1].max() - t0) / 1e3))
     for i in np.argsort(t[:, 0]):
@@ -35,4 +37,14 @@ g.replay(); torch.cuda.synchronize()
 t = tl.cpu().numpy()
 print("conv2 dgrad CTA0 cycles since start: zeroed %d filled %d mma_start %d mma_issued %d accum_ready %d epilogue_done %d" % tuple(t[1:7] - t[0]))
 print("conv2 wgrad CTA0 cycles since start: zeroed %d img0 %d all_filled %d accum_ready %d epilogue_done %d" % tuple(t[9:14] - t[8]))
+print("conv1 wgrad CTA0 cycles since start: staged+xstrip %d gathered %d accum_ready %d epilogue_done %d" % tuple(t[26:30] - t[25]))
 print("tail rows phases:", (t[17:25] - t[16:24]).tolist())
+
+if sel >= 0:
+    c = raw[64:].reshape(-1, 3); c = c[c[:, 0] > 0]
+    st = (c[:, 0] - c[:, 0].min()) / 1e3; en = (c[:, 1] - c[:, 0].min()) / 1e3
+    print("%s: %d CTAs; start spread %.1f us; durations min %.1f median %.1f max %.1f us; last end %.1f" % (names[sel], len(c), st.max(), (en - st).min(), np.median(en - st), (en - st).max(), en.max()))
+    order = np.argsort(st)
+    print("  starts (us):", np.round(st[order][::8], 1).tolist())
+    print("  durations (us) in start order:", np.round((en - st)[order][::8], 1).tolist())
+    print("  distinct SMs:", len(set(c[:, 2].tolist())))
