@@ -161,6 +161,27 @@ __device__ __forceinline__ uint4 load_chunk(const float* p) {
   return pack8(f);
 }
 __device__ __forceinline__ uint4 load_chunk(const __nv_bfloat16* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+// the same chunk, but still in the form it left memory in: lets a kernel issue many loads before the first conversion
+template <typename T> struct RawChunk;
+template <> struct RawChunk<float> { float4 a, b; };
+template <> struct RawChunk<__nv_bfloat16> { uint4 v; };
+__device__ __forceinline__ RawChunk<float> load_raw(const float* p, bool ok) {
+  RawChunk<float> r;
+  r.a = r.b = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (ok) { r.a = __ldg(reinterpret_cast<const float4*>(p)); r.b = __ldg(reinterpret_cast<const float4*>(p) + 1); }
+  return r;
+}
+__device__ __forceinline__ RawChunk<__nv_bfloat16> load_raw(const __nv_bfloat16* p, bool ok) {
+  RawChunk<__nv_bfloat16> r;
+  r.v = make_uint4(0, 0, 0, 0);
+  if (ok) r.v = __ldg(reinterpret_cast<const uint4*>(p));
+  return r;
+}
+__device__ __forceinline__ uint4 pack_raw(const RawChunk<float>& r) {
+  const float f[8] = {r.a.x, r.a.y, r.a.z, r.a.w, r.b.x, r.b.y, r.b.z, r.b.w};
+  return pack8(f);
+}
+__device__ __forceinline__ uint4 pack_raw(const RawChunk<__nv_bfloat16>& r) { return r.v; }
 
 
 // ---- MaxPoolGrad by parity-aware gather ---------------------------------------------------------------------------

@@ -78,53 +78,67 @@ __global__ void __launch_bounds__(288, 1) tc_gemm_kernel(GemmArgs g) {
     pdl_launch_dependents();   // after our own wait: a dependent overlaps this kernel only, never our producer
     const TA* A = reinterpret_cast<const TA*>(g.A);
     const TB* B = reinterpret_cast<const TB*>(g.B);
-    for (int kb = 0; kb < nkb; ++kb) {
+    // Each thread moves NA + NB chunks (8 elements) per k-block.  The global loads of a k-block are all issued
+    // before anything is converted, and the NEXT k-block's loads are issued before the current one is converted
+    // and stored: two k-blocks (96 KB per CTA) in flight instead of a round trip per operand per k-block -- with
+    // one CTA per SM the load latency, not bandwidth, bounded this kernel.
+    constexpr int NA = BM * 8 / LOADERS, NB = BN * 8 / LOADERS;
+    static_assert(BM * 8 % LOADERS == 0 && BN * 8 % LOADERS == 0, "chunks must divide over the staging threads");
+    auto issue = [&](int kb, RawChunk<TA> (&ra)[NA], RawChunk<TB> (&rb)[NB]) {
+      const int k0 = kbeg + kb * BK;
+#pragma unroll
+      for (int i = 0; i < NA; ++i) {
+        const int q = tid + i * LOADERS;
+        if (!A_MN) {   // A(m,k) = A[m*lda + k]: 8 consecutive threads read one row's 8 chunks
+          const int c = q & 7, r = q >> 3, m = m0 + r, k = k0 + c * 8;
+          ra[i] = load_raw(A + (int64_t)m * g.lda + k, m < g.M && k < kend);
+        } else {       // A(m,k) = A[k*lda + m]: consecutive threads read consecutive m-chunks of one k row
+          const int gi = q % (BM / 8), kk = q / (BM / 8), m = m0 + gi * 8, k = k0 + kk;
+          ra[i] = load_raw(A + (int64_t)k * g.lda + m, m < g.M && k < kend);
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < NB; ++i) {
+        const int q = tid + i * LOADERS;
+        if (!B_MN) {   // B(k,n) = B[n*ldb + k]
+          const int c = q & 7, r = q >> 3, n = n0 + r, k = k0 + c * 8;
+          rb[i] = load_raw(B + (int64_t)n * g.ldb + k, n < g.N && k < kend);
+        } else {       // B(k,n) = B[k*ldb + n]
+          const int gi = q % (BN / 8), kk = q / (BN / 8), n = n0 + gi * 8, k = k0 + kk;
+          rb[i] = load_raw(B + (int64_t)k * g.ldb + n, n < g.N && k < kend);
+        }
+      }
+    };
+    auto commit = [&](int kb, const RawChunk<TA> (&ra)[NA], const RawChunk<TB> (&rb)[NB]) {
       const int s = kb % STAGES;
       const uint32_t ph = (kb / STAGES) & 1;
       mbar_wait(smem_u32(empty + s), ph ^ 1);
       uint8_t* sa = smem + s * S::STAGE;
       uint8_t* sb = sa + S::A_BYTES;
-      const int k0 = kbeg + kb * BK;
-      if (!A_MN) {   // A(m,k) = A[m*lda + k]: 8 consecutive threads read one row's 8 chunks
 #pragma unroll
-        for (int q = tid; q < BM * 8; q += LOADERS) {
-          int c = q & 7, r = q >> 3;
-          int m = m0 + r, k = k0 + c * 8;
-          uint4 v = make_uint4(0, 0, 0, 0);
-          if (m < g.M && k < kend) v = load_chunk(A + (int64_t)m * g.lda + k);
-          *reinterpret_cast<uint4*>(sa + c * S::A_K_LBO + r * 16) = v;
-        }
-      } else {       // A(m,k) = A[k*lda + m]: consecutive threads read consecutive m-chunks of one k row
-#pragma unroll
-        for (int q = tid; q < BK * (BM / 8); q += LOADERS) {
-          int gi = q % (BM / 8), kk = q / (BM / 8);
-          int m = m0 + gi * 8, k = k0 + kk;
-          uint4 v = make_uint4(0, 0, 0, 0);
-          if (m < g.M && k < kend) v = load_chunk(A + (int64_t)k * g.lda + m);
-          *reinterpret_cast<uint4*>(sa + gi * S::A_MN_SBO + kk * 16) = v;
-        }
+      for (int i = 0; i < NA; ++i) {
+        const int q = tid + i * LOADERS;
+        if (!A_MN) *reinterpret_cast<uint4*>(sa + (q & 7) * S::A_K_LBO + (q >> 3) * 16) = pack_raw(ra[i]);
+        else *reinterpret_cast<uint4*>(sa + (q % (BM / 8)) * S::A_MN_SBO + (q / (BM / 8)) * 16) = pack_raw(ra[i]);
       }
-      if (!B_MN) {   // B(k,n) = B[n*ldb + k]
 #pragma unroll
-        for (int q = tid; q < BN * 8; q += LOADERS) {
-          int c = q & 7, r = q >> 3;
-          int n = n0 + r, k = k0 + c * 8;
-          uint4 v = make_uint4(0, 0, 0, 0);
-          if (n < g.N && k < kend) v = load_chunk(B + (int64_t)n * g.ldb + k);
-          *reinterpret_cast<uint4*>(sb + c * S::B_K_LBO + r * 16) = v;
-        }
-      } else {       // B(k,n) = B[k*ldb + n]
-#pragma unroll
-        for (int q = tid; q < BK * (BN / 8); q += LOADERS) {
-          int gi = q % (BN / 8), kk = q / (BN / 8);
-          int n = n0 + gi * 8, k = k0 + kk;
-          uint4 v = make_uint4(0, 0, 0, 0);
-          if (n < g.N && k < kend) v = load_chunk(B + (int64_t)k * g.ldb + n);
-          *reinterpret_cast<uint4*>(sb + gi * S::B_MN_SBO + kk * 16) = v;
-        }
+      for (int i = 0; i < NB; ++i) {
+        const int q = tid + i * LOADERS;
+        if (!B_MN) *reinterpret_cast<uint4*>(sb + (q & 7) * S::B_K_LBO + (q >> 3) * 16) = pack_raw(rb[i]);
+        else *reinterpret_cast<uint4*>(sb + (q % (BN / 8)) * S::B_MN_SBO + (q / (BN / 8)) * 16) = pack_raw(rb[i]);
       }
       fence_proxy_async();
       mbar_arrive(smem_u32(full + s));
+    };
+    RawChunk<TA> ra0[NA], ra1[NA];
+    RawChunk<TB> rb0[NB], rb1[NB];
+    if (nkb > 0) issue(0, ra0, rb0);
+#pragma unroll 1
+    for (int kb = 0; kb < nkb; kb += 2) {
+      if (kb + 1 < nkb) issue(kb + 1, ra1, rb1);
+      commit(kb, ra0, rb0);
+      if (kb + 2 < nkb) issue(kb + 2, ra0, rb0);
+      if (kb + 1 < nkb) commit(kb + 1, ra1, rb1);
     }
     // ------------------------------ epilogue (warps 0-3: one TMEM lane quarter each) -----------------
     if (warp < 4) {
