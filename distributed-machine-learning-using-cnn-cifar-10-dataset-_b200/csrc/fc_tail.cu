@@ -180,17 +180,20 @@ __global__ void __launch_bounds__(RT) fc_tail_rows_kernel(TailArgs a) {
   pdl_launch_dependents();
   if (RM == 8)      // upper half of the A tile
     for (int i = tid; i < XS; i += RT) reinterpret_cast<uint4*>(xb + 8 * XS)[i] = make_uint4(0, 0, 0, 0);
-  for (int i0 = tid; i0 < RM * f14; i0 += 3 * RT) {
+  if (a.R < RM)      // rows of the tile beyond this CTA's batch rows
+    for (int i = tid; i < (RM - a.R) * XS / 8; i += RT) reinterpret_cast<uint4*>(xb + a.R * XS)[i] = make_uint4(0, 0, 0, 0);
+  constexpr int SL = 2;      // slots (float4 of one row) per thread and batch; every split of both is in flight together
+  for (int i0 = tid; i0 < a.R * f14; i0 += SL * RT) {
     // slots past the end / rows past the batch read a valid address and are not stored: no branch around the loads
-    float4 v[3];
-    const float4* p[3];
-    int rr[3], kk[3];
-    bool on[3];
+    float4 v[SL];
+    const float4* p[SL];
+    int rr[SL], kk[SL];
+    bool on[SL];
 #pragma unroll
-    for (int u = 0; u < 3; ++u) {
-      const int i = min(i0 + u * RT, RM * f14 - 1);
+    for (int u = 0; u < SL; ++u) {
+      const int i = min(i0 + u * RT, a.R * f14 - 1);
       rr[u] = i / f14; kk[u] = i - rr[u] * f14;
-      on[u] = i0 + u * RT < RM * f14;
+      on[u] = i0 + u * RT < a.R * f14;
       const int row = r0 + min(rr[u], nr - 1);
       if (a.n_part > 0) {
         p[u] = reinterpret_cast<const float4*>(a.fc1_part) + (size_t)row * f14 + kk[u];
@@ -202,17 +205,17 @@ __global__ void __launch_bounds__(RT) fc_tail_rows_kernel(TailArgs a) {
     }
     if (a.n_part > 0) {
       const size_t stride4 = (size_t)a.B * f14;
-#pragma unroll 4
+#pragma unroll 12
       for (int s = 0; s < a.n_part; ++s) {
 #pragma unroll
-        for (int u = 0; u < 3; ++u) {
+        for (int u = 0; u < SL; ++u) {
           const float4 q = __ldg(p[u] + s * stride4);
           v[u].x += q.x; v[u].y += q.y; v[u].z += q.z; v[u].w += q.w;
         }
       }
     }
 #pragma unroll
-    for (int u = 0; u < 3; ++u) {
+    for (int u = 0; u < SL; ++u) {
       if (on[u]) {
         if (rr[u] < nr) {
           if (a.n_part > 0) {
