@@ -200,8 +200,10 @@ int b200_bind_workspace(b200_handle h, void* ws, int64_t nbytes) {
 // side streams / events for the independent branches of a bf16 step (lazily, at the first eager call)
 static int ensure_side_streams(b200_model* h) {
   if (h->side[0]) return B200_OK;
+  int prio_lo = 0, prio_hi = 0;      // stream 0 (FC1's dW: 108 big CTAs that the next main-stream kernel must not wait for)
+  B200_CUDA_TRY(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));      // gets its CTAs placed first
   for (int i = 0; i < 2; ++i) {
-    B200_CUDA_TRY(cudaStreamCreateWithFlags(&h->side[i], cudaStreamNonBlocking));
+    B200_CUDA_TRY(cudaStreamCreateWithPriority(&h->side[i], cudaStreamNonBlocking, i == 0 ? prio_hi : prio_lo));
     B200_CUDA_TRY(cudaEventCreateWithFlags(&h->ev_fork[i], cudaEventDisableTiming));
     B200_CUDA_TRY(cudaEventCreateWithFlags(&h->ev_join[i], cudaEventDisableTiming));
   }

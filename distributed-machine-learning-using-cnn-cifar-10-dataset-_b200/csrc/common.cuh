@@ -42,6 +42,15 @@ static inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 #endif
+// Small kernels that share the machine with the tensor-core kernels (side streams) ask for the maximum shared-memory
+// carve-out even though they need little: an SM whose L1/shared split was set for a small-footprint kernel cannot
+// take a 100-200 KB CTA until it has drained, which delayed FC1's dW behind the tail-gradient kernel by 3 us.
+#ifdef __CUDACC__
+template <typename K>
+inline cudaError_t prefer_max_shared(K kernel) {
+  return cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+}
+#endif
 // The next launch through launch_kernel() on this host thread is made with programmatic stream serialization when
 // this flag is set (the step driver in abi.cu sets it in front of the launches it wants overlapped); it resets itself.
 extern thread_local bool g_pdl_next;
@@ -79,22 +88,24 @@ struct TraceScope {
     if (threadIdx.x == 0 && b200_trace_buf) {
       const unsigned long long t = now();
       atomicMin(b200_trace_buf + 2 * id, t);
-      if (b200_trace_buf[2 * TR_COUNT] == (unsigned long long)id) {
-        const int cta = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
-        unsigned sm;
-        asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
-        if (cta < 512) { b200_trace_buf[64 + 3 * cta] = t; b200_trace_buf[64 + 3 * cta + 2] = sm; }
-      }
+      for (int w = 0; w < 2; ++w)       // up to two kernels log per CTA, in regions of 3 * 512 words
+        if (b200_trace_buf[2 * TR_COUNT + w] == (unsigned long long)id) {
+          const int cta = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+          unsigned sm;
+          asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
+          if (cta < 512) { b200_trace_buf[64 + 1536 * w + 3 * cta] = t; b200_trace_buf[64 + 1536 * w + 3 * cta + 2] = sm; }
+        }
     }
   }
   __device__ __forceinline__ ~TraceScope() {
     if (threadIdx.x == 0 && b200_trace_buf) {
       const unsigned long long t = now();
       atomicMax(b200_trace_buf + 2 * id + 1, t);
-      if (b200_trace_buf[2 * TR_COUNT] == (unsigned long long)id) {
-        const int cta = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
-        if (cta < 512) b200_trace_buf[64 + 3 * cta + 1] = t;
-      }
+      for (int w = 0; w < 2; ++w)
+        if (b200_trace_buf[2 * TR_COUNT + w] == (unsigned long long)id) {
+          const int cta = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+          if (cta < 512) b200_trace_buf[64 + 1536 * w + 3 * cta + 1] = t;
+        }
     }
   }
 };

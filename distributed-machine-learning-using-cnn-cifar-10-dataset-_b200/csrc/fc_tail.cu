@@ -604,6 +604,8 @@ int fc_tail(const float* fc1_part, int n_part, const float* b1, float* full1, co
   static bool grads_attr = false, rows_attr[2][5] = {};
   if (!grads_attr) {
     B200_CUDA_TRY(cudaFuncSetAttribute(fc_tail_grads_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    B200_CUDA_TRY(prefer_max_shared(fc_tail_grads_kernel));
+    B200_CUDA_TRY(prefer_max_shared(w2_to_bf16_kernel));
     grads_attr = true;
   }
   const int t1 = cdiv(F2, 64);

@@ -726,6 +726,12 @@ int pack_conv_weights(const float* w, void* wp, int Cin, int Cout, cudaStream_t 
   B200_REQUIRE(Cin % 8 == 0 && Cout % 8 == 0 && Cin > 0 && Cout > 0, "pack_conv_weights: channels must be multiples of 8");
   B200_REQUIRE(((uintptr_t)w & 15) == 0 && ((uintptr_t)wp & 15) == 0, "pack_conv_weights: pointers must be 16-byte aligned");
   const int total = 25 * Cin * (Cout / 8);
+  static bool carve = false;
+  if (!carve) {
+    B200_CUDA_TRY(prefer_max_shared(pack_conv_weights_kernel));
+    B200_CUDA_TRY(prefer_max_shared(reduce_partials_tc));
+    carve = true;
+  }
   pack_conv_weights_kernel<<<std::min(cdiv(total, 256), 2 * kNumSMs), 256, 0, st>>>(w, (uint8_t*)wp, Cin, Cout);
   B200_LAUNCH_CHECK();
   return B200_OK;

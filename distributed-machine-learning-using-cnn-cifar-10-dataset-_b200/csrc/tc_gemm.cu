@@ -46,7 +46,9 @@ struct Smem {
 };
 
 template <int BN, bool A_MN, bool B_MN, typename TA, typename TB>
-__global__ void __launch_bounds__(288, 1) tc_gemm_kernel(GemmArgs g) {
+// (register cap: warps 0, 4 and 8 share one SM sub-partition; at 136 registers they leave room there for two warps of
+//  a small kernel -- the FC tail's gradient kernel runs beside FC1's dW and could not share an SM with it at 153)
+__global__ void __maxnreg__(136) tc_gemm_kernel(GemmArgs g) {
   B200_TRACE_SCOPE(g.trace_id);
   using S = Smem<BN>;
   extern __shared__ __align__(128) uint8_t smem[];

@@ -12,11 +12,12 @@ e = b200cnn.TrainStepEngine(batch=B, mode="bf16"); e.init_params(0)
 rng = np.random.default_rng(0)
 img = torch.as_tensor(rng.integers(0, 256, (B, 3, 32, 32), dtype=np.uint8)).cuda()
 lab = torch.as_tensor(rng.integers(0, 10, (B,)).astype(np.int32)).cuda()
-buf = torch.zeros(64 + 3 * 512, dtype=torch.int64, device='cuda')
+buf = torch.zeros(64 + 2 * 3 * 512, dtype=torch.int64, device='cuda')
+sel2 = int(sys.argv[3]) if len(sys.argv) > 3 else -1
 sel = int(sys.argv[2]) if len(sys.argv) > 2 else -1      # kernel whose CTAs log individually
 _lib.check(lib.b200_debug_trace(buf.data_ptr()))
 def reset():
-    buf[0:28:2] = torch.iinfo(torch.int64).max; buf[1:28:2] = 0; buf[28] = sel; buf[64:] = 0      # stamps are < 2^63: signed view orders the same
+    buf[0:28:2] = torch.iinfo(torch.int64).max; buf[1:28:2] = 0; buf[28] = sel; buf[29] = sel2; buf[64:] = 0      # stamps are < 2^63: signed view orders the same
 tl = torch.zeros(32, dtype=torch.int64, device='cuda')
 lib.b200_debug_conv_timeline(C.cast(tl.data_ptr(), C.POINTER(C.c_int64)))
 e.train_step(img, lab, 0.1); torch.cuda.synchronize()
@@ -41,10 +42,25 @@ print("conv1 wgrad CTA0 cycles since start: staged+xstrip %d gathered %d accum_r
 print("tail rows phases:", (t[17:25] - t[16:24]).tolist())
 
 if sel >= 0:
-    c = raw[64:].reshape(-1, 3); c = c[c[:, 0] > 0]
+    c = raw[64:64 + 1536].reshape(-1, 3); c = c[c[:, 0] > 0]
     st = (c[:, 0] - c[:, 0].min()) / 1e3; en = (c[:, 1] - c[:, 0].min()) / 1e3
     print("%s: %d CTAs; start spread %.1f us; durations min %.1f median %.1f max %.1f us; last end %.1f" % (names[sel], len(c), st.max(), (en - st).min(), np.median(en - st), (en - st).max(), en.max()))
     order = np.argsort(st)
     print("  starts (us):", np.round(st[order][::8], 1).tolist())
     print("  durations (us) in start order:", np.round((en - st)[order][::8], 1).tolist())
     print("  distinct SMs:", len(set(c[:, 2].tolist())))
+
+if sel >= 0 and sel2 >= 0:
+    c2 = raw[64 + 1536:].reshape(-1, 3); c2 = c2[c2[:, 0] > 0]
+    t0 = min(c[:, 0].min(), c2[:, 0].min())
+    both = 0
+    for a in c:
+        for b in c2:
+            if a[2] == b[2] and a[0] < b[1] and b[0] < a[1]: both += 1
+    print("%s x %s: CTA pairs resident on the same SM at the same time: %d" % (names[sel], names[sel2], both))
+    sms2 = {}
+    for b in c2: sms2.setdefault(int(b[2]), []).append(((b[0]-t0)/1e3, (b[1]-t0)/1e3))
+    for a in c[np.argsort(c[:, 0])][:6]:
+        print("  %s CTA on SM %d: %.1f-%.1f; %s there: %s" % (names[sel], a[2], (a[0]-t0)/1e3, (a[1]-t0)/1e3, names[sel2], [(round(x,1), round(y,1)) for x, y in sms2.get(int(a[2]), [])]))
+    for a in c[np.argsort(c[:, 0])][-4:]:
+        print("  %s CTA on SM %d: %.1f-%.1f; %s there: %s" % (names[sel], a[2], (a[0]-t0)/1e3, (a[1]-t0)/1e3, names[sel2], [(round(x,1), round(y,1)) for x, y in sms2.get(int(a[2]), [])]))
