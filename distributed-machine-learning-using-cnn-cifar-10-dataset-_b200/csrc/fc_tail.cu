@@ -556,7 +556,7 @@ __global__ void __launch_bounds__(RT) fc_tail_grads_kernel(TailGradArgs a) {
   else if (v == o4 + 2) *a.n_bad = (int)(s + 0.5f);
 }
 
-int rows_per_cta(int B) { return B <= 1024 ? 8 : 16; }
+int rows_per_cta(int B) { return B <= 256 ? 4 : B <= 1024 ? 8 : 16; }
 long long* g_tail_timeline = nullptr;
 }  // namespace
 

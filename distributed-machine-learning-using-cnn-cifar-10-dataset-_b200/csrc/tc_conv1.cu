@@ -60,9 +60,11 @@ struct Conv1FwdArgs {
   uint8_t* arg;         // [B,OH,OW,64]
   float* conv_dbg;      // [B,H,W,64] or null (tests: lets the pool fusion be checked on its own input)
   C1Geom g;
+  long long* timeline;  // diagnostics: clock64 stamps of CTA 0 in slots 14, 15, 30, 31 of the timeline buffer, or null
 };
 
 constexpr int kWLbo = 64 * 16 + 16;      // B operand: [26 k-chunks][64 cout][16 B], chunk stride padded
+long long* g_conv1_timeline = nullptr;      // diagnostics (b200_debug_conv_timeline)
 constexpr int kConvRow = 68;             // floats per conv-output row in smem (64 + 4: conflict-free STS.128)
 
 __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) {
@@ -94,40 +96,77 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
 
+  const bool stamp = a.timeline && blockIdx.x == 0 && tid == 0;
   if (warp < 8) {
+    if (stamp) a.timeline[14] = clock64();
     for (int o = tid * 16; o < strip_bytes; o += WORKERS * 16) *reinterpret_cast<uint4*>(strip + o) = make_uint4(0, 0, 0, 0);
     workers_sync();
     const uint8_t* rec = a.img + (size_t)n * 3 * g.ih * g.iw;
     const int oy = (g.ih - g.H) / 2, ox = (g.iw - g.W) / 2;
-    for (int q = tid; q < g.H * g.W; q += WORKERS) {
-      int i = q / g.W, j = q - i * g.W;
-      *reinterpret_cast<uint4*>(strip + (g.lead + i * g.P + j) * 16) = pixel_chunk(rec, g.ih, g.iw, i + oy, j + ox, 0.f);
-    }
-    // filter: k-chunk kc = tap kc (tap 25 = zeros); element e<3 of the chunk = w[tap][e][cout]
-    for (int q = tid; q < 26 * 64; q += WORKERS) {
-      int cout = q & 63, kc = q >> 6;
-      float f[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      if (kc < 25) {
-        f[0] = __ldg(a.w + (kc * 3 + 0) * 64 + cout);
-        f[1] = __ldg(a.w + (kc * 3 + 1) * 64 + cout);
-        f[2] = __ldg(a.w + (kc * 3 + 2) * 64 + cout);
+    // Every global load of this phase (the thread's <= PXB pixels x 3 planes and its <= WB filter chunks x 3
+    // channels) is issued before the first conversion: one memory round trip instead of one per item.
+    constexpr int PXB = 3, WB = 7;                       // 3 * 256 >= 24 * 24 pixels, 7 * 256 >= 26 * 64 chunks
+    const int plane = g.ih * g.iw;
+    for (int q0 = tid; q0 < g.H * g.W; q0 += PXB * WORKERS) {
+      uint8_t px[PXB][3];
+      float wv[WB][3];
+#pragma unroll
+      for (int u = 0; u < PXB; ++u) {
+        const int q = min(q0 + u * WORKERS, g.H * g.W - 1);
+        const int i = q / g.W, j = q - i * g.W;
+        const uint8_t* src = rec + (i + oy) * g.iw + (j + ox);
+        px[u][0] = src[0]; px[u][1] = src[plane]; px[u][2] = src[2 * plane];
       }
-      *reinterpret_cast<uint4*>(wB + kc * kWLbo + cout * 16) = pack8(f);
+      const bool first = q0 == tid;                      // the filter rides along with the first pixel batch
+      if (first) {
+#pragma unroll
+        for (int u = 0; u < WB; ++u) {
+          const int q = min(tid + u * WORKERS, 25 * 64 - 1), cout = q & 63, kc = q >> 6;
+#pragma unroll
+          for (int e = 0; e < 3; ++e) wv[u][e] = __ldg(a.w + (kc * 3 + e) * 64 + cout);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < PXB; ++u) {
+        const int q = q0 + u * WORKERS;
+        if (q < g.H * g.W) {
+          const int i = q / g.W, j = q - i * g.W;
+          const float f[8] = {(float)px[u][0], (float)px[u][1], (float)px[u][2], 0.f, 0.f, 0.f, 0.f, 0.f};
+          *reinterpret_cast<uint4*>(strip + (g.lead + i * g.P + j) * 16) = pack8(f);
+        }
+      }
+      if (first) {
+        // filter: k-chunk kc = tap kc (tap 25 = zeros); element e<3 of the chunk = w[tap][e][cout]
+#pragma unroll
+        for (int u = 0; u < WB; ++u) {
+          const int q = tid + u * WORKERS, cout = q & 63, kc = q >> 6;
+          if (q < 26 * 64) {
+            const bool real = kc < 25;
+            const float f[8] = {real ? wv[u][0] : 0.f, real ? wv[u][1] : 0.f, real ? wv[u][2] : 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            *reinterpret_cast<uint4*>(wB + kc * kWLbo + cout * 16) = pack8(f);
+          }
+        }
+      }
     }
     fence_proxy_async();
     mbar_arrive(smem_u32(ready));
+    if (stamp) a.timeline[15] = clock64();
 
     // ---- epilogue 1: TMEM -> +bias, ReLU -> fp32 conv tile in shared memory ------------------------
     mbar_wait(smem_u32(accum), 0);
     tc_fence_after();
-    for (int t = (warp >> 2); t < g.tiles; t += 2) {
-      const int p = t * 128 + (warp & 3) * 32 + lane;
-      const int r = p / g.P, c = p - r * g.P;
-      const bool valid = (r < g.H) && (c < g.W);
-      float* row = convbuf + (size_t)(r * g.W + c) * kConvRow;
-      float* dbg = a.conv_dbg ? a.conv_dbg + (((size_t)n * g.H + r) * g.W + c) * 64 : nullptr;
+    if (stamp) a.timeline[30] = clock64();
 #pragma unroll 1
-      for (int c0 = 0; c0 < 64; c0 += 32) {
+    for (int c0 = 0; c0 < 64; c0 += 32) {
+      float bv[32];
+#pragma unroll
+      for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(bv + j) = __ldg(reinterpret_cast<const float4*>(a.bias + c0 + j));
+      for (int t = (warp >> 2); t < g.tiles; t += 2) {
+        const int p = t * 128 + (warp & 3) * 32 + lane;
+        const int r = p / g.P, c = p - r * g.P;
+        const bool valid = (r < g.H) && (c < g.W);
+        float* row = convbuf + (size_t)(r * g.W + c) * kConvRow;
+        float* dbg = a.conv_dbg ? a.conv_dbg + (((size_t)n * g.H + r) * g.W + c) * 64 : nullptr;
         uint32_t v[32];
         tmem_ld32(tmem + ((uint32_t)((warp & 3) * 32) << 16) + t * 64 + c0, v);
         tmem_ld_wait();
@@ -135,10 +174,10 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
             float4 o;
-            o.x = fmaxf(__uint_as_float(v[j + 0]) + __ldg(a.bias + c0 + j + 0), 0.f);
-            o.y = fmaxf(__uint_as_float(v[j + 1]) + __ldg(a.bias + c0 + j + 1), 0.f);
-            o.z = fmaxf(__uint_as_float(v[j + 2]) + __ldg(a.bias + c0 + j + 2), 0.f);
-            o.w = fmaxf(__uint_as_float(v[j + 3]) + __ldg(a.bias + c0 + j + 3), 0.f);
+            o.x = fmaxf(__uint_as_float(v[j + 0]) + bv[j + 0], 0.f);
+            o.y = fmaxf(__uint_as_float(v[j + 1]) + bv[j + 1], 0.f);
+            o.z = fmaxf(__uint_as_float(v[j + 2]) + bv[j + 2], 0.f);
+            o.w = fmaxf(__uint_as_float(v[j + 3]) + bv[j + 3], 0.f);
             *reinterpret_cast<float4*>(row + c0 + j) = o;
             if (dbg) *reinterpret_cast<float4*>(dbg + c0 + j) = o;
           }
@@ -147,34 +186,46 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
     }
     tc_fence_before();
     workers_sync();
+    if (stamp) a.timeline[31] = clock64();
     // ---- epilogue 2: 3x3/2 SAME max-pool (pad 0 before / 1 after), first max in (h,w) scan order ---
     const int pth = max((g.OH - 1) * 2 + 3 - g.H, 0), ptw = max((g.OW - 1) * 2 + 3 - g.W, 0);
     const int pbh = pth / 2, pbw = ptw / 2;
-    for (int q = tid; q < g.OH * g.OW * 16; q += WORKERS) {
-      const int cq = q & 15, cell = q >> 4;
+    // One item = 8 channels of one pooled cell (eight independent compare/select chains); window positions outside
+    // the image read a clamped address and enter the scan as -FLT_MAX, so there is no branch in the scan.  The scan
+    // runs in (kh, kw) order with a strict '>': the first maximum wins, as in the reference's MaxPoolWithArgmax use.
+#pragma unroll 1
+    for (int q = tid; q < g.OH * g.OW * 8; q += WORKERS) {
+      const int c8 = q & 7, cell = q >> 3;
       const int oh = cell / g.OW, ow = cell - oh * g.OW;
-      float best[4];
-      int bi[4] = {0, 0, 0, 0};
-      bool any = false;
+      float best[8];
+      int bi[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) { best[e] = -3.402823466e38f; bi[e] = 0; }
 #pragma unroll
       for (int kh = 0; kh < 3; ++kh) {
         const int h = 2 * oh + kh - pbh;
-        if ((unsigned)h >= (unsigned)g.H) continue;
+        const bool vh = (unsigned)h < (unsigned)g.H;
 #pragma unroll
         for (int kw = 0; kw < 3; ++kw) {
           const int w = 2 * ow + kw - pbw;
-          if ((unsigned)w >= (unsigned)g.W) continue;
-          const float4 v = *reinterpret_cast<const float4*>(convbuf + (size_t)(h * g.W + w) * kConvRow + cq * 4);
-          const float vv[4] = {v.x, v.y, v.z, v.w};
+          const bool ok = vh && (unsigned)w < (unsigned)g.W;
+          const float* src = convbuf + (size_t)(ok ? h * g.W + w : 0) * kConvRow + c8 * 8;
+          const float4 v0 = *reinterpret_cast<const float4*>(src), v1 = *reinterpret_cast<const float4*>(src + 4);
+          const float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
 #pragma unroll
-          for (int e = 0; e < 4; ++e)
-            if (!any || vv[e] > best[e]) { best[e] = vv[e]; bi[e] = kh * 3 + kw; }
-          any = true;
+          for (int e = 0; e < 8; ++e) {
+            const float x = ok ? vv[e] : -3.402823466e38f;
+            const bool gt = x > best[e];
+            best[e] = gt ? x : best[e];
+            bi[e] = gt ? kh * 3 + kw : bi[e];
+          }
         }
       }
-      const size_t o = ((size_t)n * g.OH * g.OW + cell) * 64 + cq * 4;
+      const size_t o = ((size_t)n * g.OH * g.OW + cell) * 64 + c8 * 8;
       *reinterpret_cast<float4*>(a.pool + o) = make_float4(best[0], best[1], best[2], best[3]);
-      *reinterpret_cast<uchar4*>(a.arg + o) = make_uchar4(bi[0], bi[1], bi[2], bi[3]);
+      *reinterpret_cast<float4*>(a.pool + o + 4) = make_float4(best[4], best[5], best[6], best[7]);
+      *reinterpret_cast<uint2*>(a.arg + o) = make_uint2(bi[0] | (bi[1] << 8) | (bi[2] << 16) | (bi[3] << 24),
+                                                        bi[4] | (bi[5] << 8) | (bi[6] << 16) | (bi[7] << 24));
     }
   } else {
     // warps 8..10: three issuing threads, tiles t = w, w+3, ... each (13 MMAs per tile)
@@ -228,7 +279,7 @@ int conv1_pool_fwd_tc(const uint8_t* img, const float* w, const float* bias, flo
     B200_CUDA_TRY(cudaFuncSetAttribute(conv1_pool_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr = true;
   }
-  Conv1FwdArgs a{img, w, bias, pool, arg, conv_dbg, g};
+  Conv1FwdArgs a{img, w, bias, pool, arg, conv_dbg, g, g_conv1_timeline};
   conv1_pool_fwd_kernel<<<B, 352, smem, st>>>(a);
   B200_LAUNCH_CHECK();
   return B200_OK;
@@ -404,7 +455,6 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
 }
 
 int conv1_wgrad_ctas(int B) { return std::min(B, kNumSMs); }
-long long* g_conv1_timeline = nullptr;
 size_t conv1_wgrad_smem(const C1Geom& g) {
   size_t xs = (g.npix * 16 + 127) & ~127, ch = g.npix * 16 + 16;
   return xs + ((8 * ch + 127) & ~127) + (size_t)g.OH * g.OW * 64 * 4 + (((size_t)g.OH * g.OW * 64 + 127) & ~127) +

@@ -39,6 +39,7 @@ t = tl.cpu().numpy()
 print("conv2 dgrad CTA0 cycles since start: zeroed %d filled %d mma_start %d mma_issued %d accum_ready %d epilogue_done %d" % tuple(t[1:7] - t[0]))
 print("conv2 wgrad CTA0 cycles since start: zeroed %d img0 %d all_filled %d accum_ready %d epilogue_done %d" % tuple(t[9:14] - t[8]))
 print("conv1 wgrad CTA0 cycles since start: staged+xstrip %d gathered %d accum_ready %d epilogue_done %d" % tuple(t[26:30] - t[25]))
+print("conv1 fwd CTA0 cycles since start: strip+filter ready %d accum_ready %d conv tile in smem %d" % (t[15]-t[14], t[30]-t[14], t[31]-t[14]))
 print("tail rows phases:", (t[17:25] - t[16:24]).tolist())
 
 if sel >= 0:
