@@ -78,8 +78,8 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
   float* convbuf = reinterpret_cast<float*>(wB + 26 * kWLbo + 64);
   uint8_t* ctrl = reinterpret_cast<uint8_t*>(convbuf + (size_t)g.H * g.W * kConvRow);
   uint64_t* ready = reinterpret_cast<uint64_t*>(ctrl);
-  uint64_t* accum = ready + 1;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum + 1);
+  uint64_t* accum = ready + 1;              // one per 128-pixel tile (<= 8): the epilogue of a tile overlaps later MMAs
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum + 8);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int n = blockIdx.x;
@@ -87,7 +87,7 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
 
   if (tid == 0) {
     mbar_init(smem_u32(ready), WORKERS);
-    mbar_init(smem_u32(accum), 3);
+    for (int t = 0; t < 8; ++t) mbar_init(smem_u32(accum + t), 1);
     fence_mbar_init();
   }
   if (warp == 8) tmem_alloc(smem_u32(tmem_slot), tmem_cols);
@@ -152,21 +152,21 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
     mbar_arrive(smem_u32(ready));
     if (stamp) a.timeline[15] = clock64();
 
-    // ---- epilogue 1: TMEM -> +bias, ReLU -> fp32 conv tile in shared memory ------------------------
-    mbar_wait(smem_u32(accum), 0);
-    tc_fence_after();
-    if (stamp) a.timeline[30] = clock64();
-#pragma unroll 1
-    for (int c0 = 0; c0 < 64; c0 += 32) {
-      float bv[32];
+    // ---- epilogue 1: TMEM -> +bias, ReLU -> fp32 conv tile in shared memory, tile by tile as the MMAs finish ----
+    float bv[64];
 #pragma unroll
-      for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(bv + j) = __ldg(reinterpret_cast<const float4*>(a.bias + c0 + j));
-      for (int t = (warp >> 2); t < g.tiles; t += 2) {
-        const int p = t * 128 + (warp & 3) * 32 + lane;
-        const int r = p / g.P, c = p - r * g.P;
-        const bool valid = (r < g.H) && (c < g.W);
-        float* row = convbuf + (size_t)(r * g.W + c) * kConvRow;
-        float* dbg = a.conv_dbg ? a.conv_dbg + (((size_t)n * g.H + r) * g.W + c) * 64 : nullptr;
+    for (int j = 0; j < 64; j += 4) *reinterpret_cast<float4*>(bv + j) = __ldg(reinterpret_cast<const float4*>(a.bias + j));
+    for (int t = (warp >> 2); t < g.tiles; t += 2) {
+      mbar_wait(smem_u32(accum + t), 0);
+      tc_fence_after();
+      if (stamp && t == 0) a.timeline[30] = clock64();
+      const int p = t * 128 + (warp & 3) * 32 + lane;
+      const int r = p / g.P, c = p - r * g.P;
+      const bool valid = (r < g.H) && (c < g.W);
+      float* row = convbuf + (size_t)(r * g.W + c) * kConvRow;
+      float* dbg = a.conv_dbg ? a.conv_dbg + (((size_t)n * g.H + r) * g.W + c) * 64 : nullptr;
+#pragma unroll
+      for (int c0 = 0; c0 < 64; c0 += 32) {
         uint32_t v[32];
         tmem_ld32(tmem + ((uint32_t)((warp & 3) * 32) << 16) + t * 64 + c0, v);
         tmem_ld_wait();
@@ -174,10 +174,10 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
             float4 o;
-            o.x = fmaxf(__uint_as_float(v[j + 0]) + bv[j + 0], 0.f);
-            o.y = fmaxf(__uint_as_float(v[j + 1]) + bv[j + 1], 0.f);
-            o.z = fmaxf(__uint_as_float(v[j + 2]) + bv[j + 2], 0.f);
-            o.w = fmaxf(__uint_as_float(v[j + 3]) + bv[j + 3], 0.f);
+            o.x = fmaxf(__uint_as_float(v[j + 0]) + bv[c0 + j + 0], 0.f);
+            o.y = fmaxf(__uint_as_float(v[j + 1]) + bv[c0 + j + 1], 0.f);
+            o.z = fmaxf(__uint_as_float(v[j + 2]) + bv[c0 + j + 2], 0.f);
+            o.w = fmaxf(__uint_as_float(v[j + 3]) + bv[c0 + j + 3], 0.f);
             *reinterpret_cast<float4*>(row + c0 + j) = o;
             if (dbg) *reinterpret_cast<float4*>(dbg + c0 + j) = o;
           }
@@ -185,8 +185,35 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
       }
     }
     tc_fence_before();
-    workers_sync();
-    if (stamp) a.timeline[31] = clock64();
+  } else {
+    // warps 8..10: three issuing threads, tiles t = w, w+3, ... each (13 MMAs per tile, one commit per tile)
+    if (lane == 0) {
+      const int w = warp - 8;
+      const uint32_t idesc = make_idesc(128, 64, false, false);
+      mbar_wait(smem_u32(ready), 0);
+      tc_fence_after();
+      const uint32_t a_hi = desc_hi(128), b_hi = desc_hi(128);
+      const uint32_t a_base = ((smem_u32(strip) >> 4) + g.lead) & 0x3FFFu;      // address field of slot `lead`
+      for (int t = w; t < g.tiles; t += 3) {
+        uint32_t b_lo = desc_lo(smem_u32(wB), kWLbo);
+        const uint32_t d = tmem + t * 64;
+#pragma unroll
+        for (int ks = 0; ks < 13; ++ks) {
+          const int t0 = 2 * ks, t1 = 2 * ks + 1;                               // compile-time after unrolling
+          const int off0 = (t0 / 5 - 2) * g.P + (t0 % 5 - 2);
+          const int off1 = (t1 < 25) ? (t1 / 5 - 2) * g.P + (t1 % 5 - 2) : off0 + 1;   // dummy tap: zero weights
+          const uint32_t a_lo = (a_base + (uint32_t)(off0 + t * 128)) | ((uint32_t)(off1 - off0) << 16);   // LBO = tap distance
+          umma_bf16(d, desc_join(a_lo, a_hi), desc_join(b_lo, b_hi), idesc, ks ? 1u : 0u);
+          b_lo += 2 * (kWLbo >> 4);
+        }
+        umma_commit(smem_u32(accum + t));
+      }
+    }
+    __syncwarp();
+  }
+  __syncthreads();       // the conv tile is complete; all eleven warps pool it
+  if (stamp) a.timeline[31] = clock64();
+  {
     // ---- epilogue 2: 3x3/2 SAME max-pool (pad 0 before / 1 after), first max in (h,w) scan order ---
     const int pth = max((g.OH - 1) * 2 + 3 - g.H, 0), ptw = max((g.OW - 1) * 2 + 3 - g.W, 0);
     const int pbh = pth / 2, pbw = ptw / 2;
@@ -194,7 +221,7 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
     // the image read a clamped address and enter the scan as -FLT_MAX, so there is no branch in the scan.  The scan
     // runs in (kh, kw) order with a strict '>': the first maximum wins, as in the reference's MaxPoolWithArgmax use.
 #pragma unroll 1
-    for (int q = tid; q < g.OH * g.OW * 8; q += WORKERS) {
+    for (int q = tid; q < g.OH * g.OW * 8; q += (int)blockDim.x) {
       const int c8 = q & 7, cell = q >> 3;
       const int oh = cell / g.OW, ow = cell - oh * g.OW;
       float best[8];
@@ -227,31 +254,6 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
       *reinterpret_cast<uint2*>(a.arg + o) = make_uint2(bi[0] | (bi[1] << 8) | (bi[2] << 16) | (bi[3] << 24),
                                                         bi[4] | (bi[5] << 8) | (bi[6] << 16) | (bi[7] << 24));
     }
-  } else {
-    // warps 8..10: three issuing threads, tiles t = w, w+3, ... each (13 MMAs per tile)
-    if (lane == 0) {
-      const int w = warp - 8;
-      const uint32_t idesc = make_idesc(128, 64, false, false);
-      mbar_wait(smem_u32(ready), 0);
-      tc_fence_after();
-      const uint32_t a_hi = desc_hi(128), b_hi = desc_hi(128);
-      const uint32_t a_base = ((smem_u32(strip) >> 4) + g.lead) & 0x3FFFu;      // address field of slot `lead`
-      for (int t = w; t < g.tiles; t += 3) {
-        uint32_t b_lo = desc_lo(smem_u32(wB), kWLbo);
-        const uint32_t d = tmem + t * 64;
-#pragma unroll
-        for (int ks = 0; ks < 13; ++ks) {
-          const int t0 = 2 * ks, t1 = 2 * ks + 1;                               // compile-time after unrolling
-          const int off0 = (t0 / 5 - 2) * g.P + (t0 % 5 - 2);
-          const int off1 = (t1 < 25) ? (t1 / 5 - 2) * g.P + (t1 % 5 - 2) : off0 + 1;   // dummy tap: zero weights
-          const uint32_t a_lo = (a_base + (uint32_t)(off0 + t * 128)) | ((uint32_t)(off1 - off0) << 16);   // LBO = tap distance
-          umma_bf16(d, desc_join(a_lo, a_hi), desc_join(b_lo, b_hi), idesc, ks ? 1u : 0u);
-          b_lo += 2 * (kWLbo >> 4);
-        }
-      }
-      umma_commit(smem_u32(accum));
-    }
-    __syncwarp();
   }
   __syncthreads();
   if (warp == 8) {
