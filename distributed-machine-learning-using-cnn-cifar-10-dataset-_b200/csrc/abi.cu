@@ -121,6 +121,7 @@ int b200_create(const b200_config* c, b200_handle* out) {
   h->add("full1", B * c->f1, 4); h->add("full2", B * c->f2, 4); h->add("logits", B * c->n_cls, 4);
   h->add("dlogits", B * c->n_cls, 4); h->add("dfull2", B * c->f2, 4); h->add("dfull1", B * c->f1, 4);
   h->add("dpool2", n_p2, 4);  h->add("dconv2", n_c2, 4);
+  h->add("pool1_bf16", n_p1, 2);  h->add("dconv2_bf16", n_c2, 2);      // bf16 mode: operand copies for conv2 fwd / wgrad
   h->add("dpool1", n_p1, 4);  h->add("dconv1", n_c1, 4);
   h->add("wrot", 25ll * c->c1 * c->c2, 4);
   int64_t scratch = conv5x5_wgrad_scratch_bytes(c->batch, c->crop_h, c->crop_w, c->c_in, c->c1);
@@ -272,7 +273,7 @@ static int forward_impl(b200_handle h, const uint8_t* images, const int32_t* lab
   }
   if (fused1) {
     SITE("conv1_pool1_fwd", conv1_pool_fwd_tc(images, h->P(P_W1), h->P(P_B1), pool1, h->ptr<uint8_t>("arg1"), nullptr,
-                                              c.batch, c.img_h, c.img_w, c.crop_h, c.crop_w, st));
+                                              c.batch, c.img_h, c.img_w, c.crop_h, c.crop_w, st, h->ptr<void>("pool1_bf16")));
   } else {
     SITE("crop_cast", crop_cast_f32(images, x, c.batch, c.img_h, c.img_w, c.crop_h, c.crop_w, c.c_in, st));
     SITE("conv1_fwd", conv5x5_fwd_f32(x, h->P(P_W1), h->P(P_B1), conv1, c.batch, c.crop_h, c.crop_w, c.c_in, c.c1, 1, st));
@@ -283,7 +284,8 @@ static int forward_impl(b200_handle h, const uint8_t* images, const int32_t* lab
     // conv2 + bias + ReLU + pool2 in one kernel; the un-pooled activations are not needed again (the
     // backward gathers through pool2 / arg2)
     SITE("conv2_pool2_fwd", conv5x5_pool_fwd_tc(pool1, h->ptr<void>("w2_packed"), h->P(P_B2), nullptr, pool2,
-                                                h->ptr<uint8_t>("arg2"), c.batch, h->h1, h->w1, c.c1, c.c2, st));
+                                                h->ptr<uint8_t>("arg2"), c.batch, h->h1, h->w1, c.c1, c.c2, st,
+                                                nullptr));
   }
   else
     SITE("conv2_fwd", conv5x5_fwd_f32(pool1, h->P(P_W2), h->P(P_B2), conv2, c.batch, h->h1, h->w1, c.c1, c.c2, 1, st));
@@ -366,16 +368,21 @@ int b200_backward(b200_handle h, void* stream) {
     // pool2, arg2) while it builds its strip, adds the bias gradient (atomics into the buffer the tail kernel
     // cleared) and leaves dconv2 behind for the filter gradient, which then overlaps conv1's gradient.
     SITE("conv2_dgrad", conv5x5_dgrad_pool_tc(dpool2, h->ptr<float>("pool2"), h->ptr<uint8_t>("arg2"),
-                                              h->ptr<void>("w2_packed"), dpool1, h->G(P_B2), dconv2, c.batch, h->h1,
-                                              h->w1, c.c1, c.c2, st));
+                                              h->ptr<void>("w2_packed"), dpool1, h->G(P_B2),
+                                              fused1 ? nullptr : dconv2, c.batch, h->h1, h->w1, c.c1, c.c2, st,
+                                              fused1 ? h->ptr<void>("dconv2_bf16") : nullptr));
     if (fork) {
       B200_CUDA_TRY(cudaEventRecord(h->ev_fork[1], st));
       B200_CUDA_TRY(cudaStreamWaitEvent(s1, h->ev_fork[1], 0));
     }
     {
       cudaStream_t st = s1;
+      // (x and dY as the bf16 copies conv1's forward and conv2's dgrad left behind: the five filter-row CTAs of an
+      //  image group each re-read both strips, so halving the bytes is what this L2-bound kernel needs)
       PSITE("conv2_wgrad", conv5x5_wgrad_tc(h->ptr<float>("pool1"), dconv2, h->G(P_W2), h->ptr<float>("scratch2"),
-                                           c.batch, h->h1, h->w1, c.c1, c.c2, st));
+                                           c.batch, h->h1, h->w1, c.c1, c.c2, st,
+                                           fused1 ? h->ptr<void>("pool1_bf16") : nullptr,
+                                           fused1 ? h->ptr<void>("dconv2_bf16") : nullptr));
     }
     if (fused1) {
       SITE("conv1_wgrad", conv1_wgrad_tc(h->last_images, dpool1, h->ptr<float>("pool1"), h->ptr<uint8_t>("arg1"),

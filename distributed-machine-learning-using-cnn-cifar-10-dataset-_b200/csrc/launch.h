@@ -43,20 +43,23 @@ int64_t conv5x5_packed_bytes(int Cin, int Cout);
 int pack_conv_weights(const float* w, void* wp, int Cin, int Cout, cudaStream_t st);
 int conv5x5_fwd_tc(const float* x, const void* wp, const float* bias, float* y, int B, int H, int W, int Cin,
                    int Cout, int relu, cudaStream_t st);
+// x_bf16 (optional): the same activations already rounded to bf16, [B,H,W,Cin]; read instead of x (half the bytes)
 int conv5x5_pool_fwd_tc(const float* x, const void* wp, const float* bias, float* y, float* pool, uint8_t* arg, int B,
-                        int H, int W, int Cin, int Cout, cudaStream_t st);
+                        int H, int W, int Cin, int Cout, cudaStream_t st, const void* x_bf16 = nullptr);
 int conv5x5_dgrad_tc(const float* dy, const void* wp, float* dx, int B, int H, int W, int Cin, int Cout,
                      cudaStream_t st);
 // the same two gradients fed by the POOLED gradient: dconv = MaxPoolGrad(dpool, arg) * [pool > 0] is gathered
 // inside the kernels (64 channels); dbias (optional, zero on entry) receives sum(dconv) through atomics;
 // dconv_out (optional) receives dconv as a dense [B,H,W,64] fp32 tensor
 int conv5x5_dgrad_pool_tc(const float* dpool, const float* pool, const uint8_t* arg, const void* wp, float* dx,
-                          float* dbias, float* dconv_out, int B, int H, int W, int Cin, int Cout, cudaStream_t st);
+                          float* dbias, float* dconv_out, int B, int H, int W, int Cin, int Cout, cudaStream_t st,
+                          void* dconv_out_bf16 = nullptr);      // (optional) dconv as a dense bf16 tensor
 int conv5x5_wgrad_pool_tc(const float* x, const float* dpool, const float* pool, const uint8_t* arg, float* dw,
                           float* scratch, int B, int H, int W, int Cin, int Cout, cudaStream_t st);
 int64_t conv5x5_wgrad_tc_scratch_bytes(int B);
+// x_bf16 / dy_bf16 (optional, both or none): bf16 copies of x / dy, read instead of the fp32 tensors
 int conv5x5_wgrad_tc(const float* x, const float* dy, float* dw, float* scratch, int B, int H, int W, int Cin,
-                     int Cout, cudaStream_t st);
+                     int Cout, cudaStream_t st, const void* x_bf16 = nullptr, const void* dy_bf16 = nullptr);
 int fc_fwd_tc_splits(int B, int K, int N);
 int fc_fwd_tc_splitk(const float* x, const float* w, float* part, int B, int K, int N, cudaStream_t st);
 void fc_tail_set_timeline(long long* dev_buf);
@@ -81,7 +84,8 @@ int p2p_allreduce_sgd(const void* const* peer_grads, void* const* peer_params, v
                       float lr, float scale, cudaStream_t st);
 bool conv1_tc_supported(int H, int W, int c_in, int c1);
 int conv1_pool_fwd_tc(const uint8_t* img, const float* w, const float* bias, float* pool, uint8_t* arg,
-                      float* conv_dbg, int B, int ih, int iw, int H, int W, cudaStream_t st);
+                      float* conv_dbg, int B, int ih, int iw, int H, int W, cudaStream_t st,
+                      void* pool_bf16 = nullptr);      // (optional) second copy of pool, rounded to bf16
 int64_t conv1_wgrad_tc_scratch_bytes(int B);
 int conv1_wgrad_tc(const uint8_t* img, const float* dpool, const float* pool, const uint8_t* arg, float* dw, float* db,
                    float* scratch, int B, int ih, int iw, int H, int W, cudaStream_t st, bool prezeroed = false);

@@ -74,6 +74,26 @@ __device__ __forceinline__ void fill_strip(uint8_t* strip, const float* __restri
   }
 }
 
+// the same from a tensor that is already bf16: one 16-byte load per chunk, no conversion
+__device__ __forceinline__ void fill_strip_bf16(uint8_t* strip, const __nv_bfloat16* __restrict__ x, const ConvGeom& g,
+                                                int n0, int C, int ch_stride, int tid) {
+  const int cpp = C >> 3;
+  const int per_img = g.H * g.W * cpp;
+  for (int img = 0; img < g.ipc; ++img) {
+    const int n = n0 + img;
+    if (n >= g.B) break;
+    const uint4* src = reinterpret_cast<const uint4*>(x + (int64_t)n * g.H * g.W * C);
+#pragma unroll 9
+    for (int q = tid; q < per_img; q += LOADERS) {
+      int c = q % cpp, pix = q / cpp;
+      int j = pix % g.W, i = pix / g.W;
+      uint4 v = __ldg(src + q);
+      int slot = g.lead + (img * g.rows_per_img + i) * g.P + j;
+      *reinterpret_cast<uint4*>(strip + c * ch_stride + slot * 16) = v;
+    }
+  }
+}
+
 // ---- a dY strip built straight from the pooled gradient -------------------------------------------
 // dconv = MaxPoolGrad(dpool, arg) * ReluGrad, the gradient w.r.t. the conv output that fed a 3x3/2 SAME
 // max-pool (cifar10cnn.py:123), never materialised in HBM: the pooled gradient (masked by pool > 0, the
@@ -161,6 +181,8 @@ __device__ __forceinline__ void stage_pool_grad_nt(float* dpm, uint8_t* argb, co
 
 struct ConvArgs {
   const float* x;      // [B,H,W,KC]
+  const __nv_bfloat16* xb;   // the same, already bf16 (read instead of x when given)
+  __nv_bfloat16* dconv_out_bf16;   // POOL dgrad: dense bf16 copy of the gathered dY (optional)
   const uint8_t* wp;   // filter packed by pack_conv_weights (bf16, ready-made shared-memory images per tap)
   int cin_f, cout_f;   // the FORWARD filter's channel counts (packing geometry)
   const float* bias;   // [NC] or null
@@ -239,12 +261,15 @@ __global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
       stage_pool_grad_nt<256>(dpm, argb, a.pg, n, tid);
       nt_sync<256>();                                // (also orders the clears above)
       float* dense = (a.dconv_out && blockIdx.y == 0) ? a.dconv_out + (size_t)n * g.H * g.W * 64 : nullptr;
+      __nv_bfloat16* dense16 = (a.dconv_out_bf16 && blockIdx.y == 0) ? a.dconv_out_bf16 + (size_t)n * g.H * g.W * 64 : nullptr;
       pool_grad_rows<256>(dpm, argb, g.W, a.pg.OH, a.pg.OW, a.pg.pbh, a.pg.pbw, 0, g.H, tid,
                           [&](int i, int j, int c8, const float (&acc)[8]) {
 #pragma unroll
                             for (int e = 0; e < 8; ++e) bsum[e] += acc[e];
                             const int slot = g.lead + (img * g.rows_per_img + i) * g.P + j;
-                            *reinterpret_cast<uint4*>(strip + c8 * g.ch_stride + slot * 16) = pack8(acc);
+                            const uint4 packed = pack8(acc);
+                            *reinterpret_cast<uint4*>(strip + c8 * g.ch_stride + slot * 16) = packed;
+                            if (dense16) *reinterpret_cast<uint4*>(dense16 + (size_t)(i * g.W + j) * 64 + c8 * 8) = packed;
                             if (dense) {     // dense NHWC fp32 copy for the filter gradient, which runs later
                               float4* o = reinterpret_cast<float4*>(dense + (size_t)(i * g.W + j) * 64 + c8 * 8);
                               o[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
@@ -280,7 +305,8 @@ __global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
       pdl_wait();      // these warps are the only ones that touch global memory besides the filter fetch (TMA warp)
       pdl_launch_dependents();   // after our own wait: a dependent overlaps this kernel only, never our producer
       if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) a.timeline[1] = clock64();
-      fill_strip(strip, a.x, g, n_img0, g.KC, g.ch_stride, tid);
+      if (a.xb) fill_strip_bf16(strip, a.xb, g, n_img0, g.KC, g.ch_stride, tid);
+      else fill_strip(strip, a.x, g, n_img0, g.KC, g.ch_stride, tid);
       fence_proxy_async();
       mbar_arrive(smem_u32(strip_full));
     }
@@ -471,7 +497,8 @@ long long* g_conv_timeline = nullptr;
 template <bool DGRAD>
 int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, int B, int H, int W, int KC, int NC,
                 int relu, cudaStream_t st, const PoolGradSrc* pg = nullptr, float* dbias = nullptr,
-                float* dconv_out = nullptr, float* pool_out = nullptr, uint8_t* arg_out = nullptr) {
+                float* dconv_out = nullptr, float* pool_out = nullptr, uint8_t* arg_out = nullptr,
+                const void* x_bf16 = nullptr, void* dconv_out_bf16 = nullptr) {
   B200_REQUIRE(B > 0 && H > 0 && W > 0, "conv5x5_tc: bad shape");
   B200_REQUIRE(KC % 16 == 0 && NC % 64 == 0, "conv5x5_tc: channels must be multiples of 16 (in) / 64 (out), got %d/%d",
                KC, NC);
@@ -503,7 +530,7 @@ int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, 
     default: B200_REQUIRE(false, "conv5x5_tc: contraction channels must be 32, 64, 128 or 256 (got %d)", KC);
   }
   B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-  ConvArgs a{x, wp, DGRAD ? NC : KC, DGRAD ? KC : NC, bias, y, relu, g, g_conv_timeline, pg ? *pg : PoolGradSrc{}, dbias, dconv_out, pool_out, arg_out};
+  ConvArgs a{x, reinterpret_cast<const __nv_bfloat16*>(x_bf16), reinterpret_cast<__nv_bfloat16*>(dconv_out_bf16), wp, DGRAD ? NC : KC, DGRAD ? KC : NC, bias, y, relu, g, g_conv_timeline, pg ? *pg : PoolGradSrc{}, dbias, dconv_out, pool_out, arg_out};
   dim3 grid(cdiv(B, ipc), NC / 64);
   B200_CUDA_TRY(launch_kernel(kern, grid, dim3(288), (size_t)smem, st, a));
   return B200_OK;
@@ -518,6 +545,8 @@ int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, 
 struct WgradArgs {
   const float* x;      // [B,H,W,64]
   const float* dy;     // [B,H,W,64]
+  const __nv_bfloat16* xb;    // bf16 copies of x / dy (both or none): read instead, half the bytes of the 5x re-read
+  const __nv_bfloat16* dyb;
   float* partial;      // [S][25][64][64]
   ConvGeom g;          // ipc = 1
   int imgs_per_cta;
@@ -559,6 +588,34 @@ __device__ __forceinline__ void fill_strip_pair(uint8_t* xs, uint8_t* ds, const 
         const float fd[8] = {vd[u][0].x, vd[u][0].y, vd[u][0].z, vd[u][0].w, vd[u][1].x, vd[u][1].y, vd[u][1].z, vd[u][1].w};
         *reinterpret_cast<uint4*>(xs + off) = pack8(fx);
         *reinterpret_cast<uint4*>(ds + off) = pack8(fd);
+      }
+    }
+  }
+}
+
+__device__ __forceinline__ void fill_strip_pair_bf16(uint8_t* xs, uint8_t* ds, const __nv_bfloat16* __restrict__ x,
+                                                     const __nv_bfloat16* __restrict__ dy, const ConvGeom& g, int n,
+                                                     int tid) {
+  constexpr int U = 5;
+  const int per_img = g.H * g.W * 8;
+  const uint4* sx = reinterpret_cast<const uint4*>(x + (int64_t)n * per_img * 8);
+  const uint4* sd = reinterpret_cast<const uint4*>(dy + (int64_t)n * per_img * 8);
+  for (int q0 = tid; q0 < per_img; q0 += WG_LOADERS * U) {
+    uint4 vx[U], vd[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int q = min(q0 + u * WG_LOADERS, per_img - 1);      // clamped, not predicated: no branch between the loads
+      vx[u] = __ldg(sx + q); vd[u] = __ldg(sd + q);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int q = q0 + u * WG_LOADERS;
+      if (q < per_img) {
+        const int c = q & 7, pix = q >> 3;
+        const int i = pix / g.W, j = pix - i * g.W;
+        const int off = c * g.ch_stride + (g.lead + i * g.P + j) * 16;
+        *reinterpret_cast<uint4*>(xs + off) = vx[u];
+        *reinterpret_cast<uint4*>(ds + off) = vd[u];
       }
     }
   }
@@ -621,7 +678,8 @@ __global__ void __launch_bounds__(416, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
           loaders_sync();                     // nobody restages dpm while a slower loader still gathers from it
         }
       } else {
-        fill_strip_pair(xs, ds, a.x, a.dy, g, img_beg + it, tid);
+        if (a.xb) fill_strip_pair_bf16(xs, ds, a.xb, a.dyb, g, img_beg + it, tid);
+        else fill_strip_pair(xs, ds, a.x, a.dy, g, img_beg + it, tid);
       }
       fence_proxy_async();
       mbar_arrive(smem_u32(full + b));
@@ -742,8 +800,8 @@ int conv5x5_fwd_tc(const float* x, const void* wp, const float* bias, float* y, 
 }
 // conv + bias + ReLU + 3x3/2 SAME max-pool in one kernel; y (the un-pooled activations) is optional
 int conv5x5_pool_fwd_tc(const float* x, const void* wp, const float* bias, float* y, float* pool, uint8_t* arg, int B,
-                        int H, int W, int Cin, int Cout, cudaStream_t st) {
-  return launch_conv<false>(x, (const uint8_t*)wp, bias, y, B, H, W, Cin, Cout, 1, st, nullptr, nullptr, nullptr, pool, arg);
+                        int H, int W, int Cin, int Cout, cudaStream_t st, const void* x_bf16) {
+  return launch_conv<false>(x, (const uint8_t*)wp, bias, y, B, H, W, Cin, Cout, 1, st, nullptr, nullptr, nullptr, pool, arg, x_bf16);
 }
 // dx = Conv2DBackpropInput(dy, w): contraction over the forward Cout, output the forward Cin
 int conv5x5_dgrad_tc(const float* dy, const void* wp, float* dx, int B, int H, int W, int Cin, int Cout,
@@ -759,17 +817,21 @@ static PoolGradSrc make_pool_src(const float* dpool, const float* pool, const ui
 // dx = Conv2DBackpropInput(dconv, w) with dconv = MaxPoolGrad(dpool, arg) * [pool > 0] gathered on the fly;
 // dbias (optional, zero on entry) += sum of dconv over (B,H,W)
 int conv5x5_dgrad_pool_tc(const float* dpool, const float* pool, const uint8_t* arg, const void* wp, float* dx,
-                          float* dbias, float* dconv_out, int B, int H, int W, int Cin, int Cout, cudaStream_t st) {
+                          float* dbias, float* dconv_out, int B, int H, int W, int Cin, int Cout, cudaStream_t st,
+                          void* dconv_out_bf16) {
   B200_REQUIRE(Cin % 64 == 0 && Cout == 64, "conv5x5_dgrad_pool_tc: needs Cout == 64 (got %d -> %d)", Cin, Cout);
   PoolGradSrc p = make_pool_src(dpool, pool, arg, H, W);
-  return launch_conv<true>(nullptr, (const uint8_t*)wp, nullptr, dx, B, H, W, Cout, Cin, 0, st, &p, dbias, dconv_out);
+  return launch_conv<true>(nullptr, (const uint8_t*)wp, nullptr, dx, B, H, W, Cout, Cin, 0, st, &p, dbias, dconv_out, nullptr,
+                           nullptr, nullptr, dconv_out_bf16);
 }
 int64_t conv5x5_wgrad_tc_scratch_bytes(int B) { return (int64_t)wgrad_splits_tc(B) * 25 * 64 * 64 * 4; }
 static int launch_wgrad(const float* x, const float* dy, const PoolGradSrc* pg, float* dw, float* scratch, int B, int H,
-                        int W, int Cin, int Cout, cudaStream_t st);
+                        int W, int Cin, int Cout, cudaStream_t st, const void* x_bf16 = nullptr,
+                        const void* dy_bf16 = nullptr);
 int conv5x5_wgrad_tc(const float* x, const float* dy, float* dw, float* scratch, int B, int H, int W, int Cin,
-                     int Cout, cudaStream_t st) {
-  return launch_wgrad(x, dy, nullptr, dw, scratch, B, H, W, Cin, Cout, st);
+                     int Cout, cudaStream_t st, const void* x_bf16, const void* dy_bf16) {
+  B200_REQUIRE((x_bf16 == nullptr) == (dy_bf16 == nullptr), "conv5x5_wgrad_tc: give both bf16 copies or none");
+  return launch_wgrad(x, dy, nullptr, dw, scratch, B, H, W, Cin, Cout, st, x_bf16, dy_bf16);
 }
 // filter gradient with dY = MaxPoolGrad(dpool, arg) * [pool > 0] gathered on the fly
 int conv5x5_wgrad_pool_tc(const float* x, const float* dpool, const float* pool, const uint8_t* arg, float* dw,
@@ -778,7 +840,7 @@ int conv5x5_wgrad_pool_tc(const float* x, const float* dpool, const float* pool,
   return launch_wgrad(x, nullptr, &p, dw, scratch, B, H, W, Cin, Cout, st);
 }
 static int launch_wgrad(const float* x, const float* dy, const PoolGradSrc* pg, float* dw, float* scratch, int B, int H,
-                        int W, int Cin, int Cout, cudaStream_t st) {
+                        int W, int Cin, int Cout, cudaStream_t st, const void* x_bf16, const void* dy_bf16) {
   B200_REQUIRE(Cin == 64 && Cout == 64, "conv5x5_wgrad_tc: only 64 -> 64 channels (got %d -> %d)", Cin, Cout);
   B200_REQUIRE(B > 0 && H > 0 && W > 0, "conv5x5_wgrad_tc: bad shape");
   ConvGeom g = make_geom(B, H, W, 64, 64, 1);
@@ -796,7 +858,7 @@ static int launch_wgrad(const float* x, const float* dy, const PoolGradSrc* pg, 
   int S = wgrad_splits_tc(B);
   int per = cdiv(B, S);
   S = cdiv(B, per);
-  WgradArgs a{x, dy, scratch, g, per, nbuf, pg ? *pg : PoolGradSrc{}, g_conv_timeline};
+  WgradArgs a{x, dy, reinterpret_cast<const __nv_bfloat16*>(x_bf16), reinterpret_cast<const __nv_bfloat16*>(dy_bf16), scratch, g, per, nbuf, pg ? *pg : PoolGradSrc{}, g_conv_timeline};
   const bool overlap = g_pdl_next;           // the step driver asked for overlapped launches: only the reduction is
   g_pdl_next = false;                        // programmatic (the kernel in front of this one is on another stream)
   B200_CUDA_TRY(launch_kernel(conv5x5_wgrad_tc_kernel, dim3(5, S), dim3(416), (size_t)smem, st, a));

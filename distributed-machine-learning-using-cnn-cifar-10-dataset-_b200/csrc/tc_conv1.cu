@@ -58,6 +58,7 @@ struct Conv1FwdArgs {
   const float* bias;    // [64]
   float* pool;          // [B,OH,OW,64]
   uint8_t* arg;         // [B,OH,OW,64]
+  __nv_bfloat16* pool_bf16;   // [B,OH,OW,64] or null: pool rounded to bf16 for the consumers that stage it as an MMA operand
   float* conv_dbg;      // [B,H,W,64] or null (tests: lets the pool fusion be checked on its own input)
   C1Geom g;
   long long* timeline;  // diagnostics: clock64 stamps of CTA 0 in slots 14, 15, 30, 31 of the timeline buffer, or null
@@ -251,6 +252,7 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
       const size_t o = ((size_t)n * g.OH * g.OW + cell) * 64 + c8 * 8;
       *reinterpret_cast<float4*>(a.pool + o) = make_float4(best[0], best[1], best[2], best[3]);
       *reinterpret_cast<float4*>(a.pool + o + 4) = make_float4(best[4], best[5], best[6], best[7]);
+      if (a.pool_bf16) *reinterpret_cast<uint4*>(a.pool_bf16 + o) = pack8(best);
       *reinterpret_cast<uint2*>(a.arg + o) = make_uint2(bi[0] | (bi[1] << 8) | (bi[2] << 16) | (bi[3] << 24),
                                                         bi[4] | (bi[5] << 8) | (bi[6] << 16) | (bi[7] << 24));
     }
@@ -271,7 +273,7 @@ bool conv1_tc_supported(int H, int W, int c_in, int c1) {
 }
 
 int conv1_pool_fwd_tc(const uint8_t* img, const float* w, const float* bias, float* pool, uint8_t* arg,
-                      float* conv_dbg, int B, int ih, int iw, int H, int W, cudaStream_t st) {
+                      float* conv_dbg, int B, int ih, int iw, int H, int W, cudaStream_t st, void* pool_bf16) {
   B200_REQUIRE(B > 0 && H <= ih && W <= iw && H >= 4 && W >= 4, "conv1_pool_fwd_tc: bad shape");
   B200_REQUIRE(conv1_tc_supported(H, W, 3, 64), "conv1_pool_fwd_tc: crop %dx%d does not fit one CTA", H, W);
   C1Geom g = make_c1geom(B, ih, iw, H, W);
@@ -281,7 +283,7 @@ int conv1_pool_fwd_tc(const uint8_t* img, const float* w, const float* bias, flo
     B200_CUDA_TRY(cudaFuncSetAttribute(conv1_pool_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr = true;
   }
-  Conv1FwdArgs a{img, w, bias, pool, arg, conv_dbg, g, g_conv1_timeline};
+  Conv1FwdArgs a{img, w, bias, pool, arg, reinterpret_cast<__nv_bfloat16*>(pool_bf16), conv_dbg, g, g_conv1_timeline};
   conv1_pool_fwd_kernel<<<B, 352, smem, st>>>(a);
   B200_LAUNCH_CHECK();
   return B200_OK;
@@ -295,7 +297,7 @@ int conv1_pool_fwd_tc(const uint8_t* img, const float* w, const float* bias, flo
 namespace b200 {
 namespace {
 
-constexpr int C1W_BR = 12;     // image rows per band of the dY strip
+constexpr int C1W_BR = 8;      // image rows per band of the dY strip
 constexpr int C1W_MAXB = 8;    // bands per image the barrier array allows (crops up to 96 rows)
 
 struct Conv1WgradArgs {
@@ -320,11 +322,13 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
   uint8_t* ds = xs + xs_bytes;
   float* dpm = reinterpret_cast<float*>(ds + ((8 * ch_stride + 127) & ~127));
   uint8_t* argb = reinterpret_cast<uint8_t*>(dpm + (size_t)ncell * 64);
-  uint8_t* ctrl = argb + (((size_t)ncell * 64 + 127) & ~127);
+  float* plr = reinterpret_cast<float*>(argb + (((size_t)ncell * 64 + 127) & ~127));      // pool1 of the image as fetched
+  uint8_t* ctrl = reinterpret_cast<uint8_t*>(plr + (size_t)ncell * 64);
   uint64_t* full = reinterpret_cast<uint64_t*>(ctrl);       // one per row band
   uint64_t* empty = full + C1W_MAXB;
   uint64_t* accum = empty + 1;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum + 1);
+  uint64_t* staged = accum + 1;                             // bulk copies of dpool / pool / arg have landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(staged + 1);
   const int nband = (g.H + C1W_BR - 1) / C1W_BR;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -335,6 +339,7 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
     for (int b = 0; b < C1W_MAXB; ++b) mbar_init(smem_u32(full + b), WORKERS);
     mbar_init(smem_u32(empty), 5);
     mbar_init(smem_u32(accum), 5);
+    mbar_init(smem_u32(staged), 1);
     fence_mbar_init();
   }
   if (warp == 8) tmem_alloc(smem_u32(tmem_slot), 512);
@@ -353,6 +358,21 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
     for (int it = 0; it < nimg; ++it) {
       const int n = blockIdx.x + it * gridDim.x;
       mbar_wait(smem_u32(empty), (it & 1) ^ 1);          // MMAs of the previous image are done with the strips
+      pdl_wait();
+      pdl_launch_dependents();
+      // pooled gradient, pool1 and argmax of this image: three contiguous blocks, fetched with bulk copies (TMA)
+      // while the x strip is built -- as register loads this staging cost 5-8k cycles of round trips
+      if (tid == 0) {
+        const uint32_t nb4 = (uint32_t)ncell * 64 * 4, nb1 = (uint32_t)ncell * 64, bar = smem_u32(staged);
+        const uint8_t* gd = reinterpret_cast<const uint8_t*>(a.dpool + (size_t)n * ncell * 64);
+        const uint8_t* gp = reinterpret_cast<const uint8_t*>(a.pool + (size_t)n * ncell * 64);
+        mbar_arrive_expect_tx(bar, 2 * nb4 + nb1);
+        for (uint32_t off = 0; off < nb4; off += 16384) {
+          bulk_g2s(smem_u32(dpm) + off, gd + off, min(16384u, nb4 - off), bar);
+          bulk_g2s(smem_u32(plr) + off, gp + off, min(16384u, nb4 - off), bar);
+        }
+        bulk_g2s(smem_u32(argb), a.arg + (size_t)n * ncell * 64, nb1, bar);
+      }
       // x strip: channels 0..2 = pixel bytes (0 in the pads), channel 3 = 1 in EVERY slot
       const uint8_t* rec = a.img + (size_t)n * 3 * g.ih * g.iw;
       for (int s = tid; s < g.npix; s += WORKERS) {
@@ -363,19 +383,27 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
         else { float f[8] = {0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 0.f}; v = pack8(f); }
         *reinterpret_cast<uint4*>(xs + s * 16) = v;
       }
-      pdl_wait();     // the records above do not depend on the producer of dpool (conv2's dgrad); from here on we do
-      pdl_launch_dependents();
-      // masked pool gradient and argmax of this image -> shared memory (coalesced)
-      const float4* dp4 = reinterpret_cast<const float4*>(a.dpool + (size_t)n * ncell * 64);
-      const float4* pl4 = reinterpret_cast<const float4*>(a.pool + (size_t)n * ncell * 64);
-      const uint32_t* ar4 = reinterpret_cast<const uint32_t*>(a.arg + (size_t)n * ncell * 64);
-#pragma unroll 5
-      for (int q = tid; q < ncell * 16; q += WORKERS) {
-        float4 d = __ldg(dp4 + q), p = __ldg(pl4 + q);
-        d.x = p.x > 0.f ? d.x : 0.f; d.y = p.y > 0.f ? d.y : 0.f;
-        d.z = p.z > 0.f ? d.z : 0.f; d.w = p.w > 0.f ? d.w : 0.f;
-        reinterpret_cast<float4*>(dpm)[(q & ~15) + (q & 1) * 8 + ((q & 15) >> 1)] = d;      // layout of pool_grad_px
-        reinterpret_cast<uint32_t*>(argb)[q] = __ldg(ar4 + q);
+      mbar_wait(smem_u32(staged), it & 1);
+      // ReluGrad mask (the selected cell is > 0 iff pool1 > 0) and the [half][chunk] order pool_grad_px reads, in
+      // place: a batch is read into registers, then written (the permutation stays inside a cell's 16 float4)
+      constexpr int MB = 9;
+      for (int q0 = tid; q0 < ncell * 16; q0 += MB * WORKERS) {
+        float4 dreg[MB];
+#pragma unroll
+        for (int k = 0; k < MB; ++k) {
+          const int q = min(q0 + k * WORKERS, ncell * 16 - 1);
+          float4 d = reinterpret_cast<const float4*>(dpm)[q];
+          const float4 pv = reinterpret_cast<const float4*>(plr)[q];
+          d.x = pv.x > 0.f ? d.x : 0.f; d.y = pv.y > 0.f ? d.y : 0.f;
+          d.z = pv.z > 0.f ? d.z : 0.f; d.w = pv.w > 0.f ? d.w : 0.f;
+          dreg[k] = d;
+        }
+        workers_sync();
+#pragma unroll
+        for (int k = 0; k < MB; ++k) {
+          const int q = q0 + k * WORKERS;
+          if (q < ncell * 16) reinterpret_cast<float4*>(dpm)[(q & ~15) + (q & 1) * 8 + ((q & 15) >> 1)] = dreg[k];
+        }
       }
       workers_sync();
       if (stamp) a.timeline[26] = clock64();
@@ -459,7 +487,7 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
 int conv1_wgrad_ctas(int B) { return std::min(B, kNumSMs); }
 size_t conv1_wgrad_smem(const C1Geom& g) {
   size_t xs = (g.npix * 16 + 127) & ~127, ch = g.npix * 16 + 16;
-  return xs + ((8 * ch + 127) & ~127) + (size_t)g.OH * g.OW * 64 * 4 + (((size_t)g.OH * g.OW * 64 + 127) & ~127) +
+  return xs + ((8 * ch + 127) & ~127) + 2 * (size_t)g.OH * g.OW * 64 * 4 + (((size_t)g.OH * g.OW * 64 + 127) & ~127) +
          256;
 }
 }  // namespace
