@@ -251,8 +251,11 @@ def main():
         if world == 1:
             eng.train_step(s_img, s_lab, lr)
         else:
-            eng.forward_backward(s_img, s_lab)
-            exchange_and_update()
+            if fused:
+                ex.train_step_(eng, s_img, s_lab, lr)      # exchange split in two and overlapped with the backward
+            else:
+                eng.forward_backward(s_img, s_lab)
+                exchange_and_update()
 
     def exchange_and_update():
         if fused:
@@ -268,8 +271,11 @@ def main():
             else:
                 s_img.copy_(img, non_blocking=True)
                 s_lab.copy_(lab, non_blocking=True)
-                eng.forward_backward(s_img, s_lab)
-                exchange_and_update()
+                if fused:
+                    ex.train_step_(eng, s_img, s_lab, lr)
+                else:
+                    eng.forward_backward(s_img, s_lab)
+                    exchange_and_update()
                 out.copy_(eng.loss(), non_blocking=True)
         return fn
 

@@ -46,7 +46,7 @@ struct b200_model {
   // side streams / events for the independent branches of the backward pass (created at the first
   // bf16 backward, which must therefore run once eagerly before any stream capture)
   cudaStream_t side[2] = {nullptr, nullptr};
-  cudaEvent_t ev_fork[2] = {nullptr, nullptr}, ev_join[2] = {nullptr, nullptr};
+  cudaEvent_t ev_fork[2] = {nullptr, nullptr}, ev_join[2] = {nullptr, nullptr}, ev_aux[2] = {nullptr, nullptr};
   const uint8_t* last_images = nullptr;   // records of the last forward (the fused conv1 gradient re-reads them)
   // per-launch-site timing (b200_profile_step): events are created lazily, once
   bool profiling = false;
@@ -148,6 +148,7 @@ int b200_destroy(b200_handle h) {
     for (int i = 0; i < 2; ++i) {
       if (h->ev_fork[i]) cudaEventDestroy(h->ev_fork[i]);
       if (h->ev_join[i]) cudaEventDestroy(h->ev_join[i]);
+      if (h->ev_aux[i]) cudaEventDestroy(h->ev_aux[i]);
       if (h->side[i]) cudaStreamDestroy(h->side[i]);
     }
   }
@@ -207,6 +208,7 @@ static int ensure_side_streams(b200_model* h) {
     B200_CUDA_TRY(cudaStreamCreateWithPriority(&h->side[i], cudaStreamNonBlocking, i == 0 ? prio_hi : prio_lo));
     B200_CUDA_TRY(cudaEventCreateWithFlags(&h->ev_fork[i], cudaEventDisableTiming));
     B200_CUDA_TRY(cudaEventCreateWithFlags(&h->ev_join[i], cudaEventDisableTiming));
+    B200_CUDA_TRY(cudaEventCreateWithFlags(&h->ev_aux[i], cudaEventDisableTiming));
   }
   return B200_OK;
 }
@@ -331,7 +333,15 @@ int b200_forward_backward(b200_handle h, const uint8_t* images, const int32_t* l
   return b200_backward(h, stream);
 }
 
-int b200_backward(b200_handle h, void* stream) {
+// the peer tables of b200_p2p_sgd_apply, for the variant of the backward pass that overlaps the exchange
+struct P2PCtx {
+  const void* const* peer_grads; void* const* peer_params; void* const* peer_pads;
+  const void* mc_grads; void* mc_params; uint32_t* state;
+  int rank, world;
+  float lr, scale;
+};
+
+static int backward_impl(b200_handle h, void* stream, const P2PCtx* px) {
   B200_READY(h);
   if (!h->forward_done) {
     set_error("backward: call b200_forward first");
@@ -364,6 +374,20 @@ int b200_backward(b200_handle h, void* stream) {
       SITE("full1_dw", fc_dw_tc(h->ptr<float>("pool2"), dfull1, h->G(P_FW1), c.batch, h->flat, c.f1, st));
     }
     PSITE("full1_dx", fc_dx_tc(h->ptr<float>("pool2"), h->P(P_FW1), dfull1, dpool2, c.batch, h->flat, c.f1, 0, st));
+    if (px && fork) {
+      // Channel 0 of the exchange: the FC gradients (everything from full_weight_1 on, 90 % of the buffer) are
+      // complete once FC1's dW (stream 0) and the tail-gradient kernel (stream 1) are; their all-reduce + update
+      // runs on stream 0 beside conv2's dgrad and the conv filter gradients, capped at 16 CTAs so that it lives on
+      // the SMs those 128-CTA kernels leave free.  It may not start before FC1's dX has read W1 (peers write the
+      // updated W1 into this GPU's buffer).
+      B200_CUDA_TRY(cudaEventRecord(h->ev_aux[0], st));
+      B200_CUDA_TRY(cudaEventRecord(h->ev_aux[1], h->side[1]));
+      B200_CUDA_TRY(cudaStreamWaitEvent(s0, h->ev_aux[0], 0));
+      B200_CUDA_TRY(cudaStreamWaitEvent(s0, h->ev_aux[1], 0));
+      const int64_t off = h->p_off[P_FW1];
+      TRY(p2p_allreduce_sgd(px->peer_grads, px->peer_params, px->peer_pads, px->mc_grads, px->mc_params, px->state,
+                            px->rank, px->world, h->p_total - off, px->lr, px->scale, s0, off, 0, 16));
+    }
     // pool2's backward is not a kernel of its own: conv2's dgrad gathers MaxPoolGrad * ReluGrad from (dpool2,
     // pool2, arg2) while it builds its strip, adds the bias gradient (atomics into the buffer the tail kernel
     // cleared) and leaves dconv2 behind for the filter gradient, which then overlaps conv1's gradient.
@@ -400,8 +424,18 @@ int b200_backward(b200_handle h, void* stream) {
         B200_CUDA_TRY(cudaStreamWaitEvent(st, h->ev_join[i], 0));
       }
     }
+    if (px) {      // channel 1: the conv gradients (10 % of the buffer); both channels here when nothing was forked
+      const int64_t off = h->p_off[P_FW1];
+      if (!fork)
+        TRY(p2p_allreduce_sgd(px->peer_grads, px->peer_params, px->peer_pads, px->mc_grads, px->mc_params, px->state,
+                              px->rank, px->world, h->p_total - off, px->lr, px->scale, st, off, 0, 0));
+      SITE("p2p_conv_update", p2p_allreduce_sgd(px->peer_grads, px->peer_params, px->peer_pads, px->mc_grads,
+                                                px->mc_params, px->state, px->rank, px->world, off, px->lr, px->scale,
+                                                st, 0, 1, 0));
+    }
     return B200_OK;
   }
+  B200_REQUIRE(!px, "the overlapped exchange needs the bf16 mode");
   SITE("full3_bwd", fc_bwd_f32(h->ptr<float>("full2"), h->P(P_FW3), dlogits, dfull2, h->G(P_FW3), h->G(P_FB3),
                                scratch, c.batch, c.f2, c.n_cls, 1, st));
   SITE("full2_bwd", fc_bwd_f32(h->ptr<float>("full1"), h->P(P_FW2), dfull2, dfull1, h->G(P_FW2), h->G(P_FB2), scratch,
@@ -420,6 +454,23 @@ int b200_backward(b200_handle h, void* stream) {
   SITE("conv1_wgrad", conv5x5_wgrad_f32(h->ptr<float>("x"), dconv1, h->G(P_W1), h->G(P_B1), scratch, c.batch,
                                         c.crop_h, c.crop_w, c.c_in, c.c1, st));
   return B200_OK;
+}
+
+int b200_backward(b200_handle h, void* stream) { return backward_impl(h, stream, nullptr); }
+
+int b200_train_step_p2p(b200_handle h, const uint8_t* images, const int32_t* labels, const void* const* peer_grads,
+                        void* const* peer_params, void* const* peer_pads, const void* mc_grads, void* mc_params,
+                        uint32_t* state, int32_t rank, int32_t world, float lr, float grad_scale, void* stream) {
+  B200_READY(h);
+  B200_REQUIRE(peer_grads && peer_params && peer_pads && state && rank >= 0 && rank < world && world <= 8,
+               "train_step_p2p: bad argument");
+  B200_REQUIRE(peer_grads[rank] == h->grads && peer_params[rank] == h->params,
+               "train_step_p2p: entry `rank` of the peer tables must be the buffers bound to this handle");
+  B200_REQUIRE(h->p_off[P_FW1] % (4 * world) == 0 && (h->p_total - h->p_off[P_FW1]) % (4 * world) == 0,
+               "train_step_p2p: the parameter ranges do not split into 16-byte shards for %d workers", world);
+  TRY(forward_impl(h, images, labels, stream, true));
+  const P2PCtx px{peer_grads, peer_params, peer_pads, mc_grads, mc_params, state, rank, world, lr, grad_scale};
+  return backward_impl(h, stream, &px);
 }
 
 int b200_sgd_apply(b200_handle h, float lr, float grad_scale, void* stream) {

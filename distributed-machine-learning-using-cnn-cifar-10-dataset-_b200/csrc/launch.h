@@ -81,7 +81,8 @@ int fc_tail_prepare_w2(const float* w2, void* scratch, int B, int F1, int F2, in
 // allreduce + SGD in one kernel over NVLink peer memory (p2p_update.cu)
 int p2p_allreduce_sgd(const void* const* peer_grads, void* const* peer_params, void* const* peer_pads,
                       const void* mc_grads, void* mc_params, uint32_t* state, int rank, int world, int64_t total,
-                      float lr, float scale, cudaStream_t st);
+                      float lr, float scale, cudaStream_t st,
+                      int64_t offset = 0, int channel = 0, int max_ctas = 0);
 bool conv1_tc_supported(int H, int W, int c_in, int c1);
 int conv1_pool_fwd_tc(const uint8_t* img, const float* w, const float* bias, float* pool, uint8_t* arg,
                       float* conv_dbg, int B, int ih, int iw, int H, int W, cudaStream_t st,

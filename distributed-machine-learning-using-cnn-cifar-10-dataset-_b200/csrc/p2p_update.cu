@@ -26,7 +26,7 @@ constexpr int kMaxRanks = 8;
 struct P2PArgs {
   const float* grads[kMaxRanks];    // every rank's flat gradient buffer (index = rank)
   float* params[kMaxRanks];         // every rank's flat parameter buffer
-  uint32_t* pads[kMaxRanks];        // every rank's flag pad: [0,8) "ready" slots, [8,16) "done" slots
+  uint32_t* pads[kMaxRanks];        // every rank's flag pad (of this channel): [0,8) "ready" slots, [8,16) "done" slots
   const float* mc_grads;            // multicast mapping of the gradient buffers, or null
   float* mc_params;                 // multicast mapping of the parameter buffers, or null
   uint32_t* state;                  // local: [0] epoch, [1] CTA arrival counter
@@ -81,12 +81,36 @@ __global__ void __launch_bounds__(512) p2p_allreduce_sgd_kernel(P2PArgs a) {
   const int64_t shard4 = a.total / 4 / a.world;
   const int64_t beg4 = (int64_t)a.rank * shard4;
   const bool nvls = a.mc_grads != nullptr && a.mc_params != nullptr;
+  if (nvls) {
+    // four switch reductions per thread in flight (a round trip through the switch is ~2-3 us; with few CTAs --
+    // the channel that overlaps the backward pass is capped at 16 -- latency, not bandwidth, is the limit)
+    constexpr int U = 4;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i0 = blockIdx.x * (int64_t)blockDim.x + tid; i0 < shard4; i0 += U * stride) {
+      float4 g[U], w[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int64_t i = i0 + u * stride;
+        if (i < shard4) {
+          g[u] = mc_ld_reduce(a.mc_grads + (beg4 + i) * 4);
+          w[u] = *reinterpret_cast<const float4*>(a.params[a.rank] + (beg4 + i) * 4);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int64_t i = i0 + u * stride;
+        if (i < shard4) {
+          w[u].x = fmaf(-a.step, g[u].x, w[u].x); w[u].y = fmaf(-a.step, g[u].y, w[u].y);
+          w[u].z = fmaf(-a.step, g[u].z, w[u].z); w[u].w = fmaf(-a.step, g[u].w, w[u].w);
+          mc_st(a.mc_params + (beg4 + i) * 4, w[u]);
+        }
+      }
+    }
+  } else
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + tid; i < shard4; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t o = (beg4 + i) * 4;
     float4 g;
-    if (nvls) {
-      g = mc_ld_reduce(a.mc_grads + o);
-    } else {
+    {
       float4 v[kMaxRanks];
 #pragma unroll
       for (int p = 0; p < kMaxRanks; ++p)
@@ -99,13 +123,9 @@ __global__ void __launch_bounds__(512) p2p_allreduce_sgd_kernel(P2PArgs a) {
     float4 w = *reinterpret_cast<const float4*>(a.params[a.rank] + o);
     w.x = fmaf(-a.step, g.x, w.x); w.y = fmaf(-a.step, g.y, w.y);
     w.z = fmaf(-a.step, g.z, w.z); w.w = fmaf(-a.step, g.w, w.w);
-    if (nvls) {
-      mc_st(a.mc_params + o, w);
-    } else {
 #pragma unroll
-      for (int p = 0; p < kMaxRanks; ++p)
-        if (p < a.world) *reinterpret_cast<float4*>(a.params[p] + o) = w;
-    }
+    for (int p = 0; p < kMaxRanks; ++p)
+      if (p < a.world) *reinterpret_cast<float4*>(a.params[p] + o) = w;
   }
   // ---- B: everybody done ------------------------------------------------------------------------------------
   __threadfence_system();
@@ -127,7 +147,7 @@ __global__ void __launch_bounds__(512) p2p_allreduce_sgd_kernel(P2PArgs a) {
 
 int p2p_allreduce_sgd(const void* const* peer_grads, void* const* peer_params, void* const* peer_pads,
                       const void* mc_grads, void* mc_params, uint32_t* state, int rank, int world, int64_t total,
-                      float lr, float scale, cudaStream_t st) {
+                      float lr, float scale, cudaStream_t st, int64_t offset, int channel, int max_ctas) {
   B200_REQUIRE(world >= 1 && world <= kMaxRanks && rank >= 0 && rank < world, "p2p_allreduce_sgd: bad rank %d / world %d",
                rank, world);
   B200_REQUIRE(total > 0 && total % (4 * world) == 0, "p2p_allreduce_sgd: %lld floats do not split into %d 16-byte shards",
@@ -136,14 +156,18 @@ int p2p_allreduce_sgd(const void* const* peer_grads, void* const* peer_params, v
   P2PArgs a{};
   for (int p = 0; p < world; ++p) {
     B200_REQUIRE(peer_grads[p] && peer_params[p] && peer_pads[p], "p2p_allreduce_sgd: null peer pointer for rank %d", p);
-    a.grads[p] = (const float*)peer_grads[p];
-    a.params[p] = (float*)peer_params[p];
-    a.pads[p] = (uint32_t*)peer_pads[p];
+    a.grads[p] = (const float*)peer_grads[p] + offset;
+    a.params[p] = (float*)peer_params[p] + offset;
+    a.pads[p] = (uint32_t*)peer_pads[p] + 16 * channel;
   }
-  a.mc_grads = (const float*)mc_grads; a.mc_params = (float*)mc_params;
-  a.state = state; a.rank = rank; a.world = world; a.total = total; a.step = lr * scale;
+  B200_REQUIRE(offset >= 0 && offset % 4 == 0 && channel >= 0 && channel < 2, "p2p_allreduce_sgd: bad sub-range / channel");
+  a.mc_grads = mc_grads ? (const float*)mc_grads + offset : nullptr;
+  a.mc_params = mc_params ? (float*)mc_params + offset : nullptr;
+  a.state = state + 2 * channel; a.rank = rank; a.world = world; a.total = total; a.step = lr * scale;
   const int64_t shard4 = total / 4 / world;
-  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(kNumSMs, (shard4 + 511) / 512));
+  // (with the multicast mapping a thread handles four 16-byte pieces per sweep)
+  const int64_t per_cta = 512 * ((mc_grads && mc_params) ? 4 : 1);
+  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(max_ctas > 0 ? max_ctas : kNumSMs, (shard4 + per_cta - 1) / per_cta));
   p2p_allreduce_sgd_kernel<<<grid, 512, 0, st>>>(a);
   B200_LAUNCH_CHECK();
   return B200_OK;

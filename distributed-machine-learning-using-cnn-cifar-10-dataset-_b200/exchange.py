@@ -92,14 +92,14 @@ class P2PExchange(GradientExchange):
         self._peer_params = arr(*[int(x) for x in self._hp.buffer_ptrs])
         # flags: a private corner of the gradient handle's signal pads (torch's own barrier uses the start)
         off = 2048
-        if self._hg.signal_pad_size < off + 64:
+        if self._hg.signal_pad_size < off + 128:
             raise RuntimeError("signal pad too small")
         self._peer_pads = arr(*[int(x) + off for x in self._hg.signal_pad_ptrs])
         mc_ok = use_multicast and self._hg.has_multicast_support and self._hp.has_multicast_support
         self.multicast = bool(mc_ok and self._hg.multicast_ptr and self._hp.multicast_ptr)
         self._mc_grads = int(self._hg.multicast_ptr) if self.multicast else None
         self._mc_params = int(self._hp.multicast_ptr) if self.multicast else None
-        self._state = torch.zeros(2, dtype=torch.int32, device=device)
+        self._state = torch.zeros(4, dtype=torch.int32, device=device)      # (epoch, arrivals) per flag channel
         torch.cuda.synchronize(device)
         dist.barrier(group=group)
 
@@ -109,3 +109,13 @@ class P2PExchange(GradientExchange):
         check(engine.lib.b200_p2p_sgd_apply(engine.h, self._peer_grads, self._peer_params, self._peer_pads,
                                             self._mc_grads, self._mc_params, self._state.data_ptr(), self.rank,
                                             self.world, lr, self.grad_scale, torch.cuda.current_stream().cuda_stream))
+
+    def train_step_(self, engine, images, labels, lr):
+        """forward + backward + exchange + update with the exchange overlapped with the conv layers' backward
+        kernels (b200_train_step_p2p); same result as engine.forward_backward(...) followed by apply_(engine, lr)."""
+        from ._lib import check
+        engine._check_inputs(images, labels)
+        check(engine.lib.b200_train_step_p2p(engine.h, images.data_ptr(), labels.data_ptr(), self._peer_grads,
+                                             self._peer_params, self._peer_pads, self._mc_grads, self._mc_params,
+                                             self._state.data_ptr(), self.rank, self.world, lr, self.grad_scale,
+                                             torch.cuda.current_stream().cuda_stream))

@@ -101,6 +101,14 @@ int b200_sgd_apply(b200_handle h, float lr, float grad_scale, void* stream);
 int b200_p2p_sgd_apply(b200_handle h, const void* const* peer_grads, void* const* peer_params, void* const* peer_pads,
                        const void* mc_grads, void* mc_params, uint32_t* state, int32_t rank, int32_t world, float lr,
                        float grad_scale, void* stream);
+/* One `mon_sess.run([train_op, loss])` (:230) of one worker for world > 1: forward + backward with the exchange of
+ * b200_p2p_sgd_apply split in two and overlapped -- the FC gradients (full_weight_1 onward, 90 % of the buffer) are
+ * all-reduced and applied on an internal stream as soon as they exist, beside the conv layers' backward kernels;
+ * the conv gradients follow at the end.  Same arguments and result as b200_forward_backward followed by
+ * b200_p2p_sgd_apply, except: state = 16 zero-initialised bytes, pads >= 128 B per worker.  bf16 mode only. */
+int b200_train_step_p2p(b200_handle h, const uint8_t* images, const int32_t* labels, const void* const* peer_grads,
+                        void* const* peer_params, void* const* peer_pads, const void* mc_grads, void* mc_params,
+                        uint32_t* state, int32_t rank, int32_t world, float lr, float grad_scale, void* stream);
 /* forward + backward + sgd_apply: one `mon_sess.run([train_op, loss])` (:230) for world == 1. */
 int b200_train_step(b200_handle h, const uint8_t* images, const int32_t* labels, float lr, void* stream);
 /* The same call with HOST (pinned) inputs and a host loss: copies the records and labels to

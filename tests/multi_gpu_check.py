@@ -71,6 +71,19 @@ def main():
     torch.cuda.synchronize()
     same2 = ex.replicas_identical(eng.params)
 
+    # (4) the same step with the exchange overlapped with the backward pass (b200_train_step_p2p): from params0 on the
+    #     same batch it must land on the parameters of (2) -- up to the last-bit jitter of the backward's atomics -- and
+    #     leave all replicas bit-identical, twice in a row (epoch counters of both flag channels)
+    eng.load_params(params0)
+    torch.cuda.synchronize(); dist.barrier()
+    ex.train_step_(eng, imgd, labd, lr)
+    torch.cuda.synchronize(); dist.barrier()
+    diff_ovl = float((eng.params - p_p2p).abs().max())
+    same3 = ex.replicas_identical(eng.params)
+    ex.train_step_(eng, imgd, labd, lr)
+    torch.cuda.synchronize(); dist.barrier()
+    same4 = ex.replicas_identical(eng.params)
+
     # timing inside graphs
     def timed(fn, n=200):
         g = eng.capture(fn)
@@ -97,13 +110,18 @@ def main():
     t_step_p2p = timed(full_p2p, 100)
     eng.load_params(params0)
     t_step_nccl = timed(full_nccl, 100)
+    eng.load_params(params0)
+    t_step_ovl = timed(lambda: ex.train_step_(eng, imgd, labd, lr), 100)
+    same5 = ex.replicas_identical(eng.params)
     if rank == 0:
         print(f"world={world} multicast={ex.multicast} |p2p - nccl|max = {diff:.3e} (scale {scale:.3f}), "
               f"vs oracle sum-update rel {err_oracle:.2e}, replicas identical: {same_replicas} / {same2}")
         print(f"exchange+update only: nccl allreduce + sgd kernel {t_nccl:.1f} us, fused p2p kernel {t_p2p:.1f} us")
-        print(f"whole step (batch {B}/GPU): nccl path {t_step_nccl:.1f} us, fused p2p path {t_step_p2p:.1f} us "
-              f"-> {B * world / t_step_p2p * 1e6:.0f} img/s")
-    ok = diff <= 1e-6 * scale and err_oracle <= 1e-6 and same_replicas and same2
+        print(f"whole step (batch {B}/GPU): nccl path {t_step_nccl:.1f} us, fused p2p path {t_step_p2p:.1f} us, "
+              f"overlapped p2p path {t_step_ovl:.1f} us -> {B * world / t_step_ovl * 1e6:.0f} img/s")
+        print(f"overlapped exchange: |overlapped - fused|max = {diff_ovl:.3e}, replicas identical: {same3} / {same4} / {same5}")
+    ok = diff <= 1e-6 * scale and err_oracle <= 1e-6 and same_replicas and same2 and \
+        diff_ovl <= 1e-5 * scale and same3 and same4 and same5
     torch.cuda.synchronize(); dist.barrier()
     sys.stdout.flush()
     os._exit(0 if ok else 1)
