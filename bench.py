@@ -218,7 +218,7 @@ def main():
         try:
             total = b200cnn.TrainStepEngine(batch=8, mode="fp32", device=local).total
             ex = b200cnn.P2PExchange(total, torch.device("cuda", local), reduce=args.reduce)
-            exchange = "p2p-fused" + ("-nvls" if ex.multicast else "")
+            exchange = "p2p-fused" + ("-nvls" if ex.multicast else "") + ("-overlapped" if ex.overlap else "")
         except Exception as e:          # no symmetric memory on this box: fall back to NCCL (still all CUDA)
             if rank == 0:
                 print(f"P2P exchange unavailable ({type(e).__name__}: {e}); using NCCL", file=sys.stderr)

@@ -76,6 +76,7 @@ def main():
     #     leave all replicas bit-identical, twice in a row (epoch counters of both flag channels)
     eng.load_params(params0)
     torch.cuda.synchronize(); dist.barrier()
+    ex.overlap = True       # exercise the overlapped variant whatever the world size
     ex.train_step_(eng, imgd, labd, lr)
     torch.cuda.synchronize(); dist.barrier()
     diff_ovl = float((eng.params - p_p2p).abs().max())
