@@ -337,12 +337,17 @@ def main():
     barrier()
     e0.record()
     loss_seen = 0.0
+    done = [torch.cuda.Event() for _ in range(RING)]
     for i in range(K):
         host_graphs[i % RING].replay()                      # H2D records+labels, step, D2H loss
-        torch.cuda.current_stream().synchronize()           # the reference loop returns the loss every step (:230)
-        loss_seen = float(host_ring[i % RING][2][0])
+        done[i % RING].record()
+        if i:                                               # the loss of every step is read on the host (:230) -- one step
+            done[(i - 1) % RING].synchronize()              # behind, so that the next step is already queued while the
+            loss_seen = float(host_ring[(i - 1) % RING][2][0])      # host waits (no launch gap on the GPU)
         if i % 4 == 3:
             eng.params.copy_(params0)
+    done[(K - 1) % RING].synchronize()
+    loss_seen = float(host_ring[(K - 1) % RING][2][0])
     e1.record()
     barrier()
     ms_e2e = e0.elapsed_time(e1)
@@ -410,10 +415,14 @@ def main():
             "clocks": clocks,
             "e2e": {"value": imgs / (ms_e2e * 1e-3), "unit": "images/s",
                     "h2d_bytes_per_step": B * 3072 + B * 4, "d2h_bytes_per_step": 4,
-                    "note": "pinned host records -> H2D -> step -> D2H loss, stream-synchronised and loss read "
-                            "every step; L2 not flushed (inputs arrive from the host each step)",
+                    "note": "pinned host records -> H2D -> step -> D2H loss every step; the host reads each step's loss one "
+                            "step behind (the next step is queued before it waits, so the GPU sees no launch gap); L2 not "
+                            "flushed (inputs arrive from the host each step)",
                     "last_loss": loss_seen},
-            "gpu_launches": eng.launches_per_step * K,
+            # kernels of this repo per step: the single-GPU step ends in sgd_kernel; with workers that launch is replaced
+            # by the fused peer-memory update (two launches when the exchange is overlapped) or follows NCCL's kernels
+            "gpu_launches": (eng.launches_per_step if world == 1 else
+                             eng.launches_per_step - 1 + (2 if (fused and ex.overlap) else 1)) * K,
             "roofline": roof,
             "step_roofline": {"tensor_frac_of_sustained": step_flops / (ms_step * 1e-3) / 1e12 / peaks["tflops_sustained"],
                               "hbm_frac_layer_boundary_model": step_bytes / (ms_step * 1e-3) / 1e9 / peaks["hbm_gbs"],
