@@ -54,3 +54,22 @@ def test_engine_refuses_to_run_without_cuda():
         pytest.skip("CUDA present")
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         b200cnn.TrainStepEngine()
+
+
+def test_trace_entry_point_reports_a_plain_build():
+    """b200_debug_trace only works in a B200_TRACE=1 diagnostics build; the shipped library says so."""
+    lib = _lib.load()
+    assert lib.b200_debug_trace(None) == _lib.E_STATE
+    assert b"B200_TRACE" in lib.b200_last_error()
+
+
+def test_p2p_step_validates_its_tables_without_gpu():
+    """b200_train_step_p2p (cifar10cnn.py:162-163 + :195-196 for world > 1) rejects missing peer tables before it
+    touches the device."""
+    lib = _lib.load()
+    h = C.c_void_p()
+    cfg = _lib.Config(128, 32, 32, 24, 24, 3, 64, 64, 384, 192, 10, 1)
+    assert lib.b200_create(C.byref(cfg), C.byref(h)) == 0
+    rc = lib.b200_train_step_p2p(h, None, None, None, None, None, None, None, None, 0, 2, 0.1, 1.0, None)
+    assert rc != 0
+    lib.b200_destroy(h)
