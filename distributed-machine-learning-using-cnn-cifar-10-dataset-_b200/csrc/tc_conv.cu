@@ -641,7 +641,7 @@ __global__ void __launch_bounds__(416, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
   const int img_beg = blockIdx.y * a.imgs_per_cta;
   const int img_end = min(g.B, img_beg + a.imgs_per_cta);
   const int nimg = max(0, img_end - img_beg);
-  const int ksteps = (g.rows_per_img * g.P + 15) / 16;
+  const int ksteps = (g.H * g.P + 15) / 16;      // dY is zero beyond the image's H rows of P slots
 
   if (tid == 0) {
     for (int s = 0; s < 2; ++s) { mbar_init(smem_u32(full + s), WG_LOADERS); mbar_init(smem_u32(empty + s), 5); }
