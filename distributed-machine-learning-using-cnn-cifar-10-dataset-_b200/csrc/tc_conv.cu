@@ -559,7 +559,7 @@ constexpr int WG_LOADERS = 256;     // the filter-gradient kernel is bound by it
 __device__ __forceinline__ void wg_loaders_sync() { asm volatile("bar.sync 2, 256;" ::: "memory"); }
 // x and dY strips of one image (64 channels each) filled together: every thread has its whole share of both
 // tensors (<= 5 + 5 chunks of 32 bytes) in flight before the first conversion, one memory round trip per image
-__device__ __forceinline__ void fill_strip_pair(uint8_t* xs, uint8_t* ds, const float* __restrict__ x,
+__device__ __forceinline__ void fill_strip_pair(uint8_t* xs, uint8_t* x2, uint8_t* ds, const float* __restrict__ x,
                                                 const float* __restrict__ dy, const ConvGeom& g, int n, int tid) {
   constexpr int U = 5;
   const int per_img = g.H * g.W * 8;
@@ -586,14 +586,16 @@ __device__ __forceinline__ void fill_strip_pair(uint8_t* xs, uint8_t* ds, const 
         const int off = c * g.ch_stride + (g.lead + i * g.P + j) * 16;
         const float fx[8] = {vx[u][0].x, vx[u][0].y, vx[u][0].z, vx[u][0].w, vx[u][1].x, vx[u][1].y, vx[u][1].z, vx[u][1].w};
         const float fd[8] = {vd[u][0].x, vd[u][0].y, vd[u][0].z, vd[u][0].w, vd[u][1].x, vd[u][1].y, vd[u][1].z, vd[u][1].w};
-        *reinterpret_cast<uint4*>(xs + off) = pack8(fx);
+        const uint4 px = pack8(fx);
+        *reinterpret_cast<uint4*>(xs + off) = px;
+        *reinterpret_cast<uint4*>(x2 + off - 16) = px;          // the copy shifted down one slot
         *reinterpret_cast<uint4*>(ds + off) = pack8(fd);
       }
     }
   }
 }
 
-__device__ __forceinline__ void fill_strip_pair_bf16(uint8_t* xs, uint8_t* ds, const __nv_bfloat16* __restrict__ x,
+__device__ __forceinline__ void fill_strip_pair_bf16(uint8_t* xs, uint8_t* x2, uint8_t* ds, const __nv_bfloat16* __restrict__ x,
                                                      const __nv_bfloat16* __restrict__ dy, const ConvGeom& g, int n,
                                                      int tid) {
   constexpr int U = 5;
@@ -615,6 +617,7 @@ __device__ __forceinline__ void fill_strip_pair_bf16(uint8_t* xs, uint8_t* ds, c
         const int i = pix / g.W, j = pix - i * g.W;
         const int off = c * g.ch_stride + (g.lead + i * g.P + j) * 16;
         *reinterpret_cast<uint4*>(xs + off) = vx[u];
+        *reinterpret_cast<uint4*>(x2 + off - 16) = vx[u];       // the copy shifted down one slot
         *reinterpret_cast<uint4*>(ds + off) = vd[u];
       }
     }
@@ -627,8 +630,12 @@ __global__ void __launch_bounds__(416, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
   constexpr int C = 64;
   const ConvGeom& g = a.g;
   extern __shared__ __align__(128) uint8_t smem[];
-  const int strip_bytes = ((C / 8) * g.ch_stride + 127) & ~127;
-  uint8_t* ctrl = smem + 2 * a.nbuf * strip_bytes;        // [buf][x | dy]
+  // per buffer: [x: 8 chunks][x shifted down one slot: 8 chunks][dY: 8 chunks].  The two x copies are 16 consecutive
+  // chunks at one stride, i.e. the 16 M-groups of ONE M = 128 MMA whose rows 0-63 are tap dj and rows 64-127 tap dj+1.
+  const int strip_bytes = ((C / 8) * g.ch_stride + 127) & ~127;       // one 8-chunk strip (dY); x + x2 = 2 * 8 chunks
+  const int xpair_bytes = (2 * (C / 8) * g.ch_stride + 127) & ~127;
+  const int buf_bytes = xpair_bytes + strip_bytes;
+  uint8_t* ctrl = smem + a.nbuf * buf_bytes;
   uint64_t* full = reinterpret_cast<uint64_t*>(ctrl);
   uint64_t* empty = full + 2;
   uint64_t* accum = empty + 2;
@@ -644,11 +651,11 @@ __global__ void __launch_bounds__(416, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
   const int ksteps = (g.H * g.P + 15) / 16;      // dY is zero beyond the image's H rows of P slots
 
   if (tid == 0) {
-    for (int s = 0; s < 2; ++s) { mbar_init(smem_u32(full + s), WG_LOADERS); mbar_init(smem_u32(empty + s), 5); }
-    mbar_init(smem_u32(accum), 5);
+    for (int s = 0; s < 2; ++s) { mbar_init(smem_u32(full + s), WG_LOADERS); mbar_init(smem_u32(empty + s), 3); }
+    mbar_init(smem_u32(accum), 3);
     fence_mbar_init();
   }
-  if (warp == 8) tmem_alloc(smem_u32(tmem_slot), 512);
+  if (warp == 8) tmem_alloc(smem_u32(tmem_slot), 256);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -658,16 +665,63 @@ __global__ void __launch_bounds__(416, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
   if (warp < 8) {
     if (stamp) a.timeline[8] = clock64();
     // pads stay zero for every image: fills touch valid pixels only
-    for (int o = tid * 16; o < 2 * a.nbuf * strip_bytes; o += WG_LOADERS * 16) *reinterpret_cast<uint4*>(smem + o) = make_uint4(0, 0, 0, 0);
+    for (int o = tid * 16; o < a.nbuf * buf_bytes; o += WG_LOADERS * 16) *reinterpret_cast<uint4*>(smem + o) = make_uint4(0, 0, 0, 0);
     wg_loaders_sync();
     pdl_wait();
     if (stamp) a.timeline[9] = clock64();
+    // bf16 sources, image fits one batch of 5 chunks per thread: the loads of image it+1 are in flight while image it
+    // is stored (a round trip to L2 is ~3k cycles here whatever the size; the MMAs of an image take 1.7k)
+    constexpr int PU = 5;
+    const int per_img = g.H * g.W * 8;
+    if (a.xb && !a.pg.dpool && per_img <= PU * WG_LOADERS) {
+      uint4 vxa[PU], vda[PU], vxb[PU], vdb[PU];
+      auto load = [&](int it, uint4 (&vx)[PU], uint4 (&vd)[PU]) {
+        const uint4* sx = reinterpret_cast<const uint4*>(a.xb + (int64_t)(img_beg + it) * per_img * 8);
+        const uint4* sd = reinterpret_cast<const uint4*>(a.dyb + (int64_t)(img_beg + it) * per_img * 8);
+#pragma unroll
+        for (int u = 0; u < PU; ++u) {
+          const int q = min(tid + u * WG_LOADERS, per_img - 1);      // clamped, not predicated
+          vx[u] = __ldg(sx + q); vd[u] = __ldg(sd + q);
+        }
+      };
+      auto store = [&](int it, const uint4 (&vx)[PU], const uint4 (&vd)[PU]) {
+        const int b = it % a.nbuf;
+        mbar_wait(smem_u32(empty + b), ((it / a.nbuf) & 1) ^ 1);
+        uint8_t* xs = smem + b * buf_bytes;
+        uint8_t* x2 = xs + (C / 8) * g.ch_stride;
+        uint8_t* ds = xs + xpair_bytes;
+#pragma unroll
+        for (int u = 0; u < PU; ++u) {
+          const int q = tid + u * WG_LOADERS;
+          if (q < per_img) {
+            const int c = q & 7, pix = q >> 3;
+            const int i = pix / g.W, j = pix - i * g.W;
+            const int off = c * g.ch_stride + (g.lead + i * g.P + j) * 16;
+            *reinterpret_cast<uint4*>(xs + off) = vx[u];
+            *reinterpret_cast<uint4*>(x2 + off - 16) = vx[u];
+            *reinterpret_cast<uint4*>(ds + off) = vd[u];
+          }
+        }
+        fence_proxy_async();
+        mbar_arrive(smem_u32(full + b));
+        if (stamp && it == 0) a.timeline[10] = clock64();
+      };
+      if (nimg > 0) load(0, vxa, vda);
+#pragma unroll 1
+      for (int it = 0; it < nimg; it += 2) {
+        if (it + 1 < nimg) load(it + 1, vxb, vdb);
+        store(it, vxa, vda);
+        if (it + 2 < nimg) load(it + 2, vxa, vda);
+        if (it + 1 < nimg) store(it + 1, vxb, vdb);
+      }
+    } else
     for (int it = 0; it < nimg; ++it) {
       const int b = it % a.nbuf;
       const uint32_t ph = (it / a.nbuf) & 1;
       mbar_wait(smem_u32(empty + b), ph ^ 1);
-      uint8_t* xs = smem + (2 * b) * strip_bytes;
-      uint8_t* ds = xs + strip_bytes;
+      uint8_t* xs = smem + b * buf_bytes;
+      uint8_t* x2 = xs + (C / 8) * g.ch_stride;      // x2[slot] = x[slot + 1]
+      uint8_t* ds = xs + xpair_bytes;
       if (a.pg.dpool) {                       // the pooled-gradient gather keeps its 128-thread helpers (warps 0-3)
         if (warp < 4) {
           float unused[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -676,30 +730,48 @@ __global__ void __launch_bounds__(416, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
           loaders_sync();
           fill_strip_from_pool(ds, dpm, argb, g, a.pg, 0, g.ch_stride, tid, unused);
           loaders_sync();                     // nobody restages dpm while a slower loader still gathers from it
+          for (int q = tid; q < (C / 8) * (g.npix - 1); q += LOADERS) {      // the shifted copy, from shared memory
+            const int c = q / (g.npix - 1), sl = q - c * (g.npix - 1);
+            *reinterpret_cast<uint4*>(x2 + c * g.ch_stride + sl * 16) = *reinterpret_cast<const uint4*>(xs + c * g.ch_stride + (sl + 1) * 16);
+          }
         }
       } else {
-        if (a.xb) fill_strip_pair_bf16(xs, ds, a.xb, a.dyb, g, img_beg + it, tid);
-        else fill_strip_pair(xs, ds, a.x, a.dy, g, img_beg + it, tid);
+        if (a.xb) fill_strip_pair_bf16(xs, x2, ds, a.xb, a.dyb, g, img_beg + it, tid);
+        else fill_strip_pair(xs, x2, ds, a.x, a.dy, g, img_beg + it, tid);
       }
       fence_proxy_async();
       mbar_arrive(smem_u32(full + b));
       if (stamp && it == 0) a.timeline[10] = clock64();
     }
     if (stamp) a.timeline[11] = clock64();
-    // ---- epilogue: M = 64 accumulators live in lanes 0-15 of each 32-lane subpartition --------------
+    // ---- epilogue ------------------------------------------------------------------------------------------
     mbar_wait(smem_u32(accum), 0);
     tc_fence_after();
     if (stamp) a.timeline[12] = clock64();
     float* part = a.partial + (int64_t)blockIdx.y * 25 * C * C;
-    const int q4 = warp & 3, c0 = (warp >> 2) * 32;       // TMEM lane quarter, column half of each tap
+    const int q4 = warp & 3, c0 = (warp >> 2) * 32;       // TMEM lane quarter, column half of each accumulator
+    // accumulators 0 / 1 (M = 128): lanes 0-63 = tap 2p, lanes 64-127 = tap 2p+1, lane % 64 = cin
 #pragma unroll 1
-    for (int dj = 0; dj < 5; ++dj) {
+    for (int p = 0; p < 2; ++p) {
       uint32_t v[32];
-      tmem_ld32(tmem + ((uint32_t)(q4 * 32) << 16) + dj * C + c0, v);
+      tmem_ld32(tmem + ((uint32_t)(q4 * 32) << 16) + p * C + c0, v);
+      tmem_ld_wait();
+      const int row = q4 * 32 + lane, dj = 2 * p + (row >> 6), cin = row & 63;
+      float* out = part + ((int64_t)(di * 5 + dj) * C + cin) * C + c0;
+#pragma unroll
+      for (int j = 0; j < 32; j += 4)
+        *reinterpret_cast<float4*>(out + j) =
+            (nimg > 0) ? make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]),
+                                     __uint_as_float(v[j + 3]))
+                       : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    {   // accumulator 2 (tap 4, M = 64): lanes 0-15 of each 32-lane quarter
+      uint32_t v[32];
+      tmem_ld32(tmem + ((uint32_t)(q4 * 32) << 16) + 2 * C + c0, v);
       tmem_ld_wait();
       if (lane < 16) {
         const int cin = q4 * 16 + lane;
-        float* out = part + ((int64_t)(di * 5 + dj) * C + cin) * C + c0;
+        float* out = part + ((int64_t)(di * 5 + 4) * C + cin) * C + c0;
 #pragma unroll
         for (int j = 0; j < 32; j += 4)
           *reinterpret_cast<float4*>(out + j) =
@@ -711,28 +783,26 @@ __global__ void __launch_bounds__(416, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
     tc_fence_before();
     if (stamp) a.timeline[13] = clock64();
   } else {
-    // warps 8..12: one issuing thread per filter tap dj of this CTA's filter row (own accumulator each)
-    if (lane == 0) {
-      const int dj = warp - 8;
-      const uint32_t idesc = make_idesc(64, C, true, true);
+    // warps 8..10: one issuing thread per accumulator of this CTA's filter row: taps (0,1) and (2,3) as M = 128
+    // MMAs over the x / shifted-x pair, tap 4 as an M = 64 MMA (48 + 48 + 46 cycles per k-step instead of 5 x 46)
+    if (lane == 0 && warp < 11) {
+      const int w = warp - 8;
+      const uint32_t idesc = make_idesc(w < 2 ? 128 : 64, C, true, true);
       const uint32_t hi = desc_hi(g.ch_stride);                 // MN-major: SBO = channel-chunk stride, LBO = 128
-      const uint32_t d = tmem + dj * C;
+      const uint32_t d = tmem + w * C;
       uint32_t acc = 0;
       for (int it = 0; it < nimg; ++it) {
         const int b = it % a.nbuf;
         const uint32_t ph = (it / a.nbuf) & 1;
         mbar_wait(smem_u32(full + b), ph);
         tc_fence_after();
-        const uint32_t xs = smem_u32(smem + (2 * b) * strip_bytes);
-        uint32_t x_lo = desc_lo(xs + (g.lead + (di - 2) * g.P - 2 + dj) * 16, 128);
-        uint32_t d_lo = desc_lo(xs + strip_bytes + g.lead * 16, 128);
-        int ks = 0;
-        for (; ks + 2 <= ksteps; ks += 2) {                      // 16 pixel slots = 16 x 16 bytes per k-step
+        const uint32_t xs = smem_u32(smem + b * buf_bytes);
+        uint32_t x_lo = desc_lo(xs + (g.lead + (di - 2) * g.P - 2 + 2 * w) * 16, 128);
+        uint32_t d_lo = desc_lo(xs + xpair_bytes + g.lead * 16, 128);
+        for (int ks = 0; ks < ksteps; ++ks) {                    // 16 pixel slots = 16 x 16 bytes per k-step
           umma_bf16(d, desc_join(x_lo, hi), desc_join(d_lo, hi), idesc, acc | (uint32_t)ks);
-          umma_bf16(d, desc_join(x_lo + 16, hi), desc_join(d_lo + 16, hi), idesc, 1u);
-          x_lo += 32; d_lo += 32;
+          x_lo += 16; d_lo += 16;
         }
-        if (ks < ksteps) umma_bf16(d, desc_join(x_lo, hi), desc_join(d_lo, hi), idesc, acc | (uint32_t)ks);
         acc = 1;
         umma_commit(smem_u32(empty + b));
       }
@@ -743,7 +813,7 @@ __global__ void __launch_bounds__(416, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
   __syncthreads();
   if (warp == 8) {
     tc_fence_after();
-    tmem_dealloc(tmem, 512);
+    tmem_dealloc(tmem, 256);
   }
 }
 
@@ -844,10 +914,14 @@ static int launch_wgrad(const float* x, const float* dy, const PoolGradSrc* pg, 
   B200_REQUIRE(Cin == 64 && Cout == 64, "conv5x5_wgrad_tc: only 64 -> 64 channels (got %d -> %d)", Cin, Cout);
   B200_REQUIRE(B > 0 && H > 0 && W > 0, "conv5x5_wgrad_tc: bad shape");
   ConvGeom g = make_geom(B, H, W, 64, 64, 1);
+  // compact strips: the k-steps cover H*P slots from `lead`, the taps shift the x operand by at most +-(2P + 2)
+  g.npix = g.lead + ((H * g.P + 15) / 16) * 16 + 2 * g.P + 2;
+  g.ch_stride = g.npix * 16 + 16;
   const int strip_bytes = ((8 * g.ch_stride) + 127) & ~127;
+  const int buf_bytes = ((16 * g.ch_stride + 127) & ~127) + strip_bytes;      // x, shifted x, dY
   const int extra = pg ? pg->OH * pg->OW * 64 * 5 + 16 : 0;
-  const int nbuf = (4 * strip_bytes + 256 + extra <= 227 * 1024) ? 2 : 1;
-  const int smem = 2 * nbuf * strip_bytes + 256 + extra;
+  const int nbuf = (2 * buf_bytes + 256 + extra <= 227 * 1024) ? 2 : 1;
+  const int smem = nbuf * buf_bytes + 256 + extra;
   B200_REQUIRE(smem <= 227 * 1024, "conv5x5_wgrad_tc: image %dx%d needs %d bytes of shared memory", H, W, smem);
   static bool attr = false;
   if (!attr) {
