@@ -135,6 +135,11 @@ int b200_create(const b200_config* c, b200_handle* out) {
   h->add("w2_packed", conv5x5_packed_bytes(c->c1, c->c2), 1);
   h->add("fc1_part", (int64_t)fc_fwd_tc_splits(c->batch, h->flat, c->f1) * B * c->f1, 4);
   h->add("tail_scratch", fc_tail_scratch_bytes(c->batch, c->f1, c->f2, c->n_cls), 1);
+  // FC1's bf16 operand images (bf16 mode, shapes permitting): W1 packed once per step, pool2 written by conv2's pool
+  // epilogue, dfull1 written by the FC tail -- the three FC1 products fetch them with bulk copies
+  h->add("w1_img", fc_weight_image_bytes(h->flat, c->f1), 1);
+  h->add("pool2_img", (int64_t)h->flat * B, 2);
+  h->add("dfull1_img", (int64_t)c->f1 * B, 2);
   h->add("loss", 1, 4); h->add("n_correct", 1, 4); h->add("n_bad", 1, 4); h->add("pred", B, 4);
   h->add("stage_images", B * c->c_in * c->img_h * c->img_w, 1);
   h->add("stage_labels", B, 4);
@@ -262,6 +267,7 @@ static int forward_impl(b200_handle h, const uint8_t* images, const int32_t* lab
   // parameters, so they are rebuilt on a side stream while conv1 runs (every step: the caller or the
   // last update may have changed the parameters).
   const bool fork = tc && !h->profiling;
+  const bool fcimg = tc && fc_images_supported(c.batch, h->flat, c.f1);
   if (tc) {
     if (fork) {
       TRY(ensure_side_streams(h));
@@ -271,6 +277,7 @@ static int forward_impl(b200_handle h, const uint8_t* images, const int32_t* lab
     cudaStream_t st = fork ? h->side[0] : (cudaStream_t)stream;
     SITE("weights_prep", pack_conv_weights(h->P(P_W2), h->ptr<void>("w2_packed"), c.c1, c.c2, st));
     TRY(fc_tail_prepare_w2(h->P(P_FW2), h->ptr<void>("tail_scratch"), c.batch, c.f1, c.f2, c.n_cls, st));
+    if (fcimg) TRY(pack_fc_weights(h->P(P_FW1), h->ptr<void>("w1_img"), h->flat, c.f1, st));
     if (fork) B200_CUDA_TRY(cudaEventRecord(h->ev_join[0], st));
   }
   if (fused1) {
@@ -287,7 +294,8 @@ static int forward_impl(b200_handle h, const uint8_t* images, const int32_t* lab
     // backward gathers through pool2 / arg2)
     SITE("conv2_pool2_fwd", conv5x5_pool_fwd_tc(pool1, h->ptr<void>("w2_packed"), h->P(P_B2), nullptr, pool2,
                                                 h->ptr<uint8_t>("arg2"), c.batch, h->h1, h->w1, c.c1, c.c2, st,
-                                                nullptr));
+                                                fused1 ? h->ptr<void>("pool1_bf16") : nullptr,
+                                                fcimg ? h->ptr<void>("pool2_img") : nullptr));
   }
   else
     SITE("conv2_fwd", conv5x5_fwd_f32(pool1, h->P(P_W2), h->P(P_B2), conv2, c.batch, h->h1, h->w1, c.c1, c.c2, 1, st));
@@ -299,14 +307,19 @@ static int forward_impl(b200_handle h, const uint8_t* images, const int32_t* lab
     // The tail also clears the conv gradients (first four tensors of the flat buffer): conv1's filter / bias
     // gradient and conv2's bias gradient are accumulated with atomics further down.
     float* part = h->ptr<float>("fc1_part");
-    PSITE("full1_fwd", fc_fwd_tc_splitk(pool2, h->P(P_FW1), part, c.batch, h->flat, c.f1, st));
+    if (fcimg)
+      PSITE("full1_fwd", fc_fwd_tc_splitk_img(h->ptr<void>("pool2_img"), h->ptr<void>("w1_img"), part, c.batch, h->flat,
+                                              c.f1, st));
+    else
+      PSITE("full1_fwd", fc_fwd_tc_splitk(pool2, h->P(P_FW1), part, c.batch, h->flat, c.f1, st));
     SITE("fc_tail", fc_tail(part, fc_fwd_tc_splits(c.batch, h->flat, c.f1), h->P(P_FB1), full1, h->P(P_FW2),
                             h->P(P_FB2), h->P(P_FW3), h->P(P_FB3), labels, full2, logits, h->ptr<float>("dlogits"),
                             h->ptr<float>("dfull2"), h->ptr<float>("dfull1"), h->ptr<int32_t>("pred"),
                             h->ptr<float>("loss"), h->ptr<int32_t>("n_correct"), h->ptr<int32_t>("n_bad"),
                             h->G(P_FW2), h->G(P_FB2), h->G(P_FW3), h->G(P_FB3), h->G(P_FB1),
                             h->ptr<void>("tail_scratch"), h->grads, (int)(h->p_off[P_B2] + h->p_size[P_B2]), c.batch, c.f1, c.f2,
-                            c.n_cls, st, true, fork ? h->side[1] : nullptr, h->ev_fork[1], !h->profiling));
+                            c.n_cls, st, true, fork ? h->side[1] : nullptr, h->ev_fork[1], !h->profiling,
+                            fcimg ? h->ptr<void>("dfull1_img") : nullptr));
     // (side stream 1, not 0: the backward puts FC1's dW on stream 0 and wants it to start with FC1's dX, not behind
     //  this kernel -- 36 + 108 CTAs fit the machine together)
     if (fork && !defer_tail) {
@@ -365,15 +378,23 @@ static int backward_impl(b200_handle h, void* stream, const P2PCtx* px) {
     if (fork) TRY(ensure_side_streams(h));
     cudaStream_t s0 = fork ? h->side[0] : st, s1 = fork ? h->side[1] : st;
     const bool fused1 = conv1_tc_supported(c.crop_h, c.crop_w, c.c_in, c.c1);
+    const bool fcimg = fc_images_supported(c.batch, h->flat, c.f1);
     if (fork) {
       B200_CUDA_TRY(cudaEventRecord(h->ev_fork[0], st));
       B200_CUDA_TRY(cudaStreamWaitEvent(s0, h->ev_fork[0], 0));
     }
     {
       cudaStream_t st = s0;   // SITE() launches on `st`
-      SITE("full1_dw", fc_dw_tc(h->ptr<float>("pool2"), dfull1, h->G(P_FW1), c.batch, h->flat, c.f1, st));
+      if (fcimg)
+        SITE("full1_dw", fc_dw_tc_img(h->ptr<void>("pool2_img"), h->ptr<void>("dfull1_img"), h->G(P_FW1), c.batch, h->flat,
+                                      c.f1, st));
+      else
+        SITE("full1_dw", fc_dw_tc(h->ptr<float>("pool2"), dfull1, h->G(P_FW1), c.batch, h->flat, c.f1, st));
     }
-    PSITE("full1_dx", fc_dx_tc(h->ptr<float>("pool2"), h->P(P_FW1), dfull1, dpool2, c.batch, h->flat, c.f1, 0, st));
+    if (fcimg)
+      PSITE("full1_dx", fc_dx_tc_img(h->ptr<void>("dfull1_img"), h->ptr<void>("w1_img"), dpool2, c.batch, h->flat, c.f1, st));
+    else
+      PSITE("full1_dx", fc_dx_tc(h->ptr<float>("pool2"), h->P(P_FW1), dfull1, dpool2, c.batch, h->flat, c.f1, 0, st));
     if (px && fork) {
       // Channel 0 of the exchange: the FC gradients (everything from full_weight_1 on, 90 % of the buffer) are
       // complete once FC1's dW (stream 0) and the tail-gradient kernel (stream 1) are; their all-reduce + update
@@ -565,7 +586,8 @@ int b200_launches_per_step(b200_handle h, int32_t* n) {
   if (h->cfg.mode == B200_MODE_BF16) {
     // conv1 (3 or 1), conv2, pool2, FC1 split-K, tail x2 | FC1 bwd x2, pool2 bwd, conv2 wgrad x2, dgrad, conv1 wgrad (2 or 1+4), sgd
     const bool f1 = conv1_tc_supported(h->cfg.crop_h, h->cfg.crop_w, h->cfg.c_in, h->cfg.c1);
-    *n = (f1 ? 1 : 3) + 2 + 1 + 3 + 2 + 2 + 1 + (f1 ? 1 : 5) + 1;
+    *n = (f1 ? 1 : 3) + 2 + 1 + 3 + 2 + 2 + 1 + (f1 ? 1 : 5) + 1 +
+         (fc_images_supported(h->cfg.batch, h->flat, h->cfg.f1) ? 1 : 0);      // + W1 image pack
   }
   return B200_OK;
 }
@@ -653,6 +675,7 @@ int b200_debug_conv_timeline(int64_t* device_buf8) {
   conv5x5_set_timeline(reinterpret_cast<long long*>(device_buf8));
   fc_tail_set_timeline(device_buf8 ? reinterpret_cast<long long*>(device_buf8) + 16 : nullptr);
   conv1_set_timeline(reinterpret_cast<long long*>(device_buf8));
+  gemm_set_timeline(reinterpret_cast<long long*>(device_buf8));
   return B200_OK;
 }
 int b200_debug_trace(uint64_t* device_buf) {

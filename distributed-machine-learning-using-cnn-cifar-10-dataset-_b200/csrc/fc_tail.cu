@@ -55,6 +55,7 @@ struct TailArgs {
   float* part;                     // [n_ctas][PV] per-CTA partial sums: db1 | db2 | db3(16) | dW3 | loss, ok, bad
   float* zero_ptr; int zero_n;     // buffer cleared here for later kernels' atomics (may be null)
   long long* timeline;             // diagnostics: clock64 stamps of CTA 0's phases, or null
+  uint8_t* dfull1_img;             // optional: dfull1 again as FC1's bf16 operand image [F1/8][B][8]
 };
 __host__ __device__ inline int part_len(int F1, int F2, int NC) { return F1 + F2 + 16 + F2 * NC + 4; }
 
@@ -461,10 +462,18 @@ __global__ void __launch_bounds__(RT) fc_tail_rows_kernel(TailArgs a) {
         const int col = min(j, nt - 1) * 8 + 2 * t;
         const float2 v0 = make_float2(m0[i].x > 0.f ? c[i][0] : 0.f, m0[i].y > 0.f ? c[i][1] : 0.f);
         float s0 = v0.x, s1 = v0.y;
-        if (j < nt && g < nr) *reinterpret_cast<float2*>(a.dfull1 + (size_t)(r0 + g) * a.F1 + col) = v0;
+        if (j < nt && g < nr) {
+          *reinterpret_cast<float2*>(a.dfull1 + (size_t)(r0 + g) * a.F1 + col) = v0;
+          if (a.dfull1_img)      // column chunk j, batch row r0 + g, elements 2t, 2t+1 of the chunk
+            *reinterpret_cast<uint32_t*>(a.dfull1_img + ((size_t)j * a.B + r0 + g) * 16 + 4 * t) = pack_bf16x2(v0.x, v0.y);
+        }
         if (RM == 16) {
           const float2 v1 = make_float2(m1[i].x > 0.f ? c[i][2] : 0.f, m1[i].y > 0.f ? c[i][3] : 0.f);
-          if (j < nt && g + 8 < nr) *reinterpret_cast<float2*>(a.dfull1 + (size_t)(r0 + g + 8) * a.F1 + col) = v1;
+          if (j < nt && g + 8 < nr) {
+            *reinterpret_cast<float2*>(a.dfull1 + (size_t)(r0 + g + 8) * a.F1 + col) = v1;
+            if (a.dfull1_img)
+              *reinterpret_cast<uint32_t*>(a.dfull1_img + ((size_t)j * a.B + r0 + g + 8) * 16 + 4 * t) = pack_bf16x2(v1.x, v1.y);
+          }
           s0 += v1.x; s1 += v1.y;
         }
 #pragma unroll
@@ -585,7 +594,7 @@ int fc_tail(const float* fc1_part, int n_part, const float* b1, float* full1, co
             float* dfull2, float* dfull1, int32_t* pred, float* loss, int32_t* n_correct, int32_t* n_bad, float* dw2,
             float* db2, float* dw3, float* db3, float* db1, void* scratch, float* zero_ptr, int zero_n, int B, int F1,
             int F2, int NC, cudaStream_t st, bool w2_image_ready, cudaStream_t grads_stream, cudaEvent_t rows_done,
-            bool overlap_producer) {
+            bool overlap_producer, void* dfull1_img) {
   B200_REQUIRE(B > 0 && NC > 0 && NC <= kMaxCls, "fc_tail: bad shape");
   B200_REQUIRE(F1 % KT == 0 && F2 % 32 == 0 && F2 <= RT && F2 > 0, "fc_tail: needs f1 %% 32 == 0, f2 %% 32 == 0, f2 <= 256");
   const int R = rows_per_cta(B);
@@ -597,7 +606,7 @@ int fc_tail(const float* fc1_part, int n_part, const float* b1, float* full1, co
     B200_LAUNCH_CHECK();
   }
   TailArgs a{B, F1, F2, NC, R, fc1_part, n_part, b1, full1, w2, b2, w3, b3, w2b, labels, full2, logits, dlogits,
-             dfull2, dfull1, pred, part, zero_ptr, zero_n, g_tail_timeline};
+             dfull2, dfull1, pred, part, zero_ptr, zero_n, g_tail_timeline, reinterpret_cast<uint8_t*>(dfull1_img)};
   const int RM = R <= 8 ? 8 : 16;              // rows of the MMA tile that carry batch rows
   const size_t smem = (size_t)tail_smem(RM, F1, F2, NC).total;
   B200_REQUIRE(smem <= 220 * 1024, "fc_tail: layer widths too large (%zu bytes of shared memory)", smem);

@@ -45,7 +45,8 @@ int conv5x5_fwd_tc(const float* x, const void* wp, const float* bias, float* y, 
                    int Cout, int relu, cudaStream_t st);
 // x_bf16 (optional): the same activations already rounded to bf16, [B,H,W,Cin]; read instead of x (half the bytes)
 int conv5x5_pool_fwd_tc(const float* x, const void* wp, const float* bias, float* y, float* pool, uint8_t* arg, int B,
-                        int H, int W, int Cin, int Cout, cudaStream_t st, const void* x_bf16 = nullptr);
+                        int H, int W, int Cin, int Cout, cudaStream_t st, const void* x_bf16 = nullptr,
+                        void* pool_img = nullptr);   // (optional) pooled output as FC1's bf16 operand image [H'W'Cout/8][B][8]
 int conv5x5_dgrad_tc(const float* dy, const void* wp, float* dx, int B, int H, int W, int Cin, int Cout,
                      cudaStream_t st);
 // the same two gradients fed by the POOLED gradient: dconv = MaxPoolGrad(dpool, arg) * [pool > 0] is gathered
@@ -61,9 +62,20 @@ int64_t conv5x5_wgrad_tc_scratch_bytes(int B);
 int conv5x5_wgrad_tc(const float* x, const float* dy, float* dw, float* scratch, int B, int H, int W, int Cin,
                      int Cout, cudaStream_t st, const void* x_bf16 = nullptr, const void* dy_bf16 = nullptr);
 int fc_fwd_tc_splits(int B, int K, int N);
+// FC1's three products on bf16 operand IMAGES ([chunk of 8][rows][8], the shared-memory layout of a stage: fetched
+// with bulk copies, nothing converted): x_img [K/8][B][8] (written by conv2's pool epilogue), w_img [N/8][K][8]
+// (pack_fc_weights, once per step), dy_img [N/8][B][8] (written by the FC tail).  Same arithmetic as the fp32-source
+// entry points (operands rounded to bf16 either way).
+bool fc_images_supported(int B, int K, int N);
+int64_t fc_weight_image_bytes(int K, int N);
+int pack_fc_weights(const float* w, void* img, int K, int N, cudaStream_t st);
+int fc_fwd_tc_splitk_img(const void* x_img, const void* w_img, float* part, int B, int K, int N, cudaStream_t st);
+int fc_dw_tc_img(const void* x_img, const void* dy_img, float* dw, int B, int K, int N, cudaStream_t st);
+int fc_dx_tc_img(const void* dy_img, const void* w_img, float* dx, int B, int K, int N, cudaStream_t st);
 int fc_fwd_tc_splitk(const float* x, const float* w, float* part, int B, int K, int N, cudaStream_t st);
 void fc_tail_set_timeline(long long* dev_buf);
 void conv1_set_timeline(long long* dev_buf);
+void gemm_set_timeline(long long* dev_buf);      // slots [0,6), shared with conv5x5_tc_kernel: the last kernel that ran wins
 // diagnostics build (B200_TRACE): hand the %globaltimer trace buffer to each translation unit
 void trace_set_fc_tail(unsigned long long*);
 void trace_set_tc_conv(unsigned long long*);
@@ -76,7 +88,8 @@ int fc_tail(const float* fc1_part, int n_part, const float* b1, float* full1, co
             float* dfull2, float* dfull1, int32_t* pred, float* loss, int32_t* n_correct, int32_t* n_bad, float* dw2,
             float* db2, float* dw3, float* db3, float* db1, void* scratch, float* zero_ptr, int zero_n, int B, int F1,
             int F2, int NC, cudaStream_t st, bool w2_image_ready = false, cudaStream_t grads_stream = nullptr,
-            cudaEvent_t rows_done = nullptr, bool overlap_producer = false);
+            cudaEvent_t rows_done = nullptr, bool overlap_producer = false,
+            void* dfull1_img = nullptr);     // (optional) dfull1 also as FC1's bf16 operand image [F1/8][B][8]
 int fc_tail_prepare_w2(const float* w2, void* scratch, int B, int F1, int F2, int NC, cudaStream_t st);
 // allreduce + SGD in one kernel over NVLink peer memory (p2p_update.cu)
 int p2p_allreduce_sgd(const void* const* peer_grads, void* const* peer_params, void* const* peer_pads,

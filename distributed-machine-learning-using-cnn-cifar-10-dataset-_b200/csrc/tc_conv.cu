@@ -183,6 +183,7 @@ struct ConvArgs {
   const float* x;      // [B,H,W,KC]
   const __nv_bfloat16* xb;   // the same, already bf16 (read instead of x when given)
   __nv_bfloat16* dconv_out_bf16;   // POOL dgrad: dense bf16 copy of the gathered dY (optional)
+  uint8_t* pool_img;               // fused pool: bf16 operand image of the pooled output for FC1 (optional)
   const uint8_t* wp;   // filter packed by pack_conv_weights (bf16, ready-made shared-memory images per tap)
   int cin_f, cout_f;   // the FORWARD filter's channel counts (packing geometry)
   const float* bias;   // [NC] or null
@@ -353,31 +354,42 @@ __global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
       const float* tile = reinterpret_cast<const float*>(strip);
       const int OH = (g.H + 1) / 2, OW = (g.W + 1) / 2;
       const int pbh = max((OH - 1) * 2 + 3 - g.H, 0) / 2, pbw = max((OW - 1) * 2 + 3 - g.W, 0) / 2;
-      for (int q = tid; q < OH * OW * 16; q += LOADERS) {
-        const int cq = q & 15, cell = q >> 4;
+      // one item = 8 channels of one pooled cell; window positions outside the image read a clamped address and enter
+      // the scan as -FLT_MAX (no branch); strict '>' in (kh, kw) order = first maximum
+      for (int q = tid; q < OH * OW * 8; q += LOADERS) {
+        const int c8 = q & 7, cell = q >> 3;
         const int oh = cell / OW, ow = cell - oh * OW;
-        float best[4];
-        int bi[4] = {0, 0, 0, 0};
-        bool any = false;
+        float best[8];
+        int bi[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) { best[e] = -3.402823466e38f; bi[e] = 0; }
 #pragma unroll
         for (int kh = 0; kh < 3; ++kh) {
           const int hh = 2 * oh + kh - pbh;
-          if ((unsigned)hh >= (unsigned)g.H) continue;
+          const bool vh = (unsigned)hh < (unsigned)g.H;
 #pragma unroll
           for (int kw = 0; kw < 3; ++kw) {
             const int ww = 2 * ow + kw - pbw;
-            if ((unsigned)ww >= (unsigned)g.W) continue;
-            const float4 v = *reinterpret_cast<const float4*>(tile + (size_t)(hh * g.W + ww) * 68 + cq * 4);
-            const float vv[4] = {v.x, v.y, v.z, v.w};
+            const bool ok = vh && (unsigned)ww < (unsigned)g.W;
+            const float* src = tile + (size_t)(ok ? hh * g.W + ww : 0) * 68 + c8 * 8;
+            const float4 v0 = *reinterpret_cast<const float4*>(src), v1 = *reinterpret_cast<const float4*>(src + 4);
+            const float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
 #pragma unroll
-            for (int e = 0; e < 4; ++e)
-              if (!any || vv[e] > best[e]) { best[e] = vv[e]; bi[e] = kh * 3 + kw; }
-            any = true;
+            for (int e = 0; e < 8; ++e) {
+              const float x = ok ? vv[e] : -3.402823466e38f;
+              const bool gt = x > best[e];
+              best[e] = gt ? x : best[e];
+              bi[e] = gt ? kh * 3 + kw : bi[e];
+            }
           }
         }
-        const size_t o = ((size_t)n_img0 * OH * OW + cell) * 64 + cq * 4;
+        const size_t o = ((size_t)n_img0 * OH * OW + cell) * 64 + c8 * 8;
         *reinterpret_cast<float4*>(a.pool_out + o) = make_float4(best[0], best[1], best[2], best[3]);
-        *reinterpret_cast<uchar4*>(a.arg_out + o) = make_uchar4(bi[0], bi[1], bi[2], bi[3]);
+        *reinterpret_cast<float4*>(a.pool_out + o + 4) = make_float4(best[4], best[5], best[6], best[7]);
+        *reinterpret_cast<uint2*>(a.arg_out + o) = make_uint2(bi[0] | (bi[1] << 8) | (bi[2] << 16) | (bi[3] << 24),
+                                                              bi[4] | (bi[5] << 8) | (bi[6] << 16) | (bi[7] << 24));
+        // the flattened pool output (:126, feature = cell * 64 + channel) as FC1's operand image [feature / 8][batch][8]
+        if (a.pool_img) *reinterpret_cast<uint4*>(a.pool_img + ((size_t)(cell * 8 + c8) * g.B + n_img0) * 16) = pack8(best);
       }
     }
     if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) a.timeline[6] = clock64();
@@ -498,7 +510,7 @@ template <bool DGRAD>
 int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, int B, int H, int W, int KC, int NC,
                 int relu, cudaStream_t st, const PoolGradSrc* pg = nullptr, float* dbias = nullptr,
                 float* dconv_out = nullptr, float* pool_out = nullptr, uint8_t* arg_out = nullptr,
-                const void* x_bf16 = nullptr, void* dconv_out_bf16 = nullptr) {
+                const void* x_bf16 = nullptr, void* dconv_out_bf16 = nullptr, void* pool_img = nullptr) {
   B200_REQUIRE(B > 0 && H > 0 && W > 0, "conv5x5_tc: bad shape");
   B200_REQUIRE(KC % 16 == 0 && NC % 64 == 0, "conv5x5_tc: channels must be multiples of 16 (in) / 64 (out), got %d/%d",
                KC, NC);
@@ -530,7 +542,8 @@ int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, 
     default: B200_REQUIRE(false, "conv5x5_tc: contraction channels must be 32, 64, 128 or 256 (got %d)", KC);
   }
   B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-  ConvArgs a{x, reinterpret_cast<const __nv_bfloat16*>(x_bf16), reinterpret_cast<__nv_bfloat16*>(dconv_out_bf16), wp, DGRAD ? NC : KC, DGRAD ? KC : NC, bias, y, relu, g, g_conv_timeline, pg ? *pg : PoolGradSrc{}, dbias, dconv_out, pool_out, arg_out};
+  ConvArgs a{x, reinterpret_cast<const __nv_bfloat16*>(x_bf16), reinterpret_cast<__nv_bfloat16*>(dconv_out_bf16),
+             reinterpret_cast<uint8_t*>(pool_img), wp, DGRAD ? NC : KC, DGRAD ? KC : NC, bias, y, relu, g, g_conv_timeline, pg ? *pg : PoolGradSrc{}, dbias, dconv_out, pool_out, arg_out};
   dim3 grid(cdiv(B, ipc), NC / 64);
   B200_CUDA_TRY(launch_kernel(kern, grid, dim3(288), (size_t)smem, st, a));
   return B200_OK;
@@ -870,8 +883,9 @@ int conv5x5_fwd_tc(const float* x, const void* wp, const float* bias, float* y, 
 }
 // conv + bias + ReLU + 3x3/2 SAME max-pool in one kernel; y (the un-pooled activations) is optional
 int conv5x5_pool_fwd_tc(const float* x, const void* wp, const float* bias, float* y, float* pool, uint8_t* arg, int B,
-                        int H, int W, int Cin, int Cout, cudaStream_t st, const void* x_bf16) {
-  return launch_conv<false>(x, (const uint8_t*)wp, bias, y, B, H, W, Cin, Cout, 1, st, nullptr, nullptr, nullptr, pool, arg, x_bf16);
+                        int H, int W, int Cin, int Cout, cudaStream_t st, const void* x_bf16, void* pool_img) {
+  return launch_conv<false>(x, (const uint8_t*)wp, bias, y, B, H, W, Cin, Cout, 1, st, nullptr, nullptr, nullptr, pool, arg, x_bf16,
+                            nullptr, pool_img);
 }
 // dx = Conv2DBackpropInput(dy, w): contraction over the forward Cout, output the forward Cin
 int conv5x5_dgrad_tc(const float* dy, const void* wp, float* dx, int B, int H, int W, int Cin, int Cout,

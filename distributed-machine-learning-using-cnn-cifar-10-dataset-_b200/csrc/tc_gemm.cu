@@ -32,6 +32,12 @@ struct GemmArgs {
   int k_per_split;         // multiple of BK; blockIdx.z covers K range [z*kps, (z+1)*kps)
   int64_t split_stride;    // floats between the C outputs of consecutive splits
   int trace_id;            // TraceId of this launch (diagnostics build)
+  // Operand IMAGES (optional, both or none): the operand already in bf16 as [chunk][rows][8] -- for a K-major operand
+  // chunk = k / 8 and rows = m (or n), for an MN-major one chunk = m / 8 (n / 8) and rows = k.  That is the shared-
+  // memory layout of a stage, so one thread fetches a stage with 16-24 bulk copies (TMA) and no warp converts anything.
+  const uint8_t* A_img; int A_rows;
+  const uint8_t* B_img; int B_rows;
+  long long* timeline;     // diagnostics: clock64 stamps of CTA (0,0,0) in slots [0,7) of the timeline buffer, or null
 };
 
 template <int BN>
@@ -64,7 +70,7 @@ __global__ void __maxnreg__(136) tc_gemm_kernel(GemmArgs g) {
   const int nkb = (kend - kbeg + BK - 1) / BK;
 
   if (tid == 0) {
-    for (int s = 0; s < STAGES; ++s) { mbar_init(smem_u32(full + s), LOADERS); mbar_init(smem_u32(empty + s), 1); }
+    for (int s = 0; s < STAGES; ++s) { mbar_init(smem_u32(full + s), g.A_img ? 1 : LOADERS); mbar_init(smem_u32(empty + s), 1); }
     mbar_init(smem_u32(accum), 1);
     fence_mbar_init();
   }
@@ -73,11 +79,44 @@ __global__ void __maxnreg__(136) tc_gemm_kernel(GemmArgs g) {
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  const bool stamp = g.timeline && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
+  if (stamp && tid == 0) g.timeline[0] = clock64();
 
   if (warp < 8) {
     // ------------------------------ operand staging ------------------------------------------
     pdl_wait();      // barrier / TMEM set-up above overlapped the producer; the operands are its output
     pdl_launch_dependents();   // after our own wait: a dependent overlaps this kernel only, never our producer
+    if (stamp && tid == 0) g.timeline[1] = clock64();
+    if (g.A_img) {
+      // ---- operand images: one thread streams the stages with bulk copies ------------------------------------
+      if (tid == 0) {
+        const int mrows = min(BM, g.M - m0), nrows = min(BN, g.N - n0);
+        const uint32_t a_bytes = A_MN ? (uint32_t)(BM / 8) * BK * 16 : 8u * mrows * 16;
+        const uint32_t b_bytes = B_MN ? (uint32_t)(BN / 8) * BK * 16 : 8u * nrows * 16;
+        for (int kb = 0; kb < nkb; ++kb) {
+          const int s = kb % STAGES;
+          mbar_wait(smem_u32(empty + s), ((kb / STAGES) & 1) ^ 1);
+          const uint32_t bar = smem_u32(full + s);
+          const uint32_t sa = smem_u32(smem + s * S::STAGE), sb = sa + S::A_BYTES;
+          const int k0 = kbeg + kb * BK;
+          mbar_arrive_expect_tx(bar, a_bytes + b_bytes);
+          if (!A_MN) {      // chunk = k / 8, rows = m
+            for (int c = 0; c < 8; ++c)
+              bulk_g2s(sa + c * S::A_K_LBO, g.A_img + ((int64_t)(k0 / 8 + c) * g.A_rows + m0) * 16, mrows * 16, bar);
+          } else {          // chunk = m / 8, rows = k
+            for (int gi = 0; gi < BM / 8; ++gi)
+              bulk_g2s(sa + gi * S::A_MN_SBO, g.A_img + ((int64_t)(m0 / 8 + gi) * g.A_rows + k0) * 16, BK * 16, bar);
+          }
+          if (!B_MN) {      // chunk = k / 8, rows = n
+            for (int c = 0; c < 8; ++c)
+              bulk_g2s(sb + c * S::B_K_LBO, g.B_img + ((int64_t)(k0 / 8 + c) * g.B_rows + n0) * 16, nrows * 16, bar);
+          } else {          // chunk = n / 8, rows = k
+            for (int gi = 0; gi < BN / 8; ++gi)
+              bulk_g2s(sb + gi * S::B_MN_SBO, g.B_img + ((int64_t)(n0 / 8 + gi) * g.B_rows + k0) * 16, BK * 16, bar);
+          }
+        }
+      }
+    } else {
     const TA* A = reinterpret_cast<const TA*>(g.A);
     const TB* B = reinterpret_cast<const TB*>(g.B);
     // Each thread moves NA + NB chunks (8 elements) per k-block.  The global loads of a k-block are all issued
@@ -142,44 +181,79 @@ __global__ void __maxnreg__(136) tc_gemm_kernel(GemmArgs g) {
       if (kb + 2 < nkb) issue(kb + 2, ra0, rb0);
       if (kb + 1 < nkb) commit(kb + 1, ra1, rb1);
     }
+    }
     // ------------------------------ epilogue (warps 0-3: one TMEM lane quarter each) -----------------
     if (warp < 4) {
     mbar_wait(smem_u32(accum), 0);
     tc_fence_after();
+    if (stamp && tid == 0) g.timeline[4] = clock64();
     const int m = m0 + warp * 32 + lane;
 #pragma unroll 1
     for (int c0 = 0; c0 < BN; c0 += 32) {
       uint32_t v[32];
       tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + c0, v);
       tmem_ld_wait();
+      if (stamp && tid == 0 && c0 == 0) g.timeline[6] = clock64();
+      if (stamp && tid == 0 && c0 == 32) g.timeline[7] = clock64();
+      // (conditions hoisted out of the per-element loops: as per-element branches this block cost 3.8k cycles)
       float o[32];
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        int n = n0 + c0 + j;
-        float x = __uint_as_float(v[j]);
-        if (n < g.N) {
-          if (g.bias) x += __ldg(g.bias + n);
-          if (g.relu) x = fmaxf(x, 0.f);
+      for (int j = 0; j < 32; ++j) o[j] = __uint_as_float(v[j]);
+      const bool whole = n0 + c0 + 32 <= g.N;
+      if (g.bias) {
+        if (whole) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            const float4 b = __ldg(reinterpret_cast<const float4*>(g.bias + n0 + c0 + j));
+            o[j] += b.x; o[j + 1] += b.y; o[j + 2] += b.z; o[j + 3] += b.w;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) o[j] += (n0 + c0 + j < g.N) ? __ldg(g.bias + min(n0 + c0 + j, g.N - 1)) : 0.f;
         }
-        o[j] = x;
+      }
+      if (g.relu) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) o[j] = fmaxf(o[j], 0.f);
       }
       if (g.mask && m < g.M) {
         const float* mk = g.mask + (int64_t)m * g.ldmask + n0 + c0;
+        if (whole && (g.ldmask & 3) == 0) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j)
-          if (n0 + c0 + j < g.N && !(__ldg(mk + j) > 0.f)) o[j] = 0.f;
-      }
-      if (m < g.M) {
-        float* out = g.C + (int64_t)blockIdx.z * g.split_stride + (int64_t)m * g.ldc + n0 + c0;
-        if (n0 + c0 + 32 <= g.N && ((g.ldc & 3) == 0)) {
-#pragma unroll
-          for (int j = 0; j < 32; j += 4)
-            *reinterpret_cast<float4*>(out + j) = make_float4(o[j], o[j + 1], o[j + 2], o[j + 3]);
+          for (int j = 0; j < 32; j += 4) {
+            const float4 q = __ldg(reinterpret_cast<const float4*>(mk + j));
+            o[j] = q.x > 0.f ? o[j] : 0.f; o[j + 1] = q.y > 0.f ? o[j + 1] : 0.f;
+            o[j + 2] = q.z > 0.f ? o[j + 2] : 0.f; o[j + 3] = q.w > 0.f ? o[j + 3] : 0.f;
+          }
         } else {
 #pragma unroll
           for (int j = 0; j < 32; ++j)
-            if (n0 + c0 + j < g.N) out[j] = o[j];
+            if (n0 + c0 + j < g.N && !(__ldg(mk + j) > 0.f)) o[j] = 0.f;
         }
+      }
+      if (n0 + c0 + 32 <= g.N && ((g.ldc & 3) == 0)) {
+        // A lane holds one ROW of the tile; storing it directly makes every store instruction 32 separate 16-byte
+        // requests (measured: 8.6k cycles for this 32 KB tile).  The 32 x 32 block goes through shared memory (the
+        // stage buffers are idle now; 36-float rows: conflict-free both ways) and leaves as 4 rows x 128 contiguous
+        // bytes per instruction.
+        float* tb = reinterpret_cast<float*>(smem) + warp * (32 * 36);
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 32; j += 4)
+          *reinterpret_cast<float4*>(tb + lane * 36 + j) = make_float4(o[j], o[j + 1], o[j + 2], o[j + 3]);
+        __syncwarp();
+        float* out = g.C + (int64_t)blockIdx.z * g.split_stride + (int64_t)(m0 + warp * 32) * g.ldc + n0 + c0;
+#pragma unroll
+        for (int r0 = 0; r0 < 32; r0 += 4) {
+          const int r = r0 + (lane >> 3), cc = (lane & 7) * 4;
+          const float4 x = *reinterpret_cast<const float4*>(tb + r * 36 + cc);
+          if (m0 + warp * 32 + r < g.M) *reinterpret_cast<float4*>(out + (int64_t)r * g.ldc + cc) = x;
+        }
+      } else if (m < g.M) {
+        float* out = g.C + (int64_t)blockIdx.z * g.split_stride + (int64_t)m * g.ldc + n0 + c0;
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (n0 + c0 + j < g.N) out[j] = o[j];
       }
       if (g.colsum) {   // column sums over the rows of this tile (rows >= M contribute 0): warp shuffle tree
 #pragma unroll
@@ -193,6 +267,7 @@ __global__ void __maxnreg__(136) tc_gemm_kernel(GemmArgs g) {
     }
     }
     tc_fence_before();
+    if (stamp && tid == 0) g.timeline[5] = clock64();
   } else {
     // ------------------------------ MMA issue (one thread) -----------------------------------------
     if (lane == 0) {
@@ -205,6 +280,7 @@ __global__ void __maxnreg__(136) tc_gemm_kernel(GemmArgs g) {
         const uint32_t ph = (kb / STAGES) & 1;
         mbar_wait(smem_u32(full + s), ph);
         tc_fence_after();
+        if (stamp && kb == 0) g.timeline[2] = clock64();
         uint32_t a_lo = a_lo0 + (uint32_t)s * (S::STAGE >> 4), b_lo = b_lo0 + (uint32_t)s * (S::STAGE >> 4);
 #pragma unroll
         for (int ks = 0; ks < BK / 16; ++ks) {
@@ -215,6 +291,7 @@ __global__ void __maxnreg__(136) tc_gemm_kernel(GemmArgs g) {
         umma_commit(smem_u32(empty + s));
       }
       umma_commit(smem_u32(accum));
+      if (stamp) g.timeline[3] = clock64();
     }
     __syncwarp();
   }
@@ -225,8 +302,12 @@ __global__ void __maxnreg__(136) tc_gemm_kernel(GemmArgs g) {
   }
 }
 
+long long* g_gemm_timeline = nullptr;
+
 template <int BN, bool A_MN, bool B_MN, typename TA, typename TB>
-int launch(const GemmArgs& g, cudaStream_t st) {
+int launch(const GemmArgs& g_in, cudaStream_t st) {
+  GemmArgs g = g_in;
+  g.timeline = g_gemm_timeline;
   using S = Smem<BN>;
   auto kern = tc_gemm_kernel<BN, A_MN, B_MN, TA, TB>;
   static bool attr_done = false;      // per instantiation; attribute is per-function, device-wide
@@ -305,6 +386,51 @@ int fc_bwd_tc(const float* x, const float* w, const float* dy, float* dx, float*
   return fc_dx_tc(x, w, dy, dx, Bt, K, N, mask_x, st);
 }
 
+// ---- operand images -------------------------------------------------------------------------------------------
+// w [K][N] fp32 -> bf16 image [N/8][K][8]: serves the forward product (B MN-major: chunk = n/8, rows = k) and dX
+// (B K-major with k = n_out: chunk = n_out/8, rows = k_feat) alike.  Rebuilt once per step on a side stream.
+namespace {
+__global__ void pack_fc_weights_kernel(const float* __restrict__ w, uint4* __restrict__ img, int K, int N) {
+  const int ng = N / 8;
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < K * ng; idx += gridDim.x * blockDim.x) {
+    const int g8 = idx % ng, k = idx / ng;                       // neighbouring threads read neighbouring 32 bytes
+    img[(size_t)g8 * K + k] = load_chunk(w + (size_t)k * N + g8 * 8);
+  }
+}
+int img_ok(const void* a, const void* b) { return a && b && ((uintptr_t)a & 15) == 0 && ((uintptr_t)b & 15) == 0; }
+}  // namespace
+int64_t fc_weight_image_bytes(int K, int N) { return (int64_t)K * N * 2; }
+int pack_fc_weights(const float* w, void* img, int K, int N, cudaStream_t st) {
+  B200_REQUIRE(K > 0 && N > 0 && N % 8 == 0 && ((uintptr_t)w & 15) == 0 && ((uintptr_t)img & 15) == 0,
+               "pack_fc_weights: bad shape / alignment");
+  pack_fc_weights_kernel<<<std::min(cdiv((int64_t)K * (N / 8), 256), 4 * kNumSMs), 256, 0, st>>>(w, (uint4*)img, K, N);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+bool fc_images_supported(int Bt, int K, int N) { return Bt % 64 == 0 && K % 128 == 0 && N % 64 == 0; }
+// the three FC1 products on operand images: x_img [K/8][Bt][8], w_img [N/8][K][8], dy_img [N/8][Bt][8] (all bf16)
+int fc_fwd_tc_splitk_img(const void* x_img, const void* w_img, float* part, int Bt, int K, int N, cudaStream_t st) {
+  B200_REQUIRE(img_ok(x_img, w_img) && fc_images_supported(Bt, K, N), "fc_fwd_tc_splitk_img: bad operands");
+  int s = fc_fwd_tc_splits(Bt, K, N);
+  int kps = (int)round_up(cdiv(K, s), BK);
+  GemmArgs g{Bt, N, K, nullptr, K, nullptr, N, part, N, nullptr, 0, nullptr, 0, nullptr, kps, (int64_t)Bt * N, TR_FC1_FWD,
+             (const uint8_t*)x_img, Bt, (const uint8_t*)w_img, K};
+  return dispatch<false, true>(g, st);
+}
+int fc_dw_tc_img(const void* x_img, const void* dy_img, float* dw, int Bt, int K, int N, cudaStream_t st) {
+  B200_REQUIRE(img_ok(x_img, dy_img) && fc_images_supported(Bt, K, N), "fc_dw_tc_img: bad operands");
+  GemmArgs g{K, N, Bt, nullptr, K, nullptr, N, dw, N, nullptr, 0, nullptr, 0, nullptr, (int)round_up(Bt, BK), 0, TR_FC1_DW,
+             (const uint8_t*)x_img, Bt, (const uint8_t*)dy_img, Bt};
+  return dispatch<true, true>(g, st);
+}
+int fc_dx_tc_img(const void* dy_img, const void* w_img, float* dx, int Bt, int K, int N, cudaStream_t st) {
+  B200_REQUIRE(img_ok(dy_img, w_img) && fc_images_supported(Bt, K, N), "fc_dx_tc_img: bad operands");
+  GemmArgs g{Bt, K, N, nullptr, N, nullptr, N, dx, K, nullptr, 0, nullptr, K, nullptr, (int)round_up(N, BK), 0, TR_FC1_DX,
+             (const uint8_t*)dy_img, Bt, (const uint8_t*)w_img, K};
+  return dispatch<false, false>(g, st);
+}
+
+void gemm_set_timeline(long long* dev_buf) { g_gemm_timeline = dev_buf; }
 B200_TRACE_SETTER(trace_set_tc_gemm)
 
 }  // namespace b200
