@@ -316,6 +316,7 @@ __global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
     mbar_wait(smem_u32(accum), 0);
     tc_fence_after();
     if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) a.timeline[5] = clock64();
+    const bool relu = a.relu != 0;
     for (int t = 0; t < g.tiles; ++t) {
       const int p = t * 128 + warp * 32 + lane;
       const int r = p / g.P, c = p - r * g.P;
@@ -332,18 +333,17 @@ __global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
         tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + t * BN + c0, v);
         tmem_ld_wait();
         if (valid) {
+          // (bias as vector loads and the ReLU as a select: the per-element `if (bias)` / `if (relu)`
+          //  of the first version compiled to branches and cost more than the MMAs' tail)
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
-            float o[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              float xv = __uint_as_float(v[j + e]);
-              if (a.bias) xv += __ldg(a.bias + nc0 + c0 + j + e);
-              if (a.relu) xv = fmaxf(xv, 0.f);
-              o[e] = xv;
-            }
-            if (out) *reinterpret_cast<float4*>(out + c0 + j) = make_float4(o[0], o[1], o[2], o[3]);
-            if (trow) *reinterpret_cast<float4*>(trow + c0 + j) = make_float4(o[0], o[1], o[2], o[3]);
+            const float4 b = a.bias ? __ldg(reinterpret_cast<const float4*>(a.bias + nc0 + c0 + j)) : make_float4(0.f, 0.f, 0.f, 0.f);
+            const float x0 = __uint_as_float(v[j]) + b.x, x1 = __uint_as_float(v[j + 1]) + b.y;
+            const float x2 = __uint_as_float(v[j + 2]) + b.z, x3 = __uint_as_float(v[j + 3]) + b.w;
+            const float4 o = make_float4(relu ? fmaxf(x0, 0.f) : x0, relu ? fmaxf(x1, 0.f) : x1,      // selects, not branches
+                                         relu ? fmaxf(x2, 0.f) : x2, relu ? fmaxf(x3, 0.f) : x3);
+            if (out) *reinterpret_cast<float4*>(out + c0 + j) = o;
+            if (trow) *reinterpret_cast<float4*>(trow + c0 + j) = o;
           }
         }
       }

@@ -88,31 +88,35 @@ __global__ void __maxnreg__(136) tc_gemm_kernel(GemmArgs g) {
     pdl_launch_dependents();   // after our own wait: a dependent overlaps this kernel only, never our producer
     if (stamp && tid == 0) g.timeline[1] = clock64();
     if (g.A_img) {
-      // ---- operand images: one thread streams the stages with bulk copies ------------------------------------
-      if (tid == 0) {
+      // ---- operand images: warp 0 streams the stages with bulk copies, one copy per lane (a bulk copy has a fixed
+      //      issue cost of ~100 cycles; 16-24 of them from one thread were most of a stage's latency) -----------------
+      if (warp == 0) {
         const int mrows = min(BM, g.M - m0), nrows = min(BN, g.N - n0);
         const uint32_t a_bytes = A_MN ? (uint32_t)(BM / 8) * BK * 16 : 8u * mrows * 16;
         const uint32_t b_bytes = B_MN ? (uint32_t)(BN / 8) * BK * 16 : 8u * nrows * 16;
+        constexpr int NCA = A_MN ? BM / 8 : 8, NCB = B_MN ? BN / 8 : 8;      // copies per stage: lanes [0, NCA), [NCA, NCA+NCB)
+        static_assert(NCA + NCB <= 32, "one copy per lane");
         for (int kb = 0; kb < nkb; ++kb) {
           const int s = kb % STAGES;
-          mbar_wait(smem_u32(empty + s), ((kb / STAGES) & 1) ^ 1);
           const uint32_t bar = smem_u32(full + s);
+          if (lane == 0) {
+            mbar_wait(smem_u32(empty + s), ((kb / STAGES) & 1) ^ 1);
+            mbar_arrive_expect_tx(bar, a_bytes + b_bytes);
+          }
+          __syncwarp();
           const uint32_t sa = smem_u32(smem + s * S::STAGE), sb = sa + S::A_BYTES;
           const int k0 = kbeg + kb * BK;
-          mbar_arrive_expect_tx(bar, a_bytes + b_bytes);
-          if (!A_MN) {      // chunk = k / 8, rows = m
-            for (int c = 0; c < 8; ++c)
-              bulk_g2s(sa + c * S::A_K_LBO, g.A_img + ((int64_t)(k0 / 8 + c) * g.A_rows + m0) * 16, mrows * 16, bar);
-          } else {          // chunk = m / 8, rows = k
-            for (int gi = 0; gi < BM / 8; ++gi)
-              bulk_g2s(sa + gi * S::A_MN_SBO, g.A_img + ((int64_t)(m0 / 8 + gi) * g.A_rows + k0) * 16, BK * 16, bar);
-          }
-          if (!B_MN) {      // chunk = k / 8, rows = n
-            for (int c = 0; c < 8; ++c)
-              bulk_g2s(sb + c * S::B_K_LBO, g.B_img + ((int64_t)(k0 / 8 + c) * g.B_rows + n0) * 16, nrows * 16, bar);
-          } else {          // chunk = n / 8, rows = k
-            for (int gi = 0; gi < BN / 8; ++gi)
-              bulk_g2s(sb + gi * S::B_MN_SBO, g.B_img + ((int64_t)(n0 / 8 + gi) * g.B_rows + k0) * 16, BK * 16, bar);
+          if (lane < NCA) {
+            if (!A_MN)      // chunk = k / 8, rows = m
+              bulk_g2s(sa + lane * S::A_K_LBO, g.A_img + ((int64_t)(k0 / 8 + lane) * g.A_rows + m0) * 16, mrows * 16, bar);
+            else            // chunk = m / 8, rows = k
+              bulk_g2s(sa + lane * S::A_MN_SBO, g.A_img + ((int64_t)(m0 / 8 + lane) * g.A_rows + k0) * 16, BK * 16, bar);
+          } else if (lane < NCA + NCB) {
+            const int l = lane - NCA;
+            if (!B_MN)      // chunk = k / 8, rows = n
+              bulk_g2s(sb + l * S::B_K_LBO, g.B_img + ((int64_t)(k0 / 8 + l) * g.B_rows + n0) * 16, nrows * 16, bar);
+            else            // chunk = n / 8, rows = k
+              bulk_g2s(sb + l * S::B_MN_SBO, g.B_img + ((int64_t)(n0 / 8 + l) * g.B_rows + k0) * 16, BK * 16, bar);
           }
         }
       }
