@@ -128,10 +128,15 @@ __global__ void __launch_bounds__(512) p2p_allreduce_sgd_kernel(P2PArgs a) {
       if (p < a.world) *reinterpret_cast<float4*>(a.params[p] + o) = w;
   }
   // ---- B: everybody done ------------------------------------------------------------------------------------
-  __threadfence_system();
+  // one system-scope fence per CTA, by the thread that then counts the CTA in: the barrier makes the CTA's writes
+  // visible to that thread, its fence (cumulative) publishes them to the peers before the count / the flags.
+  // (512 fences per CTA, one per thread, were several microseconds of this kernel.)
   __syncthreads();
   __shared__ bool last;
-  if (tid == 0) last = atomicAdd(a.state + 1, 1u) == gridDim.x - 1;
+  if (tid == 0) {
+    __threadfence_system();
+    last = atomicAdd(a.state + 1, 1u) == gridDim.x - 1;
+  }
   __syncthreads();
   if (last) {
     if (tid < a.world) {
