@@ -70,3 +70,10 @@ def test_session_towers_share_variables_and_step_matches_engine():
         a = sess.run(acc_te)
         assert 0.0 <= a <= 1.0 or np.isnan(a)
     assert torch.equal(out_tr.engine.params, ref.params)
+
+
+@pytest.mark.gpu
+def test_graft_entry_smoke_passes():
+    """__graft_entry__.smoke() (what the driver runs before the bench) on this build: both modes against the oracle."""
+    import __graft_entry__ as entry
+    entry.smoke()
