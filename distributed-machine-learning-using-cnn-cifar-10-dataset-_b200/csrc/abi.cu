@@ -268,7 +268,13 @@ static int forward_impl(b200_handle h, const uint8_t* images, const int32_t* lab
   // last update may have changed the parameters).
   const bool fork = tc && !h->profiling;
   const bool fcimg = tc && fc_images_supported(c.batch, h->flat, c.f1);
-  if (tc) {
+  // With the fused conv1 kernel the three image kernels go BEHIND conv1 on the same stream as programmatic
+  // dependents that never wait: conv1 releases its dependents at its first instruction, so they run beside it on
+  // the SMs it leaves free, and conv2 -- an ordinary launch after them -- waits for all four.  No fork / join: the
+  // event join in front of conv2 cost ~1.5 us more than a plain kernel-to-kernel dependency.
+  const bool prep_behind_conv1 = fork && fused1;
+  if (fork) TRY(ensure_side_streams(h));
+  if (tc && !prep_behind_conv1) {
     if (fork) {
       TRY(ensure_side_streams(h));
       B200_CUDA_TRY(cudaEventRecord(h->ev_fork[0], st));
@@ -288,8 +294,19 @@ static int forward_impl(b200_handle h, const uint8_t* images, const int32_t* lab
     SITE("conv1_fwd", conv5x5_fwd_f32(x, h->P(P_W1), h->P(P_B1), conv1, c.batch, c.crop_h, c.crop_w, c.c_in, c.c1, 1, st));
     SITE("pool1_fwd", maxpool_fwd_f32(conv1, pool1, h->ptr<uint8_t>("arg1"), c.batch, c.crop_h, c.crop_w, c.c1, st));
   }
+  if (prep_behind_conv1) {
+    g_pdl_next = true;
+    TRY(pack_conv_weights(h->P(P_W2), h->ptr<void>("w2_packed"), c.c1, c.c2, st));
+    g_pdl_next = true;
+    TRY(fc_tail_prepare_w2(h->P(P_FW2), h->ptr<void>("tail_scratch"), c.batch, c.f1, c.f2, c.n_cls, st));
+    if (fcimg) {
+      g_pdl_next = true;
+      TRY(pack_fc_weights(h->P(P_FW1), h->ptr<void>("w1_img"), h->flat, c.f1, st));
+    }
+    g_pdl_next = false;
+  }
   if (tc) {
-    if (fork) B200_CUDA_TRY(cudaStreamWaitEvent(st, h->ev_join[0], 0));
+    if (fork && !prep_behind_conv1) B200_CUDA_TRY(cudaStreamWaitEvent(st, h->ev_join[0], 0));
     // conv2 + bias + ReLU + pool2 in one kernel; the un-pooled activations are not needed again (the
     // backward gathers through pool2 / arg2)
     SITE("conv2_pool2_fwd", conv5x5_pool_fwd_tc(pool1, h->ptr<void>("w2_packed"), h->P(P_B2), nullptr, pool2,

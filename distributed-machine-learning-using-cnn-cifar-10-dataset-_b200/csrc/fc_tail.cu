@@ -71,6 +71,7 @@ __device__ __forceinline__ void stage_tile(float* dst, const float* src, int nfl
 // row (conflict-free fragment loads); fetched by the rows kernel with bulk copies
 __global__ void w2_to_bf16_kernel(const float* __restrict__ w2, __nv_bfloat16* __restrict__ out, int F1, int F2) {
   B200_TRACE_SCOPE(TR_W2IMG);
+  pdl_launch_dependents();
   const int WS = F2 + 8;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < F1 * WS; i += gridDim.x * blockDim.x) {
     const int k = i / WS, n = i - k * WS;
@@ -584,8 +585,7 @@ int64_t fc_tail_scratch_bytes(int B, int F1, int F2, int NC) {
 // the critical path, and then call fc_tail(..., w2_image_ready = true)
 int fc_tail_prepare_w2(const float* w2, void* scratch, int B, int F1, int F2, int NC, cudaStream_t st) {
   __nv_bfloat16* w2b = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<char*>(scratch) + part_bytes(B, F1, F2, NC));
-  w2_to_bf16_kernel<<<cdiv(F1 * (F2 + 8), 256), 256, 0, st>>>(w2, w2b, F1, F2);
-  B200_LAUNCH_CHECK();
+  B200_CUDA_TRY(launch_kernel(w2_to_bf16_kernel, dim3(cdiv(F1 * (F2 + 8), 256)), dim3(256), 0, st, w2, w2b, F1, F2));
   return B200_OK;
 }
 

@@ -481,6 +481,7 @@ __global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
 // K-major (groups along K) it is the input-gradient B operand of tap 24-tap.  One packed copy serves both.
 __global__ void pack_conv_weights_kernel(const float* __restrict__ w, uint8_t* __restrict__ wp, int Cin, int Cout) {
   B200_TRACE_SCOPE(TR_PACK);
+  pdl_launch_dependents();      // nothing downstream waits on this kernel programmatically: the next one may start at once
   const int gstride = Cin * 16 + 16, img = (Cout / 8) * gstride;
   const int total = 25 * Cin * (Cout / 8);
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
@@ -873,8 +874,8 @@ int pack_conv_weights(const float* w, void* wp, int Cin, int Cout, cudaStream_t 
     B200_CUDA_TRY(prefer_max_shared(reduce_partials_tc));
     carve = true;
   }
-  pack_conv_weights_kernel<<<std::min(cdiv(total, 256), 2 * kNumSMs), 256, 0, st>>>(w, (uint8_t*)wp, Cin, Cout);
-  B200_LAUNCH_CHECK();
+  B200_CUDA_TRY(launch_kernel(pack_conv_weights_kernel, dim3(std::min(cdiv(total, 256), 2 * kNumSMs)), dim3(256), 0, st, w,
+                              (uint8_t*)wp, Cin, Cout));
   return B200_OK;
 }
 int conv5x5_fwd_tc(const float* x, const void* wp, const float* bias, float* y, int B, int H, int W, int Cin,

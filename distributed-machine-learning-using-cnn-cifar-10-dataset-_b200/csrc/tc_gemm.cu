@@ -395,6 +395,7 @@ int fc_bwd_tc(const float* x, const float* w, const float* dy, float* dx, float*
 // (B K-major with k = n_out: chunk = n_out/8, rows = k_feat) alike.  Rebuilt once per step on a side stream.
 namespace {
 __global__ void pack_fc_weights_kernel(const float* __restrict__ w, uint4* __restrict__ img, int K, int N) {
+  pdl_launch_dependents();
   const int ng = N / 8;
   for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < K * ng; idx += gridDim.x * blockDim.x) {
     const int g8 = idx % ng, k = idx / ng;                       // neighbouring threads read neighbouring 32 bytes
@@ -407,8 +408,8 @@ int64_t fc_weight_image_bytes(int K, int N) { return (int64_t)K * N * 2; }
 int pack_fc_weights(const float* w, void* img, int K, int N, cudaStream_t st) {
   B200_REQUIRE(K > 0 && N > 0 && N % 8 == 0 && ((uintptr_t)w & 15) == 0 && ((uintptr_t)img & 15) == 0,
                "pack_fc_weights: bad shape / alignment");
-  pack_fc_weights_kernel<<<std::min(cdiv((int64_t)K * (N / 8), 256), 4 * kNumSMs), 256, 0, st>>>(w, (uint4*)img, K, N);
-  B200_LAUNCH_CHECK();
+  B200_CUDA_TRY(launch_kernel(pack_fc_weights_kernel, dim3(std::min(cdiv((int64_t)K * (N / 8), 256), 4 * kNumSMs)), dim3(256), 0,
+                              st, w, (uint4*)img, K, N));
   return B200_OK;
 }
 bool fc_images_supported(int Bt, int K, int N) { return Bt % 64 == 0 && K % 128 == 0 && N % 64 == 0; }
