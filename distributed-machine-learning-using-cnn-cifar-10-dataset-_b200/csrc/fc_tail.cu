@@ -227,8 +227,14 @@ __global__ void __launch_bounds__(RT) fc_tail_rows_kernel(TailArgs a) {
         } else {
           v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
-        *reinterpret_cast<uint2*>(xb + rr[u] * XS + 4 * kk[u]) =
-            make_uint2(pack_bf16x2(v[u].x, v[u].y), pack_bf16x2(v[u].z, v[u].w));
+        // (a positive fp32 value too small for bf16 is stored as the smallest bf16 subnormal, not 0: the ReluGrad mask
+        //  of the dfull1 product reads this copy, and `copy > 0` must mean `full1 > 0` exactly)
+        uint2 pk = make_uint2(pack_bf16x2(v[u].x, v[u].y), pack_bf16x2(v[u].z, v[u].w));
+        if (v[u].x > 0.f && (pk.x & 0xffffu) == 0u) pk.x |= 1u;
+        if (v[u].y > 0.f && (pk.x >> 16) == 0u) pk.x |= 0x10000u;
+        if (v[u].z > 0.f && (pk.y & 0xffffu) == 0u) pk.y |= 1u;
+        if (v[u].w > 0.f && (pk.y >> 16) == 0u) pk.y |= 0x10000u;
+        *reinterpret_cast<uint2*>(xb + rr[u] * XS + 4 * kk[u]) = pk;
       }
     }
   }
@@ -371,6 +377,10 @@ __global__ void __launch_bounds__(RT) fc_tail_rows_kernel(TailArgs a) {
     float colsum = 0.f;
 #pragma unroll
     for (int r = 0; r < RM; ++r) {
+      if (r >= a.R) {            // (uniform) rows of the MMA tile that carry no batch row: dfull2 = 0
+        d2b[r * DS + tid] = __float2bfloat16(0.f);
+        continue;
+      }
       const float f2v = f2s[r * a.F2 + tid];
       float dv[kMaxCls];
 #pragma unroll
@@ -430,11 +440,11 @@ __global__ void __launch_bounds__(RT) fc_tail_rows_kernel(TailArgs a) {
         const int j = min(jb + warp + 8 * i, nt - 1);
         // B[k = n2][n = k1] = W2[k1][n2]: rows k1 of the image, 8 consecutive n2 per 16-byte row piece
         wr[i] = tc::smem_u32(wb) + (uint32_t)((j * 8 + (lane & 7)) * WS + (lane >> 3) * 8) * 2;
-        // the ReLU mask: full1 as this CTA wrote it above (ordinary loads, ordered by the barriers)
         m0[i] = m1[i] = make_float2(0.f, 0.f);
-        if (g < nr) m0[i] = *reinterpret_cast<const float2*>(a.full1 + (size_t)(r0 + g) * a.F1 + j * 8 + 2 * t);
+        // (the bf16 copy in shared memory has full1's signs: no trip to L2 for values this CTA wrote a moment ago)
+        if (g < nr) m0[i] = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(xb + g * XS + j * 8 + 2 * t));
         if (RM == 16 && g + 8 < nr)
-          m1[i] = *reinterpret_cast<const float2*>(a.full1 + (size_t)(r0 + g + 8) * a.F1 + j * 8 + 2 * t);
+          m1[i] = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(xb + (g + 8) * XS + j * 8 + 2 * t));
       }
       uint32_t al0[4], ah0[4], al1[4], ah1[4], b0[T2][4], b1[T2][4];
       auto load = [&](int kk, uint32_t (&al)[4], uint32_t (&ah)[4], uint32_t (&b)[T2][4]) {
