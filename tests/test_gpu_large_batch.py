@@ -1,0 +1,249 @@
+"""BASELINE.json config 4 (batch 512 / 1024 / 4096 per GPU) parity, through the C ABI.
+
+The kernels change shape with the batch: from 591 images on, conv2's input-gradient kernels put two
+images into one CTA's strip (pick_ipc in csrc/tc_conv.cu), the last CTA of an odd batch holds one image
+and an empty slot, split-K / split-batch factors of the filter and FC gradients grow, and grids exceed
+one wave of the 148 SMs many times over.  So every size gets:
+  * kernel-level checks of the tcgen05 conv kernels at batches that reach the multi-image strip,
+    including an odd remainder (TIGHT against the oracle on bf16-rounded operands);
+  * the whole step (fp32 validation mode and bf16 mode) against the fp64 oracle.  The oracle is run
+    in chunks of <= 512 images -- the batch mean of the loss and of every gradient is the weighted mean
+    over chunks, an identity of the arithmetic (cifar10cnn.py:156 reduce_mean), so nothing is
+    approximated -- which keeps its im2col temporaries at a few hundred MB;
+  * a size-independent property: the batch-4096 gradient equals the mean of the thirty-two
+    batch-128 gradients computed by the (separately tested) batch-128 path on the same records.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+import b200cnn
+from b200cnn import _lib
+from oracle import ref_numpy as rn
+
+pytestmark = pytest.mark.gpu
+TIGHT, LOOSE = 2e-5, 1e-2
+RTOL_F32 = 1e-5
+CHUNK = 512
+
+
+def dev(a):
+    return torch.as_tensor(np.ascontiguousarray(a)).cuda()
+
+
+def bf16_round(a):
+    return torch.as_tensor(np.asarray(a, np.float32)).to(torch.bfloat16).to(torch.float64).numpy()
+
+
+def relerr(got, want):
+    want = np.asarray(want, np.float64)
+    return np.abs(np.asarray(got, np.float64) - want).max() / (np.abs(want).max() + 1e-30)
+
+
+def stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+@pytest.fixture(scope="module")
+def lib():
+    return _lib.load()
+
+
+def pack_filter(lib, wd, cin, cout):
+    nb = C.c_int64()
+    _lib.check(lib.b200_conv5x5_packed_bytes(cin, cout, C.byref(nb)))
+    wp = torch.full((nb.value,), 0x7f, dtype=torch.uint8, device="cuda")
+    _lib.check(lib.b200_conv5x5_pack_weights(wd.data_ptr(), wp.data_ptr(), cin, cout, stream()))
+    return wp
+
+
+def chunks(B):
+    return [(s, min(B, s + CHUNK)) for s in range(0, B, CHUNK)]
+
+
+# ---- kernel level: batches that reach the two-images-per-CTA strip -------------------------------------
+@pytest.mark.parametrize("B", [640, 1281])
+def test_conv2_kernels_multi_image_strip(lib, B):
+    """forward (no pool), input gradient, and input gradient fed by the pooled gradient (MaxPoolGrad x
+    ReluGrad gathered in the kernel, bias gradient, dense dY copy) at batches where pick_ipc packs
+    several images per CTA; 1281 leaves the last CTA half empty."""
+    H = W = 12
+    Cc = 64
+    rng = np.random.default_rng(91)
+    x = np.maximum(rng.normal(size=(B, H, W, Cc)), 0).astype(np.float32)
+    w = (rng.normal(size=(5, 5, Cc, Cc)) * 0.05).astype(np.float32)
+    b = (rng.normal(size=(Cc,)) * 0.3).astype(np.float32)
+    xd, wd, bd = dev(x), dev(w), dev(b)
+    wp = pack_filter(lib, wd, Cc, Cc)
+    xr, wr = bf16_round(x), bf16_round(w)
+    y = torch.full((B, H, W, Cc), float("nan"), device="cuda")
+    _lib.check(lib.b200_conv5x5_fwd_bf16(xd.data_ptr(), wp.data_ptr(), bd.data_ptr(), y.data_ptr(), B, H, W, Cc, Cc, 1,
+                                         stream()))
+    torch.cuda.synchronize()
+    yh = y.cpu().numpy()
+    for s, e in chunks(B):
+        assert relerr(yh[s:e], np.maximum(rn.conv2d_same(xr[s:e], wr) + b, 0)) <= TIGHT, (s, e)
+
+    dy = (rng.normal(size=(B, H, W, Cc)) * (rng.random(size=(B, H, W, Cc)) < 0.3)).astype(np.float32)
+    dyd, dyr = dev(dy), bf16_round(dy)
+    dx = torch.full((B, H, W, Cc), float("nan"), device="cuda")
+    _lib.check(lib.b200_conv5x5_dgrad_bf16(dyd.data_ptr(), wp.data_ptr(), dx.data_ptr(), B, H, W, Cc, Cc, stream()))
+    torch.cuda.synchronize()
+    dxh = dx.cpu().numpy()
+    for s, e in chunks(B):
+        assert relerr(dxh[s:e], rn.conv2d_same_grad_input(dyr[s:e], wr)) <= TIGHT, (s, e)
+
+    conv = np.maximum(rng.normal(size=(B, H, W, Cc)), 0).astype(np.float32)
+    pool, arg = rn.maxpool_3x3s2_same(conv)
+    dpool = rng.normal(size=pool.shape).astype(np.float32)
+    dconv32 = rn.maxpool_3x3s2_same_grad(dpool, arg, (H, W)) * (conv > 0)      # fp32, same (kh,kw) order as the kernel
+    dconv_r = bf16_round(dconv32)
+    dpd, pld, ard = dev(dpool), dev(pool.astype(np.float32)), dev(arg)
+    dx2 = torch.full((B, H, W, Cc), float("nan"), device="cuda")
+    db = torch.zeros(Cc, device="cuda")
+    _lib.check(lib.b200_conv5x5_dgrad_pool_bf16(dpd.data_ptr(), pld.data_ptr(), ard.data_ptr(), wp.data_ptr(),
+                                                dx2.data_ptr(), db.data_ptr(), B, H, W, Cc, Cc, stream()))
+    torch.cuda.synchronize()
+    dx2h = dx2.cpu().numpy()
+    for s, e in chunks(B):
+        assert relerr(dx2h[s:e], rn.conv2d_same_grad_input(dconv_r[s:e], wr)) <= TIGHT, (s, e)
+    assert relerr(db.cpu().numpy(), dconv32.astype(np.float64).sum((0, 1, 2))) <= 1e-5
+
+    # filter gradient with many images per CTA (fixed-order partial sums)
+    nb = C.c_int64()
+    _lib.check(lib.b200_conv5x5_wgrad_bf16_scratch_bytes(B, C.byref(nb)))
+    scr = torch.empty(nb.value, dtype=torch.uint8, device="cuda")
+    dw = torch.full((5, 5, Cc, Cc), float("nan"), device="cuda")
+    _lib.check(lib.b200_conv5x5_wgrad_bf16(xd.data_ptr(), dyd.data_ptr(), dw.data_ptr(), scr.data_ptr(), nb.value, B, H, W,
+                                           Cc, Cc, stream()))
+    torch.cuda.synchronize()
+    want = sum(rn.conv2d_same_grad_filter(xr[s:e], dyr[s:e]) for s, e in chunks(B))
+    assert relerr(dw.cpu().numpy(), want) <= TIGHT
+
+
+# ---- whole step ------------------------------------------------------------------------------------------
+def make_batch(B, kind, seed):
+    rng = np.random.default_rng(seed)
+    if kind == "u8":
+        img = rng.integers(0, 256, (B, 3, 32, 32), dtype=np.uint8)
+    else:
+        img = np.clip(np.rint(rng.normal(8.0, 2.5, (B, 3, 32, 32))), 0, 255).astype(np.uint8)
+    return img, rng.integers(0, 10, (B,)).astype(np.int32)
+
+
+def oracle_forward_chunked(params, img, lab):
+    """fp64 oracle forward per chunk -> list of activation dicts (one per chunk)."""
+    out = []
+    for s, e in chunks(img.shape[0]):
+        out.append(rn.forward(params, rn.crop_cast(img[s:e]), lab[s:e]))
+    return out
+
+
+def oracle_backward_on_gpu_forward_chunked(e, params, lab, fused, B):
+    """The oracle's backward pass evaluated on the GPU's own forward tensors (see
+    test_gpu_parity._oracle_backward_on_gpu_forward for why), chunk by chunk; the gradient of the batch
+    mean is the chunk-size-weighted mean of the chunk gradients."""
+    c = e.cfg
+    h1, h2 = (c.crop_h + 1) // 2, ((c.crop_h + 1) // 2 + 1) // 2
+    shp = {"conv1": (B, c.crop_h, c.crop_w, c.c1), "pool1": (B, h1, h1, c.c1), "conv2": (B, h1, h1, c.c2),
+           "pool2": (B, h2, h2, c.c2), "full1": (B, c.f1), "full2": (B, c.f2), "logits": (B, c.n_cls)}
+    names = ("pool1", "pool2", "full1", "full2", "logits") if fused else tuple(shp)
+    host = {n: e.tensor(n).cpu().numpy().reshape(shp[n]) for n in names}
+    for k in ("1", "2"):
+        host["arg" + k] = e.tensor("arg" + k).cpu().numpy().reshape(shp["pool" + k])
+    p64 = {k: np.asarray(v, np.float64) for k, v in params.items()}
+    total = None
+    for s, t in chunks(B):
+        a = {n: host[n][s:t].astype(np.float64) for n in names}
+        a["x"] = rn.crop_cast(e._last_img[s:t])
+        for k in ("1", "2"):
+            a["arg" + k] = host["arg" + k][s:t]
+            if fused:      # only the sign of the conv output at the selected cells matters (= sign of the pooled value)
+                a["conv" + k] = rn.maxpool_3x3s2_same_grad(a["pool" + k], a["arg" + k], shp["conv" + k][1:3])
+            else:
+                y, arg = rn.maxpool_3x3s2_same(a["conv" + k])
+                np.testing.assert_array_equal(a["arg" + k], arg)
+                np.testing.assert_array_equal(a["pool" + k], y)
+        a["flat"] = a["pool2"].reshape(t - s, -1)
+        a["loss"], a["loss_rows"], a["xent_back"] = rn.softmax_xent(a["logits"], lab[s:t])
+        g = rn.backward(p64, a)
+        wgt = (t - s) / B
+        total = {k: v * wgt for k, v in g.items()} if total is None else {k: total[k] + g[k] * wgt for k in g}
+    return total
+
+
+@pytest.mark.parametrize("mode,B,kind", [("bf16", 512, "u8"), ("bf16", 1024, "soft"), ("bf16", 4096, "u8"),
+                                         ("bf16", 4096, "soft"), ("fp32", 512, "soft"), ("fp32", 1024, "u8"),
+                                         ("fp32", 4096, "soft")])
+def test_full_step_large_batch(mode, B, kind):
+    img, lab = make_batch(B, kind, seed=100 + B)
+    params = rn.init_params(0)
+    acts = oracle_forward_chunked(params, img, lab)
+    loss = sum(a["loss"] * a["x"].shape[0] for a in acts) / B
+    e = b200cnn.TrainStepEngine(batch=B, mode=mode)
+    e.load_params(params)
+    e._last_img = img
+    e.forward(dev(img), dev(lab))
+    e.backward()
+    torch.cuda.synchronize()
+    fwd_tol = LOOSE if mode == "bf16" else RTOL_F32
+    grad_tol = 2e-2 if mode == "bf16" else 2 * RTOL_F32
+    names = ("pool1", "pool2", "full1", "full2", "logits")
+    for name in names:
+        got = e.tensor(name).cpu().numpy().reshape(B, -1)
+        want = np.concatenate([a[name].reshape(a["x"].shape[0], -1) for a in acts])
+        assert relerr(got, want) <= fwd_tol, name
+    assert abs(float(e.loss()) - loss) <= (2e-2 if mode == "bf16" else RTOL_F32) * abs(loss)
+    logits = np.concatenate([a["logits"] for a in acts])
+    pred = np.concatenate([a["pred"] for a in acts])
+    srt = np.sort(logits, axis=1)
+    gap = 2 * LOOSE if mode == "bf16" else 1e-4
+    safe = (srt[:, -1] - srt[:, -2]) > gap * np.abs(logits).max()
+    safe |= (srt[:, -1] == 0)
+    np.testing.assert_array_equal(e.pred().cpu().numpy()[safe], pred[safe])
+    assert int(e.tensor("n_bad")) == 0
+    g = oracle_backward_on_gpu_forward_chunked(e, params, lab, fused=(mode == "bf16"), B=B)
+    got = e.get_grads()
+    for k in rn.PARAM_NAMES:
+        assert relerr(got[k], g[k]) <= grad_tol, (k, relerr(got[k], g[k]))
+    # the update (cifar10cnn.py:162-163) on top of those gradients
+    e.sgd_apply(0.1)
+    torch.cuda.synchronize()
+    newp = e.get_params()
+    for k in rn.PARAM_NAMES:
+        want = np.asarray(params[k], np.float64) - 0.1 * g[k]
+        assert relerr(newp[k], want) <= grad_tol, k
+
+
+def test_batch_4096_gradient_is_mean_of_batch_128_gradients():
+    """Size-independent property (reduce_mean, cifar10cnn.py:156): one batch-4096 step sees the same
+    records as thirty-two batch-128 steps from the same weights; loss and gradients are their means.
+    Both sides are this library (different grids, split factors and strip packing), so the bound is
+    accumulation-order noise plus bf16 rounding of differently-grouped partial sums."""
+    B, b = 4096, 128
+    img, lab = make_batch(B, "soft", seed=7)
+    params = rn.init_params(1)
+    big = b200cnn.TrainStepEngine(batch=B, mode="bf16")
+    small = b200cnn.TrainStepEngine(batch=b, mode="bf16")
+    big.load_params(params); small.load_params(params)
+    imgd, labd = dev(img), dev(lab)
+    big.forward_backward(imgd, labd)
+    acc = torch.zeros_like(small.grads, dtype=torch.float64)
+    loss = 0.0
+    logits = []
+    for s in range(0, B, b):
+        small.forward_backward(imgd[s:s + b].contiguous(), labd[s:s + b].contiguous())
+        acc += small.grads.double()
+        loss += float(small.loss())
+        logits.append(small.logits().clone())
+    torch.cuda.synchronize()
+    acc /= B // b
+    assert abs(float(big.loss()) - loss / (B // b)) <= 1e-5 * abs(loss / (B // b))
+    # per-image results do not depend on the batch they were computed in (same operands, same tap order per
+    # pixel up to the filter-row rotation): logits agree to fp32 accumulation noise
+    assert relerr(big.logits().cpu().numpy(), torch.cat(logits).cpu().numpy()) <= 1e-5
+    for i, k in enumerate(rn.PARAM_NAMES):
+        o, n = big.offsets[i], big.sizes[i]
+        assert relerr(big.grads[o:o + n].cpu().numpy(), acc[o:o + n].cpu().numpy()) <= 2e-3, k
