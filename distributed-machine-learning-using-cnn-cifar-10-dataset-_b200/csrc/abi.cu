@@ -377,6 +377,7 @@ static int backward_impl(b200_handle h, void* stream, const P2PCtx* px) {
     set_error("backward: call b200_forward first");
     return B200_E_STATE;
   }
+  h->forward_done = false;      // one backward per forward (buffers cleared by the forward are consumed here)
   cudaStream_t st = (cudaStream_t)stream;
   const b200_config& c = h->cfg;
   const bool tc = c.mode == B200_MODE_BF16;

@@ -51,6 +51,19 @@ inline cudaError_t prefer_max_shared(K kernel) {
   return cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
 }
 #endif
+// Function attributes (dynamic shared-memory limit, carve-out preference) are per DEVICE: a `static bool` guard would
+// set them on the first GPU a process touches only.  PerDeviceOnce::first() is true once per device ordinal (races
+// between host threads at worst set an attribute twice, which is harmless).
+struct PerDeviceOnce {
+  bool done[64] = {};
+  bool first() {
+    int d = 0;
+    if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= 64) return true;
+    if (done[d]) return false;
+    done[d] = true;
+    return true;
+  }
+};
 // The next launch through launch_kernel() on this host thread is made with programmatic stream serialization when
 // this flag is set (the step driver in abi.cu sets it in front of the launches it wants overlapped); it resets itself.
 extern thread_local bool g_pdl_next;

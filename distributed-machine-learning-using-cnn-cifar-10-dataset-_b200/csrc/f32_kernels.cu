@@ -524,8 +524,8 @@ int sgd_apply_f32(float* p, const float* g, int64_t n, float lr, float scale, cu
   B200_REQUIRE(((uintptr_t)p & 15) == 0 && ((uintptr_t)g & 15) == 0, "sgd_apply: pointers must be 16-byte aligned");
   if (n == 0) return B200_OK;
   int grid = (int)std::min<int64_t>((n / 4 + 255) / 256 + 1, kNumSMs * 4);
-  static bool carve = false;
-  if (!carve) { B200_CUDA_TRY(prefer_max_shared(sgd_kernel)); carve = true; }
+  static PerDeviceOnce carve;
+  if (carve.first()) B200_CUDA_TRY(prefer_max_shared(sgd_kernel));
   B200_CUDA_TRY(launch_kernel(sgd_kernel, dim3(grid), dim3(256), 0, st, p, g, n, lr * scale));
   B200_LAUNCH_CHECK();
   return B200_OK;

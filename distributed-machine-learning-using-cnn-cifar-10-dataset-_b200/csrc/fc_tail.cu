@@ -620,12 +620,11 @@ int fc_tail(const float* fc1_part, int n_part, const float* b1, float* full1, co
   const int RM = R <= 8 ? 8 : 16;              // rows of the MMA tile that carry batch rows
   const size_t smem = (size_t)tail_smem(RM, F1, F2, NC).total;
   B200_REQUIRE(smem <= 220 * 1024, "fc_tail: layer widths too large (%zu bytes of shared memory)", smem);
-  static bool grads_attr = false, rows_attr[2][5] = {};
-  if (!grads_attr) {
+  static PerDeviceOnce grads_attr, rows_attr[2][5];
+  if (grads_attr.first()) {
     B200_CUDA_TRY(cudaFuncSetAttribute(fc_tail_grads_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     B200_CUDA_TRY(prefer_max_shared(fc_tail_grads_kernel));
     B200_CUDA_TRY(prefer_max_shared(w2_to_bf16_kernel));
-    grads_attr = true;
   }
   const int t1 = cdiv(F2, 64);
   // overlap_producer: the kernel in front of this one on `st` produced fc1_part and allows its dependents to start
@@ -638,11 +637,9 @@ int fc_tail(const float* fc1_part, int n_part, const float* b1, float* full1, co
   cfg.attrs = attr; cfg.numAttrs = overlap_producer ? 1 : 0;
 #define B200_TAIL_LAUNCH(RM_, T1_)                                                                                   \
   do {                                                                                                                 \
-    if (!rows_attr[RM_ / 16][T1_]) {                                                                                   \
+    if (rows_attr[RM_ / 16][T1_].first())                                                                              \
       B200_CUDA_TRY(cudaFuncSetAttribute(fc_tail_rows_kernel<RM_, T1_>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
                                          220 * 1024));                                                                 \
-      rows_attr[RM_ / 16][T1_] = true;                                                                                 \
-    }                                                                                                                  \
     B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, fc_tail_rows_kernel<RM_, T1_>, a));                                         \
   } while (0)
   if (RM == 8) {

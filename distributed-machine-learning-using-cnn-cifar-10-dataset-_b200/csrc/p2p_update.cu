@@ -15,6 +15,8 @@
 //
 // Buffers (gradients, parameters, pads) must be peer-mapped symmetric allocations of the same size on all
 // ranks; torch.distributed._symmetric_memory provides them (plumbing), see exchange.P2PExchange.
+#include <stdlib.h>
+
 #include <algorithm>
 
 #include "launch.h"
@@ -33,6 +35,7 @@ struct P2PArgs {
   int rank, world;
   int64_t total;                    // floats, divisible by 4 * world
   float step;                       // lr * scale
+  long long timeout_cycles;         // bound of one flag wait (see flag_timeout_cycles)
 };
 
 __device__ __forceinline__ void st_flag(uint32_t* p, uint32_t v) {
@@ -43,11 +46,14 @@ __device__ __forceinline__ uint32_t ld_flag(const uint32_t* p) {
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
-// bounded: a lost peer must fault this launch, not hang the GPU
-__device__ __forceinline__ void wait_flag(const uint32_t* p, uint32_t epoch) {
+// bounded: a lost peer must fault this launch, not hang the GPU.  The bound has to outlast anything that may
+// legitimately hold a peer back on the host between two steps (a checkpoint write, an evaluation pass, a lazy build,
+// a slow batch): B200_P2P_TIMEOUT_S seconds, default 120 (include/b200cnn.h).  Past it every waiting rank traps,
+// which leaves a sticky error on its context -- the job is lost either way, but the box is not.
+__device__ __forceinline__ void wait_flag(const uint32_t* p, uint32_t epoch, long long timeout_cycles) {
   const long long t0 = clock64();
   while ((int32_t)(ld_flag(p) - epoch) < 0) {
-    if (clock64() - t0 > 8000000000ll) {
+    if (clock64() - t0 > timeout_cycles) {
       printf("b200cnn: peer flag wait timed out (block %d thread %d)\n", (int)blockIdx.x, (int)threadIdx.x);
       __trap();
     }
@@ -75,7 +81,7 @@ __global__ void __launch_bounds__(512) p2p_allreduce_sgd_kernel(P2PArgs a) {
     __threadfence_system();
     st_flag(a.pads[tid] + a.rank, epoch);         // "rank `a.rank` is ready", written into peer tid's pad
   }
-  if (tid < a.world) wait_flag(a.pads[a.rank] + tid, epoch);
+  if (tid < a.world) wait_flag(a.pads[a.rank] + tid, epoch, a.timeout_cycles);
   __syncthreads();
   // ---- 1-3: reduce my shard, update, broadcast -----------------------------------------------------------
   const int64_t shard4 = a.total / 4 / a.world;
@@ -142,11 +148,23 @@ __global__ void __launch_bounds__(512) p2p_allreduce_sgd_kernel(P2PArgs a) {
     if (tid < a.world) {
       __threadfence_system();
       st_flag(a.pads[tid] + 8 + a.rank, epoch);
-      wait_flag(a.pads[a.rank] + 8 + tid, epoch);
+      wait_flag(a.pads[a.rank] + 8 + tid, epoch, a.timeout_cycles);
     }
     __syncthreads();
     if (tid == 0) { a.state[1] = 0; a.state[0] = epoch; }
   }
+}
+long long flag_timeout_cycles() {
+  static long long cycles = 0;
+  if (!cycles) {
+    double sec = 120.0;
+    if (const char* e = getenv("B200_P2P_TIMEOUT_S")) {
+      const double v = atof(e);
+      if (v > 0.0) sec = v;
+    }
+    cycles = (long long)(sec * 1.9e9);      // clock64 ticks at ~1.9 GHz
+  }
+  return cycles;
 }
 }  // namespace
 
@@ -169,6 +187,7 @@ int p2p_allreduce_sgd(const void* const* peer_grads, void* const* peer_params, v
   a.mc_grads = mc_grads ? (const float*)mc_grads + offset : nullptr;
   a.mc_params = mc_params ? (float*)mc_params + offset : nullptr;
   a.state = state + 2 * channel; a.rank = rank; a.world = world; a.total = total; a.step = lr * scale;
+  a.timeout_cycles = flag_timeout_cycles();
   const int64_t shard4 = total / 4 / world;
   // (with the multicast mapping a thread handles four 16-byte pieces per sweep)
   const int64_t per_cta = 512 * ((mc_grads && mc_params) ? 4 : 1);

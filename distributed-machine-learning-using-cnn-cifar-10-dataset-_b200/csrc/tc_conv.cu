@@ -868,11 +868,10 @@ int pack_conv_weights(const float* w, void* wp, int Cin, int Cout, cudaStream_t 
   B200_REQUIRE(Cin % 8 == 0 && Cout % 8 == 0 && Cin > 0 && Cout > 0, "pack_conv_weights: channels must be multiples of 8");
   B200_REQUIRE(((uintptr_t)w & 15) == 0 && ((uintptr_t)wp & 15) == 0, "pack_conv_weights: pointers must be 16-byte aligned");
   const int total = 25 * Cin * (Cout / 8);
-  static bool carve = false;
-  if (!carve) {
+  static PerDeviceOnce carve;
+  if (carve.first()) {
     B200_CUDA_TRY(prefer_max_shared(pack_conv_weights_kernel));
     B200_CUDA_TRY(prefer_max_shared(reduce_partials_tc));
-    carve = true;
   }
   B200_CUDA_TRY(launch_kernel(pack_conv_weights_kernel, dim3(std::min(cdiv(total, 256), 2 * kNumSMs)), dim3(256), 0, st, w,
                               (uint8_t*)wp, Cin, Cout));
@@ -938,12 +937,10 @@ static int launch_wgrad(const float* x, const float* dy, const PoolGradSrc* pg, 
   const int nbuf = (2 * buf_bytes + 256 + extra <= 227 * 1024) ? 2 : 1;
   const int smem = nbuf * buf_bytes + 256 + extra;
   B200_REQUIRE(smem <= 227 * 1024, "conv5x5_wgrad_tc: image %dx%d needs %d bytes of shared memory", H, W, smem);
-  static bool attr = false;
-  if (!attr) {
+  static PerDeviceOnce attr;
+  if (attr.first())
     B200_CUDA_TRY(cudaFuncSetAttribute(conv5x5_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        227 * 1024));
-    attr = true;
-  }
   int S = wgrad_splits_tc(B);
   int per = cdiv(B, S);
   S = cdiv(B, per);

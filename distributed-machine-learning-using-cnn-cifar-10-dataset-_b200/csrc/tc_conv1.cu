@@ -278,11 +278,9 @@ int conv1_pool_fwd_tc(const uint8_t* img, const float* w, const float* bias, flo
   B200_REQUIRE(conv1_tc_supported(H, W, 3, 64), "conv1_pool_fwd_tc: crop %dx%d does not fit one CTA", H, W);
   C1Geom g = make_c1geom(B, ih, iw, H, W);
   const int smem = ((g.npix * 16 + 127) & ~127) + 26 * kWLbo + 64 + H * W * kConvRow * 4 + 256;
-  static bool attr = false;
-  if (!attr) {
+  static PerDeviceOnce attr;
+  if (attr.first())
     B200_CUDA_TRY(cudaFuncSetAttribute(conv1_pool_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    attr = true;
-  }
   Conv1FwdArgs a{img, w, bias, pool, arg, reinterpret_cast<__nv_bfloat16*>(pool_bf16), conv_dbg, g, g_conv1_timeline};
   conv1_pool_fwd_kernel<<<B, 352, smem, st>>>(a);
   B200_LAUNCH_CHECK();
@@ -501,11 +499,9 @@ int conv1_wgrad_tc(const uint8_t* img, const float* dpool, const float* pool, co
   C1Geom g = make_c1geom(B, ih, iw, H, W);
   const size_t smem = conv1_wgrad_smem(g);
   B200_REQUIRE(smem <= 227 * 1024, "conv1_wgrad_tc: crop %dx%d needs %zu bytes of shared memory", H, W, smem);
-  static bool attr = false;
-  if (!attr) {
+  static PerDeviceOnce attr;
+  if (attr.first())
     B200_CUDA_TRY(cudaFuncSetAttribute(conv1_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    attr = true;
-  }
   const int S = conv1_wgrad_ctas(B);
   if (!prezeroed) {       // the kernel accumulates with atomics
     B200_CUDA_TRY(cudaMemsetAsync(dw, 0, 75 * 64 * sizeof(float), st));

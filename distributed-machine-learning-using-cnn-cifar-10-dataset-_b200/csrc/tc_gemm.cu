@@ -314,11 +314,8 @@ int launch(const GemmArgs& g_in, cudaStream_t st) {
   g.timeline = g_gemm_timeline;
   using S = Smem<BN>;
   auto kern = tc_gemm_kernel<BN, A_MN, B_MN, TA, TB>;
-  static bool attr_done = false;      // per instantiation; attribute is per-function, device-wide
-  if (!attr_done) {
-    B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
-    attr_done = true;
-  }
+  static PerDeviceOnce attr_done;      // per instantiation and per device
+  if (attr_done.first()) B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
   dim3 grid(cdiv(g.N, BN), cdiv(g.M, BM), cdiv(g.K, g.k_per_split));
   B200_CUDA_TRY(launch_kernel(kern, grid, dim3(288), (size_t)S::TOTAL, st, g));
   B200_LAUNCH_CHECK();

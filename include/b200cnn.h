@@ -80,7 +80,8 @@ int b200_forward(b200_handle h, const uint8_t* images, const int32_t* labels, vo
 /* the gradient graph built by minimize() (:162-163); fills the bound gradient buffer.  The `images`
  * buffer given to the last b200_forward must still be intact (the conv1 gradient re-reads the records).
  * In bf16 mode independent branches run on two internal side streams forked from / joined to `stream` with
- * events; those streams are created by the first call, which must therefore happen before any capture. */
+ * events; those streams are created by the first call, which must therefore happen before any capture.
+ * One backward per forward: a second b200_backward without a new b200_forward returns B200_E_STATE. */
 int b200_backward(b200_handle h, void* stream);
 /* b200_forward + b200_backward as one call -- what sess.run(train_op) makes of :147-163 before the update.  Same
  * results as the two calls; knowing that the backward follows lets the bf16 path leave the FC2/FC3 parameter
@@ -97,7 +98,10 @@ int b200_sgd_apply(b200_handle h, float lr, float grad_scale, void* stream);
  * allocations of the padded parameter size (pads: >= 64 B of zero-initialised uint32 flags per worker).
  * mc_grads / mc_params: NVSwitch multicast mappings of the same buffers, or NULL (then plain peer loads /
  * stores).  state: 8 zero-initialised bytes of local device memory.  Every worker must launch it once per
- * step; the kernels wait for one another (bounded), so all `world` GPUs must be running. */
+ * step; the kernels wait for one another, so all `world` GPUs must be running.  The wait is bounded: a worker
+ * that has not arrived after B200_P2P_TIMEOUT_S seconds (environment variable, read once; default 120) makes every
+ * waiting kernel trap, which leaves a sticky error on those CUDA contexts -- set it above the longest pause a
+ * worker may take between two steps (checkpoint, evaluation, data stall). */
 int b200_p2p_sgd_apply(b200_handle h, const void* const* peer_grads, void* const* peer_params, void* const* peer_pads,
                        const void* mc_grads, void* mc_params, uint32_t* state, int32_t rank, int32_t world, float lr,
                        float grad_scale, void* stream);

@@ -398,6 +398,10 @@ def test_bad_inputs_raise():
     e2 = _engine(8)
     with pytest.raises(_lib.B200Error):
         e2.backward()                                  # backward before forward
+    e2.forward(torch.zeros(8, 3, 32, 32, dtype=torch.uint8, device="cuda"), torch.zeros(8, dtype=torch.int32, device="cuda"))
+    e2.backward()
+    with pytest.raises(_lib.B200Error):
+        e2.backward()                                  # one backward per forward
 
 
 @pytest.mark.parametrize("B", [128, 6, 2048])

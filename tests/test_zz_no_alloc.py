@@ -31,9 +31,17 @@ def _run_pair(lib, B, K, N, mask, seed):
     got = [torch.full(s, float("nan"), device="cuda") for s in ((B, K), (K, N), (N,))]
     _lib.check(lib.b200_fc_bwd_f32(x.data_ptr(), w.data_ptr(), dy.data_ptr(), ref[0].data_ptr(), ref[1].data_ptr(),
                                    ref[2].data_ptr(), scr.data_ptr(), nb.value, B, K, N, mask, st))
+    # "allocates nothing" is observed, not taken on trust: the driver's free-memory figure is read with every input
+    # and output already allocated, and again after the call has run; the first call in a process also covers the
+    # once-per-device address lookup.  (Other tests' tensors sit in torch's cache; nothing here frees or allocates
+    # between the two readings.)
+    torch.cuda.synchronize()
+    free_before, _ = torch.cuda.mem_get_info()
     _lib.check(lib.b200_fc_bwd_f32_static(x.data_ptr(), w.data_ptr(), dy.data_ptr(), got[0].data_ptr(),
                                           got[1].data_ptr(), got[2].data_ptr(), B, K, N, mask, st))
     torch.cuda.synchronize()
+    free_after, _ = torch.cuda.mem_get_info()
+    assert free_after == free_before, (free_before, free_after)
     for name, r, g in zip(("dx", "dw", "db"), ref, got):
         r, g = r.cpu().numpy().astype(np.float64), g.cpu().numpy().astype(np.float64)
         assert np.isfinite(g).all(), name
