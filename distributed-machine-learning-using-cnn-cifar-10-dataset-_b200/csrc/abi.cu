@@ -696,6 +696,11 @@ int b200_debug_conv_timeline(int64_t* device_buf8) {
   gemm_set_timeline(reinterpret_cast<long long*>(device_buf8));
   return B200_OK;
 }
+int b200_debug_conv_variant(int32_t variant) {
+  B200_REQUIRE(variant >= -1 && variant <= 1, "debug_conv_variant: -1 (automatic), 0 or 1");
+  conv5x5_force_variant(variant);
+  return B200_OK;
+}
 int b200_debug_trace(uint64_t* device_buf) {
 #ifdef B200_TRACE
   unsigned long long* p = reinterpret_cast<unsigned long long*>(device_buf);
@@ -727,6 +732,12 @@ int b200_conv5x5_pool_fwd_bf16(const float* x, const void* w_packed, const float
                                void* stream) {
   B200_REQUIRE(x && w_packed && bias && pool && arg, "null pointer");
   return conv5x5_pool_fwd_tc(x, w_packed, bias, y, pool, arg, batch, h, wd, c_in, c_out, (cudaStream_t)stream);
+}
+int b200_conv5x5_pool_fwd_bf16x(const void* x_bf16, const void* w_packed, const float* bias, float* y, float* pool,
+                                uint8_t* arg, int32_t batch, int32_t h, int32_t wd, int32_t c_in, int32_t c_out,
+                                void* stream) {
+  B200_REQUIRE(x_bf16 && w_packed && bias && pool && arg, "null pointer");
+  return conv5x5_pool_fwd_tc(nullptr, w_packed, bias, y, pool, arg, batch, h, wd, c_in, c_out, (cudaStream_t)stream, x_bf16);
 }
 int b200_conv5x5_dgrad_bf16(const float* dy, const void* w_packed, float* dx, int32_t batch, int32_t h, int32_t wd,
                             int32_t c_in, int32_t c_out, void* stream) {

@@ -29,6 +29,8 @@ void set_error(const char* fmt, ...);
     }                                           \
   } while (0)
 
+#define B200_TRY(expr) do { int rc__ = (expr); if (rc__) return rc__; } while (0)
+
 static inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
 static inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 

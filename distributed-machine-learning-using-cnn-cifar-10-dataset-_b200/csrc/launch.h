@@ -39,6 +39,7 @@ int fc_dx_tc(const float* x, const float* w, const float* dy, float* dx, int B, 
              cudaStream_t st);
 // wp: the filter packed once per step by pack_conv_weights (conv5x5_packed_bytes bytes)
 void conv5x5_set_timeline(long long* dev_buf);   // diagnostics: CTA 0 of conv5x5_tc_kernel stamps clock64 per phase
+void conv5x5_force_variant(int v);               // tests: 0 = one CTA per SM, 1 = two per SM (where the shape allows), -1 = automatic
 int64_t conv5x5_packed_bytes(int Cin, int Cout);
 int pack_conv_weights(const float* w, void* wp, int Cin, int Cout, cudaStream_t st);
 int conv5x5_fwd_tc(const float* x, const void* wp, const float* bias, float* y, int B, int H, int W, int Cin,

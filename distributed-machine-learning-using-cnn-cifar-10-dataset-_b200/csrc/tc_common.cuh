@@ -69,6 +69,17 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst_smem, const void* src, uin
                : "memory");
 }
 
+// ---- tensor-map (tiled) TMA load global -> shared, 5-D box; coordinates innermost first, may be negative / out of
+// range: elements outside the tensor arrive as zeros.  `tmap` points at a CUtensorMap in kernel-parameter space
+// (a member of a __grid_constant__ argument).  Only ever used on tensors in this GPU's own memory.
+__device__ __forceinline__ void tma_load_5d(uint32_t dst_smem, const void* tmap, int c0, int c1, int c2, int c3, int c4,
+                                            uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.5d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5, %6}], [%7];"
+      ::"r"(dst_smem), "l"(tmap), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4), "r"(bar)
+      : "memory");
+}
+
 // ---- tcgen05 ----------------------------------------------------------------------------------
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }

@@ -16,6 +16,8 @@
 // The same strip read as an MN-major operand (8 channels contiguous, pixel slots along K) feeds
 // the filter gradient: dW[tap] = X_strip(shifted by tap)^T * dY_strip, where the zero pads of the
 // dY strip cancel every out-of-image product.
+#include <cuda.h>
+
 #include <algorithm>
 
 #include "launch.h"
@@ -26,7 +28,8 @@ using namespace tc;
 
 namespace {
 constexpr int LOADERS = 128;
-constexpr int WSTAGES = 3;      // filter stages in shared memory; one stage = the five taps of one filter row
+constexpr int WSTAGES = 3;      // filter stages in shared memory when a stage = the five taps of one filter row
+constexpr int MAX_WSTAGES = 8;  // ... and the most single-tap stages (two-CTAs-per-SM variants)
 
 struct ConvGeom {
   int B, H, W, KC, NC;      // batch, image size, contraction channels, output channels
@@ -34,6 +37,8 @@ struct ConvGeom {
   int ipc, tiles;           // images per CTA, 128-row M tiles per CTA
   int lead, npix;           // zero pixels before the first image row, total pixel slots
   int ch_stride;            // bytes between channel chunks of the strip (npix*16 + 16)
+  int nstages;              // filter stages in the ring (of 5 taps or 1 tap each, a template parameter of the kernel)
+  int tma_rows;             // > 0: the strip is written by the TMA (tensor-map box of P x tma_rows pixel slots per chunk)
 };
 
 __host__ inline ConvGeom make_geom(int B, int H, int W, int KC, int NC, int ipc) {
@@ -45,6 +50,24 @@ __host__ inline ConvGeom make_geom(int B, int H, int W, int KC, int NC, int ipc)
   g.lead = 2 * g.P + 2;
   g.npix = g.lead + g.tiles * 128 + 2 * g.P + 2;
   g.ch_stride = g.npix * 16 + 16;
+  g.nstages = WSTAGES;
+  g.tma_rows = 0;
+  return g;
+}
+// The strip of ONE image written by the TMA: per 8-channel chunk one tensor-map box of P = W+4 columns x H+5 rows
+// (image rows -3 .. H+1) of the dense bf16 NHWC tensor.  Everything outside the image is out of bounds for the tensor
+// map and arrives as zeros, so the box IS the padded strip -- right pad of a row = left pad of the next, three zero
+// rows above (two for the taps, one so that the slot "row -2, column -2" of tap (0,0) is still inside the box) and two
+// below: no zeroing pass, no loads through registers.  Rows of the MMA tiles past the box read whatever follows in
+// shared memory; they only feed output rows the epilogue drops (GEMM rows are independent).
+__host__ inline ConvGeom make_geom_tma(int B, int H, int W, int KC, int NC, int min_strip_bytes) {
+  ConvGeom g = make_geom(B, H, W, KC, NC, 1);
+  g.tma_rows = H + 5;
+  g.lead = 3 * g.P;
+  g.npix = g.tma_rows * g.P;
+  g.ch_stride = (g.npix * 16 + 127) & ~127;                         // TMA destinations are 128-byte aligned
+  const int chunks = KC / 8;
+  while (chunks * g.ch_stride < min_strip_bytes) g.ch_stride += 128;    // the fused pool parks its fp32 tile here
   return g;
 }
 
@@ -180,6 +203,7 @@ __device__ __forceinline__ void stage_pool_grad_nt(float* dpm, uint8_t* argb, co
 }
 
 struct ConvArgs {
+  CUtensorMap tmap;    // g.tma_rows > 0: dense bf16 [B,H,W,KC] viewed as (8 channels, KC/8 chunks, W, H, B) for the strip boxes
   const float* x;      // [B,H,W,KC]
   const __nv_bfloat16* xb;   // the same, already bf16 (read instead of x when given)
   __nv_bfloat16* dconv_out_bf16;   // POOL dgrad: dense bf16 copy of the gathered dY (optional)
@@ -205,8 +229,12 @@ struct ConvArgs {
 // DGRAD = false: y = conv(x, w)            B operand (kc,nc) = w[tap][kc][nc]     (MN-major)
 // DGRAD = true : y = conv(x, rot180(w)^T)  B operand (kc,nc) = w[24-tap][nc][kc]  (K-major)
 // ---------------------------------------------------------------------------------------------------
-template <bool DGRAD, int KSTEPS, bool POOL = false>
-__global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
+// STAPS = filter taps per ring stage: 5 (one filter row; one wait / commit per row, the cheapest issue loop) or 1 (small
+// stages, so that strip + ring stay under half an SM's shared memory).  MINB = 2 asks for two CTAs per SM: with more
+// images than SMs one CTA's MMAs then overlap the other's strip fill and epilogue / pooling (every phase of a CTA is
+// serial in itself), which is what large batches need; the single-wave batch 128 keeps the one-CTA shape.
+template <bool DGRAD, int KSTEPS, bool POOL = false, int STAPS = 5, int MINB = 1>
+__global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_constant__ ConvArgs a) {
   B200_TRACE_SCOPE(DGRAD ? TR_CONV2_DGRAD : TR_CONV2_FWD);
   constexpr int BN = 64;
   constexpr int NISS = 4;                 // MMA-issuing warps (warps 4..7); warp 8 streams the filter
@@ -217,13 +245,14 @@ __global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
   // weight stage: MN-major [BN/8 groups][KC k][16B] (SBO = KC*16+16)  |  K-major [KC/8 chunks][BN rows][16B]
   const int w_mn_sbo = g.KC * 16 + 16, w_k_lbo = BN * 16 + 16;
   const int wtap = ((DGRAD ? kchunks * w_k_lbo : (BN / 8) * w_mn_sbo) + 127) & ~127;   // one tap's operand image
-  const int wstage = 5 * wtap;
+  const int wstage = STAPS * wtap;
+  constexpr int ROUNDS = 25 / STAPS;      // ring rounds per image
   uint8_t* strip = smem;
   uint8_t* wring = smem + ((strip_bytes + 127) & ~127);
-  uint8_t* ctrl = wring + WSTAGES * wstage;
+  uint8_t* ctrl = wring + g.nstages * wstage;
   uint64_t* wfull = reinterpret_cast<uint64_t*>(ctrl);
-  uint64_t* wempty = wfull + WSTAGES;
-  uint64_t* strip_full = wempty + WSTAGES;
+  uint64_t* wempty = wfull + MAX_WSTAGES;
+  uint64_t* strip_full = wempty + MAX_WSTAGES;
   uint64_t* accum = strip_full + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum + 1);
   float* dpm = reinterpret_cast<float*>(ctrl + 256);                  // POOL: [OH*OW][64] masked pooled gradient
@@ -236,8 +265,8 @@ __global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
   const int tmem_cols = g.tiles * BN <= 64 ? 64 : g.tiles * BN <= 128 ? 128 : g.tiles * BN <= 256 ? 256 : 512;
 
   if (tid == 0) {
-    for (int s = 0; s < WSTAGES; ++s) { mbar_init(smem_u32(wfull + s), 1); mbar_init(smem_u32(wempty + s), NISS); }
-    mbar_init(smem_u32(strip_full), POOL ? 256 : LOADERS);
+    for (int s = 0; s < g.nstages; ++s) { mbar_init(smem_u32(wfull + s), 1); mbar_init(smem_u32(wempty + s), NISS); }
+    mbar_init(smem_u32(strip_full), POOL ? 256 : (g.tma_rows ? 1 : LOADERS));
     mbar_init(smem_u32(accum), NISS);
     fence_mbar_init();
   }
@@ -298,7 +327,10 @@ __global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
     }
   }
   if (warp < 4) {
-    if (!POOL) {
+    if (!POOL && g.tma_rows) {       // the TMA warp fills the strip: nothing to stage here
+      pdl_wait();
+      pdl_launch_dependents();
+    } else if (!POOL) {
       // ---- input strip --------------------------------------------------------------------------
       if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) a.timeline[0] = clock64();
       zero_smem(strip, strip_bytes, tid);
@@ -407,34 +439,37 @@ __global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
       const uint32_t a_kstep = 2 * (g.ch_stride >> 4), b_kstep = DGRAD ? 2 * (w_k_lbo >> 4) : 16;
       mbar_wait(smem_u32(strip_full), 0);
       if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && w == 0) a.timeline[3] = clock64();
-      uint32_t acc = 0;
       // Every CTA streams the same 25 filter taps out of L2; each walks them in its own rotation so
       // that the CTAs do not all pull the same lines at once (the sum over taps is order-independent).
       int di = (int)((blockIdx.x + blockIdx.y) % 5u);       // filter-row rotation (same in the producer warp)
-      for (int r = 0; r < 5; ++r) {
-        const int s = r % WSTAGES;
-        const uint32_t ph = (r / WSTAGES) & 1;
-        mbar_wait(smem_u32(wfull + s), ph);               // one wait and one commit per filter ROW: both cost
+      int dj1 = 0;                                          // STAPS == 1: the tap inside the row
+      uint32_t q = 0;                                       // taps issued so far (0 = the accumulators are not initialised)
+      for (int r = 0; r < ROUNDS; ++r) {
+        const int s = r % g.nstages;
+        const uint32_t ph = (r / g.nstages) & 1;
+        mbar_wait(smem_u32(wfull + s), ph);               // one wait and one commit per stage: both cost
         tc_fence_after();                                 // ~100 cycles of the issuing thread (measured)
         const uint32_t b_row = b_lo0 + (uint32_t)s * (wstage >> 4);
 #pragma unroll
-        for (int dj = 0; dj < 5; ++dj) {
+        for (int tt = 0; tt < STAPS; ++tt, ++q) {
+          const int dj = STAPS == 5 ? tt : dj1;
           const uint32_t a_tap = a_lo0 + (uint32_t)((di - 2) * g.P + (dj - 2));    // a tap is a slot offset
-          // dgrad correlates with the filter rotated by 180 degrees: the stage holds forward row 4-di, read backwards
-          const uint32_t b_tap = b_row + (uint32_t)(DGRAD ? 4 - dj : dj) * (wtap >> 4);
+          // dgrad correlates with the filter rotated by 180 degrees: a five-tap stage holds forward row 4-di, read
+          // backwards; a one-tap stage holds forward tap (4-di, 4-dj) itself
+          const uint32_t b_tap = b_row + (uint32_t)(STAPS == 5 ? (DGRAD ? 4 - dj : dj) : 0) * (wtap >> 4);
           for (int t = w; t < g.tiles; t += NISS) {
             uint32_t a_lo = a_tap + t * 128, b_lo = b_tap;
             const uint32_t d = tmem + t * BN;
 #pragma unroll
             for (int ks = 0; ks < KSTEPS; ++ks) {
-              umma_bf16(d, desc_join(a_lo, a_hi), desc_join(b_lo, b_hi), idesc, acc | (uint32_t)(dj | ks));
+              umma_bf16(d, desc_join(a_lo, a_hi), desc_join(b_lo, b_hi), idesc, q | (uint32_t)ks);
               a_lo += a_kstep; b_lo += b_kstep;
             }
           }
         }
-        acc = 1;
         umma_commit(smem_u32(wempty + s));        // arrives when this warp's MMAs on the stage are done
-        if (++di == 5) di = 0;
+        if (STAPS == 5) { if (++di == 5) di = 0; }
+        else if (++dj1 == 5) { dj1 = 0; if (++di == 5) di = 0; }
       }
       umma_commit(smem_u32(accum));
       if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && w == 0) a.timeline[4] = clock64();
@@ -443,28 +478,40 @@ __global__ void __launch_bounds__(288, 1) conv5x5_tc_kernel(ConvArgs a) {
   } else {
     // ---- filter taps: one thread, bulk copies global -> shared, completion counted in bytes ----------
     if (lane == 0) {
+      if (!POOL && g.tma_rows) {
+        // ---- the strip: one tensor-map box per 8-channel chunk, image rows -3 .. H+1, zeros outside the image ----
+        pdl_wait();
+        const uint32_t bar = smem_u32(strip_full);
+        mbar_arrive_expect_tx(bar, (uint32_t)(kchunks * g.P * g.tma_rows * 16));
+        for (int c = 0; c < kchunks; ++c)
+          tma_load_5d(smem_u32(strip + c * g.ch_stride), &a.tmap, 0, c, 0, -3, n_img0, bar);
+      }
       const int img = (a.cout_f / 8) * (a.cin_f * 16 + 16);             // bytes of one packed tap
       int di = (int)((blockIdx.x + blockIdx.y) % 5u);                  // same rotation as the MMA warps
-      for (int r = 0; r < 5; ++r, di = (di == 4 ? 0 : di + 1)) {
-        const int s = r % WSTAGES;
-        const uint32_t ph = (r / WSTAGES) & 1;
+      int dj1 = 0;
+      for (int r = 0; r < ROUNDS; ++r) {
+        const int s = r % g.nstages;
+        const uint32_t ph = (r / g.nstages) & 1;
         mbar_wait(smem_u32(wempty + s), ph ^ 1);
         const uint32_t bar = smem_u32(wfull + s);
-        const int prow = DGRAD ? 4 - di : di;                            // packed (forward) filter row to fetch
+        // packed (forward) taps to fetch: a filter row in forward order, or the single tap the MMA warps want next
+        const int ftap0 = STAPS == 5 ? (DGRAD ? 4 - di : di) * 5 : (DGRAD ? (4 - di) * 5 + (4 - dj1) : di * 5 + dj1);
         if (!DGRAD) {     // N-groups nc0/8 .. +8 of a tap are contiguous: one copy per tap
           const uint32_t bytes = (BN / 8) * w_mn_sbo;
-          mbar_arrive_expect_tx(bar, 5 * bytes);
-          for (int j = 0; j < 5; ++j)
+          mbar_arrive_expect_tx(bar, STAPS * bytes);
+          for (int j = 0; j < STAPS; ++j)
             bulk_g2s(smem_u32(wring + s * wstage + j * wtap),
-                     a.wp + (size_t)(prow * 5 + j) * img + (size_t)(nc0 / 8) * w_mn_sbo, bytes, bar);
+                     a.wp + (size_t)(ftap0 + j) * img + (size_t)(nc0 / 8) * w_mn_sbo, bytes, bar);
         } else {          // read K-major: per k-chunk (forward cout group) the 64 rows nc0.. are contiguous
-          mbar_arrive_expect_tx(bar, 5u * kchunks * BN * 16);
-          for (int j = 0; j < 5; ++j) {
-            const uint8_t* src = a.wp + (size_t)(prow * 5 + j) * img + (size_t)nc0 * 16;
+          mbar_arrive_expect_tx(bar, (uint32_t)STAPS * kchunks * BN * 16);
+          for (int j = 0; j < STAPS; ++j) {
+            const uint8_t* src = a.wp + (size_t)(ftap0 + j) * img + (size_t)nc0 * 16;
             const uint32_t ws = smem_u32(wring + s * wstage + j * wtap);
             for (int c = 0; c < kchunks; ++c) bulk_g2s(ws + c * w_k_lbo, src + (size_t)c * (a.cin_f * 16 + 16), BN * 16, bar);
           }
         }
+        if (STAPS == 5) { if (++di == 5) di = 0; }
+        else if (++dj1 == 5) { dj1 = 0; if (++di == 5) di = 0; }
       }
     }
     __syncwarp();
@@ -506,6 +553,36 @@ int pick_ipc(int B, int H, int W, int KC) {
 }
 
 long long* g_conv_timeline = nullptr;
+int g_conv_force_variant = -1;      // diagnostics / tests: 0 = one CTA per SM (five-tap stages), 1 = two per SM, -1 = automatic
+
+// dense bf16 [B,H,W,C] as the 5-D tensor (8 channels | C/8 chunks | W | H | B) with a box of one chunk x P x rows
+int make_strip_tensor_map(CUtensorMap* tm, const void* x_bf16, int B, int H, int W, int C, int P, int rows) {
+  const cuuint64_t gdim[5] = {8, (cuuint64_t)(C / 8), (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+  const cuuint64_t gstr[4] = {16, (cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  const cuuint32_t box[5] = {8, 1, (cuuint32_t)P, (cuuint32_t)rows, 1};
+  const cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+  // the driver entry point is looked up through the runtime (libcuda is not a link-time dependency: the library
+  // must load on a machine without a driver, e.g. for the ABI checks)
+  using EncodeFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  static EncodeFn encode = nullptr;
+  if (!encode) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    B200_CUDA_TRY(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+    B200_REQUIRE(fn && qres == cudaDriverEntryPointSuccess, "conv5x5_tc: the driver does not export cuTensorMapEncodeTiled");
+    encode = reinterpret_cast<EncodeFn>(fn);
+  }
+  const CUresult rc = encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(x_bf16), gdim, gstr,
+                                             box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                             CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (rc != CUDA_SUCCESS) {
+    set_error("conv5x5_tc: cuTensorMapEncodeTiled failed with code %d", (int)rc);
+    return B200_E_CUDA;
+  }
+  return B200_OK;
+}
 
 template <bool DGRAD>
 int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, int B, int H, int W, int KC, int NC,
@@ -518,34 +595,51 @@ int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, 
   B200_REQUIRE(y || pool_out, "conv5x5_tc: no output");
   B200_REQUIRE((pg || ((uintptr_t)x & 15) == 0) && ((uintptr_t)wp & 15) == 0 && ((uintptr_t)y & 15) == 0,
                "conv5x5_tc: pointers must be 16-byte aligned");
-  int ipc = pool_out ? 1 : pick_ipc(B, H, W, KC);       // the fused pool works on one image per CTA
-  ConvGeom g = make_geom(B, H, W, KC, NC, ipc);
+  const int kchunks = KC / 8;
+  const int wtap = ((DGRAD ? kchunks * (64 * 16 + 16) : 8 * (KC * 16 + 16)) + 127) & ~127;
+  const int extra = pg ? pg->OH * pg->OW * 64 * 5 + 16 + 256 : 0;
+  // ---- shape of the CTA: two per SM with single-tap filter stages once the grid exceeds one wave, else one per SM ----
+  constexpr int kHalfSm = 113 * 1024;                    // (228 KB per SM - 1 KB reserved per CTA) / 2
+  const bool tma_ok = x_bf16 && !pg && W + 4 <= 256 && H + 5 <= 256 && ((uintptr_t)x_bf16 & 15) == 0;
+  ConvGeom g2 = tma_ok ? make_geom_tma(B, H, W, KC, NC, pool_out ? H * W * 68 * 4 : 0) : make_geom(B, H, W, KC, NC, 1);
+  const int strip2 = (kchunks * g2.ch_stride + 127) & ~127;
+  const int nst2 = std::min(MAX_WSTAGES, (kHalfSm - strip2 - 256 - extra) / wtap);
+  bool two = KC == 64 && B > kNumSMs && nst2 >= 4 && g2.tiles * 64 <= 256;
+  if (g_conv_force_variant >= 0) two = g_conv_force_variant == 1 && KC == 64 && nst2 >= 4 && g2.tiles * 64 <= 256;
+  ConvGeom g;
+  if (two) {
+    g = g2;
+    g.nstages = nst2;
+  } else {
+    const int ipc = pool_out ? 1 : pick_ipc(B, H, W, KC);       // the fused pool works on one image per CTA
+    g = (tma_ok && ipc == 1) ? make_geom_tma(B, H, W, KC, NC, pool_out ? H * W * 68 * 4 : 0) : make_geom(B, H, W, KC, NC, ipc);
+  }
   if (pool_out) {
     B200_REQUIRE(!DGRAD && NC == 64 && arg_out, "conv5x5_tc: fused pool needs the forward kernel with 64 output channels");
     B200_REQUIRE((int64_t)H * W * 68 * 4 <= (int64_t)(KC / 8) * g.ch_stride, "conv5x5_tc: conv tile does not fit the strip");
   }
   B200_REQUIRE(g.tiles * 64 <= 512, "conv5x5_tc: image %dx%d too large for one CTA's TMEM", H, W);
-  const int kchunks = KC / 8;
-  const int wstage = 5 * (((DGRAD ? kchunks * (64 * 16 + 16) : 8 * (KC * 16 + 16)) + 127) & ~127);
-  int smem = ((kchunks * g.ch_stride + 127) & ~127) + WSTAGES * wstage + 256;
-  if (pg) smem += pg->OH * pg->OW * 64 * 5 + 16 + 256;
+  const int staps = two ? 1 : 5;
+  const int smem = ((kchunks * g.ch_stride + 127) & ~127) + g.nstages * staps * wtap + 256 + extra;
   B200_REQUIRE(smem <= 227 * 1024, "conv5x5_tc: %d bytes of shared memory needed", smem);
   void (*kern)(ConvArgs) = nullptr;
   if (pg) {
     B200_REQUIRE(DGRAD && KC == 64, "conv5x5_tc: the pooled-gradient source needs 64 channels");
-    kern = conv5x5_tc_kernel<true, 4, true>;
+    kern = two ? conv5x5_tc_kernel<true, 4, true, 1, 2> : conv5x5_tc_kernel<true, 4, true>;
   } else
   switch (KC / 16) {
     case 2: kern = conv5x5_tc_kernel<DGRAD, 2>; break;
-    case 4: kern = conv5x5_tc_kernel<DGRAD, 4>; break;
+    case 4: kern = two ? conv5x5_tc_kernel<DGRAD, 4, false, 1, 2> : conv5x5_tc_kernel<DGRAD, 4>; break;
     case 8: kern = conv5x5_tc_kernel<DGRAD, 8>; break;
     case 16: kern = conv5x5_tc_kernel<DGRAD, 16>; break;
     default: B200_REQUIRE(false, "conv5x5_tc: contraction channels must be 32, 64, 128 or 256 (got %d)", KC);
   }
   B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-  ConvArgs a{x, reinterpret_cast<const __nv_bfloat16*>(x_bf16), reinterpret_cast<__nv_bfloat16*>(dconv_out_bf16),
+  if (two) B200_CUDA_TRY(prefer_max_shared(kern));
+  ConvArgs a{{}, x, reinterpret_cast<const __nv_bfloat16*>(x_bf16), reinterpret_cast<__nv_bfloat16*>(dconv_out_bf16),
              reinterpret_cast<uint8_t*>(pool_img), wp, DGRAD ? NC : KC, DGRAD ? KC : NC, bias, y, relu, g, g_conv_timeline, pg ? *pg : PoolGradSrc{}, dbias, dconv_out, pool_out, arg_out};
-  dim3 grid(cdiv(B, ipc), NC / 64);
+  if (g.tma_rows) B200_TRY(make_strip_tensor_map(&a.tmap, x_bf16, B, H, W, KC, g.P, g.tma_rows));
+  dim3 grid(cdiv(B, g.ipc), NC / 64);
   B200_CUDA_TRY(launch_kernel(kern, grid, dim3(288), (size_t)smem, st, a));
   return B200_OK;
 }
@@ -862,6 +956,7 @@ int wgrad_splits_tc(int B) { return std::max(1, std::min(B, (kNumSMs + 4) / 5));
 }  // namespace
 
 void conv5x5_set_timeline(long long* dev_buf) { g_conv_timeline = dev_buf; }
+void conv5x5_force_variant(int v) { g_conv_force_variant = v; }
 B200_TRACE_SETTER(trace_set_tc_conv)
 int64_t conv5x5_packed_bytes(int Cin, int Cout) { return 25ll * (Cout / 8) * (Cin * 16 + 16); }
 int pack_conv_weights(const float* w, void* wp, int Cin, int Cout, cudaStream_t st) {

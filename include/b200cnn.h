@@ -198,6 +198,12 @@ int b200_conv1_wgrad_bf16(const uint8_t* images, const float* dpool, const float
  * clock64() at its phase boundaries (start, strip zeroed, strip filled, MMA start, MMA issued,
  * accumulators ready, epilogue done); NULL switches it off. */
 int b200_debug_conv_timeline(int64_t* device_buf32);
+/* diagnostics / tests: the conv2 forward and input-gradient kernels come in two shapes -- one CTA per SM with
+ * filter stages of five taps (single-wave batches), and two CTAs per SM with single-tap stages (chosen automatically
+ * once the batch exceeds the 148 SMs, so that one CTA's MMAs overlap the other's strip fill and epilogue).
+ * 0 / 1 force the first / second shape wherever it is legal, -1 restores the automatic choice.  Process-wide.
+ * No counterpart in the reference. */
+int b200_debug_conv_variant(int32_t variant);
 /* diagnostics, only in a library built with B200_TRACE=1 (else B200_E_STATE): every kernel of the bf16 step stores
  * %globaltimer (ns) of its first CTA's start / last CTA's end into device_buf[2*k], device_buf[2*k+1] (atomic min /
  * max: preset them to ~0 / 0), k = pack, W2 image, conv1 fwd, conv2 fwd, FC1 fwd, tail rows, tail grads, FC1 dW,
@@ -212,6 +218,12 @@ int b200_conv5x5_fwd_bf16(const float* x, const void* w_packed, const float* bia
 int b200_conv5x5_pool_fwd_bf16(const float* x, const void* w_packed, const float* bias, float* y, float* pool,
                                uint8_t* arg, int32_t batch, int32_t h, int32_t wd, int32_t c_in, int32_t c_out,
                                void* stream);
+/* b200_conv5x5_pool_fwd_bf16 with the input activations already in bf16 (dense [B,H,W,c_in] bf16, what conv1's pool
+ * epilogue leaves behind in the step): the strip is then written by tensor-map TMA boxes with out-of-bounds zero
+ * fill instead of loads through registers.  Replaces :118-123 likewise. */
+int b200_conv5x5_pool_fwd_bf16x(const void* x_bf16, const void* w_packed, const float* bias, float* y, float* pool,
+                                uint8_t* arg, int32_t batch, int32_t h, int32_t wd, int32_t c_in, int32_t c_out,
+                                void* stream);
 int b200_conv5x5_dgrad_bf16(const float* dy, const void* w_packed, float* dx, int32_t batch, int32_t h, int32_t wd,
                             int32_t c_in, int32_t c_out, void* stream);
 int b200_conv5x5_wgrad_bf16_scratch_bytes(int32_t batch, int64_t* nbytes);

@@ -123,6 +123,48 @@ def test_conv2_kernels_multi_image_strip(lib, B):
     assert relerr(dw.cpu().numpy(), want) <= TIGHT
 
 
+@pytest.mark.parametrize("variant", [0, 1])
+@pytest.mark.parametrize("B,H,W", [(3, 12, 12), (300, 12, 12), (5, 16, 16), (2, 6, 6)])
+def test_conv2_pool_forward_tma_strip_both_cta_shapes(lib, variant, B, H, W):
+    """The fused conv2 + pool2 forward fed by bf16 activations: the strip is written by tensor-map TMA boxes (zero
+    fill outside the image instead of a zeroing pass).  Both CTA shapes -- one per SM with five-tap filter stages,
+    two per SM with single-tap stages -- must give the oracle's conv values and TF's pooling rule on them; so must
+    the pooled-gradient input gradient, whose strip is gathered in the kernel."""
+    Cc = 64
+    rng = np.random.default_rng(93)
+    x = np.maximum(rng.normal(size=(B, H, W, Cc)), 0).astype(np.float32)
+    w = (rng.normal(size=(5, 5, Cc, Cc)) * 0.05).astype(np.float32)
+    b = (rng.normal(size=(Cc,)) * 0.3).astype(np.float32)
+    xb = dev(x).to(torch.bfloat16).contiguous()
+    wd, bd = dev(w), dev(b)
+    wp = pack_filter(lib, wd, Cc, Cc)
+    OH, OW = (H + 1) // 2, (W + 1) // 2
+    y = torch.full((B, H, W, Cc), float("nan"), device="cuda")
+    pool = torch.full((B, OH, OW, Cc), float("nan"), device="cuda")
+    arg = torch.full((B, OH, OW, Cc), 255, dtype=torch.uint8, device="cuda")
+    _lib.check(lib.b200_debug_conv_variant(variant))
+    try:
+        _lib.check(lib.b200_conv5x5_pool_fwd_bf16x(xb.data_ptr(), wp.data_ptr(), bd.data_ptr(), y.data_ptr(),
+                                                   pool.data_ptr(), arg.data_ptr(), B, H, W, Cc, Cc, stream()))
+        torch.cuda.synchronize()
+        assert relerr(y.cpu().numpy(), np.maximum(rn.conv2d_same(bf16_round(x), bf16_round(w)) + b, 0)) <= TIGHT
+        wy, warg = rn.maxpool_3x3s2_same(y.cpu().numpy())
+        np.testing.assert_array_equal(pool.cpu().numpy(), wy)
+        np.testing.assert_array_equal(arg.cpu().numpy(), warg)
+        # input gradient through the pool (strip gathered in shared memory) in the same CTA shape
+        dpool = rng.normal(size=wy.shape).astype(np.float32)
+        dconv32 = rn.maxpool_3x3s2_same_grad(dpool, warg, (H, W)) * (y.cpu().numpy() > 0)
+        dx = torch.full((B, H, W, Cc), float("nan"), device="cuda")
+        db = torch.zeros(Cc, device="cuda")
+        _lib.check(lib.b200_conv5x5_dgrad_pool_bf16(dev(dpool).data_ptr(), pool.data_ptr(), arg.data_ptr(), wp.data_ptr(),
+                                                    dx.data_ptr(), db.data_ptr(), B, H, W, Cc, Cc, stream()))
+        torch.cuda.synchronize()
+        assert relerr(dx.cpu().numpy(), rn.conv2d_same_grad_input(bf16_round(dconv32), bf16_round(w))) <= TIGHT
+        assert relerr(db.cpu().numpy(), dconv32.astype(np.float64).sum((0, 1, 2))) <= 1e-5
+    finally:
+        _lib.check(lib.b200_debug_conv_variant(-1))
+
+
 # ---- whole step ------------------------------------------------------------------------------------------
 def make_batch(B, kind, seed):
     rng = np.random.default_rng(seed)
@@ -243,7 +285,10 @@ def test_batch_4096_gradient_is_mean_of_batch_128_gradients():
     assert abs(float(big.loss()) - loss / (B // b)) <= 1e-5 * abs(loss / (B // b))
     # per-image results do not depend on the batch they were computed in (same operands, same tap order per
     # pixel up to the filter-row rotation): logits agree to fp32 accumulation noise
-    assert relerr(big.logits().cpu().numpy(), torch.cat(logits).cpu().numpy()) <= 1e-5
+    # Per-image results differ between the two batch shapes only through the order of fp32 sums (the filter rows are
+    # walked in a per-CTA rotation) -- but an fp32 last-bit difference that lands on a bf16 rounding boundary flips
+    # that operand by one bf16 ulp (2^-8) in the next layer: measured 2e-3 of max-abs on the logits.  Bound: 5e-3.
+    assert relerr(big.logits().cpu().numpy(), torch.cat(logits).cpu().numpy()) <= 5e-3
     for i, k in enumerate(rn.PARAM_NAMES):
         o, n = big.offsets[i], big.sizes[i]
-        assert relerr(big.grads[o:o + n].cpu().numpy(), acc[o:o + n].cpu().numpy()) <= 2e-3, k
+        assert relerr(big.grads[o:o + n].cpu().numpy(), acc[o:o + n].cpu().numpy()) <= 5e-3, k
