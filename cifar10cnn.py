@@ -104,7 +104,7 @@ def run_worker(flags, ps_hosts, worker_hosts):
 
     images_train, labels_train = session.input_pipeline(BATCH_SIZE, True, seed=1234 + flags.task_index)
     images_test, labels_test = session.input_pipeline(BATCH_SIZE, False, seed=4321 + flags.task_index)
-    scope = session.ModelScope(mode=flags.mode)
+    scope = session.ModelScope(mode=flags.mode, reduce=flags.reduce)
     model_output = create_cnn(images_train, BATCH_SIZE, scope)
     test_output = create_cnn(images_test, BATCH_SIZE, scope)
     loss = cifar_loss(model_output, labels_train)
@@ -113,11 +113,17 @@ def run_worker(flags, ps_hosts, worker_hosts):
     generation_num = session.Variable(0)
     train_op = train_step(loss, generation_num)
 
+    import json
+    import time
     with session.MonitoredTrainingSession(is_chief=(flags.task_index == 0), last_step=flags.max_steps,
                                           reduce=flags.reduce, checkpoint_dir=flags.log_dir) as mon_sess:
         i = 0
         print('Starting Training')
+        t_start, i_start = None, 0
         while not mon_sess.should_stop():
+            if i == 20 and t_start is None:          # the first steps build and capture the step graph: not timed
+                torch.cuda.synchronize()
+                t_start, i_start = time.perf_counter(), i
             _, loss_value = mon_sess.run([train_op, loss])
             if loss_value is None:          # restored checkpoint already at the last step
                 break
@@ -127,6 +133,17 @@ def run_worker(flags, ps_hosts, worker_hosts):
             if (i + 1) % EVAL_EVERY == 0:
                 print(' --- Test Accuracy = {:.2f}%.'.format(100. * mon_sess.run([accuracy_test])[0]))
             i += 1
+        torch.cuda.synchronize()
+        if t_start is not None and i > i_start:
+            el = time.perf_counter() - t_start
+            world = len(worker_hosts)
+            # one JSON metrics line for harnesses (not in the reference's output): loop throughput of THIS launcher,
+            # the two periodic accuracy passes included
+            print(json.dumps({"b200cnn_metrics": {
+                "task": flags.task_index, "workers": world, "local_steps": i - i_start, "seconds": el,
+                "steps_per_sec": (i - i_start) / el, "images_per_sec_this_worker": (i - i_start) * BATCH_SIZE / el,
+                "images_per_sec_all_workers": (i - i_start) * BATCH_SIZE * world / el,
+                "data": "synthetic" if images_train.source.synthetic else "files", "mode": "bf16" if scope.engines[0].mode == 1 else "fp32"}}))
     if torch.distributed.is_initialized():
         torch.distributed.destroy_process_group()
 

@@ -37,7 +37,7 @@ _CTYPE = {
     "const b200_config*": C.POINTER(Config), "float**": C.POINTER(C.c_void_p),
     "int32_t**": C.POINTER(C.c_void_p), "void**": C.POINTER(C.c_void_p),
     "const void* const*": C.POINTER(C.c_void_p), "void* const*": C.POINTER(C.c_void_p), "uint32_t*": C.c_void_p,
-    "const uint8_t* const*": C.POINTER(C.c_void_p), "uint64_t*": C.c_void_p,
+    "const uint8_t* const*": C.POINTER(C.c_void_p), "uint64_t*": C.c_void_p, "uint64_t": C.c_uint64,
 }
 _PTR_OUT = {"b200_profile_step": {5: C.POINTER(C.c_float), 7: C.POINTER(C.c_int32)},
             "b200_launches_per_step": {1: C.POINTER(C.c_int32)},

@@ -810,6 +810,13 @@ int b200_head_f32(const float* logits, const int32_t* labels, float* loss_mean, 
   return head_f32(logits, labels, loss_mean, dlogits, pred, n_correct, n_bad, batch, n_cls,
                   (cudaStream_t)stream);
 }
+int b200_shuffle_batch(const uint8_t* images, const int32_t* labels, int64_t n_records, const int32_t* file_order,
+                       int32_t n_order, int32_t per_file, const int32_t* slots_in, int32_t* slots_out, int32_t capacity,
+                       uint64_t seed, int64_t step, int64_t stream_pos, uint8_t* images_out, int32_t* labels_out,
+                       int32_t batch, int32_t image_bytes, void* stream) {
+  return shuffle_batch(images, labels, n_records, file_order, n_order, per_file, slots_in, slots_out, capacity, seed, step,
+                       stream_pos, images_out, labels_out, batch, image_bytes, (cudaStream_t)stream);
+}
 int b200_sgd_apply_f32(float* p, const float* g, int64_t n, float lr, float scale, void* stream) {
   B200_REQUIRE(p && g, "null pointer");
   return sgd_apply_f32(p, g, n, lr, scale, (cudaStream_t)stream);

@@ -29,6 +29,12 @@ int head_f32(const float* logits, const int32_t* labels, float* loss_mean, float
 int sgd_apply_f32(float* p, const float* g, int64_t n, float lr, float scale, cudaStream_t st);
 
 
+// tf.train.shuffle_batch (:82-90) over a record set resident in HBM (shuffle_batch.cu)
+int shuffle_batch(const uint8_t* images, const int32_t* labels, int64_t n_records, const int32_t* file_order,
+                  int n_order, int per_file, const int32_t* slots_in, int32_t* slots_out, int capacity, uint64_t seed,
+                  int64_t step, int64_t stream_pos, uint8_t* images_out, int32_t* labels_out, int batch, int image_bytes,
+                  cudaStream_t st);
+
 // ---- bf16 tensor-core kernels (tc_*.cu): fp32 tensors in HBM, bf16 operands, fp32 accumulation ----
 int fc_fwd_tc(const float* x, const float* w, const float* b, float* y, int B, int K, int N, int relu,
               cudaStream_t st);

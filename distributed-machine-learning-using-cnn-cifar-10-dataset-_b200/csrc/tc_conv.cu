@@ -17,6 +17,7 @@
 // the filter gradient: dW[tap] = X_strip(shifted by tap)^T * dY_strip, where the zero pads of the
 // dY strip cancel every out-of-image product.
 #include <cuda.h>
+#include <stdlib.h>
 
 #include <algorithm>
 
@@ -328,6 +329,7 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
   }
   if (warp < 4) {
     if (!POOL && g.tma_rows) {       // the TMA warp fills the strip: nothing to stage here
+      if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) a.timeline[0] = a.timeline[1] = clock64();
       pdl_wait();
       pdl_launch_dependents();
     } else if (!POOL) {
@@ -441,8 +443,10 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
       if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && w == 0) a.timeline[3] = clock64();
       // Every CTA streams the same 25 filter taps out of L2; each walks them in its own rotation so
       // that the CTAs do not all pull the same lines at once (the sum over taps is order-independent).
-      int di = (int)((blockIdx.x + blockIdx.y) % 5u);       // filter-row rotation (same in the producer warp)
-      int dj1 = 0;                                          // STAPS == 1: the tap inside the row
+      // (single-tap stages rotate over all 25 taps: 25 phases instead of 5)
+      const int rot = STAPS == 5 ? (int)((blockIdx.x + blockIdx.y) % 5u) * 5 : (int)((blockIdx.x * 7u + blockIdx.y) % 25u);
+      int di = rot / 5;                                     // filter-row rotation (same in the producer warp)
+      int dj1 = rot % 5;                                    // STAPS == 1: the tap inside the row
       uint32_t q = 0;                                       // taps issued so far (0 = the accumulators are not initialised)
       for (int r = 0; r < ROUNDS; ++r) {
         const int s = r % g.nstages;
@@ -487,8 +491,8 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
           tma_load_5d(smem_u32(strip + c * g.ch_stride), &a.tmap, 0, c, 0, -3, n_img0, bar);
       }
       const int img = (a.cout_f / 8) * (a.cin_f * 16 + 16);             // bytes of one packed tap
-      int di = (int)((blockIdx.x + blockIdx.y) % 5u);                  // same rotation as the MMA warps
-      int dj1 = 0;
+      const int rot = STAPS == 5 ? (int)((blockIdx.x + blockIdx.y) % 5u) * 5 : (int)((blockIdx.x * 7u + blockIdx.y) % 25u);
+      int di = rot / 5, dj1 = rot % 5;                                 // same rotation as the MMA warps
       for (int r = 0; r < ROUNDS; ++r) {
         const int s = r % g.nstages;
         const uint32_t ph = (r / g.nstages) & 1;
@@ -555,6 +559,16 @@ int pick_ipc(int B, int H, int W, int KC) {
 long long* g_conv_timeline = nullptr;
 int g_conv_force_variant = -1;      // diagnostics / tests: 0 = one CTA per SM (five-tap stages), 1 = two per SM, -1 = automatic
 
+// filter stages of the one-CTA-per-SM shape (five taps each); B200_CONV_STAGES overrides the default of 3 (experiments)
+int conv_row_stages() {
+  static int n = 0;
+  if (!n) {
+    const char* e = getenv("B200_CONV_STAGES");
+    n = e ? std::max(2, std::min(atoi(e), 5)) : WSTAGES;
+  }
+  return n;
+}
+
 // dense bf16 [B,H,W,C] as the 5-D tensor (8 channels | C/8 chunks | W | H | B) with a box of one chunk x P x rows
 int make_strip_tensor_map(CUtensorMap* tm, const void* x_bf16, int B, int H, int W, int C, int P, int rows) {
   const cuuint64_t gdim[5] = {8, (cuuint64_t)(C / 8), (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
@@ -613,6 +627,8 @@ int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, 
   } else {
     const int ipc = pool_out ? 1 : pick_ipc(B, H, W, KC);       // the fused pool works on one image per CTA
     g = (tma_ok && ipc == 1) ? make_geom_tma(B, H, W, KC, NC, pool_out ? H * W * 68 * 4 : 0) : make_geom(B, H, W, KC, NC, ipc);
+    g.nstages = conv_row_stages();
+    while (g.nstages > 2 && ((kchunks * g.ch_stride + 127) & ~127) + g.nstages * 5 * wtap + 256 + extra > 227 * 1024) --g.nstages;
   }
   if (pool_out) {
     B200_REQUIRE(!DGRAD && NC == 64 && arg_out, "conv5x5_tc: fused pool needs the forward kernel with 64 output channels");

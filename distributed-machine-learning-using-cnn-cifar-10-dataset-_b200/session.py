@@ -60,17 +60,42 @@ class TrainOp:
 
 class ModelScope:
     """tf.variable_scope('model_definition') with reuse (:204-210): towers built in one scope share
-    the ten variables; each tower has its own activations."""
+    the ten variables; each tower has its own activations.  With more than one worker (an initialised NCCL
+    process group) the variables and gradients of the first tower live in peer-mapped symmetric memory, so
+    that the ps push/apply can run as the fused peer-memory kernel (exchange.P2PExchange); where symmetric
+    memory is unavailable the session falls back to an NCCL allreduce + SGD kernel."""
 
-    def __init__(self, mode=None, seed=0):
-        self.mode, self.seed = mode, seed
+    def __init__(self, mode=None, seed=0, reduce="sum"):
+        self.mode, self.seed, self.reduce = mode, seed, reduce
         self.engines = []
+        self.exchange = None
+
+    def _make_exchange(self):
+        import torch.distributed as dist
+        from .exchange import P2PExchange
+        if not (dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1):
+            return GradientExchange(reduce=self.reduce)
+        if dist.get_backend() == "nccl":
+            try:
+                total = TrainStepEngine(batch=8, mode="fp32").total
+                return P2PExchange(total, torch.device("cuda", torch.cuda.current_device()), reduce=self.reduce)
+            except Exception as e:       # no symmetric memory / NVLink peer access here: NCCL is still all-CUDA
+                import sys
+                print(f"b200cnn: peer-memory exchange unavailable ({type(e).__name__}: {e}); using NCCL", file=sys.stderr)
+        return GradientExchange(reduce=self.reduce)
 
     def tower(self, batch_size):
         from . import DEFAULT_MODE
         first = self.engines[0] if self.engines else None
-        eng = TrainStepEngine(batch=batch_size, mode=self.mode or DEFAULT_MODE,
-                              params=None if first is None else first.params)
+        kw = {}
+        if first is None:
+            self.exchange = self._make_exchange()
+            if hasattr(self.exchange, "params"):
+                kw = {"params": self.exchange.params, "grads": self.exchange.grads}
+        else:
+            kw = {"params": first.params}
+        eng = TrainStepEngine(batch=batch_size, mode=self.mode or DEFAULT_MODE, **kw)
+        eng.exchange = self.exchange
         if first is None:
             eng.init_params(self.seed)
         self.engines.append(eng)
@@ -84,18 +109,149 @@ def input_pipeline(batch_size, train_logical=True, seed=0, data_dir=None, synthe
     return ImagesNode(src), LabelsNode(src)
 
 
+class LossValue:
+    """What `mon_sess.run([train_op, loss])` (:230) returns for the loss: a number that is fetched from its pinned
+    host slot the first time somebody looks at it.  The step itself never waits for the GPU, so the next step is
+    queued while this one runs; float(), comparisons, arithmetic and printing all resolve it."""
+    __slots__ = ("_buf", "_event", "_value")
+
+    def __init__(self, buf, event):
+        self._buf, self._event, self._value = buf, event, None
+
+    def resolve(self):
+        if self._value is None:
+            self._event.synchronize()
+            self._value = float(self._buf[0])
+            self._buf = self._event = None
+        return self._value
+
+    def __float__(self):
+        return self.resolve()
+
+    def __eq__(self, other):
+        return self.resolve() == float(other)
+
+    def __lt__(self, other):
+        return self.resolve() < float(other)
+
+    def __le__(self, other):
+        return self.resolve() <= float(other)
+
+    def __gt__(self, other):
+        return self.resolve() > float(other)
+
+    def __ge__(self, other):
+        return self.resolve() >= float(other)
+
+    def __hash__(self):
+        return hash(self.resolve())
+
+    def __add__(self, other):
+        return self.resolve() + other
+
+    __radd__ = __add__
+
+    def __sub__(self, other):
+        return self.resolve() - other
+
+    def __rsub__(self, other):
+        return other - self.resolve()
+
+    def __mul__(self, other):
+        return self.resolve() * other
+
+    __rmul__ = __mul__
+
+    def __truediv__(self, other):
+        return self.resolve() / other
+
+    def __repr__(self):
+        return repr(self.resolve())
+
+    def __format__(self, spec):
+        return format(self.resolve(), spec)
+
+
+class _GraphStep:
+    """The body of `mon_sess.run([train_op, loss])` as it is benchmarked: one CUDA graph per input buffer holding
+    forward + backward + exchange + update (+ the loss copy to a pinned slot), the next batch drawn from the shuffle
+    queue on a side stream while the current step runs, no host synchronisation."""
+
+    def __init__(self, eng, exchange, source, lr):
+        self.eng, self.ex, self.source, self.lr = eng, exchange, source, lr
+        dev = eng.params.device
+        B = eng.batch
+        c = eng.cfg
+        self.bufs = [(torch.empty(B, c.c_in, c.img_h, c.img_w, dtype=torch.uint8, device=dev),
+                      torch.empty(B, dtype=torch.int32, device=dev)) for _ in range(2)]
+        for img, lab in self.bufs:
+            img.zero_(); lab.zero_()
+        self.loss_host = [torch.zeros(1, dtype=torch.float32).pin_memory() for _ in range(2)]
+        self.done = [torch.cuda.Event(), torch.cuda.Event()]
+        self.ready = [torch.cuda.Event(), torch.cuda.Event()]
+        self.side = torch.cuda.Stream(device=dev)
+        self.pending = [None, None]
+        self.used = [False, False]
+        self.i = 0
+        # capturing runs the step once eagerly (library side streams are created then) and once more under
+        # capture-time validation: keep the variables as they were
+        keep = eng.params.clone()
+        self.graphs = [eng.capture(lambda k=k: self._body(k)) for k in range(2)]
+        eng.params.copy_(keep)
+        torch.cuda.synchronize(dev)
+        self._prefetch(0)
+
+    def _body(self, k):
+        img, lab = self.bufs[k]
+        eng, ex = self.eng, self.ex
+        if ex.world == 1:
+            eng.train_step(img, lab, self.lr)
+        elif hasattr(ex, "train_step_"):
+            ex.train_step_(eng, img, lab, self.lr)                 # fused peer-memory exchange + update
+        else:
+            eng.forward_backward(img, lab)
+            ex.allreduce_(eng.grads)
+            eng.sgd_apply(self.lr, ex.grad_scale)
+        self.loss_host[k].copy_(eng.loss(), non_blocking=True)
+
+    def _prefetch(self, k):
+        """draw the next batch into buffer k on the side stream (after the step that last read it)"""
+        if self.used[k]:
+            self.side.wait_event(self.done[k])
+        img, lab = self.bufs[k]
+        self.source.next_into(img, lab, stream=self.side.cuda_stream)
+        self.ready[k].record(self.side)
+
+    def step(self):
+        k = self.i & 1
+        main = torch.cuda.current_stream()
+        main.wait_event(self.ready[k])
+        if self.pending[k] is not None:
+            self.pending[k].resolve()                               # two steps old: frees the pinned slot
+        self.graphs[k].replay()
+        self.done[k].record(main)
+        self.used[k] = True
+        lv = LossValue(self.loss_host[k], self.done[k])
+        self.pending[k] = lv
+        self._prefetch(1 - k)
+        self.i += 1
+        return lv
+
+
 class MonitoredTrainingSession:
     """run() executes the fused step; should_stop() is StopAtStepHook(last_step) (:219).  global_step
-    counts WORKER updates like the reference's shared counter: one allreduce round applies
+    counts WORKER updates like the reference's shared counter: one exchange round applies
     `world` of them."""
 
     def __init__(self, is_chief=True, last_step=20000, reduce="sum", checkpoint_dir=None, save_secs=600.0):
         self.is_chief = is_chief
         self.last_step = last_step
-        self.exchange = GradientExchange(reduce=reduce)
+        self.reduce = reduce
+        self.exchange = None
         self.global_step = 0
         self._synced = False
         self._engine = None
+        self._steps = {}
         self._saver = checkpoint.Saver(checkpoint_dir, save_secs) if (is_chief and checkpoint_dir) else None
         self._restore_from = checkpoint.latest(checkpoint_dir) if (is_chief and checkpoint_dir) else None
 
@@ -110,6 +266,7 @@ class MonitoredTrainingSession:
     def _first_sync(self, eng):
         """chief restores the newest checkpoint (or keeps its fresh init) and publishes variables and
         global_step to the other workers (:222)."""
+        self.exchange = getattr(eng, "exchange", None) or GradientExchange(reduce=self.reduce)
         if self._restore_from:
             params, step = checkpoint.load(self._restore_from)
             eng.load_params(params)
@@ -132,12 +289,27 @@ class MonitoredTrainingSession:
         logits_node.engine.forward(img, lab)
         return logits_node.engine
 
+    def _train(self, op):
+        eng = op.loss.logits.engine
+        if op.loss.logits.images.source is not op.loss.labels.source:
+            raise ValueError("images and labels must come from the same input_pipeline")
+        lr = op.learning_rate()
+        key = (id(eng), lr)
+        st = self._steps.get(key)
+        if st is None:
+            if self.exchange.world > 1:
+                import torch.distributed as dist
+                dist.barrier()
+            st = self._steps[key] = _GraphStep(eng, self.exchange, op.loss.labels.source, lr)
+        return st.step()
+
     def run(self, fetches):
         single = not isinstance(fetches, (list, tuple))
         items = [fetches] if single else list(fetches)
         out = [None] * len(items)
         train = [f for f in items if isinstance(f, TrainOp)]
         done = {}
+        step_loss = None
         if train:
             op = train[0]
             eng = op.loss.logits.engine
@@ -146,10 +318,7 @@ class MonitoredTrainingSession:
                 self._first_sync(eng)
                 if self.should_stop():
                     return None if single else [None] * len(items)
-            self._forward(op.loss.logits, op.loss.labels)
-            eng.backward()
-            self.exchange.allreduce_(eng.grads)
-            eng.sgd_apply(op.learning_rate(), self.exchange.grad_scale)
+            step_loss = self._train(op)
             self.global_step += self.exchange.global_step_increment
             done[id(op.loss.logits)] = eng
             if self._saver:
@@ -162,8 +331,11 @@ class MonitoredTrainingSession:
                 if eng is None:                                  # a separate run() draws a new batch
                     eng = self._forward(f.logits, f.labels)
                     done[id(f.logits)] = eng
+                    step_is_train = False
+                else:
+                    step_is_train = train and f.logits is train[0].loss.logits
                 if isinstance(f, LossNode):
-                    out[i] = float(eng.loss().item())
+                    out[i] = step_loss if step_is_train else float(eng.loss().item())
                 else:
                     out[i] = float(eng.n_correct().item()) / eng.batch
             else:

@@ -276,6 +276,21 @@ int b200_head_f32(const float* logits, const int32_t* labels, float* loss_mean, 
                   int32_t* pred, int32_t* n_correct, int32_t* n_bad, int32_t batch, int32_t n_cls,
                   void* stream);
 /* ApplyGradientDescent (:162-163): p -= lr * scale * g over n floats. */
+/* tf.train.shuffle_batch(capacity 5384, min_after_dequeue 5000) over the file list of input_pipeline (:72-91) with
+ * the record set resident in HBM: images uint8 [n_records][image_bytes] (the 3072 CHW payload bytes of each 3073-byte
+ * record, :57-62), labels int32 [n_records].  One call = one dequeue_many(batch) + the reader's refill:
+ *   - slots_in [capacity] holds the record ids in the queue; `batch` of them are drawn uniformly without replacement
+ *     (partial Fisher-Yates, draw i = splitmix64(seed, step, i): counter-based, reproducible on the host);
+ *   - the drawn records are copied to images_out [batch][image_bytes] / labels_out [batch];
+ *   - slots_out (a DIFFERENT buffer) receives the queue with the freed slots refilled by stream positions
+ *     stream_pos .. stream_pos+batch-1 of the sequential reader: position p is record
+ *     file_order[(p / per_file) % n_order] * per_file + p % per_file (file_order = the per-epoch shuffled file lists,
+ *     flattened, as string_input_producer produces them).
+ * The caller alternates the two slot buffers and advances step by 1 and stream_pos by batch. */
+int b200_shuffle_batch(const uint8_t* images, const int32_t* labels, int64_t n_records, const int32_t* file_order,
+                       int32_t n_order, int32_t per_file, const int32_t* slots_in, int32_t* slots_out, int32_t capacity,
+                       uint64_t seed, int64_t step, int64_t stream_pos, uint8_t* images_out, int32_t* labels_out,
+                       int32_t batch, int32_t image_bytes, void* stream);
 int b200_sgd_apply_f32(float* p, const float* g, int64_t n, float lr, float scale, void* stream);
 
 #ifdef __cplusplus

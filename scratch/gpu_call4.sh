@@ -1,0 +1,12 @@
+#!/bin/bash
+cd "$GRAFT_REPO_ROOT" || exit 1
+O=gpurun_out/c4; mkdir -p $O
+export B200_TRACE=1
+python -c "
+import sys; sys.path.insert(0,'.')
+from b200cnn import build; build.build(force=True)" > $O/build.log 2>&1
+for S in 0 6000 9000 11500 14000 18000; do
+  echo "=== stagger $S" >> $O/probe.log
+  B200_CONV_STAGGER_CYCLES=$S timeout 300 python scratch/conv_probe.py 4096 2>&1 | grep -A1 "variant 1" >> $O/probe.log
+done
+cat $O/probe.log
