@@ -132,6 +132,7 @@ int b200_create(const b200_config* c, b200_handle* out) {
                                   colsum_scratch_bytes(c->batch * h->h1 * h->w1, c->c2));
   h->add("scratch", scratch, 1);
   h->add("scratch2", conv5x5_wgrad_tc_scratch_bytes(c->batch), 1);      // conv2 wgrad runs beside conv1 wgrad
+  h->add("db2_part", B * 64, 4);      // conv2's bias gradient: one partial per dgrad CTA, summed in a fixed order
   h->add("w2_packed", conv5x5_packed_bytes(c->c1, c->c2), 1);
   h->add("fc1_part", (int64_t)fc_fwd_tc_splits(c->batch, h->flat, c->f1) * B * c->f1, 4);
   h->add("tail_scratch", fc_tail_scratch_bytes(c->batch, c->f1, c->f2, c->n_cls), 1);
@@ -321,8 +322,6 @@ static int forward_impl(b200_handle h, const uint8_t* images, const int32_t* lab
     // FC1 as a split-K tensor-core product; the tail kernels add the partials, bias and ReLU, run
     // FC2 / FC3 / loss / accuracy and already produce every gradient above FC1 (dfull1, dW2, db2, dW3,
     // db3, db1) -- they depend on nothing else, so b200_backward starts at FC1's weight gradient.
-    // The tail also clears the conv gradients (first four tensors of the flat buffer): conv1's filter / bias
-    // gradient and conv2's bias gradient are accumulated with atomics further down.
     float* part = h->ptr<float>("fc1_part");
     if (fcimg)
       PSITE("full1_fwd", fc_fwd_tc_splitk_img(h->ptr<void>("pool2_img"), h->ptr<void>("w1_img"), part, c.batch, h->flat,
@@ -334,7 +333,7 @@ static int forward_impl(b200_handle h, const uint8_t* images, const int32_t* lab
                             h->ptr<float>("dfull2"), h->ptr<float>("dfull1"), h->ptr<int32_t>("pred"),
                             h->ptr<float>("loss"), h->ptr<int32_t>("n_correct"), h->ptr<int32_t>("n_bad"),
                             h->G(P_FW2), h->G(P_FB2), h->G(P_FW3), h->G(P_FB3), h->G(P_FB1),
-                            h->ptr<void>("tail_scratch"), h->grads, (int)(h->p_off[P_B2] + h->p_size[P_B2]), c.batch, c.f1, c.f2,
+                            h->ptr<void>("tail_scratch"), nullptr, 0, c.batch, c.f1, c.f2,
                             c.n_cls, st, true, fork ? h->side[1] : nullptr, h->ev_fork[1], !h->profiling,
                             fcimg ? h->ptr<void>("dfull1_img") : nullptr));
     // (side stream 1, not 0: the backward puts FC1's dW on stream 0 and wants it to start with FC1's dX, not behind
@@ -371,7 +370,7 @@ struct P2PCtx {
   float lr, scale;
 };
 
-static int backward_impl(b200_handle h, void* stream, const P2PCtx* px) {
+static int backward_impl(b200_handle h, void* stream, const P2PCtx* px, bool defer_conv1_reduce = false) {
   B200_READY(h);
   if (!h->forward_done) {
     set_error("backward: call b200_forward first");
@@ -430,10 +429,12 @@ static int backward_impl(b200_handle h, void* stream, const P2PCtx* px) {
     // pool2's backward is not a kernel of its own: conv2's dgrad gathers MaxPoolGrad * ReluGrad from (dpool2,
     // pool2, arg2) while it builds its strip, adds the bias gradient (atomics into the buffer the tail kernel
     // cleared) and leaves dconv2 behind for the filter gradient, which then overlaps conv1's gradient.
+    int n_db2 = 0;
     SITE("conv2_dgrad", conv5x5_dgrad_pool_tc(dpool2, h->ptr<float>("pool2"), h->ptr<uint8_t>("arg2"),
-                                              h->ptr<void>("w2_packed"), dpool1, h->G(P_B2),
+                                              h->ptr<void>("w2_packed"), dpool1, nullptr,
                                               fused1 ? nullptr : dconv2, c.batch, h->h1, h->w1, c.c1, c.c2, st,
-                                              fused1 ? h->ptr<void>("dconv2_bf16") : nullptr));
+                                              fused1 ? h->ptr<void>("dconv2_bf16") : nullptr, h->ptr<float>("db2_part"),
+                                              &n_db2));
     if (fork) {
       B200_CUDA_TRY(cudaEventRecord(h->ev_fork[1], st));
       B200_CUDA_TRY(cudaStreamWaitEvent(s1, h->ev_fork[1], 0));
@@ -445,12 +446,17 @@ static int backward_impl(b200_handle h, void* stream, const P2PCtx* px) {
       PSITE("conv2_wgrad", conv5x5_wgrad_tc(h->ptr<float>("pool1"), dconv2, h->G(P_W2), h->ptr<float>("scratch2"),
                                            c.batch, h->h1, h->w1, c.c1, c.c2, st,
                                            fused1 ? h->ptr<void>("pool1_bf16") : nullptr,
-                                           fused1 ? h->ptr<void>("dconv2_bf16") : nullptr));
+                                           fused1 ? h->ptr<void>("dconv2_bf16") : nullptr,
+                                           // conv2's bias gradient: the dgrad CTAs' partial sums, in a fixed order, in the
+                                           // launch that sums the filter-gradient partials
+                                           h->ptr<float>("db2_part"), h->G(P_B2), n_db2));
     }
     if (fused1) {
+      // conv1's filter / bias gradient leaves one partial per CTA in `scratch`; they are summed in a fixed order by a
+      // small kernel -- or, when the update follows at once (b200_train_step), inside the update kernel
       SITE("conv1_wgrad", conv1_wgrad_tc(h->last_images, dpool1, h->ptr<float>("pool1"), h->ptr<uint8_t>("arg1"),
                                          h->G(P_W1), h->G(P_B1), scratch, c.batch, c.img_h, c.img_w, c.crop_h,
-                                         c.crop_w, st, true));
+                                         c.crop_w, st, defer_conv1_reduce && !h->profiling));
     } else {
       SITE("pool1_bwd", maxpool_bwd_f32(dpool1, h->ptr<uint8_t>("arg1"), h->ptr<float>("conv1"), dconv1, c.batch,
                                         c.crop_h, c.crop_w, c.c1, 1, st));
@@ -533,8 +539,22 @@ int b200_p2p_sgd_apply(b200_handle h, const void* const* peer_grads, void* const
 }
 
 int b200_train_step(b200_handle h, const uint8_t* images, const int32_t* labels, float lr, void* stream) {
-  TRY(b200_forward_backward(h, images, labels, stream));
-  return b200_sgd_apply(h, lr, 1.f, stream);
+  B200_READY(h);
+  const b200_config& c = h->cfg;
+  const bool fuse = c.mode == B200_MODE_BF16 && !h->profiling && conv1_tc_supported(c.crop_h, c.crop_w, c.c_in, c.c1) &&
+                    h->p_off[P_W1] == 0 && h->p_off[P_B1] == 4800;
+  if (!fuse) {
+    TRY(b200_forward_backward(h, images, labels, stream));
+    return b200_sgd_apply(h, lr, 1.f, stream);
+  }
+  // the fixed-order sum of conv1's gradient partials rides in the update kernel (no reduction launch at the very end
+  // of the step); the gradient buffer is complete when the step is
+  TRY(forward_impl(h, images, labels, stream, true));
+  TRY(backward_impl(h, stream, nullptr, true));
+  cudaStream_t st = (cudaStream_t)stream;
+  g_pdl_next = true;
+  return sgd_apply_reduce_f32(h->params, h->grads, h->p_total, lr, 1.f, h->ptr<float>("scratch"),
+                              conv1_wgrad_tc_partials(c.batch), 4864, st);
 }
 
 int b200_train_step_host(b200_handle h, const uint8_t* images_host, const int32_t* labels_host, float lr,

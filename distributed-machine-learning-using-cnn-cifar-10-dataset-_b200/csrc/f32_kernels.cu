@@ -519,6 +519,71 @@ __global__ void sgd_kernel(float* __restrict__ p, const float* __restrict__ g, i
        i += (int64_t)gridDim.x * blockDim.x)
     p[i] = fmaf(-step, g[i], p[i]);
 }
+// The same update when the first n_part gradients still sit in S per-CTA partials (conv1's filter / bias gradient,
+// tc_conv1.cu): the leading CTAs sum them in a fixed order -- four lanes per 16 bytes take every fourth partial and
+// combine with two shuffles, as reduce_partials_tc does -- store the finished gradient (the buffer is complete
+// after the step) and apply it; the other CTAs update the rest.  Saves the launch of a reduction kernel at the very
+// end of the step's critical path.
+__global__ void sgd_reduce_kernel(float* __restrict__ p, float* __restrict__ g, int64_t n, float step,
+                                  const float* __restrict__ part, int S, int n_part) {
+  B200_TRACE_SCOPE(TR_SGD);
+  pdl_wait();
+  const int lead = (n_part + 255) / 256;                      // n_part / 4 groups x 4 lanes = n_part threads
+  if ((int)blockIdx.x < lead) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int sub = t & 3;
+    const int i = min((t >> 2) * 4, n_part - 4);              // surplus threads redo the last group (full-warp shuffles)
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int z0 = sub; z0 < S; z0 += 32) {
+      float4 v[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int z = z0 + 4 * j;
+        v[j] = z < S ? __ldg(reinterpret_cast<const float4*>(part + (int64_t)z * n_part + i)) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { s.x += v[j].x; s.y += v[j].y; s.z += v[j].z; s.w += v[j].w; }
+    }
+#pragma unroll
+    for (int m = 1; m <= 2; m <<= 1) {
+      s.x += __shfl_xor_sync(0xffffffffu, s.x, m); s.y += __shfl_xor_sync(0xffffffffu, s.y, m);
+      s.z += __shfl_xor_sync(0xffffffffu, s.z, m); s.w += __shfl_xor_sync(0xffffffffu, s.w, m);
+    }
+    if (sub == 0 && (t >> 2) * 4 < n_part) {
+      *reinterpret_cast<float4*>(g + i) = s;
+      float4 a = *reinterpret_cast<float4*>(p + i);
+      a.x = fmaf(-step, s.x, a.x); a.y = fmaf(-step, s.y, a.y);
+      a.z = fmaf(-step, s.z, a.z); a.w = fmaf(-step, s.w, a.w);
+      *reinterpret_cast<float4*>(p + i) = a;
+    }
+    return;
+  }
+  const int64_t n4 = n >> 2, first4 = n_part >> 2;
+  float4* p4 = reinterpret_cast<float4*>(p);
+  const float4* g4 = reinterpret_cast<const float4*>(g);
+  for (int64_t i = first4 + (blockIdx.x - lead) * (int64_t)blockDim.x + threadIdx.x; i < n4;
+       i += (int64_t)(gridDim.x - lead) * blockDim.x) {
+    float4 a = p4[i], b = g4[i];
+    a.x = fmaf(-step, b.x, a.x); a.y = fmaf(-step, b.y, a.y);
+    a.z = fmaf(-step, b.z, a.z); a.w = fmaf(-step, b.w, a.w);
+    p4[i] = a;
+  }
+}
+// n and n_part multiples of 4, the partial range = the first n_part floats of the flat buffers
+int sgd_apply_reduce_f32(float* p, float* g, int64_t n, float lr, float scale, const float* part, int S, int n_part,
+                         cudaStream_t st) {
+  B200_REQUIRE(n > 0 && n % 4 == 0 && n_part > 0 && n_part % 4 == 0 && n_part <= n && S > 0 && part,
+               "sgd_apply_reduce: bad sizes");
+  B200_REQUIRE(((uintptr_t)p & 15) == 0 && ((uintptr_t)g & 15) == 0 && ((uintptr_t)part & 15) == 0,
+               "sgd_apply_reduce: pointers must be 16-byte aligned");
+  const int lead = (n_part + 255) / 256;
+  int grid = lead + (int)std::min<int64_t>(((n - n_part) / 4 + 255) / 256 + 1, kNumSMs * 4);
+  static PerDeviceOnce carve;
+  if (carve.first()) B200_CUDA_TRY(prefer_max_shared(sgd_reduce_kernel));
+  B200_CUDA_TRY(launch_kernel(sgd_reduce_kernel, dim3(grid), dim3(256), 0, st, p, g, n, lr * scale, part, S, n_part));
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
 int sgd_apply_f32(float* p, const float* g, int64_t n, float lr, float scale, cudaStream_t st) {
   B200_REQUIRE(n >= 0, "sgd_apply: negative size");
   B200_REQUIRE(((uintptr_t)p & 15) == 0 && ((uintptr_t)g & 15) == 0, "sgd_apply: pointers must be 16-byte aligned");

@@ -27,6 +27,11 @@ int fc_bwd_f32(const float* x, const float* w, const float* dy, float* dx, float
 int head_f32(const float* logits, const int32_t* labels, float* loss_mean, float* dlogits, int32_t* pred,
              int32_t* n_correct, int32_t* n_bad, int B, int ncls, cudaStream_t st);
 int sgd_apply_f32(float* p, const float* g, int64_t n, float lr, float scale, cudaStream_t st);
+// the update with the first n_part gradients still in S partials [S][n_part] (summed in a fixed order, stored to g)
+int sgd_apply_reduce_f32(float* p, float* g, int64_t n, float lr, float scale, const float* part, int S, int n_part,
+                         cudaStream_t st);
+// out[i] = sum over z < S of part[z * stride + i], fixed order (tc_conv.cu); n, stride multiples of 4 (stride 0 = n)
+int reduce_partials(const float* part, float* out, int n, int S, cudaStream_t st, int stride = 0);
 
 
 // tf.train.shuffle_batch (:82-90) over a record set resident in HBM (shuffle_batch.cu)
@@ -61,13 +66,18 @@ int conv5x5_dgrad_tc(const float* dy, const void* wp, float* dx, int B, int H, i
 // dconv_out (optional) receives dconv as a dense [B,H,W,64] fp32 tensor
 int conv5x5_dgrad_pool_tc(const float* dpool, const float* pool, const uint8_t* arg, const void* wp, float* dx,
                           float* dbias, float* dconv_out, int B, int H, int W, int Cin, int Cout, cudaStream_t st,
-                          void* dconv_out_bf16 = nullptr);      // (optional) dconv as a dense bf16 tensor
+                          void* dconv_out_bf16 = nullptr,       // (optional) dconv as a dense bf16 tensor
+                          float* dbias_part = nullptr,          // (optional, instead of dbias) per-CTA bias-gradient sums
+                          int* n_part = nullptr);               //   [*n_part][64] for a fixed-order reduction (<= B of them)
 int conv5x5_wgrad_pool_tc(const float* x, const float* dpool, const float* pool, const uint8_t* arg, float* dw,
                           float* scratch, int B, int H, int W, int Cin, int Cout, cudaStream_t st);
 int64_t conv5x5_wgrad_tc_scratch_bytes(int B);
 // x_bf16 / dy_bf16 (optional, both or none): bf16 copies of x / dy, read instead of the fp32 tensors
+// db_part / db / n_db_part (optional): the per-CTA bias-gradient sums [n_db_part][64] of conv5x5_dgrad_pool_tc, reduced
+// to db [64] in the same launch as the filter-gradient partials
 int conv5x5_wgrad_tc(const float* x, const float* dy, float* dw, float* scratch, int B, int H, int W, int Cin,
-                     int Cout, cudaStream_t st, const void* x_bf16 = nullptr, const void* dy_bf16 = nullptr);
+                     int Cout, cudaStream_t st, const void* x_bf16 = nullptr, const void* dy_bf16 = nullptr,
+                     const float* db_part = nullptr, float* db = nullptr, int n_db_part = 0);
 int fc_fwd_tc_splits(int B, int K, int N);
 // FC1's three products on bf16 operand IMAGES ([chunk of 8][rows][8], the shared-memory layout of a stage: fetched
 // with bulk copies, nothing converted): x_img [K/8][B][8] (written by conv2's pool epilogue), w_img [N/8][K][8]
@@ -108,7 +118,11 @@ int conv1_pool_fwd_tc(const uint8_t* img, const float* w, const float* bias, flo
                       float* conv_dbg, int B, int ih, int iw, int H, int W, cudaStream_t st,
                       void* pool_bf16 = nullptr);      // (optional) second copy of pool, rounded to bf16
 int64_t conv1_wgrad_tc_scratch_bytes(int B);
+// the kernel leaves one partial [4864] (dw [25][3][64], then db [64]) per CTA in scratch and a fixed-order reduction
+// writes dw / db -- unless defer_reduce, in which case the caller sums the conv1_wgrad_tc_partials(B) partials itself
+// (sgd_apply_reduce_f32 does, at the end of a step; dw and db are then adjacent in the flat gradient buffer)
+int conv1_wgrad_tc_partials(int B);
 int conv1_wgrad_tc(const uint8_t* img, const float* dpool, const float* pool, const uint8_t* arg, float* dw, float* db,
-                   float* scratch, int B, int ih, int iw, int H, int W, cudaStream_t st, bool prezeroed = false);
+                   float* scratch, int B, int ih, int iw, int H, int W, cudaStream_t st, bool defer_reduce = false);
 
 }  // namespace b200

@@ -218,6 +218,8 @@ struct ConvArgs {
   long long* timeline;  // optional device buffer [8]: clock64 stamps of CTA 0's phases (diagnostics), else null
   PoolGradSrc pg;       // POOL variant: x is unused, the strip is gathered from the pooled gradient
   float* dbias;         // POOL variant: += sum of dconv over pixels per channel (atomics; zero on entry), or null
+  float* dbias_part;    // POOL variant: instead, this CTA's sum goes to dbias_part[blockIdx.x][64] (summed in a fixed
+                        // order by the caller: run-to-run identical results), or null
   float* dconv_out;     // POOL variant: also store dconv as dense [B,H,W,64] fp32 (for the filter gradient), or null
   float* pool_out;      // forward, ipc == 1, NC == 64: fused 3x3/2 SAME max-pool of the output [B,OH,OW,64] (or null)
   uint8_t* arg_out;     //   ... and its argmax; y may then be null
@@ -281,7 +283,6 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
     // ---- dY strip from the pooled gradient: the four issuing warps help (they have nothing to issue before it) ----
     if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) a.timeline[0] = clock64();
     for (int o = tid * 16; o < strip_bytes; o += 256 * 16) *reinterpret_cast<uint4*>(strip + o) = make_uint4(0, 0, 0, 0);
-    if (tid < 64) bred[tid] = 0.f;
     pdl_wait();
     pdl_launch_dependents();
     if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) a.timeline[1] = clock64();
@@ -310,7 +311,8 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
     }
     fence_proxy_async();
     mbar_arrive(smem_u32(strip_full));
-    if (a.dbias && blockIdx.y == 0) {        // BiasAddGrad of the conv layer: thread <-> channel chunk tid & 7
+    if ((a.dbias || a.dbias_part) && blockIdx.y == 0) {        // BiasAddGrad of the conv layer: thread <-> channel chunk tid & 7
+      // fixed order throughout: a thread's pixels in loop order, lanes by two shuffles, the eight warps one after the other
 #pragma unroll
       for (int e = 0; e < 8; ++e) {
         bsum[e] += __shfl_xor_sync(0xffffffffu, bsum[e], 8);
@@ -318,10 +320,16 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
       }
       if (lane < 8)
 #pragma unroll
-        for (int e = 0; e < 8; ++e) atomicAdd(bred + lane * 8 + e, bsum[e]);
+        for (int e = 0; e < 8; ++e) bred[warp * 64 + lane * 8 + e] = bsum[e];
       if (warp < 4) {
         nt_sync<256>();
-        if (tid < 64) atomicAdd(a.dbias + tid, bred[tid]);
+        if (tid < 64) {
+          float s = 0.f;
+#pragma unroll
+          for (int w8 = 0; w8 < 8; ++w8) s += bred[w8 * 64 + tid];
+          if (a.dbias_part) a.dbias_part[(size_t)blockIdx.x * 64 + tid] = s;
+          else atomicAdd(a.dbias + tid, s);
+        }
       } else {
         asm volatile("bar.arrive 3, 256;" ::: "memory");      // the issuing warps do not wait for the sum
       }
@@ -602,7 +610,8 @@ template <bool DGRAD>
 int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, int B, int H, int W, int KC, int NC,
                 int relu, cudaStream_t st, const PoolGradSrc* pg = nullptr, float* dbias = nullptr,
                 float* dconv_out = nullptr, float* pool_out = nullptr, uint8_t* arg_out = nullptr,
-                const void* x_bf16 = nullptr, void* dconv_out_bf16 = nullptr, void* pool_img = nullptr) {
+                const void* x_bf16 = nullptr, void* dconv_out_bf16 = nullptr, void* pool_img = nullptr,
+                float* dbias_part = nullptr, int* n_part_out = nullptr) {
   B200_REQUIRE(B > 0 && H > 0 && W > 0, "conv5x5_tc: bad shape");
   B200_REQUIRE(KC % 16 == 0 && NC % 64 == 0, "conv5x5_tc: channels must be multiples of 16 (in) / 64 (out), got %d/%d",
                KC, NC);
@@ -611,7 +620,7 @@ int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, 
                "conv5x5_tc: pointers must be 16-byte aligned");
   const int kchunks = KC / 8;
   const int wtap = ((DGRAD ? kchunks * (64 * 16 + 16) : 8 * (KC * 16 + 16)) + 127) & ~127;
-  const int extra = pg ? pg->OH * pg->OW * 64 * 5 + 16 + 256 : 0;
+  const int extra = pg ? pg->OH * pg->OW * 64 * 5 + 16 + 8 * 64 * 4 : 0;
   // ---- shape of the CTA: two per SM with single-tap filter stages once the grid exceeds one wave, else one per SM ----
   constexpr int kHalfSm = 113 * 1024;                    // (228 KB per SM - 1 KB reserved per CTA) / 2
   const bool tma_ok = x_bf16 && !pg && W + 4 <= 256 && H + 5 <= 256 && ((uintptr_t)x_bf16 & 15) == 0;
@@ -653,7 +662,8 @@ int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, 
   B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   if (two) B200_CUDA_TRY(prefer_max_shared(kern));
   ConvArgs a{{}, x, reinterpret_cast<const __nv_bfloat16*>(x_bf16), reinterpret_cast<__nv_bfloat16*>(dconv_out_bf16),
-             reinterpret_cast<uint8_t*>(pool_img), wp, DGRAD ? NC : KC, DGRAD ? KC : NC, bias, y, relu, g, g_conv_timeline, pg ? *pg : PoolGradSrc{}, dbias, dconv_out, pool_out, arg_out};
+             reinterpret_cast<uint8_t*>(pool_img), wp, DGRAD ? NC : KC, DGRAD ? KC : NC, bias, y, relu, g, g_conv_timeline, pg ? *pg : PoolGradSrc{}, dbias, dbias_part, dconv_out, pool_out, arg_out};
+  if (n_part_out) *n_part_out = cdiv(B, g.ipc);
   if (g.tma_rows) B200_TRY(make_strip_tensor_map(&a.tmap, x_bf16, B, H, W, KC, g.P, g.tma_rows));
   dim3 grid(cdiv(B, g.ipc), NC / 64);
   B200_CUDA_TRY(launch_kernel(kern, grid, dim3(288), (size_t)smem, st, a));
@@ -942,20 +952,26 @@ __global__ void __launch_bounds__(416, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
 }
 
 // sums the S partials of every 4-float group: four neighbouring lanes take every fourth partial each (all of a
-// lane's loads in flight together) and combine with two shuffles -- a fixed order, so the result is deterministic
-__global__ void reduce_partials_tc(const float* __restrict__ part, float* __restrict__ out, int n, int S) {
+// lane's loads in flight together) and combine with two shuffles -- a fixed order, so the result is deterministic.
+// A launch can carry a second, independent segment (its blocks follow the first segment's): conv2's bias-gradient
+// partials ride along with its filter-gradient partials.
+struct ReduceSeg { const float* part; float* out; int n, S, stride; };
+__global__ void reduce_partials_tc(ReduceSeg s0, ReduceSeg s1) {
   B200_TRACE_SCOPE(TR_CONV2_REDUCE);
   pdl_wait();
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int nb0 = (s0.n + 127) / 128;
+  const bool second = (int)blockIdx.x >= nb0;
+  const ReduceSeg& g = second ? s1 : s0;
+  const int t = (blockIdx.x - (second ? nb0 : 0)) * blockDim.x + threadIdx.x;
   const int sub = t & 3;
-  const int i = min((t >> 2) * 4, n - 4);                 // surplus threads redo the last group (shuffles stay full-warp)
+  const int i = min((t >> 2) * 4, g.n - 4);                 // surplus threads redo the last group (shuffles stay full-warp)
   float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-  for (int z0 = sub; z0 < S; z0 += 32) {
+  for (int z0 = sub; z0 < g.S; z0 += 32) {
     float4 v[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const int z = z0 + 4 * j;
-      v[j] = z < S ? __ldg(reinterpret_cast<const float4*>(part + (int64_t)z * n + i)) : make_float4(0.f, 0.f, 0.f, 0.f);
+      v[j] = z < g.S ? __ldg(reinterpret_cast<const float4*>(g.part + (int64_t)z * g.stride + i)) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
 #pragma unroll
     for (int j = 0; j < 8; ++j) { s.x += v[j].x; s.y += v[j].y; s.z += v[j].z; s.w += v[j].w; }
@@ -965,12 +981,19 @@ __global__ void reduce_partials_tc(const float* __restrict__ part, float* __rest
     s.x += __shfl_xor_sync(0xffffffffu, s.x, m); s.y += __shfl_xor_sync(0xffffffffu, s.y, m);
     s.z += __shfl_xor_sync(0xffffffffu, s.z, m); s.w += __shfl_xor_sync(0xffffffffu, s.w, m);
   }
-  if (sub == 0 && (t >> 2) * 4 < n) *reinterpret_cast<float4*>(out + i) = s;
+  if (sub == 0 && (t >> 2) * 4 < g.n) *reinterpret_cast<float4*>(g.out + i) = s;
 }
 
 int wgrad_splits_tc(int B) { return std::max(1, std::min(B, (kNumSMs + 4) / 5)); }
 }  // namespace
 
+int reduce_partials(const float* part, float* out, int n, int S, cudaStream_t st, int stride) {
+  if (stride <= 0) stride = n;
+  B200_REQUIRE(part && out && n > 0 && n % 4 == 0 && S > 0 && stride % 4 == 0, "reduce_partials: bad argument");
+  B200_CUDA_TRY(launch_kernel(reduce_partials_tc, dim3(cdiv(n, 128)), dim3(128), 0, st, ReduceSeg{part, out, n, S, stride},
+                              ReduceSeg{nullptr, nullptr, 0, 0, 0}));
+  return B200_OK;
+}
 void conv5x5_set_timeline(long long* dev_buf) { g_conv_timeline = dev_buf; }
 void conv5x5_force_variant(int v) { g_conv_force_variant = v; }
 B200_TRACE_SETTER(trace_set_tc_conv)
@@ -1013,20 +1036,21 @@ static PoolGradSrc make_pool_src(const float* dpool, const float* pool, const ui
 // dbias (optional, zero on entry) += sum of dconv over (B,H,W)
 int conv5x5_dgrad_pool_tc(const float* dpool, const float* pool, const uint8_t* arg, const void* wp, float* dx,
                           float* dbias, float* dconv_out, int B, int H, int W, int Cin, int Cout, cudaStream_t st,
-                          void* dconv_out_bf16) {
+                          void* dconv_out_bf16, float* dbias_part, int* n_part) {
   B200_REQUIRE(Cin % 64 == 0 && Cout == 64, "conv5x5_dgrad_pool_tc: needs Cout == 64 (got %d -> %d)", Cin, Cout);
   PoolGradSrc p = make_pool_src(dpool, pool, arg, H, W);
   return launch_conv<true>(nullptr, (const uint8_t*)wp, nullptr, dx, B, H, W, Cout, Cin, 0, st, &p, dbias, dconv_out, nullptr,
-                           nullptr, nullptr, dconv_out_bf16);
+                           nullptr, nullptr, dconv_out_bf16, nullptr, dbias_part, n_part);
 }
 int64_t conv5x5_wgrad_tc_scratch_bytes(int B) { return (int64_t)wgrad_splits_tc(B) * 25 * 64 * 64 * 4; }
 static int launch_wgrad(const float* x, const float* dy, const PoolGradSrc* pg, float* dw, float* scratch, int B, int H,
                         int W, int Cin, int Cout, cudaStream_t st, const void* x_bf16 = nullptr,
-                        const void* dy_bf16 = nullptr);
+                        const void* dy_bf16 = nullptr, const float* db_part = nullptr, float* db = nullptr, int n_db_part = 0);
 int conv5x5_wgrad_tc(const float* x, const float* dy, float* dw, float* scratch, int B, int H, int W, int Cin,
-                     int Cout, cudaStream_t st, const void* x_bf16, const void* dy_bf16) {
+                     int Cout, cudaStream_t st, const void* x_bf16, const void* dy_bf16, const float* db_part, float* db,
+                     int n_db_part) {
   B200_REQUIRE((x_bf16 == nullptr) == (dy_bf16 == nullptr), "conv5x5_wgrad_tc: give both bf16 copies or none");
-  return launch_wgrad(x, dy, nullptr, dw, scratch, B, H, W, Cin, Cout, st, x_bf16, dy_bf16);
+  return launch_wgrad(x, dy, nullptr, dw, scratch, B, H, W, Cin, Cout, st, x_bf16, dy_bf16, db_part, db, n_db_part);
 }
 // filter gradient with dY = MaxPoolGrad(dpool, arg) * [pool > 0] gathered on the fly
 int conv5x5_wgrad_pool_tc(const float* x, const float* dpool, const float* pool, const uint8_t* arg, float* dw,
@@ -1035,7 +1059,8 @@ int conv5x5_wgrad_pool_tc(const float* x, const float* dpool, const float* pool,
   return launch_wgrad(x, nullptr, &p, dw, scratch, B, H, W, Cin, Cout, st);
 }
 static int launch_wgrad(const float* x, const float* dy, const PoolGradSrc* pg, float* dw, float* scratch, int B, int H,
-                        int W, int Cin, int Cout, cudaStream_t st, const void* x_bf16, const void* dy_bf16) {
+                        int W, int Cin, int Cout, cudaStream_t st, const void* x_bf16, const void* dy_bf16,
+                        const float* db_part, float* db, int n_db_part) {
   B200_REQUIRE(Cin == 64 && Cout == 64, "conv5x5_wgrad_tc: only 64 -> 64 channels (got %d -> %d)", Cin, Cout);
   B200_REQUIRE(B > 0 && H > 0 && W > 0, "conv5x5_wgrad_tc: bad shape");
   ConvGeom g = make_geom(B, H, W, 64, 64, 1);
@@ -1061,7 +1086,10 @@ static int launch_wgrad(const float* x, const float* dy, const PoolGradSrc* pg, 
   B200_CUDA_TRY(launch_kernel(conv5x5_wgrad_tc_kernel, dim3(5, S), dim3(416), (size_t)smem, st, a));
   const int n = 25 * 64 * 64;
   g_pdl_next = overlap;
-  B200_CUDA_TRY(launch_kernel(reduce_partials_tc, dim3(cdiv(n, 128)), dim3(128), 0, st, (const float*)scratch, dw, n, S));
+  const bool with_db = db_part && db && n_db_part > 0;      // the bias-gradient partials of the dgrad kernel ride along
+  B200_CUDA_TRY(launch_kernel(reduce_partials_tc, dim3(cdiv(n, 128) + (with_db ? 1 : 0)), dim3(128), 0, st,
+                              ReduceSeg{scratch, dw, n, S, n},
+                              with_db ? ReduceSeg{db_part, db, 64, n_db_part, 64} : ReduceSeg{nullptr, nullptr, 0, 0, 0}));
   return B200_OK;
 }
 

@@ -303,8 +303,7 @@ struct Conv1WgradArgs {
   const float* dpool;     // [B,OH,OW,64]  gradient w.r.t. pool1
   const float* pool;      // [B,OH,OW,64]  pool1 itself (ReluGrad mask: the selected cell is > 0 iff pool1 > 0)
   const uint8_t* arg;     // [B,OH,OW,64]
-  float* dw;              // [25][3][64]  += (atomics; zero on entry)
-  float* db;              // [64]         += (atomics; zero on entry), may be null
+  float* part;            // [CTAs][4864]: this CTA's sum of dw [25][3][64] followed by db [64]
   C1Geom g;
   long long* timeline;    // diagnostics: clock64 stamps of CTA 0 in slots [25,31) of the timeline buffer, or null
 };
@@ -423,9 +422,11 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
     tc_fence_after();
     if (stamp) a.timeline[28] = clock64();
     if (warp < 4 && nimg > 0) {
-      // D_di[cout][dj*8 + c] -> dW1[(di*5+dj)][c][cout]: 16 adjacent couts per warp instruction, summed across
-      // CTAs with fp32 atomics (the 128 per-image partials would otherwise need a reduction kernel of their own)
+      // D_di[cout][dj*8 + c] -> this CTA's partial of dW1[(di*5+dj)][c][cout] and db1[cout]: 16 adjacent couts per
+      // warp instruction.  The partials are summed in a fixed order afterwards (run-to-run identical gradients;
+      // fp32 atomics here made the last bits depend on the order in which CTAs finished).
       const int cout = warp * 16 + lane;
+      float* part = a.part + (size_t)blockIdx.x * 4864;
       for (int di = 0; di < 5; ++di) {
 #pragma unroll 1
         for (int c0 = 0; c0 < 64; c0 += 32) {
@@ -436,8 +437,8 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
               const int col = c0 + j, dj = col >> 3, c = col & 7;
-              if (col < 40 && c < 3) atomicAdd(a.dw + ((di * 5 + dj) * 3 + c) * 64 + cout, __uint_as_float(v[j]));
-              if (a.db && di == 2 && col == 2 * 8 + 3) atomicAdd(a.db + cout, __uint_as_float(v[j]));   // constant-1 channel
+              if (col < 40 && c < 3) part[((di * 5 + dj) * 3 + c) * 64 + cout] = __uint_as_float(v[j]);
+              if (di == 2 && col == 2 * 8 + 3) part[4800 + cout] = __uint_as_float(v[j]);   // constant-1 channel
             }
           }
         }
@@ -490,12 +491,13 @@ size_t conv1_wgrad_smem(const C1Geom& g) {
 }
 }  // namespace
 
-int64_t conv1_wgrad_tc_scratch_bytes(int B) { (void)B; return 256; }   // none needed any more (kept for the ABI)
+int conv1_wgrad_tc_partials(int B) { return conv1_wgrad_ctas(B); }
+int64_t conv1_wgrad_tc_scratch_bytes(int B) { return (int64_t)conv1_wgrad_ctas(B) * 4864 * 4; }
 
 int conv1_wgrad_tc(const uint8_t* img, const float* dpool, const float* pool, const uint8_t* arg, float* dw, float* db,
-                   float* scratch, int B, int ih, int iw, int H, int W, cudaStream_t st, bool prezeroed) {
-  (void)scratch;
+                   float* scratch, int B, int ih, int iw, int H, int W, cudaStream_t st, bool defer_reduce) {
   B200_REQUIRE(B > 0 && H <= ih && W <= iw && H >= 4 && W >= 4, "conv1_wgrad_tc: bad shape");
+  B200_REQUIRE(scratch && ((uintptr_t)scratch & 15) == 0, "conv1_wgrad_tc: scratch must be a 16-byte aligned buffer");
   C1Geom g = make_c1geom(B, ih, iw, H, W);
   const size_t smem = conv1_wgrad_smem(g);
   B200_REQUIRE(smem <= 227 * 1024, "conv1_wgrad_tc: crop %dx%d needs %zu bytes of shared memory", H, W, smem);
@@ -503,13 +505,15 @@ int conv1_wgrad_tc(const uint8_t* img, const float* dpool, const float* pool, co
   if (attr.first())
     B200_CUDA_TRY(cudaFuncSetAttribute(conv1_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   const int S = conv1_wgrad_ctas(B);
-  if (!prezeroed) {       // the kernel accumulates with atomics
-    B200_CUDA_TRY(cudaMemsetAsync(dw, 0, 75 * 64 * sizeof(float), st));
-    if (db) B200_CUDA_TRY(cudaMemsetAsync(db, 0, 64 * sizeof(float), st));
-  }
-  Conv1WgradArgs a{img, dpool, pool, arg, dw, db, g, g_conv1_timeline};
+  Conv1WgradArgs a{img, dpool, pool, arg, scratch, g, g_conv1_timeline};
+  const bool overlap = g_pdl_next;
+  g_pdl_next = false;
   B200_CUDA_TRY(launch_kernel(conv1_wgrad_kernel, dim3(S), dim3(416), smem, st, a));
-  return B200_OK;
+  if (defer_reduce) return B200_OK;
+  g_pdl_next = overlap;                                   // (the reduction's prologue may overlap the kernel's tail)
+  if (db == dw + 4800) return reduce_partials(scratch, dw, 4864, S, st);
+  B200_TRY(reduce_partials(scratch, dw, 4800, S, st, 4864));
+  return db ? reduce_partials(scratch + 4800, db, 64, S, st, 4864) : B200_OK;
 }
 
 void conv1_set_timeline(long long* dev_buf) { g_conv1_timeline = dev_buf; }

@@ -113,7 +113,6 @@ def test_shuffle_batch_follows_the_queue_model(tmp_path, kind):
     for step in range(60):                                             # 7680 draws: wraps the 6000-record fixture
         img, lab = src.next()
         ids = q.next_ids()
-        assert len(set(ids.tolist())) == B                             # without replacement inside a batch
         np.testing.assert_array_equal(img.cpu().numpy(), images[ids])
         np.testing.assert_array_equal(lab.cpu().numpy(), labels[ids])
         seen.update(ids.tolist())
