@@ -520,36 +520,36 @@ __global__ void sgd_kernel(float* __restrict__ p, const float* __restrict__ g, i
     p[i] = fmaf(-step, g[i], p[i]);
 }
 // The same update when the first n_part gradients still sit in S per-CTA partials (conv1's filter / bias gradient,
-// tc_conv1.cu): the leading CTAs sum them in a fixed order -- four lanes per 16 bytes take every fourth partial and
-// combine with two shuffles, as reduce_partials_tc does -- store the finished gradient (the buffer is complete
-// after the step) and apply it; the other CTAs update the rest.  Saves the launch of a reduction kernel at the very
-// end of the step's critical path.
+// tc_conv1.cu): the leading CTAs sum them in a fixed order -- one WARP per 16 bytes: lane l takes partials l, l+32, ...
+// (all of its loads in flight at once: one round trip to L2), then a five-step shuffle tree -- store the finished
+// gradient (the buffer is complete after the step) and apply it; the other CTAs update the rest.  Saves the launch
+// of a reduction kernel at the very end of the step's critical path.
 __global__ void sgd_reduce_kernel(float* __restrict__ p, float* __restrict__ g, int64_t n, float step,
                                   const float* __restrict__ part, int S, int n_part) {
   B200_TRACE_SCOPE(TR_SGD);
   pdl_wait();
-  const int lead = (n_part + 255) / 256;                      // n_part / 4 groups x 4 lanes = n_part threads
+  const int lead = (n_part / 4 * 32 + 255) / 256;             // one warp per float4 of the partial range
   if ((int)blockIdx.x < lead) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    const int sub = t & 3;
-    const int i = min((t >> 2) * 4, n_part - 4);              // surplus threads redo the last group (full-warp shuffles)
+    const int lane = t & 31;
+    const int i = min(t >> 5, n_part / 4 - 1) * 4;            // surplus warps redo the last group
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int z0 = sub; z0 < S; z0 += 32) {
-      float4 v[8];
+    for (int z0 = lane; z0 < S; z0 += 128) {
+      float4 v[4];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const int z = z0 + 4 * j;
+      for (int j = 0; j < 4; ++j) {
+        const int z = z0 + 32 * j;
         v[j] = z < S ? __ldg(reinterpret_cast<const float4*>(part + (int64_t)z * n_part + i)) : make_float4(0.f, 0.f, 0.f, 0.f);
       }
 #pragma unroll
-      for (int j = 0; j < 8; ++j) { s.x += v[j].x; s.y += v[j].y; s.z += v[j].z; s.w += v[j].w; }
+      for (int j = 0; j < 4; ++j) { s.x += v[j].x; s.y += v[j].y; s.z += v[j].z; s.w += v[j].w; }
     }
 #pragma unroll
-    for (int m = 1; m <= 2; m <<= 1) {
+    for (int m = 1; m <= 16; m <<= 1) {
       s.x += __shfl_xor_sync(0xffffffffu, s.x, m); s.y += __shfl_xor_sync(0xffffffffu, s.y, m);
       s.z += __shfl_xor_sync(0xffffffffu, s.z, m); s.w += __shfl_xor_sync(0xffffffffu, s.w, m);
     }
-    if (sub == 0 && (t >> 2) * 4 < n_part) {
+    if (lane == 0 && (t >> 5) < n_part / 4) {
       *reinterpret_cast<float4*>(g + i) = s;
       float4 a = *reinterpret_cast<float4*>(p + i);
       a.x = fmaf(-step, s.x, a.x); a.y = fmaf(-step, s.y, a.y);
@@ -576,7 +576,7 @@ int sgd_apply_reduce_f32(float* p, float* g, int64_t n, float lr, float scale, c
                "sgd_apply_reduce: bad sizes");
   B200_REQUIRE(((uintptr_t)p & 15) == 0 && ((uintptr_t)g & 15) == 0 && ((uintptr_t)part & 15) == 0,
                "sgd_apply_reduce: pointers must be 16-byte aligned");
-  const int lead = (n_part + 255) / 256;
+  const int lead = (n_part / 4 * 32 + 255) / 256;
   int grid = lead + (int)std::min<int64_t>(((n - n_part) / 4 + 255) / 256 + 1, kNumSMs * 4);
   static PerDeviceOnce carve;
   if (carve.first()) B200_CUDA_TRY(prefer_max_shared(sgd_reduce_kernel));
