@@ -441,6 +441,8 @@ def main():
     barrier()
     ms_e2e = e0.elapsed_time(e1)
     clocks = sampler.stop() if sampler else None
+    if world > 1:      # after a real exchange step: every replica holds bit-identical parameters
+        assert ex.replicas_identical(eng.params), "replicas diverged"
 
     # ---- live per-site timing for the roofline (eager, CUDA events between launch sites) --------
     reset()
@@ -485,7 +487,6 @@ def main():
     t = torch.tensor([ms_cold, ms_hot, ms_e2e, ms_restore], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        assert ex.replicas_identical(eng.params), "replicas diverged"
     ms_cold, ms_hot, ms_e2e, ms_restore = (float(x) for x in t.cpu())
     import math
     assert math.isfinite(loss_seen) and math.isfinite(loss_hot), ("non-finite loss in a timed region", loss_seen, loss_hot)

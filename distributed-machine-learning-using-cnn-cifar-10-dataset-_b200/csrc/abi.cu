@@ -76,6 +76,16 @@ struct b200_model {
 
 enum { P_W1 = 0, P_B1, P_W2, P_B2, P_FW1, P_FB1, P_FW2, P_FB2, P_FW3, P_FB3 };
 
+// bf16 mode has two schedules.  The script's own widths (64 / 64 conv channels, FC <= 256 wide) run the fused,
+// multi-stream step tuned for them (conv + pool in one kernel, FC tail in two kernels, gradients gathered through the
+// pools).  Any other width (BASELINE.json's width-scaled model: 256 / 256 channels, FC 768 / 384) runs the layer-by-
+// layer schedule below it: the contractions -- conv2 forward / input gradient / filter gradient, FC1, FC2 -- on the
+// same tcgen05 kernels (channel-blocked), pooling, the 3-channel conv1, the 10-wide FC3 and the loss on the fp32
+// kernels of the validation mode.
+static bool fused_bf16_shapes(const b200_config& c) {
+  return c.c1 == 64 && c.c2 == 64 && c.f1 % 32 == 0 && c.f2 % 32 == 0 && c.f2 <= 256;
+}
+
 extern "C" {
 
 const char* b200_last_error(void) { return g_err; }
@@ -93,8 +103,9 @@ int b200_create(const b200_config* c, b200_handle* out) {
   B200_REQUIRE(c->n_cls > 0 && c->n_cls <= 16, "b200_create: n_cls must be in 1..16");
   B200_REQUIRE(c->mode == B200_MODE_FP32 || c->mode == B200_MODE_BF16, "b200_create: unknown mode %d", c->mode);
   if (c->mode == B200_MODE_BF16)
-    B200_REQUIRE(c->batch % 8 == 0 && c->c1 == 64 && c->c2 == 64 && c->f1 % 32 == 0 && c->f2 % 8 == 0 && c->f2 <= 256,
-                 "b200_create: bf16 mode needs batch %% 8 == 0, 64/64 conv channels, f1 %% 32 == 0, f2 %% 8 == 0, f2 <= 256");
+    B200_REQUIRE(c->batch % 8 == 0 && c->c1 % 64 == 0 && c->c2 % 64 == 0 && c->c1 <= 256 && c->c2 <= 256 &&
+                     c->f1 % 8 == 0 && c->f2 % 8 == 0,
+                 "b200_create: bf16 mode needs batch %% 8 == 0, conv channels in {64, 128, 192, 256}, f1 %% 8 == 0, f2 %% 8 == 0");
   b200_model* h = new (std::nothrow) b200_model();
   B200_REQUIRE(h, "b200_create: out of host memory");
   h->cfg = *c;
@@ -128,10 +139,11 @@ int b200_create(const b200_config* c, b200_handle* out) {
   scratch = std::max(scratch, conv5x5_wgrad_scratch_bytes(c->batch, h->h1, h->w1, c->c1, c->c2));
   scratch = std::max(scratch, colsum_scratch_bytes(c->batch, std::max(c->f1, std::max(c->f2, c->n_cls))));
   scratch = std::max(scratch, conv1_wgrad_tc_scratch_bytes(c->batch));
-  scratch = std::max(scratch, conv5x5_wgrad_tc_scratch_bytes(c->batch) +
-                                  colsum_scratch_bytes(c->batch * h->h1 * h->w1, c->c2));
+  if (c->c1 % 64 == 0 && c->c2 % 64 == 0)
+    scratch = std::max(scratch, conv5x5_wgrad_tc_scratch_bytes(c->batch, c->c1, c->c2));
+  scratch = std::max(scratch, colsum_scratch_bytes(c->batch * h->h1 * h->w1, c->c2));
   h->add("scratch", scratch, 1);
-  h->add("scratch2", conv5x5_wgrad_tc_scratch_bytes(c->batch), 1);      // conv2 wgrad runs beside conv1 wgrad
+  h->add("scratch2", conv5x5_wgrad_tc_scratch_bytes(c->batch), 1);      // conv2 wgrad (64 -> 64) runs beside conv1 wgrad
   h->add("db2_part", B * 64, 4);      // conv2's bias gradient: one partial per dgrad CTA, summed in a fixed order
   h->add("w2_packed", conv5x5_packed_bytes(c->c1, c->c2), 1);
   h->add("fc1_part", (int64_t)fc_fwd_tc_splits(c->batch, h->flat, c->f1) * B * c->f1, 4);
@@ -264,6 +276,22 @@ static int forward_impl(b200_handle h, const uint8_t* images, const int32_t* lab
   float *full1 = h->ptr<float>("full1"), *full2 = h->ptr<float>("full2"), *logits = h->ptr<float>("logits");
   const bool fused1 = tc && conv1_tc_supported(c.crop_h, c.crop_w, c.c_in, c.c1);
   h->last_images = images;
+  if (tc && !fused_bf16_shapes(c)) {
+    // ---- layer-by-layer bf16 schedule (widths other than the script's) ------------------------------------------
+    SITE("crop_cast", crop_cast_f32(images, x, c.batch, c.img_h, c.img_w, c.crop_h, c.crop_w, c.c_in, st));
+    SITE("conv1_fwd", conv5x5_fwd_f32(x, h->P(P_W1), h->P(P_B1), conv1, c.batch, c.crop_h, c.crop_w, c.c_in, c.c1, 1, st));
+    SITE("pool1_fwd", maxpool_fwd_f32(conv1, pool1, h->ptr<uint8_t>("arg1"), c.batch, c.crop_h, c.crop_w, c.c1, st));
+    SITE("weights_prep", pack_conv_weights(h->P(P_W2), h->ptr<void>("w2_packed"), c.c1, c.c2, st));
+    SITE("conv2_fwd", conv5x5_fwd_tc(pool1, h->ptr<void>("w2_packed"), h->P(P_B2), conv2, c.batch, h->h1, h->w1, c.c1, c.c2, 1, st));
+    SITE("pool2_fwd", maxpool_fwd_f32(conv2, pool2, h->ptr<uint8_t>("arg2"), c.batch, h->h1, h->w1, c.c2, st));
+    SITE("full1_fwd", fc_fwd_tc(pool2, h->P(P_FW1), h->P(P_FB1), full1, c.batch, h->flat, c.f1, 1, st));
+    SITE("full2_fwd", fc_fwd_tc(full1, h->P(P_FW2), h->P(P_FB2), full2, c.batch, c.f1, c.f2, 1, st));
+    SITE("full3_fwd", fc_fwd_f32(full2, h->P(P_FW3), h->P(P_FB3), logits, c.batch, c.f2, c.n_cls, 1, st));
+    SITE("head", head_f32(logits, labels, h->ptr<float>("loss"), h->ptr<float>("dlogits"), h->ptr<int32_t>("pred"),
+                          h->ptr<int32_t>("n_correct"), h->ptr<int32_t>("n_bad"), c.batch, c.n_cls, st));
+    h->forward_done = true;
+    return B200_OK;
+  }
   // bf16 mode: the weight images the tensor-core kernels stream (conv2 filter, W2) depend only on the
   // parameters, so they are rebuilt on a side stream while conv1 runs (every step: the caller or the
   // last update may have changed the parameters).
@@ -384,6 +412,27 @@ static int backward_impl(b200_handle h, void* stream, const P2PCtx* px, bool def
   float *dlogits = h->ptr<float>("dlogits"), *dfull2 = h->ptr<float>("dfull2"), *dfull1 = h->ptr<float>("dfull1");
   float *dpool2 = h->ptr<float>("dpool2"), *dconv2 = h->ptr<float>("dconv2");
   float *dpool1 = h->ptr<float>("dpool1"), *dconv1 = h->ptr<float>("dconv1");
+  if (tc && !fused_bf16_shapes(c)) {
+    // ---- layer-by-layer bf16 schedule (see fused_bf16_shapes) ----------------------------------------------------
+    B200_REQUIRE(!px, "the overlapped exchange needs the script's own layer widths");
+    SITE("full3_bwd", fc_bwd_f32(h->ptr<float>("full2"), h->P(P_FW3), dlogits, dfull2, h->G(P_FW3), h->G(P_FB3),
+                                 scratch, c.batch, c.f2, c.n_cls, 1, st));
+    SITE("full2_bwd", fc_bwd_tc(h->ptr<float>("full1"), h->P(P_FW2), dfull2, dfull1, h->G(P_FW2), c.batch, c.f1, c.f2, 1, st));
+    TRY(colsum_f32(dfull2, h->G(P_FB2), scratch, c.batch, c.f2, st));
+    SITE("full1_bwd", fc_bwd_tc(h->ptr<float>("pool2"), h->P(P_FW1), dfull1, dpool2, h->G(P_FW1), c.batch, h->flat, c.f1, 0, st));
+    TRY(colsum_f32(dfull1, h->G(P_FB1), scratch, c.batch, c.f1, st));
+    SITE("pool2_bwd", maxpool_bwd_f32(dpool2, h->ptr<uint8_t>("arg2"), h->ptr<float>("conv2"), dconv2, c.batch, h->h1,
+                                      h->w1, c.c2, 1, st));
+    SITE("conv2_wgrad", conv5x5_wgrad_tc(h->ptr<float>("pool1"), dconv2, h->G(P_W2), scratch, c.batch, h->h1, h->w1, c.c1,
+                                         c.c2, st));
+    TRY(colsum_f32(dconv2, h->G(P_B2), scratch, c.batch * h->h1 * h->w1, c.c2, st));
+    SITE("conv2_dgrad", conv5x5_dgrad_tc(dconv2, h->ptr<void>("w2_packed"), dpool1, c.batch, h->h1, h->w1, c.c1, c.c2, st));
+    SITE("pool1_bwd", maxpool_bwd_f32(dpool1, h->ptr<uint8_t>("arg1"), h->ptr<float>("conv1"), dconv1, c.batch,
+                                      c.crop_h, c.crop_w, c.c1, 1, st));
+    SITE("conv1_wgrad", conv5x5_wgrad_f32(h->ptr<float>("x"), dconv1, h->G(P_W1), h->G(P_B1), scratch, c.batch,
+                                          c.crop_h, c.crop_w, c.c_in, c.c1, st));
+    return B200_OK;
+  }
   if (tc) {
     // Dependency graph of the bf16 backward (dfull1 and everything above it came from fc_tail):
     //   main : FC1 dX -> pool2 bwd -> conv2 dgrad -> conv1 wgrad
@@ -541,7 +590,8 @@ int b200_p2p_sgd_apply(b200_handle h, const void* const* peer_grads, void* const
 int b200_train_step(b200_handle h, const uint8_t* images, const int32_t* labels, float lr, void* stream) {
   B200_READY(h);
   const b200_config& c = h->cfg;
-  const bool fuse = c.mode == B200_MODE_BF16 && !h->profiling && conv1_tc_supported(c.crop_h, c.crop_w, c.c_in, c.c1) &&
+  const bool fuse = c.mode == B200_MODE_BF16 && fused_bf16_shapes(c) && !h->profiling &&
+                    conv1_tc_supported(c.crop_h, c.crop_w, c.c_in, c.c1) &&
                     h->p_off[P_W1] == 0 && h->p_off[P_B1] == 4800;
   if (!fuse) {
     TRY(b200_forward_backward(h, images, labels, stream));
@@ -621,7 +671,11 @@ int b200_launches_per_step(b200_handle h, int32_t* n) {
   // forward 9; fc_bwd 3 x (dw, colsum x2, dx); pool bwd x2; conv wgrad 2 x (gemm, reduce, colsum x2);
   // dgrad (rot180 + gemm); sgd
   *n = 9 + 12 + 2 + 8 + 2 + 1;
-  if (h->cfg.mode == B200_MODE_BF16) {
+  if (h->cfg.mode == B200_MODE_BF16 && !fused_bf16_shapes(h->cfg)) {
+    // layer-by-layer schedule: forward 10 | FC3 bwd 4, FC2 / FC1 bwd 2 + 2 each, pool2 bwd, conv2 wgrad 2 + colsum 2, dgrad,
+    // pool1 bwd, conv1 wgrad 4 | sgd
+    *n = 10 + 4 + 4 + 4 + 1 + 4 + 1 + 1 + 4 + 1;
+  } else if (h->cfg.mode == B200_MODE_BF16) {
     // conv1 (3 or 1), conv2, pool2, FC1 split-K, tail x2 | FC1 bwd x2, pool2 bwd, conv2 wgrad x2, dgrad, conv1 wgrad (2 or 1+4), sgd
     const bool f1 = conv1_tc_supported(h->cfg.crop_h, h->cfg.crop_w, h->cfg.c_in, h->cfg.c1);
     *n = (f1 ? 1 : 3) + 2 + 1 + 3 + 2 + 2 + 1 + (f1 ? 1 : 5) + 1 +
@@ -769,10 +823,16 @@ int b200_conv5x5_wgrad_bf16_scratch_bytes(int32_t batch, int64_t* nbytes) {
   *nbytes = conv5x5_wgrad_tc_scratch_bytes(batch);
   return B200_OK;
 }
+int b200_conv5x5_wgrad_bf16_scratch_bytes_c(int32_t batch, int32_t c_in, int32_t c_out, int64_t* nbytes) {
+  B200_REQUIRE(nbytes && batch > 0 && c_in > 0 && c_out > 0 && c_in % 64 == 0 && c_out % 64 == 0, "bad argument");
+  *nbytes = conv5x5_wgrad_tc_scratch_bytes(batch, c_in, c_out);
+  return B200_OK;
+}
 int b200_conv5x5_wgrad_bf16(const float* x, const float* dy, float* dw, void* scratch, int64_t scratch_bytes,
                             int32_t batch, int32_t h, int32_t wd, int32_t c_in, int32_t c_out, void* stream) {
   B200_REQUIRE(x && dy && dw && scratch, "null pointer");
-  B200_REQUIRE(batch > 0 && scratch_bytes >= conv5x5_wgrad_tc_scratch_bytes(batch), "scratch too small");
+  B200_REQUIRE(batch > 0 && c_in > 0 && c_out > 0 && c_in % 64 == 0 && c_out % 64 == 0, "channels must be multiples of 64");
+  B200_REQUIRE(scratch_bytes >= conv5x5_wgrad_tc_scratch_bytes(batch, c_in, c_out), "scratch too small");
   return conv5x5_wgrad_tc(x, dy, dw, (float*)scratch, batch, h, wd, c_in, c_out, (cudaStream_t)stream);
 }
 int b200_conv5x5_dgrad_pool_bf16(const float* dpool, const float* pool, const uint8_t* arg, const void* w_packed,

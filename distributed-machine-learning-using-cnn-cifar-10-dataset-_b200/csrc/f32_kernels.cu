@@ -524,6 +524,34 @@ __global__ void sgd_kernel(float* __restrict__ p, const float* __restrict__ g, i
 // (all of its loads in flight at once: one round trip to L2), then a five-step shuffle tree -- store the finished
 // gradient (the buffer is complete after the step) and apply it; the other CTAs update the rest.  Saves the launch
 // of a reduction kernel at the very end of the step's critical path.
+// one warp: sum over z < S of part[z * stride + i .. i+3], lane l taking z = l, l + 32, ... and a five-step shuffle
+// tree -- THE summation order of conv1's gradient partials, shared by the update kernel and the stand-alone reduction
+__device__ __forceinline__ float4 warp_sum_partials(const float* __restrict__ part, int S, int stride, int i, int lane) {
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int z0 = lane; z0 < S; z0 += 128) {
+    float4 v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int z = z0 + 32 * j;
+      v[j] = z < S ? __ldg(reinterpret_cast<const float4*>(part + (int64_t)z * stride + i)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { s.x += v[j].x; s.y += v[j].y; s.z += v[j].z; s.w += v[j].w; }
+  }
+#pragma unroll
+  for (int m = 1; m <= 16; m <<= 1) {
+    s.x += __shfl_xor_sync(0xffffffffu, s.x, m); s.y += __shfl_xor_sync(0xffffffffu, s.y, m);
+    s.z += __shfl_xor_sync(0xffffffffu, s.z, m); s.w += __shfl_xor_sync(0xffffffffu, s.w, m);
+  }
+  return s;
+}
+__global__ void reduce_partials_warp_kernel(const float* __restrict__ part, float* __restrict__ out, int n, int S, int stride) {
+  pdl_wait();
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = min(t >> 5, n / 4 - 1) * 4;                   // surplus warps redo the last group
+  const float4 s = warp_sum_partials(part, S, stride, i, t & 31);
+  if ((t & 31) == 0 && (t >> 5) < n / 4) *reinterpret_cast<float4*>(out + i) = s;
+}
 __global__ void sgd_reduce_kernel(float* __restrict__ p, float* __restrict__ g, int64_t n, float step,
                                   const float* __restrict__ part, int S, int n_part) {
   B200_TRACE_SCOPE(TR_SGD);
@@ -533,22 +561,7 @@ __global__ void sgd_reduce_kernel(float* __restrict__ p, float* __restrict__ g, 
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = t & 31;
     const int i = min(t >> 5, n_part / 4 - 1) * 4;            // surplus warps redo the last group
-    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int z0 = lane; z0 < S; z0 += 128) {
-      float4 v[4];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int z = z0 + 32 * j;
-        v[j] = z < S ? __ldg(reinterpret_cast<const float4*>(part + (int64_t)z * n_part + i)) : make_float4(0.f, 0.f, 0.f, 0.f);
-      }
-#pragma unroll
-      for (int j = 0; j < 4; ++j) { s.x += v[j].x; s.y += v[j].y; s.z += v[j].z; s.w += v[j].w; }
-    }
-#pragma unroll
-    for (int m = 1; m <= 16; m <<= 1) {
-      s.x += __shfl_xor_sync(0xffffffffu, s.x, m); s.y += __shfl_xor_sync(0xffffffffu, s.y, m);
-      s.z += __shfl_xor_sync(0xffffffffu, s.z, m); s.w += __shfl_xor_sync(0xffffffffu, s.w, m);
-    }
+    const float4 s = warp_sum_partials(part, S, n_part, i, lane);
     if (lane == 0 && (t >> 5) < n_part / 4) {
       *reinterpret_cast<float4*>(g + i) = s;
       float4 a = *reinterpret_cast<float4*>(p + i);
@@ -582,6 +595,11 @@ int sgd_apply_reduce_f32(float* p, float* g, int64_t n, float lr, float scale, c
   if (carve.first()) B200_CUDA_TRY(prefer_max_shared(sgd_reduce_kernel));
   B200_CUDA_TRY(launch_kernel(sgd_reduce_kernel, dim3(grid), dim3(256), 0, st, p, g, n, lr * scale, part, S, n_part));
   B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+int reduce_partials_warp(const float* part, float* out, int n, int S, int stride, cudaStream_t st) {
+  B200_REQUIRE(part && out && n > 0 && n % 4 == 0 && S > 0 && stride % 4 == 0, "reduce_partials_warp: bad argument");
+  B200_CUDA_TRY(launch_kernel(reduce_partials_warp_kernel, dim3((n / 4 * 32 + 255) / 256), dim3(256), 0, st, part, out, n, S, stride));
   return B200_OK;
 }
 int sgd_apply_f32(float* p, const float* g, int64_t n, float lr, float scale, cudaStream_t st) {

@@ -30,6 +30,9 @@ int sgd_apply_f32(float* p, const float* g, int64_t n, float lr, float scale, cu
 // the update with the first n_part gradients still in S partials [S][n_part] (summed in a fixed order, stored to g)
 int sgd_apply_reduce_f32(float* p, float* g, int64_t n, float lr, float scale, const float* part, int S, int n_part,
                          cudaStream_t st);
+// the same sum in the order sgd_apply_reduce_f32 uses (one warp per 16 bytes): what conv1's gradient goes through when
+// the update does not follow at once, so that both routes give the same bits
+int reduce_partials_warp(const float* part, float* out, int n, int S, int stride, cudaStream_t st);
 // out[i] = sum over z < S of part[z * stride + i], fixed order (tc_conv.cu); n, stride multiples of 4 (stride 0 = n)
 int reduce_partials(const float* part, float* out, int n, int S, cudaStream_t st, int stride = 0);
 
@@ -71,7 +74,7 @@ int conv5x5_dgrad_pool_tc(const float* dpool, const float* pool, const uint8_t* 
                           int* n_part = nullptr);               //   [*n_part][64] for a fixed-order reduction (<= B of them)
 int conv5x5_wgrad_pool_tc(const float* x, const float* dpool, const float* pool, const uint8_t* arg, float* dw,
                           float* scratch, int B, int H, int W, int Cin, int Cout, cudaStream_t st);
-int64_t conv5x5_wgrad_tc_scratch_bytes(int B);
+int64_t conv5x5_wgrad_tc_scratch_bytes(int B, int Cin = 64, int Cout = 64);
 // x_bf16 / dy_bf16 (optional, both or none): bf16 copies of x / dy, read instead of the fp32 tensors
 // db_part / db / n_db_part (optional): the per-CTA bias-gradient sums [n_db_part][64] of conv5x5_dgrad_pool_tc, reduced
 // to db [64] in the same launch as the filter-gradient partials

@@ -236,8 +236,13 @@ struct ConvArgs {
 // stages, so that strip + ring stay under half an SM's shared memory).  MINB = 2 asks for two CTAs per SM: with more
 // images than SMs one CTA's MMAs then overlap the other's strip fill and epilogue / pooling (every phase of a CTA is
 // serial in itself), which is what large batches need; the single-wave batch 128 keeps the one-CTA shape.
-template <bool DGRAD, int KSTEPS, bool POOL = false, int STAPS = 5, int MINB = 1>
+// KSPLIT (with STAPS = 1): a stage holds 1/KSPLIT of a tap's contraction channels -- wide layers (256 channels: 33 KB
+// per tap beside a 166 KB strip) stream the filter as (tap, channel-half) pieces.
+template <bool DGRAD, int KSTEPS, bool POOL = false, int STAPS = 5, int MINB = 1, int KSPLIT = 1>
 __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_constant__ ConvArgs a) {
+  static_assert(KSPLIT == 1 || STAPS == 1, "channel-split stages are single-tap stages");
+  static_assert(KSTEPS % KSPLIT == 0, "KSPLIT must divide the k-steps");
+  constexpr int KST = KSTEPS / KSPLIT;    // k-steps per ring stage and tap
   B200_TRACE_SCOPE(DGRAD ? TR_CONV2_DGRAD : TR_CONV2_FWD);
   constexpr int BN = 64;
   constexpr int NISS = 4;                 // MMA-issuing warps (warps 4..7); warp 8 streams the filter
@@ -246,10 +251,10 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
   const int kchunks = KSTEPS * 2;         // KC = 16 * KSTEPS
   const int strip_bytes = kchunks * g.ch_stride;
   // weight stage: MN-major [BN/8 groups][KC k][16B] (SBO = KC*16+16)  |  K-major [KC/8 chunks][BN rows][16B]
-  const int w_mn_sbo = g.KC * 16 + 16, w_k_lbo = BN * 16 + 16;
-  const int wtap = ((DGRAD ? kchunks * w_k_lbo : (BN / 8) * w_mn_sbo) + 127) & ~127;   // one tap's operand image
+  const int w_mn_sbo = (g.KC / KSPLIT) * 16 + 16, w_k_lbo = BN * 16 + 16;
+  const int wtap = ((DGRAD ? (kchunks / KSPLIT) * w_k_lbo : (BN / 8) * w_mn_sbo) + 127) & ~127;   // one tap's (piece of the) operand image
   const int wstage = STAPS * wtap;
-  constexpr int ROUNDS = 25 / STAPS;      // ring rounds per image
+  constexpr int ROUNDS = 25 / STAPS * KSPLIT;      // ring rounds per image
   uint8_t* strip = smem;
   uint8_t* wring = smem + ((strip_bytes + 127) & ~127);
   uint8_t* ctrl = wring + g.nstages * wstage;
@@ -455,7 +460,8 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
       const int rot = STAPS == 5 ? (int)((blockIdx.x + blockIdx.y) % 5u) * 5 : (int)((blockIdx.x * 7u + blockIdx.y) % 25u);
       int di = rot / 5;                                     // filter-row rotation (same in the producer warp)
       int dj1 = rot % 5;                                    // STAPS == 1: the tap inside the row
-      uint32_t q = 0;                                       // taps issued so far (0 = the accumulators are not initialised)
+      uint32_t q = 0;                                       // stage pieces issued so far (0 = the accumulators are not initialised)
+      int hh = 0;                                           // KSPLIT > 1: which piece of the tap's channels
       for (int r = 0; r < ROUNDS; ++r) {
         const int s = r % g.nstages;
         const uint32_t ph = (r / g.nstages) & 1;
@@ -465,7 +471,7 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
 #pragma unroll
         for (int tt = 0; tt < STAPS; ++tt, ++q) {
           const int dj = STAPS == 5 ? tt : dj1;
-          const uint32_t a_tap = a_lo0 + (uint32_t)((di - 2) * g.P + (dj - 2));    // a tap is a slot offset
+          const uint32_t a_tap = a_lo0 + (uint32_t)((di - 2) * g.P + (dj - 2)) + (uint32_t)(hh * KST) * a_kstep;    // a tap is a slot offset
           // dgrad correlates with the filter rotated by 180 degrees: a five-tap stage holds forward row 4-di, read
           // backwards; a one-tap stage holds forward tap (4-di, 4-dj) itself
           const uint32_t b_tap = b_row + (uint32_t)(STAPS == 5 ? (DGRAD ? 4 - dj : dj) : 0) * (wtap >> 4);
@@ -473,7 +479,7 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
             uint32_t a_lo = a_tap + t * 128, b_lo = b_tap;
             const uint32_t d = tmem + t * BN;
 #pragma unroll
-            for (int ks = 0; ks < KSTEPS; ++ks) {
+            for (int ks = 0; ks < KST; ++ks) {
               umma_bf16(d, desc_join(a_lo, a_hi), desc_join(b_lo, b_hi), idesc, q | (uint32_t)ks);
               a_lo += a_kstep; b_lo += b_kstep;
             }
@@ -481,7 +487,7 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
         }
         umma_commit(smem_u32(wempty + s));        // arrives when this warp's MMAs on the stage are done
         if (STAPS == 5) { if (++di == 5) di = 0; }
-        else if (++dj1 == 5) { dj1 = 0; if (++di == 5) di = 0; }
+        else if (++hh == KSPLIT) { hh = 0; if (++dj1 == 5) { dj1 = 0; if (++di == 5) di = 0; } }
       }
       umma_commit(smem_u32(accum));
       if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && w == 0) a.timeline[4] = clock64();
@@ -500,7 +506,8 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
       }
       const int img = (a.cout_f / 8) * (a.cin_f * 16 + 16);             // bytes of one packed tap
       const int rot = STAPS == 5 ? (int)((blockIdx.x + blockIdx.y) % 5u) * 5 : (int)((blockIdx.x * 7u + blockIdx.y) % 25u);
-      int di = rot / 5, dj1 = rot % 5;                                 // same rotation as the MMA warps
+      int di = rot / 5, dj1 = rot % 5, hh = 0;                         // same rotation as the MMA warps
+      const int gstride = a.cin_f * 16 + 16;                           // packed: bytes between cout groups of a tap
       for (int r = 0; r < ROUNDS; ++r) {
         const int s = r % g.nstages;
         const uint32_t ph = (r / g.nstages) & 1;
@@ -508,22 +515,29 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
         const uint32_t bar = smem_u32(wfull + s);
         // packed (forward) taps to fetch: a filter row in forward order, or the single tap the MMA warps want next
         const int ftap0 = STAPS == 5 ? (DGRAD ? 4 - di : di) * 5 : (DGRAD ? (4 - di) * 5 + (4 - dj1) : di * 5 + dj1);
-        if (!DGRAD) {     // N-groups nc0/8 .. +8 of a tap are contiguous: one copy per tap
+        if (!DGRAD && KSPLIT == 1) {     // N-groups nc0/8 .. +8 of a tap are contiguous: one copy per tap
           const uint32_t bytes = (BN / 8) * w_mn_sbo;
           mbar_arrive_expect_tx(bar, STAPS * bytes);
           for (int j = 0; j < STAPS; ++j)
             bulk_g2s(smem_u32(wring + s * wstage + j * wtap),
                      a.wp + (size_t)(ftap0 + j) * img + (size_t)(nc0 / 8) * w_mn_sbo, bytes, bar);
+        } else if (!DGRAD) {             // a piece of the contraction channels: one copy per cout group
+          const uint32_t bytes = (uint32_t)(g.KC / KSPLIT) * 16;
+          mbar_arrive_expect_tx(bar, (BN / 8) * bytes);
+          const uint8_t* src = a.wp + (size_t)ftap0 * img + (size_t)(nc0 / 8) * gstride + (size_t)hh * bytes;
+          for (int gi = 0; gi < BN / 8; ++gi)
+            bulk_g2s(smem_u32(wring + s * wstage + gi * w_mn_sbo), src + (size_t)gi * gstride, bytes, bar);
         } else {          // read K-major: per k-chunk (forward cout group) the 64 rows nc0.. are contiguous
-          mbar_arrive_expect_tx(bar, (uint32_t)STAPS * kchunks * BN * 16);
+          constexpr int KCS = 2 * KSTEPS / KSPLIT;                      // chunks per stage and tap
+          mbar_arrive_expect_tx(bar, (uint32_t)STAPS * KCS * BN * 16);
           for (int j = 0; j < STAPS; ++j) {
-            const uint8_t* src = a.wp + (size_t)(ftap0 + j) * img + (size_t)nc0 * 16;
+            const uint8_t* src = a.wp + (size_t)(ftap0 + j) * img + (size_t)nc0 * 16 + (size_t)(hh * KCS) * gstride;
             const uint32_t ws = smem_u32(wring + s * wstage + j * wtap);
-            for (int c = 0; c < kchunks; ++c) bulk_g2s(ws + c * w_k_lbo, src + (size_t)c * (a.cin_f * 16 + 16), BN * 16, bar);
+            for (int c = 0; c < KCS; ++c) bulk_g2s(ws + c * w_k_lbo, src + (size_t)c * gstride, BN * 16, bar);
           }
         }
         if (STAPS == 5) { if (++di == 5) di = 0; }
-        else if (++dj1 == 5) { dj1 = 0; if (++di == 5) di = 0; }
+        else if (++hh == KSPLIT) { hh = 0; if (++dj1 == 5) { dj1 = 0; if (++di == 5) di = 0; } }
       }
     }
     __syncwarp();
@@ -619,7 +633,10 @@ int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, 
   B200_REQUIRE((pg || ((uintptr_t)x & 15) == 0) && ((uintptr_t)wp & 15) == 0 && ((uintptr_t)y & 15) == 0,
                "conv5x5_tc: pointers must be 16-byte aligned");
   const int kchunks = KC / 8;
-  const int wtap = ((DGRAD ? kchunks * (64 * 16 + 16) : 8 * (KC * 16 + 16)) + 127) & ~127;
+  // wide layers (>= 128 contraction channels): single-tap stages, 256 channels in two pieces per tap
+  const bool wide = KC >= 128;
+  const int ksplit = KC == 256 ? 2 : 1;
+  const int wtap = ((DGRAD ? (kchunks / ksplit) * (64 * 16 + 16) : 8 * ((KC / ksplit) * 16 + 16)) + 127) & ~127;
   const int extra = pg ? pg->OH * pg->OW * 64 * 5 + 16 + 8 * 64 * 4 : 0;
   // ---- shape of the CTA: two per SM with single-tap filter stages once the grid exceeds one wave, else one per SM ----
   constexpr int kHalfSm = 113 * 1024;                    // (228 KB per SM - 1 KB reserved per CTA) / 2
@@ -633,6 +650,10 @@ int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, 
   if (two) {
     g = g2;
     g.nstages = nst2;
+  } else if (wide) {
+    g = g2;                                              // one image per CTA
+    g.nstages = std::min(MAX_WSTAGES, (227 * 1024 - strip2 - 256 - extra) / wtap);
+    B200_REQUIRE(g.nstages >= 2, "conv5x5_tc: image %dx%d with %d channels does not leave room for the filter ring", H, W, KC);
   } else {
     const int ipc = pool_out ? 1 : pick_ipc(B, H, W, KC);       // the fused pool works on one image per CTA
     g = (tma_ok && ipc == 1) ? make_geom_tma(B, H, W, KC, NC, pool_out ? H * W * 68 * 4 : 0) : make_geom(B, H, W, KC, NC, ipc);
@@ -644,7 +665,7 @@ int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, 
     B200_REQUIRE((int64_t)H * W * 68 * 4 <= (int64_t)(KC / 8) * g.ch_stride, "conv5x5_tc: conv tile does not fit the strip");
   }
   B200_REQUIRE(g.tiles * 64 <= 512, "conv5x5_tc: image %dx%d too large for one CTA's TMEM", H, W);
-  const int staps = two ? 1 : 5;
+  const int staps = (two || wide) ? 1 : 5;
   const int smem = ((kchunks * g.ch_stride + 127) & ~127) + g.nstages * staps * wtap + 256 + extra;
   B200_REQUIRE(smem <= 227 * 1024, "conv5x5_tc: %d bytes of shared memory needed", smem);
   void (*kern)(ConvArgs) = nullptr;
@@ -655,8 +676,8 @@ int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, 
   switch (KC / 16) {
     case 2: kern = conv5x5_tc_kernel<DGRAD, 2>; break;
     case 4: kern = two ? conv5x5_tc_kernel<DGRAD, 4, false, 1, 2> : conv5x5_tc_kernel<DGRAD, 4>; break;
-    case 8: kern = conv5x5_tc_kernel<DGRAD, 8>; break;
-    case 16: kern = conv5x5_tc_kernel<DGRAD, 16>; break;
+    case 8: kern = conv5x5_tc_kernel<DGRAD, 8, false, 1, 1>; break;
+    case 16: kern = conv5x5_tc_kernel<DGRAD, 16, false, 1, 1, 2>; break;
     default: B200_REQUIRE(false, "conv5x5_tc: contraction channels must be 32, 64, 128 or 256 (got %d)", KC);
   }
   B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
@@ -683,6 +704,7 @@ struct WgradArgs {
   const __nv_bfloat16* dyb;
   float* partial;      // [S][25][64][64]
   ConvGeom g;          // ipc = 1
+  int cin_tot, cout_tot;   // channels of x / dy; a CTA works on the 64 x 64 block blockIdx.z = (cin block) * (cout_tot / 64) + (cout block)
   int imgs_per_cta;
   int nbuf;             // 2 = double-buffered strips, 1 when two pairs do not fit in shared memory
   PoolGradSrc pg;       // when pg.dpool != null, dy is unused and the dY strip is gathered from the pooled gradient
@@ -694,21 +716,23 @@ __device__ __forceinline__ void wg_loaders_sync() { asm volatile("bar.sync 2, 25
 // x and dY strips of one image (64 channels each) filled together: every thread has its whole share of both
 // tensors (<= 5 + 5 chunks of 32 bytes) in flight before the first conversion, one memory round trip per image
 __device__ __forceinline__ void fill_strip_pair(uint8_t* xs, uint8_t* x2, uint8_t* ds, const float* __restrict__ x,
-                                                const float* __restrict__ dy, const ConvGeom& g, int n, int tid) {
+                                                const float* __restrict__ dy, const ConvGeom& g, int n, int tid,
+                                                int cx, int cd) {      // channels per pixel of x / dy (64-channel slice at x / dy)
   constexpr int U = 5;
   const int per_img = g.H * g.W * 8;
-  const float* sx = x + (int64_t)n * per_img * 8;
-  const float* sd = dy + (int64_t)n * per_img * 8;
+  const float* sx = x + (int64_t)n * g.H * g.W * cx;
+  const float* sd = dy + (int64_t)n * g.H * g.W * cd;
   for (int q0 = tid; q0 < per_img; q0 += WG_LOADERS * U) {
     float4 vx[U][2], vd[U][2];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int q = q0 + u * WG_LOADERS;
       if (q < per_img) {
-        vx[u][0] = __ldg(reinterpret_cast<const float4*>(sx + q * 8));
-        vx[u][1] = __ldg(reinterpret_cast<const float4*>(sx + q * 8) + 1);
-        vd[u][0] = __ldg(reinterpret_cast<const float4*>(sd + q * 8));
-        vd[u][1] = __ldg(reinterpret_cast<const float4*>(sd + q * 8) + 1);
+        const int64_t ox = (int64_t)(q >> 3) * cx + (q & 7) * 8, od = (int64_t)(q >> 3) * cd + (q & 7) * 8;
+        vx[u][0] = __ldg(reinterpret_cast<const float4*>(sx + ox));
+        vx[u][1] = __ldg(reinterpret_cast<const float4*>(sx + ox) + 1);
+        vd[u][0] = __ldg(reinterpret_cast<const float4*>(sd + od));
+        vd[u][1] = __ldg(reinterpret_cast<const float4*>(sd + od) + 1);
       }
     }
 #pragma unroll
@@ -731,17 +755,18 @@ __device__ __forceinline__ void fill_strip_pair(uint8_t* xs, uint8_t* x2, uint8_
 
 __device__ __forceinline__ void fill_strip_pair_bf16(uint8_t* xs, uint8_t* x2, uint8_t* ds, const __nv_bfloat16* __restrict__ x,
                                                      const __nv_bfloat16* __restrict__ dy, const ConvGeom& g, int n,
-                                                     int tid) {
+                                                     int tid, int cx, int cd) {
   constexpr int U = 5;
   const int per_img = g.H * g.W * 8;
-  const uint4* sx = reinterpret_cast<const uint4*>(x + (int64_t)n * per_img * 8);
-  const uint4* sd = reinterpret_cast<const uint4*>(dy + (int64_t)n * per_img * 8);
+  const uint4* sx = reinterpret_cast<const uint4*>(x + (int64_t)n * g.H * g.W * cx);
+  const uint4* sd = reinterpret_cast<const uint4*>(dy + (int64_t)n * g.H * g.W * cd);
+  const int cx8 = cx >> 3, cd8 = cd >> 3;
   for (int q0 = tid; q0 < per_img; q0 += WG_LOADERS * U) {
     uint4 vx[U], vd[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int q = min(q0 + u * WG_LOADERS, per_img - 1);      // clamped, not predicated: no branch between the loads
-      vx[u] = __ldg(sx + q); vd[u] = __ldg(sd + q);
+      vx[u] = __ldg(sx + (q >> 3) * cx8 + (q & 7)); vd[u] = __ldg(sd + (q >> 3) * cd8 + (q & 7));
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
@@ -779,6 +804,12 @@ __global__ void __launch_bounds__(416, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int di = blockIdx.x;
+  const int nbo = a.cout_tot / C;                               // 64-channel blocks of dy
+  const int cb_in = blockIdx.z / nbo, cb_out = blockIdx.z - cb_in * nbo;
+  const float* x_f = a.x ? a.x + cb_in * C : nullptr;           // this CTA's 64-channel slices
+  const float* dy_f = a.dy ? a.dy + cb_out * C : nullptr;
+  const __nv_bfloat16* x_b = a.xb ? a.xb + cb_in * C : nullptr;
+  const __nv_bfloat16* dy_b = a.dyb ? a.dyb + cb_out * C : nullptr;
   const int img_beg = blockIdx.y * a.imgs_per_cta;
   const int img_end = min(g.B, img_beg + a.imgs_per_cta);
   const int nimg = max(0, img_end - img_beg);
@@ -807,15 +838,16 @@ __global__ void __launch_bounds__(416, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
     // is stored (a round trip to L2 is ~3k cycles here whatever the size; the MMAs of an image take 1.7k)
     constexpr int PU = 5;
     const int per_img = g.H * g.W * 8;
-    if (a.xb && !a.pg.dpool && per_img <= PU * WG_LOADERS) {
+    if (x_b && !a.pg.dpool && per_img <= PU * WG_LOADERS) {
       uint4 vxa[PU], vda[PU], vxb[PU], vdb[PU];
+      const int cx8 = a.cin_tot >> 3, cd8 = a.cout_tot >> 3;
       auto load = [&](int it, uint4 (&vx)[PU], uint4 (&vd)[PU]) {
-        const uint4* sx = reinterpret_cast<const uint4*>(a.xb + (int64_t)(img_beg + it) * per_img * 8);
-        const uint4* sd = reinterpret_cast<const uint4*>(a.dyb + (int64_t)(img_beg + it) * per_img * 8);
+        const uint4* sx = reinterpret_cast<const uint4*>(x_b + (int64_t)(img_beg + it) * g.H * g.W * a.cin_tot);
+        const uint4* sd = reinterpret_cast<const uint4*>(dy_b + (int64_t)(img_beg + it) * g.H * g.W * a.cout_tot);
 #pragma unroll
         for (int u = 0; u < PU; ++u) {
           const int q = min(tid + u * WG_LOADERS, per_img - 1);      // clamped, not predicated
-          vx[u] = __ldg(sx + q); vd[u] = __ldg(sd + q);
+          vx[u] = __ldg(sx + (q >> 3) * cx8 + (q & 7)); vd[u] = __ldg(sd + (q >> 3) * cd8 + (q & 7));
         }
       };
       auto store = [&](int it, const uint4 (&vx)[PU], const uint4 (&vd)[PU]) {
@@ -859,7 +891,7 @@ __global__ void __launch_bounds__(416, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
       if (a.pg.dpool) {                       // the pooled-gradient gather keeps its 128-thread helpers (warps 0-3)
         if (warp < 4) {
           float unused[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-          fill_strip(xs, a.x, g, img_beg + it, C, g.ch_stride, tid);
+          fill_strip(xs, x_f, g, img_beg + it, C, g.ch_stride, tid);
           stage_pool_grad(dpm, argb, a.pg, img_beg + it, tid);
           loaders_sync();
           fill_strip_from_pool(ds, dpm, argb, g, a.pg, 0, g.ch_stride, tid, unused);
@@ -870,8 +902,8 @@ __global__ void __launch_bounds__(416, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
           }
         }
       } else {
-        if (a.xb) fill_strip_pair_bf16(xs, x2, ds, a.xb, a.dyb, g, img_beg + it, tid);
-        else fill_strip_pair(xs, x2, ds, a.x, a.dy, g, img_beg + it, tid);
+        if (x_b) fill_strip_pair_bf16(xs, x2, ds, x_b, dy_b, g, img_beg + it, tid, a.cin_tot, a.cout_tot);
+        else fill_strip_pair(xs, x2, ds, x_f, dy_f, g, img_beg + it, tid, a.cin_tot, a.cout_tot);
       }
       fence_proxy_async();
       mbar_arrive(smem_u32(full + b));
@@ -882,7 +914,9 @@ __global__ void __launch_bounds__(416, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
     mbar_wait(smem_u32(accum), 0);
     tc_fence_after();
     if (stamp) a.timeline[12] = clock64();
-    float* part = a.partial + (int64_t)blockIdx.y * 25 * C * C;
+    // this block of the split's partial [25][cin_tot][cout_tot]
+    float* part = a.partial + (int64_t)blockIdx.y * 25 * a.cin_tot * a.cout_tot + (int64_t)cb_in * C * a.cout_tot + cb_out * C;
+    const int64_t tap_stride = (int64_t)a.cin_tot * a.cout_tot;
     const int q4 = warp & 3, c0 = (warp >> 2) * 32;       // TMEM lane quarter, column half of each accumulator
     // accumulators 0 / 1 (M = 128): lanes 0-63 = tap 2p, lanes 64-127 = tap 2p+1, lane % 64 = cin
 #pragma unroll 1
@@ -891,7 +925,7 @@ __global__ void __launch_bounds__(416, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
       tmem_ld32(tmem + ((uint32_t)(q4 * 32) << 16) + p * C + c0, v);
       tmem_ld_wait();
       const int row = q4 * 32 + lane, dj = 2 * p + (row >> 6), cin = row & 63;
-      float* out = part + ((int64_t)(di * 5 + dj) * C + cin) * C + c0;
+      float* out = part + (di * 5 + dj) * tap_stride + (int64_t)cin * a.cout_tot + c0;
 #pragma unroll
       for (int j = 0; j < 32; j += 4)
         *reinterpret_cast<float4*>(out + j) =
@@ -905,7 +939,7 @@ __global__ void __launch_bounds__(416, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
       tmem_ld_wait();
       if (lane < 16) {
         const int cin = q4 * 16 + lane;
-        float* out = part + ((int64_t)(di * 5 + 4) * C + cin) * C + c0;
+        float* out = part + (di * 5 + 4) * tap_stride + (int64_t)cin * a.cout_tot + c0;
 #pragma unroll
         for (int j = 0; j < 32; j += 4)
           *reinterpret_cast<float4*>(out + j) =
@@ -984,7 +1018,8 @@ __global__ void reduce_partials_tc(ReduceSeg s0, ReduceSeg s1) {
   if (sub == 0 && (t >> 2) * 4 < g.n) *reinterpret_cast<float4*>(g.out + i) = s;
 }
 
-int wgrad_splits_tc(int B) { return std::max(1, std::min(B, (kNumSMs + 4) / 5)); }
+// image splits of the filter gradient: 5 filter rows x (64 x 64 channel blocks) x splits ~ one wave of CTAs
+int wgrad_splits_tc(int B, int nblk = 1) { return std::max(1, std::min(B, (kNumSMs + 4) / (5 * nblk))); }
 }  // namespace
 
 int reduce_partials(const float* part, float* out, int n, int S, cudaStream_t st, int stride) {
@@ -1042,7 +1077,9 @@ int conv5x5_dgrad_pool_tc(const float* dpool, const float* pool, const uint8_t* 
   return launch_conv<true>(nullptr, (const uint8_t*)wp, nullptr, dx, B, H, W, Cout, Cin, 0, st, &p, dbias, dconv_out, nullptr,
                            nullptr, nullptr, dconv_out_bf16, nullptr, dbias_part, n_part);
 }
-int64_t conv5x5_wgrad_tc_scratch_bytes(int B) { return (int64_t)wgrad_splits_tc(B) * 25 * 64 * 64 * 4; }
+int64_t conv5x5_wgrad_tc_scratch_bytes(int B, int Cin, int Cout) {
+  return (int64_t)wgrad_splits_tc(B, (Cin / 64) * (Cout / 64)) * 25 * Cin * Cout * 4;
+}
 static int launch_wgrad(const float* x, const float* dy, const PoolGradSrc* pg, float* dw, float* scratch, int B, int H,
                         int W, int Cin, int Cout, cudaStream_t st, const void* x_bf16 = nullptr,
                         const void* dy_bf16 = nullptr, const float* db_part = nullptr, float* db = nullptr, int n_db_part = 0);
@@ -1061,8 +1098,11 @@ int conv5x5_wgrad_pool_tc(const float* x, const float* dpool, const float* pool,
 static int launch_wgrad(const float* x, const float* dy, const PoolGradSrc* pg, float* dw, float* scratch, int B, int H,
                         int W, int Cin, int Cout, cudaStream_t st, const void* x_bf16, const void* dy_bf16,
                         const float* db_part, float* db, int n_db_part) {
-  B200_REQUIRE(Cin == 64 && Cout == 64, "conv5x5_wgrad_tc: only 64 -> 64 channels (got %d -> %d)", Cin, Cout);
+  B200_REQUIRE(Cin > 0 && Cout > 0 && Cin % 64 == 0 && Cout % 64 == 0,
+               "conv5x5_wgrad_tc: channels must be multiples of 64 (got %d -> %d)", Cin, Cout);
+  B200_REQUIRE(!pg || (Cin == 64 && Cout == 64), "conv5x5_wgrad_tc: the pooled-gradient source needs 64 -> 64 channels");
   B200_REQUIRE(B > 0 && H > 0 && W > 0, "conv5x5_wgrad_tc: bad shape");
+  const int nblk = (Cin / 64) * (Cout / 64);
   ConvGeom g = make_geom(B, H, W, 64, 64, 1);
   // compact strips: the k-steps cover H*P slots from `lead`, the taps shift the x operand by at most +-(2P + 2)
   g.npix = g.lead + ((H * g.P + 15) / 16) * 16 + 2 * g.P + 2;
@@ -1077,14 +1117,14 @@ static int launch_wgrad(const float* x, const float* dy, const PoolGradSrc* pg, 
   if (attr.first())
     B200_CUDA_TRY(cudaFuncSetAttribute(conv5x5_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        227 * 1024));
-  int S = wgrad_splits_tc(B);
+  int S = wgrad_splits_tc(B, nblk);
   int per = cdiv(B, S);
   S = cdiv(B, per);
-  WgradArgs a{x, dy, reinterpret_cast<const __nv_bfloat16*>(x_bf16), reinterpret_cast<const __nv_bfloat16*>(dy_bf16), scratch, g, per, nbuf, pg ? *pg : PoolGradSrc{}, g_conv_timeline};
+  WgradArgs a{x, dy, reinterpret_cast<const __nv_bfloat16*>(x_bf16), reinterpret_cast<const __nv_bfloat16*>(dy_bf16), scratch, g, Cin, Cout, per, nbuf, pg ? *pg : PoolGradSrc{}, g_conv_timeline};
   const bool overlap = g_pdl_next;           // the step driver asked for overlapped launches: only the reduction is
   g_pdl_next = false;                        // programmatic (the kernel in front of this one is on another stream)
-  B200_CUDA_TRY(launch_kernel(conv5x5_wgrad_tc_kernel, dim3(5, S), dim3(416), (size_t)smem, st, a));
-  const int n = 25 * 64 * 64;
+  B200_CUDA_TRY(launch_kernel(conv5x5_wgrad_tc_kernel, dim3(5, S, nblk), dim3(416), (size_t)smem, st, a));
+  const int n = 25 * Cin * Cout;
   g_pdl_next = overlap;
   const bool with_db = db_part && db && n_db_part > 0;      // the bias-gradient partials of the dgrad kernel ride along
   B200_CUDA_TRY(launch_kernel(reduce_partials_tc, dim3(cdiv(n, 128) + (with_db ? 1 : 0)), dim3(128), 0, st,

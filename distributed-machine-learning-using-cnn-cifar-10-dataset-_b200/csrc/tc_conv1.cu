@@ -511,9 +511,9 @@ int conv1_wgrad_tc(const uint8_t* img, const float* dpool, const float* pool, co
   B200_CUDA_TRY(launch_kernel(conv1_wgrad_kernel, dim3(S), dim3(416), smem, st, a));
   if (defer_reduce) return B200_OK;
   g_pdl_next = overlap;                                   // (the reduction's prologue may overlap the kernel's tail)
-  if (db == dw + 4800) return reduce_partials(scratch, dw, 4864, S, st);
-  B200_TRY(reduce_partials(scratch, dw, 4800, S, st, 4864));
-  return db ? reduce_partials(scratch + 4800, db, 64, S, st, 4864) : B200_OK;
+  if (db == dw + 4800) return reduce_partials_warp(scratch, dw, 4864, S, 4864, st);
+  B200_TRY(reduce_partials_warp(scratch, dw, 4800, S, 4864, st));
+  return db ? reduce_partials_warp(scratch + 4800, db, 64, S, 4864, st) : B200_OK;
 }
 
 void conv1_set_timeline(long long* dev_buf) { g_conv1_timeline = dev_buf; }

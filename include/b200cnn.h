@@ -227,6 +227,9 @@ int b200_conv5x5_pool_fwd_bf16x(const void* x_bf16, const void* w_packed, const 
 int b200_conv5x5_dgrad_bf16(const float* dy, const void* w_packed, float* dx, int32_t batch, int32_t h, int32_t wd,
                             int32_t c_in, int32_t c_out, void* stream);
 int b200_conv5x5_wgrad_bf16_scratch_bytes(int32_t batch, int64_t* nbytes);
+/* scratch of b200_conv5x5_wgrad_bf16 for c_in -> c_out channels (multiples of 64; the kernel works on 64 x 64 channel
+ * blocks): b200_conv5x5_wgrad_bf16_scratch_bytes is the 64 -> 64 case.  Conv2DBackpropFilter of :118. */
+int b200_conv5x5_wgrad_bf16_scratch_bytes_c(int32_t batch, int32_t c_in, int32_t c_out, int64_t* nbytes);
 int b200_conv5x5_wgrad_bf16(const float* x, const float* dy, float* dw, void* scratch, int64_t scratch_bytes,
                             int32_t batch, int32_t h, int32_t wd, int32_t c_in, int32_t c_out, void* stream);
 /* Conv2DBackpropInput / Conv2DBackpropFilter fed by the POOLED gradient: MaxPoolGrad (:123) and the ReluGrad

@@ -79,7 +79,7 @@ def test_cli_one_ps_two_workers_is_reproducible(tmp_path):
         outs = _run_cluster(str(d), steps=60)
         for rc, o, e in outs:
             assert rc == 0, e[-3000:]
-            assert o.splitlines()[0] == "Starting Training"
+            assert "Starting Training" in o.splitlines()          # (NCCL may print its version line first)
         path = checkpoint.latest(str(d))
         assert path and path.endswith("model.ckpt-60.npz")
         finals.append(checkpoint.load(path)[0])

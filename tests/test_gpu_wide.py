@@ -1,0 +1,117 @@
+"""BASELINE.json config 5: the width-scaled CNN (conv channels x4 = 256 / 256, FC x2 = 768 / 384) in bf16 mode.
+
+The contractions of the wide model run on the same tcgen05 kernels as the script's own widths, channel-blocked:
+conv2's forward / input gradient stream the filter as (tap, 128-channel piece) stages, the filter gradient works on
+64 x 64 channel blocks, FC1 / FC2 are generic tcgen05 GEMMs.  Checked kernel by kernel (TIGHT against the oracle on
+bf16-rounded operands) and as a whole step against the fp64 oracle with the wide parameter shapes."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+import b200cnn
+from b200cnn import _lib
+from oracle import ref_numpy as rn
+
+pytestmark = pytest.mark.gpu
+TIGHT, LOOSE = 2e-5, 1e-2
+WIDE = dict(c1=256, c2=256, f1=768, f2=384)
+
+
+def dev(a):
+    return torch.as_tensor(np.ascontiguousarray(a)).cuda()
+
+
+def bf16_round(a):
+    return torch.as_tensor(np.asarray(a, np.float32)).to(torch.bfloat16).to(torch.float64).numpy()
+
+
+def relerr(got, want):
+    want = np.asarray(want, np.float64)
+    return np.abs(np.asarray(got, np.float64) - want).max() / (np.abs(want).max() + 1e-30)
+
+
+def stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+@pytest.fixture(scope="module")
+def lib():
+    return _lib.load()
+
+
+@pytest.mark.parametrize("B,H,W,Cin,Cout", [(4, 12, 12, 256, 256), (3, 12, 12, 128, 64), (3, 9, 12, 64, 128),
+                                            (2, 12, 12, 256, 128), (130, 12, 12, 128, 128)])
+def test_conv_tensorcore_wide_channels(lib, B, H, W, Cin, Cout):
+    rng = np.random.default_rng(33)
+    x = np.maximum(rng.normal(size=(B, H, W, Cin)), 0).astype(np.float32)
+    w = (rng.normal(size=(5, 5, Cin, Cout)) * 0.03).astype(np.float32)
+    b = rng.normal(size=(Cout,)).astype(np.float32)
+    dy = (rng.normal(size=(B, H, W, Cout)) * (rng.random(size=(B, H, W, Cout)) < 0.3)).astype(np.float32)
+    xd, wd, bd, dyd = dev(x), dev(w), dev(b), dev(dy)
+    xr, wr, dyr = bf16_round(x), bf16_round(w), bf16_round(dy)
+    nb = C.c_int64()
+    _lib.check(lib.b200_conv5x5_packed_bytes(Cin, Cout, C.byref(nb)))
+    wp = torch.full((nb.value,), 0x7f, dtype=torch.uint8, device="cuda")
+    _lib.check(lib.b200_conv5x5_pack_weights(wd.data_ptr(), wp.data_ptr(), Cin, Cout, stream()))
+    y = torch.full((B, H, W, Cout), float("nan"), device="cuda")
+    _lib.check(lib.b200_conv5x5_fwd_bf16(xd.data_ptr(), wp.data_ptr(), bd.data_ptr(), y.data_ptr(), B, H, W, Cin, Cout, 1,
+                                         stream()))
+    torch.cuda.synchronize()
+    assert relerr(y.cpu().numpy(), np.maximum(rn.conv2d_same(xr, wr) + b, 0)) <= TIGHT
+    dx = torch.full((B, H, W, Cin), float("nan"), device="cuda")
+    _lib.check(lib.b200_conv5x5_dgrad_bf16(dyd.data_ptr(), wp.data_ptr(), dx.data_ptr(), B, H, W, Cin, Cout, stream()))
+    torch.cuda.synchronize()
+    assert relerr(dx.cpu().numpy(), rn.conv2d_same_grad_input(dyr, wr)) <= TIGHT
+    _lib.check(lib.b200_conv5x5_wgrad_bf16_scratch_bytes_c(B, Cin, Cout, C.byref(nb)))
+    scr = torch.empty(nb.value, dtype=torch.uint8, device="cuda")
+    dw = torch.full((5, 5, Cin, Cout), float("nan"), device="cuda")
+    for _ in range(2):
+        _lib.check(lib.b200_conv5x5_wgrad_bf16(xd.data_ptr(), dyd.data_ptr(), dw.data_ptr(), scr.data_ptr(), nb.value, B, H,
+                                               W, Cin, Cout, stream()))
+        torch.cuda.synchronize()
+        assert relerr(dw.cpu().numpy(), rn.conv2d_same_grad_filter(xr, dyr)) <= TIGHT
+
+
+@pytest.mark.parametrize("kind,B", [("soft", 128), ("u8", 64)])
+def test_full_step_wide_model_bf16(kind, B):
+    from test_gpu_parity import _oracle_backward_on_gpu_forward
+    rng = np.random.default_rng(43)
+    if kind == "u8":
+        img = rng.integers(0, 256, (B, 3, 32, 32), dtype=np.uint8)
+    else:
+        img = np.clip(np.rint(rng.normal(8.0, 2.5, (B, 3, 32, 32))), 0, 255).astype(np.uint8)
+    lab = rng.integers(0, 10, (B, 1)).astype(np.int32)
+    params = rn.init_params(0, **WIDE)
+    _, loss, g, a = rn.train_step(params, img, lab, lr=np.float32(0.1))
+    e = b200cnn.TrainStepEngine(batch=B, mode="bf16", **WIDE)
+    assert e.total == sum(-(-v.size // 64) * 64 for v in params.values())
+    e.load_params(params)
+    e.forward(dev(img), dev(lab.reshape(-1)))
+    e.backward()
+    torch.cuda.synchronize()
+    for name in ("conv1", "pool1", "conv2", "pool2", "full1", "full2", "logits"):
+        assert relerr(e.tensor(name).cpu().numpy().reshape(a[name].shape), a[name]) <= LOOSE, name
+    assert abs(float(e.loss()) - loss) <= 2e-2 * abs(loss)
+    srt = np.sort(a["logits"], axis=1)
+    safe = (srt[:, -1] - srt[:, -2]) > 2 * LOOSE * np.abs(a["logits"]).max()
+    np.testing.assert_array_equal(e.pred().cpu().numpy()[safe], a["pred"][safe])
+    g2, _ = _oracle_backward_on_gpu_forward(e, params, lab, a)
+    got = e.get_grads()
+    for k in rn.PARAM_NAMES:
+        assert relerr(got[k], g2[k]) <= 2e-2, (k, relerr(got[k], g2[k]))
+    e.sgd_apply(0.1)
+    torch.cuda.synchronize()
+    newp = e.get_params()
+    for k in rn.PARAM_NAMES:
+        assert relerr(newp[k], np.asarray(params[k], np.float64) - 0.1 * g2[k]) <= 2e-2, k
+    # the step as one call, captured: same numbers
+    e2 = b200cnn.TrainStepEngine(batch=B, mode="bf16", **WIDE)
+    e2.load_params(params)
+    imgd, labd = dev(img), dev(lab.reshape(-1))
+    gr = e2.capture(lambda: e2.train_step(imgd, labd, 0.1))
+    e2.load_params(params)
+    gr.replay()
+    torch.cuda.synchronize()
+    assert relerr(e2.params.cpu().numpy(), e.params.cpu().numpy()) <= 1e-6
