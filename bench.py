@@ -23,9 +23,17 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 METRIC = "train images/sec (CIFAR-10 CNN, bs128/GPU)"
-FLOP_PER_IMAGE = 105_295_104          # 2 x train MACs, base model, 24x24 crop
-ACT_ELEMS_PER_IMAGE = 352_542         # layer-boundary activation traffic model
-PARAM_BYTES = 4_273_192
+# 2 x train MACs (24x24 crop), layer-boundary activation traffic model, parameter bytes
+MODELS = {
+    "base": dict(dims=dict(c1=64, c2=64, f1=384, f2=192), flop=105_295_104, act=352_542, param_bytes=4_273_192,
+                 name="conv5x5x64-pool-conv5x5x64-pool-fc384-fc192-fc10"),
+    # BASELINE.json configs[4]: conv channels x4, FC x2
+    "wide": dict(dims=dict(c1=256, c2=256, f1=768, f2=384), flop=1_504_074_240, act=1_392_798, param_bytes=36_143_656,
+                 name="width-scaled conv5x5x256-pool-conv5x5x256-pool-fc768-fc384-fc10"),
+}
+FLOP_PER_IMAGE = MODELS["base"]["flop"]
+ACT_ELEMS_PER_IMAGE = MODELS["base"]["act"]
+PARAM_BYTES = MODELS["base"]["param_bytes"]
 
 
 def load_peaks():
@@ -88,14 +96,14 @@ def synthetic_batch(rng, batch):
             rng.integers(0, 10, (batch,)).astype(np.int32))
 
 
-def cpu_baseline(batch, budget_s, threads=None):
+def cpu_baseline(batch, budget_s, threads=None, dims=None):
     """The reference's CPU path restated in torch-CPU fp32 (oracle/ref_torch.py, kind 'port';
     TensorFlow 1.x itself is not installable here) timed on this host's cores."""
     import numpy as np
     import torch
     from oracle import ref_numpy as rn, ref_torch as rt
     threads = threads or os.cpu_count()
-    tr = rt.CpuTrainer(rn.init_params(0), lr=0.1, threads=threads)
+    tr = rt.CpuTrainer(rn.init_params(0, **(dims or {})), lr=0.1, threads=threads)
     rng = np.random.default_rng(1234)
     pool = [synthetic_batch(rng, batch) for _ in range(4)]
     tr.step(*pool[0])
@@ -191,12 +199,14 @@ def run_reference(args):
         v, sample = cpu_ps_workers(args.batch, world, steps, warmup=min(warm, 3))
         ms = 1e3 * args.batch * world / v
     else:
-        tr = rt.CpuTrainer(rn.init_params(0), lr=0.1, threads=threads)
+        tr = rt.CpuTrainer(rn.init_params(0, **MODELS[args.model]["dims"]), lr=0.1, threads=threads)
         rng = np.random.default_rng(1234)
         pool = [synthetic_batch(rng, args.batch) for _ in range(4)]
         steps = min(args.steps, 400)
         if args.batch > 128:
             steps = max(4, steps * 128 // args.batch)
+        if args.model == "wide":
+            steps = max(4, steps // 12)
         for i in range(warm):
             tr.step(*pool[i % 4])
             tr.reset()
@@ -221,29 +231,32 @@ def run_reference(args):
 
 
 def workload_name(args):
-    return (f"cifar10cnn.py CNN train step (conv5x5x64-pool-conv5x5x64-pool-fc384-fc192-fc10, softmax-xent, "
+    return (f"cifar10cnn.py CNN train step ({MODELS[args.model]['name']}, softmax-xent, "
             f"SGD lr 0.1), 32x32x3 uint8 records centre-cropped to 24x24, batch {args.batch}/GPU")
 
 
 # algorithmic work per launch site: ("tensor", MACs per image) or ("hbm", bytes per image, fixed bytes)
-def site_work(mode):
+def site_work(mode, dims=None, param_bytes=PARAM_BYTES):
     act = 4 if mode == "fp32" else 2
-    c1, p1, c2, p2 = 36864, 9216, 9216, 2304
+    d = dims or MODELS["base"]["dims"]
+    C1, C2, F1, F2 = d["c1"], d["c2"], d["f1"], d["f2"]
+    c1, p1, c2, p2 = 576 * C1, 144 * C1, 144 * C2, 36 * C2
+    m_c1, m_c2, m_f1, m_f2, m_f3 = 576 * 75 * C1, 144 * 25 * C1 * C2, p2 * F1, F1 * F2, F2 * 10      # MACs per image
     return {
-        "conv1_fwd": ("tensor", 2_764_800), "conv1_wgrad": ("tensor", 2_764_800),
-        "conv2_fwd": ("tensor", 14_745_600), "conv2_dgrad": ("tensor", 14_745_600),
-        "conv2_wgrad": ("tensor", 14_745_600),
-        "full1_fwd": ("tensor", 884_736), "full1_bwd": ("tensor", 2 * 884_736),
-        "full1_dw": ("tensor", 884_736), "full1_dx": ("tensor", 884_736),
-        "conv1_pool1_fwd": ("tensor", 2_764_800), "conv2_pool2_fwd": ("tensor", 14_745_600), "fc_tail": ("tensor", 3 * (73_728 + 1_920)),
-        "weights_prep": ("hbm", 0, 102400 * 6 + 73728 * 6),
-        "full2_fwd": ("tensor", 73_728), "full2_bwd": ("tensor", 2 * 73_728),
-        "full3_fwd": ("tensor", 1_920), "full3_bwd": ("tensor", 2 * 1_920),
+        "conv1_fwd": ("tensor", m_c1), "conv1_wgrad": ("tensor", m_c1),
+        "conv2_fwd": ("tensor", m_c2), "conv2_dgrad": ("tensor", m_c2),
+        "conv2_wgrad": ("tensor", m_c2),
+        "full1_fwd": ("tensor", m_f1), "full1_bwd": ("tensor", 2 * m_f1),
+        "full1_dw": ("tensor", m_f1), "full1_dx": ("tensor", m_f1),
+        "conv1_pool1_fwd": ("tensor", m_c1), "conv2_pool2_fwd": ("tensor", m_c2), "fc_tail": ("tensor", 3 * (m_f2 + m_f3)),
+        "weights_prep": ("hbm", 0, 25 * C1 * C2 * 6 + F1 * F2 * 6),
+        "full2_fwd": ("tensor", m_f2), "full2_bwd": ("tensor", 2 * m_f2),
+        "full3_fwd": ("tensor", m_f3), "full3_bwd": ("tensor", 2 * m_f3),
         "crop_cast": ("hbm", 3072 + 1728 * act, 0),
         "pool1_fwd": ("hbm", c1 * act + p1 * act + p1, 0), "pool2_fwd": ("hbm", c2 * act + p2 * act + p2, 0),
         "pool1_bwd": ("hbm", p1 * act + p1 + c1 * act * 2, 0), "pool2_bwd": ("hbm", p2 * act + p2 + c2 * act * 2, 0),
-        "head": ("hbm", 10 * 4 * 2 + 4 + 4, 0), "conv2_dgrad_prep": ("hbm", 0, 2 * 102400 * 4),
-        "sgd_apply": ("hbm", 0, 3 * PARAM_BYTES),
+        "head": ("hbm", 10 * 4 * 2 + 4 + 4, 0), "conv2_dgrad_prep": ("hbm", 0, 2 * 25 * C1 * C2 * 4),
+        "sgd_apply": ("hbm", 0, 3 * param_bytes),
     }
 
 
@@ -254,6 +267,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=128)
+    ap.add_argument("--model", default="base", choices=sorted(MODELS),
+                    help="base = the script's own widths; wide = BASELINE.json's width-scaled model (conv x4, FC x2)")
     ap.add_argument("--mode", default=os.environ.get("B200CNN_MODE", "auto"), choices=["auto", "fp32", "bf16"])
     ap.add_argument("--reduce", default="sum", choices=["sum", "mean"])
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
@@ -290,7 +305,7 @@ def main():
     ex, exchange = None, "none"
     if world > 1 and args.exchange == "p2p":
         try:
-            total = b200cnn.TrainStepEngine(batch=8, mode="fp32", device=local).total
+            total = b200cnn.TrainStepEngine(batch=8, mode="fp32", device=local, **MODELS[args.model]["dims"]).total
             ex = b200cnn.P2PExchange(total, torch.device("cuda", local), reduce=args.reduce)
             exchange = "p2p-fused" + ("-nvls" if ex.multicast else "") + ("-overlapped" if ex.overlap else "")
         except Exception as e:          # no symmetric memory on this box: fall back to NCCL (still all CUDA)
@@ -301,8 +316,9 @@ def main():
         ex = b200cnn.GradientExchange(reduce=args.reduce)
         exchange = "nccl" if world > 1 else "none"
     fused = isinstance(ex, b200cnn.P2PExchange)
+    model = MODELS[args.model]
     eng = b200cnn.TrainStepEngine(batch=B, mode=mode, device=local, params=ex.params if fused else None,
-                                  grads=ex.grads if fused else None)
+                                  grads=ex.grads if fused else None, **model["dims"])
     eng.init_params(0)
     params0 = eng.params.clone()
     ex.broadcast_params_(eng.params)
@@ -325,7 +341,7 @@ def main():
         if world == 1:
             eng.train_step(s_img, s_lab, lr)
         else:
-            if fused:
+            if fused and args.model == "base":
                 ex.train_step_(eng, s_img, s_lab, lr)      # exchange split in two and overlapped with the backward
             else:
                 eng.forward_backward(s_img, s_lab)
@@ -345,7 +361,7 @@ def main():
             else:
                 s_img.copy_(img, non_blocking=True)
                 s_lab.copy_(lab, non_blocking=True)
-                if fused:
+                if fused and args.model == "base":
                     ex.train_step_(eng, s_img, s_lab, lr)
                 else:
                     eng.forward_backward(s_img, s_lab)
@@ -455,7 +471,7 @@ def main():
         if i >= 2:
             for n, ms in sites:
                 acc[n] = acc.get(n, 0.0) + ms / n_prof
-    work = site_work(mode)
+    work = site_work(mode, model["dims"], model["param_bytes"])
     table = []
     for n, ms in acc.items():
         w = work.get(n)
@@ -493,15 +509,15 @@ def main():
 
     if rank == 0:
         imgs = B * world * K
-        step_flops = FLOP_PER_IMAGE * B
+        step_flops = model["flop"] * B
         act_b = 4 if mode == "fp32" else 2
-        step_bytes = ACT_ELEMS_PER_IMAGE * act_b * B + 3 * PARAM_BYTES
+        step_bytes = model["act"] * act_b * B + 3 * model["param_bytes"]
         ms_step = ms_cold / K
         out = {
             "metric": METRIC, "value": imgs / (ms_cold * 1e-3), "unit": "images/s", "n_gpus": world, "steps": K,
             "warmup": W, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32" if mode == "fp32" else "bf16", "data": "synthetic",
-            "config": {"workload": workload_name(args), "batch_per_gpu": B, "global_batch": B * world,
+            "config": {"workload": workload_name(args), "model_widths": model["dims"], "batch_per_gpu": B, "global_batch": B * world,
                        "mode": mode, "parallelism": f"dp{world}", "reduce": args.reduce, "exchange": exchange,
                        "l2": "flushed between timed steps (256 MiB memset, untimed); per-step CUDA events summed",
                        "cuda_graph": True},
@@ -526,8 +542,8 @@ def main():
             "sites": [{k: (round(v, 5) if isinstance(v, float) else v) for k, v in r.items()} for r in table[:8]],
         }
         if world == 1 and not args.no_cpu_baseline:
-            out["cpu_baseline"] = cpu_baseline(B, args.cpu_seconds)
-            if B == 128:        # BASELINE.json configs[0] shape: 1 ps + 2 workers on localhost (README:11-13)
+            out["cpu_baseline"] = cpu_baseline(B, args.cpu_seconds, dims=model["dims"])
+            if B == 128 and args.model == "base":        # BASELINE.json configs[0] shape: 1 ps + 2 workers on localhost (README:11-13)
                 try:
                     v2, sample2 = cpu_ps_workers(B, 2, max(8, int(args.cpu_seconds * out["cpu_baseline"]["value"] / B / 4)))
                     out["cpu_baseline_1ps_2workers"] = {"value": v2, "unit": "images/s", "cores": os.cpu_count(),

@@ -138,7 +138,7 @@ int b200_create(const b200_config* c, b200_handle* out) {
   int64_t scratch = conv5x5_wgrad_scratch_bytes(c->batch, c->crop_h, c->crop_w, c->c_in, c->c1);
   scratch = std::max(scratch, conv5x5_wgrad_scratch_bytes(c->batch, h->h1, h->w1, c->c1, c->c2));
   scratch = std::max(scratch, colsum_scratch_bytes(c->batch, std::max(c->f1, std::max(c->f2, c->n_cls))));
-  scratch = std::max(scratch, conv1_wgrad_tc_scratch_bytes(c->batch));
+  scratch = std::max(scratch, conv1_wgrad_tc_scratch_bytes(c->batch, c->c1 % 64 == 0 ? c->c1 : 64));
   if (c->c1 % 64 == 0 && c->c2 % 64 == 0)
     scratch = std::max(scratch, conv5x5_wgrad_tc_scratch_bytes(c->batch, c->c1, c->c2));
   scratch = std::max(scratch, colsum_scratch_bytes(c->batch * h->h1 * h->w1, c->c2));
@@ -278,11 +278,18 @@ static int forward_impl(b200_handle h, const uint8_t* images, const int32_t* lab
   h->last_images = images;
   if (tc && !fused_bf16_shapes(c)) {
     // ---- layer-by-layer bf16 schedule (widths other than the script's) ------------------------------------------
-    SITE("crop_cast", crop_cast_f32(images, x, c.batch, c.img_h, c.img_w, c.crop_h, c.crop_w, c.c_in, st));
-    SITE("conv1_fwd", conv5x5_fwd_f32(x, h->P(P_W1), h->P(P_B1), conv1, c.batch, c.crop_h, c.crop_w, c.c_in, c.c1, 1, st));
-    SITE("pool1_fwd", maxpool_fwd_f32(conv1, pool1, h->ptr<uint8_t>("arg1"), c.batch, c.crop_h, c.crop_w, c.c1, st));
+    if (fused1) {      // crop + conv1 + bias + ReLU + pool1 on tcgen05, one CTA per image and 64-channel slice
+      SITE("conv1_pool1_fwd", conv1_pool_fwd_tc(images, h->P(P_W1), h->P(P_B1), pool1, h->ptr<uint8_t>("arg1"), nullptr,
+                                                c.batch, c.img_h, c.img_w, c.crop_h, c.crop_w, st,
+                                                h->ptr<void>("pool1_bf16"), c.c1));
+    } else {
+      SITE("crop_cast", crop_cast_f32(images, x, c.batch, c.img_h, c.img_w, c.crop_h, c.crop_w, c.c_in, st));
+      SITE("conv1_fwd", conv5x5_fwd_f32(x, h->P(P_W1), h->P(P_B1), conv1, c.batch, c.crop_h, c.crop_w, c.c_in, c.c1, 1, st));
+      SITE("pool1_fwd", maxpool_fwd_f32(conv1, pool1, h->ptr<uint8_t>("arg1"), c.batch, c.crop_h, c.crop_w, c.c1, st));
+    }
     SITE("weights_prep", pack_conv_weights(h->P(P_W2), h->ptr<void>("w2_packed"), c.c1, c.c2, st));
-    SITE("conv2_fwd", conv5x5_fwd_tc(pool1, h->ptr<void>("w2_packed"), h->P(P_B2), conv2, c.batch, h->h1, h->w1, c.c1, c.c2, 1, st));
+    SITE("conv2_fwd", conv5x5_fwd_tc(pool1, h->ptr<void>("w2_packed"), h->P(P_B2), conv2, c.batch, h->h1, h->w1, c.c1, c.c2, 1, st,
+                                     fused1 ? h->ptr<void>("pool1_bf16") : nullptr));
     SITE("pool2_fwd", maxpool_fwd_f32(conv2, pool2, h->ptr<uint8_t>("arg2"), c.batch, h->h1, h->w1, c.c2, st));
     SITE("full1_fwd", fc_fwd_tc(pool2, h->P(P_FW1), h->P(P_FB1), full1, c.batch, h->flat, c.f1, 1, st));
     SITE("full2_fwd", fc_fwd_tc(full1, h->P(P_FW2), h->P(P_FB2), full2, c.batch, c.f1, c.f2, 1, st));
@@ -427,10 +434,16 @@ static int backward_impl(b200_handle h, void* stream, const P2PCtx* px, bool def
                                          c.c2, st));
     TRY(colsum_f32(dconv2, h->G(P_B2), scratch, c.batch * h->h1 * h->w1, c.c2, st));
     SITE("conv2_dgrad", conv5x5_dgrad_tc(dconv2, h->ptr<void>("w2_packed"), dpool1, c.batch, h->h1, h->w1, c.c1, c.c2, st));
-    SITE("pool1_bwd", maxpool_bwd_f32(dpool1, h->ptr<uint8_t>("arg1"), h->ptr<float>("conv1"), dconv1, c.batch,
-                                      c.crop_h, c.crop_w, c.c1, 1, st));
-    SITE("conv1_wgrad", conv5x5_wgrad_f32(h->ptr<float>("x"), dconv1, h->G(P_W1), h->G(P_B1), scratch, c.batch,
-                                          c.crop_h, c.crop_w, c.c_in, c.c1, st));
+    if (conv1_tc_supported(c.crop_h, c.crop_w, c.c_in, c.c1)) {
+      SITE("conv1_wgrad", conv1_wgrad_tc(h->last_images, dpool1, h->ptr<float>("pool1"), h->ptr<uint8_t>("arg1"),
+                                         h->G(P_W1), h->G(P_B1), scratch, c.batch, c.img_h, c.img_w, c.crop_h,
+                                         c.crop_w, st, false, c.c1));
+    } else {
+      SITE("pool1_bwd", maxpool_bwd_f32(dpool1, h->ptr<uint8_t>("arg1"), h->ptr<float>("conv1"), dconv1, c.batch,
+                                        c.crop_h, c.crop_w, c.c1, 1, st));
+      SITE("conv1_wgrad", conv5x5_wgrad_f32(h->ptr<float>("x"), dconv1, h->G(P_W1), h->G(P_B1), scratch, c.batch,
+                                            c.crop_h, c.crop_w, c.c_in, c.c1, st));
+    }
     return B200_OK;
   }
   if (tc) {
@@ -672,9 +685,10 @@ int b200_launches_per_step(b200_handle h, int32_t* n) {
   // dgrad (rot180 + gemm); sgd
   *n = 9 + 12 + 2 + 8 + 2 + 1;
   if (h->cfg.mode == B200_MODE_BF16 && !fused_bf16_shapes(h->cfg)) {
-    // layer-by-layer schedule: forward 10 | FC3 bwd 4, FC2 / FC1 bwd 2 + 2 each, pool2 bwd, conv2 wgrad 2 + colsum 2, dgrad,
-    // pool1 bwd, conv1 wgrad 4 | sgd
-    *n = 10 + 4 + 4 + 4 + 1 + 4 + 1 + 1 + 4 + 1;
+    // layer-by-layer schedule: forward 8 (10 with the SIMT conv1) | FC3 bwd 4, FC2 / FC1 bwd 2 + 2 each, pool2 bwd, conv2
+    // wgrad 2 + colsum 2, dgrad, conv1 wgrad 2 (pool1 bwd + 4 with the SIMT conv1) | sgd
+    const bool f1 = conv1_tc_supported(h->cfg.crop_h, h->cfg.crop_w, h->cfg.c_in, h->cfg.c1);
+    *n = (f1 ? 8 : 10) + 4 + 4 + 4 + 1 + 4 + 1 + (f1 ? 2 : 5) + 1;
   } else if (h->cfg.mode == B200_MODE_BF16) {
     // conv1 (3 or 1), conv2, pool2, FC1 split-K, tail x2 | FC1 bwd x2, pool2 bwd, conv2 wgrad x2, dgrad, conv1 wgrad (2 or 1+4), sgd
     const bool f1 = conv1_tc_supported(h->cfg.crop_h, h->cfg.crop_w, h->cfg.c_in, h->cfg.c1);
@@ -762,6 +776,22 @@ int b200_conv1_wgrad_bf16(const uint8_t* images, const float* dpool, const float
   B200_REQUIRE(batch > 0 && scratch_bytes >= conv1_wgrad_tc_scratch_bytes(batch), "scratch too small");
   return conv1_wgrad_tc(images, dpool, pool, arg, dw, db, (float*)scratch, batch, img_h, img_w, crop_h, crop_w,
                         (cudaStream_t)stream);
+}
+int b200_conv1_pool_fwd_bf16_c(const uint8_t* images, const float* w, const float* bias, float* pool, uint8_t* arg,
+                               float* conv_dbg, int32_t batch, int32_t img_h, int32_t img_w, int32_t crop_h,
+                               int32_t crop_w, int32_t c1, void* stream) {
+  B200_REQUIRE(images && w && bias && pool && arg, "null pointer");
+  return conv1_pool_fwd_tc(images, w, bias, pool, arg, conv_dbg, batch, img_h, img_w, crop_h, crop_w,
+                           (cudaStream_t)stream, nullptr, c1);
+}
+int b200_conv1_wgrad_bf16_c(const uint8_t* images, const float* dpool, const float* pool, const uint8_t* arg, float* dw,
+                            float* db, void* scratch, int64_t scratch_bytes, int32_t batch, int32_t img_h, int32_t img_w,
+                            int32_t crop_h, int32_t crop_w, int32_t c1, void* stream) {
+  B200_REQUIRE(images && dpool && pool && arg && dw && scratch, "null pointer");
+  B200_REQUIRE(batch > 0 && c1 > 0 && c1 % 64 == 0 && scratch_bytes >= conv1_wgrad_tc_scratch_bytes(batch, c1),
+               "bad width or scratch too small");
+  return conv1_wgrad_tc(images, dpool, pool, arg, dw, db, (float*)scratch, batch, img_h, img_w, crop_h, crop_w,
+                        (cudaStream_t)stream, false, c1);
 }
 int b200_debug_conv_timeline(int64_t* device_buf8) {
   conv5x5_set_timeline(reinterpret_cast<long long*>(device_buf8));

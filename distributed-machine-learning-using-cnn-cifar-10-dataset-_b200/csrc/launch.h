@@ -57,7 +57,7 @@ void conv5x5_force_variant(int v);               // tests: 0 = one CTA per SM, 1
 int64_t conv5x5_packed_bytes(int Cin, int Cout);
 int pack_conv_weights(const float* w, void* wp, int Cin, int Cout, cudaStream_t st);
 int conv5x5_fwd_tc(const float* x, const void* wp, const float* bias, float* y, int B, int H, int W, int Cin,
-                   int Cout, int relu, cudaStream_t st);
+                   int Cout, int relu, cudaStream_t st, const void* x_bf16 = nullptr);      // (optional) x already in bf16
 // x_bf16 (optional): the same activations already rounded to bf16, [B,H,W,Cin]; read instead of x (half the bytes)
 int conv5x5_pool_fwd_tc(const float* x, const void* wp, const float* bias, float* y, float* pool, uint8_t* arg, int B,
                         int H, int W, int Cin, int Cout, cudaStream_t st, const void* x_bf16 = nullptr,
@@ -119,13 +119,15 @@ int p2p_allreduce_sgd(const void* const* peer_grads, void* const* peer_params, v
 bool conv1_tc_supported(int H, int W, int c_in, int c1);
 int conv1_pool_fwd_tc(const uint8_t* img, const float* w, const float* bias, float* pool, uint8_t* arg,
                       float* conv_dbg, int B, int ih, int iw, int H, int W, cudaStream_t st,
-                      void* pool_bf16 = nullptr);      // (optional) second copy of pool, rounded to bf16
-int64_t conv1_wgrad_tc_scratch_bytes(int B);
+                      void* pool_bf16 = nullptr,       // (optional) second copy of pool, rounded to bf16
+                      int C1 = 64);                    // output channels (a multiple of 64: one CTA per image and 64-channel slice)
+int64_t conv1_wgrad_tc_scratch_bytes(int B, int C1 = 64);
 // the kernel leaves one partial [4864] (dw [25][3][64], then db [64]) per CTA in scratch and a fixed-order reduction
 // writes dw / db -- unless defer_reduce, in which case the caller sums the conv1_wgrad_tc_partials(B) partials itself
 // (sgd_apply_reduce_f32 does, at the end of a step; dw and db are then adjacent in the flat gradient buffer)
 int conv1_wgrad_tc_partials(int B);
 int conv1_wgrad_tc(const uint8_t* img, const float* dpool, const float* pool, const uint8_t* arg, float* dw, float* db,
-                   float* scratch, int B, int ih, int iw, int H, int W, cudaStream_t st, bool defer_reduce = false);
+                   float* scratch, int B, int ih, int iw, int H, int W, cudaStream_t st, bool defer_reduce = false,
+                   int C1 = 64);
 
 }  // namespace b200

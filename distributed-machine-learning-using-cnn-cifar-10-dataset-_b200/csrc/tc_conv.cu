@@ -1047,8 +1047,9 @@ int pack_conv_weights(const float* w, void* wp, int Cin, int Cout, cudaStream_t 
   return B200_OK;
 }
 int conv5x5_fwd_tc(const float* x, const void* wp, const float* bias, float* y, int B, int H, int W, int Cin,
-                   int Cout, int relu, cudaStream_t st) {
-  return launch_conv<false>(x, (const uint8_t*)wp, bias, y, B, H, W, Cin, Cout, relu, st);
+                   int Cout, int relu, cudaStream_t st, const void* x_bf16) {
+  return launch_conv<false>(x, (const uint8_t*)wp, bias, y, B, H, W, Cin, Cout, relu, st, nullptr, nullptr, nullptr, nullptr,
+                            nullptr, x_bf16);
 }
 // conv + bias + ReLU + 3x3/2 SAME max-pool in one kernel; y (the un-pooled activations) is optional
 int conv5x5_pool_fwd_tc(const float* x, const void* wp, const float* bias, float* y, float* pool, uint8_t* arg, int B,

@@ -61,6 +61,7 @@ struct Conv1FwdArgs {
   __nv_bfloat16* pool_bf16;   // [B,OH,OW,64] or null: pool rounded to bf16 for the consumers that stage it as an MMA operand
   float* conv_dbg;      // [B,H,W,64] or null (tests: lets the pool fusion be checked on its own input)
   C1Geom g;
+  int C1;               // output channels of the layer; a CTA computes the 64 starting at blockIdx.y * 64
   long long* timeline;  // diagnostics: clock64 stamps of CTA 0 in slots 14, 15, 30, 31 of the timeline buffer, or null
 };
 
@@ -84,6 +85,7 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int n = blockIdx.x;
+  const int C1 = a.C1, nc0 = blockIdx.y * 64;
   const int tmem_cols = g.tiles * 64 <= 64 ? 64 : g.tiles * 64 <= 128 ? 128 : g.tiles * 64 <= 256 ? 256 : 512;
 
   if (tid == 0) {
@@ -124,7 +126,7 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
         for (int u = 0; u < WB; ++u) {
           const int q = min(tid + u * WORKERS, 25 * 64 - 1), cout = q & 63, kc = q >> 6;
 #pragma unroll
-          for (int e = 0; e < 3; ++e) wv[u][e] = __ldg(a.w + (kc * 3 + e) * 64 + cout);
+          for (int e = 0; e < 3; ++e) wv[u][e] = __ldg(a.w + (kc * 3 + e) * C1 + nc0 + cout);
         }
       }
 #pragma unroll
@@ -156,7 +158,7 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
     // ---- epilogue 1: TMEM -> +bias, ReLU -> fp32 conv tile in shared memory, tile by tile as the MMAs finish ----
     float bv[64];
 #pragma unroll
-    for (int j = 0; j < 64; j += 4) *reinterpret_cast<float4*>(bv + j) = __ldg(reinterpret_cast<const float4*>(a.bias + j));
+    for (int j = 0; j < 64; j += 4) *reinterpret_cast<float4*>(bv + j) = __ldg(reinterpret_cast<const float4*>(a.bias + nc0 + j));
     for (int t = (warp >> 2); t < g.tiles; t += 2) {
       mbar_wait(smem_u32(accum + t), 0);
       tc_fence_after();
@@ -165,7 +167,7 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
       const int r = p / g.P, c = p - r * g.P;
       const bool valid = (r < g.H) && (c < g.W);
       float* row = convbuf + (size_t)(r * g.W + c) * kConvRow;
-      float* dbg = a.conv_dbg ? a.conv_dbg + (((size_t)n * g.H + r) * g.W + c) * 64 : nullptr;
+      float* dbg = a.conv_dbg ? a.conv_dbg + (((size_t)n * g.H + r) * g.W + c) * C1 + nc0 : nullptr;
 #pragma unroll
       for (int c0 = 0; c0 < 64; c0 += 32) {
         uint32_t v[32];
@@ -249,7 +251,7 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
           }
         }
       }
-      const size_t o = ((size_t)n * g.OH * g.OW + cell) * 64 + c8 * 8;
+      const size_t o = ((size_t)n * g.OH * g.OW + cell) * C1 + nc0 + c8 * 8;
       *reinterpret_cast<float4*>(a.pool + o) = make_float4(best[0], best[1], best[2], best[3]);
       *reinterpret_cast<float4*>(a.pool + o + 4) = make_float4(best[4], best[5], best[6], best[7]);
       if (a.pool_bf16) *reinterpret_cast<uint4*>(a.pool_bf16 + o) = pack8(best);
@@ -266,23 +268,23 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
 }  // namespace
 
 bool conv1_tc_supported(int H, int W, int c_in, int c1) {
-  if (c_in != 3 || c1 != 64) return false;
+  if (c_in != 3 || c1 <= 0 || c1 % 64 != 0) return false;
   C1Geom g = make_c1geom(1, H, W, H, W);
   size_t smem = ((g.npix * 16 + 127) & ~127) + 26 * kWLbo + 64 + (size_t)H * W * kConvRow * 4 + 256;
   return g.tiles * 64 <= 512 && smem <= 227 * 1024;
 }
 
 int conv1_pool_fwd_tc(const uint8_t* img, const float* w, const float* bias, float* pool, uint8_t* arg,
-                      float* conv_dbg, int B, int ih, int iw, int H, int W, cudaStream_t st, void* pool_bf16) {
+                      float* conv_dbg, int B, int ih, int iw, int H, int W, cudaStream_t st, void* pool_bf16, int C1) {
   B200_REQUIRE(B > 0 && H <= ih && W <= iw && H >= 4 && W >= 4, "conv1_pool_fwd_tc: bad shape");
-  B200_REQUIRE(conv1_tc_supported(H, W, 3, 64), "conv1_pool_fwd_tc: crop %dx%d does not fit one CTA", H, W);
+  B200_REQUIRE(conv1_tc_supported(H, W, 3, C1), "conv1_pool_fwd_tc: crop %dx%d x %d channels is not supported", H, W, C1);
   C1Geom g = make_c1geom(B, ih, iw, H, W);
   const int smem = ((g.npix * 16 + 127) & ~127) + 26 * kWLbo + 64 + H * W * kConvRow * 4 + 256;
   static PerDeviceOnce attr;
   if (attr.first())
     B200_CUDA_TRY(cudaFuncSetAttribute(conv1_pool_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-  Conv1FwdArgs a{img, w, bias, pool, arg, reinterpret_cast<__nv_bfloat16*>(pool_bf16), conv_dbg, g, g_conv1_timeline};
-  conv1_pool_fwd_kernel<<<B, 352, smem, st>>>(a);
+  Conv1FwdArgs a{img, w, bias, pool, arg, reinterpret_cast<__nv_bfloat16*>(pool_bf16), conv_dbg, g, C1, g_conv1_timeline};
+  conv1_pool_fwd_kernel<<<dim3(B, C1 / 64), 352, smem, st>>>(a);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
@@ -303,8 +305,9 @@ struct Conv1WgradArgs {
   const float* dpool;     // [B,OH,OW,64]  gradient w.r.t. pool1
   const float* pool;      // [B,OH,OW,64]  pool1 itself (ReluGrad mask: the selected cell is > 0 iff pool1 > 0)
   const uint8_t* arg;     // [B,OH,OW,64]
-  float* part;            // [CTAs][4864]: this CTA's sum of dw [25][3][64] followed by db [64]
+  float* part;            // [slices][CTAs][4864]: this CTA's sum of dw [25][3][64] followed by db [64] of its channel slice
   C1Geom g;
+  int C1;                 // channels of the layer; a CTA works on the 64 starting at blockIdx.y * 64
   long long* timeline;    // diagnostics: clock64 stamps of CTA 0 in slots [25,31) of the timeline buffer, or null
 };
 
@@ -329,6 +332,7 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
   const int nband = (g.H + C1W_BR - 1) / C1W_BR;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int C1 = a.C1, nc0 = blockIdx.y * 64;
   const int nimg = (g.B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
   const int ksteps = (g.H * g.P + 15) / 16;
 
@@ -359,16 +363,29 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
       pdl_launch_dependents();
       // pooled gradient, pool1 and argmax of this image: three contiguous blocks, fetched with bulk copies (TMA)
       // while the x strip is built -- as register loads this staging cost 5-8k cycles of round trips
-      if (tid == 0) {
-        const uint32_t nb4 = (uint32_t)ncell * 64 * 4, nb1 = (uint32_t)ncell * 64, bar = smem_u32(staged);
-        const uint8_t* gd = reinterpret_cast<const uint8_t*>(a.dpool + (size_t)n * ncell * 64);
-        const uint8_t* gp = reinterpret_cast<const uint8_t*>(a.pool + (size_t)n * ncell * 64);
-        mbar_arrive_expect_tx(bar, 2 * nb4 + nb1);
-        for (uint32_t off = 0; off < nb4; off += 16384) {
-          bulk_g2s(smem_u32(dpm) + off, gd + off, min(16384u, nb4 - off), bar);
-          bulk_g2s(smem_u32(plr) + off, gp + off, min(16384u, nb4 - off), bar);
+      if (C1 == 64) {
+        if (tid == 0) {
+          const uint32_t nb4 = (uint32_t)ncell * 64 * 4, nb1 = (uint32_t)ncell * 64, bar = smem_u32(staged);
+          const uint8_t* gd = reinterpret_cast<const uint8_t*>(a.dpool + (size_t)n * ncell * 64);
+          const uint8_t* gp = reinterpret_cast<const uint8_t*>(a.pool + (size_t)n * ncell * 64);
+          mbar_arrive_expect_tx(bar, 2 * nb4 + nb1);
+          for (uint32_t off = 0; off < nb4; off += 16384) {
+            bulk_g2s(smem_u32(dpm) + off, gd + off, min(16384u, nb4 - off), bar);
+            bulk_g2s(smem_u32(plr) + off, gp + off, min(16384u, nb4 - off), bar);
+          }
+          bulk_g2s(smem_u32(argb), a.arg + (size_t)n * ncell * 64, nb1, bar);
         }
-        bulk_g2s(smem_u32(argb), a.arg + (size_t)n * ncell * 64, nb1, bar);
+      } else if (warp == 0) {
+        // a 64-channel slice of a wider layer: one 256 / 256 / 64-byte piece per pooled cell, issued by a whole warp
+        const uint32_t bar = smem_u32(staged);
+        if (lane == 0) mbar_arrive_expect_tx(bar, (uint32_t)ncell * (256 + 256 + 64));
+        __syncwarp();
+        const size_t base = (size_t)n * ncell * C1 + nc0;
+        for (int cell = lane; cell < ncell; cell += 32) {
+          bulk_g2s(smem_u32(dpm) + cell * 256, a.dpool + base + (size_t)cell * C1, 256, bar);
+          bulk_g2s(smem_u32(plr) + cell * 256, a.pool + base + (size_t)cell * C1, 256, bar);
+          bulk_g2s(smem_u32(argb) + cell * 64, a.arg + base + (size_t)cell * C1, 64, bar);
+        }
       }
       // x strip: channels 0..2 = pixel bytes (0 in the pads), channel 3 = 1 in EVERY slot
       const uint8_t* rec = a.img + (size_t)n * 3 * g.ih * g.iw;
@@ -426,7 +443,7 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
       // warp instruction.  The partials are summed in a fixed order afterwards (run-to-run identical gradients;
       // fp32 atomics here made the last bits depend on the order in which CTAs finished).
       const int cout = warp * 16 + lane;
-      float* part = a.part + (size_t)blockIdx.x * 4864;
+      float* part = a.part + ((size_t)blockIdx.y * gridDim.x + blockIdx.x) * 4864;
       for (int di = 0; di < 5; ++di) {
 #pragma unroll 1
         for (int c0 = 0; c0 < 64; c0 += 32) {
@@ -492,11 +509,45 @@ size_t conv1_wgrad_smem(const C1Geom& g) {
 }  // namespace
 
 int conv1_wgrad_tc_partials(int B) { return conv1_wgrad_ctas(B); }
-int64_t conv1_wgrad_tc_scratch_bytes(int B) { return (int64_t)conv1_wgrad_ctas(B) * 4864 * 4; }
+int64_t conv1_wgrad_tc_scratch_bytes(int B, int C1) { return (int64_t)conv1_wgrad_ctas(B) * (C1 / 64) * 4864 * 4; }
+
+namespace {
+// wider layers: the per-slice partials [slice][S][4864] summed (same warp order as reduce_partials_warp) into
+// dw [25][3][C1] and db [C1]
+__global__ void conv1_reduce_slices_kernel(const float* __restrict__ part, float* __restrict__ dw, float* __restrict__ db,
+                                           int S, int C1) {
+  pdl_wait();
+  const int slice = blockIdx.y;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x, lane = t & 31;
+  const int grp = min(t >> 5, 4864 / 4 - 1), i = grp * 4;
+  const float* p = part + (size_t)slice * S * 4864;
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int z0 = lane; z0 < S; z0 += 128) {
+    float4 v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int z = z0 + 32 * j;
+      v[j] = z < S ? __ldg(reinterpret_cast<const float4*>(p + (size_t)z * 4864 + i)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { s.x += v[j].x; s.y += v[j].y; s.z += v[j].z; s.w += v[j].w; }
+  }
+#pragma unroll
+  for (int m = 1; m <= 16; m <<= 1) {
+    s.x += __shfl_xor_sync(0xffffffffu, s.x, m); s.y += __shfl_xor_sync(0xffffffffu, s.y, m);
+    s.z += __shfl_xor_sync(0xffffffffu, s.z, m); s.w += __shfl_xor_sync(0xffffffffu, s.w, m);
+  }
+  if (lane == 0 && (t >> 5) < 4864 / 4) {
+    if (i < 4800) *reinterpret_cast<float4*>(dw + (size_t)(i >> 6) * C1 + slice * 64 + (i & 63)) = s;
+    else if (db) *reinterpret_cast<float4*>(db + slice * 64 + (i - 4800)) = s;
+  }
+}
+}  // namespace
 
 int conv1_wgrad_tc(const uint8_t* img, const float* dpool, const float* pool, const uint8_t* arg, float* dw, float* db,
-                   float* scratch, int B, int ih, int iw, int H, int W, cudaStream_t st, bool defer_reduce) {
+                   float* scratch, int B, int ih, int iw, int H, int W, cudaStream_t st, bool defer_reduce, int C1) {
   B200_REQUIRE(B > 0 && H <= ih && W <= iw && H >= 4 && W >= 4, "conv1_wgrad_tc: bad shape");
+  B200_REQUIRE(C1 > 0 && C1 % 64 == 0 && (C1 == 64 || !defer_reduce), "conv1_wgrad_tc: %d channels", C1);
   B200_REQUIRE(scratch && ((uintptr_t)scratch & 15) == 0, "conv1_wgrad_tc: scratch must be a 16-byte aligned buffer");
   C1Geom g = make_c1geom(B, ih, iw, H, W);
   const size_t smem = conv1_wgrad_smem(g);
@@ -505,12 +556,17 @@ int conv1_wgrad_tc(const uint8_t* img, const float* dpool, const float* pool, co
   if (attr.first())
     B200_CUDA_TRY(cudaFuncSetAttribute(conv1_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   const int S = conv1_wgrad_ctas(B);
-  Conv1WgradArgs a{img, dpool, pool, arg, scratch, g, g_conv1_timeline};
+  Conv1WgradArgs a{img, dpool, pool, arg, scratch, g, C1, g_conv1_timeline};
   const bool overlap = g_pdl_next;
   g_pdl_next = false;
-  B200_CUDA_TRY(launch_kernel(conv1_wgrad_kernel, dim3(S), dim3(416), smem, st, a));
+  B200_CUDA_TRY(launch_kernel(conv1_wgrad_kernel, dim3(S, C1 / 64), dim3(416), smem, st, a));
   if (defer_reduce) return B200_OK;
   g_pdl_next = overlap;                                   // (the reduction's prologue may overlap the kernel's tail)
+  if (C1 != 64) {
+    B200_CUDA_TRY(launch_kernel(conv1_reduce_slices_kernel, dim3((4864 / 4 * 32 + 255) / 256, C1 / 64), dim3(256), 0, st,
+                                (const float*)scratch, dw, db, S, C1));
+    return B200_OK;
+  }
   if (db == dw + 4800) return reduce_partials_warp(scratch, dw, 4864, S, 4864, st);
   B200_TRY(reduce_partials_warp(scratch, dw, 4800, S, 4864, st));
   return db ? reduce_partials_warp(scratch + 4800, db, 64, S, 4864, st) : B200_OK;

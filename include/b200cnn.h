@@ -194,6 +194,16 @@ int b200_conv1_wgrad_bf16(const uint8_t* images, const float* dpool, const float
  * forward and dgrad take the filter PACKED: b200_conv5x5_pack_weights turns the fp32 HWIO tensor into
  * bf16 shared-memory images (b200_conv5x5_packed_bytes bytes) that the kernels fetch with bulk copies;
  * one packed copy serves both directions. */
+/* b200_conv1_pool_fwd_bf16 / b200_conv1_wgrad_bf16 for a conv1 with c1 output channels (a multiple of 64; the
+ * width-scaled model of BASELINE.json has 256): w [5,5,3,c1], bias [c1], pool / arg / dpool [batch,OH,OW,c1], dw
+ * [5,5,3,c1], db [c1]; one CTA per image and 64-channel slice.  scratch for the gradient: 19456 bytes x min(batch, 148)
+ * x c1 / 64.  Replace :107-113 and their gradients like the 64-channel entry points. */
+int b200_conv1_pool_fwd_bf16_c(const uint8_t* images, const float* w, const float* bias, float* pool, uint8_t* arg,
+                               float* conv_dbg, int32_t batch, int32_t img_h, int32_t img_w, int32_t crop_h,
+                               int32_t crop_w, int32_t c1, void* stream);
+int b200_conv1_wgrad_bf16_c(const uint8_t* images, const float* dpool, const float* pool, const uint8_t* arg, float* dw,
+                            float* db, void* scratch, int64_t scratch_bytes, int32_t batch, int32_t img_h, int32_t img_w,
+                            int32_t crop_h, int32_t crop_w, int32_t c1, void* stream);
 /* diagnostics: when given a device buffer of 32 int64 (conv stamps in [0,8), FC-tail stamps in [16,25)), CTA 0 of the conv2 forward / dgrad kernel stores
  * clock64() at its phase boundaries (start, strip zeroed, strip filled, MMA start, MMA issued,
  * accumulators ready, epilogue done); NULL switches it off. */

@@ -74,6 +74,46 @@ def test_conv_tensorcore_wide_channels(lib, B, H, W, Cin, Cout):
         assert relerr(dw.cpu().numpy(), rn.conv2d_same_grad_filter(xr, dyr)) <= TIGHT
 
 
+@pytest.mark.parametrize("B,C1", [(3, 128), (130, 256)])
+def test_conv1_pool_fused_wide(lib, B, C1):
+    """crop/cast + conv1 + bias + ReLU + pool1 and its filter / bias gradient for a conv1 with more than 64 output
+    channels: one CTA per image and 64-channel slice; same checks as the 64-channel test."""
+    crop = 24
+    rng = np.random.default_rng(52)
+    img = rng.integers(0, 256, (B, 3, 32, 32), dtype=np.uint8)
+    w = (rng.normal(size=(5, 5, 3, C1)) * 0.05).astype(np.float32)
+    b = (rng.normal(size=(C1,)) * 0.5).astype(np.float32)
+    x = rn.crop_cast(img, crop, crop)
+    wr = bf16_round(w)
+    OH = crop // 2
+    imgd, wd, bd = dev(img), dev(w), dev(b)
+    pool = torch.full((B, OH, OH, C1), float("nan"), device="cuda")
+    arg = torch.full((B, OH, OH, C1), 255, dtype=torch.uint8, device="cuda")
+    conv = torch.full((B, crop, crop, C1), float("nan"), device="cuda")
+    _lib.check(lib.b200_conv1_pool_fwd_bf16_c(imgd.data_ptr(), wd.data_ptr(), bd.data_ptr(), pool.data_ptr(), arg.data_ptr(),
+                                              conv.data_ptr(), B, 32, 32, crop, crop, C1, stream()))
+    torch.cuda.synchronize()
+    assert relerr(conv.cpu().numpy(), np.maximum(rn.conv2d_same(x, wr) + b, 0)) <= TIGHT
+    wy, warg = rn.maxpool_3x3s2_same(conv.cpu().numpy())
+    np.testing.assert_array_equal(pool.cpu().numpy(), wy)
+    np.testing.assert_array_equal(arg.cpu().numpy(), warg)
+    dpool = (rng.normal(size=(B, OH, OH, C1)) * (rng.random(size=(B, OH, OH, C1)) < 0.5)).astype(np.float32)
+    nbytes = 19456 * min(B, 148) * (C1 // 64)
+    scr = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    dw = torch.full((5, 5, 3, C1), float("nan"), device="cuda")
+    db = torch.full((C1,), float("nan"), device="cuda")
+    convn = conv.cpu().numpy().astype(np.float64)
+    dconv = rn.maxpool_3x3s2_same_grad(dpool.astype(np.float64), warg, (crop, crop)) * (convn > 0)
+    dconv_r = bf16_round(dconv)
+    for _ in range(2):
+        _lib.check(lib.b200_conv1_wgrad_bf16_c(imgd.data_ptr(), dev(dpool).data_ptr(), pool.data_ptr(), arg.data_ptr(),
+                                               dw.data_ptr(), db.data_ptr(), scr.data_ptr(), nbytes, B, 32, 32, crop, crop,
+                                               C1, stream()))
+        torch.cuda.synchronize()
+        assert relerr(dw.cpu().numpy(), rn.conv2d_same_grad_filter(x, dconv_r)) <= TIGHT
+        assert relerr(db.cpu().numpy(), dconv_r.sum((0, 1, 2))) <= TIGHT
+
+
 @pytest.mark.parametrize("kind,B", [("soft", 128), ("u8", 64)])
 def test_full_step_wide_model_bf16(kind, B):
     from test_gpu_parity import _oracle_backward_on_gpu_forward
@@ -91,13 +131,13 @@ def test_full_step_wide_model_bf16(kind, B):
     e.forward(dev(img), dev(lab.reshape(-1)))
     e.backward()
     torch.cuda.synchronize()
-    for name in ("conv1", "pool1", "conv2", "pool2", "full1", "full2", "logits"):
+    for name in ("pool1", "conv2", "pool2", "full1", "full2", "logits"):      # (conv1 is fused with pool1: never in HBM)
         assert relerr(e.tensor(name).cpu().numpy().reshape(a[name].shape), a[name]) <= LOOSE, name
     assert abs(float(e.loss()) - loss) <= 2e-2 * abs(loss)
     srt = np.sort(a["logits"], axis=1)
     safe = (srt[:, -1] - srt[:, -2]) > 2 * LOOSE * np.abs(a["logits"]).max()
     np.testing.assert_array_equal(e.pred().cpu().numpy()[safe], a["pred"][safe])
-    g2, _ = _oracle_backward_on_gpu_forward(e, params, lab, a)
+    g2, _ = _oracle_backward_on_gpu_forward(e, params, lab, a, fused_conv1=True)
     got = e.get_grads()
     for k in rn.PARAM_NAMES:
         assert relerr(got[k], g2[k]) <= 2e-2, (k, relerr(got[k], g2[k]))
