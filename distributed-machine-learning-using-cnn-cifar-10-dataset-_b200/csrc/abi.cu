@@ -291,7 +291,11 @@ static int forward_impl(b200_handle h, const uint8_t* images, const int32_t* lab
     SITE("conv2_fwd", conv5x5_fwd_tc(pool1, h->ptr<void>("w2_packed"), h->P(P_B2), conv2, c.batch, h->h1, h->w1, c.c1, c.c2, 1, st,
                                      fused1 ? h->ptr<void>("pool1_bf16") : nullptr));
     SITE("pool2_fwd", maxpool_fwd_f32(conv2, pool2, h->ptr<uint8_t>("arg2"), c.batch, h->h1, h->w1, c.c2, st));
-    SITE("full1_fwd", fc_fwd_tc(pool2, h->P(P_FW1), h->P(P_FB1), full1, c.batch, h->flat, c.f1, 1, st));
+    // FC1 (M = batch is one tile row, K = 9216 in the wide model): split-K over the SMs + a bias / ReLU pass
+    SITE("full1_fwd", fc_fwd_tc_splitk(pool2, h->P(P_FW1), h->ptr<float>("fc1_part"), c.batch, h->flat, c.f1, st));
+    g_pdl_next = !h->profiling;
+    TRY(splitk_finish_f32(h->ptr<float>("fc1_part"), fc_fwd_tc_splits(c.batch, h->flat, c.f1), h->P(P_FB1), full1, c.batch,
+                          c.f1, 1, st));
     SITE("full2_fwd", fc_fwd_tc(full1, h->P(P_FW2), h->P(P_FB2), full2, c.batch, c.f1, c.f2, 1, st));
     SITE("full3_fwd", fc_fwd_f32(full2, h->P(P_FW3), h->P(P_FB3), logits, c.batch, c.f2, c.n_cls, 1, st));
     SITE("head", head_f32(logits, labels, h->ptr<float>("loss"), h->ptr<float>("dlogits"), h->ptr<int32_t>("pred"),
@@ -428,12 +432,15 @@ static int backward_impl(b200_handle h, void* stream, const P2PCtx* px, bool def
     TRY(colsum_f32(dfull2, h->G(P_FB2), scratch, c.batch, c.f2, st));
     SITE("full1_bwd", fc_bwd_tc(h->ptr<float>("pool2"), h->P(P_FW1), dfull1, dpool2, h->G(P_FW1), c.batch, h->flat, c.f1, 0, st));
     TRY(colsum_f32(dfull1, h->G(P_FB1), scratch, c.batch, c.f1, st));
+    const bool f1tc = conv1_tc_supported(c.crop_h, c.crop_w, c.c_in, c.c1);      // then pool1 also exists in bf16
     SITE("pool2_bwd", maxpool_bwd_f32(dpool2, h->ptr<uint8_t>("arg2"), h->ptr<float>("conv2"), dconv2, c.batch, h->h1,
-                                      h->w1, c.c2, 1, st));
+                                      h->w1, c.c2, 1, st, nullptr, f1tc ? h->ptr<void>("dconv2_bf16") : nullptr));
     SITE("conv2_wgrad", conv5x5_wgrad_tc(h->ptr<float>("pool1"), dconv2, h->G(P_W2), scratch, c.batch, h->h1, h->w1, c.c1,
-                                         c.c2, st));
+                                         c.c2, st, f1tc ? h->ptr<void>("pool1_bf16") : nullptr,
+                                         f1tc ? h->ptr<void>("dconv2_bf16") : nullptr));
     TRY(colsum_f32(dconv2, h->G(P_B2), scratch, c.batch * h->h1 * h->w1, c.c2, st));
-    SITE("conv2_dgrad", conv5x5_dgrad_tc(dconv2, h->ptr<void>("w2_packed"), dpool1, c.batch, h->h1, h->w1, c.c1, c.c2, st));
+    SITE("conv2_dgrad", conv5x5_dgrad_tc(dconv2, h->ptr<void>("w2_packed"), dpool1, c.batch, h->h1, h->w1, c.c1, c.c2, st,
+                                         f1tc ? h->ptr<void>("dconv2_bf16") : nullptr));
     if (conv1_tc_supported(c.crop_h, c.crop_w, c.c_in, c.c1)) {
       SITE("conv1_wgrad", conv1_wgrad_tc(h->last_images, dpool1, h->ptr<float>("pool1"), h->ptr<uint8_t>("arg1"),
                                          h->G(P_W1), h->G(P_B1), scratch, c.batch, c.img_h, c.img_w, c.crop_h,
@@ -688,7 +695,7 @@ int b200_launches_per_step(b200_handle h, int32_t* n) {
     // layer-by-layer schedule: forward 8 (10 with the SIMT conv1) | FC3 bwd 4, FC2 / FC1 bwd 2 + 2 each, pool2 bwd, conv2
     // wgrad 2 + colsum 2, dgrad, conv1 wgrad 2 (pool1 bwd + 4 with the SIMT conv1) | sgd
     const bool f1 = conv1_tc_supported(h->cfg.crop_h, h->cfg.crop_w, h->cfg.c_in, h->cfg.c1);
-    *n = (f1 ? 8 : 10) + 4 + 4 + 4 + 1 + 4 + 1 + (f1 ? 2 : 5) + 1;
+    *n = (f1 ? 8 : 10) + 1 + 4 + 4 + 4 + 1 + 4 + 1 + (f1 ? 2 : 5) + 1;      // (+1: FC1's split-K bias / ReLU pass)
   } else if (h->cfg.mode == B200_MODE_BF16) {
     // conv1 (3 or 1), conv2, pool2, FC1 split-K, tail x2 | FC1 bwd x2, pool2 bwd, conv2 wgrad x2, dgrad, conv1 wgrad (2 or 1+4), sgd
     const bool f1 = conv1_tc_supported(h->cfg.crop_h, h->cfg.crop_w, h->cfg.c_in, h->cfg.c1);

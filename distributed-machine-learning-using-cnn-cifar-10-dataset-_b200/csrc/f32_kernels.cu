@@ -7,6 +7,8 @@
 // implicit GEMM through gather loaders) and the FC forward / backward products.
 #include <algorithm>
 
+#include <cuda_bf16.h>
+
 #include "launch.h"
 
 namespace b200 {
@@ -324,7 +326,7 @@ int maxpool_fwd_f32(const float* x, float* y, uint8_t* arg, int B, int H, int W,
 __global__ void maxpool_bwd_kernel(const float* __restrict__ dy, const uint8_t* __restrict__ arg,
                                    const float* __restrict__ x, float* __restrict__ dx, int B, int H, int W,
                                    int C, int OH, int OW, int pbh, int pbw, int relu_mask,
-                                   float* __restrict__ colsum) {
+                                   float* __restrict__ colsum, __nv_bfloat16* __restrict__ dx_bf16) {
   const int64_t total = (int64_t)B * H * W * C;
   float csum = 0.f;   // with 256 % C == 0 a thread keeps one channel over the whole grid-stride loop
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
@@ -357,6 +359,7 @@ __global__ void maxpool_bwd_kernel(const float* __restrict__ dy, const uint8_t* 
       }
     }
     dx[i] = s;
+    if (dx_bf16) dx_bf16[i] = __float2bfloat16_rn(s);      // operand copy for the tensor-core filter gradient
     csum += s;
   }
   if (colsum) {       // BiasAddGrad of the layer below, fused: per-CTA partial -> one atomic per channel
@@ -371,7 +374,7 @@ __global__ void maxpool_bwd_kernel(const float* __restrict__ dy, const uint8_t* 
   }
 }
 int maxpool_bwd_f32(const float* dy, const uint8_t* arg, const float* x, float* dx, int B, int H, int W,
-                    int C, int relu_mask, cudaStream_t st, float* colsum_atomic) {
+                    int C, int relu_mask, cudaStream_t st, float* colsum_atomic, void* dx_bf16) {
   B200_REQUIRE(!colsum_atomic || (256 % C) == 0, "maxpool_bwd: fused bias gradient needs C to divide 256");
   B200_REQUIRE(B > 0 && H > 1 && W > 1 && C > 0, "maxpool_bwd: bad shape");
   B200_REQUIRE(!relu_mask || x, "maxpool_bwd: relu_mask needs x");
@@ -379,7 +382,8 @@ int maxpool_bwd_f32(const float* dy, const uint8_t* arg, const float* x, float* 
   pool_geom(H, W, OH, OW, pbh, pbw);
   int64_t total = (int64_t)B * H * W * C;
   int grid = (int)std::min<int64_t>((total + 255) / 256, kNumSMs * 16);
-  maxpool_bwd_kernel<<<grid, 256, 0, st>>>(dy, arg, x, dx, B, H, W, C, OH, OW, pbh, pbw, relu_mask, colsum_atomic);
+  maxpool_bwd_kernel<<<grid, 256, 0, st>>>(dy, arg, x, dx, B, H, W, C, OH, OW, pbh, pbw, relu_mask, colsum_atomic,
+                                           reinterpret_cast<__nv_bfloat16*>(dx_bf16));
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
@@ -595,6 +599,27 @@ int sgd_apply_reduce_f32(float* p, float* g, int64_t n, float lr, float scale, c
   if (carve.first()) B200_CUDA_TRY(prefer_max_shared(sgd_reduce_kernel));
   B200_CUDA_TRY(launch_kernel(sgd_reduce_kernel, dim3(grid), dim3(256), 0, st, p, g, n, lr * scale, part, S, n_part));
   B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+// y[b][n] = relu?(sum over splits of part[s][b][n] + bias[n]): closes a split-K product (FC1 of the layer-by-layer schedule)
+__global__ void splitk_finish_kernel(const float* __restrict__ part, int nsplit, int64_t stride, const float* __restrict__ bias,
+                                     float* __restrict__ y, int64_t total4, int N, int relu) {
+  pdl_wait();
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total4; i += (int64_t)gridDim.x * blockDim.x) {
+    float4 s = __ldg(reinterpret_cast<const float4*>(bias + (i * 4) % N));
+    for (int z = 0; z < nsplit; ++z) {
+      const float4 v = __ldg(reinterpret_cast<const float4*>(part + z * stride) + i);
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    if (relu) { s.x = fmaxf(s.x, 0.f); s.y = fmaxf(s.y, 0.f); s.z = fmaxf(s.z, 0.f); s.w = fmaxf(s.w, 0.f); }
+    reinterpret_cast<float4*>(y)[i] = s;
+  }
+}
+int splitk_finish_f32(const float* part, int nsplit, const float* bias, float* y, int B, int N, int relu, cudaStream_t st) {
+  B200_REQUIRE(part && bias && y && nsplit > 0 && B > 0 && N > 0 && N % 4 == 0, "splitk_finish: bad argument");
+  const int64_t total4 = (int64_t)B * N / 4;
+  const int grid = (int)std::min<int64_t>((total4 + 255) / 256, kNumSMs * 4);
+  B200_CUDA_TRY(launch_kernel(splitk_finish_kernel, dim3(grid), dim3(256), 0, st, part, nsplit, (int64_t)B * N, bias, y, total4, N, relu));
   return B200_OK;
 }
 int reduce_partials_warp(const float* part, float* out, int n, int S, int stride, cudaStream_t st) {

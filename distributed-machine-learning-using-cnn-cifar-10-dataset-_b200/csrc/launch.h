@@ -17,7 +17,10 @@ int maxpool_fwd_f32(const float* x, float* y, uint8_t* arg, int B, int H, int W,
 // colsum_atomic (optional, must be zero on entry): += sum of dx over (B,H,W) per channel, i.e. the
 // BiasAddGrad of the layer that fed the pool
 int maxpool_bwd_f32(const float* dy, const uint8_t* arg, const float* x, float* dx, int B, int H, int W,
-                    int C, int relu_mask, cudaStream_t st, float* colsum_atomic = nullptr);
+                    int C, int relu_mask, cudaStream_t st, float* colsum_atomic = nullptr,
+                    void* dx_bf16 = nullptr);      // (optional) dx also rounded to bf16, same layout
+// y = relu?(sum of nsplit partials [nsplit][B][N] + bias): closes fc_fwd_tc_splitk
+int splitk_finish_f32(const float* part, int nsplit, const float* bias, float* y, int B, int N, int relu, cudaStream_t st);
 int fc_fwd_f32(const float* x, const float* w, const float* b, float* y, int B, int K, int N, int relu,
                cudaStream_t st);
 int64_t colsum_scratch_bytes(int rows, int cols);
@@ -63,7 +66,7 @@ int conv5x5_pool_fwd_tc(const float* x, const void* wp, const float* bias, float
                         int H, int W, int Cin, int Cout, cudaStream_t st, const void* x_bf16 = nullptr,
                         void* pool_img = nullptr);   // (optional) pooled output as FC1's bf16 operand image [H'W'Cout/8][B][8]
 int conv5x5_dgrad_tc(const float* dy, const void* wp, float* dx, int B, int H, int W, int Cin, int Cout,
-                     cudaStream_t st);
+                     cudaStream_t st, const void* dy_bf16 = nullptr);      // (optional) dy already in bf16: TMA-filled strip
 // the same two gradients fed by the POOLED gradient: dconv = MaxPoolGrad(dpool, arg) * [pool > 0] is gathered
 // inside the kernels (64 channels); dbias (optional, zero on entry) receives sum(dconv) through atomics;
 // dconv_out (optional) receives dconv as a dense [B,H,W,64] fp32 tensor

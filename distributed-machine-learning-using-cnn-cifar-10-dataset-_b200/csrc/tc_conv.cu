@@ -30,7 +30,7 @@ using namespace tc;
 namespace {
 constexpr int LOADERS = 128;
 constexpr int WSTAGES = 3;      // filter stages in shared memory when a stage = the five taps of one filter row
-constexpr int MAX_WSTAGES = 8;  // ... and the most single-tap stages (two-CTAs-per-SM variants)
+constexpr int MAX_WSTAGES = 10; // ... and the most single-tap stages (two-CTAs-per-SM and wide variants)
 
 struct ConvGeom {
   int B, H, W, KC, NC;      // batch, image size, contraction channels, output channels
@@ -40,6 +40,9 @@ struct ConvGeom {
   int ch_stride;            // bytes between channel chunks of the strip (npix*16 + 16)
   int nstages;              // filter stages in the ring (of 5 taps or 1 tap each, a template parameter of the kernel)
   int tma_rows;             // > 0: the strip is written by the TMA (tensor-map box of P x tma_rows pixel slots per chunk)
+  int two_pass;             // KSPLIT == 2 with a TMA strip: the strip holds HALF the contraction channels at a time -- all
+                            // 25 taps of channels [0, KC/2), a refill, all 25 taps of the rest -- which leaves twice the
+                            // shared memory for filter stages in flight (the filter stream is latency-bound)
 };
 
 __host__ inline ConvGeom make_geom(int B, int H, int W, int KC, int NC, int ipc) {
@@ -53,6 +56,7 @@ __host__ inline ConvGeom make_geom(int B, int H, int W, int KC, int NC, int ipc)
   g.ch_stride = g.npix * 16 + 16;
   g.nstages = WSTAGES;
   g.tma_rows = 0;
+  g.two_pass = 0;
   return g;
 }
 // The strip of ONE image written by the TMA: per 8-channel chunk one tensor-map box of P = W+4 columns x H+5 rows
@@ -249,7 +253,8 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
   const ConvGeom& g = a.g;
   extern __shared__ __align__(128) uint8_t smem[];
   const int kchunks = KSTEPS * 2;         // KC = 16 * KSTEPS
-  const int strip_bytes = kchunks * g.ch_stride;
+  const bool two_pass = KSPLIT == 2 && g.two_pass;
+  const int strip_bytes = (two_pass ? kchunks / 2 : kchunks) * g.ch_stride;
   // weight stage: MN-major [BN/8 groups][KC k][16B] (SBO = KC*16+16)  |  K-major [KC/8 chunks][BN rows][16B]
   const int w_mn_sbo = (g.KC / KSPLIT) * 16 + 16, w_k_lbo = BN * 16 + 16;
   const int wtap = ((DGRAD ? (kchunks / KSPLIT) * w_k_lbo : (BN / 8) * w_mn_sbo) + 127) & ~127;   // one tap's (piece of the) operand image
@@ -262,7 +267,8 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
   uint64_t* wempty = wfull + MAX_WSTAGES;
   uint64_t* strip_full = wempty + MAX_WSTAGES;
   uint64_t* accum = strip_full + 1;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum + 1);
+  uint64_t* pass_done = accum + 1;        // two_pass: the MMAs on the first half of the channels have been issued and completed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pass_done + 1);
   float* dpm = reinterpret_cast<float*>(ctrl + 256);                  // POOL: [OH*OW][64] masked pooled gradient
   uint8_t* argb = reinterpret_cast<uint8_t*>(dpm + (POOL ? a.pg.OH * a.pg.OW * 64 : 0));
   float* bred = reinterpret_cast<float*>(argb + (POOL ? ((a.pg.OH * a.pg.OW * 64 + 15) & ~15) : 0));   // [64]
@@ -276,6 +282,7 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
     for (int s = 0; s < g.nstages; ++s) { mbar_init(smem_u32(wfull + s), 1); mbar_init(smem_u32(wempty + s), NISS); }
     mbar_init(smem_u32(strip_full), POOL ? 256 : (g.tma_rows ? 1 : LOADERS));
     mbar_init(smem_u32(accum), NISS);
+    mbar_init(smem_u32(pass_done), NISS);
     fence_mbar_init();
   }
   if (warp == 4) tmem_alloc(smem_u32(tmem_slot), tmem_cols);
@@ -465,13 +472,18 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
       for (int r = 0; r < ROUNDS; ++r) {
         const int s = r % g.nstages;
         const uint32_t ph = (r / g.nstages) & 1;
+        if (two_pass && r == 25) {                          // second half of the channels: the strip has been refilled
+          mbar_wait(smem_u32(strip_full), 1);
+          tc_fence_after();
+        }
         mbar_wait(smem_u32(wfull + s), ph);               // one wait and one commit per stage: both cost
         tc_fence_after();                                 // ~100 cycles of the issuing thread (measured)
         const uint32_t b_row = b_lo0 + (uint32_t)s * (wstage >> 4);
 #pragma unroll
         for (int tt = 0; tt < STAPS; ++tt, ++q) {
           const int dj = STAPS == 5 ? tt : dj1;
-          const uint32_t a_tap = a_lo0 + (uint32_t)((di - 2) * g.P + (dj - 2)) + (uint32_t)(hh * KST) * a_kstep;    // a tap is a slot offset
+          const uint32_t a_tap = a_lo0 + (uint32_t)((di - 2) * g.P + (dj - 2)) +     // a tap is a slot offset
+                                 (two_pass ? 0u : (uint32_t)(hh * KST) * a_kstep);
           // dgrad correlates with the filter rotated by 180 degrees: a five-tap stage holds forward row 4-di, read
           // backwards; a one-tap stage holds forward tap (4-di, 4-dj) itself
           const uint32_t b_tap = b_row + (uint32_t)(STAPS == 5 ? (DGRAD ? 4 - dj : dj) : 0) * (wtap >> 4);
@@ -486,7 +498,10 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
           }
         }
         umma_commit(smem_u32(wempty + s));        // arrives when this warp's MMAs on the stage are done
-        if (STAPS == 5) { if (++di == 5) di = 0; }
+        if (two_pass) {                           // pass-major: 25 taps of one half, then 25 taps of the other
+          if (r == 24) { umma_commit(smem_u32(pass_done)); hh = 1; }
+          if (++dj1 == 5) { dj1 = 0; if (++di == 5) di = 0; }
+        } else if (STAPS == 5) { if (++di == 5) di = 0; }
         else if (++hh == KSPLIT) { hh = 0; if (++dj1 == 5) { dj1 = 0; if (++di == 5) di = 0; } }
       }
       umma_commit(smem_u32(accum));
@@ -500,8 +515,9 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
         // ---- the strip: one tensor-map box per 8-channel chunk, image rows -3 .. H+1, zeros outside the image ----
         pdl_wait();
         const uint32_t bar = smem_u32(strip_full);
-        mbar_arrive_expect_tx(bar, (uint32_t)(kchunks * g.P * g.tma_rows * 16));
-        for (int c = 0; c < kchunks; ++c)
+        const int nc = two_pass ? kchunks / 2 : kchunks;
+        mbar_arrive_expect_tx(bar, (uint32_t)(nc * g.P * g.tma_rows * 16));
+        for (int c = 0; c < nc; ++c)
           tma_load_5d(smem_u32(strip + c * g.ch_stride), &a.tmap, 0, c, 0, -3, n_img0, bar);
       }
       const int img = (a.cout_f / 8) * (a.cin_f * 16 + 16);             // bytes of one packed tap
@@ -511,6 +527,15 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
       for (int r = 0; r < ROUNDS; ++r) {
         const int s = r % g.nstages;
         const uint32_t ph = (r / g.nstages) & 1;
+        if (two_pass && r == 25) {
+          // every MMA on the first half of the channels has completed: the strip may take the second half
+          mbar_wait(smem_u32(pass_done), 0);
+          const uint32_t sbar = smem_u32(strip_full);
+          mbar_arrive_expect_tx(sbar, (uint32_t)((kchunks / 2) * g.P * g.tma_rows * 16));
+          for (int c = 0; c < kchunks / 2; ++c)
+            tma_load_5d(smem_u32(strip + c * g.ch_stride), &a.tmap, 0, kchunks / 2 + c, 0, -3, n_img0, sbar);
+          hh = 1;
+        }
         mbar_wait(smem_u32(wempty + s), ph ^ 1);
         const uint32_t bar = smem_u32(wfull + s);
         // packed (forward) taps to fetch: a filter row in forward order, or the single tap the MMA warps want next
@@ -536,7 +561,8 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
             for (int c = 0; c < KCS; ++c) bulk_g2s(ws + c * w_k_lbo, src + (size_t)c * gstride, BN * 16, bar);
           }
         }
-        if (STAPS == 5) { if (++di == 5) di = 0; }
+        if (two_pass) { if (++dj1 == 5) { dj1 = 0; if (++di == 5) di = 0; } }
+        else if (STAPS == 5) { if (++di == 5) di = 0; }
         else if (++hh == KSPLIT) { hh = 0; if (++dj1 == 5) { dj1 = 0; if (++di == 5) di = 0; } }
       }
     }
@@ -652,7 +678,12 @@ int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, 
     g.nstages = nst2;
   } else if (wide) {
     g = g2;                                              // one image per CTA
-    g.nstages = std::min(MAX_WSTAGES, (227 * 1024 - strip2 - 256 - extra) / wtap);
+    // (two-pass strips double the filter bytes in flight -- 9 stages instead of 5 -- but measured no faster on the wide
+    //  model, 189 vs 172 us for conv2's forward: the stream is not bound by its depth; kept behind B200_CONV_TWO_PASS=1)
+    static const bool two_pass_env = getenv("B200_CONV_TWO_PASS") && atoi(getenv("B200_CONV_TWO_PASS")) == 1;
+    g.two_pass = (two_pass_env && ksplit == 2 && g.tma_rows > 0) ? 1 : 0;
+    const int strip_w = g.two_pass ? (((kchunks / 2) * g.ch_stride + 127) & ~127) : strip2;
+    g.nstages = std::min(MAX_WSTAGES, (227 * 1024 - strip_w - 256 - extra) / wtap);
     B200_REQUIRE(g.nstages >= 2, "conv5x5_tc: image %dx%d with %d channels does not leave room for the filter ring", H, W, KC);
   } else {
     const int ipc = pool_out ? 1 : pick_ipc(B, H, W, KC);       // the fused pool works on one image per CTA
@@ -666,7 +697,7 @@ int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, 
   }
   B200_REQUIRE(g.tiles * 64 <= 512, "conv5x5_tc: image %dx%d too large for one CTA's TMEM", H, W);
   const int staps = (two || wide) ? 1 : 5;
-  const int smem = ((kchunks * g.ch_stride + 127) & ~127) + g.nstages * staps * wtap + 256 + extra;
+  const int smem = ((((g.two_pass ? kchunks / 2 : kchunks)) * g.ch_stride + 127) & ~127) + g.nstages * staps * wtap + 256 + extra;
   B200_REQUIRE(smem <= 227 * 1024, "conv5x5_tc: %d bytes of shared memory needed", smem);
   void (*kern)(ConvArgs) = nullptr;
   if (pg) {
@@ -1059,8 +1090,9 @@ int conv5x5_pool_fwd_tc(const float* x, const void* wp, const float* bias, float
 }
 // dx = Conv2DBackpropInput(dy, w): contraction over the forward Cout, output the forward Cin
 int conv5x5_dgrad_tc(const float* dy, const void* wp, float* dx, int B, int H, int W, int Cin, int Cout,
-                     cudaStream_t st) {
-  return launch_conv<true>(dy, (const uint8_t*)wp, nullptr, dx, B, H, W, Cout, Cin, 0, st);
+                     cudaStream_t st, const void* dy_bf16) {
+  return launch_conv<true>(dy, (const uint8_t*)wp, nullptr, dx, B, H, W, Cout, Cin, 0, st, nullptr, nullptr, nullptr, nullptr,
+                           nullptr, dy_bf16);
 }
 static PoolGradSrc make_pool_src(const float* dpool, const float* pool, const uint8_t* arg, int H, int W) {
   PoolGradSrc p{dpool, pool, arg, (H + 1) / 2, (W + 1) / 2, 0, 0};
