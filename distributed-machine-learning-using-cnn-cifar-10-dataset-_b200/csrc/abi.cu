@@ -525,7 +525,7 @@ static int backward_impl(b200_handle h, void* stream, const P2PCtx* px, bool def
       // small kernel -- or, when the update follows at once (b200_train_step), inside the update kernel
       SITE("conv1_wgrad", conv1_wgrad_tc(h->last_images, dpool1, h->ptr<float>("pool1"), h->ptr<uint8_t>("arg1"),
                                          h->G(P_W1), h->G(P_B1), scratch, c.batch, c.img_h, c.img_w, c.crop_h,
-                                         c.crop_w, st, defer_conv1_reduce && !h->profiling));
+                                         c.crop_w, st, (defer_conv1_reduce || px) && !h->profiling));
     } else {
       SITE("pool1_bwd", maxpool_bwd_f32(dpool1, h->ptr<uint8_t>("arg1"), h->ptr<float>("conv1"), dconv1, c.batch,
                                         c.crop_h, c.crop_w, c.c1, 1, st));
@@ -543,9 +543,12 @@ static int backward_impl(b200_handle h, void* stream, const P2PCtx* px, bool def
       if (!fork)
         TRY(p2p_allreduce_sgd(px->peer_grads, px->peer_params, px->peer_pads, px->mc_grads, px->mc_params, px->state,
                               px->rank, px->world, h->p_total - off, px->lr, px->scale, st, off, 0, 0));
+      // (conv1's gradient partials are summed by the exchange kernel's first CTAs: no reduction launch in between)
+      const bool red = fused1 && !h->profiling && h->p_off[P_W1] == 0 && h->p_off[P_B1] == 4800;
       SITE("p2p_conv_update", p2p_allreduce_sgd(px->peer_grads, px->peer_params, px->peer_pads, px->mc_grads,
                                                 px->mc_params, px->state, px->rank, px->world, off, px->lr, px->scale,
-                                                st, 0, 1, 0));
+                                                st, 0, 1, 0, red ? scratch : nullptr,
+                                                red ? conv1_wgrad_tc_partials(c.batch) : 0, red ? 4864 : 0));
     }
     return B200_OK;
   }
@@ -585,6 +588,26 @@ int b200_train_step_p2p(b200_handle h, const uint8_t* images, const int32_t* lab
   TRY(forward_impl(h, images, labels, stream, true));
   const P2PCtx px{peer_grads, peer_params, peer_pads, mc_grads, mc_params, state, rank, world, lr, grad_scale};
   return backward_impl(h, stream, &px);
+}
+
+int b200_train_step_p2p_single(b200_handle h, const uint8_t* images, const int32_t* labels, const void* const* peer_grads,
+                               void* const* peer_params, void* const* peer_pads, const void* mc_grads, void* mc_params,
+                               uint32_t* state, int32_t rank, int32_t world, float lr, float grad_scale, void* stream) {
+  B200_READY(h);
+  B200_REQUIRE(peer_grads && peer_params && peer_pads && state && rank >= 0 && rank < world && world <= 8,
+               "train_step_p2p_single: bad argument");
+  B200_REQUIRE(peer_grads[rank] == h->grads && peer_params[rank] == h->params,
+               "train_step_p2p_single: entry `rank` of the peer tables must be the buffers bound to this handle");
+  const b200_config& c = h->cfg;
+  const bool red = c.mode == B200_MODE_BF16 && fused_bf16_shapes(c) && !h->profiling &&
+                   conv1_tc_supported(c.crop_h, c.crop_w, c.c_in, c.c1) && h->p_off[P_W1] == 0 && h->p_off[P_B1] == 4800;
+  TRY(forward_impl(h, images, labels, stream, true));
+  TRY(backward_impl(h, stream, nullptr, red));
+  cudaStream_t st = (cudaStream_t)stream;
+  SITE("p2p_sgd_apply", p2p_allreduce_sgd(peer_grads, peer_params, peer_pads, mc_grads, mc_params, state, rank, world,
+                                          h->p_total, lr, grad_scale, st, 0, 0, 0, red ? h->ptr<float>("scratch") : nullptr,
+                                          red ? conv1_wgrad_tc_partials(c.batch) : 0, red ? 4864 : 0));
+  return B200_OK;
 }
 
 int b200_sgd_apply(b200_handle h, float lr, float grad_scale, void* stream) {
@@ -815,7 +838,7 @@ int b200_debug_conv_variant(int32_t variant) {
 int b200_debug_trace(uint64_t* device_buf) {
 #ifdef B200_TRACE
   unsigned long long* p = reinterpret_cast<unsigned long long*>(device_buf);
-  trace_set_fc_tail(p); trace_set_tc_conv(p); trace_set_tc_conv1(p); trace_set_tc_gemm(p); trace_set_f32(p);
+  trace_set_fc_tail(p); trace_set_tc_conv(p); trace_set_tc_conv1(p); trace_set_tc_gemm(p); trace_set_f32(p); trace_set_p2p(p);
   B200_LAUNCH_CHECK();
   return B200_OK;
 #else

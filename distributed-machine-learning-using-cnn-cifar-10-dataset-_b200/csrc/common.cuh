@@ -44,6 +44,30 @@ static inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 #endif
+#ifdef __CUDACC__
+// one warp: sum over z < S of part[z * stride + i .. i+3], lane l taking z = l, l + 32, ... (all of its loads in flight at
+// once) and a five-step shuffle tree -- THE summation order of conv1's gradient partials, shared by the update kernels
+// (sgd_reduce_kernel, p2p_allreduce_sgd_kernel) and the stand-alone reduction, so that every route gives the same bits
+__device__ __forceinline__ float4 warp_sum_partials(const float* __restrict__ part, int S, int stride, int i, int lane) {
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int z0 = lane; z0 < S; z0 += 128) {
+    float4 v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int z = z0 + 32 * j;
+      v[j] = z < S ? __ldg(reinterpret_cast<const float4*>(part + (int64_t)z * stride + i)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { s.x += v[j].x; s.y += v[j].y; s.z += v[j].z; s.w += v[j].w; }
+  }
+#pragma unroll
+  for (int m = 1; m <= 16; m <<= 1) {
+    s.x += __shfl_xor_sync(0xffffffffu, s.x, m); s.y += __shfl_xor_sync(0xffffffffu, s.y, m);
+    s.z += __shfl_xor_sync(0xffffffffu, s.z, m); s.w += __shfl_xor_sync(0xffffffffu, s.w, m);
+  }
+  return s;
+}
+#endif
 // Small kernels that share the machine with the tensor-core kernels (side streams) ask for the maximum shared-memory
 // carve-out even though they need little: an SM whose L1/shared split was set for a small-footprint kernel cannot
 // take a 100-200 KB CTA until it has drained, which delayed FC1's dW behind the tail-gradient kernel by 3 us.
@@ -88,7 +112,7 @@ inline cudaError_t launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block
 // Every instrumented kernel stamps %globaltimer when its first CTA starts and when its last CTA ends into
 // buf[2*id], buf[2*id+1]; b200_debug_trace() hands the buffer to every translation unit.  Compiled out otherwise.
 enum TraceId { TR_PACK = 0, TR_W2IMG, TR_CONV1_FWD, TR_CONV2_FWD, TR_FC1_FWD, TR_TAIL_ROWS, TR_TAIL_GRADS, TR_FC1_DW,
-               TR_FC1_DX, TR_CONV2_DGRAD, TR_CONV2_WGRAD, TR_CONV2_REDUCE, TR_CONV1_WGRAD, TR_SGD, TR_COUNT };
+               TR_FC1_DX, TR_CONV2_DGRAD, TR_CONV2_WGRAD, TR_CONV2_REDUCE, TR_CONV1_WGRAD, TR_SGD, TR_P2P_FC, TR_P2P_CONV, TR_COUNT };
 #ifdef B200_TRACE
 static __device__ unsigned long long* b200_trace_buf;
 struct TraceScope {

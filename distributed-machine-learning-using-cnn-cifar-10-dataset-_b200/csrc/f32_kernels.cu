@@ -528,27 +528,6 @@ __global__ void sgd_kernel(float* __restrict__ p, const float* __restrict__ g, i
 // (all of its loads in flight at once: one round trip to L2), then a five-step shuffle tree -- store the finished
 // gradient (the buffer is complete after the step) and apply it; the other CTAs update the rest.  Saves the launch
 // of a reduction kernel at the very end of the step's critical path.
-// one warp: sum over z < S of part[z * stride + i .. i+3], lane l taking z = l, l + 32, ... and a five-step shuffle
-// tree -- THE summation order of conv1's gradient partials, shared by the update kernel and the stand-alone reduction
-__device__ __forceinline__ float4 warp_sum_partials(const float* __restrict__ part, int S, int stride, int i, int lane) {
-  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-  for (int z0 = lane; z0 < S; z0 += 128) {
-    float4 v[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int z = z0 + 32 * j;
-      v[j] = z < S ? __ldg(reinterpret_cast<const float4*>(part + (int64_t)z * stride + i)) : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-#pragma unroll
-    for (int j = 0; j < 4; ++j) { s.x += v[j].x; s.y += v[j].y; s.z += v[j].z; s.w += v[j].w; }
-  }
-#pragma unroll
-  for (int m = 1; m <= 16; m <<= 1) {
-    s.x += __shfl_xor_sync(0xffffffffu, s.x, m); s.y += __shfl_xor_sync(0xffffffffu, s.y, m);
-    s.z += __shfl_xor_sync(0xffffffffu, s.z, m); s.w += __shfl_xor_sync(0xffffffffu, s.w, m);
-  }
-  return s;
-}
 __global__ void reduce_partials_warp_kernel(const float* __restrict__ part, float* __restrict__ out, int n, int S, int stride) {
   pdl_wait();
   const int t = blockIdx.x * blockDim.x + threadIdx.x;

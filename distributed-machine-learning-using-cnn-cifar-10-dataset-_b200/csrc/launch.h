@@ -104,7 +104,8 @@ void trace_set_fc_tail(unsigned long long*);
 void trace_set_tc_conv(unsigned long long*);
 void trace_set_tc_conv1(unsigned long long*);
 void trace_set_tc_gemm(unsigned long long*);
-void trace_set_f32(unsigned long long*);   // diagnostics (see conv5x5_set_timeline)
+void trace_set_f32(unsigned long long*);
+void trace_set_p2p(unsigned long long*);   // diagnostics (see conv5x5_set_timeline)
 int64_t fc_tail_scratch_bytes(int B, int F1, int F2, int NC);
 int fc_tail(const float* fc1_part, int n_part, const float* b1, float* full1, const float* w2, const float* b2,
             const float* w3, const float* b3, const int32_t* labels, float* full2, float* logits, float* dlogits,
@@ -118,7 +119,10 @@ int fc_tail_prepare_w2(const float* w2, void* scratch, int B, int F1, int F2, in
 int p2p_allreduce_sgd(const void* const* peer_grads, void* const* peer_params, void* const* peer_pads,
                       const void* mc_grads, void* mc_params, uint32_t* state, int rank, int world, int64_t total,
                       float lr, float scale, cudaStream_t st,
-                      int64_t offset = 0, int channel = 0, int max_ctas = 0);
+                      int64_t offset = 0, int channel = 0, int max_ctas = 0,
+                      // (optional) the first red_n floats of this rank's range still sit in red_S partials [red_S][red_n]:
+                      // summed (fixed order) by the kernel's first CTAs before it tells the peers "ready"
+                      const float* red_part = nullptr, int red_S = 0, int red_n = 0);
 bool conv1_tc_supported(int H, int W, int c_in, int c1);
 int conv1_pool_fwd_tc(const uint8_t* img, const float* w, const float* bias, float* pool, uint8_t* arg,
                       float* conv_dbg, int B, int ih, int iw, int H, int W, cudaStream_t st,

@@ -31,11 +31,15 @@ struct P2PArgs {
   uint32_t* pads[kMaxRanks];        // every rank's flag pad (of this channel): [0,8) "ready" slots, [8,16) "done" slots
   const float* mc_grads;            // multicast mapping of the gradient buffers, or null
   float* mc_params;                 // multicast mapping of the parameter buffers, or null
-  uint32_t* state;                  // local: [0] epoch, [1] CTA arrival counter
+  uint32_t* state;                  // local: [0] epoch, [1] CTA arrival counter, [2] CTAs done with the local reduction
+  // optional local reduction in front of the exchange: out[i] = sum over z < red_S of red_part[z][i] for the first red_n
+  // floats of this rank's gradient range (conv1's per-CTA partials), done by the first red_ctas CTAs
+  const float* red_part; float* red_out; int red_S, red_n, red_ctas;
   int rank, world;
   int64_t total;                    // floats, divisible by 4 * world
   float step;                       // lr * scale
   long long timeout_cycles;         // bound of one flag wait (see flag_timeout_cycles)
+  int trace_id;                     // diagnostics build: TR_P2P_FC / TR_P2P_CONV
 };
 
 __device__ __forceinline__ void st_flag(uint32_t* p, uint32_t v) {
@@ -74,8 +78,29 @@ __device__ __forceinline__ void mc_st(float* p, const float4& v) {
 }
 
 __global__ void __launch_bounds__(512) p2p_allreduce_sgd_kernel(P2PArgs a) {
+  B200_TRACE_SCOPE(a.trace_id);
   const int tid = threadIdx.x;
   const uint32_t epoch = a.state[0] + 1;          // read by everyone before the last CTA bumps it at the very end
+  // ---- 0: finish this rank's own gradients (fixed-order sum of conv1's partials): saves a kernel launch at the very
+  //         end of the step.  CTA 0 publishes "ready" only once every reducing CTA has stored its share.
+  if (a.red_ctas > 0) {
+    if ((int)blockIdx.x < a.red_ctas) {
+      const int t = blockIdx.x * blockDim.x + tid;
+      const int i = min(t >> 5, a.red_n / 4 - 1) * 4;
+      const float4 s = warp_sum_partials(a.red_part, a.red_S, a.red_n, i, t & 31);
+      if ((t & 31) == 0 && (t >> 5) < a.red_n / 4) *reinterpret_cast<float4*>(a.red_out + i) = s;
+      __syncthreads();
+      if (tid == 0) { __threadfence(); atomicAdd(a.state + 2, 1u); }
+    }
+    if (blockIdx.x == 0) {
+      if (tid == 0) {
+        const long long t0 = clock64();
+        while (atomicAdd(a.state + 2, 0u) < (uint32_t)a.red_ctas)
+          if (clock64() - t0 > a.timeout_cycles) { printf("b200cnn: local reduction wait timed out\n"); __trap(); }
+      }
+      __syncthreads();
+    }
+  }
   // ---- A: gradients of all ranks complete ------------------------------------------------------------
   if (blockIdx.x == 0 && tid < a.world) {
     __threadfence_system();
@@ -151,7 +176,7 @@ __global__ void __launch_bounds__(512) p2p_allreduce_sgd_kernel(P2PArgs a) {
       wait_flag(a.pads[a.rank] + 8 + tid, epoch, a.timeout_cycles);
     }
     __syncthreads();
-    if (tid == 0) { a.state[1] = 0; a.state[0] = epoch; }
+    if (tid == 0) { a.state[1] = 0; a.state[2] = 0; a.state[0] = epoch; }
   }
 }
 long long flag_timeout_cycles() {
@@ -167,10 +192,12 @@ long long flag_timeout_cycles() {
   return cycles;
 }
 }  // namespace
+B200_TRACE_SETTER(trace_set_p2p)
 
 int p2p_allreduce_sgd(const void* const* peer_grads, void* const* peer_params, void* const* peer_pads,
                       const void* mc_grads, void* mc_params, uint32_t* state, int rank, int world, int64_t total,
-                      float lr, float scale, cudaStream_t st, int64_t offset, int channel, int max_ctas) {
+                      float lr, float scale, cudaStream_t st, int64_t offset, int channel, int max_ctas,
+                      const float* red_part, int red_S, int red_n) {
   B200_REQUIRE(world >= 1 && world <= kMaxRanks && rank >= 0 && rank < world, "p2p_allreduce_sgd: bad rank %d / world %d",
                rank, world);
   B200_REQUIRE(total > 0 && total % (4 * world) == 0, "p2p_allreduce_sgd: %lld floats do not split into %d 16-byte shards",
@@ -186,12 +213,21 @@ int p2p_allreduce_sgd(const void* const* peer_grads, void* const* peer_params, v
   B200_REQUIRE(offset >= 0 && offset % 4 == 0 && channel >= 0 && channel < 2, "p2p_allreduce_sgd: bad sub-range / channel");
   a.mc_grads = mc_grads ? (const float*)mc_grads + offset : nullptr;
   a.mc_params = mc_params ? (float*)mc_params + offset : nullptr;
-  a.state = state + 2 * channel; a.rank = rank; a.world = world; a.total = total; a.step = lr * scale;
+  a.state = state + 4 * channel; a.rank = rank; a.world = world; a.total = total; a.step = lr * scale;
   a.timeout_cycles = flag_timeout_cycles();
+  a.trace_id = channel == 0 ? TR_P2P_FC : TR_P2P_CONV;
   const int64_t shard4 = total / 4 / world;
   // (with the multicast mapping a thread handles four 16-byte pieces per sweep)
   const int64_t per_cta = 512 * ((mc_grads && mc_params) ? 4 : 1);
-  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(max_ctas > 0 ? max_ctas : kNumSMs, (shard4 + per_cta - 1) / per_cta));
+  int grid = (int)std::max<int64_t>(1, std::min<int64_t>(max_ctas > 0 ? max_ctas : kNumSMs, (shard4 + per_cta - 1) / per_cta));
+  if (red_part) {      // the first red_n floats of this range still sit in red_S partials: one warp per 16 bytes sums them
+    B200_REQUIRE(red_S > 0 && red_n > 0 && red_n % 4 == 0 && red_n <= total && ((uintptr_t)red_part & 15) == 0,
+                 "p2p_allreduce_sgd: bad partial range");
+    a.red_part = red_part; a.red_out = const_cast<float*>(a.grads[rank]); a.red_S = red_S; a.red_n = red_n;
+    a.red_ctas = (red_n / 4 * 32 + 511) / 512;
+    B200_REQUIRE(a.red_ctas <= kNumSMs, "p2p_allreduce_sgd: partial range too large to reduce in front of the exchange");
+    grid = std::max(grid, a.red_ctas);       // all of them resident at once (<= one CTA per SM): CTA 0 may wait for them
+  }
   p2p_allreduce_sgd_kernel<<<grid, 512, 0, st>>>(a);
   B200_LAUNCH_CHECK();
   return B200_OK;

@@ -99,7 +99,7 @@ class P2PExchange(GradientExchange):
         self.multicast = bool(mc_ok and self._hg.multicast_ptr and self._hp.multicast_ptr)
         self._mc_grads = int(self._hg.multicast_ptr) if self.multicast else None
         self._mc_params = int(self._hp.multicast_ptr) if self.multicast else None
-        self._state = torch.zeros(4, dtype=torch.int32, device=device)      # (epoch, arrivals) per flag channel
+        self._state = torch.zeros(8, dtype=torch.int32, device=device)      # (epoch, arrivals, reducers done, -) per flag channel
         # Overlapping the exchange with the backward pass costs a second pair of flag barriers.  Measured (whole step,
         # batch 128/GPU, hot): 2 GPUs 131 us overlapped vs 146 us as one kernel at the end; 8 GPUs 150 vs 147 (the
         # 8-way barriers are most of the kernel there) -- so it is used up to four workers unless `overlap` is set.
@@ -119,10 +119,8 @@ class P2PExchange(GradientExchange):
         kernels (b200_train_step_p2p); same result as engine.forward_backward(...) followed by apply_(engine, lr)."""
         from ._lib import check
         engine._check_inputs(images, labels)
-        if not self.overlap:
-            engine.forward_backward(images, labels)
-            return self.apply_(engine, lr)
-        check(engine.lib.b200_train_step_p2p(engine.h, images.data_ptr(), labels.data_ptr(), self._peer_grads,
+        fn = engine.lib.b200_train_step_p2p if self.overlap else engine.lib.b200_train_step_p2p_single
+        check(fn(engine.h, images.data_ptr(), labels.data_ptr(), self._peer_grads,
                                              self._peer_params, self._peer_pads, self._mc_grads, self._mc_params,
                                              self._state.data_ptr(), self.rank, self.world, lr, self.grad_scale,
                                              torch.cuda.current_stream().cuda_stream))

@@ -97,7 +97,7 @@ int b200_sgd_apply(b200_handle h, float lr, float grad_scale, void* stream);
  * (entry i = worker i; entry `rank` = the buffers bound to this handle); all must be peer-mapped symmetric
  * allocations of the padded parameter size (pads: >= 64 B of zero-initialised uint32 flags per worker).
  * mc_grads / mc_params: NVSwitch multicast mappings of the same buffers, or NULL (then plain peer loads /
- * stores).  state: 8 zero-initialised bytes of local device memory.  Every worker must launch it once per
+ * stores).  state: 16 zero-initialised bytes of local device memory.  Every worker must launch it once per
  * step; the kernels wait for one another, so all `world` GPUs must be running.  The wait is bounded: a worker
  * that has not arrived after B200_P2P_TIMEOUT_S seconds (environment variable, read once; default 120) makes every
  * waiting kernel trap, which leaves a sticky error on those CUDA contexts -- set it above the longest pause a
@@ -109,10 +109,16 @@ int b200_p2p_sgd_apply(b200_handle h, const void* const* peer_grads, void* const
  * b200_p2p_sgd_apply split in two and overlapped -- the FC gradients (full_weight_1 onward, 90 % of the buffer) are
  * all-reduced and applied on an internal stream as soon as they exist, beside the conv layers' backward kernels;
  * the conv gradients follow at the end.  Same arguments and result as b200_forward_backward followed by
- * b200_p2p_sgd_apply, except: state = 16 zero-initialised bytes, pads >= 128 B per worker.  bf16 mode only. */
+ * b200_p2p_sgd_apply, except: state = 32 zero-initialised bytes, pads >= 128 B per worker.  bf16 mode only. */
 int b200_train_step_p2p(b200_handle h, const uint8_t* images, const int32_t* labels, const void* const* peer_grads,
                         void* const* peer_params, void* const* peer_pads, const void* mc_grads, void* mc_params,
                         uint32_t* state, int32_t rank, int32_t world, float lr, float grad_scale, void* stream);
+/* The same step with the exchange as ONE kernel at the end (b200_forward_backward + b200_p2p_sgd_apply in one call;
+ * state = 16 zero-initialised bytes, pads >= 64 B): what eight workers use, where a second pair of flag barriers costs
+ * more than overlapping the FC gradients saves.  conv1's gradient partials are summed inside the exchange kernel. */
+int b200_train_step_p2p_single(b200_handle h, const uint8_t* images, const int32_t* labels, const void* const* peer_grads,
+                               void* const* peer_params, void* const* peer_pads, const void* mc_grads, void* mc_params,
+                               uint32_t* state, int32_t rank, int32_t world, float lr, float grad_scale, void* stream);
 /* forward + backward + sgd_apply: one `mon_sess.run([train_op, loss])` (:230) for world == 1. */
 int b200_train_step(b200_handle h, const uint8_t* images, const int32_t* labels, float lr, void* stream);
 /* The same call with HOST (pinned) inputs and a host loss: copies the records and labels to

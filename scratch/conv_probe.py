@@ -28,7 +28,7 @@ for name, (tid, fn) in kernels.items():
         lib.b200_debug_conv_variant(variant)
         ms = []
         for it in range(4):
-            buf[0:28:2] = torch.iinfo(torch.int64).max; buf[1:28:2] = 0; buf[28] = tid; buf[29] = -1; buf[64:] = 0
+            buf[0:32:2] = torch.iinfo(torch.int64).max; buf[1:32:2] = 0; buf[32] = tid; buf[33] = -1; buf[64:] = 0
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             torch.cuda.synchronize(); e0.record(); rc = fn(); e1.record(); torch.cuda.synchronize()
             assert rc == 0, lib.b200_last_error()

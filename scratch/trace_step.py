@@ -7,7 +7,7 @@ from b200cnn import _lib
 lib = _lib.load()
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 128
 names = ["pack", "w2img", "conv1_fwd", "conv2_fwd", "fc1_fwd", "tail_rows", "tail_grads", "fc1_dw", "fc1_dx",
-         "conv2_dgrad", "conv2_wgrad", "wgrad_reduce", "conv1_wgrad", "sgd"]
+         "conv2_dgrad", "conv2_wgrad", "wgrad_reduce", "conv1_wgrad", "sgd", "p2p_fc", "p2p_conv"]
 e = b200cnn.TrainStepEngine(batch=B, mode="bf16"); e.init_params(0)
 rng = np.random.default_rng(0)
 img = torch.as_tensor(rng.integers(0, 256, (B, 3, 32, 32), dtype=np.uint8)).cuda()
@@ -17,7 +17,7 @@ sel2 = int(sys.argv[3]) if len(sys.argv) > 3 else -1
 sel = int(sys.argv[2]) if len(sys.argv) > 2 else -1      # kernel whose CTAs log individually
 _lib.check(lib.b200_debug_trace(buf.data_ptr()))
 def reset():
-    buf[0:28:2] = torch.iinfo(torch.int64).max; buf[1:28:2] = 0; buf[28] = sel; buf[29] = sel2; buf[64:] = 0      # stamps are < 2^63: signed view orders the same
+    buf[0:32:2] = torch.iinfo(torch.int64).max; buf[1:32:2] = 0; buf[32] = sel; buf[33] = sel2; buf[64:] = 0      # stamps are < 2^63: signed view orders the same
 tl = torch.zeros(32, dtype=torch.int64, device='cuda')
 lib.b200_debug_conv_timeline(C.cast(tl.data_ptr(), C.POINTER(C.c_int64)))
 e.train_step(img, lab, 0.1); torch.cuda.synchronize()
@@ -28,10 +28,12 @@ for cold in (0, 1):
         if cold: flush.zero_()
         reset(); torch.cuda.synchronize(); g.replay(); torch.cuda.synchronize()
     raw = buf.cpu().numpy()
-    t = raw[:28].reshape(-1, 2).astype(np.float64)
-    t0 = t[:, 0].min()
+    t = raw[:32].reshape(-1, 2).astype(np.float64)
+    t = t[t[:, 1] > 0] if False else t
+    t0 = t[t[:, 1] > 0, 0].min()
     print("cold" if cold else "hot", "step: %.1f us from first start to last end" % ((t[:, 1].max() - t0) / 1e3))
     for i in np.argsort(t[:, 0]):
+        if t[i, 1] <= 0: continue
         print("  %-13s start %7.1f  end %7.1f  (%5.1f us)" % (names[i], (t[i, 0] - t0) / 1e3, (t[i, 1] - t0) / 1e3, (t[i, 1] - t[i, 0]) / 1e3))
 # phase stamps (clock64) of CTA 0 of the LAST conv5x5 kernel that ran (the dgrad of the step) and of the tail rows kernel
 g.replay(); torch.cuda.synchronize()

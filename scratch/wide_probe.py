@@ -14,7 +14,7 @@ lib.b200_debug_conv_timeline(C.cast(tl.data_ptr(), C.POINTER(C.c_int64)))
 buf = torch.zeros(64 + 2 * 3 * 512, dtype=torch.int64, device='cuda')
 trace = lib.b200_debug_trace(buf.data_ptr()) == 0
 def reset(sel):
-    buf[0:28:2] = torch.iinfo(torch.int64).max; buf[1:28:2] = 0; buf[28] = sel; buf[29] = -1; buf[64:] = 0
+    buf[0:32:2] = torch.iinfo(torch.int64).max; buf[1:32:2] = 0; buf[32] = sel; buf[33] = -1; buf[64:] = 0
 def ctas(name):
     raw = buf.cpu().numpy()
     c = raw[64:64 + 1536].reshape(-1, 3); c = c[c[:, 0] > 0]

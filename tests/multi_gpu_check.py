@@ -85,6 +85,17 @@ def main():
     torch.cuda.synchronize(); dist.barrier()
     same4 = ex.replicas_identical(eng.params)
 
+    # (5) the same step with the exchange as one kernel at the end and conv1's partial sums folded into it
+    #     (b200_train_step_p2p_single): bit-identical to (2), replicas identical
+    eng.load_params(params0)
+    torch.cuda.synchronize(); dist.barrier()
+    ex.overlap = False
+    ex.train_step_(eng, imgd, labd, lr)
+    torch.cuda.synchronize(); dist.barrier()
+    diff_single = float((eng.params - p_p2p).abs().max())
+    same6 = ex.replicas_identical(eng.params)
+    ex.overlap = True
+
     # timing inside graphs
     def timed(fn, n=200):
         g = eng.capture(fn)
@@ -114,15 +125,22 @@ def main():
     eng.load_params(params0)
     t_step_ovl = timed(lambda: ex.train_step_(eng, imgd, labd, lr), 100)
     same5 = ex.replicas_identical(eng.params)
+    eng.load_params(params0)
+    ex.overlap = False
+    t_step_single = timed(lambda: ex.train_step_(eng, imgd, labd, lr), 100)
+    same5 = same5 and ex.replicas_identical(eng.params)
+    ex.overlap = True
     if rank == 0:
         print(f"world={world} multicast={ex.multicast} |p2p - nccl|max = {diff:.3e} (scale {scale:.3f}), "
               f"vs oracle sum-update rel {err_oracle:.2e}, replicas identical: {same_replicas} / {same2}")
         print(f"exchange+update only: nccl allreduce + sgd kernel {t_nccl:.1f} us, fused p2p kernel {t_p2p:.1f} us")
         print(f"whole step (batch {B}/GPU): nccl path {t_step_nccl:.1f} us, fused p2p path {t_step_p2p:.1f} us, "
-              f"overlapped p2p path {t_step_ovl:.1f} us -> {B * world / t_step_ovl * 1e6:.0f} img/s")
-        print(f"overlapped exchange: |overlapped - fused|max = {diff_ovl:.3e}, replicas identical: {same3} / {same4} / {same5}")
+              f"overlapped p2p path {t_step_ovl:.1f} us -> {B * world / t_step_ovl * 1e6:.0f} img/s, "
+              f"single-kernel path with folded reduction {t_step_single:.1f} us")
+        print(f"overlapped exchange: |overlapped - fused|max = {diff_ovl:.3e}, single-kernel step: {diff_single:.3e}, "
+              f"replicas identical: {same3} / {same4} / {same5} / {same6}")
     ok = diff <= 1e-6 * scale and err_oracle <= 1e-6 and same_replicas and same2 and \
-        diff_ovl <= 1e-5 * scale and same3 and same4 and same5
+        diff_ovl <= 1e-5 * scale and same3 and same4 and same5 and diff_single <= 1e-5 * scale and same6
     torch.cuda.synchronize(); dist.barrier()
     sys.stdout.flush()
     os._exit(0 if ok else 1)
