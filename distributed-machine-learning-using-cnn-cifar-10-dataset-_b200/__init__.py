@@ -7,7 +7,7 @@ from .engine import PARAM_NAMES, PARAM_SCOPES, TrainStepEngine  # noqa: F401
 
 # (mode, tolerance) pairs exercised by __graft_entry__.smoke(); tolerance is max-abs-normalised
 # relative error against the fp64 oracle after one SGD step.
-SMOKE_MODES = (("fp32", 2e-5), ("bf16", 5e-2))
+SMOKE_MODES = (("fp32", 2e-5), ("bf16", 2e-2))
 from .exchange import GradientExchange, P2PExchange  # noqa: E402,F401
 # mode bench.py and the CLI use unless told otherwise
 DEFAULT_MODE = "bf16"

@@ -101,9 +101,12 @@ class P2PExchange(GradientExchange):
         self._mc_params = int(self._hp.multicast_ptr) if self.multicast else None
         self._state = torch.zeros(8, dtype=torch.int32, device=device)      # (epoch, arrivals, reducers done, -) per flag channel
         # Overlapping the exchange with the backward pass costs a second pair of flag barriers.  Measured (whole step,
-        # batch 128/GPU, hot): 2 GPUs 131 us overlapped vs 146 us as one kernel at the end; 8 GPUs 150 vs 147 (the
-        # 8-way barriers are most of the kernel there) -- so it is used up to four workers unless `overlap` is set.
-        self.overlap = self.world <= 4 if overlap is None else bool(overlap)
+        # batch 128/GPU, L2 flushed): 2 GPUs 140 us; 4 GPUs 142 us overlapped vs 148 us as one kernel at the end; 8 GPUs
+        # 144 vs 150 -- so it is the default at every world size (round 1 had it off at eight workers, where the
+        # reduction launch in front of the second channel ate the gain; that reduction now runs inside the kernel).
+        import os
+        env = os.environ.get("B200CNN_OVERLAP")          # experiments: force the overlapped (1) / single-kernel (0) exchange
+        self.overlap = (True if env is None else env == "1") if overlap is None else bool(overlap)
         torch.cuda.synchronize(device)
         dist.barrier(group=group)
 

@@ -231,13 +231,13 @@ def test_full_step_large_batch(mode, B, kind):
     e.backward()
     torch.cuda.synchronize()
     fwd_tol = LOOSE if mode == "bf16" else RTOL_F32
-    grad_tol = 2e-2 if mode == "bf16" else 2 * RTOL_F32
+    grad_tol = 8e-3 if mode == "bf16" else 2 * RTOL_F32      # bf16: measured <= 3.7e-3 (profiles/r2_bf16_errors.json)
     names = ("pool1", "pool2", "full1", "full2", "logits")
     for name in names:
         got = e.tensor(name).cpu().numpy().reshape(B, -1)
         want = np.concatenate([a[name].reshape(a["x"].shape[0], -1) for a in acts])
         assert relerr(got, want) <= fwd_tol, name
-    assert abs(float(e.loss()) - loss) <= (2e-2 if mode == "bf16" else RTOL_F32) * abs(loss)
+    assert abs(float(e.loss()) - loss) <= (5e-3 if mode == "bf16" else RTOL_F32) * abs(loss)
     logits = np.concatenate([a["logits"] for a in acts])
     pred = np.concatenate([a["pred"] for a in acts])
     srt = np.sort(logits, axis=1)

@@ -169,10 +169,11 @@ def test_conv_tensorcore_rectangular_and_asymmetric_channels(lib):
 @pytest.mark.parametrize("kind", ["u8", "soft"])
 def test_full_step_bf16_mode_b128(kind):
     """BASELINE.json config 3 numerics: the whole step in bf16 mode (tensor-core conv2 / FC1 / FC2,
-    fp32 everywhere else, fp32 master weights) against the fp64 oracle.  Stated bounds: forward
-    tensors and loss within 1e-2 of max-abs; gradients within 2e-2 of the oracle's backward
-    evaluated on the GPU's own forward tensors (see test_gpu_parity for why); argmax bit-exact
-    wherever the oracle's top-2 logit gap exceeds the forward bound."""
+    fp32 everywhere else, fp32 master weights) against the fp64 oracle.  Bounds set from the measured errors
+    (profiles/r2_bf16_errors.json: forward <= 6.8e-3, loss <= 2.1e-3, gradients <= 3.7e-3 of max-abs at batch 128 and
+    1024, raw-byte and well-conditioned inputs): forward tensors within 1e-2; loss within 5e-3; gradients within 8e-3
+    of the oracle's backward evaluated on the GPU's own forward tensors (see test_gpu_parity for why); argmax
+    bit-exact wherever the oracle's top-2 logit gap exceeds the forward bound."""
     import b200cnn
     from test_gpu_parity import _oracle_backward_on_gpu_forward
     rng = np.random.default_rng(41)
@@ -191,7 +192,7 @@ def test_full_step_bf16_mode_b128(kind):
     torch.cuda.synchronize()
     for name in ("pool1", "pool2", "full1", "full2", "logits"):
         assert relerr(e.tensor(name).cpu().numpy().reshape(a[name].shape), a[name]) <= LOOSE, name
-    assert abs(float(e.loss()) - loss) <= 2e-2 * abs(loss)
+    assert abs(float(e.loss()) - loss) <= 5e-3 * abs(loss)
     srt = np.sort(a["logits"], axis=1)
     safe = (srt[:, -1] - srt[:, -2]) > 2 * LOOSE * np.abs(a["logits"]).max()
     np.testing.assert_array_equal(e.pred().cpu().numpy()[safe], a["pred"][safe])
@@ -199,7 +200,30 @@ def test_full_step_bf16_mode_b128(kind):
     g2, a2 = _oracle_backward_on_gpu_forward(e, params, lab, a, fused_conv1=True)
     got = e.get_grads()
     for k in rn.PARAM_NAMES:
-        assert relerr(got[k], g2[k]) <= 2e-2, (k, relerr(got[k], g2[k]))
+        assert relerr(got[k], g2[k]) <= 8e-3, (k, relerr(got[k], g2[k]))
+
+
+def test_two_bf16_steps_follow_the_oracle_trajectory():
+    """Two consecutive SGD steps in bf16 mode on well-conditioned inputs (lr 0.01) stay on the fp64 oracle's
+    trajectory: loss within 5e-3 at both steps, parameters within 5e-3 of max-abs after the second (an update is
+    lr * gradient, small against the weights, so the parameter bound is dominated by pool near-ties moving ~1 % of a
+    conv gradient, as in the fp32 trajectory test)."""
+    rng = np.random.default_rng(14)
+    B = 64
+    params = rn.init_params(0)
+    e = b200cnn.TrainStepEngine(batch=B, mode="bf16")
+    e.load_params(params)
+    p64 = {k: v.astype(np.float64) for k, v in params.items()}
+    for _ in range(2):
+        img = np.clip(np.rint(rng.normal(8.0, 2.5, (B, 3, 32, 32))), 0, 255).astype(np.uint8)
+        lab = rng.integers(0, 10, (B,)).astype(np.int32)
+        p64, loss, _, _ = rn.train_step(p64, img, lab, lr=0.01)
+        e.train_step(dev(img), dev(lab), 0.01)
+        torch.cuda.synchronize()
+        assert abs(float(e.loss()) - loss) <= 5e-3 * abs(loss)
+    got = e.get_params()
+    for k in rn.PARAM_NAMES:
+        assert relerr(got[k], p64[k]) <= 5e-3, (k, relerr(got[k], p64[k]))
 
 
 @pytest.mark.parametrize("B,crop", [(3, 24), (128, 24), (2, 16)])

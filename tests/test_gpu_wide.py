@@ -133,19 +133,19 @@ def test_full_step_wide_model_bf16(kind, B):
     torch.cuda.synchronize()
     for name in ("pool1", "conv2", "pool2", "full1", "full2", "logits"):      # (conv1 is fused with pool1: never in HBM)
         assert relerr(e.tensor(name).cpu().numpy().reshape(a[name].shape), a[name]) <= LOOSE, name
-    assert abs(float(e.loss()) - loss) <= 2e-2 * abs(loss)
+    assert abs(float(e.loss()) - loss) <= 5e-3 * abs(loss)      # measured 7.6e-4 (profiles/r2_bf16_errors.json)
     srt = np.sort(a["logits"], axis=1)
     safe = (srt[:, -1] - srt[:, -2]) > 2 * LOOSE * np.abs(a["logits"]).max()
     np.testing.assert_array_equal(e.pred().cpu().numpy()[safe], a["pred"][safe])
     g2, _ = _oracle_backward_on_gpu_forward(e, params, lab, a, fused_conv1=True)
     got = e.get_grads()
     for k in rn.PARAM_NAMES:
-        assert relerr(got[k], g2[k]) <= 2e-2, (k, relerr(got[k], g2[k]))
+        assert relerr(got[k], g2[k]) <= 8e-3, (k, relerr(got[k], g2[k]))      # measured <= 3.0e-3
     e.sgd_apply(0.1)
     torch.cuda.synchronize()
     newp = e.get_params()
     for k in rn.PARAM_NAMES:
-        assert relerr(newp[k], np.asarray(params[k], np.float64) - 0.1 * g2[k]) <= 2e-2, k
+        assert relerr(newp[k], np.asarray(params[k], np.float64) - 0.1 * g2[k]) <= 8e-3, k
     # the step as one call, captured: same numbers
     e2 = b200cnn.TrainStepEngine(batch=B, mode="bf16", **WIDE)
     e2.load_params(params)
