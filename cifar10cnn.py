@@ -42,6 +42,9 @@ _EXTRA_FLAGS = (
     ("--reduce", str, "sum", "sum (N worker updates per round, the reference's semantics) or mean"),
     ("--max_steps", int, GENERATIONS, "stop when global_step reaches this (reference: 20000)"),
     ("--backend", str, "nccl", "torch.distributed backend for the worker group"),
+    ("--staleness", int, 0, "asynchronous-ps fidelity: apply every gradient this many exchange rounds after the "
+                            "snapshot it was computed on (-1: workers - 1, the expected staleness of the reference's "
+                            "lock-free updates with that many workers); 0 = synchronous (default)"),
 )
 
 
@@ -115,8 +118,10 @@ def run_worker(flags, ps_hosts, worker_hosts):
 
     import json
     import time
+    staleness = len(worker_hosts) - 1 if flags.staleness < 0 else flags.staleness
     with session.MonitoredTrainingSession(is_chief=(flags.task_index == 0), last_step=flags.max_steps,
-                                          reduce=flags.reduce, checkpoint_dir=flags.log_dir) as mon_sess:
+                                          reduce=flags.reduce, checkpoint_dir=flags.log_dir,
+                                          staleness=staleness) as mon_sess:
         i = 0
         print('Starting Training')
         t_start, i_start = None, 0

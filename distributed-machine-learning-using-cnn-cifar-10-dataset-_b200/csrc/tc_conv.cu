@@ -402,50 +402,6 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
         }
       }
     }
-    if (a.pool_out && n_img0 < g.B) {
-      // ---- 3x3/2 SAME max-pool (pad 0 before / rest after), first max in (h,w) scan order (:123) ------
-      loaders_sync();
-      const float* tile = reinterpret_cast<const float*>(strip);
-      const int OH = (g.H + 1) / 2, OW = (g.W + 1) / 2;
-      const int pbh = max((OH - 1) * 2 + 3 - g.H, 0) / 2, pbw = max((OW - 1) * 2 + 3 - g.W, 0) / 2;
-      // one item = 8 channels of one pooled cell; window positions outside the image read a clamped address and enter
-      // the scan as -FLT_MAX (no branch); strict '>' in (kh, kw) order = first maximum
-      for (int q = tid; q < OH * OW * 8; q += LOADERS) {
-        const int c8 = q & 7, cell = q >> 3;
-        const int oh = cell / OW, ow = cell - oh * OW;
-        float best[8];
-        int bi[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) { best[e] = -3.402823466e38f; bi[e] = 0; }
-#pragma unroll
-        for (int kh = 0; kh < 3; ++kh) {
-          const int hh = 2 * oh + kh - pbh;
-          const bool vh = (unsigned)hh < (unsigned)g.H;
-#pragma unroll
-          for (int kw = 0; kw < 3; ++kw) {
-            const int ww = 2 * ow + kw - pbw;
-            const bool ok = vh && (unsigned)ww < (unsigned)g.W;
-            const float* src = tile + (size_t)(ok ? hh * g.W + ww : 0) * 68 + c8 * 8;
-            const float4 v0 = *reinterpret_cast<const float4*>(src), v1 = *reinterpret_cast<const float4*>(src + 4);
-            const float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
-#pragma unroll
-            for (int e = 0; e < 8; ++e) {
-              const float x = ok ? vv[e] : -3.402823466e38f;
-              const bool gt = x > best[e];
-              best[e] = gt ? x : best[e];
-              bi[e] = gt ? kh * 3 + kw : bi[e];
-            }
-          }
-        }
-        const size_t o = ((size_t)n_img0 * OH * OW + cell) * 64 + c8 * 8;
-        *reinterpret_cast<float4*>(a.pool_out + o) = make_float4(best[0], best[1], best[2], best[3]);
-        *reinterpret_cast<float4*>(a.pool_out + o + 4) = make_float4(best[4], best[5], best[6], best[7]);
-        *reinterpret_cast<uint2*>(a.arg_out + o) = make_uint2(bi[0] | (bi[1] << 8) | (bi[2] << 16) | (bi[3] << 24),
-                                                              bi[4] | (bi[5] << 8) | (bi[6] << 16) | (bi[7] << 24));
-        // the flattened pool output (:126, feature = cell * 64 + channel) as FC1's operand image [feature / 8][batch][8]
-        if (a.pool_img) *reinterpret_cast<uint4*>(a.pool_img + ((size_t)(cell * 8 + c8) * g.B + n_img0) * 16) = pack8(best);
-      }
-    }
     if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) a.timeline[6] = clock64();
     tc_fence_before();
   } else if (warp < 4 + NISS) {
@@ -567,6 +523,56 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
       }
     }
     __syncwarp();
+  }
+  if (!DGRAD && !POOL && a.pool_out) {
+    // ---- 3x3/2 SAME max-pool (pad 0 before / rest after), first max in (h,w) scan order (:123), by ALL nine warps
+    //      (the issuing and the filter warps are done by now): 36 cells x 8 channel chunks = one item per thread at
+    //      12x12, where the four epilogue warps alone needed three rounds ----
+    __syncthreads();
+    if (n_img0 < g.B) {
+      const float* tile = reinterpret_cast<const float*>(strip);
+      const int OH = (g.H + 1) / 2, OW = (g.W + 1) / 2;
+      const int pbh = max((OH - 1) * 2 + 3 - g.H, 0) / 2, pbw = max((OW - 1) * 2 + 3 - g.W, 0) / 2;
+      // one item = 8 channels of one pooled cell; window positions outside the image read a clamped address and enter
+      // the scan as -FLT_MAX (no branch); strict '>' in (kh, kw) order = first maximum
+      // (four channels per item: a pixel's sixteen lanes read 256 contiguous bytes, conflict-free; see conv1's pool)
+      for (int q = tid; q < OH * OW * 16; q += (int)blockDim.x) {
+        const int c4 = q & 15, cell = q >> 4;
+        const int oh = cell / OW, ow = cell - oh * OW;
+        float best[4];
+        int bi[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) { best[e] = -3.402823466e38f; bi[e] = 0; }
+#pragma unroll
+        for (int kh = 0; kh < 3; ++kh) {
+          const int hh = 2 * oh + kh - pbh;
+          const bool vh = (unsigned)hh < (unsigned)g.H;
+#pragma unroll
+          for (int kw = 0; kw < 3; ++kw) {
+            const int ww = 2 * ow + kw - pbw;
+            const bool ok = vh && (unsigned)ww < (unsigned)g.W;
+            const float4 v0 = *reinterpret_cast<const float4*>(tile + (size_t)(ok ? hh * g.W + ww : 0) * 68 + c4 * 4);
+            const float vv[4] = {v0.x, v0.y, v0.z, v0.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float x = ok ? vv[e] : -3.402823466e38f;
+              const bool gt = x > best[e];
+              best[e] = gt ? x : best[e];
+              bi[e] = gt ? kh * 3 + kw : bi[e];
+            }
+          }
+        }
+        const size_t o = ((size_t)n_img0 * OH * OW + cell) * 64 + c4 * 4;
+        *reinterpret_cast<float4*>(a.pool_out + o) = make_float4(best[0], best[1], best[2], best[3]);
+        *reinterpret_cast<uint32_t*>(a.arg_out + o) = (uint32_t)(bi[0] | (bi[1] << 8) | (bi[2] << 16) | (bi[3] << 24));
+        // the flattened pool output (:126, feature = cell * 64 + channel) as FC1's operand image [feature / 8][batch][8]
+        if (a.pool_img) {
+          const __nv_bfloat162 p0 = __floats2bfloat162_rn(best[0], best[1]), p1 = __floats2bfloat162_rn(best[2], best[3]);
+          *reinterpret_cast<uint2*>(a.pool_img + ((size_t)(cell * 8 + (c4 >> 1)) * g.B + n_img0) * 16 + (c4 & 1) * 8) =
+              make_uint2(*reinterpret_cast<const uint32_t*>(&p0), *reinterpret_cast<const uint32_t*>(&p1));
+        }
+      }
+    }
   }
   __syncthreads();
   if (warp == 4) {

@@ -223,14 +223,17 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
     // One item = 8 channels of one pooled cell (eight independent compare/select chains); window positions outside
     // the image read a clamped address and enter the scan as -FLT_MAX, so there is no branch in the scan.  The scan
     // runs in (kh, kw) order with a strict '>': the first maximum wins, as in the reference's MaxPoolWithArgmax use.
+    // (one item = FOUR channels: the sixteen lanes of a pixel then read its 256 bytes as 16-byte pieces of distinct
+    //  banks; with eight channels per item lanes c and c+4 of a quarter-warp hit the same banks, a 2-way conflict on
+    //  every load of the scan)
 #pragma unroll 1
-    for (int q = tid; q < g.OH * g.OW * 8; q += (int)blockDim.x) {
-      const int c8 = q & 7, cell = q >> 3;
+    for (int q = tid; q < g.OH * g.OW * 16; q += (int)blockDim.x) {
+      const int c4 = q & 15, cell = q >> 4;
       const int oh = cell / g.OW, ow = cell - oh * g.OW;
-      float best[8];
-      int bi[8];
+      float best[4];
+      int bi[4];
 #pragma unroll
-      for (int e = 0; e < 8; ++e) { best[e] = -3.402823466e38f; bi[e] = 0; }
+      for (int e = 0; e < 4; ++e) { best[e] = -3.402823466e38f; bi[e] = 0; }
 #pragma unroll
       for (int kh = 0; kh < 3; ++kh) {
         const int h = 2 * oh + kh - pbh;
@@ -239,11 +242,10 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
         for (int kw = 0; kw < 3; ++kw) {
           const int w = 2 * ow + kw - pbw;
           const bool ok = vh && (unsigned)w < (unsigned)g.W;
-          const float* src = convbuf + (size_t)(ok ? h * g.W + w : 0) * kConvRow + c8 * 8;
-          const float4 v0 = *reinterpret_cast<const float4*>(src), v1 = *reinterpret_cast<const float4*>(src + 4);
-          const float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+          const float4 v0 = *reinterpret_cast<const float4*>(convbuf + (size_t)(ok ? h * g.W + w : 0) * kConvRow + c4 * 4);
+          const float vv[4] = {v0.x, v0.y, v0.z, v0.w};
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
+          for (int e = 0; e < 4; ++e) {
             const float x = ok ? vv[e] : -3.402823466e38f;
             const bool gt = x > best[e];
             best[e] = gt ? x : best[e];
@@ -251,12 +253,13 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
           }
         }
       }
-      const size_t o = ((size_t)n * g.OH * g.OW + cell) * C1 + nc0 + c8 * 8;
+      const size_t o = ((size_t)n * g.OH * g.OW + cell) * C1 + nc0 + c4 * 4;
       *reinterpret_cast<float4*>(a.pool + o) = make_float4(best[0], best[1], best[2], best[3]);
-      *reinterpret_cast<float4*>(a.pool + o + 4) = make_float4(best[4], best[5], best[6], best[7]);
-      if (a.pool_bf16) *reinterpret_cast<uint4*>(a.pool_bf16 + o) = pack8(best);
-      *reinterpret_cast<uint2*>(a.arg + o) = make_uint2(bi[0] | (bi[1] << 8) | (bi[2] << 16) | (bi[3] << 24),
-                                                        bi[4] | (bi[5] << 8) | (bi[6] << 16) | (bi[7] << 24));
+      if (a.pool_bf16) {
+        const __nv_bfloat162 p0 = __floats2bfloat162_rn(best[0], best[1]), p1 = __floats2bfloat162_rn(best[2], best[3]);
+        *reinterpret_cast<uint2*>(a.pool_bf16 + o) = make_uint2(*reinterpret_cast<const uint32_t*>(&p0), *reinterpret_cast<const uint32_t*>(&p1));
+      }
+      *reinterpret_cast<uint32_t*>(a.arg + o) = (uint32_t)(bi[0] | (bi[1] << 8) | (bi[2] << 16) | (bi[3] << 24));
     }
   }
   __syncthreads();

@@ -177,9 +177,16 @@ class _GraphStep:
     forward + backward + exchange + update (+ the loss copy to a pinned slot), the next batch drawn from the shuffle
     queue on a side stream while the current step runs, no host synchronisation."""
 
-    def __init__(self, eng, exchange, source, lr):
+    def __init__(self, eng, exchange, source, lr, staleness=0):
         self.eng, self.ex, self.source, self.lr = eng, exchange, source, lr
         dev = eng.params.device
+        # asynchronous-ps fidelity (cifar10cnn.py:162-163 without SyncReplicasOptimizer): a gradient reaches the variables
+        # `staleness` exchange rounds after the snapshot it was computed on.  A FIFO of that many flat gradient buffers
+        # sits between the backward pass and the exchange; 0 = the synchronous default.
+        self.stale_k = int(staleness)
+        if self.stale_k:
+            self._fifo = torch.zeros(self.stale_k, eng.grads.numel(), dtype=torch.float32, device=dev)
+            self._fresh = torch.zeros_like(eng.grads)
         B = eng.batch
         c = eng.cfg
         self.bufs = [(torch.empty(B, c.c_in, c.img_h, c.img_w, dtype=torch.uint8, device=dev),
@@ -198,13 +205,27 @@ class _GraphStep:
         keep = eng.params.clone()
         self.graphs = [eng.capture(lambda k=k: self._body(k)) for k in range(2)]
         eng.params.copy_(keep)
+        if self.stale_k:
+            self._fifo.zero_()                                     # (the capture runs pushed garbage through the line)
         torch.cuda.synchronize(dev)
         self._prefetch(0)
 
     def _body(self, k):
         img, lab = self.bufs[k]
         eng, ex = self.eng, self.ex
-        if ex.world == 1:
+        if self.stale_k:
+            eng.forward_backward(img, lab)
+            self._fresh.copy_(eng.grads)
+            eng.grads.copy_(self._fifo[0])                         # the gradient computed stale_k rounds ago
+            for j in range(self.stale_k - 1):
+                self._fifo[j].copy_(self._fifo[j + 1])
+            self._fifo[self.stale_k - 1].copy_(self._fresh)
+            if ex.world > 1 and hasattr(ex, "apply_"):
+                ex.apply_(eng, self.lr)
+            else:
+                ex.allreduce_(eng.grads)
+                eng.sgd_apply(self.lr, ex.grad_scale)
+        elif ex.world == 1:
             eng.train_step(img, lab, self.lr)
         elif hasattr(ex, "train_step_"):
             ex.train_step_(eng, img, lab, self.lr)                 # fused peer-memory exchange + update
@@ -243,7 +264,10 @@ class MonitoredTrainingSession:
     counts WORKER updates like the reference's shared counter: one exchange round applies
     `world` of them."""
 
-    def __init__(self, is_chief=True, last_step=20000, reduce="sum", checkpoint_dir=None, save_secs=600.0):
+    def __init__(self, is_chief=True, last_step=20000, reduce="sum", checkpoint_dir=None, save_secs=600.0, staleness=0):
+        if staleness < 0 or staleness > 64:
+            raise ValueError("staleness must be in 0..64 exchange rounds")
+        self.staleness = int(staleness)
         self.is_chief = is_chief
         self.last_step = last_step
         self.reduce = reduce
@@ -300,7 +324,7 @@ class MonitoredTrainingSession:
             if self.exchange.world > 1:
                 import torch.distributed as dist
                 dist.barrier()
-            st = self._steps[key] = _GraphStep(eng, self.exchange, op.loss.labels.source, lr)
+            st = self._steps[key] = _GraphStep(eng, self.exchange, op.loss.labels.source, lr, self.staleness)
         return st.step()
 
     def run(self, fetches):

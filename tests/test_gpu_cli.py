@@ -166,3 +166,35 @@ def test_session_loss_is_deferred_but_exact():
         #  atomics, so later steps agree to rounding, not bit for bit)
         assert (not np.isfinite(gv) and not np.isfinite(wv)) or abs(gv - wv) <= 1e-4 * abs(wv), (gv, wv)
     assert float(got[0]) == float(want[0])
+
+
+def test_async_ps_fidelity_mode_applies_gradients_late():
+    """N4: `staleness=K` emulates the reference's asynchronous parameter server (cifar10cnn.py:162-163, no
+    SyncReplicasOptimizer): the gradient of the snapshot taken at round t reaches the variables at round t + K.
+    Checked against an explicit delay line built from the engine's own forward / backward / update calls."""
+    import b200cnn
+    from b200cnn import session
+    import cifar10cnn as cli
+    B, K, steps = 32, 2, 5
+    itr, ltr = session.input_pipeline(B, True, seed=21, synthetic=True)
+    scope = session.ModelScope(mode="fp32", seed=0)
+    out = cli.create_cnn(itr, B, scope)
+    loss = cli.cifar_loss(out, ltr)
+    op = cli.train_step(loss, session.Variable(0))
+    ref = b200cnn.TrainStepEngine(batch=B, mode="fp32")
+    ref.init_params(0)
+    p_init = ref.params.clone()
+    src = b200cnn.data.BatchSource(B, True, seed=21, synthetic=True)
+    line = []
+    with session.MonitoredTrainingSession(last_step=steps, staleness=K) as sess:
+        while not sess.should_stop():
+            sess.run([op, loss])
+            img, lab = src.next()
+            ref.forward(img, lab); ref.backward()
+            line.append(ref.grads.clone())
+            ref.grads.copy_(line[-1 - K] if len(line) > K else torch.zeros_like(ref.grads))
+            ref.sgd_apply(0.1)
+    torch.cuda.synchronize()
+    assert torch.equal(out.engine.params, ref.params)
+    # the first K rounds leave the variables untouched (nothing has arrived yet): with steps > K they did move
+    assert not torch.equal(ref.params, p_init)
