@@ -483,8 +483,10 @@ def main():
         table.append(row)
     table.sort(key=lambda r: -r["ms"])
     # the roofline object is about ONE kernel: sites that time two launches together (the FC tail's rows + gradient
-    # kernels, conv2's wgrad + partial reduction, the two weight-image kernels) stay in `sites` but are not candidates
-    composite = {"fc_tail", "conv2_wgrad", "weights_prep"}
+    # kernels, conv2's wgrad + partial reduction, conv1's wgrad + partial reduction -- folded into the update kernel in
+    # the captured step, a launch of its own here --, the weight-image kernels, the layer-by-layer schedule's FC
+    # backward products) stay in `sites` but are not candidates
+    composite = {"fc_tail", "conv2_wgrad", "conv1_wgrad", "weights_prep", "full1_bwd", "full2_bwd", "full3_bwd", "full1_fwd"}
     dom = next((r for r in table if r["site"] not in composite), table[0])
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")

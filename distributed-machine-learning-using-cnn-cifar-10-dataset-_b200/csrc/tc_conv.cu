@@ -699,7 +699,9 @@ int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, 
   }
   if (pool_out) {
     B200_REQUIRE(!DGRAD && NC == 64 && arg_out, "conv5x5_tc: fused pool needs the forward kernel with 64 output channels");
-    B200_REQUIRE((int64_t)H * W * 68 * 4 <= (int64_t)(KC / 8) * g.ch_stride, "conv5x5_tc: conv tile does not fit the strip");
+    // the epilogue parks the fp32 conv tile (68 floats per pixel) where the strip was: widen the chunk planes if the
+    // strip alone is smaller (16x16 images from an fp32 source: 60 KB of strip, 70 KB of tile)
+    while ((int64_t)H * W * 68 * 4 > (int64_t)(KC / 8) * g.ch_stride) g.ch_stride += 128;
   }
   B200_REQUIRE(g.tiles * 64 <= 512, "conv5x5_tc: image %dx%d too large for one CTA's TMEM", H, W);
   const int staps = (two || wide) ? 1 : 5;
