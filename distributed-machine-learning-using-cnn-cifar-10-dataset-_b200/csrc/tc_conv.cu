@@ -1029,13 +1029,44 @@ __global__ void __launch_bounds__(416, 1) conv5x5_wgrad_tc_kernel(WgradArgs a) {
 // A launch can carry a second, independent segment (its blocks follow the first segment's): conv2's bias-gradient
 // partials ride along with its filter-gradient partials.
 struct ReduceSeg { const float* part; float* out; int n, S, stride; };
-__global__ void reduce_partials_tc(ReduceSeg s0, ReduceSeg s1) {
+__global__ void __launch_bounds__(128) reduce_partials_tc(ReduceSeg s0, ReduceSeg s1) {
   B200_TRACE_SCOPE(TR_CONV2_REDUCE);
   pdl_wait();
   const int nb0 = (s0.n + 127) / 128;
-  const bool second = (int)blockIdx.x >= nb0;
-  const ReduceSeg& g = second ? s1 : s0;
-  const int t = (blockIdx.x - (second ? nb0 : 0)) * blockDim.x + threadIdx.x;
+  if ((int)blockIdx.x >= nb0) {
+    // second segment: MANY partials of a short vector (conv2's bias gradient: one partial per dgrad CTA, up to the batch
+    // size of them, 64 floats each) -- one BLOCK per 16 bytes: thread t sums partials t, t + 128, ... in order, the 32
+    // lanes of a warp combine by a shuffle tree, the four warps' sums are added in warp order.  Fixed order again.
+    __shared__ float4 wsum[4];
+    const int i = (blockIdx.x - nb0) * 4;
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int z0 = threadIdx.x; z0 < s1.S; z0 += 128 * 8) {
+      float4 v[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int z = z0 + 128 * j;
+        v[j] = z < s1.S ? __ldg(reinterpret_cast<const float4*>(s1.part + (int64_t)z * s1.stride + i)) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { s.x += v[j].x; s.y += v[j].y; s.z += v[j].z; s.w += v[j].w; }
+    }
+#pragma unroll
+    for (int m = 1; m <= 16; m <<= 1) {
+      s.x += __shfl_xor_sync(0xffffffffu, s.x, m); s.y += __shfl_xor_sync(0xffffffffu, s.y, m);
+      s.z += __shfl_xor_sync(0xffffffffu, s.z, m); s.w += __shfl_xor_sync(0xffffffffu, s.w, m);
+    }
+    if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float4 r = wsum[0];
+#pragma unroll
+      for (int w = 1; w < 4; ++w) { r.x += wsum[w].x; r.y += wsum[w].y; r.z += wsum[w].z; r.w += wsum[w].w; }
+      *reinterpret_cast<float4*>(s1.out + i) = r;
+    }
+    return;
+  }
+  const ReduceSeg& g = s0;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
   const int sub = t & 3;
   const int i = min((t >> 2) * 4, g.n - 4);                 // surplus threads redo the last group (shuffles stay full-warp)
   float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -1168,7 +1199,7 @@ static int launch_wgrad(const float* x, const float* dy, const PoolGradSrc* pg, 
   const int n = 25 * Cin * Cout;
   g_pdl_next = overlap;
   const bool with_db = db_part && db && n_db_part > 0;      // the bias-gradient partials of the dgrad kernel ride along
-  B200_CUDA_TRY(launch_kernel(reduce_partials_tc, dim3(cdiv(n, 128) + (with_db ? 1 : 0)), dim3(128), 0, st,
+  B200_CUDA_TRY(launch_kernel(reduce_partials_tc, dim3(cdiv(n, 128) + (with_db ? 64 / 4 : 0)), dim3(128), 0, st,
                               ReduceSeg{scratch, dw, n, S, n},
                               with_db ? ReduceSeg{db_part, db, 64, n_db_part, 64} : ReduceSeg{nullptr, nullptr, 0, 0, 0}));
   return B200_OK;
