@@ -45,6 +45,8 @@ struct b200_model {
   bool forward_done = false;
   // side streams / events for the independent branches of the backward pass (created at the first
   // bf16 backward, which must therefore run once eagerly before any stream capture)
+  cudaStream_t copy_stream = nullptr;      // host-batch prefetch (b200_train_step_host_prefetch)
+  cudaEvent_t ev_copy[2] = {nullptr, nullptr};
   cudaStream_t side[2] = {nullptr, nullptr};
   cudaEvent_t ev_fork[2] = {nullptr, nullptr}, ev_join[2] = {nullptr, nullptr}, ev_aux[2] = {nullptr, nullptr};
   const uint8_t* last_images = nullptr;   // records of the last forward (the fused conv1 gradient re-reads them)
@@ -156,6 +158,8 @@ int b200_create(const b200_config* c, b200_handle* out) {
   h->add("loss", 1, 4); h->add("n_correct", 1, 4); h->add("n_bad", 1, 4); h->add("pred", B, 4);
   h->add("stage_images", B * c->c_in * c->img_h * c->img_w, 1);
   h->add("stage_labels", B, 4);
+  h->add("stage_images1", B * c->c_in * c->img_h * c->img_w, 1);      // second staging slot (b200_train_step_host_prefetch)
+  h->add("stage_labels1", B, 4);
   *out = h;
   return B200_OK;
 }
@@ -163,6 +167,9 @@ int b200_create(const b200_config* c, b200_handle* out) {
 int b200_destroy(b200_handle h) {
   if (h) {
     for (cudaEvent_t ev : h->site_events) cudaEventDestroy(ev);
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+    for (int i = 0; i < 2; ++i)
+      if (h->ev_copy[i]) cudaEventDestroy(h->ev_copy[i]);
     for (int i = 0; i < 2; ++i) {
       if (h->ev_fork[i]) cudaEventDestroy(h->ev_fork[i]);
       if (h->ev_join[i]) cudaEventDestroy(h->ev_join[i]);
@@ -663,6 +670,53 @@ int b200_train_step_host(b200_handle h, const uint8_t* images_host, const int32_
   B200_CUDA_TRY(cudaMemcpyAsync(sl, labels_host, (size_t)c.batch * 4, cudaMemcpyHostToDevice, st));
   TRY(b200_train_step(h, si, sl, lr, stream));
   B200_CUDA_TRY(cudaMemcpyAsync(loss_host, h->ptr<float>("loss"), 4, cudaMemcpyDeviceToHost, st));
+  return B200_OK;
+}
+
+// ---- host batches with prefetch: two staging slots, the copy of the NEXT batch overlaps the step on the current one ----
+static int stage_ptrs(b200_model* h, int slot, uint8_t** si, int32_t** sl) {
+  B200_REQUIRE(slot == 0 || slot == 1, "staging slot must be 0 or 1");
+  *si = h->ptr<uint8_t>(slot ? "stage_images1" : "stage_images");
+  *sl = h->ptr<int32_t>(slot ? "stage_labels1" : "stage_labels");
+  return B200_OK;
+}
+int b200_stage_host_batch(b200_handle h, int32_t slot, const uint8_t* images_host, const int32_t* labels_host, void* stream) {
+  B200_READY(h);
+  B200_REQUIRE(images_host && labels_host, "stage_host_batch: null argument");
+  uint8_t* si; int32_t* sl;
+  TRY(stage_ptrs(h, slot, &si, &sl));
+  const b200_config& c = h->cfg;
+  cudaStream_t st = (cudaStream_t)stream;
+  B200_CUDA_TRY(cudaMemcpyAsync(si, images_host, (size_t)c.batch * c.c_in * c.img_h * c.img_w, cudaMemcpyHostToDevice, st));
+  B200_CUDA_TRY(cudaMemcpyAsync(sl, labels_host, (size_t)c.batch * 4, cudaMemcpyHostToDevice, st));
+  return B200_OK;
+}
+int b200_train_step_host_prefetch(b200_handle h, int32_t slot, const uint8_t* next_images_host,
+                                  const int32_t* next_labels_host, float lr, float* loss_host, void* stream) {
+  B200_READY(h);
+  B200_REQUIRE(loss_host, "train_step_host_prefetch: null loss pointer");
+  B200_REQUIRE((next_images_host == nullptr) == (next_labels_host == nullptr),
+               "train_step_host_prefetch: give both next-batch pointers or none");
+  uint8_t *si, *ni; int32_t *sl, *nl;
+  TRY(stage_ptrs(h, slot, &si, &sl));
+  TRY(stage_ptrs(h, slot ^ 1, &ni, &nl));
+  const b200_config& c = h->cfg;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!h->copy_stream) {      // created by the first (eager) call, like the side streams
+    B200_CUDA_TRY(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) B200_CUDA_TRY(cudaEventCreateWithFlags(&h->ev_copy[i], cudaEventDisableTiming));
+  }
+  if (next_images_host) {     // fork: the next batch travels while this one is trained on
+    B200_CUDA_TRY(cudaEventRecord(h->ev_copy[0], st));
+    B200_CUDA_TRY(cudaStreamWaitEvent(h->copy_stream, h->ev_copy[0], 0));
+    B200_CUDA_TRY(cudaMemcpyAsync(ni, next_images_host, (size_t)c.batch * c.c_in * c.img_h * c.img_w,
+                                  cudaMemcpyHostToDevice, h->copy_stream));
+    B200_CUDA_TRY(cudaMemcpyAsync(nl, next_labels_host, (size_t)c.batch * 4, cudaMemcpyHostToDevice, h->copy_stream));
+    B200_CUDA_TRY(cudaEventRecord(h->ev_copy[1], h->copy_stream));
+  }
+  TRY(b200_train_step(h, si, sl, lr, stream));
+  B200_CUDA_TRY(cudaMemcpyAsync(loss_host, h->ptr<float>("loss"), 4, cudaMemcpyDeviceToHost, st));
+  if (next_images_host) B200_CUDA_TRY(cudaStreamWaitEvent(st, h->ev_copy[1], 0));      // join
   return B200_OK;
 }
 

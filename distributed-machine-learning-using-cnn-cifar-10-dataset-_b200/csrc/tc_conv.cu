@@ -1088,8 +1088,19 @@ __global__ void __launch_bounds__(128) reduce_partials_tc(ReduceSeg s0, ReduceSe
   if (sub == 0 && (t >> 2) * 4 < g.n) *reinterpret_cast<float4*>(g.out + i) = s;
 }
 
-// image splits of the filter gradient: 5 filter rows x (64 x 64 channel blocks) x splits ~ one wave of CTAs
-int wgrad_splits_tc(int B, int nblk = 1) { return std::max(1, std::min(B, (kNumSMs + 4) / (5 * nblk))); }
+// image splits of the filter gradient: 5 filter rows x (64 x 64 channel blocks) x splits ~ one wave of CTAs.
+// Up to one wave of images (batch <= 148) conv2's filter gradient SHARES the machine with conv1's (which follows dgrad
+// on the main stream at the same moment, one CTA per SM each): conv1 takes ceil(B/2) CTAs (two images each), this kernel
+// 5 x splits CTAs out of the rest -- 64 + 80 at batch 128.  Both then finish in one wave instead of one after the other:
+// 105.6 vs 110.9 us per step back to back (118.7 -> 120.7 us with L2 flushed between steps; measured, scratch/gpu_call24.sh).
+// (B200_WGRAD2_SPLITS / B200_WGRAD1_CTAS override both choices: experiments.)
+int wgrad_splits_tc(int B, int nblk = 1) {
+  static int env = -1;
+  if (env < 0) { const char* e = getenv("B200_WGRAD2_SPLITS"); env = e ? atoi(e) : 0; }
+  if (env > 0 && nblk == 1) return std::max(1, std::min(B, env));
+  if (nblk == 1 && B <= kNumSMs) return std::max(1, std::min(B, (kNumSMs - (B + 1) / 2) / 5));
+  return std::max(1, std::min(B, (kNumSMs + 4) / (5 * nblk)));
+}
 }  // namespace
 
 int reduce_partials(const float* part, float* out, int n, int S, cudaStream_t st, int stride) {

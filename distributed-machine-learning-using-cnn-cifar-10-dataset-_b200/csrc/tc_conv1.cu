@@ -16,6 +16,8 @@
 // five taps of a row are the five N-groups of an MN-major B operand whose group stride SBO is one
 // pixel slot (16 B).  Channel 3 of the x strip is the constant 1, so column dj*8+3 of the centre
 // tap is the bias gradient sum(dY) for free.
+#include <stdlib.h>
+
 #include <algorithm>
 
 #include "launch.h"
@@ -503,7 +505,13 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
   }
 }
 
-int conv1_wgrad_ctas(int B) { return std::min(B, kNumSMs); }
+int conv1_wgrad_ctas(int B) {
+  static int env = -1;      // B200_WGRAD1_CTAS: experiments (see wgrad_splits_tc in tc_conv.cu)
+  if (env < 0) { const char* e = getenv("B200_WGRAD1_CTAS"); env = e ? atoi(e) : 0; }
+  if (env > 0) return std::min(B, std::min(env, kNumSMs));
+  // up to one wave of images: two images per CTA, so that conv2's filter gradient fits beside this kernel
+  return B <= kNumSMs ? (B + 1) / 2 : kNumSMs;
+}
 size_t conv1_wgrad_smem(const C1Geom& g) {
   size_t xs = (g.npix * 16 + 127) & ~127, ch = g.npix * 16 + 16;
   return xs + ((8 * ch + 127) & ~127) + 2 * (size_t)g.OH * g.OW * 64 * 4 + (((size_t)g.OH * g.OW * 64 + 127) & ~127) +

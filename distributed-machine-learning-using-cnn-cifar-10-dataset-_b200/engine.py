@@ -22,7 +22,7 @@ PARAM_NAMES = ("conv1_kernel", "conv1_bias", "conv2_kernel", "conv2_bias", "full
 PARAM_SCOPES = ("conv1", "conv1", "conv2", "conv2", "full1", "full1", "full2", "full2", "full3", "full3")
 
 _DT = {4: torch.float32, 1: torch.uint8, 2: torch.bfloat16}
-_INT_TENSORS = {"pred", "n_correct", "n_bad", "stage_labels"}
+_INT_TENSORS = {"pred", "n_correct", "n_bad", "stage_labels", "stage_labels1"}
 
 
 def _require_cuda():
@@ -173,6 +173,25 @@ class TrainStepEngine:
         out = self._loss_host if loss_out is None else loss_out
         check(self.lib.b200_train_step_host(self.h, images_pinned.data_ptr(), labels_pinned.data_ptr(), lr,
                                             out.data_ptr(), self._stream()))
+        if sync:
+            torch.cuda.current_stream().synchronize()
+            return float(out[0])
+        return None
+
+    def stage_host_batch(self, slot, images_pinned, labels_pinned):
+        """copy a pinned host batch into staging slot 0 / 1 (primes train_step_host_prefetch)"""
+        if images_pinned.is_cuda or labels_pinned.is_cuda or not images_pinned.is_pinned():
+            raise ValueError("stage_host_batch takes pinned host tensors")
+        check(self.lib.b200_stage_host_batch(self.h, slot, images_pinned.data_ptr(), labels_pinned.data_ptr(),
+                                             self._stream()))
+
+    def train_step_host_prefetch(self, slot, next_images_pinned, next_labels_pinned, lr=0.1, loss_out=None, sync=False):
+        """Train on the batch already staged in `slot` while the NEXT pinned host batch is copied into the other
+        slot (an input pipeline with prefetch); the loss goes to `loss_out` (pinned)."""
+        out = self._loss_host if loss_out is None else loss_out
+        ni = None if next_images_pinned is None else next_images_pinned.data_ptr()
+        nl = None if next_labels_pinned is None else next_labels_pinned.data_ptr()
+        check(self.lib.b200_train_step_host_prefetch(self.h, slot, ni, nl, lr, out.data_ptr(), self._stream()))
         if sync:
             torch.cuda.current_stream().synchronize()
             return float(out[0])

@@ -126,6 +126,15 @@ int b200_train_step(b200_handle h, const uint8_t* images, const int32_t* labels,
  * synchronises the stream before reading *loss_host. */
 int b200_train_step_host(b200_handle h, const uint8_t* images_host, const int32_t* labels_host,
                          float lr, float* loss_host, void* stream);
+/* The same with the input copy taken off the critical path (what an input pipeline with prefetch does for the loop of
+ * :228-230): two staging slots in the workspace.  b200_stage_host_batch copies a pinned host batch into `slot`
+ * (0 or 1) on `stream`; b200_train_step_host_prefetch trains on the batch already in `slot` while the NEXT pinned
+ * host batch (may be NULL at the end of the data) is copied into the other slot on an internal copy stream, forked
+ * from and joined to `stream` with events (created by the first call: make it before any capture), and copies the
+ * scalar loss back.  The caller alternates `slot` and synchronises the stream before reading *loss_host. */
+int b200_stage_host_batch(b200_handle h, int32_t slot, const uint8_t* images_host, const int32_t* labels_host, void* stream);
+int b200_train_step_host_prefetch(b200_handle h, int32_t slot, const uint8_t* next_images_host,
+                                  const int32_t* next_labels_host, float lr, float* loss_host, void* stream);
 
 /* One eager b200_train_step with a CUDA event recorded on `stream` before every launch site
  * (a site = the kernels of one logical op: "conv2_fwd", "full1_bwd", "sgd_apply" ...).  Blocks
