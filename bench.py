@@ -412,6 +412,17 @@ def main():
     stage_first()
     host_graphs = [eng.capture(restoring(host_step(j))) for j in range(RING)]
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    flush_rd = torch.zeros(64 << 20, dtype=torch.int32, device="cuda")      # 256 MiB, only ever read
+    flush_mode = os.environ.get("B200_BENCH_FLUSH", "write")
+
+    def flush_l2():
+        """untimed, between timed steps: write a 256 MiB buffer (twice the 126 MB L2) so that nothing of the previous
+        step survives in L2.  B200_BENCH_FLUSH=write+read (experiment) follows it with a read pass over a second 256 MiB
+        buffer, which leaves the L2 full of CLEAN lines: the step then does not pay the write-back of the memset's dirty
+        lines on every allocation."""
+        flush_buf.zero_()
+        if flush_mode == "write+read":
+            flush_rd.sum()
 
     def barrier():
         if world > 1:
@@ -434,7 +445,7 @@ def main():
     barrier()
     for i in range(K):
         reset()                                             # untimed: every step starts from the initial weights
-        flush_buf.zero_()                                   # untimed: evicts weights/activations from the 126 MB L2
+        flush_l2()                                          # untimed: evicts weights/activations from the 126 MB L2
         a, b = ev[i]
         a.record()
         s_img.copy_(pool[i % POOL][0]); s_lab.copy_(pool[i % POOL][1])
@@ -490,7 +501,7 @@ def main():
     acc = {}
     for i in range(n_prof + 2):
         reset()
-        flush_buf.zero_()
+        flush_l2()
         sites = eng.profile_step(pool[i % POOL][0], pool[i % POOL][1], lr)
         if i >= 2:
             for n, ms in sites:
@@ -545,7 +556,8 @@ def main():
             "dtype": "f32" if mode == "fp32" else "bf16", "data": "synthetic",
             "config": {"workload": workload_name(args), "model_widths": model["dims"], "batch_per_gpu": B, "global_batch": B * world,
                        "mode": mode, "parallelism": f"dp{world}", "reduce": args.reduce, "exchange": exchange,
-                       "l2": "flushed between timed steps (256 MiB memset, untimed); per-step CUDA events summed",
+                       "l2": "flushed between timed steps (256 MiB memset, untimed%s); per-step CUDA events summed"
+                             % (" + 256 MiB read pass" if flush_mode == "write+read" else ""),
                        "cuda_graph": True},
             "value_hot_l2": imgs / (ms_hot * 1e-3),
             "restore_us_per_step": 1e3 * ms_restore / K,
