@@ -40,6 +40,9 @@ struct ConvGeom {
   int ch_stride;            // bytes between channel chunks of the strip (npix*16 + 16)
   int nstages;              // filter stages in the ring (of 5 taps or 1 tap each, a template parameter of the kernel)
   int tma_rows;             // > 0: the strip is written by the TMA (tensor-map box of P x tma_rows pixel slots per chunk)
+  int tma_h0;               // first image row of a TMA box: -3 (one image: the box brings its own zero rows above) or 0
+                            // (several images: boxes of H+2 rows tile the strip; the three zero rows above the first
+                            // image are written once by the loader warps)
   int two_pass;             // KSPLIT == 2 with a TMA strip: the strip holds HALF the contraction channels at a time -- all
                             // 25 taps of channels [0, KC/2), a refill, all 25 taps of the rest -- which leaves twice the
                             // shared memory for filter stages in flight (the filter stream is latency-bound)
@@ -56,6 +59,7 @@ __host__ inline ConvGeom make_geom(int B, int H, int W, int KC, int NC, int ipc)
   g.ch_stride = g.npix * 16 + 16;
   g.nstages = WSTAGES;
   g.tma_rows = 0;
+  g.tma_h0 = 0;
   g.two_pass = 0;
   return g;
 }
@@ -65,11 +69,21 @@ __host__ inline ConvGeom make_geom(int B, int H, int W, int KC, int NC, int ipc)
 // rows above (two for the taps, one so that the slot "row -2, column -2" of tap (0,0) is still inside the box) and two
 // below: no zeroing pass, no loads through registers.  Rows of the MMA tiles past the box read whatever follows in
 // shared memory; they only feed output rows the epilogue drops (GEMM rows are independent).
-__host__ inline ConvGeom make_geom_tma(int B, int H, int W, int KC, int NC, int min_strip_bytes) {
-  ConvGeom g = make_geom(B, H, W, KC, NC, 1);
-  g.tma_rows = H + 5;
+// Several images per CTA (wide layers): one box of H+2 rows per image and chunk -- the image and the two zero rows
+// below it, which are also the zero rows above the next image -- back to back from slot `lead` = 3 rows of zeros that the
+// loader warps write once.
+__host__ inline ConvGeom make_geom_tma(int B, int H, int W, int KC, int NC, int min_strip_bytes, int ipc = 1) {
+  ConvGeom g = make_geom(B, H, W, KC, NC, ipc);
   g.lead = 3 * g.P;
-  g.npix = g.tma_rows * g.P;
+  if (ipc == 1) {
+    g.tma_rows = H + 5;
+    g.tma_h0 = -3;
+    g.npix = g.tma_rows * g.P;
+  } else {
+    g.tma_rows = H + 2;
+    g.tma_h0 = 0;
+    g.npix = g.lead + ipc * g.rows_per_img * g.P;
+  }
   g.ch_stride = (g.npix * 16 + 127) & ~127;                         // TMA destinations are 128-byte aligned
   const int chunks = KC / 8;
   while (chunks * g.ch_stride < min_strip_bytes) g.ch_stride += 128;    // the fused pool parks its fp32 tile here
@@ -268,7 +282,8 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
   uint64_t* strip_full = wempty + MAX_WSTAGES;
   uint64_t* accum = strip_full + 1;
   uint64_t* pass_done = accum + 1;        // two_pass: the MMAs on the first half of the channels have been issued and completed
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pass_done + 1);
+  uint64_t* lead_ready = pass_done + 1;   // several images per TMA strip: the loader warps have zeroed the rows above the first image
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(lead_ready + 1);
   float* dpm = reinterpret_cast<float*>(ctrl + 256);                  // POOL: [OH*OW][64] masked pooled gradient
   uint8_t* argb = reinterpret_cast<uint8_t*>(dpm + (POOL ? a.pg.OH * a.pg.OW * 64 : 0));
   float* bred = reinterpret_cast<float*>(argb + (POOL ? ((a.pg.OH * a.pg.OW * 64 + 15) & ~15) : 0));   // [64]
@@ -283,6 +298,7 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
     mbar_init(smem_u32(strip_full), POOL ? 256 : (g.tma_rows ? 1 : LOADERS));
     mbar_init(smem_u32(accum), NISS);
     mbar_init(smem_u32(pass_done), NISS);
+    mbar_init(smem_u32(lead_ready), LOADERS);
     fence_mbar_init();
   }
   if (warp == 4) tmem_alloc(smem_u32(tmem_slot), tmem_cols);
@@ -348,8 +364,17 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
     }
   }
   if (warp < 4) {
-    if (!POOL && g.tma_rows) {       // the TMA warp fills the strip: nothing to stage here
+    if (!POOL && g.tma_rows) {       // the TMA warp fills the strip: nothing to stage here ...
       if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) a.timeline[0] = a.timeline[1] = clock64();
+      if (g.tma_h0 == 0) {           // ... but the zero rows above the first image (boxes start at the image's first row)
+        const int nplanes = two_pass ? kchunks / 2 : kchunks;
+        for (int q = tid; q < nplanes * g.lead; q += LOADERS) {
+          const int c = q / g.lead, sl = q - c * g.lead;
+          *reinterpret_cast<uint4*>(strip + c * g.ch_stride + sl * 16) = make_uint4(0, 0, 0, 0);
+        }
+        fence_proxy_async();
+        mbar_arrive(smem_u32(lead_ready));
+      }
       pdl_wait();
       pdl_launch_dependents();
     } else if (!POOL) {
@@ -416,6 +441,7 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
       const uint32_t b_lo0 = DGRAD ? desc_lo(smem_u32(wring), w_k_lbo) : desc_lo(smem_u32(wring), 128);
       const uint32_t a_kstep = 2 * (g.ch_stride >> 4), b_kstep = DGRAD ? 2 * (w_k_lbo >> 4) : 16;
       mbar_wait(smem_u32(strip_full), 0);
+      if (!POOL && g.tma_rows && g.tma_h0 == 0) { mbar_wait(smem_u32(lead_ready), 0); tc_fence_after(); }
       if (a.timeline && blockIdx.x == 0 && blockIdx.y == 0 && w == 0) a.timeline[3] = clock64();
       // Every CTA streams the same 25 filter taps out of L2; each walks them in its own rotation so
       // that the CTAs do not all pull the same lines at once (the sum over taps is order-independent).
@@ -472,9 +498,12 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
         pdl_wait();
         const uint32_t bar = smem_u32(strip_full);
         const int nc = two_pass ? kchunks / 2 : kchunks;
-        mbar_arrive_expect_tx(bar, (uint32_t)(nc * g.P * g.tma_rows * 16));
-        for (int c = 0; c < nc; ++c)
-          tma_load_5d(smem_u32(strip + c * g.ch_stride), &a.tmap, 0, c, 0, -3, n_img0, bar);
+        const int nbox = g.tma_h0 == 0 ? g.ipc : 1;                  // one box per image and chunk
+        const uint32_t box0 = g.tma_h0 == 0 ? (uint32_t)g.lead * 16 : 0u, boxstep = (uint32_t)g.rows_per_img * g.P * 16;
+        mbar_arrive_expect_tx(bar, (uint32_t)(nc * nbox * g.P * g.tma_rows * 16));
+        for (int im = 0; im < nbox; ++im)      // (an image index past the batch is out of bounds too: zeros)
+          for (int c = 0; c < nc; ++c)
+            tma_load_5d(smem_u32(strip + c * g.ch_stride) + box0 + im * boxstep, &a.tmap, 0, c, 0, g.tma_h0, n_img0 + im, bar);
       }
       const int img = (a.cout_f / 8) * (a.cin_f * 16 + 16);             // bytes of one packed tap
       const int rot = STAPS == 5 ? (int)((blockIdx.x + blockIdx.y) % 5u) * 5 : (int)((blockIdx.x * 7u + blockIdx.y) % 25u);
@@ -487,9 +516,13 @@ __global__ void __launch_bounds__(288, MINB) conv5x5_tc_kernel(const __grid_cons
           // every MMA on the first half of the channels has completed: the strip may take the second half
           mbar_wait(smem_u32(pass_done), 0);
           const uint32_t sbar = smem_u32(strip_full);
-          mbar_arrive_expect_tx(sbar, (uint32_t)((kchunks / 2) * g.P * g.tma_rows * 16));
-          for (int c = 0; c < kchunks / 2; ++c)
-            tma_load_5d(smem_u32(strip + c * g.ch_stride), &a.tmap, 0, kchunks / 2 + c, 0, -3, n_img0, sbar);
+          const int nbox = g.tma_h0 == 0 ? g.ipc : 1;
+          const uint32_t box0 = g.tma_h0 == 0 ? (uint32_t)g.lead * 16 : 0u, boxstep = (uint32_t)g.rows_per_img * g.P * 16;
+          mbar_arrive_expect_tx(sbar, (uint32_t)((kchunks / 2) * nbox * g.P * g.tma_rows * 16));
+          for (int im = 0; im < nbox; ++im)
+            for (int c = 0; c < kchunks / 2; ++c)
+              tma_load_5d(smem_u32(strip + c * g.ch_stride) + box0 + im * boxstep, &a.tmap, 0, kchunks / 2 + c, 0, g.tma_h0,
+                          n_img0 + im, sbar);
           hh = 1;
         }
         mbar_wait(smem_u32(wempty + s), ph ^ 1);
@@ -683,11 +716,19 @@ int launch_conv(const float* x, const uint8_t* wp, const float* bias, float* y, 
     g = g2;
     g.nstages = nst2;
   } else if (wide) {
-    g = g2;                                              // one image per CTA
-    // (two-pass strips double the filter bytes in flight -- 9 stages instead of 5 -- but measured no faster on the wide
-    //  model, 189 vs 172 us for conv2's forward: the stream is not bound by its depth; kept behind B200_CONV_TWO_PASS=1)
-    static const bool two_pass_env = getenv("B200_CONV_TWO_PASS") && atoi(getenv("B200_CONV_TWO_PASS")) == 1;
-    g.two_pass = (two_pass_env && ksplit == 2 && g.tma_rows > 0) ? 1 : 0;
+    g = g2;                                              // one image per CTA ...
+    // ... or two, where the strip can be a TMA strip of half the channels at a time (256 channels, bf16 source): the
+    // filter stream -- 819 KB per CTA at ~9 B/clk per SM, what bounds these kernels -- then feeds twice the MMAs.
+    // (Two-pass strips alone, which only double the stages in flight, measured no faster: 189 vs 172 us for the wide
+    //  conv2 forward.  B200_CONV_WIDE_IPC=1 switches back to one image per CTA.)
+    static const int wide_ipc_env = getenv("B200_CONV_WIDE_IPC") ? atoi(getenv("B200_CONV_WIDE_IPC")) : 2;
+    if (ksplit == 2 && tma_ok && wide_ipc_env >= 2 && B >= 2) {
+      ConvGeom g3 = make_geom_tma(B, H, W, KC, NC, 0, 2);
+      if (g3.tiles * 64 <= 512 && (((kchunks / 2) * g3.ch_stride + 127) & ~127) + 3 * wtap + 256 <= 227 * 1024) {
+        g = g3;
+        g.two_pass = 1;
+      }
+    }
     const int strip_w = g.two_pass ? (((kchunks / 2) * g.ch_stride + 127) & ~127) : strip2;
     g.nstages = std::min(MAX_WSTAGES, (227 * 1024 - strip_w - 256 - extra) / wtap);
     B200_REQUIRE(g.nstages >= 2, "conv5x5_tc: image %dx%d with %d channels does not leave room for the filter ring", H, W, KC);
@@ -1099,7 +1140,18 @@ int wgrad_splits_tc(int B, int nblk = 1) {
   if (env < 0) { const char* e = getenv("B200_WGRAD2_SPLITS"); env = e ? atoi(e) : 0; }
   if (env > 0 && nblk == 1) return std::max(1, std::min(B, env));
   if (nblk == 1 && B <= kNumSMs) return std::max(1, std::min(B, (kNumSMs - (B + 1) / 2) / 5));
-  return std::max(1, std::min(B, (kNumSMs + 4) / (5 * nblk)));
+  if (nblk == 1) return std::max(1, std::min(B, (kNumSMs + 4) / 5));
+  // several 64 x 64 channel blocks (wide layers): 5 * nblk CTAs per split do not fill a wave by themselves (80 of 148 for
+  // 256 x 256 channels), so the splits are chosen by a small cost model -- waves x (images per CTA x 3.6k cycles measured
+  // per image + 10k cycles of set-up and epilogue) + 2k cycles of partial-sum traffic per split
+  int best = 1;
+  long best_cost = -1;
+  for (int s = 1; s <= std::min(B, 16); ++s) {
+    const long waves = (5L * nblk * s + kNumSMs - 1) / kNumSMs;
+    const long cost = waves * (((B + s - 1) / s) * 3600L + 10000L) + 2000L * s;
+    if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = s; }
+  }
+  return best;
 }
 }  // namespace
 
