@@ -322,6 +322,10 @@ def main():
     eng.init_params(0)
     params0 = eng.params.clone()
     ex.broadcast_params_(eng.params)
+    if fused and ex.overlap and args.model == "base":
+        ex.bind(eng)                   # inbox of the one-shot conv-gradient exchange (collective, outside any capture)
+        if ex._inbox is not None:
+            exchange += "-push"
 
     rng = np.random.default_rng(1234 + rank)
     POOL, RING = 16, 8

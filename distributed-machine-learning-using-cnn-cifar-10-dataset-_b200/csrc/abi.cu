@@ -50,6 +50,8 @@ struct b200_model {
   cudaStream_t side[2] = {nullptr, nullptr};
   cudaEvent_t ev_fork[2] = {nullptr, nullptr}, ev_join[2] = {nullptr, nullptr}, ev_aux[2] = {nullptr, nullptr};
   const uint8_t* last_images = nullptr;   // records of the last forward (the fused conv1 gradient re-reads them)
+  // inbox of the one-shot conv-gradient exchange (b200_p2p_set_inbox), or null
+  float* inbox_local = nullptr; void* inbox_mc = nullptr; void* inbox_peers[8] = {}; int64_t inbox_floats = 0;
   // per-launch-site timing (b200_profile_step): events are created lazily, once
   bool profiling = false;
   std::vector<std::string> site_names;
@@ -552,6 +554,13 @@ static int backward_impl(b200_handle h, void* stream, const P2PCtx* px, bool def
                               px->rank, px->world, h->p_total - off, px->lr, px->scale, st, off, 0, 0));
       // (conv1's gradient partials are summed by the exchange kernel's first CTAs: no reduction launch in between)
       const bool red = fused1 && !h->profiling && h->p_off[P_W1] == 0 && h->p_off[P_B1] == 4800;
+      if (h->inbox_local && h->inbox_floats >= 2 * px->world * off && fork)
+        // one-shot: push the conv gradients into every worker's inbox, one flag wait, local rank-ordered sum + update
+        SITE("p2p_conv_update", p2p_push_sum_sgd(h->grads, h->params, h->inbox_local, h->inbox_mc, h->inbox_peers,
+                                                 px->peer_pads, px->state, px->rank, px->world, off, px->lr, px->scale, st,
+                                                 1, red ? scratch : nullptr, red ? conv1_wgrad_tc_partials(c.batch) : 0,
+                                                 red ? 4864 : 0));
+      else
       SITE("p2p_conv_update", p2p_allreduce_sgd(px->peer_grads, px->peer_params, px->peer_pads, px->mc_grads,
                                                 px->mc_params, px->state, px->rank, px->world, off, px->lr, px->scale,
                                                 st, 0, 1, 0, red ? scratch : nullptr,
@@ -595,6 +604,20 @@ int b200_train_step_p2p(b200_handle h, const uint8_t* images, const int32_t* lab
   TRY(forward_impl(h, images, labels, stream, true));
   const P2PCtx px{peer_grads, peer_params, peer_pads, mc_grads, mc_params, state, rank, world, lr, grad_scale};
   return backward_impl(h, stream, &px);
+}
+
+int b200_p2p_set_inbox(b200_handle h, void* inbox_local, void* inbox_mc, void* const* inbox_peers, int32_t world,
+                       int64_t inbox_floats) {
+  B200_REQUIRE(h, "null handle");
+  if (!inbox_local) { h->inbox_local = nullptr; h->inbox_floats = 0; return B200_OK; }
+  B200_REQUIRE(inbox_peers && world >= 2 && world <= 8 && inbox_floats > 0 && ((uintptr_t)inbox_local & 15) == 0,
+               "p2p_set_inbox: bad argument");
+  h->inbox_local = (float*)inbox_local; h->inbox_mc = inbox_mc; h->inbox_floats = inbox_floats;
+  for (int p = 0; p < world; ++p) {
+    B200_REQUIRE(inbox_peers[p], "p2p_set_inbox: null peer pointer for rank %d", p);
+    h->inbox_peers[p] = inbox_peers[p];
+  }
+  return B200_OK;
 }
 
 int b200_train_step_p2p_single(b200_handle h, const uint8_t* images, const int32_t* labels, const void* const* peer_grads,

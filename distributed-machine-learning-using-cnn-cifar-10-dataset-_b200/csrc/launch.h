@@ -123,6 +123,11 @@ int p2p_allreduce_sgd(const void* const* peer_grads, void* const* peer_params, v
                       // (optional) the first red_n floats of this rank's range still sit in red_S partials [red_S][red_n]:
                       // summed (fixed order) by the kernel's first CTAs before it tells the peers "ready"
                       const float* red_part = nullptr, int red_S = 0, int red_n = 0);
+// one-shot exchange of a small range: push into every rank's inbox, one flag wait, local rank-ordered sum + update
+// (p2p_update.cu); inbox = [2][world][n] floats of symmetric memory per rank
+int p2p_push_sum_sgd(float* grads, float* params, const float* inbox_local, void* inbox_mc, void* const* inbox_peers,
+                     void* const* peer_pads, uint32_t* state, int rank, int world, int64_t n, float lr, float scale,
+                     cudaStream_t st, int channel, const float* red_part = nullptr, int red_S = 0, int red_n = 0);
 bool conv1_tc_supported(int H, int W, int c_in, int c1);
 int conv1_pool_fwd_tc(const uint8_t* img, const float* w, const float* bias, float* pool, uint8_t* arg,
                       float* conv_dbg, int B, int ih, int iw, int H, int W, cudaStream_t st,

@@ -179,6 +179,94 @@ __global__ void __launch_bounds__(512) p2p_allreduce_sgd_kernel(P2PArgs a) {
     if (tid == 0) { a.state[1] = 0; a.state[2] = 0; a.state[0] = epoch; }
   }
 }
+// ---------------------------------------------------------------------------------------------------------------------
+// One-shot variant for a SMALL range that is exposed at the end of the step (the conv gradients, 10 % of the buffer):
+// every rank PUSHES its gradients into an inbox slot on every rank, tells them so, waits for the others' pushes and
+// sums the slots of its own inbox in rank order (identical on all ranks) into its own parameters.  One flag wait instead
+// of two barriers and no remote reads or parameter writes: a rank is done as soon as the last peer's push has landed.
+//   inbox: [2 parities][world slots][n floats] of symmetric memory per rank.  A slot of parity p is rewritten two steps
+//   later, which a peer can only do after this rank has published its flag of the step in between, i.e. after it has
+//   finished reading this one -- so two parities make a trailing "done" barrier unnecessary.
+// The first red_ctas CTAs compute the fixed-order sums of conv1's per-CTA partials for the head of the range themselves
+// (and store them to the local gradient buffer), so nothing waits for a reduction launch.
+struct PushArgs {
+  float* grads;                     // local flat gradient buffer (range start)
+  float* params;                    // local flat parameter buffer (range start)
+  const float* inbox_local;         // this rank's inbox
+  float* inbox_mc;                  // multicast mapping of all inboxes, or null
+  float* inbox_peers[kMaxRanks];    // every rank's inbox (peer stores when there is no multicast mapping)
+  uint32_t* pads[kMaxRanks];        // flag pads of this channel: slot r = "rank r has pushed epoch e"
+  uint32_t* state;                  // local: [0] epoch, [1] CTAs finished, [3] CTAs that have pushed
+  const float* red_part; int red_S, red_n, red_ctas;
+  int rank, world;
+  int64_t n;                        // floats in the range, a multiple of 4
+  float step;
+  long long timeout_cycles;
+  int trace_id;
+};
+__global__ void __launch_bounds__(512) p2p_push_sum_sgd_kernel(PushArgs a) {
+  B200_TRACE_SCOPE(a.trace_id);
+  const int tid = threadIdx.x;
+  const uint32_t epoch = a.state[0] + 1;
+  const int64_t n4 = a.n >> 2;
+  float* my_slot_mc = a.inbox_mc ? a.inbox_mc + ((int64_t)(epoch & 1) * a.world + a.rank) * a.n : nullptr;
+  const int64_t slot_off = ((int64_t)(epoch & 1) * a.world + a.rank) * a.n;
+  auto push = [&](int64_t i4, const float4& v) {
+    if (my_slot_mc) mc_st(my_slot_mc + i4 * 4, v);
+    else
+      for (int p = 0; p < a.world; ++p) *reinterpret_cast<float4*>(a.inbox_peers[p] + slot_off + i4 * 4) = v;
+  };
+  // ---- 1: push my gradients (the head of the range straight out of the partial sums) ----------------------------
+  const int64_t red4 = a.red_ctas > 0 ? a.red_n >> 2 : 0;
+  if ((int)blockIdx.x < a.red_ctas) {
+    const int t = blockIdx.x * blockDim.x + tid;
+    const int g4 = min(t >> 5, (int)red4 - 1);
+    const float4 s = warp_sum_partials(a.red_part, a.red_S, a.red_n, g4 * 4, t & 31);
+    if ((t & 31) == 0 && (t >> 5) < red4) {
+      *reinterpret_cast<float4*>(a.grads + g4 * 4) = s;
+      push(g4, s);
+    }
+  } else {
+    const int nb = gridDim.x - a.red_ctas;
+    for (int64_t i = red4 + (int64_t)(blockIdx.x - a.red_ctas) * blockDim.x + tid; i < n4; i += (int64_t)nb * blockDim.x)
+      push(i, *reinterpret_cast<const float4*>(a.grads + i * 4));
+  }
+  // ---- 2: "pushed": the last CTA to get here tells every rank (its own included) ---------------------------------
+  __syncthreads();
+  __shared__ bool last;
+  if (tid == 0) {
+    __threadfence_system();
+    last = atomicAdd(a.state + 3, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (last && tid < a.world) {
+    __threadfence_system();
+    st_flag(a.pads[tid] + a.rank, epoch);
+  }
+  // ---- 3: all pushes of this step have landed here ------------------------------------------------------------------
+  if (tid < a.world) wait_flag(a.pads[a.rank] + tid, epoch, a.timeout_cycles);
+  __syncthreads();
+  // ---- 4: sum the slots in rank order, update -------------------------------------------------------------------------
+  const float* in = a.inbox_local + (int64_t)(epoch & 1) * a.world * a.n;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + tid; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    float4 v[kMaxRanks];
+#pragma unroll
+    for (int p = 0; p < kMaxRanks; ++p)
+      if (p < a.world) v[p] = __ldcg(reinterpret_cast<const float4*>(in + (int64_t)p * a.n) + i);
+    float4 g = v[0];
+#pragma unroll
+    for (int p = 1; p < kMaxRanks; ++p)
+      if (p < a.world) { g.x += v[p].x; g.y += v[p].y; g.z += v[p].z; g.w += v[p].w; }
+    float4 w = *reinterpret_cast<const float4*>(a.params + i * 4);
+    w.x = fmaf(-a.step, g.x, w.x); w.y = fmaf(-a.step, g.y, w.y);
+    w.z = fmaf(-a.step, g.z, w.z); w.w = fmaf(-a.step, g.w, w.w);
+    *reinterpret_cast<float4*>(a.params + i * 4) = w;
+  }
+  // ---- 5: the last CTA to finish resets the counters and advances the epoch -------------------------------------------
+  __syncthreads();
+  if (tid == 0 && atomicAdd(a.state + 1, 1u) == gridDim.x - 1) { a.state[1] = 0; a.state[3] = 0; __threadfence(); a.state[0] = epoch; }
+}
+
 long long flag_timeout_cycles() {
   static long long cycles = 0;
   if (!cycles) {
@@ -193,6 +281,36 @@ long long flag_timeout_cycles() {
 }
 }  // namespace
 B200_TRACE_SETTER(trace_set_p2p)
+
+int p2p_push_sum_sgd(float* grads, float* params, const float* inbox_local, void* inbox_mc, void* const* inbox_peers,
+                     void* const* peer_pads, uint32_t* state, int rank, int world, int64_t n, float lr, float scale,
+                     cudaStream_t st, int channel, const float* red_part, int red_S, int red_n) {
+  B200_REQUIRE(world >= 2 && world <= kMaxRanks && rank >= 0 && rank < world, "p2p_push_sum_sgd: bad rank %d / world %d", rank, world);
+  B200_REQUIRE(grads && params && inbox_local && inbox_peers && peer_pads && state && n > 0 && n % 4 == 0,
+               "p2p_push_sum_sgd: bad argument");
+  PushArgs a{};
+  a.grads = grads; a.params = params; a.inbox_local = inbox_local; a.inbox_mc = (float*)inbox_mc;
+  for (int p = 0; p < world; ++p) {
+    B200_REQUIRE(inbox_peers[p] && peer_pads[p], "p2p_push_sum_sgd: null peer pointer for rank %d", p);
+    a.inbox_peers[p] = (float*)inbox_peers[p];
+    a.pads[p] = (uint32_t*)peer_pads[p] + 16 * channel;
+  }
+  a.state = state + 4 * channel; a.rank = rank; a.world = world; a.n = n; a.step = lr * scale;
+  a.timeout_cycles = flag_timeout_cycles();
+  a.trace_id = channel == 0 ? TR_P2P_FC : TR_P2P_CONV;
+  int grid = (int)std::min<int64_t>(kNumSMs, (n / 4 + 511) / 512);
+  if (red_part) {
+    B200_REQUIRE(red_S > 0 && red_n > 0 && red_n % 4 == 0 && red_n <= n && ((uintptr_t)red_part & 15) == 0,
+                 "p2p_push_sum_sgd: bad partial range");
+    a.red_part = red_part; a.red_S = red_S; a.red_n = red_n;
+    a.red_ctas = (red_n / 4 * 32 + 511) / 512;
+    grid = std::min(kNumSMs, a.red_ctas + std::max(1, (int)(((n - red_n) / 4 + 511) / 512)));
+    B200_REQUIRE(grid > a.red_ctas, "p2p_push_sum_sgd: partial range too large");
+  }
+  p2p_push_sum_sgd_kernel<<<grid, 512, 0, st>>>(a);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
 
 int p2p_allreduce_sgd(const void* const* peer_grads, void* const* peer_params, void* const* peer_pads,
                       const void* mc_grads, void* mc_params, uint32_t* state, int rank, int world, int64_t total,

@@ -78,6 +78,7 @@ class P2PExchange(GradientExchange):
         if self.world > 8 or total_floats % (4 * self.world):
             raise ValueError("P2PExchange supports 2..8 workers and sizes divisible by 4*world")
         import ctypes as C
+        import os
         import torch.distributed._symmetric_memory as symm_mem
         grp = group if group is not None else dist.group.WORLD
         self.grads = symm_mem.empty(total_floats, dtype=torch.float32, device=device)
@@ -99,6 +100,10 @@ class P2PExchange(GradientExchange):
         self.multicast = bool(mc_ok and self._hg.multicast_ptr and self._hp.multicast_ptr)
         self._mc_grads = int(self._hg.multicast_ptr) if self.multicast else None
         self._mc_params = int(self._hp.multicast_ptr) if self.multicast else None
+        # inbox of the one-shot conv-gradient exchange (second flag channel): [2 parities][world][conv range] floats
+        self._inbox = None                                # allocated by bind(), once the engine's conv range is known
+        self._grp = grp
+        self._device = device
         self._state = torch.zeros(8, dtype=torch.int32, device=device)      # (epoch, arrivals, reducers done, -) per flag channel
         # Overlapping the exchange with the backward pass costs a second pair of flag barriers.  Measured (whole step,
         # batch 128/GPU, L2 flushed): 2 GPUs 140 us; 4 GPUs 142 us overlapped vs 148 us as one kernel at the end; 8 GPUs
@@ -109,6 +114,33 @@ class P2PExchange(GradientExchange):
         self.overlap = (True if env is None else env == "1") if overlap is None else bool(overlap)
         torch.cuda.synchronize(device)
         dist.barrier(group=group)
+
+    INBOX_MAX_FLOATS = 1 << 18       # 1 MB of conv gradients (the script's widths: 107,392 floats)
+
+    def bind(self, engine):
+        """Give `engine` (built on self.params / self.grads) the inbox of the one-shot conv-gradient exchange: 2 x world x
+        (offset of full_weight_1) floats of symmetric memory.  Collective: every worker calls it once."""
+        import ctypes as C
+        import os
+        import torch.distributed._symmetric_memory as symm_mem
+        from ._lib import check
+        if getattr(engine, "_inbox_bound", False) or os.environ.get("B200CNN_INBOX", "1") != "1":
+            return
+        n_conv = int(engine.offsets[4])                  # full_weight_1 starts where the conv tensors end
+        if n_conv > self.INBOX_MAX_FLOATS:               # every rank receives world x the range: only pays while it is small
+            engine._inbox_bound = True
+            return
+        floats = 2 * self.world * n_conv
+        self._inbox = symm_mem.empty(floats, dtype=torch.float32, device=self._device)
+        self._inbox.zero_()
+        hi = symm_mem.rendezvous(self._inbox, self._grp)
+        arr = (C.c_void_p * self.world)(*[int(x) for x in hi.buffer_ptrs])
+        mc = int(hi.multicast_ptr) if (self.multicast and hi.has_multicast_support and hi.multicast_ptr) else None
+        self._inbox_handle, self._inbox_peers = hi, arr
+        check(engine.lib.b200_p2p_set_inbox(engine.h, self._inbox.data_ptr(), mc, arr, self.world, floats))
+        engine._inbox_bound = True
+        torch.cuda.synchronize(self._device)
+        dist.barrier(group=self.group)
 
     def apply_(self, engine, lr):
         """allreduce + update in one launch on the current stream (replaces allreduce_ + engine.sgd_apply)."""
@@ -122,6 +154,8 @@ class P2PExchange(GradientExchange):
         kernels (b200_train_step_p2p); same result as engine.forward_backward(...) followed by apply_(engine, lr)."""
         from ._lib import check
         engine._check_inputs(images, labels)
+        if self.overlap:
+            self.bind(engine)
         fn = engine.lib.b200_train_step_p2p if self.overlap else engine.lib.b200_train_step_p2p_single
         check(fn(engine.h, images.data_ptr(), labels.data_ptr(), self._peer_grads,
                                              self._peer_params, self._peer_pads, self._mc_grads, self._mc_params,

@@ -113,6 +113,15 @@ int b200_p2p_sgd_apply(b200_handle h, const void* const* peer_grads, void* const
 int b200_train_step_p2p(b200_handle h, const uint8_t* images, const int32_t* labels, const void* const* peer_grads,
                         void* const* peer_params, void* const* peer_pads, const void* mc_grads, void* mc_params,
                         uint32_t* state, int32_t rank, int32_t world, float lr, float grad_scale, void* stream);
+/* Optional inbox for b200_train_step_p2p's SECOND channel (the conv gradients, exposed at the end of the step): with
+ * it that channel runs as a one-shot exchange -- every worker pushes its conv gradients into a slot of every worker's
+ * inbox (multimem.st through inbox_mc when given, peer stores otherwise), publishes one flag, waits for the others'
+ * flags and sums the slots in rank order into its OWN parameters: one flag wait instead of two barriers, no remote
+ * reads.  inbox_local: this worker's inbox, inbox_floats >= 2 * world * (offset of full_weight_1) floats of symmetric
+ * memory, zero-initialised; inbox_peers: host array of `world` device pointers to every worker's inbox.  NULL
+ * inbox_local switches back to the two-barrier kernel.  No counterpart in the reference (its gRPC runtime did this). */
+int b200_p2p_set_inbox(b200_handle h, void* inbox_local, void* inbox_mc, void* const* inbox_peers, int32_t world,
+                       int64_t inbox_floats);
 /* The same step with the exchange as ONE kernel at the end (b200_forward_backward + b200_p2p_sgd_apply in one call;
  * state = 16 zero-initialised bytes, pads >= 64 B): what eight workers use, where a second pair of flag barriers costs
  * more than overlapping the FC gradients saves.  conv1's gradient partials are summed inside the exchange kernel. */
