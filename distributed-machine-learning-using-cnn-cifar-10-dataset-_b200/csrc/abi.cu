@@ -612,11 +612,9 @@ int b200_p2p_set_inbox(b200_handle h, void* inbox_local, void* inbox_mc, void* c
   if (!inbox_local) { h->inbox_local = nullptr; h->inbox_floats = 0; return B200_OK; }
   B200_REQUIRE(inbox_peers && world >= 2 && world <= 8 && inbox_floats > 0 && ((uintptr_t)inbox_local & 15) == 0,
                "p2p_set_inbox: bad argument");
+  for (int p = 0; p < world; ++p) B200_REQUIRE(inbox_peers[p], "p2p_set_inbox: null peer pointer for rank %d", p);
+  for (int p = 0; p < world; ++p) h->inbox_peers[p] = inbox_peers[p];
   h->inbox_local = (float*)inbox_local; h->inbox_mc = inbox_mc; h->inbox_floats = inbox_floats;
-  for (int p = 0; p < world; ++p) {
-    B200_REQUIRE(inbox_peers[p], "p2p_set_inbox: null peer pointer for rank %d", p);
-    h->inbox_peers[p] = inbox_peers[p];
-  }
   return B200_OK;
 }
 

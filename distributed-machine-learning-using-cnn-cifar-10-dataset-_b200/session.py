@@ -200,6 +200,8 @@ class _GraphStep:
         self.pending = [None, None]
         self.used = [False, False]
         self.i = 0
+        if exchange.world > 1 and not self.stale_k and getattr(exchange, "overlap", False) and hasattr(exchange, "bind"):
+            exchange.bind(eng)              # inbox of the one-shot conv-gradient exchange (collective; outside the capture)
         # capturing runs the step once eagerly (library side streams are created then) and once more under
         # capture-time validation: keep the variables as they were
         keep = eng.params.clone()

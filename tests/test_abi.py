@@ -73,3 +73,23 @@ def test_p2p_step_validates_its_tables_without_gpu():
     rc = lib.b200_train_step_p2p(h, None, None, None, None, None, None, None, None, 0, 2, 0.1, 1.0, None)
     assert rc != 0
     lib.b200_destroy(h)
+
+
+def test_p2p_inbox_setter_validates_its_arguments_without_gpu():
+    """b200_p2p_set_inbox (inbox of the one-shot conv-gradient exchange) stores pointers only: null handle, bad world
+    size, missing peer table and a null peer entry are rejected; a null inbox switches the two-barrier kernel back on."""
+    lib = _lib.load()
+    assert lib.b200_p2p_set_inbox(None, None, None, None, 2, 0) != 0
+    h = C.c_void_p()
+    cfg = _lib.Config(128, 32, 32, 24, 24, 3, 64, 64, 384, 192, 10, 1)
+    assert lib.b200_create(C.byref(cfg), C.byref(h)) == 0
+    peers = (C.c_void_p * 2)(4096, 8192)
+    assert lib.b200_p2p_set_inbox(h, 4096, None, peers, 2, 1 << 20) == 0
+    assert lib.b200_p2p_set_inbox(h, None, None, None, 0, 0) == 0             # back to the two-barrier kernel
+    assert lib.b200_p2p_set_inbox(h, 4096, None, None, 2, 1 << 20) == _lib.E_INVALID
+    assert lib.b200_p2p_set_inbox(h, 4096, None, peers, 9, 1 << 20) == _lib.E_INVALID
+    assert lib.b200_p2p_set_inbox(h, 4100, None, peers, 2, 1 << 20) == _lib.E_INVALID   # misaligned
+    peers[1] = None
+    assert lib.b200_p2p_set_inbox(h, 4096, None, peers, 2, 1 << 20) == _lib.E_INVALID
+    assert b"rank 1" in lib.b200_last_error()
+    lib.b200_destroy(h)
