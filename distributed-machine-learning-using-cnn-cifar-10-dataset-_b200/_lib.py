@@ -70,7 +70,7 @@ def load():
     global _lib
     if _lib is not None:
         return _lib
-    path = _build.build()
+    path = os.environ.get("B200CNN_LIB") or _build.build()      # (diagnostics: a B200_TRACE=1 build kept beside the product library)
     lib = C.CDLL(path)
     for ret, name, types in declared_functions():
         fn = getattr(lib, name)

@@ -32,6 +32,12 @@ for cold in (0, 1):
     t = t[t[:, 1] > 0] if False else t
     t0 = t[t[:, 1] > 0, 0].min()
     print("cold" if cold else "hot", "step: %.1f us from first start to last end" % ((t[:, 1].max() - t0) / 1e3))
+    tt = tl.cpu().numpy()
+    print("  [%s] conv2 dgrad CTA0: zeroed %d filled %d mma_start %d mma_issued %d accum_ready %d epilogue_done %d" % (("cold" if cold else "hot",) + tuple(tt[1:7] - tt[0])))
+    print("  [%s] conv2 wgrad CTA0: zeroed %d img0 %d all_filled %d accum_ready %d epilogue_done %d" % (("cold" if cold else "hot",) + tuple(tt[9:14] - tt[8])))
+    print("  [%s] conv1 wgrad CTA0: staged+xstrip %d gathered %d accum_ready %d epilogue_done %d" % (("cold" if cold else "hot",) + tuple(tt[26:30] - tt[25])))
+    print("  [%s] conv1 fwd CTA0: strip+filter ready %d accum_ready %d conv tile in smem %d" % ("cold" if cold else "hot", tt[15]-tt[14], tt[30]-tt[14], tt[31]-tt[14]))
+    print("  [%s] tail rows phases:" % ("cold" if cold else "hot"), (tt[17:25] - tt[16:24]).tolist())
     for i in np.argsort(t[:, 0]):
         if t[i, 1] <= 0: continue
         print("  %-13s start %7.1f  end %7.1f  (%5.1f us)" % (names[i], (t[i, 0] - t0) / 1e3, (t[i, 1] - t0) / 1e3, (t[i, 1] - t[i, 0]) / 1e3))
