@@ -316,7 +316,12 @@ struct Conv1WgradArgs {
   long long* timeline;    // diagnostics: clock64 stamps of CTA 0 in slots [25,31) of the timeline buffer, or null
 };
 
-__global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
+// NW worker threads build the strips (the gather is ALU- and latency-bound: with 8 warps it issued on a third of the
+// cycles, and a band's 384 items per parity class left half of a second round idle); warps NW/32 .. NW/32+4 issue MMAs
+template <int NW>
+__global__ void __launch_bounds__(NW + 160, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
+  constexpr int WORKERS = NW, MMA0 = NW / 32;
+  auto workers_sync = [] { asm volatile("bar.sync 1, %0;" ::"n"(NW) : "memory"); };
   B200_TRACE_SCOPE(TR_CONV1_WGRAD);
   const C1Geom& g = a.g;
   extern __shared__ __align__(128) uint8_t smem[];
@@ -348,14 +353,14 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
     mbar_init(smem_u32(staged), 1);
     fence_mbar_init();
   }
-  if (warp == 8) tmem_alloc(smem_u32(tmem_slot), 512);
+  if (warp == MMA0) tmem_alloc(smem_u32(tmem_slot), 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
 
   const bool stamp = a.timeline && blockIdx.x == 0 && tid == 0;
-  if (warp < 8) {
+  if (warp < MMA0) {
     if (stamp) a.timeline[25] = clock64();
     for (int o = tid * 16; o < 8 * ch_stride; o += WORKERS * 16) *reinterpret_cast<uint4*>(ds + o) = make_uint4(0, 0, 0, 0);
     const int pth = max((g.OH - 1) * 2 + 3 - g.H, 0), ptw = max((g.OW - 1) * 2 + 3 - g.W, 0);
@@ -405,8 +410,9 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
       mbar_wait(smem_u32(staged), it & 1);
       // ReluGrad mask (the selected cell is > 0 iff pool1 > 0) and the [half][chunk] order pool_grad_px reads, in
       // place: a batch is read into registers, then written (the permutation stays inside a cell's 16 float4)
-      constexpr int MB = 9;
-      for (int q0 = tid; q0 < ncell * 16; q0 += MB * WORKERS) {
+      constexpr int MB = NW >= 512 ? 5 : 9;
+      for (int base = 0; base < ncell * 16; base += MB * WORKERS) {      // (uniform trip count: the loop holds a barrier)
+        const int q0 = base + tid;
         float4 dreg[MB];
 #pragma unroll
         for (int k = 0; k < MB; ++k) {
@@ -469,9 +475,9 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
     tc_fence_before();
     if (stamp) a.timeline[29] = clock64();
   } else {
-    // warps 8..12: one issuing thread per filter row di (own accumulator each)
+    // five warps: one issuing thread per filter row di (own accumulator each)
     if (lane == 0) {
-      const int di = warp - 8;
+      const int di = warp - MMA0;
       const uint32_t idesc = make_idesc(64, 40, true, true);
       const uint32_t d_hi = desc_hi(ch_stride), x_hi = desc_hi(16);     // x: N-group stride = one pixel slot
       const uint32_t d_lo0 = desc_lo(smem_u32(ds) + g.lead * 16, 128);
@@ -499,7 +505,7 @@ __global__ void __launch_bounds__(416, 1) conv1_wgrad_kernel(Conv1WgradArgs a) {
     __syncwarp();
   }
   __syncthreads();
-  if (warp == 8) {
+  if (warp == MMA0) {
     tc_fence_after();
     tmem_dealloc(tmem, 512);
   }
@@ -563,14 +569,18 @@ int conv1_wgrad_tc(const uint8_t* img, const float* dpool, const float* pool, co
   C1Geom g = make_c1geom(B, ih, iw, H, W);
   const size_t smem = conv1_wgrad_smem(g);
   B200_REQUIRE(smem <= 227 * 1024, "conv1_wgrad_tc: crop %dx%d needs %zu bytes of shared memory", H, W, smem);
+  static const int nw = getenv("B200_WGRAD1_WORKERS") ? atoi(getenv("B200_WGRAD1_WORKERS")) : 512;      // experiments: 256
   static PerDeviceOnce attr;
-  if (attr.first())
-    B200_CUDA_TRY(cudaFuncSetAttribute(conv1_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  if (attr.first()) {
+    B200_CUDA_TRY(cudaFuncSetAttribute(conv1_wgrad_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    B200_CUDA_TRY(cudaFuncSetAttribute(conv1_wgrad_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  }
   const int S = conv1_wgrad_ctas(B);
   Conv1WgradArgs a{img, dpool, pool, arg, scratch, g, C1, g_conv1_timeline};
   const bool overlap = g_pdl_next;
   g_pdl_next = false;
-  B200_CUDA_TRY(launch_kernel(conv1_wgrad_kernel, dim3(S, C1 / 64), dim3(416), smem, st, a));
+  if (nw == 256) B200_CUDA_TRY(launch_kernel(conv1_wgrad_kernel<256>, dim3(S, C1 / 64), dim3(256 + 160), smem, st, a));
+  else B200_CUDA_TRY(launch_kernel(conv1_wgrad_kernel<512>, dim3(S, C1 / 64), dim3(512 + 160), smem, st, a));
   if (defer_reduce) return B200_OK;
   g_pdl_next = overlap;                                   // (the reduction's prologue may overlap the kernel's tail)
   if (C1 != 64) {
