@@ -27,7 +27,6 @@ namespace b200 {
 using namespace tc;
 
 namespace {
-constexpr int WORKERS = 256;   // 8 warps stage / epilogue; warp 8 issues MMAs
 
 struct C1Geom {
   int B, ih, iw, H, W;     // batch, record image size, crop size
@@ -44,7 +43,6 @@ __host__ inline C1Geom make_c1geom(int B, int ih, int iw, int H, int W) {
   g.OH = (H + 1) / 2; g.OW = (W + 1) / 2;
   return g;
 }
-__device__ __forceinline__ void workers_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
 // one 16-byte slot: channels 0..2 = the pixel's bytes, channel 3 = `c3`, channels 4..7 = 0
 __device__ __forceinline__ uint4 pixel_chunk(const uint8_t* __restrict__ rec, int ih, int iw, int y, int x, float c3) {
@@ -71,7 +69,12 @@ constexpr int kWLbo = 64 * 16 + 16;      // B operand: [26 k-chunks][64 cout][16
 long long* g_conv1_timeline = nullptr;      // diagnostics (b200_debug_conv_timeline)
 constexpr int kConvRow = 68;             // floats per conv-output row in smem (64 + 4: conflict-free STS.128)
 
-__global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) {
+// NW worker threads stage the strip / filter and move the conv tile out of TMEM; warps NW/32 .. NW/32+2 issue MMAs; all
+// warps run the pool scan (280 instructions per item of four channels, most of them selects / integer compares)
+template <int NW>
+__global__ void __launch_bounds__(NW + 96, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) {
+  constexpr int WORKERS = NW, MMA0 = NW / 32;
+  auto workers_sync = [] { asm volatile("bar.sync 1, %0;" ::"n"(NW) : "memory"); };
   B200_TRACE_SCOPE(TR_CONV1_FWD);
   pdl_launch_dependents();
   const C1Geom& g = a.g;
@@ -95,14 +98,14 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
     for (int t = 0; t < 8; ++t) mbar_init(smem_u32(accum + t), 1);
     fence_mbar_init();
   }
-  if (warp == 8) tmem_alloc(smem_u32(tmem_slot), tmem_cols);
+  if (warp == MMA0) tmem_alloc(smem_u32(tmem_slot), tmem_cols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
 
   const bool stamp = a.timeline && blockIdx.x == 0 && tid == 0;
-  if (warp < 8) {
+  if (warp < MMA0) {
     if (stamp) a.timeline[14] = clock64();
     for (int o = tid * 16; o < strip_bytes; o += WORKERS * 16) *reinterpret_cast<uint4*>(strip + o) = make_uint4(0, 0, 0, 0);
     workers_sync();
@@ -110,9 +113,10 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
     const int oy = (g.ih - g.H) / 2, ox = (g.iw - g.W) / 2;
     // Every global load of this phase (the thread's <= PXB pixels x 3 planes and its <= WB filter chunks x 3
     // channels) is issued before the first conversion: one memory round trip instead of one per item.
-    constexpr int PXB = 3, WB = 7;                       // 3 * 256 >= 24 * 24 pixels, 7 * 256 >= 26 * 64 chunks
+    constexpr int PXB = NW >= 512 ? 2 : 3, WB = NW >= 512 ? 4 : 7;      // PXB * NW >= 24 * 24 pixels, WB * NW >= 26 * 64 chunks
     const int plane = g.ih * g.iw;
-    for (int q0 = tid; q0 < g.H * g.W; q0 += PXB * WORKERS) {
+    for (int base = 0; base < g.H * g.W; base += PXB * WORKERS) {      // (every thread runs the first round: the filter)
+      const int q0 = base + tid;
       uint8_t px[PXB][3];
       float wv[WB][3];
 #pragma unroll
@@ -122,7 +126,7 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
         const uint8_t* src = rec + (i + oy) * g.iw + (j + ox);
         px[u][0] = src[0]; px[u][1] = src[plane]; px[u][2] = src[2 * plane];
       }
-      const bool first = q0 == tid;                      // the filter rides along with the first pixel batch
+      const bool first = base == 0;                      // the filter rides along with the first pixel batch
       if (first) {
 #pragma unroll
         for (int u = 0; u < WB; ++u) {
@@ -158,10 +162,7 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
     if (stamp) a.timeline[15] = clock64();
 
     // ---- epilogue 1: TMEM -> +bias, ReLU -> fp32 conv tile in shared memory, tile by tile as the MMAs finish ----
-    float bv[64];
-#pragma unroll
-    for (int j = 0; j < 64; j += 4) *reinterpret_cast<float4*>(bv + j) = __ldg(reinterpret_cast<const float4*>(a.bias + nc0 + j));
-    for (int t = (warp >> 2); t < g.tiles; t += 2) {
+    for (int t = (warp >> 2); t < g.tiles; t += NW / 128) {
       mbar_wait(smem_u32(accum + t), 0);
       tc_fence_after();
       if (stamp && t == 0) a.timeline[30] = clock64();
@@ -174,15 +175,18 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
       for (int c0 = 0; c0 < 64; c0 += 32) {
         uint32_t v[32];
         tmem_ld32(tmem + ((uint32_t)((warp & 3) * 32) << 16) + t * 64 + c0, v);
+        float bv[32];                                    // (half of the bias at a time: registers)
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(bv + j) = __ldg(reinterpret_cast<const float4*>(a.bias + nc0 + c0 + j));
         tmem_ld_wait();
         if (valid) {
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
             float4 o;
-            o.x = fmaxf(__uint_as_float(v[j + 0]) + bv[c0 + j + 0], 0.f);
-            o.y = fmaxf(__uint_as_float(v[j + 1]) + bv[c0 + j + 1], 0.f);
-            o.z = fmaxf(__uint_as_float(v[j + 2]) + bv[c0 + j + 2], 0.f);
-            o.w = fmaxf(__uint_as_float(v[j + 3]) + bv[c0 + j + 3], 0.f);
+            o.x = fmaxf(__uint_as_float(v[j + 0]) + bv[j + 0], 0.f);
+            o.y = fmaxf(__uint_as_float(v[j + 1]) + bv[j + 1], 0.f);
+            o.z = fmaxf(__uint_as_float(v[j + 2]) + bv[j + 2], 0.f);
+            o.w = fmaxf(__uint_as_float(v[j + 3]) + bv[j + 3], 0.f);
             *reinterpret_cast<float4*>(row + c0 + j) = o;
             if (dbg) *reinterpret_cast<float4*>(dbg + c0 + j) = o;
           }
@@ -191,9 +195,9 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
     }
     tc_fence_before();
   } else {
-    // warps 8..10: three issuing threads, tiles t = w, w+3, ... each (13 MMAs per tile, one commit per tile)
+    // three warps with one issuing thread each: tiles t = w, w+3, ... (13 MMAs per tile, one commit per tile)
     if (lane == 0) {
-      const int w = warp - 8;
+      const int w = warp - MMA0;
       const uint32_t idesc = make_idesc(128, 64, false, false);
       mbar_wait(smem_u32(ready), 0);
       tc_fence_after();
@@ -216,7 +220,7 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
     }
     __syncwarp();
   }
-  __syncthreads();       // the conv tile is complete; all eleven warps pool it
+  __syncthreads();       // the conv tile is complete; all warps pool it
   if (stamp) a.timeline[31] = clock64();
   {
     // ---- epilogue 2: 3x3/2 SAME max-pool (pad 0 before / 1 after), first max in (h,w) scan order ---
@@ -265,7 +269,7 @@ __global__ void __launch_bounds__(352, 1) conv1_pool_fwd_kernel(Conv1FwdArgs a) 
     }
   }
   __syncthreads();
-  if (warp == 8) {
+  if (warp == MMA0) {
     tc_fence_after();
     tmem_dealloc(tmem, tmem_cols);
   }
@@ -285,11 +289,17 @@ int conv1_pool_fwd_tc(const uint8_t* img, const float* w, const float* bias, flo
   B200_REQUIRE(conv1_tc_supported(H, W, 3, C1), "conv1_pool_fwd_tc: crop %dx%d x %d channels is not supported", H, W, C1);
   C1Geom g = make_c1geom(B, ih, iw, H, W);
   const int smem = ((g.npix * 16 + 127) & ~127) + 26 * kWLbo + 64 + H * W * kConvRow * 4 + 256;
+  // (16 worker warps measured no faster than 8 here -- 0.1179 vs 0.1181 ms per step: the pool scan is bound by the
+  //  integer / select pipe, not by latency -- so the smaller CTA stays the default)
+  static const int nw = getenv("B200_CONV1_WORKERS") ? atoi(getenv("B200_CONV1_WORKERS")) : 256;
   static PerDeviceOnce attr;
-  if (attr.first())
-    B200_CUDA_TRY(cudaFuncSetAttribute(conv1_pool_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  if (attr.first()) {
+    B200_CUDA_TRY(cudaFuncSetAttribute(conv1_pool_fwd_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    B200_CUDA_TRY(cudaFuncSetAttribute(conv1_pool_fwd_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  }
   Conv1FwdArgs a{img, w, bias, pool, arg, reinterpret_cast<__nv_bfloat16*>(pool_bf16), conv_dbg, g, C1, g_conv1_timeline};
-  conv1_pool_fwd_kernel<<<dim3(B, C1 / 64), 352, smem, st>>>(a);
+  if (nw == 256) conv1_pool_fwd_kernel<256><<<dim3(B, C1 / 64), 256 + 96, smem, st>>>(a);
+  else conv1_pool_fwd_kernel<512><<<dim3(B, C1 / 64), 512 + 96, smem, st>>>(a);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
