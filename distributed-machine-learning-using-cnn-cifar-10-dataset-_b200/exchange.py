@@ -131,13 +131,17 @@ class P2PExchange(GradientExchange):
             engine._inbox_bound = True
             return
         floats = 2 * self.world * n_conv
-        self._inbox = symm_mem.empty(floats, dtype=torch.float32, device=self._device)
-        self._inbox.zero_()
-        hi = symm_mem.rendezvous(self._inbox, self._grp)
-        arr = (C.c_void_p * self.world)(*[int(x) for x in hi.buffer_ptrs])
-        mc = int(hi.multicast_ptr) if (self.multicast and hi.has_multicast_support and hi.multicast_ptr) else None
-        self._inbox_handle, self._inbox_peers = hi, arr
-        check(engine.lib.b200_p2p_set_inbox(engine.h, self._inbox.data_ptr(), mc, arr, self.world, floats))
+        if self._inbox is not None and self._inbox_floats != floats:
+            raise ValueError("P2PExchange.bind: engines of one exchange must have the same conv-gradient range")
+        if self._inbox is None:                          # (a second engine on this exchange shares the inbox: one step at a time)
+            self._inbox = symm_mem.empty(floats, dtype=torch.float32, device=self._device)
+            self._inbox.zero_()
+            hi = symm_mem.rendezvous(self._inbox, self._grp)
+            arr = (C.c_void_p * self.world)(*[int(x) for x in hi.buffer_ptrs])
+            mc = int(hi.multicast_ptr) if (self.multicast and hi.has_multicast_support and hi.multicast_ptr) else None
+            self._inbox_handle, self._inbox_peers, self._inbox_mc, self._inbox_floats = hi, arr, mc, floats
+        check(engine.lib.b200_p2p_set_inbox(engine.h, self._inbox.data_ptr(), self._inbox_mc, self._inbox_peers, self.world,
+                                            floats))
         engine._inbox_bound = True
         torch.cuda.synchronize(self._device)
         dist.barrier(group=self.group)
